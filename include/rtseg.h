@@ -1,0 +1,264 @@
+/*
+ * rtseg.h — C ABI of librtseg.so, the B200 (sm_100a) kernels behind the
+ * real-time-segmentation hot path.
+ *
+ * The reference (acai66/realtime-semantic-segmentation-pytorch) has no FFI
+ * layer at all: its hot path is `nn.Module.forward` of the blocks in
+ * models/modules.py, dispatched by PyTorch to ATen/cuDNN.  Every entry point
+ * below therefore cites the reference *module or function* whose arithmetic
+ * it replaces (file:line relative to the reference tree); the Python host in
+ * realtime-semantic-segmentation-pytorch_b200/ binds these symbols with
+ * ctypes and exposes them under the reference's own class names.
+ *
+ * Conventions
+ *  - plain C types only; every pointer is a DEVICE pointer unless its name
+ *    ends in `_host`; the caller owns all memory (inputs, outputs, scratch).
+ *  - activations are dense NHWC ("channels_last"); a tensor may be a channel
+ *    slice [c_off, c_off+c) of a wider NHWC buffer with `c_total` channels
+ *    per pixel (this is how concat / split are fused away).
+ *  - all work is enqueued on the `stream` argument (a cudaStream_t); nothing
+ *    synchronises, nothing uses the legacy default stream.
+ *  - return value: 0 on success, negative rtseg_status otherwise; the text is
+ *    available from rtseg_last_error() (thread local).  There is no CPU
+ *    fallback anywhere: an unsupported shape is an error.
+ */
+#ifndef RTSEG_H_
+#define RTSEG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTSEG_VERSION 100
+
+typedef void *rtseg_stream_t; /* cudaStream_t */
+
+typedef enum rtseg_status {
+  RTSEG_OK = 0,
+  RTSEG_ERR_INVALID = -1,     /* bad argument / inconsistent descriptor      */
+  RTSEG_ERR_UNSUPPORTED = -2, /* legal request this library has no kernel for */
+  RTSEG_ERR_CUDA = -3,        /* a CUDA runtime / driver call failed          */
+  RTSEG_ERR_ARCH = -4         /* device is not sm_100                         */
+} rtseg_status;
+
+typedef enum rtseg_dtype { RTSEG_F32 = 0, RTSEG_BF16 = 1 } rtseg_dtype;
+
+/* Activation hub of models/modules.py:111-131 (elementwise members only;
+ * 'glu' and 'softmax' are not pointwise and are rejected by the host). */
+typedef enum rtseg_act {
+  RTSEG_ACT_NONE = 0,
+  RTSEG_ACT_RELU = 1,
+  RTSEG_ACT_RELU6 = 2,
+  RTSEG_ACT_LEAKYRELU = 3, /* p0 = negative_slope                      */
+  RTSEG_ACT_PRELU = 4,     /* per-channel slope vector (`slope`)       */
+  RTSEG_ACT_ELU = 5,       /* p0 = alpha                               */
+  RTSEG_ACT_CELU = 6,      /* p0 = alpha                               */
+  RTSEG_ACT_SELU = 7,
+  RTSEG_ACT_HARDSWISH = 8,
+  RTSEG_ACT_HARDTANH = 9,  /* p0 = min_val, p1 = max_val               */
+  RTSEG_ACT_GELU = 10,     /* exact erf form                           */
+  RTSEG_ACT_SILU = 11,
+  RTSEG_ACT_SIGMOID = 12,
+  RTSEG_ACT_TANH = 13
+} rtseg_act;
+
+/* Where the residual tensor enters the epilogue
+ *   v = acc (+ res if PRE);  v = v*scale[c] + shift[c];  v = act(v);
+ *   (+ res if POST);  v = act2(v)
+ * PRE  = NonBt1DBlock, models/erfnet.py:77-82 (add, then BN, then act);
+ *        FeatureFusionModule, models/fastscnn.py:86-93.
+ * POST = InvertedResidual models/fastscnn.py:117-121, DABModule
+ *        models/dabnet.py:93-96, SSnbtUnit models/lednet.py:80-87 (act2). */
+typedef enum rtseg_res_mode { RTSEG_RES_NONE = 0, RTSEG_RES_PRE = 1, RTSEG_RES_POST = 2 } rtseg_res_mode;
+
+/* One fused "conv -> folded BatchNorm -> activation (-> residual)" layer. */
+typedef struct rtseg_conv_desc {
+  int32_t n, h, w;          /* input batch and spatial size                      */
+  int32_t cin, cout;        /* logical channels of this op                       */
+  int32_t kh, kw;           /* kernel size (3,1) / (1,3) / (3,3) / (1,1) / ...   */
+  int32_t stride;           /* applied to both dims, like nn.Conv2d(int)         */
+  int32_t dil;              /* applied to both dims                              */
+  int32_t pad_h, pad_w;
+  int32_t groups;           /* 1 = dense, cin = depthwise (cout = m*cin)         */
+  int32_t dtype;            /* rtseg_dtype of x, res and y                       */
+  int32_t act;              /* rtseg_act                                         */
+  float act_p0, act_p1;
+  int32_t res_mode;         /* rtseg_res_mode                                    */
+  int32_t act2;             /* second activation after a POST residual           */
+  int32_t x_ctotal, x_coff; /* x is channels [x_coff, x_coff+cin) of x_ctotal   */
+  int32_t y_ctotal, y_coff; /* y is channels [y_coff, y_coff+cout) of y_ctotal  */
+  int32_t r_ctotal, r_coff; /* residual slice (same spatial size as y)          */
+} rtseg_conv_desc;
+
+/* ---- library ---------------------------------------------------------- */
+int rtseg_version(void);
+const char *rtseg_last_error(void);
+/* 0 if the current device is a compute-capability 10.x part, else RTSEG_ERR_ARCH. */
+int rtseg_device_check(void);
+/* Make `device` current for this library's (statically linked) CUDA runtime on
+ * the calling thread; the Python host calls it when torch's device changes. */
+int rtseg_set_device(int device);
+/* Number of kernel launches this library has enqueued from the calling
+ * process since load (monotonic; bench.py reports the delta as gpu_launches). */
+uint64_t rtseg_launch_count(void);
+int rtseg_out_hw(const rtseg_conv_desc *d, int32_t *ho, int32_t *wo);
+
+/* ---- K1': depthwise conv + BN + act ------------------------------------
+ * Replaces DWConvBNAct, models/modules.py:46-59 (nn.Conv2d(groups=in) :55,
+ * nn.BatchNorm2d :57, Activation :58).  Any kh,kw in {1,3,5}, stride 1/2,
+ * dilation >= 1, channel multiplier m = cout/cin >= 1.
+ *   w      fp32 [kh][kw][cout]
+ *   scale, shift  fp32 [cout]  (BN folded: scale = g/sqrt(var+eps),
+ *                               shift = b - mean*scale + conv_bias*scale)
+ *   slope  fp32 [cout] or NULL (PReLU only)                               */
+int rtseg_conv_dw(const rtseg_conv_desc *d, const void *x, const float *w, const float *scale,
+                  const float *shift, const float *slope, const void *res, void *y,
+                  rtseg_stream_t stream);
+
+/* ---- K3'/K4' CUDA-core path: dense conv + BN + act ----------------------
+ * Replaces ConvBNAct, models/modules.py:73-85, PWConvBNAct :63-69, conv1x1 /
+ * conv3x3 :7-15 for every shape (fp32 parity path, odd channel counts).
+ *   w fp32 [kh][kw][cin][cout]                                              */
+int rtseg_conv_dense(const rtseg_conv_desc *d, const void *x, const float *w, const float *scale,
+                     const float *shift, const float *slope, const void *res, void *y,
+                     rtseg_stream_t stream);
+
+/* ---- K2'/K3'/K4' tensor-core path (tcgen05 + TMEM + TMA), bf16 only ------
+ * Same arithmetic as rtseg_conv_dense with bf16 operands and fp32
+ * accumulation.  Constraints (else RTSEG_ERR_UNSUPPORTED, see
+ * rtseg_conv_tc_supported): groups == 1, dtype bf16, stride 1 or 2 (even H, W),
+ * cin % 16 == 0, kh*kw <= 9, channel slices 16-byte aligned, and the weights
+ * of one output-channel tile must fit in shared memory.
+ *   w  bf16 [kh*kw][cout_pad][cin]  (K-major per tap; cout_pad = cout rounded
+ *      up to 16, padding rows zero)                                         */
+int rtseg_conv_tc_supported(const rtseg_conv_desc *d);
+int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,
+                  const float *shift, const float *slope, const void *res, void *y,
+                  rtseg_stream_t stream);
+/* Every mbarrier wait in the tensor-core kernels carries a ~2 s watchdog: a
+ * lost TMA or a wrong descriptor ends the kernel with garbage output and sets
+ * a device flag instead of hanging the GPU.  This call synchronises `stream`,
+ * returns the flag (1 = a kernel gave up since the last call) and clears it. */
+int rtseg_tc_timeout_flag(rtseg_stream_t stream);
+
+/* ---- K4'+K8: network stem ------------------------------------------------
+ * Replaces InitialBlock, models/enet.py:38-48 (conv 3x3 s2 + BN + act on
+ * channels [0,cconv) || MaxPool2d(3,2,1) of the input on channels
+ * [cconv, cconv+cin)) and the plain stride-2 stems ConvBNAct(3, C, 3, 2)
+ * (models/fastscnn.py:38, models/dabnet.py:19) when pool == 0.
+ * The input is the caller's NCHW tensor (x_is_nchw=1, x_dtype f32/bf16) or an
+ * NHWC one; cin <= 4.  Output is NHWC `dtype`, y_ctotal channels per pixel.
+ *   w fp32 [3][3][cin][cconv]                                              */
+int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int32_t pool,
+               const void *x, const float *w, const float *scale, const float *shift,
+               const float *slope, void *y, rtseg_stream_t stream);
+
+/* MaxPool2d(3,2,1) branch of InitialBlock (models/enet.py:43) for NHWC inputs
+ * with many channels; writes a channel slice of y. Uses d->n,h,w,cin,
+ * x_ctotal/x_coff, y_ctotal/y_coff, dtype. */
+int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void *y, rtseg_stream_t stream);
+
+/* ---- K5': transposed conv 3x3 s2 p1 op1 + BN + act -----------------------
+ * Replaces DeConvBNAct, models/modules.py:89-108 (scale_factor 2).
+ * d->h,w are the INPUT size; output is 2h x 2w.  d->kh=kw=3, stride=2.
+ *   w fp32 [3][3][cin][cout]  with w[ky][kx][ci][co] = torch weight[ci][co][ky][kx]
+ * If labels != NULL the per-pixel first-max channel index (torch.max(dim=1)
+ * semantics, models/ddrnet.py:55-58, core/seg_trainer.py:172) is written as
+ * uint8 [n][2h][2w].  The CUDA-core version always needs y (it takes the
+ * argmax in a second kernel); the tensor-core version fuses the argmax into
+ * its epilogue and accepts y == NULL, so the logits are never materialised. */
+int rtseg_deconv3x3s2(const rtseg_conv_desc *d, const void *x, const float *w, const float *scale,
+                      const float *shift, const float *slope, void *y, uint8_t *labels,
+                      rtseg_stream_t stream);
+/* tcgen05 variant: bf16, cin % 16 == 0; w bf16 [9][cout_pad][cin], cout_pad = cout rounded up to 16. */
+int rtseg_deconv3x3s2_tc_supported(const rtseg_conv_desc *d);
+int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16,
+                         const float *scale, const float *shift, const float *slope, void *y,
+                         uint8_t *labels, rtseg_stream_t stream);
+
+/* ---- K10'/K11: bilinear resize, fused head -------------------------------
+ * Replaces F.interpolate(mode='bilinear') at models/fastscnn.py:30,89,
+ * models/modules.py:153-156, models/dabnet.py:60, models/enet.py:198-202
+ * (align_corners = 0 there).  NHWC in, NHWC out (channel slices allowed via
+ * x_ctotal/x_coff, y_ctotal/y_coff in elements).                           */
+int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                            int32_t align_corners, int32_t dtype, const void *x, int32_t x_ctotal,
+                            int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff,
+                            rtseg_stream_t stream);
+/* Fused bilinear upsample + first-max argmax over channels (+ optional
+ * confusion-matrix update when target != NULL): the full-resolution logits
+ * never exist.  labels_u8 and/or labels_i64 may be NULL.  confmat is int64
+ * [c][c], rows = target (utils/metrics.py:4-7 semantics).                   */
+int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                          int32_t align_corners, int32_t dtype, const void *x, uint8_t *labels_u8,
+                          int64_t *labels_i64, const int64_t *target, int32_t ignore_index,
+                          int64_t *confmat, rtseg_stream_t stream);
+/* argmax over channels of an NHWC tensor (preds.max(dim=1)[1], core/seg_trainer.py:172). */
+int rtseg_argmax_nhwc(int64_t npix, int32_t c, int32_t c_total, int32_t dtype, const void *x,
+                      uint8_t *labels_u8, int64_t *labels_i64, rtseg_stream_t stream);
+/* argmax over dim 1 of an NCHW tensor (what the reference's models return). */
+int rtseg_argmax_nchw(int32_t n, int32_t c, int64_t hw, int32_t dtype, const void *x,
+                      uint8_t *labels_u8, int64_t *labels_i64, rtseg_stream_t stream);
+
+/* ---- K13': confusion matrix ----------------------------------------------
+ * Replaces torchmetrics JaccardIndex.update as called at utils/metrics.py:4-7
+ * / core/seg_trainer.py:131: drop target == ignore_index, confmat[t][p] += 1.
+ * pred is uint8 (pred_is_i64 = 0) or int64 class indices.  Pixels whose
+ * target or pred is outside [0,c) and not ignore_index set *bad_count (may be
+ * NULL) instead of being counted.                                           */
+int rtseg_confmat_update(int64_t npix, int32_t c, int32_t ignore_index, const void *pred,
+                         int32_t pred_is_i64, const int64_t *target, int64_t *confmat,
+                         int64_t *bad_count, rtseg_stream_t stream);
+
+/* ---- K12': OHEM cross entropy ---------------------------------------------
+ * Replaces OhemCELoss.forward, core/loss.py:13-20.  logits are NCHW
+ * (layout = 0, what the reference trainer passes) or NHWC (layout = 1),
+ * f32 or bf16; labels int64 [n][h][w].
+ *   thresh      = -log(config.ohem_thrs) as fp32 (core/loss.py:9)
+ *   loss_px     fp32 [n*h*w] scratch: per-pixel CE (0 where ignored)
+ *   workspace   rtseg_ohem_workspace_bytes() bytes of scratch, any content
+ *   out         fp32 [4]: {loss, kth_value (top-k branch threshold or thresh),
+ *                          n_selected, branch (0 = loss>thresh, 1 = top-k)}
+ * The branch is decided on the device; no host synchronisation.            */
+size_t rtseg_ohem_workspace_bytes(void);
+int rtseg_ohem_fwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_t layout, int32_t dtype,
+                   const void *logits, const int64_t *labels, int32_t ignore_index, float thresh,
+                   float *loss_px, void *workspace, float *out, rtseg_stream_t stream);
+/* d loss / d logits = (softmax - onehot) * [pixel selected] * grad_out / n_selected,
+ * written in the logits' layout and dtype.  `loss_px` and `workspace` are the
+ * buffers rtseg_ohem_fwd filled for the same logits; grad_out is a device scalar. */
+int rtseg_ohem_bwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_t layout, int32_t dtype,
+                   const void *logits, const int64_t *labels, int32_t ignore_index,
+                   const float *loss_px, const void *workspace, const float *grad_out,
+                   void *grad_logits, rtseg_stream_t stream);
+
+/* ---- layout plumbing --------------------------------------------------------
+ * NCHW <-> NHWC with dtype conversion (the reference's tensors are NCHW fp32,
+ * tools/test_speed.py:29; ours are NHWC bf16/fp32).                         */
+int rtseg_nchw_to_nhwc(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_dtype,
+                       const void *src, int32_t dst_dtype, void *dst, int32_t dst_ctotal,
+                       int32_t dst_coff, rtseg_stream_t stream);
+int rtseg_nhwc_to_nchw(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_dtype,
+                       const void *src, int32_t src_ctotal, int32_t src_coff, int32_t dst_dtype,
+                       void *dst, rtseg_stream_t stream);
+/* AdaptiveAvgPool2d(p) of PyramidPoolingModule, models/modules.py:145-149.
+ * NHWC in (channel slice allowed), dense NHWC [n][p][p][c] out, same dtype. */
+int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype,
+                           const void *x, int32_t x_ctotal, int32_t x_coff, void *y,
+                           rtseg_stream_t stream);
+
+/* ---- host-buffer convenience (pinned or pageable HOST pointers) ------------
+ * One call = H2D copy of the low-resolution logits, the fused head kernel,
+ * D2H copy of the uint8 class map, all on `stream`, then a stream
+ * synchronise.  `dev_scratch` must hold logits bytes + n*ho*wo bytes.       */
+int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                               int32_t align_corners, int32_t dtype, const void *x_host,
+                               uint8_t *labels_host, void *dev_scratch, rtseg_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTSEG_H_ */

@@ -1,0 +1,128 @@
+"""Functional fp32 restatement of the benchmark networks and their seeded weight recipe."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from . import ref_blocks as B
+
+
+# ----------------------------------------------------------------------------- ERFNet ----
+def non_bt_1d(x, sd, prefix, dilation=1, act_type="relu"):
+    """NonBt1DBlock (reference models/erfnet.py:62-82); inner activations are always ReLU (:66-68)."""
+    y = B.conv_bn_act(x, sd, prefix + "conv.0.", (3, 1), 1, 1, "relu")
+    y = B.conv_bn_act(y, sd, prefix + "conv.1.", (1, 3), 1, 1, "relu")
+    y = B.conv_bn_act(y, sd, prefix + "conv.2.", (3, 1), 1, dilation, "relu")
+    y = F.conv2d(y, sd[prefix + "conv.3.weight"], None, 1, (0, dilation), dilation)
+    y = y + x
+    y = B.batch_norm(y, sd, prefix + "bn_act.0.")
+    return B.activation(y, act_type, sd, prefix + "bn_act.1.")
+
+
+def erfnet_forward(sd, x, act_type="relu"):
+    """ERFNet.forward (reference models/erfnet.py:35-46)."""
+    x = B.initial_block(x, sd, "layer1.", act_type)
+    x = B.initial_block(x, sd, "layer2.", act_type)
+    for i in range(5):
+        x = non_bt_1d(x, sd, f"layer3_7.{i}.", 1, act_type)
+    x = B.initial_block(x, sd, "layer8.", act_type)
+    for i, d in enumerate([2, 4, 8, 16, 2, 4, 8, 16]):
+        x = non_bt_1d(x, sd, f"layer9_16.{i}.", d, act_type)
+    x = B.deconv_bn_act(x, sd, "layer17.", 2, act_type)
+    for i in range(2):
+        x = non_bt_1d(x, sd, f"layer18_19.{i}.", 1, act_type)
+    x = B.deconv_bn_act(x, sd, "layer20.", 2, act_type)
+    for i in range(2):
+        x = non_bt_1d(x, sd, f"layer21_22.{i}.", 1, act_type)
+    return B.deconv_bn_act(x, sd, "layer23.", 2, act_type)
+
+
+# -------------------------------------------------------------------------- Fast-SCNN ----
+_IR_SETTING = [(6, 64, 3, 2), (6, 96, 2, 2), (6, 128, 3, 1)]  # t, c, n, s — reference models/fastscnn.py:47-52
+
+
+def inverted_residual(x, sd, prefix, cin, cout, stride, act_type="relu"):
+    """InvertedResidual (reference models/fastscnn.py:105-121)."""
+    y = B.pw_conv_bn_act(x, sd, prefix + "conv.0.", act_type)
+    y = B.dw_conv_bn_act(y, sd, prefix + "conv.1.", 3, stride, 1, act_type)
+    y = B.conv_bn_act(y, sd, prefix + "conv.2.", 1, 1, 1, "none")
+    return x + y if (stride == 1 and cin == cout) else y
+
+
+def fastscnn_lowres_logits(sd, x, act_type="relu"):
+    # LearningToDownsample (reference models/fastscnn.py:35-41)
+    p = "learning_to_downsample."
+    hi = B.conv_bn_act(x, sd, p + "0.", 3, 2, 1, act_type)
+    hi = B.ds_conv_bn_act(hi, sd, p + "1.", 3, 2, 1, act_type)
+    hi = B.ds_conv_bn_act(hi, sd, p + "2.", 3, 2, 1, act_type)
+    # GlobalFeatureExtractor (:44-70)
+    lo, cin, idx = hi, 64, 0
+    for _t, c, n, s in _IR_SETTING:
+        for i in range(n):
+            lo = inverted_residual(lo, sd, f"global_feature_extractor.bottlenecks.{idx}.", cin, c, s if i == 0 else 1,
+                                   act_type)
+            cin, idx = c, idx + 1
+    lo = B.pyramid_pooling(lo, sd, "global_feature_extractor.ppm.", act_type)
+    # FeatureFusionModule (:73-93)
+    p = "feature_fusion."
+    h = F.conv2d(hi, sd[p + "higher_res_conv.weight"])
+    l = F.interpolate(lo, hi.shape[2:], mode="bilinear", align_corners=True)
+    l = B.dw_conv_bn_act(l, sd, p + "lower_res_conv.0.", 3, 1, 1, act_type)
+    l = F.conv2d(l, sd[p + "lower_res_conv.1.weight"])
+    y = B.activation(B.batch_norm(h + l, sd, p + "non_linear.0."), act_type, sd, p + "non_linear.1.")
+    # Classifier (:96-102)
+    p = "classifier."
+    y = B.ds_conv_bn_act(y, sd, p + "0.", 3, 1, 1, act_type)
+    y = B.ds_conv_bn_act(y, sd, p + "1.", 3, 1, 1, act_type)
+    return B.pw_conv_bn_act(y, sd, p + "2.", act_type)
+
+
+def fastscnn_forward(sd, x, act_type="relu"):
+    """FastSCNN.forward (reference models/fastscnn.py:24-32): x8 bilinear, align_corners=True."""
+    return F.interpolate(fastscnn_lowres_logits(sd, x, act_type), x.shape[2:], mode="bilinear", align_corners=True)
+
+
+FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward}
+
+
+# --------------------------------------------------------------------- seeded weights ----
+def make_state(spec, seed: int, perturb_bn: bool = True):
+    """Deterministic state dict for `spec` = [(key, shape, dtype_str), ...] (reference key order).
+
+    perturb_bn=False reproduces the information content of a default init (BatchNorm = identity,
+    SURVEY F6); perturb_bn=True draws running statistics / affine terms so that a wrong BN fold,
+    a dropped bias or a wrong PReLU slope cannot hide.  CPU generator => identical on every host.
+    """
+    keys = {k for k, _, _ in spec}
+    sd = {}
+    for idx, (key, shape, dtype) in enumerate(spec):
+        g = torch.Generator().manual_seed(seed * 1000003 + idx)
+        leaf = key.rsplit(".", 1)[-1]
+        stem = key[: -len(leaf)]
+        is_bn = (stem + "running_mean") in keys
+        if leaf == "num_batches_tracked":
+            t = torch.zeros(shape, dtype=torch.int64)
+        elif len(shape) == 4:  # conv / deconv weight, He-style so activations stay O(1)
+            fan_in = shape[1] * shape[2] * shape[3]
+            t = torch.randn(shape, generator=g) * (2.0 / max(fan_in, 1)) ** 0.5
+        elif is_bn:
+            if not perturb_bn:
+                t = {"weight": torch.ones, "bias": torch.zeros, "running_mean": torch.zeros,
+                     "running_var": torch.ones}[leaf](shape)
+            elif leaf == "weight":
+                t = 1.0 + 0.2 * torch.randn(shape, generator=g)
+            elif leaf == "running_var":
+                t = 0.5 + torch.rand(shape, generator=g)
+            else:  # bias, running_mean
+                t = 0.1 * torch.randn(shape, generator=g)
+        elif "activation" in key:  # PReLU slope
+            t = 0.25 + (0.05 * torch.randn(shape, generator=g) if perturb_bn else torch.zeros(shape))
+        else:  # conv bias
+            t = 0.1 * torch.randn(shape, generator=g)
+        sd[key] = t
+    return sd
+
+
+def make_input(seed: int, n: int, h: int, w: int, c: int = 3):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn((n, c, h, w), generator=g)

@@ -1,0 +1,24 @@
+"""rtseg-b200: the B200-native hot path of acai66/realtime-semantic-segmentation-pytorch.
+
+Import name: `rtseg_b200` (this directory carries the repository's mandated,
+hyphenated name, so a two-line shim package at the repo root points here).
+
+    csrc/        hand-written sm_100a CUDA kernels + the C ABI (include/rtseg.h)
+    _lib.py      ctypes binding of librtseg.so (fails loudly if absent)
+    ops.py       tensor-level calls into the C ABI
+    modules.py   drop-in ConvBNAct / DWConvBNAct / PWConvBNAct / ... (reference models/modules.py)
+    nets.py      ERFNet, Fast-SCNN built from fused blocks, reference-compatible state dicts
+    loss.py      OhemCELoss / get_loss_fn (reference core/loss.py)
+    metrics.py   confusion-matrix mIoU / get_seg_metrics (reference utils/metrics.py)
+    parallel.py  set_device / parallel_model / de_parallel (reference utils/parallel.py)
+    engine.py    CUDA-graph inference engine with pinned-host I/O (what bench.py times)
+    inject.py    installs modules.py under the reference's `models.modules` name
+"""
+from . import _lib, ops  # noqa: F401
+from .engine import InferenceEngine  # noqa: F401
+from .loss import OhemCELoss, get_loss_fn  # noqa: F401
+from .metrics import SegMetrics, get_seg_metrics, iou_from_confmat  # noqa: F401
+from .nets import ERFNet, FastSCNN, get_model  # noqa: F401
+from .ops import upsample_argmax  # noqa: F401
+
+__version__ = "0.1.0"

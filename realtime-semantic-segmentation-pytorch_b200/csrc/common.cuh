@@ -1,0 +1,184 @@
+// common.cuh — shared host/device helpers for librtseg (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/rtseg.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "librtseg is written for sm_100a (B200) only"
+#endif
+
+namespace rtseg {
+
+// ---- error plumbing -------------------------------------------------------
+void set_error(const char *fmt, ...);
+void count_launch(int n = 1);
+
+#define RTSEG_FAIL(code, ...)      \
+  do {                             \
+    rtseg::set_error(__VA_ARGS__); \
+    return (code);                 \
+  } while (0)
+
+#define RTSEG_REQUIRE(cond, ...)                            \
+  do {                                                      \
+    if (!(cond)) RTSEG_FAIL(RTSEG_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+#define RTSEG_CUDA(call)                                                                \
+  do {                                                                                  \
+    cudaError_t e__ = (call);                                                           \
+    if (e__ != cudaSuccess)                                                             \
+      RTSEG_FAIL(RTSEG_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                 __FILE__, __LINE__);                                                   \
+  } while (0)
+
+// Call right after a <<<>>> launch.
+#define RTSEG_LAUNCH_CHECK(name)                                                       \
+  do {                                                                                 \
+    cudaError_t e__ = cudaGetLastError();                                              \
+    if (e__ != cudaSuccess)                                                            \
+      RTSEG_FAIL(RTSEG_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
+    rtseg::count_launch();                                                             \
+  } while (0)
+
+static inline cudaStream_t as_stream(rtseg_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+int num_sms();
+
+// ---- epilogue parameters passed by value to kernels -------------------------
+struct Epilogue {
+  const float *scale;  // [cout] or nullptr (=1)
+  const float *shift;  // [cout] or nullptr (=0)
+  const float *slope;  // [cout] PReLU slopes or nullptr
+  int act, act2, res_mode;
+  float p0, p1;
+};
+
+static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scale, const float *shift,
+                                     const float *slope) {
+  Epilogue e;
+  e.scale = scale;
+  e.shift = shift;
+  e.slope = slope;
+  e.act = d->act;
+  e.act2 = d->act2;
+  e.res_mode = d->res_mode;
+  e.p0 = d->act_p0;
+  e.p1 = d->act_p1;
+  return e;
+}
+
+int validate_conv_desc(const rtseg_conv_desc *d, const void *res);
+
+// ---- device side ---------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float act_apply(float v, int act, float p0, float p1, float slope) {
+  switch (act) {
+    case RTSEG_ACT_NONE: return v;
+    case RTSEG_ACT_RELU: return fmaxf(v, 0.f);
+    case RTSEG_ACT_RELU6: return fminf(fmaxf(v, 0.f), 6.f);
+    case RTSEG_ACT_LEAKYRELU: return v > 0.f ? v : v * p0;
+    case RTSEG_ACT_PRELU: return v > 0.f ? v : v * slope;
+    case RTSEG_ACT_ELU: return v > 0.f ? v : p0 * expm1f(v);
+    case RTSEG_ACT_CELU: return fmaxf(v, 0.f) + fminf(0.f, p0 * expm1f(v / p0));
+    case RTSEG_ACT_SELU: {
+      const float alpha = 1.6732632423543772848170429916717f;
+      const float lam = 1.0507009873554804934193349852946f;
+      return lam * (v > 0.f ? v : alpha * expm1f(v));
+    }
+    case RTSEG_ACT_HARDSWISH: return v * fminf(fmaxf(v + 3.f, 0.f), 6.f) * (1.f / 6.f);
+    case RTSEG_ACT_HARDTANH: return fminf(fmaxf(v, p0), p1);
+    case RTSEG_ACT_GELU: return 0.5f * v * (1.f + erff(v * 0.70710678118654752440f));
+    case RTSEG_ACT_SILU: return v / (1.f + expf(-v));
+    case RTSEG_ACT_SIGMOID: return 1.f / (1.f + expf(-v));
+    case RTSEG_ACT_TANH: return tanhf(v);
+    default: return v;
+  }
+}
+
+// v = acc (+res PRE) -> affine -> act (+res POST) -> act2
+__device__ __forceinline__ float epilogue_apply(float acc, float res, int c, const Epilogue &e) {
+  float v = acc;
+  if (e.res_mode == RTSEG_RES_PRE) v += res;
+  const float sc = e.scale ? __ldg(e.scale + c) : 1.f;
+  const float sh = e.shift ? __ldg(e.shift + c) : 0.f;
+  v = fmaf(v, sc, sh);
+  const float sl = (e.act == RTSEG_ACT_PRELU && e.slope) ? __ldg(e.slope + c) : 0.f;
+  v = act_apply(v, e.act, e.p0, e.p1, sl);
+  if (e.res_mode == RTSEG_RES_POST) {
+    v += res;
+    v = act_apply(v, e.act2, e.p0, e.p1, sl);
+  }
+  return v;
+}
+
+// Scalar typed load/store.
+template <typename T>
+__device__ __forceinline__ float ld_f(const T *p);
+template <>
+__device__ __forceinline__ float ld_f<float>(const float *p) {
+  return __ldg(p);
+}
+template <>
+__device__ __forceinline__ float ld_f<__nv_bfloat16>(const __nv_bfloat16 *p) {
+  return __bfloat162float(*p);
+}
+template <typename T>
+__device__ __forceinline__ void st_f(T *p, float v);
+template <>
+__device__ __forceinline__ void st_f<float>(float *p, float v) {
+  *p = v;
+}
+template <>
+__device__ __forceinline__ void st_f<__nv_bfloat16>(__nv_bfloat16 *p, float v) {
+  *p = __float2bfloat16_rn(v);
+}
+
+// 16-byte vectors: 4 x f32 or 8 x bf16.
+template <typename T>
+struct Vec16;
+template <>
+struct Vec16<float> {
+  static constexpr int N = 4;
+  __device__ static __forceinline__ void load(const float *p, float (&v)[4]) {
+    const float4 t = __ldg(reinterpret_cast<const float4 *>(p));
+    v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+  }
+  __device__ static __forceinline__ void store(float *p, const float (&v)[4]) {
+    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <>
+struct Vec16<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ static __forceinline__ void load(const __nv_bfloat16 *p, float (&v)[8]) {
+    const uint4 t = __ldg(reinterpret_cast<const uint4 *>(p));
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static __forceinline__ void store(__nv_bfloat16 *p, const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t *>(&h);
+    }
+    *reinterpret_cast<uint4 *>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+#endif  // __CUDACC__
+
+}  // namespace rtseg

@@ -1,0 +1,272 @@
+// conv_dw.cu — K1': NHWC depthwise convolution + folded BatchNorm + activation.
+//
+// Replaces DWConvBNAct (reference models/modules.py:46-59): Conv2d(groups=cin)
+// -> BatchNorm2d -> Activation, i.e. three ATen kernels and five tensor passes,
+// with ONE pass: read x once, write y once.  The op is 1.5-4.5 flop/byte, so the
+// only roofline that matters is HBM; the design rules are
+//   * channels innermost (NHWC) so that a thread owns a 16-byte channel vector
+//     (8 x bf16 / 4 x f32) and a warp reads/writes 512 contiguous bytes,
+//   * each thread produces PX neighbouring output pixels so that every input
+//     vector fetched from L1/L2 feeds up to KW outputs (dilation 1) and the
+//     per-tap weight vectors are amortised over PX pixels,
+//   * fp32 accumulation, one rounding at the store.
+#include "common.cuh"
+
+namespace rtseg {
+
+struct DwParams {
+  int n, h, w, c;  // c = cin = cout for the vector kernels
+  int ho, wo;
+  int kh, kw, stride, dil, pad_h, pad_w;
+  int x_ct, x_co, y_ct, y_co, r_ct, r_co;
+  int mult;  // channel multiplier (scalar kernel only)
+  int cout;
+};
+
+// ---- dilation-1 kernel with a sliding register window -----------------------
+template <typename T, int KH, int KW, int S, int PX>
+__global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__restrict__ x,
+                                                     const float *__restrict__ wgt, Epilogue ep,
+                                                     const T *__restrict__ res, T *__restrict__ y) {
+  constexpr int V = Vec16<T>::N;
+  constexpr int NW = (PX - 1) * S + KW;  // input columns feeding PX outputs
+  const int cvecs = p.c / V;
+  const int wq_n = (p.wo + PX - 1) / PX;
+  const int64_t total = (int64_t)p.n * p.ho * wq_n * cvecs;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int cv = (int)(tid % cvecs);
+  int64_t r = tid / cvecs;
+  const int wq = (int)(r % wq_n);
+  r /= wq_n;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int c0 = cv * V;
+
+  float acc[PX][V];
+#pragma unroll
+  for (int i = 0; i < PX; ++i)
+#pragma unroll
+    for (int v = 0; v < V; ++v) acc[i][v] = 0.f;
+
+  const int wi0 = wq * PX * S - p.pad_w;
+  const int hi0 = ho * S - p.pad_h;
+  const T *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + c0;
+
+#pragma unroll
+  for (int ky = 0; ky < KH; ++ky) {
+    const int hi = hi0 + ky;
+    if (hi < 0 || hi >= p.h) continue;
+    float wv[KW][V];
+#pragma unroll
+    for (int kx = 0; kx < KW; ++kx) {
+      const float *wp = wgt + (int64_t)(ky * KW + kx) * p.cout + c0;
+#pragma unroll
+      for (int v = 0; v < V; v += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(wp + v));
+        wv[kx][v] = t.x, wv[kx][v + 1] = t.y, wv[kx][v + 2] = t.z, wv[kx][v + 3] = t.w;
+      }
+    }
+    const T *xr = xn + (int64_t)hi * p.w * p.x_ct;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      const int wi = wi0 + j;
+      if (wi < 0 || wi >= p.w) continue;
+      float xv[V];
+      Vec16<T>::load(xr + (int64_t)wi * p.x_ct, xv);
+#pragma unroll
+      for (int kx = 0; kx < KW; ++kx) {
+        const int d = j - kx;
+        if (d >= 0 && d % S == 0 && d / S < PX) {
+#pragma unroll
+          for (int v = 0; v < V; ++v) acc[d / S][v] = fmaf(xv[v], wv[kx][v], acc[d / S][v]);
+        }
+      }
+    }
+  }
+
+  const int64_t pix0 = ((int64_t)n * p.ho + ho) * p.wo + (int64_t)wq * PX;
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    if (wq * PX + i >= p.wo) break;
+    float rv[V];
+    if (ep.res_mode != RTSEG_RES_NONE) {
+      Vec16<T>::load(res + (pix0 + i) * p.r_ct + p.r_co + c0, rv);
+    } else {
+#pragma unroll
+      for (int v = 0; v < V; ++v) rv[v] = 0.f;
+    }
+    float ov[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) ov[v] = epilogue_apply(acc[i][v], rv[v], c0 + v, ep);
+    Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
+  }
+}
+
+// ---- any kernel size / dilation / stride, vectorised over channels ------------
+template <typename T, int PX>
+__global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__restrict__ x,
+                                                     const float *__restrict__ wgt, Epilogue ep,
+                                                     const T *__restrict__ res, T *__restrict__ y) {
+  constexpr int V = Vec16<T>::N;
+  const int cvecs = p.c / V;
+  const int wq_n = (p.wo + PX - 1) / PX;
+  const int64_t total = (int64_t)p.n * p.ho * wq_n * cvecs;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int cv = (int)(tid % cvecs);
+  int64_t r = tid / cvecs;
+  const int wq = (int)(r % wq_n);
+  r /= wq_n;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int c0 = cv * V;
+
+  float acc[PX][V];
+#pragma unroll
+  for (int i = 0; i < PX; ++i)
+#pragma unroll
+    for (int v = 0; v < V; ++v) acc[i][v] = 0.f;
+
+  const T *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + c0;
+  for (int ky = 0; ky < p.kh; ++ky) {
+    const int hi = ho * p.stride - p.pad_h + ky * p.dil;
+    if (hi < 0 || hi >= p.h) continue;
+    const T *xr = xn + (int64_t)hi * p.w * p.x_ct;
+    for (int kx = 0; kx < p.kw; ++kx) {
+      float wv[V];
+      const float *wp = wgt + (int64_t)(ky * p.kw + kx) * p.cout + c0;
+#pragma unroll
+      for (int v = 0; v < V; v += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(wp + v));
+        wv[v] = t.x, wv[v + 1] = t.y, wv[v + 2] = t.z, wv[v + 3] = t.w;
+      }
+#pragma unroll
+      for (int i = 0; i < PX; ++i) {
+        const int wi = (wq * PX + i) * p.stride - p.pad_w + kx * p.dil;
+        if (wi < 0 || wi >= p.w) continue;
+        float xv[V];
+        Vec16<T>::load(xr + (int64_t)wi * p.x_ct, xv);
+#pragma unroll
+        for (int v = 0; v < V; ++v) acc[i][v] = fmaf(xv[v], wv[v], acc[i][v]);
+      }
+    }
+  }
+
+  const int64_t pix0 = ((int64_t)n * p.ho + ho) * p.wo + (int64_t)wq * PX;
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    if (wq * PX + i >= p.wo) break;
+    float rv[V];
+    if (ep.res_mode != RTSEG_RES_NONE) {
+      Vec16<T>::load(res + (pix0 + i) * p.r_ct + p.r_co + c0, rv);
+    } else {
+#pragma unroll
+      for (int v = 0; v < V; ++v) rv[v] = 0.f;
+    }
+    float ov[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) ov[v] = epilogue_apply(acc[i][v], rv[v], c0 + v, ep);
+    Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
+  }
+}
+
+// ---- scalar fallback: channel multiplier, odd channel counts, unaligned slices ---
+template <typename T>
+__global__ void __launch_bounds__(256) dw_scalar_kernel(DwParams p, const T *__restrict__ x,
+                                                        const float *__restrict__ wgt, Epilogue ep,
+                                                        const T *__restrict__ res, T *__restrict__ y) {
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * p.cout;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int co = (int)(tid % p.cout);
+  int64_t r = tid / p.cout;
+  const int wo = (int)(r % p.wo);
+  r /= p.wo;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int ci = co / p.mult;
+  float acc = 0.f;
+  const T *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + ci;
+  for (int ky = 0; ky < p.kh; ++ky) {
+    const int hi = ho * p.stride - p.pad_h + ky * p.dil;
+    if (hi < 0 || hi >= p.h) continue;
+    for (int kx = 0; kx < p.kw; ++kx) {
+      const int wi = wo * p.stride - p.pad_w + kx * p.dil;
+      if (wi < 0 || wi >= p.w) continue;
+      acc = fmaf(ld_f<T>(xn + ((int64_t)hi * p.w + wi) * p.x_ct), __ldg(wgt + (int64_t)(ky * p.kw + kx) * p.cout + co), acc);
+    }
+  }
+  const int64_t pix = ((int64_t)n * p.ho + ho) * p.wo + wo;
+  const float rv = ep.res_mode != RTSEG_RES_NONE ? ld_f<T>(res + pix * p.r_ct + p.r_co + co) : 0.f;
+  st_f<T>(y + pix * p.y_ct + p.y_co + co, epilogue_apply(acc, rv, co, ep));
+}
+
+template <typename T>
+static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, const Epilogue &ep,
+                     const void *res_, void *y_, cudaStream_t st) {
+  const T *x = static_cast<const T *>(x_);
+  const T *res = static_cast<const T *>(res_);
+  T *y = static_cast<T *>(y_);
+  DwParams p;
+  p.n = d->n, p.h = d->h, p.w = d->w, p.c = d->cin, p.cout = d->cout;
+  rtseg_out_hw(d, &p.ho, &p.wo);
+  p.kh = d->kh, p.kw = d->kw, p.stride = d->stride, p.dil = d->dil, p.pad_h = d->pad_h, p.pad_w = d->pad_w;
+  p.x_ct = d->x_ctotal, p.x_co = d->x_coff, p.y_ct = d->y_ctotal, p.y_co = d->y_coff;
+  p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
+  p.mult = d->cout / d->cin;
+
+  constexpr int V = Vec16<T>::N;
+  const bool aligned = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (reinterpret_cast<uintptr_t>(y) % 16 == 0) &&
+                       (res == nullptr || reinterpret_cast<uintptr_t>(res) % 16 == 0) &&
+                       (reinterpret_cast<uintptr_t>(w) % 16 == 0);
+  const bool vec_ok = aligned && p.mult == 1 && d->cin % V == 0 && d->x_ctotal % V == 0 && d->x_coff % V == 0 &&
+                      d->y_ctotal % V == 0 && d->y_coff % V == 0 &&
+                      (d->res_mode == RTSEG_RES_NONE || (d->r_ctotal % V == 0 && d->r_coff % V == 0));
+  const int threads = 256;
+  if (!vec_ok) {
+    const int64_t total = (int64_t)p.n * p.ho * p.wo * p.cout;
+    dw_scalar_kernel<T><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y);
+    RTSEG_LAUNCH_CHECK("dw_scalar_kernel");
+    return RTSEG_OK;
+  }
+  const int cvecs = p.c / V;
+#define RTSEG_DW_WIN(KH_, KW_, S_, PX_)                                                             \
+  do {                                                                                              \
+    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX_) * cvecs;                            \
+    dw_win_kernel<T, KH_, KW_, S_, PX_><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y); \
+    RTSEG_LAUNCH_CHECK("dw_win_kernel");                                                            \
+    return RTSEG_OK;                                                                                \
+  } while (0)
+  if (d->dil == 1 && d->kh == 3 && d->kw == 3) {
+    if (d->stride == 1) {
+      if (p.wo >= 64) RTSEG_DW_WIN(3, 3, 1, 8);
+      RTSEG_DW_WIN(3, 3, 1, 4);
+    }
+    if (d->stride == 2) RTSEG_DW_WIN(3, 3, 2, 4);
+  }
+  if (d->dil == 1 && d->stride == 1 && d->kh == 1 && d->kw == 3) RTSEG_DW_WIN(1, 3, 1, 8);
+#undef RTSEG_DW_WIN
+  {
+    constexpr int PX = 4;
+    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX) * cvecs;
+    dw_vec_kernel<T, PX><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y);
+    RTSEG_LAUNCH_CHECK("dw_vec_kernel");
+  }
+  return RTSEG_OK;
+}
+
+}  // namespace rtseg
+
+extern "C" int rtseg_conv_dw(const rtseg_conv_desc *d, const void *x, const float *w, const float *scale,
+                             const float *shift, const float *slope, const void *res, void *y,
+                             rtseg_stream_t stream) {
+  using namespace rtseg;
+  if (int rc = validate_conv_desc(d, res)) return rc;
+  RTSEG_REQUIRE(x && w && y, "NULL tensor pointer");
+  RTSEG_REQUIRE(d->groups == d->cin, "rtseg_conv_dw needs groups == cin");
+  RTSEG_REQUIRE(d->cout % d->cin == 0, "depthwise cout (%d) must be a multiple of cin (%d)", d->cout, d->cin);
+  const Epilogue ep = make_epilogue(d, scale, shift, slope);
+  if (d->dtype == RTSEG_BF16) return launch_dw<__nv_bfloat16>(d, x, w, ep, res, y, as_stream(stream));
+  return launch_dw<float>(d, x, w, ep, res, y, as_stream(stream));
+}

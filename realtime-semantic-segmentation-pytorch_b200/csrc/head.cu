@@ -1,0 +1,545 @@
+// head.cu — segmentation head and metric kernels.
+//
+//  * rtseg_upsample_bilinear  : F.interpolate(mode='bilinear') (reference
+//    models/fastscnn.py:30,89, models/modules.py:153-156, models/enet.py:198-202)
+//  * rtseg_upsample_argmax    : the same + preds.max(dim=1)[1]
+//    (core/seg_trainer.py:172, models/ddrnet.py:55-58) + optionally the
+//    torchmetrics confusion-matrix update (utils/metrics.py:4-7) in ONE pass;
+//    the 19 x 1024 x 2048 full-resolution logits (159 MB fp32 per image) are
+//    never written or re-read.
+//  * rtseg_argmax_nhwc / _nchw, rtseg_confmat_update: the unfused pieces.
+//  * layout plumbing: NCHW <-> NHWC transposes, AdaptiveAvgPool2d.
+//
+// Index arithmetic follows ATen's area_pixel_compute_source_index so that the
+// sampled positions are the ones the reference computes:
+//   align_corners:   src = dst * (in-1)/(out-1)
+//   otherwise:       src = max(0, (dst+0.5) * in/out - 0.5)
+// and  v = l0y*(l0x*v00 + l1x*v01) + l1y*(l0x*v10 + l1x*v11).
+#include <algorithm>
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace rtseg {
+
+__host__ __device__ __forceinline__ float resize_scale(int in, int out, int align) {
+  if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f;
+  return (float)in / (float)out;
+}
+
+__device__ __forceinline__ void src_index(int dst, float scale, int in, int align, int &i0, int &i1, float &l0,
+                                          float &l1) {
+  float s;
+  if (align) {
+    s = scale * (float)dst;
+  } else {
+    s = scale * ((float)dst + 0.5f) - 0.5f;
+    if (s < 0.f) s = 0.f;
+  }
+  i0 = (int)s;
+  if (i0 > in - 1) i0 = in - 1;
+  i1 = i0 + (i0 < in - 1 ? 1 : 0);
+  l1 = s - (float)i0;
+  l0 = 1.f - l1;
+}
+
+// torch.max(dim) semantics: first maximal index, NaN beats everything.
+__device__ __forceinline__ void argmax_step(float v, int c, float &best, int &idx) {
+  if (v > best || (v != v && best == best)) {
+    best = v;
+    idx = c;
+  }
+}
+
+// ---------------------------------------------------------------- bilinear ----
+template <typename T, int V>
+__global__ void __launch_bounds__(256) bilinear_kernel(int n, int hi, int wi, int c, int ho, int wo, int align,
+                                                       float sy, float sx, const T *__restrict__ x, int x_ct,
+                                                       int x_co, T *__restrict__ y, int y_ct, int y_co) {
+  const int cv_n = c / V;
+  const int64_t total = (int64_t)n * ho * wo * cv_n;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cv_n) * V;
+  int64_t r = tid / cv_n;
+  const int ox = (int)(r % wo);
+  r /= wo;
+  const int oy = (int)(r % ho);
+  const int b = (int)(r / ho);
+  int y0, y1, x0, x1;
+  float ly0, ly1, lx0, lx1;
+  src_index(oy, sy, hi, align, y0, y1, ly0, ly1);
+  src_index(ox, sx, wi, align, x0, x1, lx0, lx1);
+  const T *xb = x + (int64_t)b * hi * wi * x_ct + x_co + c0;
+  const T *p00 = xb + ((int64_t)y0 * wi + x0) * x_ct, *p01 = xb + ((int64_t)y0 * wi + x1) * x_ct;
+  const T *p10 = xb + ((int64_t)y1 * wi + x0) * x_ct, *p11 = xb + ((int64_t)y1 * wi + x1) * x_ct;
+  T *yp = y + (((int64_t)b * ho + oy) * wo + ox) * y_ct + y_co + c0;
+  if constexpr (V == 1) {
+    const float v = ly0 * (lx0 * ld_f<T>(p00) + lx1 * ld_f<T>(p01)) + ly1 * (lx0 * ld_f<T>(p10) + lx1 * ld_f<T>(p11));
+    st_f<T>(yp, v);
+  } else {
+    float a[V], bq[V], cq[V], dq[V], o[V];
+    Vec16<T>::load(p00, a);
+    Vec16<T>::load(p01, bq);
+    Vec16<T>::load(p10, cq);
+    Vec16<T>::load(p11, dq);
+#pragma unroll
+    for (int e = 0; e < V; ++e) o[e] = ly0 * (lx0 * a[e] + lx1 * bq[e]) + ly1 * (lx0 * cq[e] + lx1 * dq[e]);
+    Vec16<T>::store(yp, o);
+  }
+}
+
+// ------------------------------------------------- fused upsample + argmax ----
+constexpr int kHeadThreads = 128;  // output columns per block
+constexpr int kHeadRows = 16;      // output rows per thread
+constexpr int kMaxBins = 32 * 32;
+
+__device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool valid) {
+  // Lanes of a warp that hit the same bin (segmentation labels are spatially
+  // coherent, so usually all 32) are merged into one shared-memory atomic.
+  const unsigned active = __ballot_sync(0xffffffffu, valid);
+  if (!valid) return;
+  const unsigned peers = __match_any_sync(active, bin);
+  const int leader = __ffs(peers) - 1;
+  if ((int)(threadIdx.x & 31) == leader) atomicAdd(&hist[bin], __popc(peers));
+}
+
+template <typename T, int CMAX>
+__global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
+    int n, int hi, int wi, int c, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
+    uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
+    unsigned long long *__restrict__ confmat) {
+  __shared__ int hist[kMaxBins];
+  const bool do_cm = target != nullptr;
+  if (do_cm) {
+    for (int i = threadIdx.x; i < c * c; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+  }
+  const int ox = blockIdx.x * kHeadThreads + threadIdx.x;
+  const int oy_begin = blockIdx.y * kHeadRows;
+  const int b = blockIdx.z;
+  const bool col_ok = ox < wo;
+
+  int x0 = 0, x1 = 0;
+  float lx0 = 1.f, lx1 = 0.f;
+  if (col_ok) src_index(ox, sx, wi, align, x0, x1, lx0, lx1);
+  const T *xb = x + (int64_t)b * hi * wi * c;
+
+  float rowA[CMAX], rowB[CMAX];
+  int ia = -1, ib = -1;
+
+  auto load_row = [&](int i, float(&row)[CMAX]) {
+    const T *p0 = xb + ((int64_t)i * wi + x0) * c;
+    const T *p1 = xb + ((int64_t)i * wi + x1) * c;
+#pragma unroll
+    for (int k = 0; k < CMAX; ++k)
+      if (k < c) row[k] = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
+  };
+
+  for (int ry = 0; ry < kHeadRows; ++ry) {
+    const int oy = oy_begin + ry;
+    if (oy >= ho) break;  // uniform across the block
+    int y0, y1;
+    float ly0, ly1;
+    src_index(oy, sy, hi, align, y0, y1, ly0, ly1);
+    int label = 0;
+    if (col_ok) {
+      if (!(y0 == ia && y1 == ib)) {
+        if (y0 == ib) {
+#pragma unroll
+          for (int k = 0; k < CMAX; ++k) rowA[k] = rowB[k];
+        } else if (y0 != ia) {
+          load_row(y0, rowA);
+        }
+        ia = y0;
+        if (y1 == y0) {
+#pragma unroll
+          for (int k = 0; k < CMAX; ++k) rowB[k] = rowA[k];
+        } else {
+          load_row(y1, rowB);
+        }
+        ib = y1;
+      }
+      float best = -FLT_MAX;
+      bool first = true;
+#pragma unroll
+      for (int k = 0; k < CMAX; ++k) {
+        if (k < c) {
+          const float v = ly0 * rowA[k] + ly1 * rowB[k];
+          if (first) {
+            best = v, label = 0, first = false;
+          } else {
+            argmax_step(v, k, best, label);
+          }
+        }
+      }
+      const int64_t opix = ((int64_t)b * ho + oy) * wo + ox;
+      if (lab8) lab8[opix] = (uint8_t)label;
+      if (lab64) lab64[opix] = (int64_t)label;
+    }
+    if (do_cm) {
+      bool valid = false;
+      int bin = 0;
+      if (col_ok) {
+        const int64_t t = __ldg(target + ((int64_t)b * ho + oy) * wo + ox);
+        valid = t != (int64_t)ignore_index && t >= 0 && t < c;
+        bin = valid ? (int)t * c + label : 0;
+      }
+      hist_add_aggregated(hist, bin, valid);
+    }
+  }
+  if (do_cm) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < c * c; i += blockDim.x) {
+      const int v = hist[i];
+      if (v) atomicAdd(confmat + i, (unsigned long long)v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ argmax ----
+template <typename T>
+__global__ void __launch_bounds__(256) argmax_nhwc_kernel(int64_t npix, int c, int c_total, const T *__restrict__ x,
+                                                          uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64) {
+  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= npix) return;
+  const T *p = x + pix * c_total;
+  float best = ld_f<T>(p);
+  int idx = 0;
+  for (int k = 1; k < c; ++k) argmax_step(ld_f<T>(p + k), k, best, idx);
+  if (lab8) lab8[pix] = (uint8_t)idx;
+  if (lab64) lab64[pix] = idx;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) argmax_nchw_kernel(int n, int c, int64_t hw, const T *__restrict__ x,
+                                                          uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)n * hw) return;
+  const int64_t b = tid / hw, s = tid % hw;
+  const T *p = x + b * c * hw + s;
+  float best = ld_f<T>(p);
+  int idx = 0;
+  for (int k = 1; k < c; ++k) argmax_step(ld_f<T>(p + (int64_t)k * hw), k, best, idx);
+  if (lab8) lab8[tid] = (uint8_t)idx;
+  if (lab64) lab64[tid] = idx;
+}
+
+// ------------------------------------------------------------ confusion matrix ----
+template <typename P>
+__global__ void __launch_bounds__(256) confmat_kernel(int64_t npix, int c, int ignore_index, const P *__restrict__ pred,
+                                                      const int64_t *__restrict__ target,
+                                                      unsigned long long *__restrict__ confmat,
+                                                      unsigned long long *__restrict__ bad) {
+  __shared__ int hist[kMaxBins];
+  __shared__ int nbad;
+  for (int i = threadIdx.x; i < c * c; i += blockDim.x) hist[i] = 0;
+  if (threadIdx.x == 0) nbad = 0;
+  __syncthreads();
+  // Each block walks a contiguous chunk; every warp iteration is full or fully masked.
+  const int64_t per_block = (npix + gridDim.x - 1) / gridDim.x;
+  const int64_t begin = (int64_t)blockIdx.x * per_block;
+  const int64_t end = min(npix, begin + per_block);
+  for (int64_t i0 = begin; i0 < end; i0 += blockDim.x) {
+    const int64_t i = i0 + threadIdx.x;
+    bool valid = false;
+    int bin = 0;
+    if (i < end) {
+      const int64_t t = __ldg(target + i);
+      const int64_t q = (int64_t)pred[i];
+      if (t != (int64_t)ignore_index) {
+        if (t >= 0 && t < c && q >= 0 && q < c) {
+          valid = true;
+          bin = (int)t * c + (int)q;
+        } else {
+          atomicAdd(&nbad, 1);
+        }
+      }
+    }
+    hist_add_aggregated(hist, bin, valid);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < c * c; i += blockDim.x) {
+    const int v = hist[i];
+    if (v) atomicAdd(confmat + i, (unsigned long long)v);
+  }
+  if (threadIdx.x == 0 && nbad && bad) atomicAdd(bad, (unsigned long long)nbad);
+}
+
+// ------------------------------------------------------------------- transposes ----
+// dst[b][col][row] = src[b][row][col] on 32x32 tiles; rows/cols refer to src.
+template <typename TS, typename TD>
+__global__ void __launch_bounds__(256) transpose_kernel(int rows, int cols, const TS *__restrict__ src,
+                                                        int64_t src_pitch, int64_t src_batch, TD *__restrict__ dst,
+                                                        int64_t dst_pitch, int64_t dst_batch) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  const int tx = threadIdx.x % 32, ty = threadIdx.x / 32;  // 32 x 8
+  const TS *s = src + (int64_t)b * src_batch;
+  TD *d = dst + (int64_t)b * dst_batch;
+#pragma unroll
+  for (int k = 0; k < 32; k += 8) {
+    const int r = r0 + ty + k, c = c0 + tx;
+    if (r < rows && c < cols) tile[ty + k][tx] = ld_f<TS>(s + (int64_t)r * src_pitch + c);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 32; k += 8) {
+    const int c = c0 + ty + k, r = r0 + tx;
+    if (r < rows && c < cols) st_f<TD>(d + (int64_t)c * dst_pitch + r, tile[tx][ty + k]);
+  }
+}
+
+template <typename TS, typename TD>
+static int launch_transpose(int n, int rows, int cols, const void *src, int64_t src_pitch, int64_t src_batch,
+                            void *dst, int64_t dst_pitch, int64_t dst_batch, cudaStream_t st) {
+  // grid.y is limited to 65535: fold very tall matrices over several launches.
+  const int max_rows = 65535 * 32;
+  for (int r0 = 0; r0 < rows; r0 += max_rows) {
+    const int rr = min(max_rows, rows - r0);
+    dim3 grid((unsigned)cdiv(cols, 32), (unsigned)cdiv(rr, 32), (unsigned)n);
+    transpose_kernel<TS, TD><<<grid, 256, 0, st>>>(rr, cols, static_cast<const TS *>(src) + (int64_t)r0 * src_pitch,
+                                                   src_pitch, src_batch, static_cast<TD *>(dst) + r0, dst_pitch,
+                                                   dst_batch);
+    RTSEG_LAUNCH_CHECK("transpose_kernel");
+  }
+  return RTSEG_OK;
+}
+
+static int dispatch_transpose(int n, int rows, int cols, int sdt, const void *src, int64_t sp, int64_t sb, int ddt,
+                              void *dst, int64_t dp, int64_t db, cudaStream_t st) {
+  if (sdt == RTSEG_F32 && ddt == RTSEG_F32) return launch_transpose<float, float>(n, rows, cols, src, sp, sb, dst, dp, db, st);
+  if (sdt == RTSEG_F32 && ddt == RTSEG_BF16)
+    return launch_transpose<float, __nv_bfloat16>(n, rows, cols, src, sp, sb, dst, dp, db, st);
+  if (sdt == RTSEG_BF16 && ddt == RTSEG_F32)
+    return launch_transpose<__nv_bfloat16, float>(n, rows, cols, src, sp, sb, dst, dp, db, st);
+  if (sdt == RTSEG_BF16 && ddt == RTSEG_BF16)
+    return launch_transpose<__nv_bfloat16, __nv_bfloat16>(n, rows, cols, src, sp, sb, dst, dp, db, st);
+  RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+}
+
+// ------------------------------------------------------------- adaptive avg pool ----
+template <typename T>
+__global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int c, int p, const T *__restrict__ x,
+                                                               int x_ct, int x_co, T *__restrict__ y) {
+  __shared__ float part[8][32];
+  const int cell = blockIdx.x, b = blockIdx.y, c0 = blockIdx.z * 32;
+  const int pi = cell / p, pj = cell % p;
+  const int hs = (pi * h) / p, he = ((pi + 1) * h + p - 1) / p;
+  const int wsx = (pj * w) / p, we = ((pj + 1) * w + p - 1) / p;
+  const int lane = threadIdx.x % 32, ty = threadIdx.x / 32;
+  const int ch = c0 + lane;
+  const int ww = we - wsx, cnt = (he - hs) * ww;
+  float s = 0.f;
+  if (ch < c) {
+    const T *xb = x + (int64_t)b * h * w * x_ct + x_co + ch;
+    for (int i = ty; i < cnt; i += 8) {
+      const int yy = hs + i / ww, xx = wsx + i % ww;
+      s += ld_f<T>(xb + ((int64_t)yy * w + xx) * x_ct);
+    }
+  }
+  part[ty][lane] = s;
+  __syncthreads();
+  if (ty == 0 && ch < c) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][lane];
+    st_f<T>(y + (((int64_t)b * p + pi) * p + pj) * c + ch, t / (float)cnt);
+  }
+}
+
+}  // namespace rtseg
+
+using namespace rtseg;
+
+extern "C" int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                                       int32_t align, int32_t dtype, const void *x, int32_t x_ct, int32_t x_co,
+                                       void *y, int32_t y_ct, int32_t y_co, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y, "NULL tensor pointer");
+  RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && c > 0 && ho > 0 && wo > 0, "non-positive extent");
+  RTSEG_REQUIRE(x_ct >= x_co + c && y_ct >= y_co + c && x_co >= 0 && y_co >= 0, "channel slice out of range");
+  const float sy = resize_scale(hi, ho, align), sx = resize_scale(wi, wo, align);
+  cudaStream_t st = as_stream(stream);
+  const int V = dtype == RTSEG_BF16 ? 8 : 4;
+  const bool vec = c % V == 0 && x_ct % V == 0 && x_co % V == 0 && y_ct % V == 0 && y_co % V == 0 &&
+                   reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
+  const int64_t total = (int64_t)n * ho * wo * (vec ? c / V : c);
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  if (dtype == RTSEG_BF16) {
+    auto xs = (const __nv_bfloat16 *)x;
+    auto ys = (__nv_bfloat16 *)y;
+    if (vec)
+      bilinear_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
+    else
+      bilinear_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
+  } else if (dtype == RTSEG_F32) {
+    auto xs = (const float *)x;
+    auto ys = (float *)y;
+    if (vec)
+      bilinear_kernel<float, 4><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
+    else
+      bilinear_kernel<float, 1><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
+  } else {
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  }
+  RTSEG_LAUNCH_CHECK("bilinear_kernel");
+  return RTSEG_OK;
+}
+
+template <typename T>
+static int launch_upsample_argmax(int n, int hi, int wi, int c, int ho, int wo, int align, const void *x,
+                                  uint8_t *l8, int64_t *l64, const int64_t *target, int ignore, int64_t *confmat,
+                                  cudaStream_t st) {
+  const float sy = resize_scale(hi, ho, align), sx = resize_scale(wi, wo, align);
+  dim3 grid((unsigned)cdiv(wo, kHeadThreads), (unsigned)cdiv(ho, kHeadRows), (unsigned)n);
+  auto cm = reinterpret_cast<unsigned long long *>(confmat);
+  const T *xs = static_cast<const T *>(x);
+#define RTSEG_HEAD(CM)                                                                                              \
+  if (c <= CM) {                                                                                                    \
+    upsample_argmax_kernel<T, CM><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, l8, l64, \
+                                                                 target, ignore, cm);                              \
+    RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");                                                                   \
+    return RTSEG_OK;                                                                                                \
+  }
+  RTSEG_HEAD(8)
+  RTSEG_HEAD(16)
+  RTSEG_HEAD(24)
+  RTSEG_HEAD(32)
+#undef RTSEG_HEAD
+  RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_upsample_argmax supports at most 32 classes (got %d)", c);
+}
+
+extern "C" int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                                     int32_t align, int32_t dtype, const void *x, uint8_t *labels_u8,
+                                     int64_t *labels_i64, const int64_t *target, int32_t ignore_index,
+                                     int64_t *confmat, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x, "NULL logits pointer");
+  RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && c > 0 && ho > 0 && wo > 0, "non-positive extent");
+  RTSEG_REQUIRE(n <= 65535 && cdiv(ho, kHeadRows) <= 65535, "batch or height too large for one launch");
+  RTSEG_REQUIRE((target == nullptr) == (confmat == nullptr), "target and confmat must be given together");
+  RTSEG_REQUIRE(labels_u8 || labels_i64 || confmat, "nothing to compute");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == RTSEG_BF16)
+    return launch_upsample_argmax<__nv_bfloat16>(n, hi, wi, c, ho, wo, align, x, labels_u8, labels_i64, target,
+                                                 ignore_index, confmat, st);
+  if (dtype == RTSEG_F32)
+    return launch_upsample_argmax<float>(n, hi, wi, c, ho, wo, align, x, labels_u8, labels_i64, target, ignore_index,
+                                         confmat, st);
+  RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+}
+
+extern "C" int rtseg_argmax_nhwc(int64_t npix, int32_t c, int32_t c_total, int32_t dtype, const void *x,
+                                 uint8_t *labels_u8, int64_t *labels_i64, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && (labels_u8 || labels_i64), "NULL pointer");
+  RTSEG_REQUIRE(npix > 0 && c > 0 && c_total >= c, "bad extent");
+  RTSEG_REQUIRE(labels_u8 == nullptr || c <= 256, "uint8 labels need c <= 256");
+  cudaStream_t st = as_stream(stream);
+  const unsigned grid = (unsigned)cdiv(npix, 256);
+  if (dtype == RTSEG_BF16)
+    argmax_nhwc_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, c_total, (const __nv_bfloat16 *)x, labels_u8, labels_i64);
+  else if (dtype == RTSEG_F32)
+    argmax_nhwc_kernel<float><<<grid, 256, 0, st>>>(npix, c, c_total, (const float *)x, labels_u8, labels_i64);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("argmax_nhwc_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_argmax_nchw(int32_t n, int32_t c, int64_t hw, int32_t dtype, const void *x, uint8_t *labels_u8,
+                                 int64_t *labels_i64, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && (labels_u8 || labels_i64), "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && c > 0 && hw > 0, "bad extent");
+  RTSEG_REQUIRE(labels_u8 == nullptr || c <= 256, "uint8 labels need c <= 256");
+  cudaStream_t st = as_stream(stream);
+  const unsigned grid = (unsigned)cdiv((int64_t)n * hw, 256);
+  if (dtype == RTSEG_BF16)
+    argmax_nchw_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(n, c, hw, (const __nv_bfloat16 *)x, labels_u8, labels_i64);
+  else if (dtype == RTSEG_F32)
+    argmax_nchw_kernel<float><<<grid, 256, 0, st>>>(n, c, hw, (const float *)x, labels_u8, labels_i64);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("argmax_nchw_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_confmat_update(int64_t npix, int32_t c, int32_t ignore_index, const void *pred,
+                                    int32_t pred_is_i64, const int64_t *target, int64_t *confmat, int64_t *bad_count,
+                                    rtseg_stream_t stream) {
+  RTSEG_REQUIRE(pred && target && confmat, "NULL pointer");
+  RTSEG_REQUIRE(npix >= 0 && c > 0 && c <= 32, "confusion matrix supports 1..32 classes (got %d)", c);
+  if (npix == 0) return RTSEG_OK;
+  cudaStream_t st = as_stream(stream);
+  const unsigned grid = (unsigned)std::min<int64_t>(cdiv(npix, 256 * 8), (int64_t)num_sms() * 8);
+  auto cm = reinterpret_cast<unsigned long long *>(confmat);
+  auto bad = reinterpret_cast<unsigned long long *>(bad_count);
+  if (pred_is_i64)
+    confmat_kernel<int64_t><<<grid, 256, 0, st>>>(npix, c, ignore_index, (const int64_t *)pred, target, cm, bad);
+  else
+    confmat_kernel<uint8_t><<<grid, 256, 0, st>>>(npix, c, ignore_index, (const uint8_t *)pred, target, cm, bad);
+  RTSEG_LAUNCH_CHECK("confmat_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_nchw_to_nhwc(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_dtype, const void *src,
+                                  int32_t dst_dtype, void *dst, int32_t dst_ctotal, int32_t dst_coff,
+                                  rtseg_stream_t stream) {
+  RTSEG_REQUIRE(src && dst, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0 && dst_ctotal >= dst_coff + c && dst_coff >= 0, "bad extent");
+  const int64_t hw = (int64_t)h * w;
+  RTSEG_REQUIRE(hw < (int64_t)INT32_MAX, "image too large");
+  void *d = static_cast<char *>(dst) + (size_t)dst_coff * (dst_dtype == RTSEG_BF16 ? 2 : 4);
+  // src per image: [c rows][hw cols]  ->  dst [hw][ctotal]
+  return dispatch_transpose(n, c, (int)hw, src_dtype, src, hw, (int64_t)c * hw, dst_dtype, d, dst_ctotal,
+                            hw * dst_ctotal, as_stream(stream));
+}
+
+extern "C" int rtseg_nhwc_to_nchw(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_dtype, const void *src,
+                                  int32_t src_ctotal, int32_t src_coff, int32_t dst_dtype, void *dst,
+                                  rtseg_stream_t stream) {
+  RTSEG_REQUIRE(src && dst, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0 && src_ctotal >= src_coff + c && src_coff >= 0, "bad extent");
+  const int64_t hw = (int64_t)h * w;
+  RTSEG_REQUIRE(hw < (int64_t)INT32_MAX, "image too large");
+  const void *s = static_cast<const char *>(src) + (size_t)src_coff * (src_dtype == RTSEG_BF16 ? 2 : 4);
+  // src per image: [hw rows][c cols] (pitch ctotal)  ->  dst [c][hw]
+  return dispatch_transpose(n, (int)hw, c, src_dtype, s, src_ctotal, hw * src_ctotal, dst_dtype, dst, hw,
+                            (int64_t)c * hw, as_stream(stream));
+}
+
+extern "C" int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype,
+                                      const void *x, int32_t x_ct, int32_t x_co, void *y, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && h > 0 && w > 0 && c > 0 && p > 0 && x_ct >= x_co + c && x_co >= 0, "bad extent");
+  RTSEG_REQUIRE(n <= 65535 && cdiv(c, 32) <= 65535, "extent too large");
+  dim3 grid((unsigned)(p * p), (unsigned)n, (unsigned)cdiv(c, 32));
+  cudaStream_t st = as_stream(stream);
+  if (dtype == RTSEG_BF16)
+    adaptive_avgpool_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(h, w, c, p, (const __nv_bfloat16 *)x, x_ct, x_co, (__nv_bfloat16 *)y);
+  else if (dtype == RTSEG_F32)
+    adaptive_avgpool_kernel<float><<<grid, 256, 0, st>>>(h, w, c, p, (const float *)x, x_ct, x_co, (float *)y);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("adaptive_avgpool_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                                          int32_t align, int32_t dtype, const void *x_host, uint8_t *labels_host,
+                                          void *dev_scratch, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x_host && labels_host && dev_scratch, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && c > 0 && ho > 0 && wo > 0, "non-positive extent");
+  const size_t es = dtype == RTSEG_BF16 ? 2 : 4;
+  size_t in_bytes = (size_t)n * hi * wi * c * es;
+  const size_t out_bytes = (size_t)n * ho * wo;
+  const size_t in_padded = (in_bytes + 255) / 256 * 256;
+  cudaStream_t st = as_stream(stream);
+  uint8_t *dlab = static_cast<uint8_t *>(dev_scratch) + in_padded;
+  RTSEG_CUDA(cudaMemcpyAsync(dev_scratch, x_host, in_bytes, cudaMemcpyHostToDevice, st));
+  if (int rc = rtseg_upsample_argmax(n, hi, wi, c, ho, wo, align, dtype, dev_scratch, dlab, nullptr, nullptr, 255,
+                                     nullptr, stream))
+    return rc;
+  RTSEG_CUDA(cudaMemcpyAsync(labels_host, dlab, out_bytes, cudaMemcpyDeviceToHost, st));
+  RTSEG_CUDA(cudaStreamSynchronize(st));
+  return RTSEG_OK;
+}

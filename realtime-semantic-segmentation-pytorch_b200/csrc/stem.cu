@@ -1,0 +1,251 @@
+// stem.cu — K4'+K8: the first layer of every net on the path.
+//
+// Replaces InitialBlock (reference models/enet.py:38-48; ERFNet's
+// DownsamplerBlock alias, models/erfnet.py:12): cat([ConvBNAct(cin, cout-cin,
+// 3, stride 2)(x), MaxPool2d(3, 2, 1)(x)], dim=1) — conv, BN, act, pool and
+// cat are five launches in the reference and the 1024x2048 input is read
+// twice.  Here one thread produces one output pixel: it reads the 3x3xcin
+// input window once (straight from the caller's NCHW fp32 tensor, so no layout
+// conversion pass exists), computes every conv channel from weights staged in
+// shared memory (broadcast reads), takes the window max for the pool branch and
+// writes cconv+cin contiguous NHWC channels.  With pool == 0 it is the plain
+// stride-2 stem ConvBNAct(3, C, 3, 2) of Fast-SCNN / DABNet.
+//
+// Also here: the NHWC MaxPool2d(3,2,1) branch for the deeper InitialBlocks.
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace rtseg {
+
+struct StemParams {
+  int n, h, w, cin, cconv, ho, wo;
+  int64_t sn, sc, sh, sw;  // input strides in elements
+  int y_ct, y_co;
+  int pool;
+};
+
+template <typename TI, typename TO, int CIN, int CC>
+__global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__restrict__ x,
+                                                   const float *__restrict__ wgt, Epilogue ep,
+                                                   TO *__restrict__ y) {
+  // weights [3][3][CIN][cconv] padded to CC output channels
+  __shared__ __align__(16) float ws[9 * CIN * CC];
+  for (int i = threadIdx.x; i < 9 * CIN * CC; i += blockDim.x) {
+    const int co = i % CC, t = i / CC;
+    ws[i] = co < p.cconv ? __ldg(wgt + (int64_t)t * p.cconv + co) : 0.f;
+  }
+  __syncthreads();
+
+  const int64_t total = (int64_t)p.n * p.ho * p.wo;
+  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= total) return;
+  const int wo = (int)(pix % p.wo);
+  const int64_t r = pix / p.wo;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+
+  float acc[CC];
+#pragma unroll
+  for (int c = 0; c < CC; ++c) acc[c] = 0.f;
+  float mx[CIN];
+#pragma unroll
+  for (int c = 0; c < CIN; ++c) mx[c] = -FLT_MAX;
+
+  const TI *xn = x + (int64_t)n * p.sn;
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    const int hi = ho * 2 - 1 + ky;
+    if (hi < 0 || hi >= p.h) continue;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int wi = wo * 2 - 1 + kx;
+      if (wi < 0 || wi >= p.w) continue;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float v = ld_f<TI>(xn + ci * p.sc + hi * p.sh + wi * p.sw);
+        mx[ci] = fmaxf(mx[ci], v);
+        const float *wp = &ws[((ky * 3 + kx) * CIN + ci) * CC];
+#pragma unroll
+        for (int c = 0; c < CC; c += 4) {
+          const float4 w4 = *reinterpret_cast<const float4 *>(wp + c);
+          acc[c] = fmaf(v, w4.x, acc[c]);
+          acc[c + 1] = fmaf(v, w4.y, acc[c + 1]);
+          acc[c + 2] = fmaf(v, w4.z, acc[c + 2]);
+          acc[c + 3] = fmaf(v, w4.w, acc[c + 3]);
+        }
+      }
+    }
+  }
+
+  TO *yp = y + pix * p.y_ct + p.y_co;
+  const int ctot = p.cconv + (p.pool ? CIN : 0);
+  // Assemble the output channel vector in registers, then store 16-byte chunks when possible.
+  constexpr int CT = CC + 4;  // CC >= cconv, CIN <= 4
+  float out[CT];
+#pragma unroll
+  for (int c = 0; c < CT; ++c) out[c] = 0.f;
+#pragma unroll
+  for (int c = 0; c < CC; ++c)
+    if (c < p.cconv) out[c] = epilogue_apply(acc[c], 0.f, c, ep);
+  if (p.pool) {  // static register indexing: place mx[] right behind the conv channels
+#pragma unroll
+    for (int c = 0; c < CT; ++c)
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci)
+        if (c == p.cconv + ci) out[c] = mx[ci];
+  }
+  constexpr int V = Vec16<TO>::N;
+  const bool vec = (ctot % V == 0) && (p.y_ct % V == 0) && (p.y_co % V == 0) &&
+                   (reinterpret_cast<uintptr_t>(y) % 16 == 0);
+  if (vec) {
+#pragma unroll
+    for (int c = 0; c + V <= CT; c += V) {
+      if (c < ctot) {
+        float v[V];
+#pragma unroll
+        for (int e = 0; e < V; ++e) v[e] = out[c + e];
+        Vec16<TO>::store(yp + c, v);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < CT; ++c)
+      if (c < ctot) st_f<TO>(yp + c, out[c]);
+  }
+}
+
+struct PoolParams {
+  int n, h, w, c, ho, wo;
+  int x_ct, x_co, y_ct, y_co;
+};
+
+template <typename T, int V>
+__global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T *__restrict__ x, T *__restrict__ y) {
+  const int cv_n = p.c / V;
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * cv_n;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cv_n) * V;
+  int64_t r = tid / cv_n;
+  const int wo = (int)(r % p.wo);
+  r /= p.wo;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  float m[V];
+#pragma unroll
+  for (int e = 0; e < V; ++e) m[e] = -FLT_MAX;
+  for (int ky = 0; ky < 3; ++ky) {
+    const int hi = ho * 2 - 1 + ky;
+    if (hi < 0 || hi >= p.h) continue;
+    for (int kx = 0; kx < 3; ++kx) {
+      const int wi = wo * 2 - 1 + kx;
+      if (wi < 0 || wi >= p.w) continue;
+      const T *xp = x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0;
+      if constexpr (V == 1) {
+        m[0] = fmaxf(m[0], ld_f<T>(xp));
+      } else {
+        float v[V];
+        Vec16<T>::load(xp, v);
+#pragma unroll
+        for (int e = 0; e < V; ++e) m[e] = fmaxf(m[e], v[e]);
+      }
+    }
+  }
+  T *yp = y + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.y_ct + p.y_co + c0;
+  if constexpr (V == 1) {
+    st_f<T>(yp, m[0]);
+  } else {
+    Vec16<T>::store(yp, m);
+  }
+}
+
+template <typename TI, typename TO>
+static int launch_stem(const StemParams &p, const void *x, const float *w, const Epilogue &ep, void *y,
+                       cudaStream_t st) {
+  const int64_t total = (int64_t)p.n * p.ho * p.wo;
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  const TI *xi = static_cast<const TI *>(x);
+  TO *yo = static_cast<TO *>(y);
+#define RTSEG_STEM(CIN_, CC_)                                                    \
+  if (p.cin == CIN_ && p.cconv <= CC_) {                                         \
+    stem_kernel<TI, TO, CIN_, CC_><<<grid, 256, 0, st>>>(p, xi, w, ep, yo);      \
+    RTSEG_LAUNCH_CHECK("stem_kernel");                                           \
+    return RTSEG_OK;                                                             \
+  }
+  RTSEG_STEM(3, 16)
+  RTSEG_STEM(3, 32)
+  RTSEG_STEM(1, 16)
+  RTSEG_STEM(1, 32)
+  RTSEG_STEM(4, 16)
+  RTSEG_STEM(4, 32)
+#undef RTSEG_STEM
+  RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_stem: cin=%d cconv=%d has no kernel (cin in {1,3,4}, cconv <= 32)", p.cin,
+             p.cconv);
+}
+
+}  // namespace rtseg
+
+extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int32_t pool, const void *x,
+                          const float *w, const float *scale, const float *shift, const float *slope, void *y,
+                          rtseg_stream_t stream) {
+  using namespace rtseg;
+  RTSEG_REQUIRE(d && x && w && y, "NULL argument");
+  RTSEG_REQUIRE(d->kh == 3 && d->kw == 3 && d->stride == 2 && d->dil == 1 && d->pad_h == 1 && d->pad_w == 1 &&
+                    d->groups == 1,
+                "rtseg_stem is the 3x3 stride-2 pad-1 stem only");
+  RTSEG_REQUIRE(d->res_mode == RTSEG_RES_NONE, "stem has no residual");
+  RTSEG_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0 && d->cin > 0 && d->cout > 0, "non-positive extent");
+  StemParams p;
+  p.n = d->n, p.h = d->h, p.w = d->w, p.cin = d->cin, p.cconv = d->cout;
+  p.ho = (d->h - 1) / 2 + 1, p.wo = (d->w - 1) / 2 + 1;
+  p.pool = pool ? 1 : 0;
+  p.y_ct = d->y_ctotal, p.y_co = d->y_coff;
+  RTSEG_REQUIRE(p.y_ct >= p.y_co + p.cconv + (p.pool ? p.cin : 0), "output channel slice too small");
+  if (x_is_nchw) {
+    p.sn = (int64_t)d->cin * d->h * d->w, p.sc = (int64_t)d->h * d->w, p.sh = d->w, p.sw = 1;
+  } else {
+    p.sn = (int64_t)d->h * d->w * d->x_ctotal, p.sc = 1, p.sh = (int64_t)d->w * d->x_ctotal, p.sw = d->x_ctotal;
+    x = static_cast<const char *>(x) + (size_t)d->x_coff * (x_dtype == RTSEG_BF16 ? 2 : 4);
+  }
+  const Epilogue ep = make_epilogue(d, scale, shift, slope);
+  cudaStream_t st = as_stream(stream);
+  if (x_dtype == RTSEG_F32 && d->dtype == RTSEG_F32) return launch_stem<float, float>(p, x, w, ep, y, st);
+  if (x_dtype == RTSEG_F32 && d->dtype == RTSEG_BF16) return launch_stem<float, __nv_bfloat16>(p, x, w, ep, y, st);
+  if (x_dtype == RTSEG_BF16 && d->dtype == RTSEG_BF16)
+    return launch_stem<__nv_bfloat16, __nv_bfloat16>(p, x, w, ep, y, st);
+  if (x_dtype == RTSEG_BF16 && d->dtype == RTSEG_F32) return launch_stem<__nv_bfloat16, float>(p, x, w, ep, y, st);
+  RTSEG_FAIL(RTSEG_ERR_INVALID, "bad dtype combination");
+}
+
+extern "C" int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void *y, rtseg_stream_t stream) {
+  using namespace rtseg;
+  RTSEG_REQUIRE(d && x && y, "NULL argument");
+  RTSEG_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0 && d->cin > 0, "non-positive extent");
+  PoolParams p;
+  p.n = d->n, p.h = d->h, p.w = d->w, p.c = d->cin;
+  p.ho = (d->h - 1) / 2 + 1, p.wo = (d->w - 1) / 2 + 1;
+  p.x_ct = d->x_ctotal, p.x_co = d->x_coff, p.y_ct = d->y_ctotal, p.y_co = d->y_coff;
+  RTSEG_REQUIRE(p.x_ct >= p.x_co + p.c && p.y_ct >= p.y_co + p.c, "channel slice out of range");
+  cudaStream_t st = as_stream(stream);
+  const int V = d->dtype == RTSEG_BF16 ? 8 : 4;
+  const bool vec = p.c % V == 0 && p.x_ct % V == 0 && p.x_co % V == 0 && p.y_ct % V == 0 && p.y_co % V == 0 &&
+                   reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * (vec ? p.c / V : p.c);
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  if (d->dtype == RTSEG_BF16) {
+    if (vec)
+      maxpool3x3s2_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y);
+    else
+      maxpool3x3s2_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y);
+  } else if (d->dtype == RTSEG_F32) {
+    if (vec)
+      maxpool3x3s2_kernel<float, 4><<<grid, 256, 0, st>>>(p, (const float *)x, (float *)y);
+    else
+      maxpool3x3s2_kernel<float, 1><<<grid, 256, 0, st>>>(p, (const float *)x, (float *)y);
+  } else {
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  }
+  RTSEG_LAUNCH_CHECK("maxpool3x3s2_kernel");
+  return RTSEG_OK;
+}

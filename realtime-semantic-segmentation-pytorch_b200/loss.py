@@ -1,0 +1,79 @@
+"""OHEM cross-entropy on the rtseg kernels — drop-in for reference core/loss.py:6-20,55-71."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import _lib, ops
+
+
+class _OhemFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, thresh: float, ignore_index: int):
+        ops._require_cuda(logits, "OhemCELoss")
+        if logits.dtype not in (torch.float32, torch.bfloat16):
+            logits = logits.float()  # fp16 autocast outputs: CE is an fp32 op under autocast anyway
+        if logits.is_contiguous():
+            layout = 0
+        elif ops.is_nhwc(logits):
+            layout = 1
+        else:
+            logits, layout = logits.contiguous(), 0
+        if labels.dtype != torch.int64:
+            labels = labels.long()
+        labels = labels.contiguous()
+        n, c, h, w = logits.shape
+        if tuple(labels.shape) != (n, h, w):
+            raise ValueError(f"labels {tuple(labels.shape)} do not match logits {tuple(logits.shape)}")
+        lib = _lib.load()
+        dev = logits.device
+        loss_px = torch.empty(n * h * w, dtype=torch.float32, device=dev)
+        ws = torch.empty(lib.rtseg_ohem_workspace_bytes(), dtype=torch.uint8, device=dev)
+        out = torch.empty(4, dtype=torch.float32, device=dev)
+        _lib.check(lib.rtseg_ohem_fwd(n, c, h, w, layout, ops._dtype_code(logits.dtype), logits.data_ptr(),
+                                      labels.data_ptr(), int(ignore_index), float(thresh), loss_px.data_ptr(),
+                                      ws.data_ptr(), out.data_ptr(), ops._stream()), "rtseg_ohem_fwd")
+        ctx.save_for_backward(logits, labels, loss_px, ws)
+        ctx.meta = (layout, int(ignore_index))
+        ctx.stats = out
+        return out[0].clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        logits, labels, loss_px, ws = ctx.saved_tensors
+        layout, ignore_index = ctx.meta
+        n, c, h, w = logits.shape
+        grad = torch.empty_like(logits)  # preserves the NCHW / channels_last layout
+        g = grad_out.detach().to(device=logits.device, dtype=torch.float32).reshape(1).contiguous()
+        _lib.check(_lib.load().rtseg_ohem_bwd(n, c, h, w, layout, ops._dtype_code(logits.dtype), logits.data_ptr(),
+                                              labels.data_ptr(), ignore_index, loss_px.data_ptr(), ws.data_ptr(),
+                                              g.data_ptr(), grad.data_ptr(), ops._stream()), "rtseg_ohem_bwd")
+        return grad, None, None, None
+
+
+class OhemCELoss(nn.Module):
+    """mean of the per-pixel CE losses above -log(thresh), or of the top n_valid//16 if fewer qualify.
+
+    Same constructor and call signature as the reference (core/loss.py:6-20); unlike it, the threshold
+    is a Python float, so constructing the module does not need a GPU.
+    """
+
+    def __init__(self, thresh, ignore_index=255):
+        super().__init__()
+        self.thresh = float(-torch.log(torch.tensor(thresh, dtype=torch.float)))  # fp32 value, core/loss.py:9
+        self.ignore_index = ignore_index
+
+    def forward(self, logits, labels):
+        return _OhemFunction.apply(logits, labels, self.thresh, self.ignore_index)
+
+
+def get_loss_fn(config, device):
+    """Factory with the reference's contract (core/loss.py:55-71)."""
+    if config.loss_type == "ohem":
+        if config.class_weights is not None:
+            raise NotImplementedError("class_weights are ignored by the reference's OHEM branch and unsupported here")
+        return OhemCELoss(thresh=config.ohem_thrs, ignore_index=config.ignore_index)
+    if config.loss_type == "ce":
+        weights = None if config.class_weights is None else torch.Tensor(config.class_weights).to(device)
+        return nn.CrossEntropyLoss(ignore_index=config.ignore_index, reduction=config.reduction, weight=weights)
+    raise NotImplementedError(f"Unsupport loss type: {config.loss_type}")

@@ -1,0 +1,273 @@
+"""ERFNet and Fast-SCNN assembled from the fused blocks (configs 2, 3 and 5 of BASELINE.json).
+
+The GPU box has no copy of the reference, so the two benchmark networks are
+defined here.  Attribute names and child order reproduce the reference's
+state-dict keys exactly (ERFNet: reference models/erfnet.py:15-46, 2,065,458
+parameters; Fast-SCNN: models/fastscnn.py:16-121, 1,023,769 parameters — both
+pinned by tests/golden/state_specs.json, generated from the reference), so a
+reference checkpoint loads with `load_state_dict` and vice versa.
+
+What differs from the reference is the execution plan of `forward`:
+  * every conv+BN+act is one kernel; residual adds, the BN after an add, the
+    InitialBlock max-pool + concat, PPM concat and FFM add are epilogue/slice
+    fusions (no separate elementwise or cat passes);
+  * activations stay NHWC bf16/fp32 between layers;
+  * `predict(x)` ends in the fused argmax (ERFNet: inside the last transposed
+    conv; Fast-SCNN: fused x8 bilinear upsample + argmax), so the
+    19 x 1024 x 2048 logits are never written.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .modules import (Activation, Conv2d, ConvBNAct, DeConvBNAct, DSConvBNAct, DWConvBNAct, PWConvBNAct,
+                      PyramidPoolingModule, _bn_tensors, _check_eval, _FoldCache, conv1x1)
+
+
+def _param_dtype(m: nn.Module) -> torch.dtype:
+    return next(m.parameters()).dtype
+
+
+class InitialBlock(nn.Module):
+    """cat([ConvBNAct(in, out-in, 3, stride 2)(x), MaxPool2d(3,2,1)(x)]) — reference models/enet.py:38-48."""
+
+    def __init__(self, in_channels, out_channels, act_type, kernel_size=3, **kwargs):
+        super().__init__()
+        assert out_channels > in_channels, "out_channels should be larger than in_channels.\n"
+        self.conv = ConvBNAct(in_channels, out_channels - in_channels, kernel_size, 2, act_type=act_type, **kwargs)
+        self.pool = nn.MaxPool2d(3, 2, 1)
+
+    def forward(self, x):
+        conv = self.conv[0]
+        cin, cconv = conv.in_channels, conv.out_channels
+        _check_eval(self, self.conv[1])
+        folded, post = self.conv._folded()
+        if post is not None:
+            raise NotImplementedError("non-pointwise activation in InitialBlock")
+        if cin <= 4 and cconv <= 32 and conv.kernel_size == (3, 3):
+            return ops.stem(folded, x, pool=True, out_dtype=_param_dtype(self.conv))
+        x = ops.to_nhwc(x)
+        n, _, h, w = x.shape
+        out = ops.empty_nhwc(n, cconv + cin, (h - 1) // 2 + 1, (w - 1) // 2 + 1, x.dtype, x.device)
+        ops.conv(folded, x, out=out, y_coff=0)
+        ops.maxpool3x3s2(x, out, y_coff=cconv)
+        return out
+
+
+class NonBt1DBlock(nn.Module):
+    """ERFNet non-bottleneck-1D block — reference models/erfnet.py:62-82.
+
+    3x1 -> 1x3 -> 3x1(d) -> 1x3(d) -> (+x) -> BN -> act: four launches; the add,
+    the trailing BatchNorm and the activation ride in the fourth conv's epilogue.
+    The three inner activations are ReLU whatever `act_type` says (erfnet.py:66-68).
+    """
+
+    def __init__(self, channels, dilation=1, act_type="relu"):
+        super().__init__()
+        self.conv = nn.Sequential(
+            ConvBNAct(channels, channels, (3, 1), inplace=True),
+            ConvBNAct(channels, channels, (1, 3), inplace=True),
+            ConvBNAct(channels, channels, (3, 1), dilation=dilation, inplace=True),
+            Conv2d(channels, channels, (1, 3), dilation=dilation, padding=(0, dilation), bias=False),
+        )
+        self.bn_act = nn.Sequential(nn.BatchNorm2d(channels), Activation(act_type, inplace=True))
+
+    def forward(self, x):
+        x = ops.to_nhwc(x)
+        t = self.conv[0](x)
+        t = self.conv[1](t)
+        t = self.conv[2](t)
+        return self.conv[3](t, res=x, res_mode=ops.RES_PRE, bn=self.bn_act[0], act=self.bn_act[1].activation)
+
+
+def _blocks(block, channels, count, dilations=(), act_type="relu"):
+    dilations = list(dilations) or [1] * count
+    if len(dilations) != count:
+        raise ValueError("Number of dilation should be equal to number of blocks")
+    return nn.Sequential(*[block(channels, dilation=d, act_type=act_type) for d in dilations])
+
+
+class ERFNet(nn.Module):
+    """ERFNet — reference models/erfnet.py:15-46 (same layer names / state-dict keys)."""
+
+    def __init__(self, num_class=1, n_channel=3, act_type="relu"):
+        super().__init__()
+        self.layer1 = InitialBlock(n_channel, 16, act_type=act_type)
+        self.layer2 = InitialBlock(16, 64, act_type=act_type)
+        self.layer3_7 = _blocks(NonBt1DBlock, 64, 5, act_type=act_type)
+        self.layer8 = InitialBlock(64, 128, act_type=act_type)
+        self.layer9_16 = _blocks(NonBt1DBlock, 128, 8, dilations=[2, 4, 8, 16, 2, 4, 8, 16], act_type=act_type)
+        self.layer17 = DeConvBNAct(128, 64, act_type=act_type)
+        self.layer18_19 = _blocks(NonBt1DBlock, 64, 2, act_type=act_type)
+        self.layer20 = DeConvBNAct(64, 16, act_type=act_type)
+        self.layer21_22 = _blocks(NonBt1DBlock, 16, 2, act_type=act_type)
+        self.layer23 = DeConvBNAct(16, num_class, act_type=act_type)
+        self.num_class = num_class
+
+    def _trunk(self, x):
+        x = self.layer1(x)
+        x = self.layer2(x)
+        x = self.layer3_7(x)
+        x = self.layer8(x)
+        x = self.layer9_16(x)
+        x = self.layer17(x)
+        x = self.layer18_19(x)
+        x = self.layer20(x)
+        return self.layer21_22(x)
+
+    def forward(self, x):
+        """Logits [N, num_class, H, W] like the reference."""
+        return self.layer23(self._trunk(x))
+
+    def predict(self, x, labels: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """uint8 class map [N, H, W] == forward(x).max(dim=1)[1]; the logits are never materialised."""
+        n, _, h, w = x.shape
+        if labels is None:
+            labels = torch.empty((n, h, w), dtype=torch.uint8, device=x.device)
+        self.layer23(self._trunk(x), labels=labels, want_logits=False)
+        return labels
+
+
+class InvertedResidual(nn.Module):
+    """MobileNetV2 block of Fast-SCNN — reference models/fastscnn.py:105-121."""
+
+    def __init__(self, in_channels, out_channels, stride, expand_ratio=6, act_type="relu"):
+        super().__init__()
+        hid = int(round(in_channels * expand_ratio))
+        self.use_res_connect = stride == 1 and in_channels == out_channels
+        self.conv = nn.Sequential(
+            PWConvBNAct(in_channels, hid, act_type=act_type),
+            DWConvBNAct(hid, hid, 3, stride, act_type=act_type),
+            ConvBNAct(hid, out_channels, 1, act_type="none"),
+        )
+
+    def forward(self, x):
+        x = ops.to_nhwc(x)
+        t = self.conv[1](self.conv[0](x))
+        if self.use_res_connect:  # x + conv(x): the add rides in the projection's epilogue
+            return self.conv[2](t, res=x, res_mode=ops.RES_POST)
+        return self.conv[2](t)
+
+
+class LearningToDownsample(nn.Sequential):
+    """reference models/fastscnn.py:35-41"""
+
+    def __init__(self, in_channels, out_channels, hid_channels=[32, 48], act_type="relu"):
+        super().__init__(
+            ConvBNAct(in_channels, hid_channels[0], 3, 2, act_type=act_type),
+            DSConvBNAct(hid_channels[0], hid_channels[1], 3, 2, act_type=act_type),
+            DSConvBNAct(hid_channels[1], out_channels, 3, 2, act_type=act_type),
+        )
+
+    def forward(self, x):
+        stem = self[0]
+        conv = stem[0]
+        if conv.in_channels <= 4 and conv.out_channels <= 32:
+            _check_eval(self, stem[1])
+            folded, post = stem._folded()
+            if post is not None:
+                raise NotImplementedError("non-pointwise activation in the stem")
+            x = ops.stem(folded, x, pool=False, out_dtype=_param_dtype(stem))
+        else:
+            x = stem(x)
+        return self[2](self[1](x))
+
+
+class GlobalFeatureExtractor(nn.Module):
+    """reference models/fastscnn.py:44-70"""
+
+    def __init__(self, in_channels, out_channels, act_type="relu"):
+        super().__init__()
+        feats = []
+        for t, c, n, s in ([6, 64, 3, 2], [6, 96, 2, 2], [6, 128, 3, 1]):
+            for i in range(n):
+                feats.append(InvertedResidual(in_channels, c, s if i == 0 else 1, t, act_type=act_type))
+                in_channels = c
+        self.bottlenecks = nn.Sequential(*feats)
+        self.ppm = PyramidPoolingModule(in_channels, out_channels, act_type=act_type, bias=True)
+
+    def forward(self, x):
+        return self.ppm(self.bottlenecks(x))
+
+
+class FeatureFusionModule(nn.Module):
+    """reference models/fastscnn.py:73-93.  act(BN(conv_hi(hi) + conv_lo(DW(up(lo))))):
+    the add, BN and activation are the epilogue of the low-resolution branch's 1x1 conv."""
+
+    def __init__(self, higher_channels, lower_channels, out_channels, act_type="relu"):
+        super().__init__()
+        self.higher_res_conv = conv1x1(higher_channels, out_channels)
+        self.lower_res_conv = nn.Sequential(
+            DWConvBNAct(lower_channels, lower_channels, 3, 1, act_type=act_type),
+            conv1x1(lower_channels, out_channels),
+        )
+        self.non_linear = nn.Sequential(nn.BatchNorm2d(out_channels), Activation(act_type))
+
+    def forward(self, higher_res_feat, lower_res_feat):
+        size = higher_res_feat.shape[2:]
+        hi = self.higher_res_conv(higher_res_feat)
+        lo = ops.upsample_bilinear(lower_res_feat, size, True)
+        lo = self.lower_res_conv[0](lo)
+        return self.lower_res_conv[1](lo, res=hi, res_mode=ops.RES_PRE, bn=self.non_linear[0],
+                                      act=self.non_linear[1].activation)
+
+
+class Classifier(nn.Sequential):
+    """reference models/fastscnn.py:96-102"""
+
+    def __init__(self, in_channels, num_class, act_type="relu"):
+        super().__init__(
+            DSConvBNAct(in_channels, in_channels, 3, 1, act_type=act_type),
+            DSConvBNAct(in_channels, in_channels, 3, 1, act_type=act_type),
+            PWConvBNAct(in_channels, num_class, act_type=act_type),
+        )
+
+
+class FastSCNN(nn.Module):
+    """Fast-SCNN — reference models/fastscnn.py:16-32 (same attribute names / state-dict keys)."""
+
+    def __init__(self, num_class=1, n_channel=3, act_type="relu"):
+        super().__init__()
+        self.learning_to_downsample = LearningToDownsample(n_channel, 64, act_type=act_type)
+        self.global_feature_extractor = GlobalFeatureExtractor(64, 128, act_type=act_type)
+        self.feature_fusion = FeatureFusionModule(64, 128, 128, act_type=act_type)
+        self.classifier = Classifier(128, num_class, act_type=act_type)
+        self.num_class = num_class
+
+    def lowres_logits(self, x):
+        hi = self.learning_to_downsample(x)
+        lo = self.global_feature_extractor(hi)
+        return self.classifier(self.feature_fusion(hi, lo))
+
+    def forward(self, x):
+        """Full-resolution logits like the reference (bilinear x8, align_corners=True)."""
+        return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+
+    def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
+                ignore_index: int = 255) -> torch.Tensor:
+        """uint8 class map via the fused upsample+argmax head (+ confusion-matrix update)."""
+        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
+                                   ignore_index=ignore_index)
+
+
+MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN}
+
+
+def get_model(config) -> nn.Module:
+    """Subset of reference models/__init__.py:47-99 for the nets defined in this package."""
+    name = config.model
+    if name not in MODEL_HUB:
+        raise NotImplementedError(f"Unsupport model type: {name}")
+    if getattr(config, "use_aux", False):
+        raise ValueError(f"Model {name} does not support auxiliary heads.\n")
+    if getattr(config, "use_detail_head", False):
+        raise ValueError(f"Model {name} does not support detail heads.\n")
+    return MODEL_HUB[name](num_class=config.num_class)
+
+
+__all__ = ["ERFNet", "FastSCNN", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "get_model", "MODEL_HUB"]
+_ = (_bn_tensors, _FoldCache)

@@ -1,0 +1,440 @@
+"""Tensor-level host API over the C ABI (include/rtseg.h).
+
+PyTorch is used here for device memory, streams and views only; every FLOP
+goes through librtseg.so.  Tensors are NCHW-*logical* torch tensors stored
+channels_last (dense NHWC), which is what the kernels read and write; a
+channel slice of a wider NHWC buffer is passed as (buffer, c_offset, channels).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import ACT_CODES, BF16, F32, RES_NONE, RES_POST, RES_PRE, ConvDesc
+
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def _dtype_code(t: torch.dtype) -> int:
+    try:
+        return _DT[t]
+    except KeyError:
+        raise TypeError(f"rtseg kernels support float32 and bfloat16 tensors, got {t}") from None
+
+
+def _require_cuda(x: torch.Tensor, what: str) -> None:
+    if not x.is_cuda:
+        raise RuntimeError(
+            f"{what}: input is on {x.device}; the rtseg path has no CPU implementation "
+            "(the CPU restatement lives in oracle/ and is test infrastructure only)")
+    _lib.sync_device(x.device.index)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def is_nhwc(x: torch.Tensor) -> bool:
+    return x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last)
+
+
+def empty_nhwc(n: int, c: int, h: int, w: int, dtype, device) -> torch.Tensor:
+    return torch.empty((n, c, h, w), dtype=dtype, device=device, memory_format=torch.channels_last)
+
+
+def to_nhwc(x: torch.Tensor, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """Dense-NHWC copy of an NCHW tensor (our transpose kernel), or x itself if already NHWC."""
+    _require_cuda(x, "to_nhwc")
+    dtype = dtype or x.dtype
+    if is_nhwc(x) and x.dtype == dtype:
+        return x
+    n, c, h, w = x.shape
+    if is_nhwc(x):  # dtype change only: treat as [n*h*w, c] -> same layout
+        src = x.permute(0, 2, 3, 1).reshape(1, 1, n * h * w, c)  # view, "NCHW" with c'=1
+        out = empty_nhwc(n, c, h, w, dtype, x.device)
+        # a [rows=1][cols] transpose is a dtype-converting copy
+        _lib.check(_lib.load().rtseg_nchw_to_nhwc(1, 1, 1, n * h * w * c, _dtype_code(x.dtype), src.data_ptr(),
+                                                  _dtype_code(dtype), out.data_ptr(), 1, 0, _stream()), "convert")
+        return out
+    if not x.is_contiguous():
+        x = x.contiguous()
+    out = empty_nhwc(n, c, h, w, dtype, x.device)
+    _lib.check(_lib.load().rtseg_nchw_to_nhwc(n, c, h, w, _dtype_code(x.dtype), x.data_ptr(), _dtype_code(dtype),
+                                              out.data_ptr(), c, 0, _stream()), "rtseg_nchw_to_nhwc")
+    return out
+
+
+def to_nchw(x: torch.Tensor, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """NCHW-contiguous copy of an NHWC tensor (what the reference's callers index into)."""
+    _require_cuda(x, "to_nchw")
+    dtype = dtype or x.dtype
+    n, c, h, w = x.shape
+    if not is_nhwc(x):
+        return x.contiguous().to(dtype)
+    out = torch.empty((n, c, h, w), dtype=dtype, device=x.device)
+    _lib.check(_lib.load().rtseg_nhwc_to_nchw(n, c, h, w, _dtype_code(x.dtype), x.data_ptr(), c, 0,
+                                              _dtype_code(dtype), out.data_ptr(), _stream()), "rtseg_nhwc_to_nchw")
+    return out
+
+
+# --------------------------------------------------------------------- folding ----
+@dataclass
+class Folded:
+    """Device-resident, kernel-ready parameters of one conv(+BN)(+act) layer."""
+
+    kind: str  # 'dense' | 'dw' | 'deconv'
+    cin: int
+    cout: int
+    kh: int
+    kw: int
+    stride: int
+    dil: int
+    pad_h: int
+    pad_w: int
+    w_f32: torch.Tensor            # dense/deconv [kh][kw][cin][cout]; dw [kh][kw][cout]
+    w_tc: Optional[torch.Tensor]   # bf16 [kh*kw][cout_pad][cin] or None
+    scale: Optional[torch.Tensor]
+    shift: Optional[torch.Tensor]
+    slope: Optional[torch.Tensor]
+    act: int = 0
+    p0: float = 0.0
+    p1: float = 0.0
+
+    @property
+    def groups(self) -> int:
+        return self.cin if self.kind == "dw" else 1
+
+
+def act_spec(module) -> Tuple[int, float, float, Optional[torch.Tensor], Optional[torch.nn.Module]]:
+    """(code, p0, p1, prelu_weight, post_module) for an nn activation module.
+
+    `post_module` is returned for the two non-pointwise hub members (GLU, Softmax),
+    which cannot live in a conv epilogue; the kernel then runs with act = none.
+    Mirrors the name table of reference models/modules.py:114-123.
+    """
+    nn = torch.nn
+    m = module
+    if m is None or isinstance(m, nn.Identity):
+        return ACT_CODES["none"], 0.0, 0.0, None, None
+    if isinstance(m, nn.ReLU6):
+        return ACT_CODES["relu6"], 0.0, 0.0, None, None
+    if isinstance(m, nn.ReLU):
+        return ACT_CODES["relu"], 0.0, 0.0, None, None
+    if isinstance(m, nn.LeakyReLU):
+        return ACT_CODES["leakyrelu"], float(m.negative_slope), 0.0, None, None
+    if isinstance(m, nn.PReLU):
+        return ACT_CODES["prelu"], 0.0, 0.0, m.weight, None
+    if isinstance(m, nn.ELU):
+        return ACT_CODES["elu"], float(m.alpha), 0.0, None, None
+    if isinstance(m, nn.CELU):
+        return ACT_CODES["celu"], float(m.alpha), 0.0, None, None
+    if isinstance(m, nn.SELU):
+        return ACT_CODES["selu"], 0.0, 0.0, None, None
+    if isinstance(m, nn.Hardswish):
+        return ACT_CODES["hardswish"], 0.0, 0.0, None, None
+    if isinstance(m, nn.Hardtanh):
+        return ACT_CODES["hardtanh"], float(m.min_val), float(m.max_val), None, None
+    if isinstance(m, nn.GELU):
+        if getattr(m, "approximate", "none") != "none":
+            raise NotImplementedError("GELU(approximate='tanh') has no fused epilogue")
+        return ACT_CODES["gelu"], 0.0, 0.0, None, None
+    if isinstance(m, nn.SiLU):
+        return ACT_CODES["silu"], 0.0, 0.0, None, None
+    if isinstance(m, nn.Sigmoid):
+        return ACT_CODES["sigmoid"], 0.0, 0.0, None, None
+    if isinstance(m, nn.Tanh):
+        return ACT_CODES["tanh"], 0.0, 0.0, None, None
+    if isinstance(m, (nn.GLU, nn.Softmax)):
+        return ACT_CODES["none"], 0.0, 0.0, None, m
+    raise NotImplementedError(f"no fused epilogue for activation {type(m).__name__}")
+
+
+def fold_affine(cout: int, bias: Optional[torch.Tensor], bn: Optional[torch.nn.BatchNorm2d]):
+    """Eval-mode BatchNorm (+ conv bias) as per-channel fp32 (scale, shift), folded in fp64."""
+    if bn is None:
+        if bias is None:
+            return None, None
+        return None, bias.detach().double()
+    if bn.running_mean is None or bn.running_var is None:
+        raise NotImplementedError("BatchNorm2d(track_running_stats=False) cannot be folded")
+    g = bn.weight.detach().double() if bn.weight is not None else torch.ones(cout, dtype=torch.float64, device=bn.running_mean.device)
+    b = bn.bias.detach().double() if bn.bias is not None else torch.zeros_like(g)
+    mean, var = bn.running_mean.detach().double(), bn.running_var.detach().double()
+    scale = g / torch.sqrt(var + bn.eps)
+    shift = b - mean * scale
+    if bias is not None:
+        shift = shift + bias.detach().double() * scale
+    return scale, shift
+
+
+def _f32(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
+    return None if t is None else t.to(device=device, dtype=torch.float32).contiguous()
+
+
+def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None) -> Tuple[Folded, Optional[torch.nn.Module]]:
+    """Pack nn.Conv2d / nn.ConvTranspose2d (+BN, +activation) for the kernels."""
+    nn = torch.nn
+    device = device or conv.weight.device
+    code, p0, p1, prelu_w, post = act_spec(act_module)
+    w = conv.weight.detach().to(device=device, dtype=torch.float32)
+    kh, kw = conv.kernel_size
+    sh, sw = conv.stride
+    dh, dw_ = conv.dilation
+    ph, pw = conv.padding if not isinstance(conv.padding, str) else (None, None)
+    if ph is None:
+        raise NotImplementedError("string padding modes are not supported")
+    if sh != sw or dh != dw_:
+        raise NotImplementedError("anisotropic stride/dilation is not supported")
+    if getattr(conv, "padding_mode", "zeros") != "zeros":
+        raise NotImplementedError("only zero padding is supported")
+    if isinstance(conv, nn.ConvTranspose2d):
+        cin, cout = conv.in_channels, conv.out_channels
+        if not (kh == 3 and kw == 3 and sh == 2 and ph == 1 and pw == 1 and tuple(conv.output_padding) == (1, 1)
+                and conv.groups == 1 and dh == 1):
+            raise NotImplementedError("only ConvTranspose2d(k=3, s=2, p=1, output_padding=1) has a kernel "
+                                      "(DeConvBNAct with scale_factor=2, reference models/modules.py:92-102)")
+        kind = "deconv"
+        w_f32 = w.permute(2, 3, 0, 1).contiguous()          # [kh][kw][cin][cout]
+        w_kmaj = w.permute(2, 3, 1, 0)                        # [kh][kw][cout][cin]
+    else:
+        cin, cout = conv.in_channels, conv.out_channels
+        if conv.groups == 1:
+            kind = "dense"
+            w_f32 = w.permute(2, 3, 1, 0).contiguous()       # [kh][kw][cin][cout]
+            w_kmaj = w.permute(2, 3, 0, 1)                    # [kh][kw][cout][cin]
+        elif conv.groups == cin and cout % cin == 0:
+            kind = "dw"
+            w_f32 = w[:, 0].permute(1, 2, 0).contiguous()    # [kh][kw][cout]
+            w_kmaj = None
+        else:
+            raise NotImplementedError(f"grouped convolution groups={conv.groups} has no kernel (only 1 or cin)")
+    w_tc = None
+    if w_kmaj is not None and cin % 16 == 0:
+        cpad = (cout + 15) // 16 * 16
+        w_tc = torch.zeros((kh * kw, cpad, cin), dtype=torch.bfloat16, device=device)
+        w_tc[:, :cout] = w_kmaj.reshape(kh * kw, cout, cin).to(torch.bfloat16)
+    scale, shift = fold_affine(cout, conv.bias, bn)
+    slope = None
+    if prelu_w is not None:
+        slope = prelu_w.detach().float().reshape(-1)
+        slope = slope.expand(cout) if slope.numel() == 1 else slope
+        if slope.numel() != cout:
+            raise ValueError("PReLU num_parameters must be 1 or the number of output channels")
+    f = Folded(kind, cin, cout, kh, kw, sh, dh, ph, pw, w_f32, w_tc, _f32(scale, device), _f32(shift, device),
+               _f32(slope, device), code, p0, p1)
+    return f, post
+
+
+# ------------------------------------------------------------------- conv calls ----
+def _desc(f: Folded, n, h, w, dtype_code, x_ct, x_co, y_ct, y_co, res_mode=RES_NONE, r_ct=0, r_co=0, act2=0,
+          act: Optional[int] = None) -> ConvDesc:
+    return ConvDesc(n, h, w, f.cin, f.cout, f.kh, f.kw, f.stride, f.dil, f.pad_h, f.pad_w, f.groups, dtype_code,
+                    f.act if act is None else act, f.p0, f.p1, res_mode, act2, x_ct, x_co, y_ct, y_co, r_ct, r_co)
+
+
+def out_hw(f: Folded, h: int, w: int) -> Tuple[int, int]:
+    if f.kind == "deconv":
+        return 2 * h, 2 * w
+    ho = (h + 2 * f.pad_h - f.dil * (f.kh - 1) - 1) // f.stride + 1
+    wo = (w + 2 * f.pad_w - f.dil * (f.kw - 1) - 1) // f.stride + 1
+    return ho, wo
+
+
+USE_TENSOR_CORES = True  # module-level switch used by tests to force the CUDA-core path
+
+
+def conv(f: Folded, x: torch.Tensor, *, res: Optional[torch.Tensor] = None, res_mode: int = RES_NONE,
+         out: Optional[torch.Tensor] = None, x_coff: int = 0, y_coff: int = 0, r_coff: int = 0, act2: int = 0,
+         labels: Optional[torch.Tensor] = None, want_logits: bool = True, allow_tc: Optional[bool] = None):
+    """One fused conv/deconv (+BN +act +residual) layer.
+
+    x, res, out are NHWC buffers; the op reads channels [x_coff, x_coff+cin) of x and
+    writes channels [y_coff, y_coff+cout) of out (allocated dense if None).
+    For kind == 'deconv', `labels` (uint8 [n, 2h, 2w]) requests the fused argmax.
+    """
+    _require_cuda(x, "conv")
+    if not is_nhwc(x):
+        raise ValueError("conv expects a dense NHWC (channels_last) tensor; use ops.to_nhwc")
+    lib = _lib.load()
+    n, x_ct, h, w = x.shape
+    dt = _dtype_code(x.dtype)
+    ho, wo = out_hw(f, h, w)
+    allow_tc = USE_TENSOR_CORES if allow_tc is None else allow_tc
+    if out is None and want_logits:
+        out = empty_nhwc(n, f.cout, ho, wo, x.dtype, x.device)
+    y_ct = out.shape[1] if out is not None else f.cout
+    if out is not None:
+        if not is_nhwc(out) or out.dtype != x.dtype or tuple(out.shape[2:]) != (ho, wo) or out.shape[0] != n:
+            raise ValueError("bad output buffer")
+    r_ct = 0
+    if res_mode != RES_NONE:
+        if res is None or not is_nhwc(res) or res.dtype != x.dtype or tuple(res.shape[2:]) != (ho, wo):
+            raise ValueError("bad residual tensor")
+        r_ct = res.shape[1]
+    d = _desc(f, n, h, w, dt, x_ct, x_coff, y_ct, y_coff, res_mode, r_ct, r_coff, act2)
+    st = _stream()
+    args = (_ptr(f.scale), _ptr(f.shift), _ptr(f.slope))
+    if f.kind == "dw":
+        _lib.check(lib.rtseg_conv_dw(C.byref(d), x.data_ptr(), f.w_f32.data_ptr(), *args, _ptr(res), out.data_ptr(), st),
+                   "rtseg_conv_dw")
+    elif f.kind == "dense":
+        if allow_tc and dt == BF16 and f.w_tc is not None and lib.rtseg_conv_tc_supported(C.byref(d)):
+            _lib.check(lib.rtseg_conv_tc(C.byref(d), x.data_ptr(), f.w_tc.data_ptr(), *args, _ptr(res), out.data_ptr(), st),
+                       "rtseg_conv_tc")
+        else:
+            _lib.check(lib.rtseg_conv_dense(C.byref(d), x.data_ptr(), f.w_f32.data_ptr(), *args, _ptr(res),
+                                            out.data_ptr(), st), "rtseg_conv_dense")
+    elif f.kind == "deconv":
+        if allow_tc and dt == BF16 and f.w_tc is not None and lib.rtseg_deconv3x3s2_tc_supported(C.byref(d)):
+            _lib.check(lib.rtseg_deconv3x3s2_tc(C.byref(d), x.data_ptr(), f.w_tc.data_ptr(), *args, _ptr(out),
+                                                _ptr(labels), st), "rtseg_deconv3x3s2_tc")
+        else:
+            if out is None:  # the CUDA-core deconv takes its argmax from materialised logits
+                out = empty_nhwc(n, f.cout, ho, wo, x.dtype, x.device)
+                d.y_ctotal = f.cout
+            _lib.check(lib.rtseg_deconv3x3s2(C.byref(d), x.data_ptr(), f.w_f32.data_ptr(), *args, out.data_ptr(),
+                                             _ptr(labels), st), "rtseg_deconv3x3s2")
+    else:
+        raise ValueError(f.kind)
+    return out
+
+
+def stem(f: Folded, x: torch.Tensor, pool: bool, out_dtype: torch.dtype, out: Optional[torch.Tensor] = None,
+         y_coff: int = 0) -> torch.Tensor:
+    """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor."""
+    _require_cuda(x, "stem")
+    n, cin, h, w = x.shape
+    if x.is_contiguous():
+        nchw = 1
+    elif is_nhwc(x):
+        nchw = 0
+    else:
+        x, nchw = x.contiguous(), 1
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    ctot = f.cout + (cin if pool else 0)
+    if out is None:
+        out = empty_nhwc(n, ctot, ho, wo, out_dtype, x.device)
+    d = _desc(f, n, h, w, _dtype_code(out_dtype), cin, 0, out.shape[1], y_coff)
+    _lib.check(_lib.load().rtseg_stem(C.byref(d), nchw, _dtype_code(x.dtype), 1 if pool else 0, x.data_ptr(),
+                                      f.w_f32.data_ptr(), _ptr(f.scale), _ptr(f.shift), _ptr(f.slope), out.data_ptr(),
+                                      _stream()), "rtseg_stem")
+    return out
+
+
+def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor, y_coff: int, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    _require_cuda(x, "maxpool3x3s2")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct
+    d = ConvDesc(n, h, w, c, c, 3, 3, 2, 1, 1, 1, 1, _dtype_code(x.dtype), 0, 0.0, 0.0, 0, 0, x_ct, x_coff,
+                 out.shape[1], y_coff, 0, 0)
+    _lib.check(_lib.load().rtseg_maxpool3x3s2(C.byref(d), x.data_ptr(), out.data_ptr(), _stream()), "rtseg_maxpool3x3s2")
+    return out
+
+
+# -------------------------------------------------------------------- head ops ----
+def upsample_bilinear(x: torch.Tensor, size: Tuple[int, int], align_corners: bool, out: Optional[torch.Tensor] = None,
+                      y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    _require_cuda(x, "upsample_bilinear")
+    if not is_nhwc(x):
+        x = to_nhwc(x)
+    n, x_ct, hi, wi = x.shape
+    c = c if c is not None else x_ct
+    ho, wo = int(size[0]), int(size[1])
+    if out is None:
+        out = empty_nhwc(n, c, ho, wo, x.dtype, x.device)
+    _lib.check(_lib.load().rtseg_upsample_bilinear(n, hi, wi, c, ho, wo, int(bool(align_corners)), _dtype_code(x.dtype),
+                                                   x.data_ptr(), x_ct, x_coff, out.data_ptr(), out.shape[1], y_coff,
+                                                   _stream()), "rtseg_upsample_bilinear")
+    return out
+
+
+def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: bool = True, *,
+                    out_dtype: torch.dtype = torch.uint8, target: Optional[torch.Tensor] = None,
+                    confmat: Optional[torch.Tensor] = None, ignore_index: int = 255,
+                    want_labels: bool = True) -> Optional[torch.Tensor]:
+    """Fused F.interpolate(bilinear) + max(dim=1)[1] (+ confusion-matrix update).
+
+    Replaces reference models/fastscnn.py:30 followed by core/seg_trainer.py:172 /
+    utils/metrics.py.  `logits` is the low-resolution [N, C, h, w] tensor.
+    """
+    _require_cuda(logits, "upsample_argmax")
+    x = to_nhwc(logits)
+    n, c, hi, wi = x.shape
+    ho, wo = int(size[0]), int(size[1])
+    l8 = l64 = None
+    if want_labels:
+        if out_dtype == torch.uint8:
+            l8 = torch.empty((n, ho, wo), dtype=torch.uint8, device=x.device)
+        elif out_dtype == torch.int64:
+            l64 = torch.empty((n, ho, wo), dtype=torch.int64, device=x.device)
+        else:
+            raise TypeError("labels are uint8 or int64")
+    if (target is None) != (confmat is None):
+        raise ValueError("target and confmat go together")
+    if target is not None:
+        if target.dtype != torch.int64 or tuple(target.shape) != (n, ho, wo) or not target.is_contiguous():
+            raise ValueError("target must be a contiguous int64 [N, H, W] tensor")
+        if confmat.dtype != torch.int64 or tuple(confmat.shape) != (c, c) or not confmat.is_contiguous():
+            raise ValueError("confmat must be a contiguous int64 [C, C] tensor")
+    _lib.check(_lib.load().rtseg_upsample_argmax(n, hi, wi, c, ho, wo, int(bool(align_corners)), _dtype_code(x.dtype),
+                                                 x.data_ptr(), _ptr(l8), _ptr(l64), _ptr(target), int(ignore_index),
+                                                 _ptr(confmat), _stream()), "rtseg_upsample_argmax")
+    return l8 if l8 is not None else l64
+
+
+def argmax_channels(x: torch.Tensor, out_dtype: torch.dtype = torch.int64) -> torch.Tensor:
+    """preds.max(dim=1)[1] (reference core/seg_trainer.py:172) for NCHW or NHWC storage."""
+    _require_cuda(x, "argmax_channels")
+    n, c, h, w = x.shape
+    out = torch.empty((n, h, w), dtype=out_dtype, device=x.device)
+    l8, l64 = (out, None) if out_dtype == torch.uint8 else (None, out)
+    if out_dtype not in (torch.uint8, torch.int64):
+        raise TypeError("labels are uint8 or int64")
+    lib = _lib.load()
+    if is_nhwc(x) and not (x.is_contiguous() and c > 1 and h * w > 1):
+        _lib.check(lib.rtseg_argmax_nhwc(n * h * w, c, c, _dtype_code(x.dtype), x.data_ptr(), _ptr(l8), _ptr(l64),
+                                         _stream()), "rtseg_argmax_nhwc")
+    else:
+        x = x.contiguous()
+        _lib.check(lib.rtseg_argmax_nchw(n, c, h * w, _dtype_code(x.dtype), x.data_ptr(), _ptr(l8), _ptr(l64),
+                                         _stream()), "rtseg_argmax_nchw")
+    return out
+
+
+def confmat_update(confmat: torch.Tensor, pred: torch.Tensor, target: torch.Tensor, ignore_index: int = 255,
+                   bad_count: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _require_cuda(pred, "confmat_update")
+    c = confmat.shape[0]
+    if confmat.dtype != torch.int64 or not confmat.is_contiguous() or confmat.shape != (c, c):
+        raise ValueError("confmat must be a contiguous int64 [C, C] tensor")
+    if pred.dtype not in (torch.uint8, torch.int64) or target.dtype != torch.int64:
+        raise TypeError("pred must be uint8/int64 and target int64")
+    if pred.numel() != target.numel():
+        raise ValueError("pred and target differ in size")
+    pred, target = pred.contiguous(), target.contiguous()
+    _lib.check(_lib.load().rtseg_confmat_update(pred.numel(), c, int(ignore_index), pred.data_ptr(),
+                                                int(pred.dtype == torch.int64), target.data_ptr(), confmat.data_ptr(),
+                                                _ptr(bad_count), _stream()), "rtseg_confmat_update")
+    return confmat
+
+
+def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    _require_cuda(x, "adaptive_avgpool")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct
+    out = empty_nhwc(n, c, p, p, x.dtype, x.device)
+    _lib.check(_lib.load().rtseg_adaptive_avgpool(n, h, w, c, p, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                                  out.data_ptr(), _stream()), "rtseg_adaptive_avgpool")
+    return out
+
+
+def tc_timeout_flag() -> int:
+    return int(_lib.load().rtseg_tc_timeout_flag(_stream()))

@@ -1,0 +1,38 @@
+"""Shared helpers for the test-suite (fixtures on disk, tolerances, oracle glue)."""
+from __future__ import annotations
+
+import json
+import os
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+
+# BASELINE.json north_star tolerances
+TOL_FP32 = 1e-4      # max |err| / max |ref|
+TOL_BF16 = 2e-2
+ARGMAX_AGREE_FP32 = 0.999
+
+
+def load_specs():
+    with open(os.path.join(GOLDEN, "state_specs.json")) as f:
+        raw = json.load(f)
+    return {k: {**v, "spec": [(a, tuple(b), c) for a, b, c in v["spec"]]} for k, v in raw.items()}
+
+
+def load_net_outputs():
+    return dict(np.load(os.path.join(GOLDEN, "net_outputs.npz")))
+
+
+def rel_err(out: torch.Tensor, ref: torch.Tensor) -> float:
+    """max-abs error over max-abs reference (SURVEY §8c tolerance definition)."""
+    out, ref = out.detach().float().cpu(), ref.detach().float().cpu()
+    denom = ref.abs().max().item()
+    return (out - ref).abs().max().item() / (denom if denom > 0 else 1.0)
+
+
+def seeded(shape, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(shape, generator=g) * scale

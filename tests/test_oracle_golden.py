@@ -1,0 +1,84 @@
+"""CPU: the oracle restatement against vectors produced by the real reference (tests/golden)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_head, ref_nets, ref_ohem
+from tests.helpers import GOLDEN, load_net_outputs, load_specs, rel_err
+
+
+@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("tag,perturb", [("perturbed", True), ("identity_bn", False)])
+def test_net_restatement_matches_reference_vectors(name, tag, perturb):
+    specs, golden = load_specs(), load_net_outputs()
+    sd = ref_nets.make_state(specs[name]["spec"], seed=1, perturb_bn=perturb)
+    x = ref_nets.make_input(0, 1, 32, 64)
+    with torch.no_grad():
+        y = ref_nets.FORWARD[name](sd, x)
+    ref = torch.from_numpy(golden[f"{name}.{tag}"])
+    assert y.shape == ref.shape
+    assert rel_err(y, ref) < 1e-5
+    assert (y.argmax(1) == ref.argmax(1)).float().mean().item() >= 0.9999
+
+
+def test_param_counts_match_readme():
+    # README.md:148,153 "my" column; SURVEY §4 known answers
+    specs = load_specs()
+    assert specs["erfnet"]["n_params"] == 2065458
+    assert specs["fastscnn"]["n_params"] == 1023769
+
+
+def test_ohem_restatement_matches_reference_losses():
+    with open(os.path.join(GOLDEN, "ohem_cases.json")) as f:
+        cases = json.load(f)
+    branches = []
+    for c in cases:
+        g = torch.Generator().manual_seed(100 + c["case"])
+        logits = torch.randn((2, 19, 24, 40), generator=g)
+        labels = torch.randint(0, 19, (2, 24, 40), generator=g)
+        if c["margin"]:
+            logits.scatter_add_(1, labels.unsqueeze(1), torch.full((2, 1, 24, 40), c["margin"]))
+        labels[torch.rand((2, 24, 40), generator=g) < c["ignore_frac"]] = 255
+        logits.requires_grad_(True)
+        loss, branch = ref_ohem.ohem_ce_loss(logits, labels, 0.7, 255)
+        loss.backward()
+        branches.append(branch)
+        assert abs(float(loss) - c["loss"]) <= 1e-6 * max(1.0, abs(c["loss"]))
+        assert abs(float(logits.grad.abs().sum()) - c["grad_abs_sum"]) <= 1e-5 * c["grad_abs_sum"]
+    assert set(branches) == {0, 1}, "golden cases must exercise both OHEM branches"
+
+
+def test_ohem_all_ignored_is_nan():
+    logits = torch.randn(1, 19, 4, 4)
+    labels = torch.full((1, 4, 4), 255)
+    loss, _ = ref_ohem.ohem_ce_loss(logits, labels)
+    assert torch.isnan(loss)  # empty selection -> NaN
+
+
+def test_confusion_matrix_restatement():
+    rng = np.random.default_rng(0)
+    pred = rng.integers(0, 19, size=5000)
+    target = rng.integers(0, 19, size=5000)
+    target[rng.random(5000) < 0.1] = 255
+    cm = ref_head.confusion_matrix(pred, target, 19, 255)
+    assert cm.dtype == np.int64 and cm.shape == (19, 19)
+    assert (cm == ref_head.confusion_matrix_loops(pred, target, 19, 255)).all()
+    assert cm.sum() == (target != 255).sum()
+    # empty / all ignored
+    assert ref_head.confusion_matrix(np.zeros(0, int), np.zeros(0, int), 19).sum() == 0
+    assert ref_head.confusion_matrix(pred, np.full(5000, 255), 19).sum() == 0
+
+
+def test_iou_known_answer():
+    cm = np.array([[3, 1, 0], [2, 4, 0], [0, 0, 0]], dtype=np.int64)
+    iou = ref_head.iou_from_confmat(cm)
+    np.testing.assert_allclose(iou, [3 / 6, 4 / 7, 0.0], rtol=1e-6)
+    assert abs(ref_head.miou(cm) - (3 / 6 + 4 / 7) / 3) < 1e-6  # absent class counts as 0
+
+
+def test_upsample_argmax_first_max_on_ties():
+    x = torch.zeros(1, 3, 2, 2)  # all ties -> index 0 everywhere
+    assert (ref_head.upsample_argmax(x, (8, 8)) == 0).all()
