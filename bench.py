@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — images/s at 1024x2048 on N B200s (BASELINE.json metric), one JSON line on rank 0.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn] [--batch B]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
+
+A step = one forward pass of the workload over one batch of synthetic images per GPU
+(default: ERFNet, batch 16, 1024x2048 = BASELINE.json configs[1]); ranks shard by batch with no
+data-path collective (weak scaling).  `value` is device-timed with inputs resident in HBM;
+`e2e` goes through the public host API (pinned host images in, class map out) with both copies
+inside the timed region.  See DESIGN.md §Measurement for the roofline arithmetic.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W, NUM_CLASS = 1024, 2048, 19
+DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32}
+WORKLOAD_NAME = {
+    "erfnet": "ERFNet inference batch {b} at 1024x2048 (BASELINE configs[1])",
+    "fastscnn": "Fast-SCNN inference batch {b} at 1024x2048 (BASELINE configs[2])",
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="rtseg", choices=["rtseg", "reference"])
+    ap.add_argument("--workload", default="erfnet", choices=["erfnet", "fastscnn"])
+    ap.add_argument("--batch", type=int, default=0, help="images per GPU per step (default 16 ERFNet / 32 Fast-SCNN)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------- CPU baseline ----
+def cpu_reference_run(workload: str, steps: int, warmup: int):
+    """The reference's CPU implementation of the path: oracle port (functional fp32 PyTorch on the
+    host cores, same op sequence as the reference modules — the Python reference itself cannot
+    travel to the GPU box).  One step = ONE 1024x2048 image (bounded sample of the batch)."""
+    import torch
+    from oracle import ref_nets
+    from tests.helpers import load_specs
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = load_specs()[workload]["spec"]
+    sd = ref_nets.make_state(spec, 1, True)
+    x = ref_nets.make_input(0, 1, H, W)
+    fwd = ref_nets.FORWARD[workload]
+    with torch.no_grad():
+        for _ in range(warmup):
+            fwd(sd, x)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fwd(sd, x)
+        dt = time.perf_counter() - t0
+    return {"value": steps / dt, "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} forward passes of 1 image 1x3x{H}x{W} fp32 after {warmup} warm-up "
+                      f"(oracle/ref_nets.py, torch CPU)", "ms_per_image": 1e3 * dt / steps}
+
+
+# --------------------------------------------------------------------------- clocks ----
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, power, reasons = [], [], [], set()
+        for r in self.rows:
+            f = [t.strip() for t in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+                power.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, flag in zip(self.NAMES, f[3:7]):
+                if flag.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------- dominant kernel ----
+def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, peak_src: str):
+    """Times the dominant kernel family alone, launch by launch, with CUDA events on the launch stream.
+
+    ERFNet: the tcgen05 implicit-GEMM kernel behind the 68 dense 3x1/1x3 dilated convs of the
+    NonBt1D blocks (93 % of the net's FLOPs, 79 % of its bytes).  Fast-SCNN: the NHWC depthwise kernel.
+    achieved = sum(algorithmic bytes per launch) / sum(event-timed duration per launch) over one
+    forward's launches of that family; algorithmic bytes = (in + out [+ residual]) elements x 2 B
+    + weights + 8 B/channel of folded BN.
+    """
+    import torch
+    from rtseg_b200 import nets, ops
+    from rtseg_b200.modules import DWConvBNAct
+
+    dev = torch.device("cuda", torch.cuda.current_device())
+    reps, total_bytes, total_ms, launches, per_cfg = 5, 0.0, 0.0, 0, {}
+    stream = torch.cuda.current_stream()
+
+    def time_call(fn):
+        fn()
+        stream.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        e1.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    if workload == "erfnet":
+        res_hw = {64: (256, 512), 128: (128, 256), 16: (512, 1024)}
+        for blk in [m for m in model.modules() if isinstance(m, nets.NonBt1DBlock)]:
+            c = blk.conv[0][0].in_channels
+            h, w = res_hw[c]
+            key = (c, blk.conv[2][0].dilation[0])
+            if key not in per_cfg:
+                x = torch.randn((batch, c, h, w), device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+                r = torch.randn_like(x)
+                ms = [time_call(lambda i=i: blk.conv[i](x)) for i in range(3)]
+                ms.append(time_call(lambda: blk.conv[3](x, res=r, res_mode=ops.RES_PRE, bn=blk.bn_act[0],
+                                                        act=blk.bn_act[1].activation)))
+                elems = batch * c * h * w
+                wbytes = 3 * c * c * 2 + 8 * c
+                by = [2 * elems * 2 + wbytes] * 3 + [3 * elems * 2 + wbytes]
+                per_cfg[key] = (ms, by)
+                del x, r
+            ms, by = per_cfg[key]
+            total_ms += sum(ms)
+            total_bytes += sum(by)
+            launches += 4
+        kernel = "conv_tc_kernel (tcgen05 implicit GEMM, 3x1/1x3 dilated, fused BN/act/residual)"
+    else:
+        x_in = torch.randn((batch, 3, H, W), device=dev)
+        shapes = {}
+        hooks = []
+        for m in model.modules():
+            if isinstance(m, DWConvBNAct):
+                hooks.append(m.register_forward_pre_hook(lambda mod, inp: shapes.__setitem__(mod, tuple(inp[0].shape))))
+        with torch.no_grad():
+            model.lowres_logits(x_in)
+        for hk in hooks:
+            hk.remove()
+        del x_in
+        for m, shp in shapes.items():
+            x = torch.randn(shp, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+            with torch.no_grad():
+                y = m(x)
+                ms = time_call(lambda: m(x))
+            total_ms += ms
+            total_bytes += (x.numel() + y.numel()) * 2 + m[0].weight.numel() * 4 + 8 * y.shape[1]
+            launches += 1
+            del x, y
+        kernel = "dw_win_kernel / dw_vec_kernel (NHWC depthwise 3x3 + BN + act)"
+    achieved = total_bytes / (total_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 1), "peak": peak_gbs, "unit": "GB/s",
+            "frac": round(achieved / peak_gbs, 4), "traffic": None, "peak_source": peak_src,
+            "launches_per_step": launches, "bytes_per_step": int(total_bytes), "ms_per_step": round(total_ms, 4),
+            "frac_of_8TBps_nominal": round(achieved / 8000.0, 4)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+# ---------------------------------------------------------------------------- main ----
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    batch = args.batch or DEFAULT_BATCH[args.workload]
+    workload_name = WORKLOAD_NAME[args.workload].format(b=batch)
+    metric = f"images/sec @1024x2048 ({'ERFNet' if args.workload == 'erfnet' else 'Fast-SCNN'})"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        base = cpu_reference_run(args.workload, max(1, args.steps), max(0, args.warmup))
+        line = {
+            "impl": "reference", "metric": metric, "value": round(base["value"], 4), "unit": "images/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(base["ms_per_image"], 2), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name, "sample": "1 image per step on the host cores",
+                       "weights": "seeded random init (oracle.ref_nets.make_state)"},
+            "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": round(base["value"], 4), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU path in rtseg_b200)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import rtseg_b200
+    from rtseg_b200 import _lib
+
+    _lib.check(_lib.load().rtseg_device_check(), "rtseg_device_check")
+    torch.manual_seed(1)  # the reference's seed (configs/base_config.py:70); default random init
+    model = rtseg_b200.nets.MODEL_HUB[args.workload](num_class=NUM_CLASS).eval().cuda()
+    model.set_act_dtype(torch.bfloat16)
+    eng = rtseg_b200.InferenceEngine(model, batch=batch, height=H, width=W, use_graph=True, slots=2)
+
+    # synthetic inputs: per-rank seeds, resident on the device for `value`, pinned on the host for `e2e`
+    g = torch.Generator(device="cuda").manual_seed(rank)
+    for s in eng.slots:
+        s.x.copy_(torch.randn(s.x.shape, generator=g, device="cuda"))
+    host_in = [torch.randn(eng.slots[0].x.shape).pin_memory() for _ in range(2)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) -------------------------------------------------------
+    stream = eng.slots[0].stream
+    for _ in range(max(3, args.warmup)):
+        eng.run_device(0)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.launch_count()
+    e0.record(stream)
+    for _ in range(args.steps):
+        eng.run_device(0)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    eager_launches = _lib.launch_count() - launches0  # 0 under graph replay; the graph replays launches_per_step
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([dev_ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    value = world * batch * args.steps / (dev_ms * 1e-3)
+
+    # ---- end to end through the public API (pinned host in, host class map out) --------------------
+    for i in range(2):
+        eng(host_in[i])
+    barrier()
+    t0 = time.perf_counter()
+    pending = []
+    for i in range(args.steps):
+        pending.append(eng.submit(host_in[i % 2]))
+        if len(pending) == 2:
+            eng.collect(pending.pop(0))
+    while pending:
+        eng.collect(pending.pop(0))
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * batch * args.steps / float(t.item())
+
+    line = None
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        roof = dominant_kernel_roofline(model, args.workload, batch, peak, peak_src)
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            b = cpu_reference_run(args.workload, 3, 1)
+            cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            cpu["value"] = round(cpu["value"], 4)
+        line = {
+            "metric": metric, "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name, "per_gpu_batch": batch, "global_batch": batch * world,
+                       "weights": "random init, torch.manual_seed(1)", "activations": "NHWC bf16, fp32 accumulate",
+                       "output": "uint8 class map (fused argmax head)",
+                       "l2": f"input {eng.h2d_bytes() / 1e6:.0f} MB and every activation tensor exceed the 126 MB L2",
+                       "parallelism": f"dp{world}: batch sharded across ranks, no data-path collective",
+                       "cuda_graph": True},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 2), "unit": "images/s", "h2d_bytes_per_step": eng.h2d_bytes(),
+                    "d2h_bytes_per_step": eng.d2h_bytes(), "pipelined_slots": 2},
+            "gpu_launches": int(eng.launches_per_step * args.steps + eager_launches),
+            "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

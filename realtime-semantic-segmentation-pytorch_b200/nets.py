@@ -35,6 +35,8 @@ def _param_dtype(m: nn.Module) -> torch.dtype:
 class InitialBlock(nn.Module):
     """cat([ConvBNAct(in, out-in, 3, stride 2)(x), MaxPool2d(3,2,1)(x)]) — reference models/enet.py:38-48."""
 
+    act_dtype: Optional[torch.dtype] = None  # storage type of the activations this stem emits (None: parameter dtype)
+
     def __init__(self, in_channels, out_channels, act_type, kernel_size=3, **kwargs):
         super().__init__()
         assert out_channels > in_channels, "out_channels should be larger than in_channels.\n"
@@ -49,7 +51,7 @@ class InitialBlock(nn.Module):
         if post is not None:
             raise NotImplementedError("non-pointwise activation in InitialBlock")
         if cin <= 4 and cconv <= 32 and conv.kernel_size == (3, 3):
-            return ops.stem(folded, x, pool=True, out_dtype=_param_dtype(self.conv))
+            return ops.stem(folded, x, pool=True, out_dtype=self.act_dtype or _param_dtype(self.conv))
         x = ops.to_nhwc(x)
         n, _, h, w = x.shape
         out = ops.empty_nhwc(n, cconv + cin, (h - 1) // 2 + 1, (w - 1) // 2 + 1, x.dtype, x.device)
@@ -108,6 +110,12 @@ class ERFNet(nn.Module):
         self.layer23 = DeConvBNAct(16, num_class, act_type=act_type)
         self.num_class = num_class
 
+    def set_act_dtype(self, dtype: Optional[torch.dtype]):
+        """bf16 activations with fp32 master parameters: the stem converts while it reads the fp32 image,
+        BN is folded in fp32 and the weights are rounded to bf16 once (SURVEY §7 'hard parts')."""
+        self.layer1.act_dtype = dtype
+        return self
+
     def _trunk(self, x):
         x = self.layer1(x)
         x = self.layer2(x)
@@ -156,6 +164,8 @@ class InvertedResidual(nn.Module):
 class LearningToDownsample(nn.Sequential):
     """reference models/fastscnn.py:35-41"""
 
+    act_dtype: Optional[torch.dtype] = None
+
     def __init__(self, in_channels, out_channels, hid_channels=[32, 48], act_type="relu"):
         super().__init__(
             ConvBNAct(in_channels, hid_channels[0], 3, 2, act_type=act_type),
@@ -171,7 +181,7 @@ class LearningToDownsample(nn.Sequential):
             folded, post = stem._folded()
             if post is not None:
                 raise NotImplementedError("non-pointwise activation in the stem")
-            x = ops.stem(folded, x, pool=False, out_dtype=_param_dtype(stem))
+            x = ops.stem(folded, x, pool=False, out_dtype=self.act_dtype or _param_dtype(stem))
         else:
             x = stem(x)
         return self[2](self[1](x))
@@ -237,6 +247,10 @@ class FastSCNN(nn.Module):
         self.feature_fusion = FeatureFusionModule(64, 128, 128, act_type=act_type)
         self.classifier = Classifier(128, num_class, act_type=act_type)
         self.num_class = num_class
+
+    def set_act_dtype(self, dtype: Optional[torch.dtype]):
+        self.learning_to_downsample.act_dtype = dtype
+        return self
 
     def lowres_logits(self, x):
         hi = self.learning_to_downsample(x)

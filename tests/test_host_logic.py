@@ -1,0 +1,162 @@
+"""CPU: host-side logic — C-ABI surface, state-dict layout, BN folding, error behaviour, sharding."""
+import copy
+import ctypes
+import os
+import re
+import types
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+import rtseg_b200
+from oracle import ref_blocks, ref_head, ref_nets
+from rtseg_b200 import _lib, metrics, modules, nets, ops, parallel
+from tests.helpers import load_specs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "rtseg.h")).read()
+    declared = set(re.findall(r"\b(rtseg_[a-z0-9_]+)\s*\(", header))
+    declared -= {"rtseg_status", "rtseg_dtype", "rtseg_act", "rtseg_res_mode"}
+    assert len(declared) >= 25
+    lib = _lib.load()
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"librtseg.so does not export {name}"
+    assert declared == set(_lib.PROTOTYPES), "ctypes prototypes and include/rtseg.h disagree"
+    assert lib.rtseg_version() == 100
+    assert lib.rtseg_ohem_workspace_bytes() % 256 == 0
+
+
+def test_conv_desc_matches_header_layout():
+    header = open(os.path.join(ROOT, "include", "rtseg.h")).read()
+    body = header[header.index("typedef struct rtseg_conv_desc {"):header.index("} rtseg_conv_desc;")]
+    fields = re.findall(r"\b(?:int32_t|float)\s+([a-z0-9_, ]+);", body)
+    names = [n.strip() for grp in fields for n in grp.split(",")]
+    assert names == [f[0] for f in _lib.ConvDesc._fields_]
+    assert ctypes.sizeof(_lib.ConvDesc) == 4 * len(names)
+
+
+def test_out_hw_and_validation_without_gpu():
+    lib = _lib.load()
+    d = _lib.ConvDesc(1, 128, 256, 64, 64, 3, 1, 1, 16, 16, 0, 1, 1, 1, 0, 0, 0, 0, 64, 0, 64, 0, 0, 0)
+    ho, wo = ctypes.c_int32(), ctypes.c_int32()
+    assert lib.rtseg_out_hw(ctypes.byref(d), ctypes.byref(ho), ctypes.byref(wo)) == 0
+    assert (ho.value, wo.value) == (128, 256)
+    d.kh, d.pad_h, d.dil, d.stride = 3, 1, 1, 2
+    d.kw, d.pad_w = 3, 1
+    lib.rtseg_out_hw(ctypes.byref(d), ctypes.byref(ho), ctypes.byref(wo))
+    assert (ho.value, wo.value) == (64, 128)
+    # tensor-core eligibility is pure host logic
+    assert lib.rtseg_conv_tc_supported(ctypes.byref(d)) == 1
+    d.cin = 13
+    d.x_ctotal = 13
+    assert lib.rtseg_conv_tc_supported(ctypes.byref(d)) == 0
+    # invalid descriptor -> negative status and a message, no crash
+    d.cin = 0
+    assert lib.rtseg_conv_dense(ctypes.byref(d), None, None, None, None, None, None, None, None) < 0
+    assert b"extent" in lib.rtseg_last_error()
+
+
+@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+def test_state_dict_layout_equals_reference(name):
+    spec = load_specs()[name]
+    model = nets.MODEL_HUB[name](num_class=19)
+    ours = [(k, tuple(v.shape), str(v.dtype).replace("torch.", "")) for k, v in model.state_dict().items()]
+    assert ours == spec["spec"]
+    assert sum(p.numel() for p in model.parameters()) == spec["n_params"]
+    # a reference-shaped state dict loads strictly, caches never leak into it
+    sd = ref_nets.make_state(spec["spec"], 1)
+    model.load_state_dict(sd, strict=True)
+    assert not any("rtseg" in k for k in model.state_dict())
+
+
+def test_fold_matches_unfused_arithmetic():
+    torch.manual_seed(0)
+    m = modules.PWConvBNAct(8, 5, act_type="prelu")
+    with torch.no_grad():
+        m[1].running_mean.normal_()
+        m[1].running_var.uniform_(0.5, 1.5)
+        m[1].weight.normal_()
+        m[1].bias.normal_()
+    m.eval()
+    f, post = ops.fold_conv(m[0], m[1], m[2].activation)
+    assert post is None and f.kind == "dense" and f.act == _lib.ACT_CODES["prelu"]
+    x = torch.randn(2, 8, 4, 4)
+    ref = m[1](m[0](x))
+    w = f.w_f32.reshape(8, 5)  # [1][1][cin][cout]
+    y = torch.einsum("nchw,co->nohw", x, w) * f.scale.view(1, -1, 1, 1) + f.shift.view(1, -1, 1, 1)
+    assert torch.allclose(y, ref, atol=1e-5)
+    assert f.slope.shape == (5,) and torch.allclose(f.slope, torch.full((5,), 0.25))
+    assert f.w_tc is None  # cin % 16 != 0
+    m2 = modules.ConvBNAct(32, 19, (3, 1), dilation=4).eval()
+    f2, _ = ops.fold_conv(m2[0], m2[1], m2[2].activation)
+    assert f2.w_tc.shape == (3, 32, 32) and f2.w_tc.dtype == torch.bfloat16
+    assert (f2.w_tc[:, 19:] == 0).all() and (f2.pad_h, f2.pad_w, f2.dil) == (4, 0, 4)
+
+
+def test_fold_cache_invalidation_and_deepcopy():
+    m = modules.ConvBNAct(4, 4, 3).eval()
+    a = m._folded()
+    assert m._folded() is a
+    with torch.no_grad():
+        m[0].weight.add_(1.0)
+    b = m._folded()
+    assert b is not a
+    m.load_state_dict(copy.deepcopy(m.state_dict()))
+    assert m._folded() is not b
+    c = copy.deepcopy(m)  # EMA path, reference utils/model_ema.py:20
+    assert "_rtseg_cache" not in c.__dict__ and list(c.state_dict()) == list(m.state_dict())
+
+
+def test_error_behaviour_mirrors_reference():
+    with pytest.raises(NotImplementedError):
+        modules.Activation("swishish")  # reference models/modules.py:125-126
+    with pytest.raises(TypeError):
+        modules.ConvBNAct(3, 3, kernel_size=3.0)
+    with pytest.raises(TypeError):  # kwargs reach the activation only (App. B.2: regseg's groups= crashes)
+        modules.ConvBNAct(3, 3, 3, groups=2)
+    m = modules.ConvBNAct(3, 8).eval()
+    with pytest.raises(RuntimeError, match="no CPU implementation"):
+        m(torch.randn(1, 3, 8, 8))
+    with pytest.raises(AssertionError):
+        nets.InitialBlock(16, 16, "relu")  # reference models/enet.py:41
+    cfg = types.SimpleNamespace(model="nope", num_class=19, use_aux=False, use_detail_head=False)
+    with pytest.raises(NotImplementedError):
+        nets.get_model(cfg)
+
+
+def test_activation_hub_has_the_reference_names():
+    assert set(modules.Activation._HUB) == {
+        "relu", "relu6", "leakyrelu", "prelu", "celu", "elu", "hardswish", "hardtanh", "gelu", "glu", "selu", "silu",
+        "sigmoid", "softmax", "tanh", "none"}
+    assert isinstance(modules.Activation("PReLU").activation, nn.PReLU)
+    assert ops.act_spec(nn.LeakyReLU(0.2))[:2] == (_lib.ACT_CODES["leakyrelu"], pytest.approx(0.2))
+    assert ops.act_spec(nn.GLU())[4] is not None
+
+
+def test_iou_host_function_equals_oracle():
+    rng = np.random.default_rng(1)
+    cm = rng.integers(0, 1000, size=(19, 19)).astype(np.int64)
+    cm[5] = 0
+    cm[:, 5] = 0
+    ours = metrics.iou_from_confmat(torch.from_numpy(cm)).numpy()
+    np.testing.assert_array_equal(ours, ref_head.iou_from_confmat(cm))
+    assert ours[5] == 0.0
+
+
+def test_ohem_threshold_value():
+    assert rtseg_b200.OhemCELoss(0.7).thresh == pytest.approx(0.35667494, abs=1e-7)
+
+
+def test_shard_range_partitions_batch():
+    for total in (1, 7, 16, 32):
+        for world in (1, 2, 4, 8):
+            spans = [parallel.shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
