@@ -11,6 +11,24 @@ import torch.nn.functional as F
 
 BN_EPS = 1e-5  # nn.BatchNorm2d default, never overridden in the reference
 
+# Optional emulation of reduced-precision STORAGE (not arithmetic): when set to torch.bfloat16 every
+# fused layer's output, and the weights of every tensor-core-eligible dense conv (groups == 1,
+# cin % 16 == 0), are rounded to bf16 exactly where the CUDA path rounds them; all arithmetic stays
+# fp32.  Used by the bf16 parity tests to separate "the kernel is wrong" from "bf16 has 8 bits".
+STORAGE = None
+
+
+def q(t):
+    """Round a layer output to the emulated storage type."""
+    return t if STORAGE is None else t.to(STORAGE).float()
+
+
+def qw(w, groups=1, transposed=False):
+    cin = w.shape[0] if transposed else w.shape[1] * groups
+    if STORAGE is None or groups != 1 or cin % 16:
+        return w
+    return w.to(STORAGE).float()
+
 
 def activation(x, act_type: str, sd=None, prefix: str = "", **kw):
     """Activation hub of reference models/modules.py:111-131 (the pointwise members)."""
@@ -61,10 +79,10 @@ def _pad(kernel_size, dilation):
 
 def conv_bn_act(x, sd, prefix, kernel_size=3, stride=1, dilation=1, act_type="relu", groups=1, **kw):
     """ConvBNAct (reference models/modules.py:73-85); children `0` conv, `1` bn, `2` activation."""
-    y = F.conv2d(x, sd[prefix + "0.weight"], sd.get(prefix + "0.bias"), stride, _pad(kernel_size, dilation), dilation,
-                 groups)
+    y = F.conv2d(x, qw(sd[prefix + "0.weight"], groups), sd.get(prefix + "0.bias"), stride, _pad(kernel_size, dilation),
+                 dilation, groups)
     y = batch_norm(y, sd, prefix + "1.")
-    return activation(y, act_type, sd, prefix + "2.", **kw)
+    return q(activation(y, act_type, sd, prefix + "2.", **kw))
 
 
 def dw_conv_bn_act(x, sd, prefix, kernel_size, stride=1, dilation=1, act_type="relu", **kw):
@@ -86,10 +104,10 @@ def ds_conv_bn_act(x, sd, prefix, kernel_size, stride=1, dilation=1, act_type="r
 def deconv_bn_act(x, sd, prefix, scale_factor=2, act_type="relu", **kw):
     """DeConvBNAct (reference models/modules.py:89-108): k = 2s-1, p = (k-1)//2, output_padding = s-1."""
     k = 2 * scale_factor - 1
-    y = F.conv_transpose2d(x, sd[prefix + "up_conv.0.weight"], sd.get(prefix + "up_conv.0.bias"), scale_factor,
-                           (k - 1) // 2, scale_factor - 1)
+    y = F.conv_transpose2d(x, qw(sd[prefix + "up_conv.0.weight"], 1, True), sd.get(prefix + "up_conv.0.bias"),
+                           scale_factor, (k - 1) // 2, scale_factor - 1)
     y = batch_norm(y, sd, prefix + "up_conv.1.")
-    return activation(y, act_type, sd, prefix + "up_conv.2.", **kw)
+    return q(activation(y, act_type, sd, prefix + "up_conv.2.", **kw))
 
 
 def initial_block(x, sd, prefix, act_type="relu"):
@@ -104,7 +122,7 @@ def pyramid_pooling(x, sd, prefix, act_type="relu", pool_sizes=(1, 2, 4, 6)):
     size = x.shape[2:]
     feats = [x]
     for i, p in enumerate(pool_sizes, start=1):
-        z = F.adaptive_avg_pool2d(x, p)
-        z = F.conv2d(z, sd[f"{prefix}stage{i}.1.weight"])
-        feats.append(F.interpolate(z, size, mode="bilinear", align_corners=True))
+        z = q(F.adaptive_avg_pool2d(x, p))
+        z = q(F.conv2d(z, qw(sd[f"{prefix}stage{i}.1.weight"])))
+        feats.append(q(F.interpolate(z, size, mode="bilinear", align_corners=True)))
     return pw_conv_bn_act(torch.cat(feats, dim=1), sd, prefix + "conv.", act_type)

@@ -13,10 +13,10 @@ def non_bt_1d(x, sd, prefix, dilation=1, act_type="relu"):
     y = B.conv_bn_act(x, sd, prefix + "conv.0.", (3, 1), 1, 1, "relu")
     y = B.conv_bn_act(y, sd, prefix + "conv.1.", (1, 3), 1, 1, "relu")
     y = B.conv_bn_act(y, sd, prefix + "conv.2.", (3, 1), 1, dilation, "relu")
-    y = F.conv2d(y, sd[prefix + "conv.3.weight"], None, 1, (0, dilation), dilation)
+    y = F.conv2d(y, B.qw(sd[prefix + "conv.3.weight"]), None, 1, (0, dilation), dilation)
     y = y + x
     y = B.batch_norm(y, sd, prefix + "bn_act.0.")
-    return B.activation(y, act_type, sd, prefix + "bn_act.1.")
+    return B.q(B.activation(y, act_type, sd, prefix + "bn_act.1."))
 
 
 def erfnet_forward(sd, x, act_type="relu"):
@@ -46,7 +46,7 @@ def inverted_residual(x, sd, prefix, cin, cout, stride, act_type="relu"):
     y = B.pw_conv_bn_act(x, sd, prefix + "conv.0.", act_type)
     y = B.dw_conv_bn_act(y, sd, prefix + "conv.1.", 3, stride, 1, act_type)
     y = B.conv_bn_act(y, sd, prefix + "conv.2.", 1, 1, 1, "none")
-    return x + y if (stride == 1 and cin == cout) else y
+    return B.q(x + y) if (stride == 1 and cin == cout) else y
 
 
 def fastscnn_lowres_logits(sd, x, act_type="relu"):
@@ -65,11 +65,11 @@ def fastscnn_lowres_logits(sd, x, act_type="relu"):
     lo = B.pyramid_pooling(lo, sd, "global_feature_extractor.ppm.", act_type)
     # FeatureFusionModule (:73-93)
     p = "feature_fusion."
-    h = F.conv2d(hi, sd[p + "higher_res_conv.weight"])
-    l = F.interpolate(lo, hi.shape[2:], mode="bilinear", align_corners=True)
+    h = B.q(F.conv2d(hi, B.qw(sd[p + "higher_res_conv.weight"])))
+    l = B.q(F.interpolate(lo, hi.shape[2:], mode="bilinear", align_corners=True))
     l = B.dw_conv_bn_act(l, sd, p + "lower_res_conv.0.", 3, 1, 1, act_type)
-    l = F.conv2d(l, sd[p + "lower_res_conv.1.weight"])
-    y = B.activation(B.batch_norm(h + l, sd, p + "non_linear.0."), act_type, sd, p + "non_linear.1.")
+    l = F.conv2d(l, B.qw(sd[p + "lower_res_conv.1.weight"]))
+    y = B.q(B.activation(B.batch_norm(h + l, sd, p + "non_linear.0."), act_type, sd, p + "non_linear.1."))
     # Classifier (:96-102)
     p = "classifier."
     y = B.ds_conv_bn_act(y, sd, p + "0.", 3, 1, 1, act_type)

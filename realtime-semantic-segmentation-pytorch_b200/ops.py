@@ -419,6 +419,8 @@ def confmat_update(confmat: torch.Tensor, pred: torch.Tensor, target: torch.Tens
         raise TypeError("pred must be uint8/int64 and target int64")
     if pred.numel() != target.numel():
         raise ValueError("pred and target differ in size")
+    if pred.numel() == 0:
+        return confmat
     pred, target = pred.contiguous(), target.contiguous()
     _lib.check(_lib.load().rtseg_confmat_update(pred.numel(), c, int(ignore_index), pred.data_ptr(),
                                                 int(pred.dtype == torch.int64), target.data_ptr(), confmat.data_ptr(),

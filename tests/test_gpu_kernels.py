@@ -406,13 +406,13 @@ def test_ohem_forward_backward_vs_oracle(margin, ignore_frac, dtype, layout):
     import rtseg_b200
     logits, labels = _ohem_case(7, margin, ignore_frac, (2, 19, 33, 47))
     logits = logits.to(dtype)
-    ref_in = logits.float().requires_grad_(True)
+    ref_in = logits.float().clone().requires_grad_(True)
     ref_loss, branch = ref_ohem.ohem_ce_loss(ref_in, labels, 0.7, 255)
     ref_loss.backward()
-    lg = logits.cuda()
+    lg = logits.detach().cuda()
     if layout == "nhwc":
         lg = lg.contiguous(memory_format=torch.channels_last)
-    lg.requires_grad_(True)
+    lg = lg.detach().requires_grad_(True)
     loss = rtseg_b200.OhemCELoss(0.7, 255)(lg, labels.cuda())
     (2.0 * loss).backward()  # upstream gradient != 1
     assert abs(loss.item() - ref_loss.item()) <= 1e-5 * max(1.0, abs(ref_loss.item()))
