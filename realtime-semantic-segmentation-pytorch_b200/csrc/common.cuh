@@ -59,7 +59,25 @@ struct Epilogue {
   const float *slope;  // [cout] PReLU slopes or nullptr
   int act, act2, res_mode;
   float p0, p1;
+  // Fast forms chosen on the host (epilogue_mode): 0 = clamp(v, lo, hi) covers none / relu / relu6 /
+  // hardtanh; 1 = max(v,0) + slope[c]*min(v,0) covers prelu; 2 = general switch.
+  int mode;
+  float lo, hi;
 };
+
+static inline int epilogue_mode(int act, int act2, int res_mode, const float *slope, float act_p0, float act_p1,
+                                float &lo, float &hi) {
+  lo = -3.402823466e+38f, hi = 3.402823466e+38f;
+  if (res_mode == RTSEG_RES_POST && act2 != RTSEG_ACT_NONE) return 2;
+  switch (act) {
+    case RTSEG_ACT_NONE: return 0;
+    case RTSEG_ACT_RELU: lo = 0.f; return 0;
+    case RTSEG_ACT_RELU6: lo = 0.f, hi = 6.f; return 0;
+    case RTSEG_ACT_HARDTANH: lo = act_p0, hi = act_p1; return 0;
+    case RTSEG_ACT_PRELU: return slope ? 1 : 2;
+    default: return 2;
+  }
+}
 
 static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scale, const float *shift,
                                      const float *slope) {
@@ -72,6 +90,7 @@ static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scal
   e.res_mode = d->res_mode;
   e.p0 = d->act_p0;
   e.p1 = d->act_p1;
+  e.mode = epilogue_mode(d->act, d->act2, d->res_mode, slope, d->act_p0, d->act_p1, e.lo, e.hi);
   return e;
 }
 
@@ -118,6 +137,35 @@ __device__ __forceinline__ float epilogue_apply(float acc, float res, int c, con
     v = act_apply(v, e.act2, e.p0, e.p1, sl);
   }
   return v;
+}
+
+// One output element with the per-channel affine already in registers.  MODE as in Epilogue::mode.
+template <int MODE>
+__device__ __forceinline__ float epi_elem(float acc, float rv, float sc, float sh, float sl, const Epilogue &e) {
+  float v = e.res_mode == RTSEG_RES_PRE ? acc + rv : acc;
+  v = fmaf(v, sc, sh);
+  if constexpr (MODE == 0) {
+    v = fminf(fmaxf(v, e.lo), e.hi);
+    if (e.res_mode == RTSEG_RES_POST) v += rv;
+  } else if constexpr (MODE == 1) {
+    v = fmaf(sl, fminf(v, 0.f), fmaxf(v, 0.f));
+    if (e.res_mode == RTSEG_RES_POST) v += rv;
+  } else {
+    v = act_apply(v, e.act, e.p0, e.p1, sl);
+    if (e.res_mode == RTSEG_RES_POST) v = act_apply(v + rv, e.act2, e.p0, e.p1, sl);
+  }
+  return v;
+}
+
+// Per-channel epilogue vectors of V consecutive channels (scale = 1, shift = 0, slope = 0 when absent).
+template <int V>
+__device__ __forceinline__ void load_affine(const Epilogue &e, int c0, float (&sc)[V], float (&sh)[V], float (&sl)[V]) {
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    sc[v] = e.scale ? __ldg(e.scale + c0 + v) : 1.f;
+    sh[v] = e.shift ? __ldg(e.shift + c0 + v) : 0.f;
+    sl[v] = (e.slope && e.act == RTSEG_ACT_PRELU) ? __ldg(e.slope + c0 + v) : 0.f;
+  }
 }
 
 // Scalar typed load/store.

@@ -24,7 +24,7 @@ struct DwParams {
 };
 
 // ---- dilation-1 kernel with a sliding register window -----------------------
-template <typename T, int KH, int KW, int S, int PX>
+template <typename T, int KH, int KW, int S, int PX, int MODE>
 __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__restrict__ x,
                                                      const float *__restrict__ wgt, Epilogue ep,
                                                      const T *__restrict__ res, T *__restrict__ y) {
@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
   }
 
   const int64_t pix0 = ((int64_t)n * p.ho + ho) * p.wo + (int64_t)wq * PX;
+  float sc[V], sh[V], sl[V];
+  load_affine<V>(ep, c0, sc, sh, sl);
 #pragma unroll
   for (int i = 0; i < PX; ++i) {
     if (wq * PX + i >= p.wo) break;
@@ -98,13 +100,13 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
     }
     float ov[V];
 #pragma unroll
-    for (int v = 0; v < V; ++v) ov[v] = epilogue_apply(acc[i][v], rv[v], c0 + v, ep);
+    for (int v = 0; v < V; ++v) ov[v] = epi_elem<MODE>(acc[i][v], rv[v], sc[v], sh[v], sl[v], ep);
     Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
   }
 }
 
 // ---- any kernel size / dilation / stride, vectorised over channels ------------
-template <typename T, int PX>
+template <typename T, int PX, int MODE>
 __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__restrict__ x,
                                                      const float *__restrict__ wgt, Epilogue ep,
                                                      const T *__restrict__ res, T *__restrict__ y) {
@@ -154,6 +156,8 @@ __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__rest
   }
 
   const int64_t pix0 = ((int64_t)n * p.ho + ho) * p.wo + (int64_t)wq * PX;
+  float sc[V], sh[V], sl[V];
+  load_affine<V>(ep, c0, sc, sh, sl);
 #pragma unroll
   for (int i = 0; i < PX; ++i) {
     if (wq * PX + i >= p.wo) break;
@@ -166,7 +170,7 @@ __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__rest
     }
     float ov[V];
 #pragma unroll
-    for (int v = 0; v < V; ++v) ov[v] = epilogue_apply(acc[i][v], rv[v], c0 + v, ep);
+    for (int v = 0; v < V; ++v) ov[v] = epi_elem<MODE>(acc[i][v], rv[v], sc[v], sh[v], sl[v], ep);
     Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
   }
 }
@@ -231,12 +235,18 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
     return RTSEG_OK;
   }
   const int cvecs = p.c / V;
-#define RTSEG_DW_WIN(KH_, KW_, S_, PX_)                                                             \
-  do {                                                                                              \
-    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX_) * cvecs;                            \
-    dw_win_kernel<T, KH_, KW_, S_, PX_><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y); \
-    RTSEG_LAUNCH_CHECK("dw_win_kernel");                                                            \
-    return RTSEG_OK;                                                                                \
+#define RTSEG_DW_WIN(KH_, KW_, S_, PX_)                                                                     \
+  do {                                                                                                      \
+    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX_) * cvecs;                                    \
+    const unsigned grid = (unsigned)cdiv(total, threads);                                                   \
+    if (ep.mode == 0)                                                                                       \
+      dw_win_kernel<T, KH_, KW_, S_, PX_, 0><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);                \
+    else if (ep.mode == 1)                                                                                  \
+      dw_win_kernel<T, KH_, KW_, S_, PX_, 1><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);                \
+    else                                                                                                    \
+      dw_win_kernel<T, KH_, KW_, S_, PX_, 2><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);                \
+    RTSEG_LAUNCH_CHECK("dw_win_kernel");                                                                    \
+    return RTSEG_OK;                                                                                        \
   } while (0)
   if (d->dil == 1 && d->kh == 3 && d->kw == 3) {
     if (d->stride == 1) {
@@ -250,7 +260,13 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
   {
     constexpr int PX = 4;
     const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX) * cvecs;
-    dw_vec_kernel<T, PX><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y);
+    const unsigned grid = (unsigned)cdiv(total, threads);
+    if (ep.mode == 0)
+      dw_vec_kernel<T, PX, 0><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
+    else if (ep.mode == 1)
+      dw_vec_kernel<T, PX, 1><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
+    else
+      dw_vec_kernel<T, PX, 2><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
     RTSEG_LAUNCH_CHECK("dw_vec_kernel");
   }
   return RTSEG_OK;

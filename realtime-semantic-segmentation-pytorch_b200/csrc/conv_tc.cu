@@ -7,42 +7,56 @@
 //        D[pixel][cout] = sum_tap  A_tap[pixel][cin] * W_tap[cout][cin]^T
 // with M = 128 output pixels per tile, N = cout (<= 256) and K = taps * cin.
 //
-// Blackwell mapping (one persistent CTA per SM, 192 threads):
-//   warp 0   TMA producer.  For every (tap, 64-channel K block) it issues one
-//            cp.async.bulk.tensor.4d box [KB ch, TW px, TH rows, 1 image] at the
-//            tap's shifted coordinates; TMA's out-of-bounds zero fill IS the
-//            convolution padding.  A stride-2 conv reads four parity views of
-//            the input (one tensor map each), so no strided box is needed.
-//   warp 1   allocates TMEM and issues tcgen05.mma (cta_group::1, kind::f16,
-//            bf16 x bf16 -> fp32) with A and B from 128B/64B/32B-swizzled shared
-//            memory; accumulators live in TMEM, double buffered (2 x N columns)
-//            so the epilogue of tile i overlaps the MMAs of tile i+1.
-//   warps 2-5 epilogue: tcgen05.ld 32 lanes x 16 columns, folded-BN scale and
-//            shift, residual (before or after), activation, bf16 pack, 16-byte
-//            stores; optionally the channel argmax (segmentation labels).
+// Blackwell mapping (one persistent CTA per SM, 320 threads):
+//   warp 0    TMA producer.  For every (tap, 64-channel K block) it issues one
+//             cp.async.bulk.tensor.4d box [KB ch, TW px, TH rows, 1 image] at the
+//             tap's shifted coordinates; TMA's out-of-bounds zero fill IS the
+//             convolution padding.  A stride-2 conv reads four parity views of
+//             the input (one tensor map each), so no strided box is needed.
+//   warp 1    allocates TMEM and issues tcgen05.mma (cta_group::1, kind::f16,
+//             bf16 x bf16 -> fp32), A and B from 128B/64B/32B-swizzled shared
+//             memory.  Accumulators live in TMEM, double buffered, so the
+//             epilogue of tile i overlaps the MMAs of tile i+1.  A transposed
+//             conv keeps FOUR accumulators (one per output parity): each of its
+//             four shifted input tiles is loaded once and feeds up to four MMAs.
+//   warps 2-9 epilogue (two warps per TMEM lane quarter, alternating 16-column
+//             chunks): tcgen05.ld, folded-BN scale/shift from shared memory,
+//             residual (prefetched into registers before the accumulator is
+//             ready), activation, bf16 pack, swizzled st.shared into a staging
+//             tile, then ONE elected thread issues cp.async.bulk.tensor stores —
+//             full 128-byte lines leave the SM, partial tiles are clipped by TMA.
+//             Optional channel argmax (segmentation labels) in the same pass.
 // The weights of one N tile stay resident in shared memory for the lifetime of
-// the CTA (<= 96 KB), the A operand flows through a 4-8 stage mbarrier ring.
+// the CTA, the A operand flows through a 3-8 stage mbarrier ring.
 //
 // Everything here is hand-written PTX; no CUTLASS/CuTe.
 #include <cuda.h>
 
 #include <algorithm>
+#include <cfloat>
 #include <mutex>
 
 #include "common.cuh"
 
 namespace rtseg {
 
-constexpr int kTcThreads = 192;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = 32 * kEpiWarps;
+constexpr int kTcThreads = 64 + kEpiThreads;
 constexpr int kTileM = 128;
 constexpr int kMaxTcTaps = 9;
 constexpr int kMaxStages = 8;
+constexpr int kMaxAcc = 4;
+constexpr int kOutBufs = 2;
+constexpr int kMaxMyChunks = 8;  // 16-column chunks one epilogue warp may own (bn <= 256 split over two warps)
 constexpr uint32_t kSmemBudget = 220 * 1024;
 
 struct TcTap {
-  int16_t map;   // which A tensor map (parity view)
+  int16_t map;  // which A tensor map (parity view)
   int16_t dy, dx;
-  int16_t widx;  // weight tap index
+  int16_t nops;      // MMAs fed by this A tile
+  int16_t widx[4];   // weight tap of each MMA
+  int16_t acc[4];    // accumulator of each MMA
 };
 
 struct TcParams {
@@ -51,18 +65,24 @@ struct TcParams {
   int tiles_w, tiles_h;   // tiles per image along w / h
   int64_t num_m_tiles;
   int oh, ow;             // full output size
-  int ostride, oy0, ox0;  // output pixel = grid * ostride + o?0
+  int ostride;            // output pixel = grid * ostride + (oy0, ox0)[acc]
+  int oy0[kMaxAcc], ox0[kMaxAcc];
+  int nacc;
   int cin, cout;          // logical
-  int cout_pad;           // rows per tap in the packed weights
+  int cout_pad;           // rows per weight tap in the packed weights
   int bn;                 // N tile (multiple of 16, <= 256)
   int nkb;                // K blocks per tap = cin / KB
-  int ntaps;
+  int ntaps;              // A tiles per output tile
   int x_coff;
   int y_ct, y_co, r_ct, r_co;
-  int y_vec;              // 16-byte vector stores allowed (slice aligned)
+  int y_mode;             // 0: no logits (labels only), 1: direct global stores, 2: staged TMA stores
+  int ob;                 // channels per staged sub-box (64 / 32 / 16)
   int stages;
-  uint32_t b_block_bytes;  // smem bytes of one (tap, kb) weight block (1024-aligned)
+  uint32_t b_block_bytes;  // smem bytes of one (weight tap, kb) block (1024-aligned)
+  uint32_t b_bytes;        // all resident weight blocks
+  uint32_t out_buf_bytes;  // one staging buffer = 128 * bn * 2
   uint32_t tmem_cols;
+  float lo, hi;            // fast epilogue: clamp(v, lo, hi) covers none / relu / relu6 / hardtanh
   TcTap taps[kMaxTcTaps];
 };
 
@@ -94,8 +114,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // must end in an error code, never in a hung GPU.
 __device__ unsigned int g_tc_timeout_flag = 0;
 
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, volatile uint32_t *dead) {
-  if (mbar_try_wait(bar, parity)) return;
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, volatile uint32_t *dead) {
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (*dead) return;
@@ -105,6 +124,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, volatil
       return;
     }
   }
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, volatile uint32_t *dead) {
+  if (mbar_try_wait(bar, parity)) return;
+  mbar_wait_slow(bar, parity, dead);
 }
 
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2,
@@ -120,8 +143,23 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap *map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map),
+               "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap *map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync(int id) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kEpiThreads) : "memory");
 }
 
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -149,6 +187,21 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t *>(&h);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
 // Shared-memory matrix descriptor, K-major operand whose rows are KB bf16 wide
 // (KB*2 bytes == the swizzle span) and densely packed: 8-row groups are
 // 8*KB*2 bytes apart (SBO); LBO is unused for swizzled K-major layouts.
@@ -166,32 +219,42 @@ __device__ __forceinline__ uint32_t make_idesc(int n) {
 
 // ------------------------------------------------------------------------ kernel ----
 struct TcMaps {
-  CUtensorMap a[4];
-  CUtensorMap b;
+  CUtensorMap a[4];        // input (parity views for stride 2)
+  CUtensorMap b;           // packed weights
+  CUtensorMap c[kMaxAcc];  // output (parity views for the transposed conv)
 };
 
-template <int KB>
+__device__ __noinline__ float act_generic(float v, int act, float p0, float p1, float slope) {
+  return act_apply(v, act, p0, p1, slope);
+}
+
+// MODE 0: clamp epilogue (none / relu / relu6 / hardtanh), staged output.
+// MODE 1: slope epilogue (leakyrelu / prelu), staged output.
+// MODE 2: everything else (any activation, fused argmax, unaligned output, labels only).
+template <int KB, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps, const TcParams p,
                                                                 Epilogue ep, const __nv_bfloat16 *__restrict__ res,
                                                                 __nv_bfloat16 *__restrict__ y,
                                                                 uint8_t *__restrict__ labels) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve-up (all offsets multiples of 1024 until the small tail)
-  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t kStageBytes = kTileM * KB * 2;
-  const uint32_t b_bytes = p.b_block_bytes * p.ntaps * p.nkb;
-  uint8_t *smem_b = smem;
-  uint8_t *smem_a = smem + b_bytes;
-  float *s_scale = reinterpret_cast<float *>(smem_a + (size_t)p.stages * kStageBytes);
-  float *s_shift = s_scale + p.bn;
-  float *s_slope = s_shift + p.bn;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(s_slope + p.bn);  // 8-byte aligned: bn % 16 == 0
-  uint64_t *full_bar = bars;                                      // [stages]
-  uint64_t *empty_bar = full_bar + kMaxStages;                    // [stages]
-  uint64_t *tfull_bar = empty_bar + kMaxStages;                   // [2]
-  uint64_t *tempty_bar = tfull_bar + 2;                           // [2]
-  uint64_t *b_bar = tempty_bar + 2;                               // [1]
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(b_bar + 1);
+  // carve-up in the shared address space (all offsets multiples of 1024 until the small tail)
+  const uint32_t s_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t s_b = s_base;
+  const uint32_t s_a = s_b + p.b_bytes;
+  const uint32_t s_out = s_a + (uint32_t)p.stages * kStageBytes;
+  const uint32_t s_scale = s_out + kOutBufs * p.out_buf_bytes;
+  const uint32_t s_shift = s_scale + (uint32_t)p.bn * 4;
+  const uint32_t s_slope = s_shift + (uint32_t)p.bn * 4;
+  const uint32_t s_bars = s_slope + (uint32_t)p.bn * 4;  // 8-byte aligned: bn % 16 == 0
+  const uint32_t full_bar = s_bars;                       // [kMaxStages]
+  const uint32_t empty_bar = full_bar + 8 * kMaxStages;   // [kMaxStages]
+  const uint32_t tfull_bar = empty_bar + 8 * kMaxStages;  // [2]
+  const uint32_t tempty_bar = tfull_bar + 16;             // [2]
+  const uint32_t b_bar = tempty_bar + 16;                 // [1]
+  uint8_t *gen = smem_raw + (s_base - smem_u32(smem_raw));  // generic view of the same carve-up
+  float *g_scale = reinterpret_cast<float *>(gen + (s_scale - s_base));
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(gen + (b_bar + 8 - s_base));
   volatile uint32_t *dead = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -200,23 +263,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(smem_u32(&full_bar[s]), 1);
-      mbar_init(smem_u32(&empty_bar[s]), 1);
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), 4);
+      mbar_init(tfull_bar + 8 * s, 1);
+      mbar_init(tempty_bar + 8 * s, kEpiWarps);
     }
-    mbar_init(smem_u32(b_bar), 1);
+    mbar_init(b_bar, 1);
     *dead = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   for (int i = threadIdx.x; i < p.bn; i += blockDim.x) {
     const int c = co_base + i;
     const bool ok = c < p.cout;
-    s_scale[i] = (ok && ep.scale) ? ep.scale[c] : 1.f;
-    s_shift[i] = (ok && ep.shift) ? ep.shift[c] : 0.f;
-    s_slope[i] = (ok && ep.slope) ? ep.slope[c] : 0.f;
+    g_scale[i] = (ok && ep.scale) ? ep.scale[c] : 1.f;
+    g_scale[p.bn + i] = (ok && ep.shift) ? ep.shift[c] : 0.f;
+    g_scale[2 * p.bn + i] = (ok && ep.slope) ? ep.slope[c] : 0.f;
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
@@ -228,18 +291,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t acc_cols = (uint32_t)(p.nacc * p.bn);  // TMEM columns of one accumulator stage
 
   if (warp == 0) {
     // ===================================================== TMA producer ====
     if (lane == 0) {
       prefetch_tmap(&maps.b);
       prefetch_tmap(&maps.a[0]);
-      // resident weights: ntaps * nkb boxes of [KB x bn]
-      mbar_expect_tx(smem_u32(b_bar), (uint32_t)(p.ntaps * p.nkb) * (uint32_t)(p.bn * KB * 2));
-      for (int t = 0; t < p.ntaps; ++t)
+      const int nwt = (int)(p.b_bytes / p.b_block_bytes) / p.nkb;  // resident weight taps
+      mbar_expect_tx(b_bar, (uint32_t)(nwt * p.nkb) * (uint32_t)(p.bn * KB * 2));
+      for (int t = 0; t < nwt; ++t)
         for (int kb = 0; kb < p.nkb; ++kb)
-          tma_load_2d(smem_u32(smem_b + (size_t)(t * p.nkb + kb) * p.b_block_bytes), &maps.b, smem_u32(b_bar), kb * KB,
-                      p.taps[t].widx * p.cout_pad + co_base);
+          tma_load_2d(s_b + (uint32_t)(t * p.nkb + kb) * p.b_block_bytes, &maps.b, b_bar, kb * KB,
+                      t * p.cout_pad + co_base);
       uint32_t stage = 0, phase = 0;
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
         const int twi = (int)(tile % p.tiles_w);
@@ -250,10 +314,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         for (int t = 0; t < p.ntaps; ++t) {
           const CUtensorMap *am = &maps.a[p.taps[t].map];
           for (int kb = 0; kb < p.nkb; ++kb) {
-            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1, dead);
-            mbar_expect_tx(smem_u32(&full_bar[stage]), kStageBytes);
-            tma_load_4d(smem_u32(smem_a + (size_t)stage * kStageBytes), am, smem_u32(&full_bar[stage]),
-                        p.x_coff + kb * KB, w0 + p.taps[t].dx, h0 + p.taps[t].dy, img);
+            mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+            mbar_expect_tx(full_bar + 8 * stage, kStageBytes);
+            tma_load_4d(s_a + stage * kStageBytes, am, full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.taps[t].dx,
+                        h0 + p.taps[t].dy, img);
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         }
@@ -263,39 +327,52 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     // ======================================================= MMA issuer ====
     if (lane == 0) {
       const uint32_t idesc = make_idesc(p.bn);
-      mbar_wait(smem_u32(b_bar), 0, dead);
+      mbar_wait(b_bar, 0, dead);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
-        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1, dead);
+        mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, dead);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.bn;
-        uint32_t first = 1;
+        const uint32_t d_tmem = tmem_base + acc * acc_cols;
+        uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
         for (int t = 0; t < p.ntaps; ++t) {
+          const TcTap &tap = p.taps[t];
           for (int kb = 0; kb < p.nkb; ++kb) {
-            mbar_wait(smem_u32(&full_bar[stage]), phase, dead);
+            mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem_a + (size_t)stage * kStageBytes);
-            const uint32_t b_addr = smem_u32(smem_b + (size_t)(t * p.nkb + kb) * p.b_block_bytes);
+            const uint32_t a_addr = s_a + stage * kStageBytes;
+            for (int o = 0; o < tap.nops; ++o) {
+              const uint32_t b_addr = s_b + (uint32_t)(tap.widx[o] * p.nkb + kb) * p.b_block_bytes;
+              const uint32_t a_sel = (uint32_t)tap.acc[o];
 #pragma unroll
-            for (int k = 0; k < KB / 16; ++k) {
-              umma_bf16(d_tmem, make_smem_desc<KB>(a_addr + k * 32), make_smem_desc<KB>(b_addr + k * 32), idesc,
-                        first ? 0u : 1u);
-              first = 0;
+              for (int k = 0; k < KB / 16; ++k) {
+                umma_bf16(d_tmem + a_sel * (uint32_t)p.bn, make_smem_desc<KB>(a_addr + k * 32),
+                          make_smem_desc<KB>(b_addr + k * 32), idesc, (started >> a_sel) & 1u);
+                started |= 1u << a_sel;
+              }
             }
-            umma_commit(smem_u32(&empty_bar[stage]));  // frees the A stage when these MMAs retire
+            umma_commit(empty_bar + 8 * stage);  // frees the A stage when these MMAs retire
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));  // accumulator complete -> epilogue
+        umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
         if (++acc == 2) acc = 0, acc_phase ^= 1;
       }
     }
   } else {
     // ========================================================= epilogue ====
-    const int q = warp & 3;  // TMEM lane quarter this warp may touch
+    const int e = warp - 2;
+    const int q = warp & 3;      // TMEM lane quarter this warp may touch
+    const int hsel = e >> 2;     // which of the two warps of that quarter
     const int row = q * 32 + lane;
     const int th_i = row / p.tw, tw_i = row % p.tw;
-    uint32_t acc = 0, acc_phase = 0;
+    const bool elected = threadIdx.x == 64;
+    const int nchunks = p.bn >> 4;
+    const bool want_labels = labels != nullptr;
+    const uint32_t sw_mask = p.ob == 64 ? 7u : (p.ob == 32 ? 3u : 1u);
+    const uint32_t ob_bytes = (uint32_t)p.ob * 2;
+    const bool has_res = ep.res_mode != RTSEG_RES_NONE;
+    const float pre_w = ep.res_mode == RTSEG_RES_PRE ? 1.f : 0.f, post_w = ep.res_mode == RTSEG_RES_POST ? 1.f : 0.f;
+    uint32_t acc = 0, acc_phase = 0, unit = 0;
     for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
       const int twi = (int)(tile % p.tiles_w);
       const int64_t r = tile / p.tiles_w;
@@ -303,84 +380,169 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const int img = (int)(r / p.tiles_h);
       const int gy = thi * p.th + th_i, gx = twi * p.tw + tw_i;
       const bool valid = gy < p.gh && gx < p.gw;
-      const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0)) * p.ow + (gx * p.ostride + p.ox0);
 
-      mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase, dead);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.bn;
-      float best = 0.f;
-      int best_idx = 0;
-      for (int c0 = 0; c0 < p.bn; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(taddr + c0, v);
-        tmem_ld_wait();
-        const int cg = co_base + c0;  // first global channel of this chunk
-        if (valid && cg < p.cout) {
-          float rv[16];
-          if (ep.res_mode != RTSEG_RES_NONE) {
-            const __nv_bfloat16 *rp = res + opix * p.r_ct + p.r_co + cg;
-            float t8[8];
-            Vec16<__nv_bfloat16>::load(rp, t8);
+      if constexpr (MODE != 2) {
+        // ---- fast path: staged TMA-store output, branch-free activation, residual prefetched into
+        // registers while the MMAs of this tile are still running.
+        uint4 rr[kMaxMyChunks][2];
+        if (has_res) {
+          const int64_t opix0 = ((int64_t)img * p.oh + gy) * p.ow + gx;  // forward conv: ostride 1
 #pragma unroll
-            for (int e = 0; e < 8; ++e) rv[e] = t8[e];
-            Vec16<__nv_bfloat16>::load(rp + 8, t8);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) rv[8 + e] = t8[e];
-          } else {
-#pragma unroll
-            for (int e = 0; e < 16; ++e) rv[e] = 0.f;
-          }
-          float o[16];
-#pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            float a = __uint_as_float(v[e]);
-            if (ep.res_mode == RTSEG_RES_PRE) a += rv[e];
-            a = fmaf(a, s_scale[c0 + e], s_shift[c0 + e]);
-            a = act_apply(a, ep.act, ep.p0, ep.p1, s_slope[c0 + e]);
-            if (ep.res_mode == RTSEG_RES_POST) {
-              a += rv[e];
-              a = act_apply(a, ep.act2, ep.p0, ep.p1, s_slope[c0 + e]);
-            }
-            o[e] = a;
-          }
-          if (labels) {
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              if (cg + e < p.cout) {
-                // labels follow the values the logits tensor would hold (bf16-rounded)
-                const float vr = __bfloat162float(__float2bfloat16_rn(o[e]));
-                if (cg + e == 0) {
-                  best = vr, best_idx = 0;
-                } else if (vr > best || (vr != vr && best == best)) {
-                  best = vr, best_idx = cg + e;
-                }
-              }
-            }
-          }
-          if (y) {
-            __nv_bfloat16 *yp = y + opix * p.y_ct + p.y_co + cg;
-            if (p.y_vec && cg + 16 <= p.cout) {
-              float t8[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) t8[e] = o[e];
-              Vec16<__nv_bfloat16>::store(yp, t8);
-#pragma unroll
-              for (int e = 0; e < 8; ++e) t8[e] = o[8 + e];
-              Vec16<__nv_bfloat16>::store(yp + 8, t8);
-            } else {
-#pragma unroll
-              for (int e = 0; e < 16; ++e)
-                if (cg + e < p.cout) yp[e] = __float2bfloat16_rn(o[e]);
+          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
+            const int c = hsel + 2 * ci;
+            rr[ci][0] = make_uint4(0, 0, 0, 0);
+            rr[ci][1] = make_uint4(0, 0, 0, 0);
+            if (c < nchunks && valid) {
+              const uint4 *rp = reinterpret_cast<const uint4 *>(res + opix0 * p.r_ct + p.r_co + co_base + c * 16);
+              rr[ci][0] = __ldg(rp);
+              rr[ci][1] = __ldg(rp + 1);
             }
           }
         }
+        mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
+        tc_fence_after();
+        for (int a = 0; a < p.nacc; ++a) {
+          const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
+          epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
+#pragma unroll
+          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
+            const int c = hsel + 2 * ci;
+            if (c < nchunks) {  // warp-uniform
+              const int c0 = c * 16;
+              uint32_t v[16];
+              tmem_ld16(taddr + c0, v);
+              tmem_ld_wait();
+              uint32_t pk[8];
+#pragma unroll
+              for (int e4 = 0; e4 < 16; e4 += 4) {
+                const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
+                const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
+                float rv[4] = {0.f, 0.f, 0.f, 0.f};
+                if (has_res) {
+                  const uint4 w4 = rr[ci][e4 >> 3];
+                  const uint32_t lo2 = (e4 & 4) ? w4.z : w4.x, hi2 = (e4 & 4) ? w4.w : w4.y;
+                  rv[0] = bf16_lo(lo2), rv[1] = bf16_hi(lo2), rv[2] = bf16_lo(hi2), rv[3] = bf16_hi(hi2);
+                }
+                const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
+                float o[4];
+                if constexpr (MODE == 0) {  // none / relu / relu6 / hardtanh: clamp
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    float t = fmaf(pre_w, rv[j], __uint_as_float(v[e4 + j]));
+                    t = fminf(fmaxf(fmaf(t, scv[j], shv[j]), p.lo), p.hi);
+                    o[j] = fmaf(post_w, rv[j], t);
+                  }
+                } else {  // leakyrelu / prelu: max(v,0) + slope*min(v,0)
+                  const float4 sl = lds128(s_slope + (uint32_t)(c0 + e4) * 4);
+                  const float slv[4] = {sl.x, sl.y, sl.z, sl.w};
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    float t = fmaf(pre_w, rv[j], __uint_as_float(v[e4 + j]));
+                    t = fmaf(t, scv[j], shv[j]);
+                    t = fmaf(slv[j], fminf(t, 0.f), fmaxf(t, 0.f));
+                    o[j] = fmaf(post_w, rv[j], t);
+                  }
+                }
+                pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
+                pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
+              }
+              // staged, swizzled exactly like the TMA store's tensor map expects
+              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * (kTileM * ob_bytes);
+              const uint32_t off0 = (uint32_t)row * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+              const uint32_t off1 = off0 + 16;
+              sts128(box + (off0 ^ (((off0 >> 7) & sw_mask) << 4)), pk[0], pk[1], pk[2], pk[3]);
+              sts128(box + (off1 ^ (((off1 >> 7) & sw_mask) << 4)), pk[4], pk[5], pk[6], pk[7]);
+            }
+          }
+          fence_async_smem();
+          epi_bar_sync(1);  // every warp has written its part of the staging tile
+          if (elected) {
+            const int nbox = p.bn / p.ob;
+            for (int sb = 0; sb < nbox; ++sb)
+              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * (kTileM * ob_bytes), p.y_co + co_base + sb * p.ob,
+                           twi * p.tw, thi * p.th, img);
+            bulk_commit();
+            bulk_wait_read<kOutBufs - 1>();  // the OTHER buffer is free again for the next unit
+          }
+          ++unit;
+        }
+      } else {
+        // ---- general path: any activation, fused argmax, unaligned channel counts.  Compact code
+        // (rolled chunk loop, out-of-line activation) — correctness first, used off the hot path.
+        mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
+        tc_fence_after();
+        for (int a = 0; a < p.nacc; ++a) {
+          const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0[a])) * p.ow + (gx * p.ostride + p.ox0[a]);
+          const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
+          if (p.y_mode == 2) epi_bar_sync(2);
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
+          float best = -FLT_MAX;
+          int best_idx = 0;
+          // with labels the first warp of each quarter walks all chunks in order (argmax needs every channel)
+          const int c_step = want_labels ? 1 : 2;
+          const int c_begin = want_labels ? (hsel == 0 ? 0 : nchunks) : hsel;
+#pragma unroll 1
+          for (int c = c_begin; c < nchunks; c += c_step) {
+            const int c0 = c * 16;
+            const int cg = co_base + c0;
+            uint32_t v[16];
+            tmem_ld16(taddr + c0, v);
+            tmem_ld_wait();
+            uint32_t pk[8];
+            float prev = 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float sc = g_scale[c0 + j], sh = g_scale[p.bn + c0 + j], sl = g_scale[2 * p.bn + c0 + j];
+              float rv = 0.f;
+              if (has_res && valid && cg + j < p.cout) rv = __bfloat162float(res[opix * p.r_ct + p.r_co + cg + j]);
+              float t = fmaf(pre_w, rv, __uint_as_float(v[j]));
+              t = act_generic(fmaf(t, sc, sh), ep.act, ep.p0, ep.p1, sl);
+              if (ep.res_mode == RTSEG_RES_POST) t = act_generic(t + rv, ep.act2, ep.p0, ep.p1, sl);
+              if (j & 1) pk[j >> 1] = pack_bf16(prev, t);
+              prev = t;
+              if (want_labels && cg + j < p.cout) {
+                // labels follow the values the logits tensor would hold (bf16-rounded)
+                const float vr = __bfloat162float(__float2bfloat16_rn(t));
+                if (cg + j == 0) {
+                  best = vr, best_idx = 0;
+                } else if (vr > best || (vr != vr && best == best)) {
+                  best = vr, best_idx = cg + j;
+                }
+              }
+              if (p.y_mode == 1 && valid && cg + j < p.cout)
+                y[opix * p.y_ct + p.y_co + cg + j] = __float2bfloat16_rn(t);
+            }
+            if (p.y_mode == 2) {
+              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * (kTileM * ob_bytes);
+              const uint32_t off0 = (uint32_t)row * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+              const uint32_t off1 = off0 + 16;
+              sts128(box + (off0 ^ (((off0 >> 7) & sw_mask) << 4)), pk[0], pk[1], pk[2], pk[3]);
+              sts128(box + (off1 ^ (((off1 >> 7) & sw_mask) << 4)), pk[4], pk[5], pk[6], pk[7]);
+            }
+          }
+          if (want_labels && hsel == 0 && valid && gridDim.y == 1) labels[opix] = (uint8_t)best_idx;
+          if (p.y_mode == 2) {
+            fence_async_smem();
+            epi_bar_sync(1);
+            if (elected) {
+              const int nbox = p.bn / p.ob;
+              for (int sb = 0; sb < nbox; ++sb)
+                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * (kTileM * ob_bytes), p.y_co + co_base + sb * p.ob,
+                             twi * p.tw, thi * p.th, img);
+              bulk_commit();
+              bulk_wait_read<kOutBufs - 1>();
+            }
+          }
+          ++unit;
+        }
       }
-      if (labels && valid && gridDim.y == 1) labels[opix] = (uint8_t)best_idx;
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);
       if (++acc == 2) acc = 0, acc_phase ^= 1;
     }
+    if (elected && p.y_mode == 2) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -414,40 +576,43 @@ static CUtensorMapSwizzle swizzle_for(int kb) {
   return kb == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (kb == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
 }
 
-static int pick_kb(int cin) { return cin % 64 == 0 ? 64 : (cin % 32 == 0 ? 32 : 16); }
+static int pick_kb(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : 16); }
 
 struct TcPlan {
-  int kb, bn, n_tiles, stages;
-  uint32_t b_block_bytes, smem_bytes, tmem_cols;
+  int kb, bn, n_tiles, stages, ob;
+  uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols;
 };
 
-// Chooses the N tile so that the resident weights leave room for >= 3 A stages.
-static bool plan_tc(int cin, int cout_pad, int ntaps, TcPlan &pl) {
+// Chooses the N tile so that resident weights + output staging leave room for >= 3 A stages.
+static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, TcPlan &pl) {
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
   const uint32_t stage_bytes = kTileM * pl.kb * 2;
   for (int bn = std::min(256, cout_pad); bn >= 16; bn -= 16) {
     if (cout_pad % bn) continue;
+    if (2 * nacc * bn > 512) continue;  // TMEM: two accumulator stages
     const uint32_t blk = ((uint32_t)bn * pl.kb * 2 + 1023) / 1024 * 1024;
-    const uint32_t b_bytes = blk * ntaps * nkb;
-    const uint32_t tail = 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16;
-    if (b_bytes + tail + 1024 > kSmemBudget) continue;
-    const int stages = (int)std::min<uint32_t>(kMaxStages, (kSmemBudget - 1024 - b_bytes - tail) / stage_bytes);
-    if (stages < 3) continue;
+    const uint32_t b_bytes = blk * nwtaps * nkb;
+    const uint32_t out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
+    const uint32_t fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+    if (fixed + 3 * stage_bytes > kSmemBudget) continue;
     pl.bn = bn;
     pl.n_tiles = cout_pad / bn;
-    pl.stages = stages;
+    pl.stages = (int)std::min<uint32_t>(kMaxStages, (kSmemBudget - fixed) / stage_bytes);
     pl.b_block_bytes = blk;
-    pl.smem_bytes = 1024 + b_bytes + stages * stage_bytes + tail;
+    pl.b_bytes = b_bytes;
+    pl.out_buf_bytes = out_buf;
+    pl.ob = pick_kb(bn);
+    pl.smem_bytes = fixed + pl.stages * stage_bytes;
     uint32_t cols = 32;
-    while (cols < (uint32_t)(2 * bn)) cols <<= 1;
+    while (cols < (uint32_t)(2 * nacc * bn)) cols <<= 1;
     pl.tmem_cols = cols;
     return true;
   }
   return false;
 }
 
-static int check_tc_common(const rtseg_conv_desc *d, bool deconv, bool has_y, const char **why) {
+static int check_tc_common(const rtseg_conv_desc *d, bool deconv, const char **why) {
   *why = nullptr;
   if (d->dtype != RTSEG_BF16) *why = "dtype must be bf16";
   else if (d->groups != 1) *why = "groups must be 1";
@@ -460,18 +625,19 @@ static int check_tc_common(const rtseg_conv_desc *d, bool deconv, bool has_y, co
   return *why ? RTSEG_ERR_UNSUPPORTED : RTSEG_OK;
 }
 
-static int encode_act_map(CUtensorMap *m, const void *base, int ctotal, int64_t w, int64_t h, int64_t n, int64_t sw,
-                          int64_t sh, int64_t sn, int kb, int tw, int th) {
+// 4-D bf16 tensor map over an NHWC view: dims {c, w, h, n}, element strides {1, sw, sh, sn}.
+static int encode_nhwc_map(CUtensorMap *m, const void *base, int cdim, int64_t w, int64_t h, int64_t n, int64_t sw,
+                           int64_t sh, int64_t sn, int cbox, int tw, int th) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) RTSEG_FAIL(RTSEG_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-  const cuuint64_t dims[4] = {(cuuint64_t)ctotal, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+  const cuuint64_t dims[4] = {(cuuint64_t)cdim, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
   const cuuint64_t strides[3] = {(cuuint64_t)sw * 2, (cuuint64_t)sh * 2, (cuuint64_t)sn * 2};
-  const cuuint32_t box[4] = {(cuuint32_t)kb, (cuuint32_t)tw, (cuuint32_t)th, 1};
+  const cuuint32_t box[4] = {(cuuint32_t)cbox, (cuuint32_t)tw, (cuuint32_t)th, 1};
   const cuuint32_t es[4] = {1, 1, 1, 1};
   const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, strides, box, es,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(kb), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(cbox), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) RTSEG_FAIL(RTSEG_ERR_CUDA, "cuTensorMapEncodeTiled(activations) failed with CUresult %d", (int)r);
+  if (r != CUDA_SUCCESS) RTSEG_FAIL(RTSEG_ERR_CUDA, "cuTensorMapEncodeTiled(NHWC view) failed with CUresult %d", (int)r);
   return RTSEG_OK;
 }
 
@@ -489,37 +655,39 @@ static int encode_weight_map(CUtensorMap *m, const void *w, int cin, int rows, i
   return RTSEG_OK;
 }
 
-static int check_timeout_flag(cudaStream_t st) {
-  (void)st;
-  return RTSEG_OK;
-}
-
-template <int KB>
-static int launch_tc_kb(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, const void *res,
-                        void *y, uint8_t *labels, cudaStream_t st) {
+template <int KB, int MODE>
+static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, const void *res,
+                          void *y, uint8_t *labels, cudaStream_t st) {
   static bool attr_set[64] = {false};
   int dev = 0;
   RTSEG_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBudget + 2048));
+    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kSmemBudget + 2048));
     attr_set[dev] = true;
   }
   const int sms = num_sms();
   const int gx = (int)std::min<int64_t>(p.num_m_tiles, std::max(1, sms / pl.n_tiles));
   dim3 grid((unsigned)gx, (unsigned)pl.n_tiles);
-  conv_tc_kernel<KB><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(maps, p, ep, static_cast<const __nv_bfloat16 *>(res),
-                                                                   static_cast<__nv_bfloat16 *>(y), labels);
+  conv_tc_kernel<KB, MODE><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
+      maps, p, ep, static_cast<const __nv_bfloat16 *>(res), static_cast<__nv_bfloat16 *>(y), labels);
   RTSEG_LAUNCH_CHECK("conv_tc_kernel");
-  return check_timeout_flag(st);
+  return RTSEG_OK;
 }
 
-static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, const void *res, void *y,
-                     uint8_t *labels, cudaStream_t st) {
+static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, int mode,
+                     const void *res, void *y, uint8_t *labels, cudaStream_t st) {
+  if (labels != nullptr || p.y_mode != 2) mode = 2;
+#define RTSEG_TC(KB_)                                                                              \
+  return mode == 0   ? launch_tc_inst<KB_, 0>(maps, p, pl, ep, res, y, labels, st)                 \
+         : mode == 1 ? launch_tc_inst<KB_, 1>(maps, p, pl, ep, res, y, labels, st)                 \
+                     : launch_tc_inst<KB_, 2>(maps, p, pl, ep, res, y, labels, st)
   switch (pl.kb) {
-    case 64: return launch_tc_kb<64>(maps, p, pl, ep, res, y, labels, st);
-    case 32: return launch_tc_kb<32>(maps, p, pl, ep, res, y, labels, st);
-    default: return launch_tc_kb<16>(maps, p, pl, ep, res, y, labels, st);
+    case 64: RTSEG_TC(64);
+    case 32: RTSEG_TC(32);
+    default: RTSEG_TC(16);
   }
+#undef RTSEG_TC
 }
 
 static void pick_tile(int gw, int &tw, int &th) {
@@ -528,16 +696,36 @@ static void pick_tile(int gw, int &tw, int &th) {
   th = kTileM / tw;
 }
 
+// Epilogue mode: 0 = clamp (none / relu / relu6 / hardtanh), 1 = slope form (prelu with a slope
+// vector), 2 = general.
+static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, float &lo, float &hi) {
+  lo = -FLT_MAX, hi = FLT_MAX;
+  if (d->res_mode == RTSEG_RES_POST && d->act2 != RTSEG_ACT_NONE) return 2;
+  switch (d->act) {
+    case RTSEG_ACT_NONE: return 0;
+    case RTSEG_ACT_RELU: lo = 0.f; return 0;
+    case RTSEG_ACT_RELU6: lo = 0.f, hi = 6.f; return 0;
+    case RTSEG_ACT_HARDTANH: lo = d->act_p0, hi = d->act_p1; return 0;
+    case RTSEG_ACT_PRELU: return slope ? 1 : 2;
+    default: return 2;
+  }
+}
+
 static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl, int cout_pad) {
   p.cin = d->cin, p.cout = d->cout, p.cout_pad = cout_pad;
-  p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages;
-  p.b_block_bytes = pl.b_block_bytes, p.tmem_cols = pl.tmem_cols;
+  p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages, p.ob = pl.ob;
+  p.b_block_bytes = pl.b_block_bytes, p.b_bytes = pl.b_bytes, p.out_buf_bytes = pl.out_buf_bytes;
+  p.tmem_cols = pl.tmem_cols;
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
-  p.y_vec = (d->y_ctotal % 8 == 0 && d->y_coff % 8 == 0) ? 1 : 0;
   pick_tile(p.gw, p.tw, p.th);
   p.tiles_w = (int)cdiv(p.gw, p.tw), p.tiles_h = (int)cdiv(p.gh, p.th);
   p.num_m_tiles = (int64_t)p.n * p.tiles_w * p.tiles_h;
+}
+
+// TMA stores need 16-byte global strides: the per-pixel channel count must be a multiple of 8.
+static bool can_stage_output(const rtseg_conv_desc *d, const void *y) {
+  return y != nullptr && d->y_ctotal % 8 == 0 && d->y_coff % 8 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
 }
 
 }  // namespace rtseg
@@ -547,9 +735,9 @@ using namespace rtseg;
 extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
   if (!d) return 0;
   const char *why;
-  if (check_tc_common(d, false, true, &why)) return 0;
+  if (check_tc_common(d, false, &why)) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, pl) ? 1 : 0;
 }
 
 // Reads and clears the device-side watchdog flag (synchronises the stream). Used by tests.
@@ -567,70 +755,87 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   if (int rc = validate_conv_desc(d, res)) return rc;
   RTSEG_REQUIRE(x && w_bf16 && y, "NULL tensor pointer");
   const char *why;
-  if (check_tc_common(d, false, true, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: %s", why);
+  if (check_tc_common(d, false, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: %s", why);
   RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(w_bf16) % 16 == 0 &&
-                    reinterpret_cast<uintptr_t>(y) % 16 == 0 && reinterpret_cast<uintptr_t>(res) % 16 == 0,
+                    reinterpret_cast<uintptr_t>(res) % 16 == 0,
                 "tensor pointers must be 16-byte aligned");
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const int ntaps = d->kh * d->kw;
+  const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, ntaps, pl))
+  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, pl))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
                d->cin, cout_pad);
   TcParams p;
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
-  p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.oy0 = 0, p.ox0 = 0;
+  p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
+  for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
   p.ntaps = ntaps;
+  p.y_mode = staged ? 2 : 1;
   fill_common(p, d, pl, cout_pad);
+  const int mode = epilogue_mode(d, slope, p.lo, p.hi);
 
   TcMaps maps;
   const int64_t ct = d->x_ctotal;
+  auto set_tap = [&](int t, int map, int dy, int dx) {
+    TcTap &tp = p.taps[t];
+    tp.map = (int16_t)map, tp.dy = (int16_t)dy, tp.dx = (int16_t)dx, tp.nops = 1;
+    tp.widx[0] = (int16_t)t, tp.acc[0] = 0;
+  };
   if (d->stride == 1) {
-    if (int rc = encode_act_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
-                                p.tw, p.th))
+    if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
+                                 p.tw, p.th))
       return rc;
     for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
-      for (int kx = 0; kx < d->kw; ++kx, ++t) {
-        p.taps[t].map = 0;
-        p.taps[t].dy = (int16_t)(ky * d->dil - d->pad_h);
-        p.taps[t].dx = (int16_t)(kx * d->dil - d->pad_w);
-        p.taps[t].widx = (int16_t)t;
-      }
+      for (int kx = 0; kx < d->kw; ++kx, ++t) set_tap(t, 0, ky * d->dil - d->pad_h, kx * d->dil - d->pad_w);
   } else {
     // stride 2: input (h, w) = (2*h2 + ph, 2*w2 + pw); one tensor map per parity (ph, pw)
     for (int ph = 0; ph < 2; ++ph)
       for (int pw = 0; pw < 2; ++pw) {
         const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(x) + ((int64_t)ph * d->w + pw) * ct;
-        if (int rc = encode_act_map(&maps.a[ph * 2 + pw], base, d->x_ctotal, d->w / 2, d->h / 2, d->n, 2 * ct,
-                                    2 * ct * d->w, ct * d->w * d->h, pl.kb, p.tw, p.th))
+        if (int rc = encode_nhwc_map(&maps.a[ph * 2 + pw], base, d->x_ctotal, d->w / 2, d->h / 2, d->n, 2 * ct,
+                                     2 * ct * d->w, ct * d->w * d->h, pl.kb, p.tw, p.th))
           return rc;
       }
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
       for (int kx = 0; kx < d->kw; ++kx, ++t) {
         const int oy = ky * d->dil - d->pad_h, ox = kx * d->dil - d->pad_w;  // input = 2*out + o
         const int ph = ((oy % 2) + 2) % 2, pw = ((ox % 2) + 2) % 2;
-        p.taps[t].map = (int16_t)(ph * 2 + pw);
-        p.taps[t].dy = (int16_t)((oy - ph) / 2);
-        p.taps[t].dx = (int16_t)((ox - pw) / 2);
-        p.taps[t].widx = (int16_t)t;
+        set_tap(t, ph * 2 + pw, (oy - ph) / 2, (ox - pw) / 2);
       }
   }
   if (int rc = encode_weight_map(&maps.b, w_bf16, d->cin, ntaps * cout_pad, pl.kb, pl.bn)) return rc;
+  if (staged) {
+    const int64_t yc = d->y_ctotal;
+    if (int rc = encode_nhwc_map(&maps.c[0], y, d->y_coff + d->cout, p.ow, p.oh, d->n, yc, yc * p.ow, yc * p.ow * p.oh,
+                                 pl.ob, p.tw, p.th))
+      return rc;
+  } else {
+    maps.c[0] = maps.a[0];
+  }
+  for (int a = 1; a < kMaxAcc; ++a) maps.c[a] = maps.c[0];
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
-  return launch_tc(maps, p, pl, ep, res, y, nullptr, as_stream(stream));
+  return launch_tc(maps, p, pl, ep, mode, res, y, nullptr, as_stream(stream));
 }
 
 extern "C" int rtseg_deconv3x3s2_tc_supported(const rtseg_conv_desc *d) {
   if (!d) return 0;
   const char *why;
-  if (check_tc_common(d, true, true, &why)) return 0;
+  if (check_tc_common(d, true, &why)) return 0;
   if (d->kh != 3 || d->kw != 3 || d->stride != 2 || d->dil != 1) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 4, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 9, 4, true, pl) ? 1 : 0;
 }
 
+// Transposed conv k=3, s=2, p=1, output_padding=1: oy = 2*iy - 1 + ky.  With A(dy,dx) the input tile
+// shifted by (dy,dx) and W[ky][kx] the weight taps, the four output parities of input pixel (i,j) are
+//   (2i  ,2j  ) = A00*W11
+//   (2i  ,2j+1) = A01*W10 + A00*W12
+//   (2i+1,2j  ) = A10*W01 + A00*W21
+//   (2i+1,2j+1) = A11*W00 + A10*W02 + A01*W20 + A00*W22
+// so one launch loads each of the four shifted tiles once and runs nine MMAs into four accumulators.
 extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,
                                     const float *shift, const float *slope, void *y, uint8_t *labels,
                                     rtseg_stream_t stream) {
@@ -640,41 +845,56 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   RTSEG_REQUIRE(d->res_mode == RTSEG_RES_NONE, "deconv has no residual input");
   RTSEG_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0 && d->cin > 0 && d->cout > 0, "non-positive extent");
   const char *why;
-  if (check_tc_common(d, true, y != nullptr, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: %s", why);
-  RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(w_bf16) % 16 == 0 &&
-                    reinterpret_cast<uintptr_t>(y) % 16 == 0,
+  if (check_tc_common(d, true, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: %s", why);
+  RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(w_bf16) % 16 == 0,
                 "tensor pointers must be 16-byte aligned");
-  RTSEG_REQUIRE(labels == nullptr || d->cout <= 256, "uint8 labels need cout <= 256");
+  RTSEG_REQUIRE(labels == nullptr || d->cout <= 128, "fused argmax supports at most 128 classes");
   const int cout_pad = (d->cout + 15) / 16 * 16;
+  const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, 4, pl) || (labels && pl.n_tiles != 1))
+  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, pl) || (labels && pl.n_tiles != 1))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
   TcMaps maps;
   TcParams p;
   p.n = d->n, p.gh = d->h, p.gw = d->w;
-  p.oh = 2 * d->h, p.ow = 2 * d->w, p.ostride = 2;
+  p.oh = 2 * d->h, p.ow = 2 * d->w, p.ostride = 2, p.nacc = 4;
+  for (int a = 0; a < 4; ++a) p.oy0[a] = a >> 1, p.ox0[a] = a & 1;
+  p.y_mode = y == nullptr ? 0 : (staged ? 2 : 1);
   fill_common(p, d, pl, cout_pad);
+  const int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  // four shifted input tiles and the MMAs each one feeds: {ky, kx, accumulator}
+  static const int kOps[4][4][3] = {
+      {{1, 1, 0}, {1, 2, 1}, {2, 1, 2}, {2, 2, 3}},      // A00
+      {{1, 0, 1}, {2, 0, 3}, {-1, 0, 0}, {-1, 0, 0}},    // A01 (dx = 1)
+      {{0, 1, 2}, {0, 2, 3}, {-1, 0, 0}, {-1, 0, 0}},    // A10 (dy = 1)
+      {{0, 0, 3}, {-1, 0, 0}, {-1, 0, 0}, {-1, 0, 0}}};  // A11
+  p.ntaps = 4;
+  for (int t = 0; t < 4; ++t) {
+    TcTap &tp = p.taps[t];
+    tp.map = 0, tp.dy = (int16_t)(t >> 1), tp.dx = (int16_t)(t & 1), tp.nops = 0;
+    for (int o = 0; o < 4 && kOps[t][o][0] >= 0; ++o) {
+      tp.widx[tp.nops] = (int16_t)(kOps[t][o][0] * 3 + kOps[t][o][1]);
+      tp.acc[tp.nops] = (int16_t)kOps[t][o][2];
+      ++tp.nops;
+    }
+  }
   const int64_t ct = d->x_ctotal;
-  if (int rc = encode_act_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb, p.tw,
-                              p.th))
+  if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb, p.tw,
+                               p.th))
     return rc;
   for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
   if (int rc = encode_weight_map(&maps.b, w_bf16, d->cin, 9 * cout_pad, pl.kb, pl.bn)) return rc;
-  const Epilogue ep = make_epilogue(d, scale, shift, slope);
-  // oy = 2*iy - 1 + ky: even rows take ky=1 (iy=i); odd rows ky=0 (iy=i+1) and ky=2 (iy=i). Same in x.
-  for (int py = 0; py < 2; ++py)
-    for (int px = 0; px < 2; ++px) {
-      const int kys[2] = {py == 0 ? 1 : 0, 2}, dys[2] = {py == 0 ? 0 : 1, 0};
-      const int kxs[2] = {px == 0 ? 1 : 0, 2}, dxs[2] = {px == 0 ? 0 : 1, 0};
-      const int ny = py == 0 ? 1 : 2, nx = px == 0 ? 1 : 2;
-      p.ntaps = 0;
-      for (int a = 0; a < ny; ++a)
-        for (int b = 0; b < nx; ++b) {
-          TcTap &t = p.taps[p.ntaps++];
-          t.map = 0, t.dy = (int16_t)dys[a], t.dx = (int16_t)dxs[b], t.widx = (int16_t)(kys[a] * 3 + kxs[b]);
-        }
-      p.oy0 = py, p.ox0 = px;
-      if (int rc = launch_tc(maps, p, pl, ep, nullptr, y, labels, as_stream(stream))) return rc;
+  for (int a = 0; a < 4; ++a) {
+    if (staged) {
+      const int64_t yc = d->y_ctotal;
+      const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(y) + ((int64_t)p.oy0[a] * p.ow + p.ox0[a]) * yc;
+      if (int rc = encode_nhwc_map(&maps.c[a], base, d->y_coff + d->cout, d->w, d->h, d->n, 2 * yc, 2 * yc * p.ow,
+                                   yc * p.ow * p.oh, pl.ob, p.tw, p.th))
+        return rc;
+    } else {
+      maps.c[a] = maps.a[0];
     }
-  return RTSEG_OK;
+  }
+  const Epilogue ep = make_epilogue(d, scale, shift, slope);
+  return launch_tc(maps, p, pl, ep, mode, nullptr, y, labels, as_stream(stream));
 }

@@ -71,7 +71,9 @@ def test_fp32_and_bf16_vs_oracle_medium(name):
     agree16 = (y16.float().cpu().max(1)[1] == ref.max(1)[1]).float().mean().item()
     print(f"{name}: fp32 argmax agreement {agree32:.5f}; bf16 vs storage-emulating oracle {err_emu:.3e}; "
           f"bf16 vs fp32 {err16:.3e} (format alone: {err_fmt:.3e}), argmax agreement {agree16:.5f}")
-    assert err_emu < 1e-2
+    # Two bf16 evaluations that differ only in accumulation order decorrelate after ~70 layers (one
+    # flipped rounding propagates), so kernel-vs-emulation sits near sqrt(2) x the format's own error.
+    assert err_emu < 2.0 * err_fmt
     assert err16 < max(TOL_BF16, 1.5 * err_fmt)
     if name == "erfnet":  # fused argmax epilogue == argmax of the kernel's own bf16 logits
         own = y16.float().max(1)[1].cpu()
