@@ -61,7 +61,8 @@ struct TcTap {
 
 struct TcParams {
   int n, gh, gw;          // output grid (pixels enumerated by tiles)
-  int tw, th;             // tile = th rows x tw columns, tw*th == 128
+  int tw, th;             // MMA sub-tile = th rows x tw columns, tw*th == 128
+  int ms;                 // sub-tiles per unit tile, stacked along h: unit = (ms*th) rows x tw columns
   int tiles_w, tiles_h;   // tiles per image along w / h
   int64_t num_m_tiles;
   int oh, ow;             // full output size
@@ -231,13 +232,15 @@ __device__ __noinline__ float act_generic(float v, int act, float p0, float p1, 
 // MODE 0: clamp epilogue (none / relu / relu6 / hardtanh), staged output.
 // MODE 1: slope epilogue (leakyrelu / prelu), staged output.
 // MODE 2: everything else (any activation, fused argmax, unaligned output, labels only).
+// MODE 3: transposed conv with labels only (clamp activation): argmax straight out of TMEM.
 template <int KB, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps, const TcParams p,
                                                                 Epilogue ep, const __nv_bfloat16 *__restrict__ res,
                                                                 __nv_bfloat16 *__restrict__ y,
                                                                 uint8_t *__restrict__ labels) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  constexpr uint32_t kStageBytes = kTileM * KB * 2;
+  constexpr uint32_t kSubBytes = kTileM * KB * 2;    // one 128-pixel A sub-tile
+  const uint32_t kStageBytes = kSubBytes * p.ms;     // one pipeline stage = the unit tile of one (tap, kb)
   // carve-up in the shared address space (all offsets multiples of 1024 until the small tail)
   const uint32_t s_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t s_b = s_base;
@@ -291,7 +294,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t acc_cols = (uint32_t)(p.nacc * p.bn);  // TMEM columns of one accumulator stage
+  const uint32_t acc_cols = (uint32_t)(p.ms * p.nacc * p.bn);  // TMEM columns of one accumulator stage
+  const int unit_h = p.th * p.ms;
 
   if (warp == 0) {
     // ===================================================== TMA producer ====
@@ -310,7 +314,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         const int64_t r = tile / p.tiles_w;
         const int thi = (int)(r % p.tiles_h);
         const int img = (int)(r / p.tiles_h);
-        const int w0 = twi * p.tw, h0 = thi * p.th;
+        const int w0 = twi * p.tw, h0 = thi * unit_h;
         for (int t = 0; t < p.ntaps; ++t) {
           const CUtensorMap *am = &maps.a[p.taps[t].map];
           for (int kb = 0; kb < p.nkb; ++kb) {
@@ -339,15 +343,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
-            const uint32_t a_addr = s_a + stage * kStageBytes;
-            for (int o = 0; o < tap.nops; ++o) {
-              const uint32_t b_addr = s_b + (uint32_t)(tap.widx[o] * p.nkb + kb) * p.b_block_bytes;
-              const uint32_t a_sel = (uint32_t)tap.acc[o];
+            for (int sub = 0; sub < p.ms; ++sub) {
+              const uint32_t a_addr = s_a + stage * kStageBytes + (uint32_t)sub * kSubBytes;
+              for (int o = 0; o < tap.nops; ++o) {
+                const uint32_t b_addr = s_b + (uint32_t)(tap.widx[o] * p.nkb + kb) * p.b_block_bytes;
+                const uint32_t a_sel = (uint32_t)(sub * p.nacc + tap.acc[o]);
 #pragma unroll
-              for (int k = 0; k < KB / 16; ++k) {
-                umma_bf16(d_tmem + a_sel * (uint32_t)p.bn, make_smem_desc<KB>(a_addr + k * 32),
-                          make_smem_desc<KB>(b_addr + k * 32), idesc, (started >> a_sel) & 1u);
-                started |= 1u << a_sel;
+                for (int k = 0; k < KB / 16; ++k) {
+                  umma_bf16(d_tmem + a_sel * (uint32_t)p.bn, make_smem_desc<KB>(a_addr + k * 32),
+                            make_smem_desc<KB>(b_addr + k * 32), idesc, (started >> a_sel) & 1u);
+                  started |= 1u << a_sel;
+                }
               }
             }
             umma_commit(empty_bar + 8 * stage);  // frees the A stage when these MMAs retire
@@ -364,12 +370,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     const int q = warp & 3;      // TMEM lane quarter this warp may touch
     const int hsel = e >> 2;     // which of the two warps of that quarter
     const int row = q * 32 + lane;
-    const int th_i = row / p.tw, tw_i = row % p.tw;
     const bool elected = threadIdx.x == 64;
     const int nchunks = p.bn >> 4;
     const bool want_labels = labels != nullptr;
     const uint32_t sw_mask = p.ob == 64 ? 7u : (p.ob == 32 ? 3u : 1u);
     const uint32_t ob_bytes = (uint32_t)p.ob * 2;
+    const uint32_t box_bytes = (uint32_t)p.ms * kTileM * ob_bytes;  // one staged channel group of the unit tile
+    const int total_chunks = p.ms * nchunks;
     const bool has_res = ep.res_mode != RTSEG_RES_NONE;
     const float pre_w = ep.res_mode == RTSEG_RES_PRE ? 1.f : 0.f, post_w = ep.res_mode == RTSEG_RES_POST ? 1.f : 0.f;
     uint32_t acc = 0, acc_phase = 0, unit = 0;
@@ -378,21 +385,75 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const int64_t r = tile / p.tiles_w;
       const int thi = (int)(r % p.tiles_h);
       const int img = (int)(r / p.tiles_h);
-      const int gy = thi * p.th + th_i, gx = twi * p.tw + tw_i;
-      const bool valid = gy < p.gh && gx < p.gw;
+      // grid coordinates of this thread's pixel in sub-tile `sub`
+      auto pixel = [&](int sub, int &gy, int &gx) -> bool {
+        const int idx = sub * kTileM + row;
+        gy = thi * unit_h + idx / p.tw;
+        gx = twi * p.tw + idx % p.tw;
+        return gy < p.gh && gx < p.gw;
+      };
 
-      if constexpr (MODE != 2) {
+      if constexpr (MODE == 3) {
+        // ---- labels-only transposed conv (the segmentation head): the logits never leave TMEM.
+        // The two warps of a lane quarter split the output ROW parity; each thread reduces both
+        // column parities of its input pixel and writes two adjacent uint8 labels with one store.
+        mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
+        tc_fence_after();
+#pragma unroll 1
+        for (int sub = 0; sub < p.ms; ++sub) {
+        uint32_t lab2 = 0;
+#pragma unroll 1
+        for (int px = 0; px < 2; ++px) {
+          const int a = hsel * 2 + px;
+          const uint32_t taddr =
+              tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + a) * p.bn);
+          float best = -FLT_MAX;
+          int best_idx = 0;
+#pragma unroll
+          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
+            if (ci < nchunks) {  // warp-uniform
+              const int c0 = ci * 16;
+              uint32_t v[16];
+              tmem_ld16(taddr + c0, v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e4 = 0; e4 < 16; e4 += 4) {
+                const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
+                const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
+                const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  float t = fminf(fmaxf(fmaf(__uint_as_float(v[e4 + j]), scv[j], shv[j]), p.lo), p.hi);
+                  // compare the values the logits tensor would hold (bf16-rounded), first maximum wins
+                  t = __bfloat162float(__float2bfloat16_rn(t));
+                  const int ch = c0 + e4 + j;
+                  if (ch < p.cout && (ch == 0 || t > best || (t != t && best == best))) best = t, best_idx = ch;
+                }
+              }
+            }
+          }
+          lab2 |= (uint32_t)best_idx << (8 * px);
+        }
+        int gy, gx;
+        if (pixel(sub, gy, gx)) {
+          const int64_t opix = ((int64_t)img * p.oh + (gy * 2 + hsel)) * p.ow + gx * 2;
+          *reinterpret_cast<uint16_t *>(labels + opix) = (uint16_t)lab2;
+        }
+        }
+      } else if constexpr (MODE != 2) {
         // ---- fast path: staged TMA-store output, branch-free activation, residual prefetched into
         // registers while the MMAs of this tile are still running.
         uint4 rr[kMaxMyChunks][2];
         if (has_res) {
-          const int64_t opix0 = ((int64_t)img * p.oh + gy) * p.ow + gx;  // forward conv: ostride 1
 #pragma unroll
           for (int ci = 0; ci < kMaxMyChunks; ++ci) {
-            const int c = hsel + 2 * ci;
+            const int k = hsel + 2 * ci;  // flattened (sub-tile, chunk)
+            const int sub = k / nchunks, c = k - sub * nchunks;
             rr[ci][0] = make_uint4(0, 0, 0, 0);
             rr[ci][1] = make_uint4(0, 0, 0, 0);
-            if (c < nchunks && valid) {
+            int gy, gx;
+            if (k < total_chunks && pixel(sub, gy, gx)) {
+              const int64_t opix0 = ((int64_t)img * p.oh + gy) * p.ow + gx;  // forward conv: ostride 1
               const uint4 *rp = reinterpret_cast<const uint4 *>(res + opix0 * p.r_ct + p.r_co + co_base + c * 16);
               rr[ci][0] = __ldg(rp);
               rr[ci][1] = __ldg(rp + 1);
@@ -404,14 +465,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         for (int a = 0; a < p.nacc; ++a) {
           const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
           epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols;
 #pragma unroll
           for (int ci = 0; ci < kMaxMyChunks; ++ci) {
-            const int c = hsel + 2 * ci;
-            if (c < nchunks) {  // warp-uniform
+            const int k = hsel + 2 * ci;  // flattened (sub-tile, chunk)
+            if (k < total_chunks) {  // warp-uniform
+              const int sub = k / nchunks, c = k - sub * nchunks;
               const int c0 = c * 16;
+              const uint32_t srow = (uint32_t)(sub * kTileM + row);
               uint32_t v[16];
-              tmem_ld16(taddr + c0, v);
+              tmem_ld16(tbase + (uint32_t)((sub * p.nacc + a) * p.bn + c0), v);
               tmem_ld_wait();
               uint32_t pk[8];
 #pragma unroll
@@ -448,8 +511,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
               }
               // staged, swizzled exactly like the TMA store's tensor map expects
-              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * (kTileM * ob_bytes);
-              const uint32_t off0 = (uint32_t)row * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * box_bytes;
+              const uint32_t off0 = srow * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
               const uint32_t off1 = off0 + 16;
               sts128(box + (off0 ^ (((off0 >> 7) & sw_mask) << 4)), pk[0], pk[1], pk[2], pk[3]);
               sts128(box + (off1 ^ (((off1 >> 7) & sw_mask) << 4)), pk[4], pk[5], pk[6], pk[7]);
@@ -460,8 +523,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           if (elected) {
             const int nbox = p.bn / p.ob;
             for (int sb = 0; sb < nbox; ++sb)
-              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * (kTileM * ob_bytes), p.y_co + co_base + sb * p.ob,
-                           twi * p.tw, thi * p.th, img);
+              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
+                           thi * unit_h, img);
             bulk_commit();
             bulk_wait_read<kOutBufs - 1>();  // the OTHER buffer is free again for the next unit
           }
@@ -473,10 +536,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
         for (int a = 0; a < p.nacc; ++a) {
-          const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0[a])) * p.ow + (gx * p.ostride + p.ox0[a]);
           const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
           if (p.y_mode == 2) epi_bar_sync(2);
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
+#pragma unroll 1
+          for (int sub = 0; sub < p.ms; ++sub) {
+          int gy, gx;
+          const bool valid = pixel(sub, gy, gx);
+          const uint32_t srow = (uint32_t)(sub * kTileM + row);
+          const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0[a])) * p.ow + (gx * p.ostride + p.ox0[a]);
+          const uint32_t taddr =
+              tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + a) * p.bn);
           float best = -FLT_MAX;
           int best_idx = 0;
           // with labels the first warp of each quarter walks all chunks in order (argmax needs every channel)
@@ -514,22 +583,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 y[opix * p.y_ct + p.y_co + cg + j] = __float2bfloat16_rn(t);
             }
             if (p.y_mode == 2) {
-              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * (kTileM * ob_bytes);
-              const uint32_t off0 = (uint32_t)row * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * box_bytes;
+              const uint32_t off0 = srow * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
               const uint32_t off1 = off0 + 16;
               sts128(box + (off0 ^ (((off0 >> 7) & sw_mask) << 4)), pk[0], pk[1], pk[2], pk[3]);
               sts128(box + (off1 ^ (((off1 >> 7) & sw_mask) << 4)), pk[4], pk[5], pk[6], pk[7]);
             }
           }
           if (want_labels && hsel == 0 && valid && gridDim.y == 1) labels[opix] = (uint8_t)best_idx;
+          }
           if (p.y_mode == 2) {
             fence_async_smem();
             epi_bar_sync(1);
             if (elected) {
               const int nbox = p.bn / p.ob;
               for (int sb = 0; sb < nbox; ++sb)
-                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * (kTileM * ob_bytes), p.y_co + co_base + sb * p.ob,
-                             twi * p.tw, thi * p.th, img);
+                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
+                             thi * unit_h, img);
               bulk_commit();
               bulk_wait_read<kOutBufs - 1>();
             }
@@ -579,23 +649,39 @@ static CUtensorMapSwizzle swizzle_for(int kb) {
 static int pick_kb(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : 16); }
 
 struct TcPlan {
-  int kb, bn, n_tiles, stages, ob;
+  int kb, bn, n_tiles, stages, ob, ms;
   uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols;
 };
 
 // Chooses the N tile so that resident weights + output staging leave room for >= 3 A stages.
-static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, TcPlan &pl) {
+// Narrow layers (small N) stack `ms` 128-pixel sub-tiles per unit so that the fixed per-unit costs
+// (barrier hand-offs, TMA issue, TMEM round trip) are spread over ms times more pixels.
+static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, TcPlan &pl) {
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
-  const uint32_t stage_bytes = kTileM * pl.kb * 2;
   for (int bn = std::min(256, cout_pad); bn >= 16; bn -= 16) {
     if (cout_pad % bn) continue;
     if (2 * nacc * bn > 512) continue;  // TMEM: two accumulator stages
     const uint32_t blk = ((uint32_t)bn * pl.kb * 2 + 1023) / 1024 * 1024;
     const uint32_t b_bytes = blk * nwtaps * nkb;
-    const uint32_t out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
-    const uint32_t fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+    int ms = std::max(1, max_ms);
+    uint32_t stage_bytes = 0, out_buf = 0, fixed = 0;
+    for (; ms >= 1; ms >>= 1) {
+      stage_bytes = (uint32_t)ms * kTileM * pl.kb * 2;
+      out_buf = staged_out ? (uint32_t)ms * kTileM * bn * 2 : 0;
+      fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+      const bool fits = 2 * ms * nacc * bn <= 512 && ms * (bn / 16) <= 2 * kMaxMyChunks &&
+                        fixed + 4 * stage_bytes <= kSmemBudget;
+      if (fits) break;
+    }
+    if (ms < 1) {
+      ms = 1;
+      stage_bytes = (uint32_t)kTileM * pl.kb * 2;
+      out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
+      fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+    }
     if (fixed + 3 * stage_bytes > kSmemBudget) continue;
+    pl.ms = ms;
     pl.bn = bn;
     pl.n_tiles = cout_pad / bn;
     pl.stages = (int)std::min<uint32_t>(kMaxStages, (kSmemBudget - fixed) / stage_bytes);
@@ -605,7 +691,7 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     pl.ob = pick_kb(bn);
     pl.smem_bytes = fixed + pl.stages * stage_bytes;
     uint32_t cols = 32;
-    while (cols < (uint32_t)(2 * nacc * bn)) cols <<= 1;
+    while (cols < (uint32_t)(2 * ms * nacc * bn)) cols <<= 1;
     pl.tmem_cols = cols;
     return true;
   }
@@ -677,9 +763,13 @@ static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &p
 
 static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, int mode,
                      const void *res, void *y, uint8_t *labels, cudaStream_t st) {
-  if (labels != nullptr || p.y_mode != 2) mode = 2;
+  if (labels != nullptr && p.y_mode == 0 && p.nacc == 4 && mode == 0 && pl.n_tiles == 1 && (p.ow & 1) == 0)
+    mode = 3;
+  else if (labels != nullptr || p.y_mode != 2)
+    mode = 2;
 #define RTSEG_TC(KB_)                                                                              \
-  return mode == 0   ? launch_tc_inst<KB_, 0>(maps, p, pl, ep, res, y, labels, st)                 \
+  return mode == 3   ? launch_tc_inst<KB_, 3>(maps, p, pl, ep, res, y, labels, st)                 \
+         : mode == 0 ? launch_tc_inst<KB_, 0>(maps, p, pl, ep, res, y, labels, st)                 \
          : mode == 1 ? launch_tc_inst<KB_, 1>(maps, p, pl, ep, res, y, labels, st)                 \
                      : launch_tc_inst<KB_, 2>(maps, p, pl, ep, res, y, labels, st)
   switch (pl.kb) {
@@ -711,6 +801,15 @@ static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, float &lo
   }
 }
 
+// Largest sub-tile stack that still leaves every SM at least two unit tiles.
+static int max_stack(int n, int gh, int gw) {
+  int tw, th;
+  pick_tile(gw, tw, th);
+  int ms = 8;
+  while (ms > 1 && (th * ms > gh || (int64_t)n * cdiv(gw, tw) * cdiv(gh, th * ms) < 2 * (int64_t)num_sms())) ms >>= 1;
+  return ms;
+}
+
 static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl, int cout_pad) {
   p.cin = d->cin, p.cout = d->cout, p.cout_pad = cout_pad;
   p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages, p.ob = pl.ob;
@@ -719,7 +818,8 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
   pick_tile(p.gw, p.tw, p.th);
-  p.tiles_w = (int)cdiv(p.gw, p.tw), p.tiles_h = (int)cdiv(p.gh, p.th);
+  p.ms = pl.ms;
+  p.tiles_w = (int)cdiv(p.gw, p.tw), p.tiles_h = (int)cdiv(p.gh, p.th * p.ms);
   p.num_m_tiles = (int64_t)p.n * p.tiles_w * p.tiles_h;
 }
 
@@ -737,7 +837,7 @@ extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
   const char *why;
   if (check_tc_common(d, false, &why)) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, 1, pl) ? 1 : 0;
 }
 
 // Reads and clears the device-side watchdog flag (synchronises the stream). Used by tests.
@@ -763,12 +863,12 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   const int ntaps = d->kh * d->kw;
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, pl))
-    RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
-               d->cin, cout_pad);
   TcParams p;
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
+  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), pl))
+    RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
+               d->cin, cout_pad);
   p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
   for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
   p.ntaps = ntaps;
@@ -785,7 +885,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   };
   if (d->stride == 1) {
     if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
-                                 p.tw, p.th))
+                                 p.tw, p.th * p.ms))
       return rc;
     for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
@@ -796,7 +896,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
       for (int pw = 0; pw < 2; ++pw) {
         const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(x) + ((int64_t)ph * d->w + pw) * ct;
         if (int rc = encode_nhwc_map(&maps.a[ph * 2 + pw], base, d->x_ctotal, d->w / 2, d->h / 2, d->n, 2 * ct,
-                                     2 * ct * d->w, ct * d->w * d->h, pl.kb, p.tw, p.th))
+                                     2 * ct * d->w, ct * d->w * d->h, pl.kb, p.tw, p.th * p.ms))
           return rc;
       }
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
@@ -810,7 +910,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   if (staged) {
     const int64_t yc = d->y_ctotal;
     if (int rc = encode_nhwc_map(&maps.c[0], y, d->y_coff + d->cout, p.ow, p.oh, d->n, yc, yc * p.ow, yc * p.ow * p.oh,
-                                 pl.ob, p.tw, p.th))
+                                 pl.ob, p.tw, p.th * p.ms))
       return rc;
   } else {
     maps.c[0] = maps.a[0];
@@ -826,7 +926,7 @@ extern "C" int rtseg_deconv3x3s2_tc_supported(const rtseg_conv_desc *d) {
   if (check_tc_common(d, true, &why)) return 0;
   if (d->kh != 3 || d->kw != 3 || d->stride != 2 || d->dil != 1) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 9, 4, true, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 9, 4, true, 1, pl) ? 1 : 0;
 }
 
 // Transposed conv k=3, s=2, p=1, output_padding=1: oy = 2*iy - 1 + ky.  With A(dy,dx) the input tile
@@ -852,7 +952,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, pl) || (labels && pl.n_tiles != 1))
+  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, max_stack(d->n, d->h, d->w), pl) || (labels && pl.n_tiles != 1))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
   TcMaps maps;
   TcParams p;
@@ -880,7 +980,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   }
   const int64_t ct = d->x_ctotal;
   if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb, p.tw,
-                               p.th))
+                               p.th * p.ms))
     return rc;
   for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
   if (int rc = encode_weight_map(&maps.b, w_bf16, d->cin, 9 * cout_pad, pl.kb, pl.bn)) return rc;
@@ -889,7 +989,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
       const int64_t yc = d->y_ctotal;
       const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(y) + ((int64_t)p.oy0[a] * p.ow + p.ox0[a]) * yc;
       if (int rc = encode_nhwc_map(&maps.c[a], base, d->y_coff + d->cout, d->w, d->h, d->n, 2 * yc, 2 * yc * p.ow,
-                                   yc * p.ow * p.oh, pl.ob, p.tw, p.th))
+                                   yc * p.ow * p.oh, pl.ob, p.tw, p.th * p.ms))
         return rc;
     } else {
       maps.c[a] = maps.a[0];
