@@ -225,6 +225,13 @@ struct TcMaps {
   CUtensorMap c[kMaxAcc];  // output (parity views for the transposed conv)
 };
 
+// MODE 0: clamp (none / relu / relu6 / hardtanh).  MODE 1: max(v,0) + slope*min(v,0) (prelu).
+template <int MODE>
+__device__ __forceinline__ float fast_act(float v, float slope, float lo, float hi) {
+  if constexpr (MODE == 1) return fmaf(slope, fminf(v, 0.f), fmaxf(v, 0.f));
+  return fminf(fmaxf(v, lo), hi);
+}
+
 __device__ __noinline__ float act_generic(float v, int act, float p0, float p1, float slope) {
   return act_apply(v, act, p0, p1, slope);
 }
@@ -233,7 +240,7 @@ __device__ __noinline__ float act_generic(float v, int act, float p0, float p1, 
 // MODE 1: slope epilogue (leakyrelu / prelu), staged output.
 // MODE 2: everything else (any activation, fused argmax, unaligned output, labels only).
 // MODE 3: transposed conv with labels only (clamp activation): argmax straight out of TMEM.
-template <int KB, int MODE>
+template <int KB, int MODE, bool RES>
 __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps, const TcParams p,
                                                                 Epilogue ep, const __nv_bfloat16 *__restrict__ res,
                                                                 __nv_bfloat16 *__restrict__ y,
@@ -331,6 +338,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     // ======================================================= MMA issuer ====
     if (lane == 0) {
       const uint32_t idesc = make_idesc(p.bn);
+      // Descriptors differ only in their 14-bit start-address field: build them once and add
+      // (byte offset >> 4) — the issuing thread is a single lane, every instruction counts.
+      const uint64_t a_desc0 = make_smem_desc<KB>(s_a);
+      const uint64_t b_desc0 = make_smem_desc<KB>(s_b);
+      const uint32_t stage16 = kStageBytes >> 4, sub16 = kSubBytes >> 4, blk16 = p.b_block_bytes >> 4;
       mbar_wait(b_bar, 0, dead);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
@@ -343,18 +355,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
-            for (int sub = 0; sub < p.ms; ++sub) {
-              const uint32_t a_addr = s_a + stage * kStageBytes + (uint32_t)sub * kSubBytes;
-              for (int o = 0; o < tap.nops; ++o) {
-                const uint32_t b_addr = s_b + (uint32_t)(tap.widx[o] * p.nkb + kb) * p.b_block_bytes;
-                const uint32_t a_sel = (uint32_t)(sub * p.nacc + tap.acc[o]);
+            const uint64_t a_st = a_desc0 + (uint64_t)(stage * stage16);
+            for (int o = 0; o < tap.nops; ++o) {
+              const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
+              const uint32_t a_acc = (uint32_t)tap.acc[o];
+              const uint32_t fresh = (started >> a_acc) & 1u;  // same for every sub-tile of this accumulator
+              for (int sub = 0; sub < p.ms; ++sub) {
+                const uint64_t a_d = a_st + (uint64_t)((uint32_t)sub * sub16);
+                const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
+                umma_bf16(d_col, a_d, b_d, idesc, fresh);
 #pragma unroll
-                for (int k = 0; k < KB / 16; ++k) {
-                  umma_bf16(d_tmem + a_sel * (uint32_t)p.bn, make_smem_desc<KB>(a_addr + k * 32),
-                            make_smem_desc<KB>(b_addr + k * 32), idesc, (started >> a_sel) & 1u);
-                  started |= 1u << a_sel;
-                }
+                for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
               }
+              started |= 1u << a_acc;
             }
             umma_commit(empty_bar + 8 * stage);  // frees the A stage when these MMAs retire
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
@@ -379,6 +392,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     const int total_chunks = p.ms * nchunks;
     const bool has_res = ep.res_mode != RTSEG_RES_NONE;
     const float pre_w = ep.res_mode == RTSEG_RES_PRE ? 1.f : 0.f, post_w = ep.res_mode == RTSEG_RES_POST ? 1.f : 0.f;
+    // Which (sub-tile, 16-column chunk) pairs this warp owns never changes: hoist all index math
+    // (divisions, swizzle) out of the tile loop.  Flattened chunk k = hsel + 2*ci.
+    constexpr int kMy = RES ? kMaxMyChunks / 2 : kMaxMyChunks;  // residual registers halve the capacity
+    uint32_t ck_meta[kMy];  // c0 | sub << 16
+    uint32_t ck_tcol[kMy], ck_st0[kMy];
+    int my_chunks = 0;
+#pragma unroll
+    for (int ci = 0; ci < kMy; ++ci) {
+      const int k = hsel + 2 * ci;
+      const int sub = k / nchunks, c0 = (k - sub * nchunks) * 16;
+      if (k < total_chunks) my_chunks = ci + 1;
+      ck_meta[ci] = (uint32_t)c0 | ((uint32_t)sub << 16);
+      ck_tcol[ci] = (uint32_t)(sub * p.nacc * p.bn + c0);
+      // 32-byte-aligned offset of the chunk in the staged box; its second 16-byte half is `^ 16`
+      const uint32_t off0 = (uint32_t)(sub * kTileM + row) * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+      ck_st0[ci] = (uint32_t)(c0 / p.ob) * box_bytes + (off0 ^ (((off0 >> 7) & sw_mask) << 4));
+    }
     uint32_t acc = 0, acc_phase = 0, unit = 0;
     for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
       const int twi = (int)(tile % p.tiles_w);
@@ -442,19 +472,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         }
       } else if constexpr (MODE != 2) {
         // ---- fast path: staged TMA-store output, branch-free activation, residual prefetched into
-        // registers while the MMAs of this tile are still running.
-        uint4 rr[kMaxMyChunks][2];
-        if (has_res) {
+        // registers while the MMAs of this tile are still running, TMEM loads one chunk ahead.
+        uint4 rr[RES ? kMy : 1][2];
+        if constexpr (RES) {
 #pragma unroll
-          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
-            const int k = hsel + 2 * ci;  // flattened (sub-tile, chunk)
-            const int sub = k / nchunks, c = k - sub * nchunks;
+          for (int ci = 0; ci < kMy; ++ci) {
             rr[ci][0] = make_uint4(0, 0, 0, 0);
             rr[ci][1] = make_uint4(0, 0, 0, 0);
             int gy, gx;
-            if (k < total_chunks && pixel(sub, gy, gx)) {
+            if (ci < my_chunks && pixel((int)(ck_meta[ci] >> 16), gy, gx)) {
               const int64_t opix0 = ((int64_t)img * p.oh + gy) * p.ow + gx;  // forward conv: ostride 1
-              const uint4 *rp = reinterpret_cast<const uint4 *>(res + opix0 * p.r_ct + p.r_co + co_base + c * 16);
+              const uint4 *rp = reinterpret_cast<const uint4 *>(res + opix0 * p.r_ct + p.r_co + co_base +
+                                                                (int)(ck_meta[ci] & 0xffffu));
               rr[ci][0] = __ldg(rp);
               rr[ci][1] = __ldg(rp + 1);
             }
@@ -465,57 +494,52 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         for (int a = 0; a < p.nacc; ++a) {
           const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
           epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
-          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols;
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
+          uint32_t v[2][16];
+          if (my_chunks > 0) tmem_ld16(tbase + ck_tcol[0], v[0]);
 #pragma unroll
-          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
-            const int k = hsel + 2 * ci;  // flattened (sub-tile, chunk)
-            if (k < total_chunks) {  // warp-uniform
-              const int sub = k / nchunks, c = k - sub * nchunks;
-              const int c0 = c * 16;
-              const uint32_t srow = (uint32_t)(sub * kTileM + row);
-              uint32_t v[16];
-              tmem_ld16(tbase + (uint32_t)((sub * p.nacc + a) * p.bn + c0), v);
+          for (int ci = 0; ci < kMy; ++ci) {
+            if (ci < my_chunks) {  // warp-uniform
               tmem_ld_wait();
+              if (ci + 1 < kMy && ci + 1 < my_chunks) tmem_ld16(tbase + ck_tcol[ci + 1], v[(ci + 1) & 1]);
+              const int c0 = (int)(ck_meta[ci] & 0xffffu);
               uint32_t pk[8];
 #pragma unroll
               for (int e4 = 0; e4 < 16; e4 += 4) {
                 const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
                 const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
-                float rv[4] = {0.f, 0.f, 0.f, 0.f};
-                if (has_res) {
+                const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
+                float slv[4] = {0.f, 0.f, 0.f, 0.f};
+                if constexpr (MODE == 1) {
+                  const float4 sl = lds128(s_slope + (uint32_t)(c0 + e4) * 4);
+                  slv[0] = sl.x, slv[1] = sl.y, slv[2] = sl.z, slv[3] = sl.w;
+                }
+                float o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) o[j] = __uint_as_float(v[ci & 1][e4 + j]);
+                if constexpr (!RES) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) o[j] = fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi);
+                } else {
                   const uint4 w4 = rr[ci][e4 >> 3];
                   const uint32_t lo2 = (e4 & 4) ? w4.z : w4.x, hi2 = (e4 & 4) ? w4.w : w4.y;
-                  rv[0] = bf16_lo(lo2), rv[1] = bf16_hi(lo2), rv[2] = bf16_lo(hi2), rv[3] = bf16_hi(hi2);
-                }
-                const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
-                float o[4];
-                if constexpr (MODE == 0) {  // none / relu / relu6 / hardtanh: clamp
+                  const float rv[4] = {bf16_lo(lo2), bf16_hi(lo2), bf16_lo(hi2), bf16_hi(hi2)};
+                  if (ep.res_mode == RTSEG_RES_PRE) {
 #pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    float t = fmaf(pre_w, rv[j], __uint_as_float(v[e4 + j]));
-                    t = fminf(fmaxf(fmaf(t, scv[j], shv[j]), p.lo), p.hi);
-                    o[j] = fmaf(post_w, rv[j], t);
-                  }
-                } else {  // leakyrelu / prelu: max(v,0) + slope*min(v,0)
-                  const float4 sl = lds128(s_slope + (uint32_t)(c0 + e4) * 4);
-                  const float slv[4] = {sl.x, sl.y, sl.z, sl.w};
+                    for (int j = 0; j < 4; ++j)
+                      o[j] = fast_act<MODE>(fmaf(o[j] + rv[j], scv[j], shv[j]), slv[j], p.lo, p.hi);
+                  } else {
 #pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    float t = fmaf(pre_w, rv[j], __uint_as_float(v[e4 + j]));
-                    t = fmaf(t, scv[j], shv[j]);
-                    t = fmaf(slv[j], fminf(t, 0.f), fmaxf(t, 0.f));
-                    o[j] = fmaf(post_w, rv[j], t);
+                    for (int j = 0; j < 4; ++j)
+                      o[j] = fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi) + rv[j];
                   }
                 }
                 pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
                 pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
               }
-              // staged, swizzled exactly like the TMA store's tensor map expects
-              const uint32_t box = buf + (uint32_t)(c0 / p.ob) * box_bytes;
-              const uint32_t off0 = srow * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
-              const uint32_t off1 = off0 + 16;
-              sts128(box + (off0 ^ (((off0 >> 7) & sw_mask) << 4)), pk[0], pk[1], pk[2], pk[3]);
-              sts128(box + (off1 ^ (((off1 >> 7) & sw_mask) << 4)), pk[4], pk[5], pk[6], pk[7]);
+              // staged, swizzled exactly like the TMA store's tensor map expects (offsets hoisted)
+              sts128(buf + ck_st0[ci], pk[0], pk[1], pk[2], pk[3]);
+              sts128(buf + (ck_st0[ci] ^ 16u), pk[4], pk[5], pk[6], pk[7]);
             }
           }
           fence_async_smem();
@@ -656,12 +680,15 @@ struct TcPlan {
 // Chooses the N tile so that resident weights + output staging leave room for >= 3 A stages.
 // Narrow layers (small N) stack `ms` 128-pixel sub-tiles per unit so that the fixed per-unit costs
 // (barrier hand-offs, TMA issue, TMEM round trip) are spread over ms times more pixels.
-static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, TcPlan &pl) {
+static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, bool has_res,
+                    TcPlan &pl) {
+  const int chunk_cap = has_res ? kMaxMyChunks : 2 * kMaxMyChunks;  // 16-column chunks per unit (two warps share)
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
   for (int bn = std::min(256, cout_pad); bn >= 16; bn -= 16) {
     if (cout_pad % bn) continue;
     if (2 * nacc * bn > 512) continue;  // TMEM: two accumulator stages
+    if (bn / 16 > chunk_cap) continue;
     const uint32_t blk = ((uint32_t)bn * pl.kb * 2 + 1023) / 1024 * 1024;
     const uint32_t b_bytes = blk * nwtaps * nkb;
     int ms = std::max(1, max_ms);
@@ -670,7 +697,7 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
       stage_bytes = (uint32_t)ms * kTileM * pl.kb * 2;
       out_buf = staged_out ? (uint32_t)ms * kTileM * bn * 2 : 0;
       fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
-      const bool fits = 2 * ms * nacc * bn <= 512 && ms * (bn / 16) <= 2 * kMaxMyChunks &&
+      const bool fits = 2 * ms * nacc * bn <= 512 && ms * (bn / 16) <= chunk_cap &&
                         fixed + 4 * stage_bytes <= kSmemBudget;
       if (fits) break;
     }
@@ -741,21 +768,21 @@ static int encode_weight_map(CUtensorMap *m, const void *w, int cin, int rows, i
   return RTSEG_OK;
 }
 
-template <int KB, int MODE>
+template <int KB, int MODE, bool RES>
 static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, const void *res,
                           void *y, uint8_t *labels, cudaStream_t st) {
   static bool attr_set[64] = {false};
   int dev = 0;
   RTSEG_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB, MODE, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kSmemBudget + 2048));
     attr_set[dev] = true;
   }
   const int sms = num_sms();
   const int gx = (int)std::min<int64_t>(p.num_m_tiles, std::max(1, sms / pl.n_tiles));
   dim3 grid((unsigned)gx, (unsigned)pl.n_tiles);
-  conv_tc_kernel<KB, MODE><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
+  conv_tc_kernel<KB, MODE, RES><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
       maps, p, ep, static_cast<const __nv_bfloat16 *>(res), static_cast<__nv_bfloat16 *>(y), labels);
   RTSEG_LAUNCH_CHECK("conv_tc_kernel");
   return RTSEG_OK;
@@ -767,11 +794,14 @@ static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, co
     mode = 3;
   else if (labels != nullptr || p.y_mode != 2)
     mode = 2;
-#define RTSEG_TC(KB_)                                                                              \
-  return mode == 3   ? launch_tc_inst<KB_, 3>(maps, p, pl, ep, res, y, labels, st)                 \
-         : mode == 0 ? launch_tc_inst<KB_, 0>(maps, p, pl, ep, res, y, labels, st)                 \
-         : mode == 1 ? launch_tc_inst<KB_, 1>(maps, p, pl, ep, res, y, labels, st)                 \
-                     : launch_tc_inst<KB_, 2>(maps, p, pl, ep, res, y, labels, st)
+  const bool has_res = ep.res_mode != RTSEG_RES_NONE;
+#define RTSEG_TC(KB_)                                                                                          \
+  return mode == 3   ? launch_tc_inst<KB_, 3, false>(maps, p, pl, ep, res, y, labels, st)                      \
+         : mode == 2 ? launch_tc_inst<KB_, 2, false>(maps, p, pl, ep, res, y, labels, st)                      \
+         : mode == 0 ? (has_res ? launch_tc_inst<KB_, 0, true>(maps, p, pl, ep, res, y, labels, st)            \
+                                : launch_tc_inst<KB_, 0, false>(maps, p, pl, ep, res, y, labels, st))          \
+                     : (has_res ? launch_tc_inst<KB_, 1, true>(maps, p, pl, ep, res, y, labels, st)            \
+                                : launch_tc_inst<KB_, 1, false>(maps, p, pl, ep, res, y, labels, st))
   switch (pl.kb) {
     case 64: RTSEG_TC(64);
     case 32: RTSEG_TC(32);
@@ -837,7 +867,7 @@ extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
   const char *why;
   if (check_tc_common(d, false, &why)) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, 1, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, 1, d->res_mode != RTSEG_RES_NONE, pl) ? 1 : 0;
 }
 
 // Reads and clears the device-side watchdog flag (synchronises the stream). Used by tests.
@@ -866,7 +896,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   TcParams p;
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
-  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), pl))
+  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
                d->cin, cout_pad);
   p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
@@ -926,7 +956,7 @@ extern "C" int rtseg_deconv3x3s2_tc_supported(const rtseg_conv_desc *d) {
   if (check_tc_common(d, true, &why)) return 0;
   if (d->kh != 3 || d->kw != 3 || d->stride != 2 || d->dil != 1) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 9, 4, true, 1, pl) ? 1 : 0;
+  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, 9, 4, true, 1, false, pl) ? 1 : 0;
 }
 
 // Transposed conv k=3, s=2, p=1, output_padding=1: oy = 2*iy - 1 + ky.  With A(dy,dx) the input tile
@@ -952,7 +982,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, max_stack(d->n, d->h, d->w), pl) || (labels && pl.n_tiles != 1))
+  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, max_stack(d->n, d->h, d->w), false, pl) || (labels && pl.n_tiles != 1))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
   TcMaps maps;
   TcParams p;
