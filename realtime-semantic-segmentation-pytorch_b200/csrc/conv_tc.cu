@@ -81,7 +81,8 @@ struct TcParams {
   int stages;
   uint32_t b_block_bytes;  // smem bytes of one (weight tap, kb) block (1024-aligned)
   uint32_t b_bytes;        // all resident weight blocks
-  uint32_t out_buf_bytes;  // one staging buffer = 128 * bn * 2
+  uint32_t out_buf_bytes;  // one staging buffer = ms * 128 * bn * 2
+  int out_bufs;            // 2 (store of unit u overlaps the epilogue of u+1) or 1 when shared memory is tight
   uint32_t tmem_cols;
   float lo, hi;            // fast epilogue: clamp(v, lo, hi) covers none / relu / relu6 / hardtanh
   TcTap taps[kMaxTcTaps];
@@ -253,7 +254,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
   const uint32_t s_b = s_base;
   const uint32_t s_a = s_b + p.b_bytes;
   const uint32_t s_out = s_a + (uint32_t)p.stages * kStageBytes;
-  const uint32_t s_scale = s_out + kOutBufs * p.out_buf_bytes;
+  const uint32_t s_scale = s_out + (uint32_t)p.out_bufs * p.out_buf_bytes;
   const uint32_t s_shift = s_scale + (uint32_t)p.bn * 4;
   const uint32_t s_slope = s_shift + (uint32_t)p.bn * 4;
   const uint32_t s_bars = s_slope + (uint32_t)p.bn * 4;  // 8-byte aligned: bn % 16 == 0
@@ -448,6 +449,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
               tmem_ld_wait();
 #pragma unroll
               for (int e4 = 0; e4 < 16; e4 += 4) {
+                if (c0 + e4 >= p.cout) break;  // padded classes (e.g. 19 -> 32) never win; skip their math
                 const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
                 const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
                 const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
@@ -475,6 +477,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // registers while the MMAs of this tile are still running, TMEM loads one chunk ahead.
         uint4 rr[RES ? kMy : 1][2];
         if constexpr (RES) {
+          // Warm L2 with the NEXT tile's residual rows now; their register loads (issued one tile
+          // later, just before that tile's accumulator is ready) then cost an L2 hit, not a DRAM trip.
+          const int64_t nt = tile + gridDim.x;
+          if (nt < p.num_m_tiles && hsel == 0 && p.bn >= 64) {  // (narrow layers: 32-byte rows, not worth the issue slots)
+            const int ntwi = (int)(nt % p.tiles_w);
+            const int64_t nr = nt / p.tiles_w;
+            const int nthi = (int)(nr % p.tiles_h), nimg = (int)(nr / p.tiles_h);
+            for (int sub = 0; sub < p.ms; ++sub) {
+              const int idx = sub * kTileM + row;
+              const int ngy = nthi * unit_h + idx / p.tw, ngx = ntwi * p.tw + idx % p.tw;
+              if (ngy < p.gh && ngx < p.gw) {
+                const __nv_bfloat16 *rp = res + (((int64_t)nimg * p.oh + ngy) * p.ow + ngx) * p.r_ct + p.r_co + co_base;
+                for (int b = 0; b < p.bn * 2; b += 128)
+                  asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(rp) + b));
+              }
+            }
+          }
 #pragma unroll
           for (int ci = 0; ci < kMy; ++ci) {
             rr[ci][0] = make_uint4(0, 0, 0, 0);
@@ -492,7 +511,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
         for (int a = 0; a < p.nacc; ++a) {
-          const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
+          const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
           epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
           const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
           uint32_t v[2][16];
@@ -550,7 +569,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
               tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
                            thi * unit_h, img);
             bulk_commit();
-            bulk_wait_read<kOutBufs - 1>();  // the OTHER buffer is free again for the next unit
+            if (p.out_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();  // the OTHER buffer is free again for the next unit
           }
           ++unit;
         }
@@ -560,7 +579,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
         for (int a = 0; a < p.nacc; ++a) {
-          const uint32_t buf = s_out + (unit % kOutBufs) * p.out_buf_bytes;
+          const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
           if (p.y_mode == 2) epi_bar_sync(2);
 #pragma unroll 1
           for (int sub = 0; sub < p.ms; ++sub) {
@@ -625,7 +644,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
                              thi * unit_h, img);
               bulk_commit();
-              bulk_wait_read<kOutBufs - 1>();
+              if (p.out_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
             }
           }
           ++unit;
@@ -673,7 +692,7 @@ static CUtensorMapSwizzle swizzle_for(int kb) {
 static int pick_kb(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : 16); }
 
 struct TcPlan {
-  int kb, bn, n_tiles, stages, ob, ms;
+  int kb, bn, n_tiles, stages, ob, ms, out_bufs;
   uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols;
 };
 
@@ -692,11 +711,13 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     const uint32_t blk = ((uint32_t)bn * pl.kb * 2 + 1023) / 1024 * 1024;
     const uint32_t b_bytes = blk * nwtaps * nkb;
     int ms = std::max(1, max_ms);
+    int out_bufs = kOutBufs;
     uint32_t stage_bytes = 0, out_buf = 0, fixed = 0;
+    const uint32_t misc = 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
     for (; ms >= 1; ms >>= 1) {
       stage_bytes = (uint32_t)ms * kTileM * pl.kb * 2;
       out_buf = staged_out ? (uint32_t)ms * kTileM * bn * 2 : 0;
-      fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+      fixed = b_bytes + kOutBufs * out_buf + misc;
       const bool fits = 2 * ms * nacc * bn <= 512 && ms * (bn / 16) <= chunk_cap &&
                         fixed + 4 * stage_bytes <= kSmemBudget;
       if (fits) break;
@@ -705,9 +726,16 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
       ms = 1;
       stage_bytes = (uint32_t)kTileM * pl.kb * 2;
       out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
-      fixed = b_bytes + kOutBufs * out_buf + 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
+      fixed = b_bytes + kOutBufs * out_buf + misc;
+      // Fewer than five A stages in flight starve the MMAs (each tile needs taps*nkb of them):
+      // give up the second staging buffer instead.
+      if (fixed + 5 * stage_bytes > kSmemBudget && out_buf) {
+        out_bufs = 1;
+        fixed = b_bytes + out_buf + misc;
+      }
     }
     if (fixed + 3 * stage_bytes > kSmemBudget) continue;
+    pl.out_bufs = out_bufs;
     pl.ms = ms;
     pl.bn = bn;
     pl.n_tiles = cout_pad / bn;
@@ -779,7 +807,10 @@ static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &p
                                     (int)kSmemBudget + 2048));
     attr_set[dev] = true;
   }
-  const int sms = num_sms();
+  // The labels-only head is epilogue-bound and light on registers / shared memory / TMEM:
+  // two CTAs per SM double the number of epilogue warps.
+  const int ctas_per_sm = (MODE == 3 && pl.tmem_cols <= 256 && pl.smem_bytes + 1024 <= 110 * 1024) ? 2 : 1;
+  const int sms = num_sms() * ctas_per_sm;
   const int gx = (int)std::min<int64_t>(p.num_m_tiles, std::max(1, sms / pl.n_tiles));
   dim3 grid((unsigned)gx, (unsigned)pl.n_tiles);
   conv_tc_kernel<KB, MODE, RES><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
@@ -844,6 +875,7 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
   p.cin = d->cin, p.cout = d->cout, p.cout_pad = cout_pad;
   p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages, p.ob = pl.ob;
   p.b_block_bytes = pl.b_block_bytes, p.b_bytes = pl.b_bytes, p.out_buf_bytes = pl.out_buf_bytes;
+  p.out_bufs = pl.out_bufs;
   p.tmem_cols = pl.tmem_cols;
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
@@ -982,7 +1014,8 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, max_stack(d->n, d->h, d->w), false, pl) || (labels && pl.n_tiles != 1))
+  const int stack = (labels && !y) ? 1 : max_stack(d->n, d->h, d->w);  // labels-only: small TMEM footprint, 2 CTAs/SM
+  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, stack, false, pl) || (labels && pl.n_tiles != 1))
     RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
   TcMaps maps;
   TcParams p;
