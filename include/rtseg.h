@@ -235,6 +235,27 @@ int rtseg_ohem_bwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_t layout, i
                    const float *loss_px, const void *workspace, const float *grad_out,
                    void *grad_logits, rtseg_stream_t stream);
 
+/* OHEM forward without caller-provided scratch — NO COUNTERPART IN THE REFERENCE (which lets
+ * PyTorch allocate whatever core/loss.py:14-20 needs).  It exists for callers that cannot
+ * allocate device memory: a host embedding this library from another runtime (cgo / JNI / a
+ * plugin sandbox) that owns only the logits and labels it was handed, or a loop that must not
+ * call cudaMalloc (real-time inference, code between cudaStreamBeginCapture/EndCapture).
+ * The per-pixel losses and the selection workspace live in a device array inside the library
+ * (about 8.4 MB per GPU that loads it, held until the process exits), so:
+ *   - n*h*w must not exceed rtseg_ohem_fwd_static_max_pixels() (2,097,152 — one 1024x2048
+ *     image); larger inputs are refused with RTSEG_ERR_UNSUPPORTED and a message;
+ *   - the call allocates nothing (no cudaMalloc / cudaFree / library allocator) and frees nothing;
+ *   - the first call on each device looks the array's address up (cudaGetSymbolAddress) and
+ *     caches it — make that first call outside any stream capture;
+ *   - every call on a device shares the one array, which still holds the previous call's
+ *     contents: the library re-zeroes the part that must start at zero, but two calls whose GPU
+ *     work overlaps (different streams, or threads) race on it — serialise them.
+ * Arguments and `out` are those of rtseg_ohem_fwd; there is no matching backward.              */
+int64_t rtseg_ohem_fwd_static_max_pixels(void);
+int rtseg_ohem_fwd_static(int32_t n, int32_t c, int32_t h, int32_t w, int32_t layout, int32_t dtype,
+                          const void *logits, const int64_t *labels, int32_t ignore_index,
+                          float thresh, float *out, rtseg_stream_t stream);
+
 /* ---- layout plumbing --------------------------------------------------------
  * NCHW <-> NHWC with dtype conversion (the reference's tensors are NCHW fp32,
  * tools/test_speed.py:29; ours are NHWC bf16/fp32).                         */

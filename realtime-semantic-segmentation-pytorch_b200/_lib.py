@@ -69,6 +69,8 @@ PROTOTYPES = {
     "rtseg_ohem_workspace_bytes": (c_sz, []),
     "rtseg_ohem_fwd": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_f32, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_ohem_bwd": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_ohem_fwd_static_max_pixels": (c_i64, []),
+    "rtseg_ohem_fwd_static": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_f32, c_vp, c_vp]),
     "rtseg_nchw_to_nhwc": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_nhwc_to_nchw": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "rtseg_adaptive_avgpool": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_vp, c_vp]),

@@ -25,6 +25,7 @@
 // the ties; the symmetric choice has the same loss value and is deterministic).
 #include <algorithm>
 #include <cfloat>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -334,4 +335,67 @@ extern "C" int rtseg_ohem_bwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
   RTSEG_LAUNCH_CHECK("ohem_bwd_kernel");
   return RTSEG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// OHEM forward for callers that cannot allocate device memory.
+//
+// rtseg_ohem_fwd needs two scratch buffers from its caller (the per-pixel loss and the selection
+// workspace).  Some callers have no allocator to get them from: code running inside a CUDA-graph
+// capture or a real-time loop where cudaMalloc is forbidden, a host that owns its logits/labels
+// through another runtime (a Go or Java service reaching this library over cgo/JNI with nothing
+// but the two tensors it was handed), or a plugin sandbox that may launch kernels but not grow the
+// heap.  For them the scratch lives in the library image itself: one file-scope device array per
+// GPU, sized for kOhemStaticMaxPixels pixels, present from module load until process exit.
+//
+// `g_ohem_static_scratch` below is a *device* symbol.  In host code its name is only a handle for
+// the runtime — not an address a kernel can dereference — so the device address is looked up once
+// per device with cudaGetSymbolAddress (with that device current) and cached.
+namespace rtseg {
+
+constexpr int64_t kOhemStaticMaxPixels = 1 << 21;  // 2,097,152 = one 1024 x 2048 image (or 8 x 512 x 512 ...)
+constexpr size_t kOhemStaticWsBytes = (sizeof(OhemWs) + 255) / 256 * 256;
+constexpr size_t kOhemStaticBytes = kOhemStaticWsBytes + (size_t)kOhemStaticMaxPixels * sizeof(float);
+
+static __device__ __align__(256) unsigned char g_ohem_static_scratch[kOhemStaticBytes];
+
+// Device address of the scratch array on the CURRENT device (resolved on first use, then cached).
+static int ohem_static_scratch_ptr(unsigned char **out) {
+  static std::mutex mu;
+  static unsigned char *cached[64] = {nullptr};
+  int dev = 0;
+  RTSEG_CUDA(cudaGetDevice(&dev));
+  RTSEG_REQUIRE(dev >= 0 && dev < 64, "device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == nullptr) {
+    void *p = nullptr;
+    RTSEG_CUDA(cudaGetSymbolAddress(&p, g_ohem_static_scratch));
+    RTSEG_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a NULL scratch address");
+    cached[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = cached[dev];
+  return RTSEG_OK;
+}
+
+}  // namespace rtseg
+
+extern "C" int64_t rtseg_ohem_fwd_static_max_pixels(void) { return rtseg::kOhemStaticMaxPixels; }
+
+extern "C" int rtseg_ohem_fwd_static(int32_t n, int32_t c, int32_t h, int32_t w, int32_t layout, int32_t dtype,
+                                     const void *logits, const int64_t *labels, int32_t ignore_index, float thresh,
+                                     float *out, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0, "non-positive extent");
+  const int64_t npix = (int64_t)n * h * w;
+  if (npix > kOhemStaticMaxPixels)
+    RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED,
+               "rtseg_ohem_fwd_static: %lld pixels exceed the built-in scratch (%lld pixels); use rtseg_ohem_fwd with "
+               "caller-provided buffers",
+               (long long)npix, (long long)kOhemStaticMaxPixels);
+  unsigned char *scratch = nullptr;
+  if (int rc = ohem_static_scratch_ptr(&scratch)) return rc;
+  // Layout of the array: [selection workspace | per-pixel loss].  rtseg_ohem_fwd zeroes the workspace
+  // itself (cudaMemsetAsync on `stream`) and overwrites every loss it later reads, so nothing stale
+  // from the previous call survives into this one.
+  float *loss_px = reinterpret_cast<float *>(scratch + kOhemStaticWsBytes);
+  return rtseg_ohem_fwd(n, c, h, w, layout, dtype, logits, labels, ignore_index, thresh, loss_px, scratch, out, stream);
 }
