@@ -196,6 +196,16 @@ struct Vec16;
 template <>
 struct Vec16<float> {
   static constexpr int N = 4;
+  using Raw = float4;
+  __device__ static __forceinline__ Raw zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ static __forceinline__ Raw ldg(const float *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
+  __device__ static __forceinline__ void unpack(const Raw &t, float (&v)[4]) {
+    v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+  }
+  // channel pairs for the packed fp32 FMA (FFMA2) of sm_100
+  __device__ static __forceinline__ void unpack2(const Raw &t, float2 (&v)[2]) {
+    v[0] = make_float2(t.x, t.y), v[1] = make_float2(t.z, t.w);
+  }
   __device__ static __forceinline__ void load(const float *p, float (&v)[4]) {
     const float4 t = __ldg(reinterpret_cast<const float4 *>(p));
     v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
@@ -207,6 +217,22 @@ struct Vec16<float> {
 template <>
 struct Vec16<__nv_bfloat16> {
   static constexpr int N = 8;
+  using Raw = uint4;
+  __device__ static __forceinline__ Raw zero() { return make_uint4(0, 0, 0, 0); }
+  __device__ static __forceinline__ Raw ldg(const __nv_bfloat16 *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+  __device__ static __forceinline__ void unpack(const Raw &t, float (&v)[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static __forceinline__ void unpack2(const Raw &t, float2 (&v)[4]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = make_float2(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
+  }
   __device__ static __forceinline__ void load(const __nv_bfloat16 *p, float (&v)[8]) {
     const uint4 t = __ldg(reinterpret_cast<const uint4 *>(p));
     const uint32_t w[4] = {t.x, t.y, t.z, t.w};

@@ -10,6 +10,8 @@
 //     vector fetched from L1/L2 feeds up to KW outputs (dilation 1) and the
 //     per-tap weight vectors are amortised over PX pixels,
 //   * fp32 accumulation, one rounding at the store.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace rtseg {
@@ -43,11 +45,14 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
   const int n = (int)(r / p.ho);
   const int c0 = cv * V;
 
-  float acc[PX][V];
+  // fp32 accumulation on channel PAIRS: sm_100's packed FFMA2 retires two fp32 FMAs per issue slot,
+  // which matters because a stride-1 3x3 depthwise layer is issue-bound, not HBM-bound, on B200.
+  constexpr int V2 = V / 2;
+  float2 acc[PX][V2];
 #pragma unroll
   for (int i = 0; i < PX; ++i)
 #pragma unroll
-    for (int v = 0; v < V; ++v) acc[i][v] = 0.f;
+    for (int v = 0; v < V2; ++v) acc[i][v] = make_float2(0.f, 0.f);
 
   const int wi0 = wq * PX * S - p.pad_w;
   const int hi0 = ho * S - p.pad_h;
@@ -57,29 +62,35 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
   for (int ky = 0; ky < KH; ++ky) {
     const int hi = hi0 + ky;
     if (hi < 0 || hi >= p.h) continue;
-    float wv[KW][V];
+    float2 wv[KW][V2];
 #pragma unroll
     for (int kx = 0; kx < KW; ++kx) {
       const float *wp = wgt + (int64_t)(ky * KW + kx) * p.cout + c0;
 #pragma unroll
       for (int v = 0; v < V; v += 4) {
         const float4 t = __ldg(reinterpret_cast<const float4 *>(wp + v));
-        wv[kx][v] = t.x, wv[kx][v + 1] = t.y, wv[kx][v + 2] = t.z, wv[kx][v + 3] = t.w;
+        wv[kx][v / 2] = make_float2(t.x, t.y), wv[kx][v / 2 + 1] = make_float2(t.z, t.w);
       }
     }
     const T *xr = xn + (int64_t)hi * p.w * p.x_ct;
+    // Issue the whole row of loads before touching any of them: NW independent 16-byte requests in
+    // flight per thread instead of NW serial DRAM round trips (out-of-image columns read as zero).
+    typename Vec16<T>::Raw raw[NW];
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
       const int wi = wi0 + j;
-      if (wi < 0 || wi >= p.w) continue;
-      float xv[V];
-      Vec16<T>::load(xr + (int64_t)wi * p.x_ct, xv);
+      raw[j] = (wi >= 0 && wi < p.w) ? Vec16<T>::ldg(xr + (int64_t)wi * p.x_ct) : Vec16<T>::zero();
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      float2 xv[V2];
+      Vec16<T>::unpack2(raw[j], xv);
 #pragma unroll
       for (int kx = 0; kx < KW; ++kx) {
         const int d = j - kx;
         if (d >= 0 && d % S == 0 && d / S < PX) {
 #pragma unroll
-          for (int v = 0; v < V; ++v) acc[d / S][v] = fmaf(xv[v], wv[kx][v], acc[d / S][v]);
+          for (int v = 0; v < V2; ++v) acc[d / S][v] = __ffma2_rn(xv[v], wv[kx][v], acc[d / S][v]);
         }
       }
     }
@@ -100,7 +111,10 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
     }
     float ov[V];
 #pragma unroll
-    for (int v = 0; v < V; ++v) ov[v] = epi_elem<MODE>(acc[i][v], rv[v], sc[v], sh[v], sl[v], ep);
+    for (int v = 0; v < V2; ++v) {
+      ov[2 * v] = epi_elem<MODE>(acc[i][v].x, rv[2 * v], sc[2 * v], sh[2 * v], sl[2 * v], ep);
+      ov[2 * v + 1] = epi_elem<MODE>(acc[i][v].y, rv[2 * v + 1], sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
+    }
     Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
   }
 }
@@ -143,12 +157,16 @@ __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__rest
         const float4 t = __ldg(reinterpret_cast<const float4 *>(wp + v));
         wv[v] = t.x, wv[v + 1] = t.y, wv[v + 2] = t.z, wv[v + 3] = t.w;
       }
+      typename Vec16<T>::Raw raw[PX];
 #pragma unroll
       for (int i = 0; i < PX; ++i) {
         const int wi = (wq * PX + i) * p.stride - p.pad_w + kx * p.dil;
-        if (wi < 0 || wi >= p.w) continue;
+        raw[i] = (wi >= 0 && wi < p.w) ? Vec16<T>::ldg(xr + (int64_t)wi * p.x_ct) : Vec16<T>::zero();
+      }
+#pragma unroll
+      for (int i = 0; i < PX; ++i) {
         float xv[V];
-        Vec16<T>::load(xr + (int64_t)wi * p.x_ct, xv);
+        Vec16<T>::unpack(raw[i], xv);
 #pragma unroll
         for (int v = 0; v < V; ++v) acc[i][v] = fmaf(xv[v], wv[v], acc[i][v]);
       }
@@ -250,6 +268,9 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
   } while (0)
   if (d->dil == 1 && d->kh == 3 && d->kw == 3) {
     if (d->stride == 1) {
+      static const int px_override = getenv("RTSEG_DW_PX") ? atoi(getenv("RTSEG_DW_PX")) : 0;  // tuning knob
+      if (px_override == 2) RTSEG_DW_WIN(3, 3, 1, 2);
+      if (px_override == 4) RTSEG_DW_WIN(3, 3, 1, 4);
       if (p.wo >= 64) RTSEG_DW_WIN(3, 3, 1, 8);
       RTSEG_DW_WIN(3, 3, 1, 4);
     }

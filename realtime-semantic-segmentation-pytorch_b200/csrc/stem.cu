@@ -53,18 +53,29 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
   for (int c = 0; c < CIN; ++c) mx[c] = -FLT_MAX;
 
   const TI *xn = x + (int64_t)n * p.sn;
+  // All 9*CIN window loads are issued up front (independent requests in flight), then consumed.
+  float win[3][3][CIN];
+  bool inb[3][3];
 #pragma unroll
   for (int ky = 0; ky < 3; ++ky) {
     const int hi = ho * 2 - 1 + ky;
-    if (hi < 0 || hi >= p.h) continue;
 #pragma unroll
     for (int kx = 0; kx < 3; ++kx) {
       const int wi = wo * 2 - 1 + kx;
-      if (wi < 0 || wi >= p.w) continue;
+      inb[ky][kx] = hi >= 0 && hi < p.h && wi >= 0 && wi < p.w;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci)
+        win[ky][kx][ci] = inb[ky][kx] ? ld_f<TI>(xn + ci * p.sc + hi * p.sh + wi * p.sw) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
 #pragma unroll
       for (int ci = 0; ci < CIN; ++ci) {
-        const float v = ld_f<TI>(xn + ci * p.sc + hi * p.sh + wi * p.sw);
-        mx[ci] = fmaxf(mx[ci], v);
+        const float v = win[ky][kx][ci];
+        if (inb[ky][kx]) mx[ci] = fmaxf(mx[ci], v);
         const float *wp = &ws[((ky * 3 + kx) * CIN + ci) * CC];
 #pragma unroll
         for (int c = 0; c < CC; c += 4) {
@@ -85,9 +96,16 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
   float out[CT];
 #pragma unroll
   for (int c = 0; c < CT; ++c) out[c] = 0.f;
+  if (ep.mode == 0) {  // none / relu / relu6 / hardtanh: branch-free clamp
 #pragma unroll
-  for (int c = 0; c < CC; ++c)
-    if (c < p.cconv) out[c] = epilogue_apply(acc[c], 0.f, c, ep);
+    for (int c = 0; c < CC; ++c)
+      if (c < p.cconv)
+        out[c] = fminf(fmaxf(fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f), ep.lo), ep.hi);
+  } else {
+#pragma unroll
+    for (int c = 0; c < CC; ++c)
+      if (c < p.cconv) out[c] = epilogue_apply(acc[c], 0.f, c, ep);
+  }
   if (p.pool) {  // static register indexing: place mx[] right behind the conv channels
 #pragma unroll
     for (int c = 0; c < CT; ++c)
