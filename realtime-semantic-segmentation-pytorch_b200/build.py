@@ -15,7 +15,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "librtseg.so")
-SOURCES = ["runtime.cu", "conv_dw.cu", "conv_dense.cu", "conv_tc.cu", "stem.cu", "head.cu", "ohem.cu"]
+SOURCES = ["runtime.cu", "conv_dw.cu", "dw_tma.cu", "conv_dense.cu", "conv_tc.cu", "stem.cu", "head.cu", "ohem.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
@@ -37,6 +37,7 @@ def sources_newer_than_lib() -> bool:
     t = os.path.getmtime(LIB_PATH)
     deps = [os.path.join(CSRC, s) for s in SOURCES] + [
         os.path.join(CSRC, "common.cuh"),
+        os.path.join(CSRC, "ptx.cuh"),
         os.path.join(HERE, "..", "include", "rtseg.h"),
     ]
     return any(os.path.getmtime(d) > t for d in deps)

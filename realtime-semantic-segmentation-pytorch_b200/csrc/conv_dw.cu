@@ -16,6 +16,9 @@
 
 namespace rtseg {
 
+int dw_tma_try(const rtseg_conv_desc *d, const void *x, const float *w, const Epilogue &ep, const void *res, void *y,
+               cudaStream_t st);  // dw_tma.cu
+
 struct DwParams {
   int n, h, w, c;  // c = cin = cout for the vector kernels
   int ho, wo;
@@ -304,6 +307,12 @@ extern "C" int rtseg_conv_dw(const rtseg_conv_desc *d, const void *x, const floa
   RTSEG_REQUIRE(d->groups == d->cin, "rtseg_conv_dw needs groups == cin");
   RTSEG_REQUIRE(d->cout % d->cin == 0, "depthwise cout (%d) must be a multiple of cin (%d)", d->cout, d->cin);
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
+  // Large 3x3 bf16 layers: TMA-staged shared-memory tiles (dw_tma.cu); everything else: register kernels.
+  static const bool use_tma = !(getenv("RTSEG_DW_TMA") && atoi(getenv("RTSEG_DW_TMA")) == 0);  // A/B knob
+  if (use_tma) {
+    const int rc = dw_tma_try(d, x, w, ep, res, y, as_stream(stream));
+    if (rc != RTSEG_ERR_UNSUPPORTED) return rc;
+  }
   if (d->dtype == RTSEG_BF16) return launch_dw<__nv_bfloat16>(d, x, w, ep, res, y, as_stream(stream));
   return launch_dw<float>(d, x, w, ep, res, y, as_stream(stream));
 }
