@@ -104,6 +104,11 @@ __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool val
   if ((int)(threadIdx.x & 31) == leader) atomicAdd(&hist[bin], __popc(peers));
 }
 
+// One thread owns one output column and walks kHeadRows output rows.  Per source-row pair it caches the
+// horizontally interpolated row A and the difference D = B - A (channels >= c padded with -inf / 0),
+// so that one output pixel costs, per class, one FFMA (A + ly1*D) and a branch-free compare/select —
+// the x8 upsampled logits exist only in registers.  NaNs (which must win, torch.max semantics) are
+// detected when a source row is loaded and handled by a slow exact path.
 template <typename T, int CMAX>
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int n, int hi, int wi, int c, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
@@ -125,15 +130,23 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
   if (col_ok) src_index(ox, sx, wi, align, x0, x1, lx0, lx1);
   const T *xb = x + (int64_t)b * hi * wi * c;
 
-  float rowA[CMAX], rowB[CMAX];
+  float rowA[CMAX], rowD[CMAX];  // A and (B - A)
   int ia = -1, ib = -1;
+  bool has_nan = false;
 
+  // horizontally interpolated source row i, channels >= c padded so that they never win
   auto load_row = [&](int i, float(&row)[CMAX]) {
     const T *p0 = xb + ((int64_t)i * wi + x0) * c;
     const T *p1 = xb + ((int64_t)i * wi + x1) * c;
 #pragma unroll
-    for (int k = 0; k < CMAX; ++k)
-      if (k < c) row[k] = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
+    for (int k = 0; k < CMAX; ++k) {
+      float v = -FLT_MAX;
+      if (k < c) {
+        v = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
+        has_nan |= (v != v);
+      }
+      row[k] = v;
+    }
   };
 
   for (int ry = 0; ry < kHeadRows; ++ry) {
@@ -145,33 +158,34 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int label = 0;
     if (col_ok) {
       if (!(y0 == ia && y1 == ib)) {
-        if (y0 == ib) {
-#pragma unroll
-          for (int k = 0; k < CMAX; ++k) rowA[k] = rowB[k];
-        } else if (y0 != ia) {
-          load_row(y0, rowA);
-        }
+        // new source-row pair: A <- row y0, D <- row y1 - A
+        float rowB[CMAX];
+        if (y0 != ia) load_row(y0, rowA);  // (A + D would reproduce the old B only up to a rounding: reload)
         ia = y0;
         if (y1 == y0) {
 #pragma unroll
-          for (int k = 0; k < CMAX; ++k) rowB[k] = rowA[k];
+          for (int k = 0; k < CMAX; ++k) rowD[k] = 0.f;
         } else {
           load_row(y1, rowB);
+#pragma unroll
+          for (int k = 0; k < CMAX; ++k) rowD[k] = (k < c) ? rowB[k] - rowA[k] : 0.f;
         }
         ib = y1;
       }
-      float best = -FLT_MAX;
-      bool first = true;
+      if (!has_nan) {
+        float best = rowA[0] + ly1 * rowD[0];
 #pragma unroll
-      for (int k = 0; k < CMAX; ++k) {
-        if (k < c) {
-          const float v = ly0 * rowA[k] + ly1 * rowB[k];
-          if (first) {
-            best = v, label = 0, first = false;
-          } else {
-            argmax_step(v, k, best, label);
-          }
+        for (int k = 1; k < CMAX; ++k) {
+          const float v = fmaf(ly1, rowD[k], rowA[k]);
+          const bool g = v > best;  // strict: the first maximum keeps the label
+          best = g ? v : best;
+          label = g ? k : label;
         }
+      } else {  // exact torch.max semantics with NaNs present: the first NaN wins
+        float best = rowA[0] + ly1 * rowD[0];
+#pragma unroll
+        for (int k = 1; k < CMAX; ++k)  // static indices: the row caches must stay in registers
+          if (k < c) argmax_step(fmaf(ly1, rowD[k], rowA[k]), k, best, label);
       }
       const int64_t opix = ((int64_t)b * ho + oy) * wo + ox;
       if (lab8) lab8[opix] = (uint8_t)label;
@@ -401,6 +415,12 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ho, int wo, 
                                                                  target, ignore, cm);                              \
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");                                                                   \
     return RTSEG_OK;                                                                                                \
+  }
+  if (c == 19) {  // Cityscapes: exact instantiation, no padded classes
+    upsample_argmax_kernel<T, 19><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, l8, l64,
+                                                                 target, ignore, cm);
+    RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");
+    return RTSEG_OK;
   }
   RTSEG_HEAD(8)
   RTSEG_HEAD(16)
