@@ -34,6 +34,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -65,7 +66,20 @@ struct TcTap {
 struct TcParams {
   int n, gh, gw;          // output grid (pixels enumerated by tiles)
   int tw, th;             // MMA sub-tile = th rows x tw columns, tw*th == 128
-  int ms;                 // sub-tiles per unit tile, stacked along h: unit = (ms*th) rows x tw columns
+  int ms;                 // sub-tiles per unit tile
+  int wstack;             // 0: sub-tiles stacked along h (unit = ms*th rows x tw cols); 1: along w (th rows x ms*tw cols)
+  int unit_w, unit_h;     // unit tile extent in output-grid pixels
+  // A-operand sharing ("halo tiles"): 0 = one TMA box per (tap, kb); 1 = ONE box per kb that contains every
+  // tap's rows, each tap addressing it through a shifted UMMA descriptor.
+  int a_share;
+  int a_dy, a_dx;          // shared box origin relative to the unit tile origin
+  uint32_t stage_bytes;    // bytes of one pipeline stage (1024-aligned)
+  uint32_t a_tx_bytes;     // bytes one A box delivers (what the full barrier expects)
+  uint32_t a_sub16;        // (byte offset between consecutive sub-tiles inside a stage) >> 4
+  uint32_t a_sbo16;        // (byte stride between 8-row groups of the A tile) >> 4
+  int a_boff;              // 1: start addresses are not 8-row aligned -> fill the descriptor's base-offset field
+  int box_w, box_h;        // spatial extent of one A box (host side: tensor-map box)
+  uint32_t tap_off16[kMaxTcTaps];  // a_share: (byte offset of tap t's first row inside the stage) >> 4
   int tiles_w, tiles_h;   // tiles per image along w / h
   int64_t num_m_tiles;
   int oh, ow;             // full output size
@@ -105,6 +119,12 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
   return (uint64_t)((addr & 0x3ffffu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
 }
 
+template <int KB>
+__device__ __forceinline__ uint64_t make_smem_desc_sbo(uint32_t addr, uint32_t sbo16) {
+  constexpr uint64_t layout = KB == 64 ? 2 : (KB == 32 ? 4 : 6);
+  return (uint64_t)((addr & 0x3ffffu) >> 4) | (1ull << 16) | ((uint64_t)sbo16 << 32) | (1ull << 46) | (layout << 61);
+}
+
 // kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, M = 128.
 __device__ __forceinline__ uint32_t make_idesc(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
@@ -138,8 +158,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                                                                 __nv_bfloat16 *__restrict__ y,
                                                                 uint8_t *__restrict__ labels) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  constexpr uint32_t kSubBytes = kTileM * KB * 2;    // one 128-pixel A sub-tile
-  const uint32_t kStageBytes = kSubBytes * p.ms;     // one pipeline stage = the unit tile of one (tap, kb)
+  const uint32_t kStageBytes = p.stage_bytes;        // one pipeline stage = the A data of one (tap, kb) or one kb
   // carve-up in the shared address space (all offsets multiples of 1024 until the small tail)
   const uint32_t s_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t s_b = s_base;
@@ -194,7 +213,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t acc_cols = (uint32_t)(p.ms * p.nacc * p.bn);  // TMEM columns of one accumulator stage
-  const int unit_h = p.th * p.ms;
+  const int unit_h = p.unit_h, unit_w = p.unit_w;
 
   if (warp == 0) {
     // ===================================================== TMA producer ====
@@ -213,15 +232,25 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         const int64_t r = tile / p.tiles_w;
         const int thi = (int)(r % p.tiles_h);
         const int img = (int)(r / p.tiles_h);
-        const int w0 = twi * p.tw, h0 = thi * unit_h;
-        for (int t = 0; t < p.ntaps; ++t) {
-          const CUtensorMap *am = &maps.a[p.taps[t].map];
+        const int w0 = twi * unit_w, h0 = thi * unit_h;
+        if (p.a_share) {
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
-            mbar_expect_tx(full_bar + 8 * stage, kStageBytes);
-            tma_load_4d(s_a + stage * kStageBytes, am, full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.taps[t].dx,
-                        h0 + p.taps[t].dy, img);
+            mbar_expect_tx(full_bar + 8 * stage, p.a_tx_bytes);
+            tma_load_4d(s_a + stage * kStageBytes, &maps.a[0], full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.a_dx,
+                        h0 + p.a_dy, img);
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+          }
+        } else {
+          for (int t = 0; t < p.ntaps; ++t) {
+            const CUtensorMap *am = &maps.a[p.taps[t].map];
+            for (int kb = 0; kb < p.nkb; ++kb) {
+              mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+              mbar_expect_tx(full_bar + 8 * stage, p.a_tx_bytes);
+              tma_load_4d(s_a + stage * kStageBytes, am, full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.taps[t].dx,
+                          h0 + p.taps[t].dy, img);
+              if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+            }
           }
         }
       }
@@ -232,9 +261,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const uint32_t idesc = make_idesc(p.bn);
       // Descriptors differ only in their 14-bit start-address field: build them once and add
       // (byte offset >> 4) — the issuing thread is a single lane, every instruction counts.
-      const uint64_t a_desc0 = make_smem_desc<KB>(s_a);
+      const uint64_t a_desc0 = make_smem_desc_sbo<KB>(s_a, p.a_sbo16);
       const uint64_t b_desc0 = make_smem_desc<KB>(s_b);
-      const uint32_t stage16 = kStageBytes >> 4, sub16 = kSubBytes >> 4, blk16 = p.b_block_bytes >> 4;
+      const uint32_t stage16 = kStageBytes >> 4, sub16 = p.a_sub16, blk16 = p.b_block_bytes >> 4;
       mbar_wait(b_bar, 0, dead);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
@@ -242,6 +271,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * acc_cols;
         uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
+        if (p.a_share) {
+          // one stage per kb holds the rows of every tap; tap t starts tap_off16[t] into it
+          for (int kb = 0; kb < p.nkb; ++kb) {
+            mbar_wait(full_bar + 8 * stage, phase, dead);
+            tc_fence_after();
+            for (int t = 0; t < p.ntaps; ++t) {
+              const TcTap &tap = p.taps[t];
+              const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[0] * p.nkb + kb) * blk16);
+              const uint32_t fresh = started & 1u;
+              for (int sub = 0; sub < p.ms; ++sub) {
+                const uint32_t off16 = stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16;
+                uint64_t a_d = a_desc0 + (uint64_t)off16;
+                // rows not aligned to the 8-row swizzle atom: tell the MMA the phase of the first row
+                if (p.a_boff) a_d |= (uint64_t)((((s_a >> 4) + off16) >> 3) & 7u) << 49;
+                const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc) * (uint32_t)p.bn;
+                umma_bf16(d_col, a_d, b_d, idesc, fresh);
+#pragma unroll
+                for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+              }
+              started |= 1u;
+            }
+            umma_commit(empty_bar + 8 * stage);
+            if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+          }
+        } else
         for (int t = 0; t < p.ntaps; ++t) {
           const TcTap &tap = p.taps[t];
           for (int kb = 0; kb < p.nkb; ++kb) {
@@ -286,6 +340,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     const float pre_w = ep.res_mode == RTSEG_RES_PRE ? 1.f : 0.f, post_w = ep.res_mode == RTSEG_RES_POST ? 1.f : 0.f;
     // Which (sub-tile, 16-column chunk) pairs this warp owns never changes: hoist all index math
     // (divisions, swizzle) out of the tile loop.  Flattened chunk k = hsel + 2*ci.
+    // row of this thread's pixel (sub-tile `sub`) inside the staged output box [unit_h][unit_w]
+    auto stage_row = [&](int sub) -> uint32_t {
+      return p.wstack ? (uint32_t)((row / p.tw) * p.unit_w + sub * p.tw + row % p.tw) : (uint32_t)(sub * kTileM + row);
+    };
     constexpr int kMy = RES ? kMaxMyChunks / 2 : kMaxMyChunks;  // residual registers halve the capacity
     uint32_t ck_meta[kMy];  // c0 | sub << 16
     uint32_t ck_tcol[kMy], ck_st0[kMy];
@@ -298,7 +356,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       ck_meta[ci] = (uint32_t)c0 | ((uint32_t)sub << 16);
       ck_tcol[ci] = (uint32_t)(sub * p.nacc * p.bn + c0);
       // 32-byte-aligned offset of the chunk in the staged box; its second 16-byte half is `^ 16`
-      const uint32_t off0 = (uint32_t)(sub * kTileM + row) * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
+      const uint32_t off0 = stage_row(sub) * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
       ck_st0[ci] = (uint32_t)(c0 / p.ob) * box_bytes + (off0 ^ (((off0 >> 7) & sw_mask) << 4));
     }
     uint32_t acc = 0, acc_phase = 0, unit = 0;
@@ -309,9 +367,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const int img = (int)(r / p.tiles_h);
       // grid coordinates of this thread's pixel in sub-tile `sub`
       auto pixel = [&](int sub, int &gy, int &gx) -> bool {
-        const int idx = sub * kTileM + row;
-        gy = thi * unit_h + idx / p.tw;
-        gx = twi * p.tw + idx % p.tw;
+        if (p.wstack) {  // sub-tiles side by side along w
+          gy = thi * unit_h + row / p.tw;
+          gx = twi * unit_w + sub * p.tw + row % p.tw;
+        } else {
+          const int idx = sub * kTileM + row;
+          gy = thi * unit_h + idx / p.tw;
+          gx = twi * unit_w + idx % p.tw;
+        }
         return gy < p.gh && gx < p.gw;
       };
 
@@ -376,8 +439,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             const int64_t nr = nt / p.tiles_w;
             const int nthi = (int)(nr % p.tiles_h), nimg = (int)(nr / p.tiles_h);
             for (int sub = 0; sub < p.ms; ++sub) {
-              const int idx = sub * kTileM + row;
-              const int ngy = nthi * unit_h + idx / p.tw, ngx = ntwi * p.tw + idx % p.tw;
+              int ngy, ngx;
+              if (p.wstack) {
+                ngy = nthi * unit_h + row / p.tw, ngx = ntwi * unit_w + sub * p.tw + row % p.tw;
+              } else {
+                const int idx = sub * kTileM + row;
+                ngy = nthi * unit_h + idx / p.tw, ngx = ntwi * unit_w + idx % p.tw;
+              }
               if (ngy < p.gh && ngx < p.gw) {
                 const __nv_bfloat16 *rp = res + (((int64_t)nimg * p.oh + ngy) * p.ow + ngx) * p.r_ct + p.r_co + co_base;
                 for (int b = 0; b < p.bn * 2; b += 128)
@@ -457,7 +525,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           if (elected) {
             const int nbox = p.bn / p.ob;
             for (int sb = 0; sb < nbox; ++sb)
-              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
+              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * unit_w,
                            thi * unit_h, img);
             bulk_commit();
             if (p.out_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();  // the OTHER buffer is free again for the next unit
@@ -476,7 +544,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int sub = 0; sub < p.ms; ++sub) {
           int gy, gx;
           const bool valid = pixel(sub, gy, gx);
-          const uint32_t srow = (uint32_t)(sub * kTileM + row);
+          const uint32_t srow = stage_row(sub);
           const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0[a])) * p.ow + (gx * p.ostride + p.ox0[a]);
           const uint32_t taddr =
               tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + a) * p.bn);
@@ -532,7 +600,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             if (elected) {
               const int nbox = p.bn / p.ob;
               for (int sb = 0; sb < nbox; ++sb)
-                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * p.tw,
+                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * unit_w,
                              thi * unit_h, img);
               bulk_commit();
               if (p.out_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
@@ -590,8 +658,18 @@ struct TcPlan {
 // Chooses the N tile so that resident weights + output staging leave room for >= 3 A stages.
 // Narrow layers (small N) stack `ms` 128-pixel sub-tiles per unit so that the fixed per-unit costs
 // (barrier hand-offs, TMA issue, TMEM round trip) are spread over ms times more pixels.
+// share: 0 = one A box per (tap, kb); 1 = vertical halo tile (8x16-pixel sub-tiles side by side);
+// 2 = horizontal halo tile (128-pixel rows, taps are row-shifted descriptors).  halo = (k-1)*dilation.
+static uint32_t tc_stage_bytes(int share, int halo, int ms, int kb) {
+  uint32_t b;
+  if (share == 1) b = (uint32_t)(16 + halo) * 8 * ms * kb * 2;
+  else if (share == 2) b = (uint32_t)ms * (kTileM + halo) * kb * 2;
+  else b = (uint32_t)ms * kTileM * kb * 2;
+  return (b + 1023) / 1024 * 1024;
+}
+
 static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, bool has_res,
-                    TcPlan &pl) {
+                    TcPlan &pl, int share = 0, int halo = 0) {
   const int chunk_cap = has_res ? kMaxMyChunks : 2 * kMaxMyChunks;  // 16-column chunks per unit (two warps share)
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
@@ -606,16 +684,17 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     uint32_t stage_bytes = 0, out_buf = 0, fixed = 0;
     const uint32_t misc = 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
     for (; ms >= 1; ms >>= 1) {
-      stage_bytes = (uint32_t)ms * kTileM * pl.kb * 2;
+      stage_bytes = tc_stage_bytes(share, halo, ms, pl.kb);
       out_buf = staged_out ? (uint32_t)ms * kTileM * bn * 2 : 0;
       fixed = b_bytes + kOutBufs * out_buf + misc;
+      // a shared halo stage feeds a whole K block (all taps), so three of them already cover three units
       const bool fits = 2 * ms * nacc * bn <= 512 && ms * (bn / 16) <= chunk_cap &&
-                        fixed + 4 * stage_bytes <= kSmemBudget;
+                        fixed + (share ? 3 : 4) * stage_bytes <= kSmemBudget;
       if (fits) break;
     }
     if (ms < 1) {
       ms = 1;
-      stage_bytes = (uint32_t)kTileM * pl.kb * 2;
+      stage_bytes = tc_stage_bytes(share, halo, 1, pl.kb);
       out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
       fixed = b_bytes + kOutBufs * out_buf + misc;
       // Fewer than five A stages in flight starve the MMAs (each tile needs taps*nkb of them):
@@ -754,15 +833,32 @@ static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, float &lo
 }
 
 // Largest sub-tile stack that still leaves every SM at least two unit tiles.
-static int max_stack(int n, int gh, int gw) {
+static int max_stack(int n, int gh, int gw, int share = 0) {
   int tw, th;
   pick_tile(gw, tw, th);
+  if (share == 1) tw = 8, th = 16;
+  if (share == 2) tw = kTileM, th = 1;
   int ms = 8;
-  while (ms > 1 && (th * ms > gh || (int64_t)n * cdiv(gw, tw) * cdiv(gh, th * ms) < 2 * (int64_t)num_sms())) ms >>= 1;
+  auto units = [&](int m) {
+    return share == 1 ? (int64_t)n * cdiv(gw, tw * m) * cdiv(gh, th) : (int64_t)n * cdiv(gw, tw) * cdiv(gh, th * m);
+  };
+  while (ms > 1 && ((share == 1 ? tw * ms > gw : th * ms > gh) || units(ms) < 2 * (int64_t)num_sms())) ms >>= 1;
   return ms;
 }
 
-static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl, int cout_pad) {
+// Which A-sharing mode a forward conv can use (0 = none).  RTSEG_TC_SHARE=0 disables, =1 vertical only.
+static int pick_share(const rtseg_conv_desc *d, int gh, int gw, int kb) {
+  static const int knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 3;
+  if (d->stride != 1) return 0;
+  if ((knob & 1) && d->kw == 1 && d->kh >= 2 && (d->kh - 1) * d->dil < (d->kh - 1) * 16 && d->pad_w == 0 && gw >= 8 &&
+      gh >= 16)
+    return 1;
+  if ((knob & 2) && d->kh == 1 && d->kw >= 2 && kb == 64 && (d->kw - 1) * d->dil <= 64 && d->pad_h == 0 && gw > 64)
+    return 2;
+  return 0;
+}
+
+static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl, int cout_pad, int share = 0) {
   p.cin = d->cin, p.cout = d->cout, p.cout_pad = cout_pad;
   p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages, p.ob = pl.ob;
   p.b_block_bytes = pl.b_block_bytes, p.b_bytes = pl.b_bytes, p.out_buf_bytes = pl.out_buf_bytes;
@@ -770,9 +866,41 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
   p.tmem_cols = pl.tmem_cols;
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
-  pick_tile(p.gw, p.tw, p.th);
   p.ms = pl.ms;
-  p.tiles_w = (int)cdiv(p.gw, p.tw), p.tiles_h = (int)cdiv(p.gh, p.th * p.ms);
+  const int halo = share == 1 ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  if (share == 1) {  // vertical taps: 8 wide x 16 tall sub-tiles, stacked along w, one box holds all taps' rows
+    p.tw = 8, p.th = 16, p.wstack = 1;
+    p.unit_w = 8 * p.ms, p.unit_h = 16;
+    p.a_share = 1, p.a_dy = -d->pad_h, p.a_dx = 0, p.a_boff = 0;
+    p.box_w = p.unit_w, p.box_h = 16 + halo;
+    p.a_sub16 = (8u * pl.kb * 2) >> 4;
+    p.a_sbo16 = ((uint32_t)p.unit_w * pl.kb * 2) >> 4;
+    for (int t = 0; t < d->kh; ++t) p.tap_off16[t] = ((uint32_t)(t * d->dil) * p.unit_w * pl.kb * 2) >> 4;
+  } else if (share == 2) {  // horizontal taps: 128-pixel rows (+halo), stacked along h, taps = row-shifted descriptors
+    p.tw = kTileM, p.th = 1, p.wstack = 0;
+    p.unit_w = kTileM, p.unit_h = p.ms;
+    // Measured on B200: with the base-offset field left at 0 a descriptor whose start address is shifted by
+    // d rows (d*128 bytes, not a multiple of the 1024-byte swizzle atom) reads exactly the rows TMA wrote —
+    // the MMA derives the 128B-swizzle phase from the absolute shared-memory address bits [7,10).  Setting
+    // base_offset = (addr >> 7) & 7 instead produces wrong results (RTSEG_TC_BOFF=1 reproduces that).
+    static const int boff_knob = getenv("RTSEG_TC_BOFF") ? atoi(getenv("RTSEG_TC_BOFF")) : 0;
+    p.a_share = 1, p.a_dy = 0, p.a_dx = -d->pad_w, p.a_boff = boff_knob;
+    p.box_w = kTileM + halo, p.box_h = p.ms;
+    p.a_sub16 = ((uint32_t)(kTileM + halo) * pl.kb * 2) >> 4;
+    p.a_sbo16 = (8u * pl.kb * 2) >> 4;
+    for (int t = 0; t < d->kw; ++t) p.tap_off16[t] = ((uint32_t)(t * d->dil) * pl.kb * 2) >> 4;
+  } else {
+    pick_tile(p.gw, p.tw, p.th);
+    p.wstack = 0;
+    p.unit_w = p.tw, p.unit_h = p.th * p.ms;
+    p.a_share = 0, p.a_dy = 0, p.a_dx = 0, p.a_boff = 0;
+    p.box_w = p.tw, p.box_h = p.unit_h;
+    p.a_sub16 = ((uint32_t)kTileM * pl.kb * 2) >> 4;
+    p.a_sbo16 = (8u * pl.kb * 2) >> 4;
+  }
+  p.stage_bytes = tc_stage_bytes(share, halo, p.ms, pl.kb);
+  p.a_tx_bytes = (uint32_t)p.box_w * p.box_h * pl.kb * 2;
+  p.tiles_w = (int)cdiv(p.gw, p.unit_w), p.tiles_h = (int)cdiv(p.gh, p.unit_h);
   p.num_m_tiles = (int64_t)p.n * p.tiles_w * p.tiles_h;
 }
 
@@ -817,14 +945,20 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   TcParams p;
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
-  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
-    RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
-               d->cin, cout_pad);
+  int share = pick_share(d, p.gh, p.gw, pick_kb(d->cin));
+  const int halo = share == 1 ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw, share), d->res_mode != RTSEG_RES_NONE, pl,
+               share, halo)) {
+    share = 0;
+    if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
+      RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
+                 d->cin, cout_pad);
+  }
   p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
   for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
   p.ntaps = ntaps;
   p.y_mode = staged ? 2 : 1;
-  fill_common(p, d, pl, cout_pad);
+  fill_common(p, d, pl, cout_pad, share);
   const int mode = epilogue_mode(d, slope, p.lo, p.hi);
 
   TcMaps maps;
@@ -836,7 +970,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   };
   if (d->stride == 1) {
     if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
-                                 p.tw, p.th * p.ms))
+                                 p.box_w, p.box_h))
       return rc;
     for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
@@ -847,7 +981,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
       for (int pw = 0; pw < 2; ++pw) {
         const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(x) + ((int64_t)ph * d->w + pw) * ct;
         if (int rc = encode_nhwc_map(&maps.a[ph * 2 + pw], base, d->x_ctotal, d->w / 2, d->h / 2, d->n, 2 * ct,
-                                     2 * ct * d->w, ct * d->w * d->h, pl.kb, p.tw, p.th * p.ms))
+                                     2 * ct * d->w, ct * d->w * d->h, pl.kb, p.box_w, p.box_h))
           return rc;
       }
     for (int ky = 0, t = 0; ky < d->kh; ++ky)
@@ -861,7 +995,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   if (staged) {
     const int64_t yc = d->y_ctotal;
     if (int rc = encode_nhwc_map(&maps.c[0], y, d->y_coff + d->cout, p.ow, p.oh, d->n, yc, yc * p.ow, yc * p.ow * p.oh,
-                                 pl.ob, p.tw, p.th * p.ms))
+                                 pl.ob, p.unit_w, p.unit_h))
       return rc;
   } else {
     maps.c[0] = maps.a[0];
@@ -931,8 +1065,8 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
     }
   }
   const int64_t ct = d->x_ctotal;
-  if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb, p.tw,
-                               p.th * p.ms))
+  if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb, p.box_w,
+                               p.box_h))
     return rc;
   for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
   if (int rc = encode_weight_map(&maps.b, w_bf16, d->cin, 9 * cout_pad, pl.kb, pl.bn)) return rc;
@@ -941,7 +1075,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
       const int64_t yc = d->y_ctotal;
       const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(y) + ((int64_t)p.oy0[a] * p.ow + p.ox0[a]) * yc;
       if (int rc = encode_nhwc_map(&maps.c[a], base, d->y_coff + d->cout, d->w, d->h, d->n, 2 * yc, 2 * yc * p.ow,
-                                   yc * p.ow * p.oh, pl.ob, p.tw, p.th * p.ms))
+                                   yc * p.ow * p.oh, pl.ob, p.unit_w, p.unit_h))
         return rc;
     } else {
       maps.c[a] = maps.a[0];
