@@ -79,6 +79,8 @@ struct TcParams {
   uint32_t a_sbo16;        // (byte stride between 8-row groups of the A tile) >> 4
   int a_boff;              // 1: start addresses are not 8-row aligned -> fill the descriptor's base-offset field
   int box_w, box_h;        // spatial extent of one A box (host side: tensor-map box)
+  int res_boxes;           // residual sub-boxes (bn / ob) that travel through the A ring per unit, 0 = no residual
+  int a_stages_per_unit;   // ring stages the MMA consumes per unit
   uint32_t tap_off16[kMaxTcTaps];  // a_share: (byte offset of tap t's first row inside the stage) >> 4
   int tiles_w, tiles_h;   // tiles per image along w / h
   int64_t num_m_tiles;
@@ -135,6 +137,7 @@ struct TcMaps {
   CUtensorMap a[4];        // input (parity views for stride 2)
   CUtensorMap b;           // packed weights
   CUtensorMap c[kMaxAcc];  // output (parity views for the transposed conv)
+  CUtensorMap r;           // residual (same geometry as c[0])
 };
 
 // MODE 0: clamp (none / relu / relu6 / hardtanh).  MODE 1: max(v,0) + slope*min(v,0) (prelu).
@@ -253,6 +256,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             }
           }
         }
+        // The residual tile rides the same ring (consumed by the epilogue warps, not by the MMA): it is
+        // in shared memory, swizzled like the output staging tile, long before its accumulator is ready.
+        for (int sb = 0; sb < p.res_boxes; ++sb) {
+          mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+          mbar_expect_tx(full_bar + 8 * stage, (uint32_t)p.ms * kTileM * (uint32_t)p.ob * 2);
+          tma_load_4d(s_a + stage * kStageBytes, &maps.r, full_bar + 8 * stage, p.r_co + co_base + sb * p.ob, w0, h0, img);
+          if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+        }
       }
     }
   } else if (warp == 1) {
@@ -319,6 +330,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         }
+        for (int sb = 0; sb < p.res_boxes; ++sb)  // residual stages belong to the epilogue
+          if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
         umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
         if (++acc == 2) acc = 0, acc_phase ^= 1;
       }
@@ -344,7 +357,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     auto stage_row = [&](int sub) -> uint32_t {
       return p.wstack ? (uint32_t)((row / p.tw) * p.unit_w + sub * p.tw + row % p.tw) : (uint32_t)(sub * kTileM + row);
     };
-    constexpr int kMy = RES ? kMaxMyChunks / 2 : kMaxMyChunks;  // residual registers halve the capacity
+    constexpr int kMy = kMaxMyChunks;
     uint32_t ck_meta[kMy];  // c0 | sub << 16
     uint32_t ck_tcol[kMy], ck_st0[kMy];
     int my_chunks = 0;
@@ -353,13 +366,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const int k = hsel + 2 * ci;
       const int sub = k / nchunks, c0 = (k - sub * nchunks) * 16;
       if (k < total_chunks) my_chunks = ci + 1;
-      ck_meta[ci] = (uint32_t)c0 | ((uint32_t)sub << 16);
+      ck_meta[ci] = (uint32_t)c0 | ((uint32_t)sub << 16) | ((uint32_t)(c0 / p.ob) << 24);  // c0 | sub | sub-box
       ck_tcol[ci] = (uint32_t)(sub * p.nacc * p.bn + c0);
       // 32-byte-aligned offset of the chunk in the staged box; its second 16-byte half is `^ 16`
       const uint32_t off0 = stage_row(sub) * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
       ck_st0[ci] = (uint32_t)(c0 / p.ob) * box_bytes + (off0 ^ (((off0 >> 7) & sw_mask) << 4));
     }
     uint32_t acc = 0, acc_phase = 0, unit = 0;
+    uint32_t ring = 0, ring_phase = 0;  // position in the A ring (the residual stages live there)
+    auto ring_advance = [&](int nsteps) {
+      for (int i = 0; i < nsteps; ++i)
+        if (++ring == (uint32_t)p.stages) ring = 0, ring_phase ^= 1;
+    };
     for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
       const int twi = (int)(tile % p.tiles_w);
       const int64_t r = tile / p.tiles_w;
@@ -429,43 +447,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       } else if constexpr (MODE != 2) {
         // ---- fast path: staged TMA-store output, branch-free activation, residual prefetched into
         // registers while the MMAs of this tile are still running, TMEM loads one chunk ahead.
-        uint4 rr[RES ? kMy : 1][2];
+        // Residual sub-boxes of this unit: ring stages right behind the unit's A stages.
+        uint32_t res_first = 0;  // ring slot of residual sub-box 0 (sub-box sb sits sb slots further, modulo)
         if constexpr (RES) {
-          // Warm L2 with the NEXT tile's residual rows now; their register loads (issued one tile
-          // later, just before that tile's accumulator is ready) then cost an L2 hit, not a DRAM trip.
-          const int64_t nt = tile + gridDim.x;
-          if (nt < p.num_m_tiles && hsel == 0 && p.bn >= 64) {  // (narrow layers: 32-byte rows, not worth the issue slots)
-            const int ntwi = (int)(nt % p.tiles_w);
-            const int64_t nr = nt / p.tiles_w;
-            const int nthi = (int)(nr % p.tiles_h), nimg = (int)(nr / p.tiles_h);
-            for (int sub = 0; sub < p.ms; ++sub) {
-              int ngy, ngx;
-              if (p.wstack) {
-                ngy = nthi * unit_h + row / p.tw, ngx = ntwi * unit_w + sub * p.tw + row % p.tw;
-              } else {
-                const int idx = sub * kTileM + row;
-                ngy = nthi * unit_h + idx / p.tw, ngx = ntwi * unit_w + idx % p.tw;
-              }
-              if (ngy < p.gh && ngx < p.gw) {
-                const __nv_bfloat16 *rp = res + (((int64_t)nimg * p.oh + ngy) * p.ow + ngx) * p.r_ct + p.r_co + co_base;
-                for (int b = 0; b < p.bn * 2; b += 128)
-                  asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(rp) + b));
-              }
-            }
-          }
+          ring_advance(p.a_stages_per_unit);
+          res_first = ring;
+          uint32_t rs = ring, rph = ring_phase;
 #pragma unroll
-          for (int ci = 0; ci < kMy; ++ci) {
-            rr[ci][0] = make_uint4(0, 0, 0, 0);
-            rr[ci][1] = make_uint4(0, 0, 0, 0);
-            int gy, gx;
-            if (ci < my_chunks && pixel((int)(ck_meta[ci] >> 16), gy, gx)) {
-              const int64_t opix0 = ((int64_t)img * p.oh + gy) * p.ow + gx;  // forward conv: ostride 1
-              const uint4 *rp = reinterpret_cast<const uint4 *>(res + opix0 * p.r_ct + p.r_co + co_base +
-                                                                (int)(ck_meta[ci] & 0xffffu));
-              rr[ci][0] = __ldg(rp);
-              rr[ci][1] = __ldg(rp + 1);
+          for (int sb = 0; sb < 4; ++sb) {
+            if (sb < p.res_boxes) {
+              mbar_wait(full_bar + 8 * rs, rph, dead);
+              if (++rs == (uint32_t)p.stages) rs = 0, rph ^= 1;
             }
           }
+          ring_advance(p.res_boxes);
         }
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
@@ -481,6 +476,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
               tmem_ld_wait();
               if (ci + 1 < kMy && ci + 1 < my_chunks) tmem_ld16(tbase + ck_tcol[ci + 1], v[(ci + 1) & 1]);
               const int c0 = (int)(ck_meta[ci] & 0xffffu);
+              uint4 rres0 = make_uint4(0, 0, 0, 0), rres1 = rres0;
+              if constexpr (RES) {  // residual chunk: same swizzled position as the output chunk, in its ring stage
+                const uint32_t sb = ck_meta[ci] >> 24;
+                uint32_t rslot = res_first + sb;
+                if (rslot >= (uint32_t)p.stages) rslot -= (uint32_t)p.stages;
+                const uint32_t ra = s_a + rslot * kStageBytes + (ck_st0[ci] - sb * box_bytes);
+                const float4 f0 = lds128(ra), f1 = lds128(ra ^ 16u);
+                rres0 = make_uint4(__float_as_uint(f0.x), __float_as_uint(f0.y), __float_as_uint(f0.z), __float_as_uint(f0.w));
+                rres1 = make_uint4(__float_as_uint(f1.x), __float_as_uint(f1.y), __float_as_uint(f1.z), __float_as_uint(f1.w));
+              }
               uint32_t pk[8];
 #pragma unroll
               for (int e4 = 0; e4 < 16; e4 += 4) {
@@ -499,7 +504,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
                   for (int j = 0; j < 4; ++j) o[j] = fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi);
                 } else {
-                  const uint4 w4 = rr[ci][e4 >> 3];
+                  const uint4 w4 = (e4 & 8) ? rres1 : rres0;
                   const uint32_t lo2 = (e4 & 4) ? w4.z : w4.x, hi2 = (e4 & 4) ? w4.w : w4.y;
                   const float rv[4] = {bf16_lo(lo2), bf16_hi(lo2), bf16_lo(hi2), bf16_hi(hi2)};
                   if (ep.res_mode == RTSEG_RES_PRE) {
@@ -522,6 +527,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           }
           fence_async_smem();
           epi_bar_sync(1);  // every warp has written its part of the staging tile
+          if constexpr (RES) {
+            if (elected) {  // ... and has read its residual chunks: hand the ring stages back to the producer
+              uint32_t rs = res_first;
+              for (int sb = 0; sb < p.res_boxes; ++sb) {
+                mbar_arrive(empty_bar + 8 * rs);
+                if (++rs == (uint32_t)p.stages) rs = 0;
+              }
+            }
+          }
           if (elected) {
             const int nbox = p.bn / p.ob;
             for (int sb = 0; sb < nbox; ++sb)
@@ -652,7 +666,7 @@ static int pick_kb(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : 16); }
 
 struct TcPlan {
   int kb, bn, n_tiles, stages, ob, ms, out_bufs;
-  uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols;
+  uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols, stage_bytes;
 };
 
 // Chooses the N tile so that resident weights + output staging leave room for >= 3 A stages.
@@ -670,7 +684,7 @@ static uint32_t tc_stage_bytes(int share, int halo, int ms, int kb) {
 
 static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, bool has_res,
                     TcPlan &pl, int share = 0, int halo = 0) {
-  const int chunk_cap = has_res ? kMaxMyChunks : 2 * kMaxMyChunks;  // 16-column chunks per unit (two warps share)
+  const int chunk_cap = 2 * kMaxMyChunks;  // 16-column chunks per unit (two warps share)
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
   for (int bn = std::min(256, cout_pad); bn >= 16; bn -= 16) {
@@ -685,6 +699,8 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     const uint32_t misc = 3 * bn * 4 + (2 * kMaxStages + 5) * 8 + 16 + 1024;
     for (; ms >= 1; ms >>= 1) {
       stage_bytes = tc_stage_bytes(share, halo, ms, pl.kb);
+      if (has_res)  // residual sub-boxes [ob ch x unit] travel through the same ring
+        stage_bytes = std::max(stage_bytes, ((uint32_t)ms * kTileM * pick_kb(bn) * 2 + 1023) / 1024 * 1024);
       out_buf = staged_out ? (uint32_t)ms * kTileM * bn * 2 : 0;
       fixed = b_bytes + kOutBufs * out_buf + misc;
       // a shared halo stage feeds a whole K block (all taps), so three of them already cover three units
@@ -695,6 +711,7 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     if (ms < 1) {
       ms = 1;
       stage_bytes = tc_stage_bytes(share, halo, 1, pl.kb);
+      if (has_res) stage_bytes = std::max(stage_bytes, ((uint32_t)kTileM * pick_kb(bn) * 2 + 1023) / 1024 * 1024);
       out_buf = staged_out ? (uint32_t)kTileM * bn * 2 : 0;
       fixed = b_bytes + kOutBufs * out_buf + misc;
       // Fewer than five A stages in flight starve the MMAs (each tile needs taps*nkb of them):
@@ -706,6 +723,7 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     }
     if (fixed + 3 * stage_bytes > kSmemBudget) continue;
     pl.out_bufs = out_bufs;
+    pl.stage_bytes = stage_bytes;
     pl.ms = ms;
     pl.bn = bn;
     pl.n_tiles = cout_pad / bn;
@@ -795,7 +813,7 @@ static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, co
     mode = 3;
   else if (labels != nullptr || p.y_mode != 2)
     mode = 2;
-  const bool has_res = ep.res_mode != RTSEG_RES_NONE;
+  const bool has_res = p.res_boxes > 0;
 #define RTSEG_TC(KB_)                                                                                          \
   return mode == 3   ? launch_tc_inst<KB_, 3, false>(maps, p, pl, ep, res, y, labels, st)                      \
          : mode == 2 ? launch_tc_inst<KB_, 2, false>(maps, p, pl, ep, res, y, labels, st)                      \
@@ -898,7 +916,9 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
     p.a_sub16 = ((uint32_t)kTileM * pl.kb * 2) >> 4;
     p.a_sbo16 = (8u * pl.kb * 2) >> 4;
   }
-  p.stage_bytes = tc_stage_bytes(share, halo, p.ms, pl.kb);
+  p.stage_bytes = pl.stage_bytes;
+  p.a_stages_per_unit = 0;  // set by the caller
+  p.res_boxes = 0;
   p.a_tx_bytes = (uint32_t)p.box_w * p.box_h * pl.kb * 2;
   p.tiles_w = (int)cdiv(p.gw, p.unit_w), p.tiles_h = (int)cdiv(p.gh, p.unit_h);
   p.num_m_tiles = (int64_t)p.n * p.tiles_w * p.tiles_h;
@@ -959,7 +979,12 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   p.ntaps = ntaps;
   p.y_mode = staged ? 2 : 1;
   fill_common(p, d, pl, cout_pad, share);
-  const int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  p.a_stages_per_unit = share ? p.nkb : ntaps * p.nkb;
+  const bool has_res = d->res_mode != RTSEG_RES_NONE;
+  const bool ring_res = has_res && staged && mode <= 1 && pl.bn / pl.ob <= 4;
+  if (has_res && !ring_res) mode = 2;  // general path reads the residual with plain loads
+  if (ring_res) p.res_boxes = pl.bn / pl.ob;
 
   TcMaps maps;
   const int64_t ct = d->x_ctotal;
@@ -1001,6 +1026,14 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
     maps.c[0] = maps.a[0];
   }
   for (int a = 1; a < kMaxAcc; ++a) maps.c[a] = maps.c[0];
+  if (ring_res) {
+    const int64_t rc = d->r_ctotal;
+    if (int e = encode_nhwc_map(&maps.r, res, d->r_coff + d->cout, p.ow, p.oh, d->n, rc, rc * p.ow, rc * p.ow * p.oh,
+                                pl.ob, p.unit_w, p.unit_h))
+      return e;
+  } else {
+    maps.r = maps.a[0];
+  }
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   return launch_tc(maps, p, pl, ep, mode, res, y, nullptr, as_stream(stream));
 }
@@ -1048,6 +1081,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   p.y_mode = y == nullptr ? 0 : (staged ? 2 : 1);
   fill_common(p, d, pl, cout_pad);
   const int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  p.a_stages_per_unit = 4 * p.nkb;
   // four shifted input tiles and the MMAs each one feeds: {ky, kx, accumulator}
   static const int kOps[4][4][3] = {
       {{1, 1, 0}, {1, 2, 1}, {2, 1, 2}, {2, 2, 3}},      // A00
@@ -1081,6 +1115,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
       maps.c[a] = maps.a[0];
     }
   }
+  maps.r = maps.a[0];
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   return launch_tc(maps, p, pl, ep, mode, nullptr, y, labels, as_stream(stream));
 }
