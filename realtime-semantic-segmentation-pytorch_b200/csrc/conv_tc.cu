@@ -268,7 +268,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer ====
-    if (lane == 0) {
+    // The whole warp walks the loop (uniform control flow, uniform registers); one elected lane issues.
+    {
       const uint32_t idesc = make_idesc(p.bn);
       // Descriptors differ only in their 14-bit start-address field: build them once and add
       // (byte offset >> 4) — the issuing thread is a single lane, every instruction counts.
@@ -287,10 +288,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
+            if (elect_one()) {
             for (int t = 0; t < p.ntaps; ++t) {
               const TcTap &tap = p.taps[t];
               const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[0] * p.nkb + kb) * blk16);
-              const uint32_t fresh = started & 1u;
+              const uint32_t fresh = (started & 1u) | (t > 0 ? 1u : 0u);
               for (int sub = 0; sub < p.ms; ++sub) {
                 const uint32_t off16 = stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16;
                 uint64_t a_d = a_desc0 + (uint64_t)off16;
@@ -301,9 +303,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
                 for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
               }
-              started |= 1u;
             }
             umma_commit(empty_bar + 8 * stage);
+            }
+            __syncwarp();
+            started |= 1u;
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         } else
@@ -313,26 +317,30 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
             const uint64_t a_st = a_desc0 + (uint64_t)(stage * stage16);
-            for (int o = 0; o < tap.nops; ++o) {
-              const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
-              const uint32_t a_acc = (uint32_t)tap.acc[o];
-              const uint32_t fresh = (started >> a_acc) & 1u;  // same for every sub-tile of this accumulator
-              for (int sub = 0; sub < p.ms; ++sub) {
-                const uint64_t a_d = a_st + (uint64_t)((uint32_t)sub * sub16);
-                const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
-                umma_bf16(d_col, a_d, b_d, idesc, fresh);
+            if (elect_one()) {
+              for (int o = 0; o < tap.nops; ++o) {
+                const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
+                const uint32_t a_acc = (uint32_t)tap.acc[o];
+                const uint32_t fresh = (started >> a_acc) & 1u;  // same for every sub-tile of this accumulator
+                for (int sub = 0; sub < p.ms; ++sub) {
+                  const uint64_t a_d = a_st + (uint64_t)((uint32_t)sub * sub16);
+                  const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
+                  umma_bf16(d_col, a_d, b_d, idesc, fresh);
 #pragma unroll
-                for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                  for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                }
               }
-              started |= 1u << a_acc;
+              umma_commit(empty_bar + 8 * stage);  // frees the A stage when these MMAs retire
             }
-            umma_commit(empty_bar + 8 * stage);  // frees the A stage when these MMAs retire
+            __syncwarp();
+            for (int o = 0; o < tap.nops; ++o) started |= 1u << (uint32_t)tap.acc[o];
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         }
         for (int sb = 0; sb < p.res_boxes; ++sb)  // residual stages belong to the epilogue
           if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
-        umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
+        if (elect_one()) umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
+        __syncwarp();
         if (++acc == 2) acc = 0, acc_phase ^= 1;
       }
     }
@@ -716,7 +724,8 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
       fixed = b_bytes + kOutBufs * out_buf + misc;
       // Fewer than five A stages in flight starve the MMAs (each tile needs taps*nkb of them):
       // give up the second staging buffer instead.
-      if (fixed + 5 * stage_bytes > kSmemBudget && out_buf) {
+      static const int min_stages_knob = getenv("RTSEG_TC_MINSTAGES") ? atoi(getenv("RTSEG_TC_MINSTAGES")) : 5;
+      if (fixed + (uint32_t)min_stages_knob * stage_bytes > kSmemBudget && out_buf) {
         out_bufs = 1;
         fixed = b_bytes + out_buf + misc;
       }
