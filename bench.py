@@ -195,8 +195,20 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             del x, y
         kernel = "dw_win_kernel / dw_vec_kernel (NHWC depthwise 3x3 + BN + act)"
     achieved = total_bytes / (total_ms * 1e-3) / 1e9
+    # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the same kernel family over one step, from the
+    # committed ncu launch list of this command (profiles/launches_r01.md); null for workloads not captured.
+    traffic = None
+    if workload == "erfnet" and batch == 16:
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+                traffic = int(json.load(f)["conv_tc_dram_bytes_per_step"])
+        except Exception:
+            traffic = None
     return {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 1), "peak": peak_gbs, "unit": "GB/s",
-            "frac": round(achieved / peak_gbs, 4), "traffic": None, "peak_source": peak_src,
+            "frac": round(achieved / peak_gbs, 4), "traffic": traffic,
+            "traffic_note": "DRAM bytes per step of all 73 conv_tc launches (ncu, profiles/launches_r01.md); "
+                            "bytes_per_step is the algorithmic figure of the 68 timed launches",
+            "peak_source": peak_src,
             "launches_per_step": launches, "bytes_per_step": int(total_bytes), "ms_per_step": round(total_ms, 4),
             "frac_of_8TBps_nominal": round(achieved / 8000.0, 4)}
 

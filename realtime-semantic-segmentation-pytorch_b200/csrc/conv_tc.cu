@@ -880,7 +880,9 @@ static int pick_share(const rtseg_conv_desc *d, int gh, int gw, int kb) {
   if ((knob & 1) && d->kw == 1 && d->kh >= 2 && (d->kh - 1) * d->dil < (d->kh - 1) * 16 && d->pad_w == 0 && gw >= 8 &&
       gh >= 16)
     return 1;
-  if ((knob & 2) && d->kh == 1 && d->kw >= 2 && kb == 64 && (d->kw - 1) * d->dil <= 64 && d->pad_h == 0 && gw > 64)
+  static const int h_any_kb = getenv("RTSEG_TC_HANYKB") ? atoi(getenv("RTSEG_TC_HANYKB")) : 1;
+  if ((knob & 2) && d->kh == 1 && d->kw >= 2 && (kb == 64 || h_any_kb) && (d->kw - 1) * d->dil <= 64 && d->pad_h == 0 &&
+      gw > 64)
     return 2;
   return 0;
 }

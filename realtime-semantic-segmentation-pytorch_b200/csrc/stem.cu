@@ -153,21 +153,36 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T
   float m[V];
 #pragma unroll
   for (int e = 0; e < V; ++e) m[e] = -FLT_MAX;
-  for (int ky = 0; ky < 3; ++ky) {
-    const int hi = ho * 2 - 1 + ky;
-    if (hi < 0 || hi >= p.h) continue;
-    for (int kx = 0; kx < 3; ++kx) {
-      const int wi = wo * 2 - 1 + kx;
-      if (wi < 0 || wi >= p.w) continue;
-      const T *xp = x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0;
-      if constexpr (V == 1) {
-        m[0] = fmaxf(m[0], ld_f<T>(xp));
-      } else {
-        float v[V];
-        Vec16<T>::load(xp, v);
-#pragma unroll
-        for (int e = 0; e < V; ++e) m[e] = fmaxf(m[e], v[e]);
+  if constexpr (V == 1) {
+    for (int ky = 0; ky < 3; ++ky) {
+      const int hi = ho * 2 - 1 + ky;
+      if (hi < 0 || hi >= p.h) continue;
+      for (int kx = 0; kx < 3; ++kx) {
+        const int wi = wo * 2 - 1 + kx;
+        if (wi < 0 || wi >= p.w) continue;
+        m[0] = fmaxf(m[0], ld_f<T>(x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0));
       }
+    }
+  } else {
+    // nine independent 16-byte loads in flight, then the reduction (out-of-image taps replicate the centre)
+    typename Vec16<T>::Raw raw[9];
+    const T *centre = x + (((int64_t)n * p.h + ho * 2) * p.w + wo * 2) * p.x_ct + p.x_co + c0;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int hi = ho * 2 - 1 + ky;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int wi = wo * 2 - 1 + kx;
+        const bool ok = hi >= 0 && hi < p.h && wi >= 0 && wi < p.w;
+        raw[ky * 3 + kx] = Vec16<T>::ldg(ok ? x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0 : centre);
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      float v[V];
+      Vec16<T>::unpack(raw[t], v);
+#pragma unroll
+      for (int e = 0; e < V; ++e) m[e] = fmaxf(m[e], v[e]);
     }
   }
   T *yp = y + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.y_ct + p.y_co + c0;
