@@ -190,10 +190,11 @@ int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_
                             rtseg_stream_t stream);
 /* Fused bilinear upsample + first-max argmax over channels (+ optional
  * confusion-matrix update when target != NULL): the full-resolution logits
- * never exist.  labels_u8 and/or labels_i64 may be NULL.  confmat is int64
+ * never exist.  x holds x_ctotal >= c channels per pixel (the classifier may write a padded,
+ * 16-byte-aligned buffer); only the first c are classes.  labels_u8 and/or labels_i64 may be NULL.  confmat is int64
  * [c][c], rows = target (utils/metrics.py:4-7 semantics).                   */
-int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
-                          int32_t align_corners, int32_t dtype, const void *x, uint8_t *labels_u8,
+int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t x_ctotal, int32_t ho,
+                          int32_t wo, int32_t align_corners, int32_t dtype, const void *x, uint8_t *labels_u8,
                           int64_t *labels_i64, const int64_t *target, int32_t ignore_index,
                           int64_t *confmat, rtseg_stream_t stream);
 /* argmax over channels of an NHWC tensor (preds.max(dim=1)[1], core/seg_trainer.py:172). */

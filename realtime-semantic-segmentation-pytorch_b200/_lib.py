@@ -62,7 +62,7 @@ PROTOTYPES = {
     "rtseg_deconv3x3s2_tc_supported": (c_i32, [_DP]),
     "rtseg_deconv3x3s2_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_upsample_bilinear": (c_i32, [c_i32] * 8 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
-    "rtseg_upsample_argmax": (c_i32, [c_i32] * 8 + [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "rtseg_upsample_argmax": (c_i32, [c_i32] * 9 + [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "rtseg_argmax_nhwc": (c_i32, [c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_argmax_nchw": (c_i32, [c_i32, c_i32, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_confmat_update": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),

@@ -202,7 +202,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
     const int c = co_base + i;
     const bool ok = c < p.cout;
     g_scale[i] = (ok && ep.scale) ? ep.scale[c] : 1.f;
-    g_scale[p.bn + i] = (ok && ep.shift) ? ep.shift[c] : 0.f;
+    // (labels-only mode: padded classes get shift = -inf so that they evaluate to the clamp's lower bound)
+    g_scale[p.bn + i] = ok ? (ep.shift ? ep.shift[c] : 0.f) : (MODE == 3 ? -INFINITY : 0.f);
     g_scale[2 * p.bn + i] = (ok && ep.slope) ? ep.slope[c] : 0.f;
   }
   if (warp == 1) {
@@ -406,51 +407,94 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
 
       if constexpr (MODE == 3) {
         // ---- labels-only transposed conv (the segmentation head): the logits never leave TMEM.
-        // The two warps of a lane quarter split the output ROW parity; each thread reduces both
-        // column parities of its input pixel and writes two adjacent uint8 labels with one store.
+        // The two warps of a lane quarter split the output ROW parity; each thread reduces both column
+        // parities of its input pixel and writes two adjacent uint8 labels with one store.  The argmax
+        // runs as four independent compare/select chains (2 output pixels x 2 interleaved channel groups)
+        // merged at the end with "larger value, then smaller index" — the first maximum wins, like
+        // torch.max.  Padded classes evaluate to the clamp's lower bound (shift = -inf in shared memory)
+        // and can never beat a real class.  NaNs poison a running sum and divert to an exact slow path.
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
 #pragma unroll 1
         for (int sub = 0; sub < p.ms; ++sub) {
-        uint32_t lab2 = 0;
-#pragma unroll 1
-        for (int px = 0; px < 2; ++px) {
-          const int a = hsel * 2 + px;
-          const uint32_t taddr =
-              tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + a) * p.bn);
-          float best = -FLT_MAX;
-          int best_idx = 0;
+          const uint32_t t0 =
+              tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + hsel * 2) * p.bn);
+          float best[2][2];
+          int bidx[2][2];
+#pragma unroll
+          for (int px = 0; px < 2; ++px) {
+            best[px][0] = best[px][1] = -INFINITY;
+            bidx[px][0] = 0, bidx[px][1] = 8;
+          }
+          float nansum = 0.f;
 #pragma unroll
           for (int ci = 0; ci < kMaxMyChunks; ++ci) {
             if (ci < nchunks) {  // warp-uniform
               const int c0 = ci * 16;
-              uint32_t v[16];
-              tmem_ld16(taddr + c0, v);
+              uint32_t v[2][16];
+              tmem_ld16(t0 + c0, v[0]);
+              tmem_ld16(t0 + (uint32_t)p.bn + c0, v[1]);
               tmem_ld_wait();
 #pragma unroll
               for (int e4 = 0; e4 < 16; e4 += 4) {
-                if (c0 + e4 >= p.cout) break;  // padded classes (e.g. 19 -> 32) never win; skip their math
-                const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
-                const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
-                const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
+                if (c0 + e4 < p.cout) {  // whole groups of padded classes: skip their math (warp-uniform)
+                  const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
+                  const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
+                  const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  float t = fminf(fmaxf(fmaf(__uint_as_float(v[e4 + j]), scv[j], shv[j]), p.lo), p.hi);
-                  // compare the values the logits tensor would hold (bf16-rounded), first maximum wins
-                  t = __bfloat162float(__float2bfloat16_rn(t));
-                  const int ch = c0 + e4 + j;
-                  if (ch < p.cout && (ch == 0 || t > best || (t != t && best == best))) best = t, best_idx = ch;
+                  for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                    for (int px = 0; px < 2; ++px) {
+                      float t = fminf(fmaxf(fmaf(__uint_as_float(v[px][e4 + j]), scv[j], shv[j]), p.lo), p.hi);
+                      // compare the values the logits tensor would hold (bf16-rounded)
+                      t = __bfloat162float(__float2bfloat16_rn(t));
+                      nansum += t;
+                      constexpr int kChainSel = 0;
+                      const int h = ((e4 + j) >> 3) & 1;  // compile-time after unrolling
+                      const bool g = t > best[px][h];
+                      best[px][h] = g ? t : best[px][h];
+                      bidx[px][h] = g ? (c0 + e4 + j) : bidx[px][h];
+                      (void)kChainSel;
+                    }
+                  }
                 }
               }
             }
           }
-          lab2 |= (uint32_t)best_idx << (8 * px);
-        }
-        int gy, gx;
-        if (pixel(sub, gy, gx)) {
-          const int64_t opix = ((int64_t)img * p.oh + (gy * 2 + hsel)) * p.ow + gx * 2;
-          *reinterpret_cast<uint16_t *>(labels + opix) = (uint16_t)lab2;
-        }
+          uint32_t lab2 = 0;
+#pragma unroll
+          for (int px = 0; px < 2; ++px) {
+            const bool take1 = best[px][1] > best[px][0] || (best[px][1] == best[px][0] && bidx[px][1] < bidx[px][0]);
+            lab2 |= (uint32_t)(take1 ? bidx[px][1] : bidx[px][0]) << (8 * px);
+          }
+          if (nansum != nansum) {  // a NaN (or inf - inf) somewhere: redo this pixel pair with exact semantics
+            lab2 = 0;
+#pragma unroll 1
+            for (int px = 0; px < 2; ++px) {
+              float bs = 0.f;
+              int bi = 0;
+#pragma unroll 1
+              for (int c0 = 0; c0 < p.bn; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(t0 + (uint32_t)(px * p.bn) + c0, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  if (c0 + j < p.cout) {
+                    float t = fminf(fmaxf(fmaf(__uint_as_float(v[j]), g_scale[c0 + j], g_scale[p.bn + c0 + j]), p.lo), p.hi);
+                    t = __bfloat162float(__float2bfloat16_rn(t));
+                    if (c0 + j == 0 || t > bs || (t != t && bs == bs)) bs = t, bi = c0 + j;
+                  }
+                }
+              }
+              lab2 |= (uint32_t)bi << (8 * px);
+            }
+          }
+          int gy, gx;
+          if (pixel(sub, gy, gx)) {
+            const int64_t opix = ((int64_t)img * p.oh + (gy * 2 + hsel)) * p.ow + gx * 2;
+            *reinterpret_cast<uint16_t *>(labels + opix) = (uint16_t)lab2;
+          }
         }
       } else if constexpr (MODE != 2) {
         // ---- fast path: staged TMA-store output, branch-free activation, residual prefetched into

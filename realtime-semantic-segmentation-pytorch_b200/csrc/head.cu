@@ -111,7 +111,7 @@ __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool val
 // detected when a source row is loaded and handled by a slow exact path.
 template <typename T, int CMAX>
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
-    int n, int hi, int wi, int c, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
+    int n, int hi, int wi, int c, int ct, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
     uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
     unsigned long long *__restrict__ confmat) {
   __shared__ int hist[kMaxBins];
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
   int x0 = 0, x1 = 0;
   float lx0 = 1.f, lx1 = 0.f;
   if (col_ok) src_index(ox, sx, wi, align, x0, x1, lx0, lx1);
-  const T *xb = x + (int64_t)b * hi * wi * c;
+  const T *xb = x + (int64_t)b * hi * wi * ct;  // ct = channels per pixel of the (possibly padded) logits buffer
 
   float rowA[CMAX], rowD[CMAX];  // A and (B - A)
   int ia = -1, ib = -1;
@@ -136,8 +136,8 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
 
   // horizontally interpolated source row i, channels >= c padded so that they never win
   auto load_row = [&](int i, float(&row)[CMAX]) {
-    const T *p0 = xb + ((int64_t)i * wi + x0) * c;
-    const T *p1 = xb + ((int64_t)i * wi + x1) * c;
+    const T *p0 = xb + ((int64_t)i * wi + x0) * ct;
+    const T *p1 = xb + ((int64_t)i * wi + x1) * ct;
 #pragma unroll
     for (int k = 0; k < CMAX; ++k) {
       float v = -FLT_MAX;
@@ -402,7 +402,7 @@ extern "C" int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_
 }
 
 template <typename T>
-static int launch_upsample_argmax(int n, int hi, int wi, int c, int ho, int wo, int align, const void *x,
+static int launch_upsample_argmax(int n, int hi, int wi, int c, int ct, int ho, int wo, int align, const void *x,
                                   uint8_t *l8, int64_t *l64, const int64_t *target, int ignore, int64_t *confmat,
                                   cudaStream_t st) {
   const float sy = resize_scale(hi, ho, align), sx = resize_scale(wi, wo, align);
@@ -411,13 +411,13 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ho, int wo, 
   const T *xs = static_cast<const T *>(x);
 #define RTSEG_HEAD(CM)                                                                                              \
   if (c <= CM) {                                                                                                    \
-    upsample_argmax_kernel<T, CM><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, l8, l64, \
+    upsample_argmax_kernel<T, CM><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64, \
                                                                  target, ignore, cm);                              \
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");                                                                   \
     return RTSEG_OK;                                                                                                \
   }
   if (c == 19) {  // Cityscapes: exact instantiation, no padded classes
-    upsample_argmax_kernel<T, 19><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, l8, l64,
+    upsample_argmax_kernel<T, 19><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
                                                                  target, ignore, cm);
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");
     return RTSEG_OK;
@@ -430,21 +430,22 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ho, int wo, 
   RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_upsample_argmax supports at most 32 classes (got %d)", c);
 }
 
-extern "C" int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
-                                     int32_t align, int32_t dtype, const void *x, uint8_t *labels_u8,
+extern "C" int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t x_ctotal, int32_t ho,
+                                     int32_t wo, int32_t align, int32_t dtype, const void *x, uint8_t *labels_u8,
                                      int64_t *labels_i64, const int64_t *target, int32_t ignore_index,
                                      int64_t *confmat, rtseg_stream_t stream) {
   RTSEG_REQUIRE(x, "NULL logits pointer");
   RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && c > 0 && ho > 0 && wo > 0, "non-positive extent");
+  RTSEG_REQUIRE(x_ctotal >= c, "x_ctotal (%d) smaller than the class count (%d)", x_ctotal, c);
   RTSEG_REQUIRE(n <= 65535 && cdiv(ho, kHeadRows) <= 65535, "batch or height too large for one launch");
   RTSEG_REQUIRE((target == nullptr) == (confmat == nullptr), "target and confmat must be given together");
   RTSEG_REQUIRE(labels_u8 || labels_i64 || confmat, "nothing to compute");
   cudaStream_t st = as_stream(stream);
   if (dtype == RTSEG_BF16)
-    return launch_upsample_argmax<__nv_bfloat16>(n, hi, wi, c, ho, wo, align, x, labels_u8, labels_i64, target,
+    return launch_upsample_argmax<__nv_bfloat16>(n, hi, wi, c, x_ctotal, ho, wo, align, x, labels_u8, labels_i64, target,
                                                  ignore_index, confmat, st);
   if (dtype == RTSEG_F32)
-    return launch_upsample_argmax<float>(n, hi, wi, c, ho, wo, align, x, labels_u8, labels_i64, target, ignore_index,
+    return launch_upsample_argmax<float>(n, hi, wi, c, x_ctotal, ho, wo, align, x, labels_u8, labels_i64, target, ignore_index,
                                          confmat, st);
   RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
 }
@@ -556,7 +557,7 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
   cudaStream_t st = as_stream(stream);
   uint8_t *dlab = static_cast<uint8_t *>(dev_scratch) + in_padded;
   RTSEG_CUDA(cudaMemcpyAsync(dev_scratch, x_host, in_bytes, cudaMemcpyHostToDevice, st));
-  if (int rc = rtseg_upsample_argmax(n, hi, wi, c, ho, wo, align, dtype, dev_scratch, dlab, nullptr, nullptr, 255,
+  if (int rc = rtseg_upsample_argmax(n, hi, wi, c, c, ho, wo, align, dtype, dev_scratch, dlab, nullptr, nullptr, 255,
                                      nullptr, stream))
     return rc;
   RTSEG_CUDA(cudaMemcpyAsync(labels_host, dlab, out_bytes, cudaMemcpyDeviceToHost, st));

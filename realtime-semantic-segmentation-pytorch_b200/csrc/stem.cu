@@ -45,9 +45,10 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
   const int ho = (int)(r % p.ho);
   const int n = (int)(r / p.ho);
 
-  float acc[CC];
+  // channel pairs: sm_100's packed FFMA2 halves the FMA issue count of this FMA-bound kernel
+  float2 acc2[CC / 2];
 #pragma unroll
-  for (int c = 0; c < CC; ++c) acc[c] = 0.f;
+  for (int c = 0; c < CC / 2; ++c) acc2[c] = make_float2(0.f, 0.f);
   float mx[CIN];
 #pragma unroll
   for (int c = 0; c < CIN; ++c) mx[c] = -FLT_MAX;
@@ -77,18 +78,20 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
         const float v = win[ky][kx][ci];
         if (inb[ky][kx]) mx[ci] = fmaxf(mx[ci], v);
         const float *wp = &ws[((ky * 3 + kx) * CIN + ci) * CC];
+        const float2 vv = make_float2(v, v);
 #pragma unroll
         for (int c = 0; c < CC; c += 4) {
           const float4 w4 = *reinterpret_cast<const float4 *>(wp + c);
-          acc[c] = fmaf(v, w4.x, acc[c]);
-          acc[c + 1] = fmaf(v, w4.y, acc[c + 1]);
-          acc[c + 2] = fmaf(v, w4.z, acc[c + 2]);
-          acc[c + 3] = fmaf(v, w4.w, acc[c + 3]);
+          acc2[c / 2] = __ffma2_rn(vv, make_float2(w4.x, w4.y), acc2[c / 2]);
+          acc2[c / 2 + 1] = __ffma2_rn(vv, make_float2(w4.z, w4.w), acc2[c / 2 + 1]);
         }
       }
     }
   }
 
+  float acc[CC];
+#pragma unroll
+  for (int c = 0; c < CC / 2; ++c) acc[2 * c] = acc2[c].x, acc[2 * c + 1] = acc2[c].y;
   TO *yp = y + pix * p.y_ct + p.y_co;
   const int ctot = p.cconv + (p.pool ? CIN : 0);
   // Assemble the output channel vector in registers, then store 16-byte chunks when possible.

@@ -252,10 +252,13 @@ class FastSCNN(nn.Module):
         self.learning_to_downsample.act_dtype = dtype
         return self
 
-    def lowres_logits(self, x):
+    def _features(self, x):
         hi = self.learning_to_downsample(x)
         lo = self.global_feature_extractor(hi)
-        return self.classifier(self.feature_fusion(hi, lo))
+        return self.classifier[1](self.classifier[0](self.feature_fusion(hi, lo)))
+
+    def lowres_logits(self, x):
+        return self.classifier[2](self._features(x))
 
     def forward(self, x):
         """Full-resolution logits like the reference (bilinear x8, align_corners=True)."""
@@ -264,8 +267,15 @@ class FastSCNN(nn.Module):
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
         """uint8 class map via the fused upsample+argmax head (+ confusion-matrix update)."""
-        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
-                                   ignore_index=ignore_index)
+        f = self._features(x)
+        n, _, h, w = f.shape
+        # the 19-class head writes into a 32-channel (16-byte aligned) buffer so that its output leaves the
+        # tensor-core kernel through the TMA-store path; the fused head reads the first num_class channels
+        cpad = (self.num_class + 15) // 16 * 16
+        buf = ops.empty_nhwc(n, cpad, h, w, f.dtype, f.device)
+        self.classifier[2](f, out=buf)
+        return ops.upsample_argmax(buf, x.shape[2:], True, target=target, confmat=confmat, ignore_index=ignore_index,
+                                   num_classes=self.num_class)
 
 
 MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN}

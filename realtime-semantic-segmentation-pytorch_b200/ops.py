@@ -359,7 +359,7 @@ def upsample_bilinear(x: torch.Tensor, size: Tuple[int, int], align_corners: boo
 def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: bool = True, *,
                     out_dtype: torch.dtype = torch.uint8, target: Optional[torch.Tensor] = None,
                     confmat: Optional[torch.Tensor] = None, ignore_index: int = 255,
-                    want_labels: bool = True) -> Optional[torch.Tensor]:
+                    want_labels: bool = True, num_classes: Optional[int] = None) -> Optional[torch.Tensor]:
     """Fused F.interpolate(bilinear) + max(dim=1)[1] (+ confusion-matrix update).
 
     Replaces reference models/fastscnn.py:30 followed by core/seg_trainer.py:172 /
@@ -367,7 +367,10 @@ def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: 
     """
     _require_cuda(logits, "upsample_argmax")
     x = to_nhwc(logits)
-    n, c, hi, wi = x.shape
+    n, x_ct, hi, wi = x.shape
+    c = num_classes if num_classes is not None else x_ct  # a padded logits buffer carries extra channels
+    if not 0 < c <= x_ct:
+        raise ValueError("num_classes must be in (0, channels of logits]")
     ho, wo = int(size[0]), int(size[1])
     l8 = l64 = None
     if want_labels:
@@ -384,7 +387,7 @@ def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: 
             raise ValueError("target must be a contiguous int64 [N, H, W] tensor")
         if confmat.dtype != torch.int64 or tuple(confmat.shape) != (c, c) or not confmat.is_contiguous():
             raise ValueError("confmat must be a contiguous int64 [C, C] tensor")
-    _lib.check(_lib.load().rtseg_upsample_argmax(n, hi, wi, c, ho, wo, int(bool(align_corners)), _dtype_code(x.dtype),
+    _lib.check(_lib.load().rtseg_upsample_argmax(n, hi, wi, c, x_ct, ho, wo, int(bool(align_corners)), _dtype_code(x.dtype),
                                                  x.data_ptr(), _ptr(l8), _ptr(l64), _ptr(target), int(ignore_index),
                                                  _ptr(confmat), _stream()), "rtseg_upsample_argmax")
     return l8 if l8 is not None else l64
