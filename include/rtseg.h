@@ -272,6 +272,17 @@ int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p
                            const void *x, int32_t x_ctotal, int32_t x_coff, void *y,
                            rtseg_stream_t stream);
 
+/* F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid, models/dabnet.py:32-34 (padding counted: /9).
+ * Input: the caller's NCHW tensor (x_is_nchw = 1) or an NHWC channel slice; output: NHWC channel slice. */
+int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
+                       const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
+                       int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream);
+/* channel_shuffle, models/modules.py:18-32 (used by SSnbtUnit, models/lednet.py:87): NHWC slices,
+ * out[.., i*groups + g] = in[.., g*(c/groups) + i]; x and y must not alias.                      */
+int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, int32_t dtype, const void *x,
+                          int32_t x_ctotal, int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff,
+                          rtseg_stream_t stream);
+
 /* ---- host-buffer convenience (pinned or pageable HOST pointers) ------------
  * One call = H2D copy of the low-resolution logits, the fused head kernel,
  * D2H copy of the uint8 class map, all on `stream`, then a stream

@@ -77,12 +77,19 @@ def _pad(kernel_size, dilation):
     return (kernel_size - 1) // 2 * dilation
 
 
-def conv_bn_act(x, sd, prefix, kernel_size=3, stride=1, dilation=1, act_type="relu", groups=1, **kw):
-    """ConvBNAct (reference models/modules.py:73-85); children `0` conv, `1` bn, `2` activation."""
+def conv_bn_act(x, sd, prefix, kernel_size=3, stride=1, dilation=1, act_type="relu", groups=1, post_add=None,
+                post_act="none", **kw):
+    """ConvBNAct (reference models/modules.py:73-85); children `0` conv, `1` bn, `2` activation.
+
+    `post_add` / `post_act` restate a caller's `y += t; y = act(y)` that follows the block (DABModule,
+    SSnbtUnit, AttentionPyramidNetwork) so that storage emulation rounds once, where the fused kernel does."""
     y = F.conv2d(x, qw(sd[prefix + "0.weight"], groups), sd.get(prefix + "0.bias"), stride, _pad(kernel_size, dilation),
                  dilation, groups)
     y = batch_norm(y, sd, prefix + "1.")
-    return q(activation(y, act_type, sd, prefix + "2.", **kw))
+    y = activation(y, act_type, sd, prefix + "2.", **kw)
+    if post_add is not None:
+        y = activation(y + post_add, post_act)
+    return q(y)
 
 
 def dw_conv_bn_act(x, sd, prefix, kernel_size, stride=1, dilation=1, act_type="relu", **kw):

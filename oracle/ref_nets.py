@@ -82,7 +82,96 @@ def fastscnn_forward(sd, x, act_type="relu"):
     return F.interpolate(fastscnn_lowres_logits(sd, x, act_type), x.shape[2:], mode="bilinear", align_corners=True)
 
 
-FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward}
+# ----------------------------------------------------------------------------- DABNet ----
+def dab_module(x, sd, prefix, dilation, act_type="prelu"):
+    """DABModule (reference models/dabnet.py:71-98)."""
+    t = B.conv_bn_act(x, sd, prefix + "init_conv.", 3, 1, 1, act_type)
+    left = B.dw_conv_bn_act(t, sd, prefix + "left_branch.0.", (3, 1), 1, 1, act_type)
+    left = B.dw_conv_bn_act(left, sd, prefix + "left_branch.1.", (1, 3), 1, 1, act_type)
+    right = B.dw_conv_bn_act(t, sd, prefix + "right_branch.0.", (3, 1), 1, dilation, act_type)
+    both = B.dw_conv_bn_act(right, sd, prefix + "right_branch.1.", (1, 3), 1, dilation, act_type, post_add=left)
+    return B.conv_bn_act(both, sd, prefix + "last_conv.", 1, 1, 1, act_type, post_add=x)
+
+
+def dabnet_lowres_logits(sd, x, act_type="prelu"):
+    """DABNet.forward up to layer15 (reference models/dabnet.py:30-58)."""
+    x_d2 = B.q(F.avg_pool2d(x, 3, 2, 1))
+    x_d4 = B.q(F.avg_pool2d(x_d2, 3, 2, 1))
+    x_d8 = B.q(F.avg_pool2d(x_d4, 3, 2, 1))
+    y = B.conv_bn_act(x, sd, "layer1.", 3, 2, 1, act_type)
+    y = B.conv_bn_act(y, sd, "layer2.", 3, 1, 1, act_type)
+    y = B.conv_bn_act(y, sd, "layer3.", 3, 1, 1, act_type)
+    y = B.initial_block(torch.cat([y, x_d2], dim=1), sd, "layer4.", act_type)
+    block1 = y
+    for i in range(3):
+        y = dab_module(y, sd, f"layer5_7.{i}.", 2, act_type)
+    y = B.conv_bn_act(torch.cat([y, block1, x_d4], dim=1), sd, "layer8.", 3, 2, 1, act_type)
+    block2 = y
+    for name, d in (("layer9_10", 4), ("layer11_12", 8), ("layer13_14", 16)):
+        for i in range(2):
+            y = dab_module(y, sd, f"{name}.{i}.", d, act_type)
+    y = torch.cat([y, block2, x_d8], dim=1)
+    return B.q(F.conv2d(y, B.qw(sd["layer15.weight"])))
+
+
+def dabnet_forward(sd, x, act_type="prelu"):
+    return F.interpolate(dabnet_lowres_logits(sd, x, act_type), x.shape[2:], mode="bilinear", align_corners=True)
+
+
+# ----------------------------------------------------------------------------- LEDNet ----
+def channel_shuffle(x, groups=2):
+    """reference models/modules.py:18-32: out[:, i*groups + g] = x[:, g*(C/groups) + i]."""
+    n, c, h, w = x.shape
+    return x.reshape(n, groups, c // groups, h, w).transpose(1, 2).reshape(n, c, h, w)
+
+
+def ss_nbt_unit(x, sd, prefix, dilation, act_type="relu"):
+    """SSnbtUnit (reference models/lednet.py:52-88)."""
+    sc = x.shape[1] // 2
+    halves = []
+    for name, first, second, xs in (("left_branch.", (3, 1), (1, 3), x[:, :sc]), ("right_branch.", (1, 3), (3, 1), x[:, sc:])):
+        p = prefix + name
+        t = F.conv2d(xs, B.qw(sd[p + "0.weight"]), sd[p + "0.bias"], 1, B._pad(first, 1), 1)
+        t = B.q(B.activation(t, act_type, sd, p + "1."))
+        t = B.conv_bn_act(t, sd, p + "2.", second, 1, 1, act_type)
+        t = F.conv2d(t, B.qw(sd[p + "3.weight"]), sd[p + "3.bias"], 1, B._pad(first, dilation), dilation)
+        t = B.q(B.activation(t, act_type, sd, p + "4."))
+        halves.append(B.conv_bn_act(t, sd, p + "5.", second, 1, dilation, act_type, post_add=xs, post_act=act_type))
+    return channel_shuffle(torch.cat(halves, dim=1))
+
+
+def attention_pyramid(x, sd, prefix, act_type="relu"):
+    """AttentionPyramidNetwork (reference models/lednet.py:91-136)."""
+    up = lambda t, size: B.q(F.interpolate(t, size, mode="bilinear", align_corners=True))
+    size0 = x.shape[2:]
+    l1 = B.conv_bn_act(x, sd, prefix + "left_conv1_1.", 3, 2, 1, act_type)
+    l2 = B.conv_bn_act(l1, sd, prefix + "left_conv2_1.", 3, 2, 1, act_type)
+    l3 = B.conv_bn_act(l2, sd, prefix + "left_conv3.0.", 3, 2, 1, act_type)
+    l3 = up(B.conv_bn_act(l3, sd, prefix + "left_conv3.1.", 3, 1, 1, act_type), l2.shape[2:])
+    l2 = up(B.conv_bn_act(l2, sd, prefix + "left_conv2_2.", 3, 1, 1, act_type, post_add=l3), l1.shape[2:])
+    l1 = up(B.conv_bn_act(l1, sd, prefix + "left_conv1_2.", 3, 1, 1, act_type, post_add=l2), size0)
+    mid = B.q(B.conv_bn_act(x, sd, prefix + "mid_branch.", 3, 1, 1, act_type) * l1)
+    right = B.conv_bn_act(B.q(F.adaptive_avg_pool2d(x, 1)), sd, prefix + "right_branch.1.", 3, 1, 1, act_type)
+    return B.q(mid + up(right, size0))
+
+
+def lednet_lowres_logits(sd, x, act_type="relu"):
+    """LEDNet encoder + APN (reference models/lednet.py:16-50)."""
+    idx = 0
+    for cout, dils in ((32, [1, 1, 1]), (64, [1, 1]), (128, [1, 2, 5, 9, 2, 5, 9, 17])):
+        x = B.initial_block(x, sd, f"encoder.{idx}.", act_type)
+        idx += 1
+        for d in dils:
+            x = ss_nbt_unit(x, sd, f"encoder.{idx}.", d, act_type)
+            idx += 1
+    return attention_pyramid(x, sd, "apn.", act_type)
+
+
+def lednet_forward(sd, x, act_type="relu"):
+    return F.interpolate(lednet_lowres_logits(sd, x, act_type), x.shape[2:], mode="bilinear", align_corners=True)
+
+
+FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward, "dabnet": dabnet_forward, "lednet": lednet_forward}
 
 
 # --------------------------------------------------------------------- seeded weights ----

@@ -363,6 +363,50 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int
   }
 }
 
+
+// ------------------------------------------------- avg-pool 3x3 s2 p1, channel shuffle ----
+// F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid (reference models/dabnet.py:32-34): padding counts
+// (count_include_pad=True, the default), i.e. always divide by 9.  Input strides are explicit so that the
+// caller's NCHW image and our NHWC buffers both work; output is an NHWC channel slice.
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) avgpool3x3s2_kernel(int n, int h, int w, int c, int ho, int wo, int64_t sn,
+                                                           int64_t sc, int64_t sh, int64_t sw, const TI *__restrict__ x,
+                                                           TO *__restrict__ y, int y_ct, int y_co) {
+  const int64_t total = (int64_t)n * ho * wo * c;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int ch = (int)(tid % c);
+  int64_t r = tid / c;
+  const int ox = (int)(r % wo);
+  r /= wo;
+  const int oy = (int)(r % ho);
+  const int b = (int)(r / ho);
+  float s = 0.f;
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    const int iy = oy * 2 - 1 + ky;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int ix = ox * 2 - 1 + kx;
+      if (iy >= 0 && iy < h && ix >= 0 && ix < w) s += ld_f<TI>(x + b * sn + ch * sc + iy * sh + ix * sw);
+    }
+  }
+  st_f<TO>(y + (((int64_t)b * ho + oy) * wo + ox) * y_ct + y_co + ch, s * (1.f / 9.f));
+}
+
+// channel_shuffle (reference models/modules.py:18-32): out[.., i*groups + g] = in[.., g*(c/groups) + i].
+template <typename T>
+__global__ void __launch_bounds__(256) channel_shuffle_kernel(int64_t npix, int c, int groups, const T *__restrict__ x,
+                                                              int x_ct, int x_co, T *__restrict__ y, int y_ct, int y_co) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= npix * c) return;
+  const int k = (int)(tid % c);
+  const int64_t pix = tid / c;
+  const int cpg = c / groups;
+  const int g = k % groups, i = k / groups;
+  y[pix * y_ct + y_co + k] = x[pix * x_ct + x_co + g * cpg + i];
+}
+
 }  // namespace rtseg
 
 using namespace rtseg;
@@ -562,5 +606,55 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
     return rc;
   RTSEG_CUDA(cudaMemcpyAsync(labels_host, dlab, out_bytes, cudaMemcpyDeviceToHost, st));
   RTSEG_CUDA(cudaStreamSynchronize(st));
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
+                                  const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
+                                  int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && h > 0 && w > 0 && c > 0 && y_ctotal >= y_coff + c && y_coff >= 0, "bad extent");
+  const int ho = (h - 1) / 2 + 1, wo = (w - 1) / 2 + 1;
+  int64_t sn, sc, sh, sw;
+  if (x_is_nchw) {
+    sn = (int64_t)c * h * w, sc = (int64_t)h * w, sh = w, sw = 1;
+  } else {
+    RTSEG_REQUIRE(x_ctotal >= x_coff + c && x_coff >= 0, "input channel slice out of range");
+    sn = (int64_t)h * w * x_ctotal, sc = 1, sh = (int64_t)w * x_ctotal, sw = x_ctotal;
+    x = static_cast<const char *>(x) + (size_t)x_coff * (x_dtype == RTSEG_BF16 ? 2 : 4);
+  }
+  const int64_t total = (int64_t)n * ho * wo * c;
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  cudaStream_t st = as_stream(stream);
+#define RTSEG_AVG(TI_, TO_)                                                                                     \
+  avgpool3x3s2_kernel<TI_, TO_><<<grid, 256, 0, st>>>(n, h, w, c, ho, wo, sn, sc, sh, sw, (const TI_ *)x, (TO_ *)y, \
+                                                      y_ctotal, y_coff)
+  if (x_dtype == RTSEG_F32 && y_dtype == RTSEG_F32) RTSEG_AVG(float, float);
+  else if (x_dtype == RTSEG_F32 && y_dtype == RTSEG_BF16) RTSEG_AVG(float, __nv_bfloat16);
+  else if (x_dtype == RTSEG_BF16 && y_dtype == RTSEG_BF16) RTSEG_AVG(__nv_bfloat16, __nv_bfloat16);
+  else if (x_dtype == RTSEG_BF16 && y_dtype == RTSEG_F32) RTSEG_AVG(__nv_bfloat16, float);
+  else RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+#undef RTSEG_AVG
+  RTSEG_LAUNCH_CHECK("avgpool3x3s2_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, int32_t dtype, const void *x,
+                                     int32_t x_ctotal, int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff,
+                                     rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y && x != y, "NULL pointer or in-place shuffle");
+  RTSEG_REQUIRE(npix > 0 && c > 0 && groups > 0 && c % groups == 0, "channels must be divisible by groups");
+  RTSEG_REQUIRE(x_ctotal >= x_coff + c && y_ctotal >= y_coff + c && x_coff >= 0 && y_coff >= 0, "channel slice out of range");
+  const unsigned grid = (unsigned)cdiv(npix * c, 256);
+  cudaStream_t st = as_stream(stream);
+  if (dtype == RTSEG_BF16)
+    channel_shuffle_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, groups, (const __nv_bfloat16 *)x, x_ctotal, x_coff,
+                                                                (__nv_bfloat16 *)y, y_ctotal, y_coff);
+  else if (dtype == RTSEG_F32)
+    channel_shuffle_kernel<float><<<grid, 256, 0, st>>>(npix, c, groups, (const float *)x, x_ctotal, x_coff, (float *)y,
+                                                        y_ctotal, y_coff);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("channel_shuffle_kernel");
   return RTSEG_OK;
 }

@@ -86,10 +86,11 @@ class _FusedConvMixin:
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
         return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act))
 
-    def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, act2=0):
+    def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, act2=0, r_coff=0):
         _check_eval(self, self[1])
         folded, post = self._folded()
-        y = ops.conv(folded, ops.to_nhwc(x), res=res, res_mode=res_mode, out=out, x_coff=x_coff, y_coff=y_coff, act2=act2)
+        y = ops.conv(folded, ops.to_nhwc(x), res=res, res_mode=res_mode, out=out, x_coff=x_coff, y_coff=y_coff,
+                     act2=act2, r_coff=r_coff)
         return post(y) if post is not None else y
 
     def __deepcopy__(self, memo):  # keep the cache out of EMA copies (utils/model_ema.py:20)

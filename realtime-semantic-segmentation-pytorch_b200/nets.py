@@ -278,7 +278,204 @@ class FastSCNN(nn.Module):
                                    num_classes=self.num_class)
 
 
-MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN}
+# ------------------------------------------------------------------------------ DABNet ----
+class DABModule(nn.Module):
+    """Depthwise asymmetric bottleneck — reference models/dabnet.py:71-98.
+
+    3x3 (C -> C/2) -> [DW(3,1) -> DW(1,3)] || [DW(3,1,d) -> DW(1,3,d)] -> add -> 1x1 (C/2 -> C) -> += x:
+    six launches; the branch sum rides in the second dilated depthwise conv's epilogue and the block
+    residual in the 1x1 conv's epilogue (the reference needs 18 ATen kernels + 2 adds)."""
+
+    def __init__(self, channels, dilation, act_type):
+        super().__init__()
+        assert channels % 2 == 0, "Input channel of DABModule should be multiple of 2.\n"
+        hid = channels // 2
+        self.init_conv = ConvBNAct(channels, hid, 3, act_type=act_type)
+        self.left_branch = nn.Sequential(DWConvBNAct(hid, hid, (3, 1), act_type=act_type),
+                                         DWConvBNAct(hid, hid, (1, 3), act_type=act_type))
+        self.right_branch = nn.Sequential(DWConvBNAct(hid, hid, (3, 1), dilation=dilation, act_type=act_type),
+                                          DWConvBNAct(hid, hid, (1, 3), dilation=dilation, act_type=act_type))
+        self.last_conv = ConvBNAct(hid, channels, 1, act_type=act_type)
+
+    def forward(self, x):
+        x = ops.to_nhwc(x)
+        t = self.init_conv(x)
+        left = self.left_branch[1](self.left_branch[0](t))
+        s = self.right_branch[1](self.right_branch[0](t), res=left, res_mode=ops.RES_POST)   # x_left + x_right
+        return self.last_conv(s, res=x, res_mode=ops.RES_POST)                               # x += residual
+
+
+def _dab_blocks(channels, count, dilation, act_type):
+    return nn.Sequential(*[DABModule(channels, dilation, act_type=act_type) for _ in range(count)])
+
+
+class DABNet(nn.Module):
+    """DABNet — reference models/dabnet.py:16-61 (same layer names / state-dict keys).
+
+    The three concatenations with the average-pooled input pyramid are torch.cat calls (pure data
+    movement); every convolution, pooling and resize is an rtseg kernel."""
+
+    def __init__(self, num_class=1, n_channel=3, act_type="prelu"):
+        super().__init__()
+        self.layer1 = ConvBNAct(n_channel, 32, 3, 2, act_type=act_type)
+        self.layer2 = ConvBNAct(32, 32, 3, 1, act_type=act_type)
+        self.layer3 = ConvBNAct(32, 32, 3, 1, act_type=act_type)
+        self.layer4 = InitialBlock(32 + n_channel, 64, act_type=act_type)
+        self.layer5_7 = _dab_blocks(64, 3, 2, act_type)
+        self.layer8 = ConvBNAct(64 * 2 + n_channel, 128, 3, 2, act_type=act_type)
+        self.layer9_10 = _dab_blocks(128, 2, 4, act_type)
+        self.layer11_12 = _dab_blocks(128, 2, 8, act_type)
+        self.layer13_14 = _dab_blocks(128, 2, 16, act_type)
+        self.layer15 = conv1x1(128 * 2 + n_channel, num_class)
+        self.num_class = num_class
+        self.act_dtype: Optional[torch.dtype] = None
+
+    def set_act_dtype(self, dtype: Optional[torch.dtype]):
+        self.act_dtype = dtype
+        return self
+
+    def lowres_logits(self, x):
+        dt = self.act_dtype or _param_dtype(self.layer1)
+        x_d2 = ops.avgpool3x3s2(x, out_dtype=dt)
+        x_d4 = ops.avgpool3x3s2(x_d2)
+        x_d8 = ops.avgpool3x3s2(x_d4)
+        stem, conv = self.layer1, self.layer1[0]
+        _check_eval(self, stem[1])
+        folded, post = stem._folded()
+        if post is None and conv.in_channels <= 4:
+            y = ops.stem(folded, x, pool=False, out_dtype=dt)
+        else:
+            y = stem(ops.to_nhwc(x, dt))
+        y = self.layer3(self.layer2(y))
+        y = self.layer4(ops.to_nhwc(torch.cat([y, x_d2], dim=1)))
+        block1 = y
+        y = self.layer5_7(y)
+        y = self.layer8(ops.to_nhwc(torch.cat([y, block1, x_d4], dim=1)))
+        block2 = y
+        y = self.layer13_14(self.layer11_12(self.layer9_10(y)))
+        return self.layer15(ops.to_nhwc(torch.cat([y, block2, x_d8], dim=1)))
+
+    def forward(self, x):
+        return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+
+    def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
+                ignore_index: int = 255) -> torch.Tensor:
+        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
+                                   ignore_index=ignore_index)
+
+
+# ------------------------------------------------------------------------------ LEDNet ----
+class SSnbtUnit(nn.Module):
+    """Split-shuffle non-bottleneck unit — reference models/lednet.py:52-88.
+
+    The two halves are channel SLICES of the input (no clone), each branch's last conv writes its
+    half of the output with `+ x` and the activation in its epilogue (no cat, no separate add);
+    the channel shuffle is one permutation kernel."""
+
+    def __init__(self, channels, dilation, act_type):
+        super().__init__()
+        assert channels % 2 == 0, "Input channel should be multiple of 2.\n"
+        sc = channels // 2
+        self.split_channels = sc
+        self.left_branch = nn.Sequential(
+            Conv2d(sc, sc, (3, 1), padding=(1, 0)), Activation(act_type),
+            ConvBNAct(sc, sc, (1, 3), act_type=act_type),
+            Conv2d(sc, sc, (3, 1), padding=(dilation, 0), dilation=dilation), Activation(act_type),
+            ConvBNAct(sc, sc, (1, 3), dilation=dilation, act_type=act_type),
+        )
+        self.right_branch = nn.Sequential(
+            Conv2d(sc, sc, (1, 3), padding=(0, 1)), Activation(act_type),
+            ConvBNAct(sc, sc, (3, 1), act_type=act_type),
+            Conv2d(sc, sc, (1, 3), padding=(0, dilation), dilation=dilation), Activation(act_type),
+            ConvBNAct(sc, sc, (3, 1), dilation=dilation, act_type=act_type),
+        )
+        self.act = Activation(act_type)
+
+    def _branch(self, br, x, coff, out):
+        t = br[0](x, x_coff=coff, act=br[1].activation)
+        t = br[2](t)
+        t = br[3](t, act=br[4].activation)
+        act2 = ops.act_spec(self.act.activation)
+        if act2[3] is not None or act2[4] is not None:
+            raise NotImplementedError("SSnbtUnit: parametrised final activation is not fused")
+        br[5](t, res=x, res_mode=ops.RES_POST, out=out, y_coff=coff, act2=act2[0], r_coff=coff)
+
+    def forward(self, x):
+        x = ops.to_nhwc(x)
+        out = torch.empty_like(x, memory_format=torch.channels_last)
+        self._branch(self.left_branch, x, 0, out)
+        self._branch(self.right_branch, x, self.split_channels, out)
+        return ops.channel_shuffle(out, 2)
+
+
+class AttentionPyramidNetwork(nn.Module):
+    """LEDNet decoder — reference models/lednet.py:91-136.  Convolutions, pooling and resizes are rtseg
+    kernels; the two pyramid additions are conv epilogues; the attention product and the final sum are
+    element-wise torch ops on 1/8-resolution 19-channel maps (0.1 % of the net's bytes)."""
+
+    def __init__(self, in_channels, out_channels, act_type):
+        super().__init__()
+        self.left_conv1_1 = ConvBNAct(in_channels, in_channels, 3, 2, act_type=act_type)
+        self.left_conv1_2 = ConvBNAct(in_channels, out_channels, 3, act_type=act_type)
+        self.left_conv2_1 = ConvBNAct(in_channels, in_channels, 3, 2, act_type=act_type)
+        self.left_conv2_2 = ConvBNAct(in_channels, out_channels, 3, act_type=act_type)
+        self.left_conv3 = nn.Sequential(ConvBNAct(in_channels, in_channels, 3, 2, act_type=act_type),
+                                        ConvBNAct(in_channels, out_channels, 3, act_type=act_type))
+        self.mid_branch = ConvBNAct(in_channels, out_channels, act_type=act_type)
+        self.right_branch = nn.Sequential(nn.AdaptiveAvgPool2d(1), ConvBNAct(in_channels, out_channels, act_type=act_type))
+
+    def forward(self, x):
+        x = ops.to_nhwc(x)
+        size0 = x.shape[2:]
+        l1 = self.left_conv1_1(x)
+        size1 = l1.shape[2:]
+        l2 = self.left_conv2_1(l1)
+        size2 = l2.shape[2:]
+        l3 = ops.upsample_bilinear(self.left_conv3(l2), size2, True)
+        l2 = self.left_conv2_2(l2, res=l3, res_mode=ops.RES_POST)        # x_left2 += x_left3
+        l2 = ops.upsample_bilinear(l2, size1, True)
+        l1 = self.left_conv1_2(l1, res=l2, res_mode=ops.RES_POST)        # x_left += x_left2
+        l1 = ops.upsample_bilinear(l1, size0, True)
+        mid = self.mid_branch(x) * l1
+        right = self.right_branch[1](ops.adaptive_avgpool(x, 1))
+        right = ops.upsample_bilinear(right, size0, True)
+        return ops.to_nhwc(mid + right)
+
+
+class LEDNet(nn.Module):
+    """LEDNet — reference models/lednet.py:16-50 (same attribute names / state-dict keys)."""
+
+    def __init__(self, num_class=1, n_channel=3, act_type="relu"):
+        super().__init__()
+        dils = [1, 2, 5, 9, 2, 5, 9, 17]
+        self.encoder = nn.Sequential(
+            InitialBlock(n_channel, 32, act_type),
+            *[SSnbtUnit(32, 1, act_type=act_type) for _ in range(3)],
+            InitialBlock(32, 64, act_type),
+            *[SSnbtUnit(64, 1, act_type=act_type) for _ in range(2)],
+            InitialBlock(64, 128, act_type),
+            *[SSnbtUnit(128, d, act_type=act_type) for d in dils],
+        )
+        self.apn = AttentionPyramidNetwork(128, num_class, act_type)
+        self.num_class = num_class
+
+    def set_act_dtype(self, dtype: Optional[torch.dtype]):
+        self.encoder[0].act_dtype = dtype
+        return self
+
+    def lowres_logits(self, x):
+        return self.apn(self.encoder(x))
+
+    def forward(self, x):
+        return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+
+    def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
+                ignore_index: int = 255) -> torch.Tensor:
+        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
+                                   ignore_index=ignore_index)
+
+
+MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet}
 
 
 def get_model(config) -> nn.Module:
@@ -293,5 +490,6 @@ def get_model(config) -> nn.Module:
     return MODEL_HUB[name](num_class=config.num_class)
 
 
-__all__ = ["ERFNet", "FastSCNN", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "get_model", "MODEL_HUB"]
+__all__ = ["ERFNet", "FastSCNN", "DABNet", "LEDNet", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "DABModule",
+           "SSnbtUnit", "get_model", "MODEL_HUB"]
 _ = (_bn_tensors, _FoldCache)

@@ -443,3 +443,37 @@ def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] 
 
 def tc_timeout_flag() -> int:
     return int(_lib.load().rtseg_tc_timeout_flag(_stream()))
+
+
+def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: Optional[torch.Tensor] = None,
+                 y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    """F.avg_pool2d(x, 3, 2, 1) (reference models/dabnet.py:32-34) from an NCHW or NHWC tensor into an NHWC slice."""
+    _require_cuda(x, "avgpool3x3s2")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct
+    if x.is_contiguous() and x_coff == 0 and c == x_ct:
+        nchw = 1
+    elif is_nhwc(x):
+        nchw = 0
+    else:
+        x, nchw = x.contiguous(), 1
+        if x_coff or c != x_ct:
+            raise ValueError("channel slices need an NHWC tensor")
+    out_dtype = out_dtype or (out.dtype if out is not None else x.dtype)
+    if out is None:
+        out = empty_nhwc(n, c, (h - 1) // 2 + 1, (w - 1) // 2 + 1, out_dtype, x.device)
+    _lib.check(_lib.load().rtseg_avgpool3x3s2(n, h, w, c, nchw, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                              _dtype_code(out.dtype), out.data_ptr(), out.shape[1], y_coff, _stream()),
+               "rtseg_avgpool3x3s2")
+    return out
+
+
+def channel_shuffle(x: torch.Tensor, groups: int = 2) -> torch.Tensor:
+    """channel_shuffle (reference models/modules.py:18-32) as one NHWC permutation kernel."""
+    _require_cuda(x, "channel_shuffle")
+    x = to_nhwc(x)
+    n, c, h, w = x.shape
+    out = torch.empty_like(x, memory_format=torch.channels_last)
+    _lib.check(_lib.load().rtseg_channel_shuffle(n * h * w, c, groups, _dtype_code(x.dtype), x.data_ptr(), c, 0,
+                                                 out.data_ptr(), c, 0, _stream()), "rtseg_channel_shuffle")
+    return out

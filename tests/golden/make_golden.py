@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 from oracle import ref_import, ref_nets  # noqa: E402
 
-NETS = ["erfnet", "fastscnn"]
+NETS = ["erfnet", "fastscnn", "dabnet", "lednet"]
 H, W = 32, 64  # multiple of 32 so every stage of both nets has a valid size
 
 

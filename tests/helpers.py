@@ -36,3 +36,6 @@ def rel_err(out: torch.Tensor, ref: torch.Tensor) -> float:
 def seeded(shape, seed, scale=1.0):
     g = torch.Generator().manual_seed(seed)
     return torch.randn(shape, generator=g) * scale
+
+# the four networks of SURVEY §8 (a7, a9, a10, a11) that have an rtseg_b200 implementation
+NETS = ["erfnet", "fastscnn", "dabnet", "lednet"]

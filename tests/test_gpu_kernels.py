@@ -12,7 +12,7 @@ import torch
 import torch.nn.functional as F
 
 from oracle import ref_blocks as B
-from oracle import ref_head, ref_ohem
+from oracle import ref_head, ref_nets, ref_ohem
 from tests.helpers import GOLDEN, TOL_BF16, TOL_FP32, rel_err, seeded
 
 pytestmark = pytest.mark.gpu
@@ -466,3 +466,67 @@ def test_c_abi_host_buffer_entry_point():
     ref = ref_head.upsample_argmax(x.permute(0, 3, 1, 2), (128, 256), True)
     assert (labels.long() == ref).float().mean().item() >= 0.999
     assert ctypes.sizeof(ctypes.c_void_p) == 8
+
+
+# --------------------------------------------------- DABNet / LEDNet building blocks ----
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("shape", [(2, 3, 32, 64), (1, 3, 17, 33), (1, 8, 9, 7)])
+def test_avgpool3x3s2_matches_avg_pool2d(shape, dtype):
+    """F.avg_pool2d(x, 3, 2, 1): zero padding counted in the divisor (reference models/dabnet.py:32-34)."""
+    from rtseg_b200 import ops
+    x = seeded(shape, 50)
+    ref = F.avg_pool2d(x, 3, 2, 1)
+    tol = 1e-6 if dtype == torch.float32 else TOL_BF16
+    out = ops.avgpool3x3s2(x.cuda(), out_dtype=dtype)                       # NCHW fp32 image in, NHWC out
+    assert out.dtype == dtype and out.shape == ref.shape and ops.is_nhwc(out)
+    assert rel_err(out, ref) < tol
+    out2 = ops.avgpool3x3s2(ops.to_nhwc(x.to("cuda", dtype)))               # NHWC in, chained like x_d4 / x_d8
+    assert rel_err(out2, ref) < tol
+    # into a channel slice of a wider buffer
+    wide = torch.zeros((shape[0], shape[1] + 5, ref.shape[2], ref.shape[3]), device="cuda", dtype=dtype).contiguous(
+        memory_format=torch.channels_last)
+    ops.avgpool3x3s2(x.cuda(), out=wide, y_coff=4)
+    assert rel_err(wide[:, 4:4 + shape[1]], ref) < tol
+    assert wide[:, :4].abs().sum().item() == 0 and wide[:, 4 + shape[1]:].abs().sum().item() == 0
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("c,groups", [(32, 2), (128, 2), (24, 3), (6, 2)])
+def test_channel_shuffle_is_the_reference_permutation(c, groups, dtype):
+    from rtseg_b200 import ops
+    x = seeded((2, c, 5, 9), 51).to(dtype)
+    ref = ref_nets.channel_shuffle(x.float(), groups)
+    out = ops.channel_shuffle(x.cuda(), groups)
+    assert torch.equal(out.float().cpu(), ref)                              # a permutation: bit-exact
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("channels,dilation", [(64, 2), (128, 16)])
+def test_dab_module(channels, dilation, dtype):
+    from rtseg_b200 import nets
+    m = _randomise(nets.DABModule(channels, dilation, "prelu"), 52)
+    x = seeded((1, channels, 24, 40), 53)
+    with torch.no_grad():
+        ref = ref_nets.dab_module(x, _sd(m), "m.", dilation, "prelu")
+    assert rel_err(_run(m, x, dtype), ref) < _tol(dtype)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("channels,dilation", [(32, 1), (64, 1), (128, 5), (128, 17)])
+def test_ss_nbt_unit(channels, dilation, dtype):
+    from rtseg_b200 import nets
+    m = _randomise(nets.SSnbtUnit(channels, dilation, "relu"), 54)
+    x = seeded((1, channels, 24, 40), 55)
+    with torch.no_grad():
+        ref = ref_nets.ss_nbt_unit(x, _sd(m), "m.", dilation, "relu")
+    assert rel_err(_run(m, x, dtype), ref) < _tol(dtype)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_attention_pyramid_network(dtype):
+    from rtseg_b200 import nets
+    m = _randomise(nets.AttentionPyramidNetwork(128, 19, "relu"), 56)
+    x = seeded((1, 128, 16, 32), 57)
+    with torch.no_grad():
+        ref = ref_nets.attention_pyramid(x, _sd(m), "m.", "relu")
+    assert rel_err(_run(m, x, dtype), ref) < _tol(dtype)

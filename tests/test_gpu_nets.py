@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from oracle import ref_head, ref_nets
-from tests.helpers import ARGMAX_AGREE_FP32, TOL_BF16, TOL_FP32, load_net_outputs, load_specs, rel_err
+from tests.helpers import NETS, ARGMAX_AGREE_FP32, TOL_BF16, TOL_FP32, load_net_outputs, load_specs, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -19,7 +19,7 @@ def _model(name, seed=1, perturb=True):
     return m.eval().cuda(), sd
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 @pytest.mark.parametrize("tag,perturb", [("perturbed", True), ("identity_bn", False)])
 def test_fp32_logits_match_reference_golden_vectors(name, tag, perturb):
     """The reference's own outputs (tests/golden, generated from /root/reference) — fp32 <= 1e-4."""
@@ -44,7 +44,7 @@ def _emulated_bf16(name, sd, x):
         ref_blocks.STORAGE = None
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 def test_fp32_and_bf16_vs_oracle_medium(name):
     """Seeded, BN-perturbed weights (a wrong BN fold cannot hide).
 
@@ -85,7 +85,7 @@ def test_fp32_and_bf16_vs_oracle_medium(name):
         assert (labels.cpu().long() == want).float().mean().item() >= ARGMAX_AGREE_FP32
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 def test_bf16_default_init_within_2e_2(name):
     """The contractual recipe (BASELINE north_star): random-init weights as the reference creates them
     (torch.manual_seed(1), default initialisers), bf16 logits within 2e-2 of fp32."""
@@ -114,7 +114,7 @@ def test_bfloat16_module_conversion_also_works():
     assert y.dtype == torch.bfloat16 and rel_err(y, ref) < 1e-1
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 def test_full_size_1024x2048_fp32(name):
     """BASELINE size: one 1024x2048 image, fp32 path vs the CPU oracle (a few seconds of CPU)."""
     m, sd = _model(name, 4)
@@ -155,7 +155,7 @@ def test_fastscnn_fused_head_with_confmat_full_size():
     assert cm.sum().item() == (target != 255).sum().item()  # every valid pixel counted exactly once
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_inference_engine_host_io(name, use_graph):
     import rtseg_b200

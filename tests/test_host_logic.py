@@ -13,7 +13,7 @@ import torch.nn as nn
 import rtseg_b200
 from oracle import ref_blocks, ref_head, ref_nets
 from rtseg_b200 import _lib, metrics, modules, nets, ops, parallel
-from tests.helpers import load_specs
+from tests.helpers import NETS, load_specs
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -61,7 +61,7 @@ def test_out_hw_and_validation_without_gpu():
     assert b"extent" in lib.rtseg_last_error()
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 def test_state_dict_layout_equals_reference(name):
     spec = load_specs()[name]
     model = nets.MODEL_HUB[name](num_class=19)

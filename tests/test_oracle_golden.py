@@ -7,10 +7,10 @@ import pytest
 import torch
 
 from oracle import ref_head, ref_nets, ref_ohem
-from tests.helpers import GOLDEN, load_net_outputs, load_specs, rel_err
+from tests.helpers import NETS, GOLDEN, load_net_outputs, load_specs, rel_err
 
 
-@pytest.mark.parametrize("name", ["erfnet", "fastscnn"])
+@pytest.mark.parametrize("name", NETS)
 @pytest.mark.parametrize("tag,perturb", [("perturbed", True), ("identity_bn", False)])
 def test_net_restatement_matches_reference_vectors(name, tag, perturb):
     specs, golden = load_specs(), load_net_outputs()
@@ -29,6 +29,8 @@ def test_param_counts_match_readme():
     specs = load_specs()
     assert specs["erfnet"]["n_params"] == 2065458
     assert specs["fastscnn"]["n_params"] == 1023769
+    assert specs["dabnet"]["n_params"] == 750269
+    assert specs["lednet"]["n_params"] == 1461383
 
 
 def test_ohem_restatement_matches_reference_losses():
