@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — images/s at 1024x2048 on N B200s (BASELINE.json metric), one JSON line on rank 0.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn] [--batch B]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet] [--batch B]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
   python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
 
@@ -26,11 +26,14 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 H, W, NUM_CLASS = 1024, 2048, 19
-DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32}
+DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16}
 WORKLOAD_NAME = {
     "erfnet": "ERFNet inference batch {b} at 1024x2048 (BASELINE configs[1])",
     "fastscnn": "Fast-SCNN inference batch {b} at 1024x2048 (BASELINE configs[2])",
+    "dabnet": "DABNet inference batch {b} at 1024x2048 (SURVEY §8 a10)",
+    "lednet": "LEDNet inference batch {b} at 1024x2048 (SURVEY §8 a11)",
 }
+NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet"}
 
 
 def parse_args():
@@ -39,7 +42,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="rtseg", choices=["rtseg", "reference"])
-    ap.add_argument("--workload", default="erfnet", choices=["erfnet", "fastscnn"])
+    ap.add_argument("--workload", default="erfnet", choices=sorted(DEFAULT_BATCH))
     ap.add_argument("--batch", type=int, default=0, help="images per GPU per step (default 16 ERFNet / 32 Fast-SCNN)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -172,6 +175,45 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             total_bytes += sum(by)
             launches += 4
         kernel = "conv_tc_kernel (tcgen05 implicit GEMM, 3x1/1x3 dilated, fused BN/act/residual)"
+    elif workload in ("dabnet", "lednet"):
+        # every fused conv layer is captured with the tensors / keyword arguments the net really passes, timed
+        # alone, and binned by kernel family; the family with the largest share of the time is reported
+        from rtseg_b200.modules import Conv2d, _FusedConvMixin
+        calls, hooks = [], []
+        for m in model.modules():
+            if isinstance(m, (Conv2d, _FusedConvMixin)):
+                hooks.append(m.register_forward_pre_hook(
+                    lambda mod, a, kw: calls.append((mod, a, dict(kw))), with_kwargs=True))
+        x_in = torch.randn((batch, 3, H, W), device=dev)
+        with torch.no_grad():
+            model.lowres_logits(x_in)
+        for hk in hooks:
+            hk.remove()
+        del x_in
+        fam = {}
+        with torch.no_grad():
+            for mod, a, kw in calls:
+                conv = mod if isinstance(mod, Conv2d) else mod[0]
+                x = a[0]
+                if x.dtype != torch.bfloat16:
+                    continue
+                y = mod(*a, **kw)
+                ms = time_call(lambda: mod(*a, **kw))
+                n, _, hh, ww = x.shape
+                by = (n * hh * ww * conv.in_channels + y.shape[0] * y.shape[2] * y.shape[3] * conv.out_channels *
+                      (2 if kw.get("res") is not None else 1)) * 2 + conv.weight.numel() * 2 + 8 * conv.out_channels
+                name = ("dw" if conv.groups > 1 else "tc" if conv.in_channels % 16 == 0 else "dense")
+                f = fam.setdefault(name, [0.0, 0.0, 0])
+                f[0] += ms
+                f[1] += by
+                f[2] += 1
+        top = max(fam, key=lambda k: fam[k][0])
+        total_ms, total_bytes, launches = fam[top]
+        kernel = {"dw": "dw_win_kernel / dw_vec_kernel (NHWC depthwise 3x1 / 1x3 dilated + BN + act + residual)",
+                  "tc": "conv_tc_kernel (tcgen05 implicit GEMM, fused bias/BN/act/residual, channel-slice I/O)",
+                  "dense": "conv_dense_kernel (CUDA-core implicit GEMM for channel counts that are not multiples of 16)"}[top]
+        kernel += "; family shares of conv time: " + ", ".join(
+            f"{k} {100 * v[0] / sum(t[0] for t in fam.values()):.0f}% ({v[2]} launches)" for k, v in sorted(fam.items()))
     else:
         x_in = torch.randn((batch, 3, H, W), device=dev)
         shapes = {}
@@ -230,7 +272,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     batch = args.batch or DEFAULT_BATCH[args.workload]
     workload_name = WORKLOAD_NAME[args.workload].format(b=batch)
-    metric = f"images/sec @1024x2048 ({'ERFNet' if args.workload == 'erfnet' else 'Fast-SCNN'})"
+    metric = f"images/sec @1024x2048 ({NET_LABEL[args.workload]})"
 
     if args.impl == "reference":
         if rank != 0:

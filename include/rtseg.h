@@ -130,10 +130,13 @@ int rtseg_conv_dense(const rtseg_conv_desc *d, const void *x, const float *w, co
  * Same arithmetic as rtseg_conv_dense with bf16 operands and fp32
  * accumulation.  Constraints (else RTSEG_ERR_UNSUPPORTED, see
  * rtseg_conv_tc_supported): groups == 1, dtype bf16, stride 1 or 2 (even H, W),
- * cin % 16 == 0, kh*kw <= 9, channel slices 16-byte aligned, and the weights
- * of one output-channel tile must fit in shared memory.
- *   w  bf16 [kh*kw][cout_pad][cin]  (K-major per tap; cout_pad = cout rounded
- *      up to 16, padding rows zero)                                         */
+ * kh*kw <= 9, channel slices 16-byte aligned (x_ctotal, x_coff multiples of
+ * 8; cin itself is free: DABNet's 35/131/259-channel concatenations,
+ * models/dabnet.py:42-58, run here), and the weights of one output-channel
+ * tile must fit in shared memory.
+ *   w  bf16 [kh*kw][cout_pad][cin_pad]  (K-major per tap; cout_pad / cin_pad
+ *      = cout / cin rounded up to 16, padding zero).  The kernel never reads
+ *      input channels past cin: the TMA unit zero-fills the last K block.   */
 int rtseg_conv_tc_supported(const rtseg_conv_desc *d);
 int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,
                   const float *shift, const float *slope, const void *res, void *y,
@@ -266,10 +269,11 @@ int rtseg_nchw_to_nhwc(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_d
 int rtseg_nhwc_to_nchw(int32_t n, int32_t c, int32_t h, int32_t w, int32_t src_dtype,
                        const void *src, int32_t src_ctotal, int32_t src_coff, int32_t dst_dtype,
                        void *dst, rtseg_stream_t stream);
-/* AdaptiveAvgPool2d(p) of PyramidPoolingModule, models/modules.py:145-149.
- * NHWC in (channel slice allowed), dense NHWC [n][p][p][c] out, same dtype. */
+/* AdaptiveAvgPool2d(p) of PyramidPoolingModule, models/modules.py:145-149, and of LEDNet's attention
+ * pyramid, models/lednet.py:104.  NHWC in (channel slice allowed), dense NHWC [n][p][p][c] out in
+ * y_dtype (an fp32 output lets a caller pool a large map in two exact stages). */
 int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype,
-                           const void *x, int32_t x_ctotal, int32_t x_coff, void *y,
+                           const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
                            rtseg_stream_t stream);
 
 /* F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid, models/dabnet.py:32-34 (padding counted: /9).

@@ -13,7 +13,7 @@ BN_EPS = 1e-5  # nn.BatchNorm2d default, never overridden in the reference
 
 # Optional emulation of reduced-precision STORAGE (not arithmetic): when set to torch.bfloat16 every
 # fused layer's output, and the weights of every tensor-core-eligible dense conv (groups == 1,
-# cin % 16 == 0), are rounded to bf16 exactly where the CUDA path rounds them; all arithmetic stays
+# more than 4 input channels), are rounded to bf16 exactly where the CUDA path rounds them; all arithmetic stays
 # fp32.  Used by the bf16 parity tests to separate "the kernel is wrong" from "bf16 has 8 bits".
 STORAGE = None
 
@@ -25,7 +25,7 @@ def q(t):
 
 def qw(w, groups=1, transposed=False):
     cin = w.shape[0] if transposed else w.shape[1] * groups
-    if STORAGE is None or groups != 1 or cin % 16:
+    if STORAGE is None or groups != 1 or cin <= 4:   # depthwise and image-stem weights stay fp32 in the kernels
         return w
     return w.to(STORAGE).float()
 

@@ -73,7 +73,7 @@ PROTOTYPES = {
     "rtseg_ohem_fwd_static": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_f32, c_vp, c_vp]),
     "rtseg_nchw_to_nhwc": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_nhwc_to_nchw": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
-    "rtseg_adaptive_avgpool": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "rtseg_adaptive_avgpool": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "rtseg_avgpool3x3s2": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_channel_shuffle": (c_i32, [c_i64, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_upsample_argmax_host": (c_i32, [c_i32] * 8 + [c_vp, c_vp, c_vp, c_vp]),

@@ -63,12 +63,20 @@ struct Epilogue {
   // hardtanh; 1 = max(v,0) + slope[c]*min(v,0) covers prelu; 2 = general switch.
   int mode;
   float lo, hi;
+  float lo2, hi2;  // modes 0/1 with a POST residual: clamp(v + res, lo2, hi2) restates act2 in {none, relu, relu6}
 };
 
 static inline int epilogue_mode(int act, int act2, int res_mode, const float *slope, float act_p0, float act_p1,
-                                float &lo, float &hi) {
-  lo = -3.402823466e+38f, hi = 3.402823466e+38f;
-  if (res_mode == RTSEG_RES_POST && act2 != RTSEG_ACT_NONE) return 2;
+                                float &lo, float &hi, float &lo2, float &hi2) {
+  lo = lo2 = -3.402823466e+38f, hi = hi2 = 3.402823466e+38f;
+  if (res_mode == RTSEG_RES_POST) {
+    switch (act2) {
+      case RTSEG_ACT_NONE: break;
+      case RTSEG_ACT_RELU: lo2 = 0.f; break;
+      case RTSEG_ACT_RELU6: lo2 = 0.f, hi2 = 6.f; break;
+      default: return 2;
+    }
+  }
   switch (act) {
     case RTSEG_ACT_NONE: return 0;
     case RTSEG_ACT_RELU: lo = 0.f; return 0;
@@ -90,7 +98,7 @@ static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scal
   e.res_mode = d->res_mode;
   e.p0 = d->act_p0;
   e.p1 = d->act_p1;
-  e.mode = epilogue_mode(d->act, d->act2, d->res_mode, slope, d->act_p0, d->act_p1, e.lo, e.hi);
+  e.mode = epilogue_mode(d->act, d->act2, d->res_mode, slope, d->act_p0, d->act_p1, e.lo, e.hi, e.lo2, e.hi2);
   return e;
 }
 
@@ -146,10 +154,10 @@ __device__ __forceinline__ float epi_elem(float acc, float rv, float sc, float s
   v = fmaf(v, sc, sh);
   if constexpr (MODE == 0) {
     v = fminf(fmaxf(v, e.lo), e.hi);
-    if (e.res_mode == RTSEG_RES_POST) v += rv;
+    if (e.res_mode == RTSEG_RES_POST) v = fminf(fmaxf(v + rv, e.lo2), e.hi2);
   } else if constexpr (MODE == 1) {
     v = fmaf(sl, fminf(v, 0.f), fmaxf(v, 0.f));
-    if (e.res_mode == RTSEG_RES_POST) v += rv;
+    if (e.res_mode == RTSEG_RES_POST) v = fminf(fmaxf(v + rv, e.lo2), e.hi2);
   } else {
     v = act_apply(v, e.act, e.p0, e.p1, sl);
     if (e.res_mode == RTSEG_RES_POST) v = act_apply(v + rv, e.act2, e.p0, e.p1, sl);

@@ -104,6 +104,7 @@ struct TcParams {
   int out_bufs;            // 2 (store of unit u overlaps the epilogue of u+1) or 1 when shared memory is tight
   uint32_t tmem_cols;
   float lo, hi;            // fast epilogue: clamp(v, lo, hi) covers none / relu / relu6 / hardtanh
+  float lo2, hi2;          // ... and clamp(v + res, lo2, hi2) the activation after a POST residual
   TcTap taps[kMaxTcTaps];
 };
 
@@ -566,7 +567,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                   } else {
 #pragma unroll
                     for (int j = 0; j < 4; ++j)
-                      o[j] = fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi) + rv[j];
+                      o[j] = fminf(fmaxf(fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi) + rv[j], p.lo2), p.hi2);
                   }
                 }
                 pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
@@ -798,7 +799,7 @@ static int check_tc_common(const rtseg_conv_desc *d, bool deconv, const char **w
   *why = nullptr;
   if (d->dtype != RTSEG_BF16) *why = "dtype must be bf16";
   else if (d->groups != 1) *why = "groups must be 1";
-  else if (d->cin % 16) *why = "cin must be a multiple of 16";
+  else if (deconv && d->cin % 16) *why = "cin must be a multiple of 16";
   else if (d->x_ctotal % 8 || d->x_coff % 8) *why = "input channel slice must be 16-byte aligned";
   else if (d->res_mode != RTSEG_RES_NONE && (d->r_ctotal % 8 || d->r_coff % 8)) *why = "residual slice must be 16-byte aligned";
   else if (d->kh * d->kw > kMaxTcTaps) *why = "more than 9 taps";
@@ -890,17 +891,8 @@ static void pick_tile(int gw, int &tw, int &th) {
 
 // Epilogue mode: 0 = clamp (none / relu / relu6 / hardtanh), 1 = slope form (prelu with a slope
 // vector), 2 = general.
-static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, float &lo, float &hi) {
-  lo = -FLT_MAX, hi = FLT_MAX;
-  if (d->res_mode == RTSEG_RES_POST && d->act2 != RTSEG_ACT_NONE) return 2;
-  switch (d->act) {
-    case RTSEG_ACT_NONE: return 0;
-    case RTSEG_ACT_RELU: lo = 0.f; return 0;
-    case RTSEG_ACT_RELU6: lo = 0.f, hi = 6.f; return 0;
-    case RTSEG_ACT_HARDTANH: lo = d->act_p0, hi = d->act_p1; return 0;
-    case RTSEG_ACT_PRELU: return slope ? 1 : 2;
-    default: return 2;
-  }
+static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, TcParams &p) {
+  return rtseg::epilogue_mode(d->act, d->act2, d->res_mode, slope, d->act_p0, d->act_p1, p.lo, p.hi, p.lo2, p.hi2);
 }
 
 // Largest sub-tile stack that still leaves every SM at least two unit tiles.
@@ -993,7 +985,8 @@ extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
   const char *why;
   if (check_tc_common(d, false, &why)) return 0;
   TcPlan pl;
-  return plan_tc(d->cin, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, 1, d->res_mode != RTSEG_RES_NONE, pl) ? 1 : 0;
+  return plan_tc((d->cin + 15) / 16 * 16, (d->cout + 15) / 16 * 16, d->kh * d->kw, 1, true, 1,
+                 d->res_mode != RTSEG_RES_NONE, pl) ? 1 : 0;
 }
 
 // Reads and clears the device-side watchdog flag (synchronises the stream). Used by tests.
@@ -1013,6 +1006,12 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(w_bf16) % 16 == 0 &&
                     reinterpret_cast<uintptr_t>(res) % 16 == 0,
                 "tensor pointers must be 16-byte aligned");
+  // K is padded to a multiple of 16 with zero weights; the input tensor map ends at the last REAL channel, so the
+  // TMA unit zero-fills the tail of the last K block (no padded copy of the input, nothing read past the slice).
+  const int cin_real = d->cin;
+  rtseg_conv_desc padded = *d;
+  padded.cin = (d->cin + 15) / 16 * 16;
+  d = &padded;
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const int ntaps = d->kh * d->kw;
   const bool staged = can_stage_output(d, y);
@@ -1034,7 +1033,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   p.ntaps = ntaps;
   p.y_mode = staged ? 2 : 1;
   fill_common(p, d, pl, cout_pad, share);
-  int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  int mode = epilogue_mode(d, slope, p);
   p.a_stages_per_unit = share ? p.nkb : ntaps * p.nkb;
   const bool has_res = d->res_mode != RTSEG_RES_NONE;
   const bool ring_res = has_res && staged && mode <= 1 && pl.bn / pl.ob <= 4;
@@ -1049,7 +1048,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
     tp.widx[0] = (int16_t)t, tp.acc[0] = 0;
   };
   if (d->stride == 1) {
-    if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_ctotal, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
+    if (int rc = encode_nhwc_map(&maps.a[0], x, d->x_coff + cin_real, d->w, d->h, d->n, ct, ct * d->w, ct * d->w * d->h, pl.kb,
                                  p.box_w, p.box_h))
       return rc;
     for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
@@ -1060,7 +1059,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
     for (int ph = 0; ph < 2; ++ph)
       for (int pw = 0; pw < 2; ++pw) {
         const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(x) + ((int64_t)ph * d->w + pw) * ct;
-        if (int rc = encode_nhwc_map(&maps.a[ph * 2 + pw], base, d->x_ctotal, d->w / 2, d->h / 2, d->n, 2 * ct,
+        if (int rc = encode_nhwc_map(&maps.a[ph * 2 + pw], base, d->x_coff + cin_real, d->w / 2, d->h / 2, d->n, 2 * ct,
                                      2 * ct * d->w, ct * d->w * d->h, pl.kb, p.box_w, p.box_h))
           return rc;
       }
@@ -1135,7 +1134,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   for (int a = 0; a < 4; ++a) p.oy0[a] = a >> 1, p.ox0[a] = a & 1;
   p.y_mode = y == nullptr ? 0 : (staged ? 2 : 1);
   fill_common(p, d, pl, cout_pad);
-  const int mode = epilogue_mode(d, slope, p.lo, p.hi);
+  const int mode = epilogue_mode(d, slope, p);
   p.a_stages_per_unit = 4 * p.nkb;
   // four shifted input tiles and the MMAs each one feeds: {ky, kx, accumulator}
   static const int kOps[4][4][3] = {

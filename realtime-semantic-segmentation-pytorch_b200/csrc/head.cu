@@ -334,9 +334,9 @@ static int dispatch_transpose(int n, int rows, int cols, int sdt, const void *sr
 }
 
 // ------------------------------------------------------------- adaptive avg pool ----
-template <typename T>
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int c, int p, const T *__restrict__ x,
-                                                               int x_ct, int x_co, T *__restrict__ y) {
+                                                               int x_ct, int x_co, TO *__restrict__ y) {
   __shared__ float part[8][32];
   const int cell = blockIdx.x, b = blockIdx.y, c0 = blockIdx.z * 32;
   const int pi = cell / p, pj = cell % p;
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += part[k][lane];
-    st_f<T>(y + (((int64_t)b * p + pi) * p + pj) * c + ch, t / (float)cnt);
+    st_f<TO>(y + (((int64_t)b * p + pi) * p + pj) * c + ch, t / (float)cnt);
   }
 }
 
@@ -405,6 +405,29 @@ __global__ void __launch_bounds__(256) channel_shuffle_kernel(int64_t npix, int 
   const int cpg = c / groups;
   const int g = k % groups, i = k / groups;
   y[pix * y_ct + y_co + k] = x[pix * x_ct + x_co + g * cpg + i];
+}
+
+// groups == 2, 16-byte output chunks: chunk k of a pixel interleaves 8 bytes of the first half with 8 bytes of the
+// second half (out[2i] = in[i], out[2i+1] = in[c/2 + i]).  ES = element size in bytes (2 or 4).
+template <int ES>
+__global__ void __launch_bounds__(256) channel_shuffle2_kernel(int64_t npix, int chunks, int half_bytes,
+                                                               const char *__restrict__ x, int64_t x_pitch,
+                                                               char *__restrict__ y, int64_t y_pitch) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= npix * chunks) return;
+  const int k = (int)(tid % chunks);
+  const int64_t pix = tid / chunks;
+  const char *xp = x + pix * x_pitch + k * 8;
+  const uint2 a = __ldg(reinterpret_cast<const uint2 *>(xp));
+  const uint2 b = __ldg(reinterpret_cast<const uint2 *>(xp + half_bytes));
+  uint4 o;
+  if constexpr (ES == 2) {
+    o.x = __byte_perm(a.x, b.x, 0x5410), o.y = __byte_perm(a.x, b.x, 0x7632);
+    o.z = __byte_perm(a.y, b.y, 0x5410), o.w = __byte_perm(a.y, b.y, 0x7632);
+  } else {
+    o = make_uint4(a.x, b.x, a.y, b.y);
+  }
+  *reinterpret_cast<uint4 *>(y + pix * y_pitch + k * 16) = o;
 }
 
 }  // namespace rtseg
@@ -573,18 +596,21 @@ extern "C" int rtseg_nhwc_to_nchw(int32_t n, int32_t c, int32_t h, int32_t w, in
 }
 
 extern "C" int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype,
-                                      const void *x, int32_t x_ct, int32_t x_co, void *y, rtseg_stream_t stream) {
+                                      const void *x, int32_t x_ct, int32_t x_co, int32_t y_dtype, void *y,
+                                      rtseg_stream_t stream) {
   RTSEG_REQUIRE(x && y, "NULL pointer");
   RTSEG_REQUIRE(n > 0 && h > 0 && w > 0 && c > 0 && p > 0 && x_ct >= x_co + c && x_co >= 0, "bad extent");
   RTSEG_REQUIRE(n <= 65535 && cdiv(c, 32) <= 65535, "extent too large");
   dim3 grid((unsigned)(p * p), (unsigned)n, (unsigned)cdiv(c, 32));
   cudaStream_t st = as_stream(stream);
-  if (dtype == RTSEG_BF16)
-    adaptive_avgpool_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(h, w, c, p, (const __nv_bfloat16 *)x, x_ct, x_co, (__nv_bfloat16 *)y);
-  else if (dtype == RTSEG_F32)
-    adaptive_avgpool_kernel<float><<<grid, 256, 0, st>>>(h, w, c, p, (const float *)x, x_ct, x_co, (float *)y);
-  else
-    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+#define RTSEG_AAP(TI_, TO_) \
+  adaptive_avgpool_kernel<TI_, TO_><<<grid, 256, 0, st>>>(h, w, c, p, (const TI_ *)x, x_ct, x_co, (TO_ *)y)
+  if (dtype == RTSEG_BF16 && y_dtype == RTSEG_BF16) RTSEG_AAP(__nv_bfloat16, __nv_bfloat16);
+  else if (dtype == RTSEG_BF16 && y_dtype == RTSEG_F32) RTSEG_AAP(__nv_bfloat16, float);
+  else if (dtype == RTSEG_F32 && y_dtype == RTSEG_F32) RTSEG_AAP(float, float);
+  else if (dtype == RTSEG_F32 && y_dtype == RTSEG_BF16) RTSEG_AAP(float, __nv_bfloat16);
+  else RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+#undef RTSEG_AAP
   RTSEG_LAUNCH_CHECK("adaptive_avgpool_kernel");
   return RTSEG_OK;
 }
@@ -645,8 +671,26 @@ extern "C" int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, in
   RTSEG_REQUIRE(x && y && x != y, "NULL pointer or in-place shuffle");
   RTSEG_REQUIRE(npix > 0 && c > 0 && groups > 0 && c % groups == 0, "channels must be divisible by groups");
   RTSEG_REQUIRE(x_ctotal >= x_coff + c && y_ctotal >= y_coff + c && x_coff >= 0 && y_coff >= 0, "channel slice out of range");
-  const unsigned grid = (unsigned)cdiv(npix * c, 256);
   cudaStream_t st = as_stream(stream);
+  RTSEG_REQUIRE(dtype == RTSEG_BF16 || dtype == RTSEG_F32, "unknown dtype");
+  const int es = dtype == RTSEG_BF16 ? 2 : 4;
+  const int V = 16 / es;
+  if (groups == 2 && c % V == 0 && x_ctotal % V == 0 && x_coff % V == 0 && y_ctotal % V == 0 && y_coff % V == 0 &&
+      (c / 2) % (V / 2) == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0) {
+    const int chunks = c / V;
+    const unsigned g2 = (unsigned)cdiv(npix * chunks, 256);
+    const char *xb = static_cast<const char *>(x) + (size_t)x_coff * es;
+    char *yb = static_cast<char *>(y) + (size_t)y_coff * es;
+    if (es == 2)
+      channel_shuffle2_kernel<2><<<g2, 256, 0, st>>>(npix, chunks, c / 2 * es, xb, (int64_t)x_ctotal * es, yb,
+                                                     (int64_t)y_ctotal * es);
+    else
+      channel_shuffle2_kernel<4><<<g2, 256, 0, st>>>(npix, chunks, c / 2 * es, xb, (int64_t)x_ctotal * es, yb,
+                                                     (int64_t)y_ctotal * es);
+    RTSEG_LAUNCH_CHECK("channel_shuffle2_kernel");
+    return RTSEG_OK;
+  }
+  const unsigned grid = (unsigned)cdiv(npix * c, 256);
   if (dtype == RTSEG_BF16)
     channel_shuffle_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, groups, (const __nv_bfloat16 *)x, x_ctotal, x_coff,
                                                                 (__nv_bfloat16 *)y, y_ctotal, y_coff);

@@ -104,6 +104,13 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
     for (int c = 0; c < CC; ++c)
       if (c < p.cconv)
         out[c] = fminf(fmaxf(fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f), ep.lo), ep.hi);
+  } else if (ep.mode == 1) {  // prelu with a slope vector
+#pragma unroll
+    for (int c = 0; c < CC; ++c)
+      if (c < p.cconv) {
+        const float v = fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f);
+        out[c] = fmaf(__ldg(ep.slope + c), fminf(v, 0.f), fmaxf(v, 0.f));
+      }
   } else {
 #pragma unroll
     for (int c = 0; c < CC; ++c)

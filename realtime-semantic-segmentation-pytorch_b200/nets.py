@@ -43,20 +43,24 @@ class InitialBlock(nn.Module):
         self.conv = ConvBNAct(in_channels, out_channels - in_channels, kernel_size, 2, act_type=act_type, **kwargs)
         self.pool = nn.MaxPool2d(3, 2, 1)
 
-    def forward(self, x):
+    def forward(self, x, out=None, y_coff=0):
+        """`x` may be a wider NHWC buffer whose first in_channels channels are the input; `out` / `y_coff`
+        place the result in a channel slice of a caller-owned buffer (DABNet's concatenations)."""
         conv = self.conv[0]
         cin, cconv = conv.in_channels, conv.out_channels
         _check_eval(self, self.conv[1])
         folded, post = self.conv._folded()
         if post is not None:
             raise NotImplementedError("non-pointwise activation in InitialBlock")
-        if cin <= 4 and cconv <= 32 and conv.kernel_size == (3, 3):
-            return ops.stem(folded, x, pool=True, out_dtype=self.act_dtype or _param_dtype(self.conv))
+        if cin <= 4 and cconv <= 32 and conv.kernel_size == (3, 3) and x.shape[1] == cin:
+            return ops.stem(folded, x, pool=True, out_dtype=self.act_dtype or _param_dtype(self.conv), out=out,
+                            y_coff=y_coff)
         x = ops.to_nhwc(x)
         n, _, h, w = x.shape
-        out = ops.empty_nhwc(n, cconv + cin, (h - 1) // 2 + 1, (w - 1) // 2 + 1, x.dtype, x.device)
-        ops.conv(folded, x, out=out, y_coff=0)
-        ops.maxpool3x3s2(x, out, y_coff=cconv)
+        if out is None:
+            out = ops.empty_nhwc(n, cconv + cin, (h - 1) // 2 + 1, (w - 1) // 2 + 1, x.dtype, x.device)
+        ops.conv(folded, x, out=out, y_coff=y_coff)
+        ops.maxpool3x3s2(x, out, y_coff=y_coff + cconv, c=cin)
         return out
 
 
@@ -297,12 +301,14 @@ class DABModule(nn.Module):
                                           DWConvBNAct(hid, hid, (1, 3), dilation=dilation, act_type=act_type))
         self.last_conv = ConvBNAct(hid, channels, 1, act_type=act_type)
 
-    def forward(self, x):
+    def forward(self, x, x_coff=0, out=None, y_coff=0):
+        """x_coff: the block's input is channels [x_coff, x_coff + C) of `x`; out / y_coff: write the result into
+        a channel slice of a caller-owned buffer."""
         x = ops.to_nhwc(x)
-        t = self.init_conv(x)
+        t = self.init_conv(x, x_coff=x_coff)
         left = self.left_branch[1](self.left_branch[0](t))
         s = self.right_branch[1](self.right_branch[0](t), res=left, res_mode=ops.RES_POST)   # x_left + x_right
-        return self.last_conv(s, res=x, res_mode=ops.RES_POST)                               # x += residual
+        return self.last_conv(s, res=x, res_mode=ops.RES_POST, r_coff=x_coff, out=out, y_coff=y_coff)  # x += residual
 
 
 def _dab_blocks(channels, count, dilation, act_type):
@@ -312,8 +318,10 @@ def _dab_blocks(channels, count, dilation, act_type):
 class DABNet(nn.Module):
     """DABNet — reference models/dabnet.py:16-61 (same layer names / state-dict keys).
 
-    The three concatenations with the average-pooled input pyramid are torch.cat calls (pure data
-    movement); every convolution, pooling and resize is an rtseg kernel."""
+    The three concatenations never run: each stage owns one NHWC buffer (channel pitch rounded up to 8 so that
+    every slice is 16-byte aligned) and the producers — layer3 / layer4 / layer8, the last DABModule of a stage,
+    the average-pool pyramid — write their channel slices of it directly.  The 35-, 131- and 259-channel
+    convolutions that read those buffers run on the tensor cores (K zero-filled by the TMA unit)."""
 
     def __init__(self, num_class=1, n_channel=3, act_type="prelu"):
         super().__init__()
@@ -334,11 +342,30 @@ class DABNet(nn.Module):
         self.act_dtype = dtype
         return self
 
+    @staticmethod
+    def _stage(blocks, buf, x_coff):
+        """Runs a chain of DABModules whose input is buf[:, x_coff : x_coff + C]; the last one writes buf[:, :C]."""
+        y, coff = buf, x_coff
+        for i, m in enumerate(blocks):
+            last = i == len(blocks) - 1
+            y = m(y, x_coff=coff, out=buf if last else None, y_coff=0)
+            coff = 0
+        return buf
+
     def lowres_logits(self, x):
         dt = self.act_dtype or _param_dtype(self.layer1)
-        x_d2 = ops.avgpool3x3s2(x, out_dtype=dt)
-        x_d4 = ops.avgpool3x3s2(x_d2)
-        x_d8 = ops.avgpool3x3s2(x_d4)
+        n, cin, h, w = x.shape
+        half = lambda v: (v - 1) // 2 + 1
+        pitch = lambda c: (c + 7) // 8 * 8
+        h2, w2, h4, w4, h8, w8 = half(h), half(w), half(half(h)), half(half(w)), half(half(half(h))), half(half(half(w)))
+        c1, c2, c3 = self.layer3[0].out_channels, self.layer4.conv[0].out_channels + self.layer4.conv[0].in_channels, \
+            self.layer8[0].out_channels
+        buf1 = ops.empty_nhwc(n, pitch(c1 + cin), h2, w2, dt, x.device)          # [layer3 | x_d2]
+        buf2 = ops.empty_nhwc(n, pitch(2 * c2 + cin), h4, w4, dt, x.device)      # [layer5_7 | layer4 | x_d4]
+        buf3 = ops.empty_nhwc(n, pitch(2 * c3 + cin), h8, w8, dt, x.device)      # [layer13_14 | layer8 | x_d8]
+        ops.avgpool3x3s2(x, out=buf1, y_coff=c1)
+        ops.avgpool3x3s2(buf1, out=buf2, y_coff=2 * c2, x_coff=c1, c=cin)
+        ops.avgpool3x3s2(buf2, out=buf3, y_coff=2 * c3, x_coff=2 * c2, c=cin)
         stem, conv = self.layer1, self.layer1[0]
         _check_eval(self, stem[1])
         folded, post = stem._folded()
@@ -346,14 +373,12 @@ class DABNet(nn.Module):
             y = ops.stem(folded, x, pool=False, out_dtype=dt)
         else:
             y = stem(ops.to_nhwc(x, dt))
-        y = self.layer3(self.layer2(y))
-        y = self.layer4(ops.to_nhwc(torch.cat([y, x_d2], dim=1)))
-        block1 = y
-        y = self.layer5_7(y)
-        y = self.layer8(ops.to_nhwc(torch.cat([y, block1, x_d4], dim=1)))
-        block2 = y
-        y = self.layer13_14(self.layer11_12(self.layer9_10(y)))
-        return self.layer15(ops.to_nhwc(torch.cat([y, block2, x_d8], dim=1)))
+        self.layer3(self.layer2(y), out=buf1, y_coff=0)
+        self.layer4(buf1, out=buf2, y_coff=c2)
+        self._stage(self.layer5_7, buf2, c2)
+        self.layer8(buf2, out=buf3, y_coff=c3)
+        self._stage([*self.layer9_10, *self.layer11_12, *self.layer13_14], buf3, c3)
+        return self.layer15(buf3)
 
     def forward(self, x):
         return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)

@@ -217,10 +217,11 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None) -> T
         else:
             raise NotImplementedError(f"grouped convolution groups={conv.groups} has no kernel (only 1 or cin)")
     w_tc = None
-    if w_kmaj is not None and cin % 16 == 0:
-        cpad = (cout + 15) // 16 * 16
-        w_tc = torch.zeros((kh * kw, cpad, cin), dtype=torch.bfloat16, device=device)
-        w_tc[:, :cout] = w_kmaj.reshape(kh * kw, cout, cin).to(torch.bfloat16)
+    if w_kmaj is not None and (cin % 16 == 0 or (kind == "dense" and cin > 4)):
+        # K (and N) zero-padded to multiples of 16; the conv kernel's input tensor map stops at the last real channel
+        cpad, kpad = (cout + 15) // 16 * 16, (cin + 15) // 16 * 16
+        w_tc = torch.zeros((kh * kw, cpad, kpad), dtype=torch.bfloat16, device=device)
+        w_tc[:, :cout, :cin] = w_kmaj.reshape(kh * kw, cout, cin).to(torch.bfloat16)
     scale, shift = fold_affine(cout, conv.bias, bn)
     slope = None
     if prelu_w is not None:
@@ -431,13 +432,30 @@ def confmat_update(confmat: torch.Tensor, pred: torch.Tensor, target: torch.Tens
     return confmat
 
 
-def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] = None,
+                     out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """nn.AdaptiveAvgPool2d(p) on an NHWC tensor (channel slice allowed).
+
+    Large cells (LEDNet pools a 128x256 map to 1x1) run in two stages with an fp32 intermediate: first to a
+    grid of equal cells that the target cells tile exactly, then to p x p — the mean of equal-sized cell means
+    is the cell mean, and every block of the first stage reads a short run of pixels."""
     _require_cuda(x, "adaptive_avgpool")
     n, x_ct, h, w = x.shape
     c = c if c is not None else x_ct
-    out = empty_nhwc(n, c, p, p, x.dtype, x.device)
-    _lib.check(_lib.load().rtseg_adaptive_avgpool(n, h, w, c, p, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
-                                                  out.data_ptr(), _stream()), "rtseg_adaptive_avgpool")
+    out_dtype = out_dtype or x.dtype
+    lib = _lib.load()
+    if (h // p) * (w // p) >= 4096:
+        for q in (16, 8, 4):
+            if h % (p * q) == 0 and w % (p * q) == 0:
+                mid = empty_nhwc(n, c, p * q, p * q, torch.float32, x.device)
+                _lib.check(lib.rtseg_adaptive_avgpool(n, h, w, c, p * q, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                                      _dtype_code(mid.dtype), mid.data_ptr(), _stream()),
+                           "rtseg_adaptive_avgpool")
+                x, x_ct, x_coff, h, w = mid, c, 0, p * q, p * q
+                break
+    out = empty_nhwc(n, c, p, p, out_dtype, x.device)
+    _lib.check(lib.rtseg_adaptive_avgpool(n, h, w, c, p, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                          _dtype_code(out.dtype), out.data_ptr(), _stream()), "rtseg_adaptive_avgpool")
     return out
 
 

@@ -530,3 +530,34 @@ def test_attention_pyramid_network(dtype):
     with torch.no_grad():
         ref = ref_nets.attention_pyramid(x, _sd(m), "m.", "relu")
     assert rel_err(_run(m, x, dtype), ref) < _tol(dtype)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("p", [1, 2])
+def test_adaptive_avgpool_large_map_two_stage(p, dtype):
+    """LEDNet's APN pools a 1/8-resolution map to 1x1 (reference models/lednet.py:104): two exact stages."""
+    from rtseg_b200 import ops
+    x = seeded((2, 24, 128, 256), 58).to(dtype).float()
+    ref = F.adaptive_avg_pool2d(x, p)
+    out = ops.adaptive_avgpool(ops.to_nhwc(x.to("cuda", dtype)), p)
+    assert out.shape == ref.shape and out.dtype == dtype
+    assert (out.float().cpu() - ref).abs().max().item() < (1e-5 if dtype == torch.float32 else 2e-3)
+
+
+@pytest.mark.parametrize("cin,cout,k,stride", [(35, 29, 3, 2), (131, 128, 3, 2), (259, 19, 1, 1), (40, 24, 3, 1)])
+def test_tensor_core_conv_with_ragged_k(cin, cout, k, stride):
+    """cin not a multiple of 16 (DABNet's concatenations): K is zero-filled by the TMA unit; channels of the
+    buffer beyond cin are poisoned with NaN to prove they are never read."""
+    from rtseg_b200 import modules
+    m = _randomise(modules.ConvBNAct(cin, cout, k, stride, act_type="prelu"), 59)
+    x = seeded((1, cin, 32, 48), 60)
+    with torch.no_grad():
+        ref = B.conv_bn_act(x, _sd(m), "m.", k, stride, 1, "prelu")
+    pitch = (cin + 7) // 8 * 8 + 8
+    buf = torch.full((1, pitch, 32, 48), float("nan"), device="cuda", dtype=torch.bfloat16).contiguous(
+        memory_format=torch.channels_last)
+    buf[:, :cin] = x.cuda().to(torch.bfloat16)
+    with torch.no_grad():
+        out = m.cuda()(buf)
+    assert out.shape == ref.shape and torch.isfinite(out).all()
+    assert rel_err(out, ref) < TOL_BF16

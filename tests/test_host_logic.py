@@ -91,7 +91,10 @@ def test_fold_matches_unfused_arithmetic():
     y = torch.einsum("nchw,co->nohw", x, w) * f.scale.view(1, -1, 1, 1) + f.shift.view(1, -1, 1, 1)
     assert torch.allclose(y, ref, atol=1e-5)
     assert f.slope.shape == (5,) and torch.allclose(f.slope, torch.full((5,), 0.25))
-    assert f.w_tc is None  # cin % 16 != 0
+    # K padded to 16 with zeros (the tensor-core kernel's TMA map stops at the last real channel)
+    assert f.w_tc.shape == (1, 16, 16) and (f.w_tc[:, :, 8:] == 0).all() and (f.w_tc[:, 5:] == 0).all()
+    f3, _ = ops.fold_conv(modules.ConvBNAct(3, 8, 3).eval()[0])
+    assert f3.w_tc is None  # image stems stay on the fp32 stem / CUDA-core kernels
     m2 = modules.ConvBNAct(32, 19, (3, 1), dilation=4).eval()
     f2, _ = ops.fold_conv(m2[0], m2[1], m2[2].activation)
     assert f2.w_tc.shape == (3, 32, 32) and f2.w_tc.dtype == torch.bfloat16
