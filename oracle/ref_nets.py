@@ -150,9 +150,9 @@ def attention_pyramid(x, sd, prefix, act_type="relu"):
     l3 = up(B.conv_bn_act(l3, sd, prefix + "left_conv3.1.", 3, 1, 1, act_type), l2.shape[2:])
     l2 = up(B.conv_bn_act(l2, sd, prefix + "left_conv2_2.", 3, 1, 1, act_type, post_add=l3), l1.shape[2:])
     l1 = up(B.conv_bn_act(l1, sd, prefix + "left_conv1_2.", 3, 1, 1, act_type, post_add=l2), size0)
-    mid = B.q(B.conv_bn_act(x, sd, prefix + "mid_branch.", 3, 1, 1, act_type) * l1)
+    mid = B.conv_bn_act(x, sd, prefix + "mid_branch.", 3, 1, 1, act_type)
     right = B.conv_bn_act(B.q(F.adaptive_avg_pool2d(x, 1)), sd, prefix + "right_branch.1.", 3, 1, 1, act_type)
-    return B.q(mid + up(right, size0))
+    return B.q(mid * l1 + up(right, size0))   # one rounding: the CUDA path evaluates mul + add in a single pass
 
 
 def lednet_lowres_logits(sd, x, act_type="relu"):

@@ -122,6 +122,83 @@ __global__ void __launch_bounds__(256) dw_win_kernel(DwParams p, const T *__rest
   }
 }
 
+// ---- 3x1 / 1x3 with any dilation, stride 1 (DABNet's asymmetric depthwise pairs) -----------------
+// All 3*PX tap loads and the PX residual loads are issued before the first FMA: one DRAM round trip per
+// thread instead of three (the generic kernel below waits once per tap).
+template <typename T, bool VERT, int PX, int MODE>
+__global__ void __launch_bounds__(256) dw_tap3_kernel(DwParams p, const T *__restrict__ x,
+                                                      const float *__restrict__ wgt, Epilogue ep,
+                                                      const T *__restrict__ res, T *__restrict__ y) {
+  constexpr int V = Vec16<T>::N;
+  constexpr int V2 = V / 2;
+  const int cvecs = p.c / V;
+  const int wq_n = (p.wo + PX - 1) / PX;
+  const int64_t total = (int64_t)p.n * p.ho * wq_n * cvecs;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int cv = (int)(tid % cvecs);
+  int64_t r = tid / cvecs;
+  const int wq = (int)(r % wq_n);
+  r /= wq_n;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int c0 = cv * V;
+  const T *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + c0;
+  const int64_t pix0 = ((int64_t)n * p.ho + ho) * p.wo + (int64_t)wq * PX;
+
+  typename Vec16<T>::Raw raw[3][PX], rraw[PX];
+#pragma unroll
+  for (int t = 0; t < 3; ++t) {
+    const int hi = VERT ? ho - p.pad_h + t * p.dil : ho - p.pad_h;
+    const bool row_ok = hi >= 0 && hi < p.h;
+    const T *xr = xn + (int64_t)hi * p.w * p.x_ct;
+#pragma unroll
+    for (int i = 0; i < PX; ++i) {
+      const int wi = wq * PX + i - p.pad_w + (VERT ? 0 : t * p.dil);
+      raw[t][i] = (row_ok && wi >= 0 && wi < p.w) ? Vec16<T>::ldg(xr + (int64_t)wi * p.x_ct) : Vec16<T>::zero();
+    }
+  }
+  const bool has_res = ep.res_mode != RTSEG_RES_NONE;
+#pragma unroll
+  for (int i = 0; i < PX; ++i)
+    rraw[i] = (has_res && wq * PX + i < p.wo) ? Vec16<T>::ldg(res + (pix0 + i) * p.r_ct + p.r_co + c0) : Vec16<T>::zero();
+
+  float2 wv[3][V2];
+#pragma unroll
+  for (int t = 0; t < 3; ++t) {
+    const float *wp = wgt + (int64_t)t * p.cout + c0;
+#pragma unroll
+    for (int v = 0; v < V; v += 4) {
+      const float4 q = __ldg(reinterpret_cast<const float4 *>(wp + v));
+      wv[t][v / 2] = make_float2(q.x, q.y), wv[t][v / 2 + 1] = make_float2(q.z, q.w);
+    }
+  }
+  float sc[V], sh[V], sl[V];
+  load_affine<V>(ep, c0, sc, sh, sl);
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    if (wq * PX + i >= p.wo) break;
+    float2 acc[V2];
+#pragma unroll
+    for (int v = 0; v < V2; ++v) acc[v] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+      float2 xv[V2];
+      Vec16<T>::unpack2(raw[t][i], xv);
+#pragma unroll
+      for (int v = 0; v < V2; ++v) acc[v] = __ffma2_rn(xv[v], wv[t][v], acc[v]);
+    }
+    float rv[V], ov[V];
+    Vec16<T>::unpack(rraw[i], rv);
+#pragma unroll
+    for (int v = 0; v < V2; ++v) {
+      ov[2 * v] = epi_elem<MODE>(acc[v].x, rv[2 * v], sc[2 * v], sh[2 * v], sl[2 * v], ep);
+      ov[2 * v + 1] = epi_elem<MODE>(acc[v].y, rv[2 * v + 1], sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
+    }
+    Vec16<T>::store(y + (pix0 + i) * p.y_ct + p.y_co + c0, ov);
+  }
+}
+
 // ---- any kernel size / dilation / stride, vectorised over channels ------------
 template <typename T, int PX, int MODE>
 __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__restrict__ x,
@@ -279,8 +356,24 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
     }
     if (d->stride == 2) RTSEG_DW_WIN(3, 3, 2, 4);
   }
-  if (d->dil == 1 && d->stride == 1 && d->kh == 1 && d->kw == 3) RTSEG_DW_WIN(1, 3, 1, 8);
+  static const int tap3_knob = getenv("RTSEG_DW_TAP3") ? atoi(getenv("RTSEG_DW_TAP3")) : 1;  // 0 off, 2 = also 1x3 d1
+  if (d->dil == 1 && d->stride == 1 && d->kh == 1 && d->kw == 3 && tap3_knob != 2) RTSEG_DW_WIN(1, 3, 1, 8);
 #undef RTSEG_DW_WIN
+  if (tap3_knob && d->stride == 1 && ((d->kh == 3 && d->kw == 1) || (d->kh == 1 && d->kw == 3))) {
+    constexpr int PX = 4;
+    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX) * cvecs;
+    const unsigned grid = (unsigned)cdiv(total, threads);
+#define RTSEG_DW_TAP3(VERT_)                                                                   \
+  do {                                                                                         \
+    if (ep.mode == 0) dw_tap3_kernel<T, VERT_, PX, 0><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);      \
+    else if (ep.mode == 1) dw_tap3_kernel<T, VERT_, PX, 1><<<grid, threads, 0, st>>>(p, x, w, ep, res, y); \
+    else dw_tap3_kernel<T, VERT_, PX, 2><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);                   \
+  } while (0)
+    if (d->kh == 3) RTSEG_DW_TAP3(true); else RTSEG_DW_TAP3(false);
+#undef RTSEG_DW_TAP3
+    RTSEG_LAUNCH_CHECK("dw_tap3_kernel");
+    return RTSEG_OK;
+  }
   {
     constexpr int PX = 4;
     const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX) * cvecs;

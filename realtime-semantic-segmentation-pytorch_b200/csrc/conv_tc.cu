@@ -726,11 +726,13 @@ struct TcPlan {
 // Narrow layers (small N) stack `ms` 128-pixel sub-tiles per unit so that the fixed per-unit costs
 // (barrier hand-offs, TMA issue, TMEM round trip) are spread over ms times more pixels.
 // share: 0 = one A box per (tap, kb); 1 = vertical halo tile (8x16-pixel sub-tiles side by side);
-// 2 = horizontal halo tile (128-pixel rows, taps are row-shifted descriptors).  halo = (k-1)*dilation.
+// 2 = horizontal halo tile (128-pixel rows, taps are row-shifted descriptors); 3 = two-dimensional halo tile for
+// square k x k kernels (8x16-pixel sub-tiles side by side, every tap a shifted descriptor).  halo = (k-1)*dilation.
 static uint32_t tc_stage_bytes(int share, int halo, int ms, int kb) {
   uint32_t b;
   if (share == 1) b = (uint32_t)(16 + halo) * 8 * ms * kb * 2;
   else if (share == 2) b = (uint32_t)ms * (kTileM + halo) * kb * 2;
+  else if (share == 3) b = (uint32_t)(16 + halo) * (8 * ms + halo) * kb * 2;
   else b = (uint32_t)ms * kTileM * kb * 2;
   return (b + 1023) / 1024 * 1024;
 }
@@ -899,23 +901,25 @@ static int epilogue_mode(const rtseg_conv_desc *d, const float *slope, TcParams 
 static int max_stack(int n, int gh, int gw, int share = 0) {
   int tw, th;
   pick_tile(gw, tw, th);
-  if (share == 1) tw = 8, th = 16;
+  const bool wide = share == 1 || share == 3;  // sub-tiles stacked along w
+  if (wide) tw = 8, th = 16;
   if (share == 2) tw = kTileM, th = 1;
   int ms = 8;
   auto units = [&](int m) {
-    return share == 1 ? (int64_t)n * cdiv(gw, tw * m) * cdiv(gh, th) : (int64_t)n * cdiv(gw, tw) * cdiv(gh, th * m);
+    return wide ? (int64_t)n * cdiv(gw, tw * m) * cdiv(gh, th) : (int64_t)n * cdiv(gw, tw) * cdiv(gh, th * m);
   };
-  while (ms > 1 && ((share == 1 ? tw * ms > gw : th * ms > gh) || units(ms) < 2 * (int64_t)num_sms())) ms >>= 1;
+  while (ms > 1 && ((wide ? tw * ms > gw : th * ms > gh) || units(ms) < 2 * (int64_t)num_sms())) ms >>= 1;
   return ms;
 }
 
 // Which A-sharing mode a forward conv can use (0 = none).  RTSEG_TC_SHARE=0 disables, =1 vertical only.
 static int pick_share(const rtseg_conv_desc *d, int gh, int gw, int kb) {
-  static const int knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 3;
+  static const int knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 7;
   if (d->stride != 1) return 0;
   if ((knob & 1) && d->kw == 1 && d->kh >= 2 && (d->kh - 1) * d->dil < (d->kh - 1) * 16 && d->pad_w == 0 && gw >= 8 &&
       gh >= 16)
     return 1;
+  if ((knob & 4) && d->kh == d->kw && d->kh >= 2 && (d->kh - 1) * d->dil <= 8 && gw >= 8 && gh >= 16) return 3;
   static const int h_any_kb = getenv("RTSEG_TC_HANYKB") ? atoi(getenv("RTSEG_TC_HANYKB")) : 1;
   if ((knob & 2) && d->kh == 1 && d->kw >= 2 && (kb == 64 || h_any_kb) && (d->kw - 1) * d->dil <= 64 && d->pad_h == 0 &&
       gw > 64)
@@ -932,7 +936,7 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
   p.ms = pl.ms;
-  const int halo = share == 1 ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  const int halo = (share == 1 || share == 3) ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
   if (share == 1) {  // vertical taps: 8 wide x 16 tall sub-tiles, stacked along w, one box holds all taps' rows
     p.tw = 8, p.th = 16, p.wstack = 1;
     p.unit_w = 8 * p.ms, p.unit_h = 16;
@@ -941,6 +945,20 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
     p.a_sub16 = (8u * pl.kb * 2) >> 4;
     p.a_sbo16 = ((uint32_t)p.unit_w * pl.kb * 2) >> 4;
     for (int t = 0; t < d->kh; ++t) p.tap_off16[t] = ((uint32_t)(t * d->dil) * p.unit_w * pl.kb * 2) >> 4;
+  } else if (share == 3) {
+    // k x k taps from ONE box per K block: (16 + halo) rows of (8*ms + halo) pixels.  An 8-pixel core-matrix group of
+    // tap (ky, kx) starts (ky*dil) box rows and (kx*dil) pixels into the box, and consecutive groups are one box row
+    // apart (the descriptor's stride-byte-offset).  Neither is a multiple of the swizzle atom: as in the horizontal
+    // mode this relies on the MMA taking the swizzle phase from the shared-memory address itself.
+    p.tw = 8, p.th = 16, p.wstack = 1;
+    p.unit_w = 8 * p.ms, p.unit_h = 16;
+    p.a_share = 1, p.a_dy = -d->pad_h, p.a_dx = -d->pad_w, p.a_boff = 0;
+    p.box_w = p.unit_w + halo, p.box_h = 16 + halo;
+    p.a_sub16 = (8u * pl.kb * 2) >> 4;
+    p.a_sbo16 = ((uint32_t)p.box_w * pl.kb * 2) >> 4;
+    for (int ky = 0, t = 0; ky < d->kh; ++ky)
+      for (int kx = 0; kx < d->kw; ++kx, ++t)
+        p.tap_off16[t] = ((uint32_t)(ky * d->dil * p.box_w + kx * d->dil) * pl.kb * 2) >> 4;
   } else if (share == 2) {  // horizontal taps: 128-pixel rows (+halo), stacked along h, taps = row-shifted descriptors
     p.tw = kTileM, p.th = 1, p.wstack = 0;
     p.unit_w = kTileM, p.unit_h = p.ms;
@@ -1020,7 +1038,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
   int share = pick_share(d, p.gh, p.gw, pick_kb(d->cin));
-  const int halo = share == 1 ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  const int halo = (share == 1 || share == 3) ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
   if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw, share), d->res_mode != RTSEG_RES_NONE, pl,
                share, halo)) {
     share = 0;

@@ -148,9 +148,11 @@ struct PoolParams {
   int x_ct, x_co, y_ct, y_co;
 };
 
-template <typename T, int V>
+// RAGGED: 16-byte loads from an aligned input slice, element-wise stores (output slice not 16-byte aligned or a
+// channel count that is not a multiple of V: DABNet's 35-channel pool written behind 29 conv channels).
+template <typename T, int V, bool RAGGED = false>
 __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T *__restrict__ x, T *__restrict__ y) {
-  const int cv_n = p.c / V;
+  const int cv_n = RAGGED ? (p.c + V - 1) / V : p.c / V;
   const int64_t total = (int64_t)p.n * p.ho * p.wo * cv_n;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= total) return;
@@ -198,6 +200,10 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T
   T *yp = y + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.y_ct + p.y_co + c0;
   if constexpr (V == 1) {
     st_f<T>(yp, m[0]);
+  } else if constexpr (RAGGED) {
+#pragma unroll
+    for (int e = 0; e < V; ++e)
+      if (c0 + e < p.c) st_f<T>(yp + e, m[e]);
   } else {
     Vec16<T>::store(yp, m);
   }
@@ -274,8 +280,20 @@ extern "C" int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void 
   const int V = d->dtype == RTSEG_BF16 ? 8 : 4;
   const bool vec = p.c % V == 0 && p.x_ct % V == 0 && p.x_co % V == 0 && p.y_ct % V == 0 && p.y_co % V == 0 &&
                    reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
-  const int64_t total = (int64_t)p.n * p.ho * p.wo * (vec ? p.c / V : p.c);
+  const bool ragged = !vec && p.x_ct % V == 0 && p.x_co % V == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 &&
+                      p.x_ct >= p.x_co + (p.c + V - 1) / V * V;
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * (vec ? p.c / V : ragged ? (p.c + V - 1) / V : p.c);
   const unsigned grid = (unsigned)cdiv(total, 256);
+  if (ragged) {
+    if (d->dtype == RTSEG_BF16)
+      maxpool3x3s2_kernel<__nv_bfloat16, 8, true><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y);
+    else if (d->dtype == RTSEG_F32)
+      maxpool3x3s2_kernel<float, 4, true><<<grid, 256, 0, st>>>(p, (const float *)x, (float *)y);
+    else
+      RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+    RTSEG_LAUNCH_CHECK("maxpool3x3s2_kernel");
+    return RTSEG_OK;
+  }
   if (d->dtype == RTSEG_BF16) {
     if (vec)
       maxpool3x3s2_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y);

@@ -32,6 +32,16 @@ def _param_dtype(m: nn.Module) -> torch.dtype:
     return next(m.parameters()).dtype
 
 
+def _pitch8(c: int) -> int:
+    """Channel pitch that keeps every pixel of an NHWC bf16/fp32 buffer 16-byte aligned (TMA stores, vector I/O)."""
+    return (c + 7) // 8 * 8
+
+
+def _first_channels(t: torch.Tensor, c: int) -> torch.Tensor:
+    """Channels [0, c) of a pitch-padded NHWC buffer as a dense NHWC tensor."""
+    return t if t.shape[1] == c else t[:, :c].contiguous(memory_format=torch.channels_last)
+
+
 class InitialBlock(nn.Module):
     """cat([ConvBNAct(in, out-in, 3, stride 2)(x), MaxPool2d(3,2,1)(x)]) — reference models/enet.py:38-48."""
 
@@ -352,11 +362,11 @@ class DABNet(nn.Module):
             coff = 0
         return buf
 
-    def lowres_logits(self, x):
+    def _lowres_padded(self, x):
         dt = self.act_dtype or _param_dtype(self.layer1)
         n, cin, h, w = x.shape
         half = lambda v: (v - 1) // 2 + 1
-        pitch = lambda c: (c + 7) // 8 * 8
+        pitch = _pitch8
         h2, w2, h4, w4, h8, w8 = half(h), half(w), half(half(h)), half(half(w)), half(half(half(h))), half(half(half(w)))
         c1, c2, c3 = self.layer3[0].out_channels, self.layer4.conv[0].out_channels + self.layer4.conv[0].in_channels, \
             self.layer8[0].out_channels
@@ -378,15 +388,19 @@ class DABNet(nn.Module):
         self._stage(self.layer5_7, buf2, c2)
         self.layer8(buf2, out=buf3, y_coff=c3)
         self._stage([*self.layer9_10, *self.layer11_12, *self.layer13_14], buf3, c3)
-        return self.layer15(buf3)
+        logits = ops.empty_nhwc(n, _pitch8(self.num_class), h8, w8, dt, x.device)   # pitch 24 for 19 classes
+        return self.layer15(buf3, out=logits)
+
+    def lowres_logits(self, x):
+        return _first_channels(self._lowres_padded(x), self.num_class)
 
     def forward(self, x):
-        return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+        return ops.upsample_bilinear(self._lowres_padded(x), x.shape[2:], True, c=self.num_class)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
-        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
-                                   ignore_index=ignore_index)
+        return ops.upsample_argmax(self._lowres_padded(x), x.shape[2:], True, target=target, confmat=confmat,
+                                   ignore_index=ignore_index, num_classes=self.num_class)
 
 
 # ------------------------------------------------------------------------------ LEDNet ----
@@ -449,22 +463,27 @@ class AttentionPyramidNetwork(nn.Module):
         self.mid_branch = ConvBNAct(in_channels, out_channels, act_type=act_type)
         self.right_branch = nn.Sequential(nn.AdaptiveAvgPool2d(1), ConvBNAct(in_channels, out_channels, act_type=act_type))
 
-    def forward(self, x):
+    def forward(self, x, padded=False):
+        """padded=True returns the [n, pitch8(out_channels), h, w] buffer the kernels write (channels beyond
+        out_channels are undefined); the default returns the dense tensor the reference returns."""
         x = ops.to_nhwc(x)
+        n, cout = x.shape[0], self.mid_branch[0].out_channels
+        # every out_channels-wide map lives in a pitch-8 buffer: TMA stores / ring residuals need 16-byte pixels
+        buf = lambda size: ops.empty_nhwc(n, _pitch8(cout), int(size[0]), int(size[1]), x.dtype, x.device)
+        up = lambda t, size: ops.upsample_bilinear(t, size, True, out=buf(size), c=cout)
         size0 = x.shape[2:]
         l1 = self.left_conv1_1(x)
         size1 = l1.shape[2:]
         l2 = self.left_conv2_1(l1)
         size2 = l2.shape[2:]
-        l3 = ops.upsample_bilinear(self.left_conv3(l2), size2, True)
-        l2 = self.left_conv2_2(l2, res=l3, res_mode=ops.RES_POST)        # x_left2 += x_left3
-        l2 = ops.upsample_bilinear(l2, size1, True)
-        l1 = self.left_conv1_2(l1, res=l2, res_mode=ops.RES_POST)        # x_left += x_left2
-        l1 = ops.upsample_bilinear(l1, size0, True)
-        mid = self.mid_branch(x) * l1
-        right = self.right_branch[1](ops.adaptive_avgpool(x, 1))
-        right = ops.upsample_bilinear(right, size0, True)
-        return ops.to_nhwc(mid + right)
+        l3 = self.left_conv3[0](l2)
+        l3 = up(self.left_conv3[1](l3, out=buf(l3.shape[2:])), size2)
+        l2 = up(self.left_conv2_2(l2, res=l3, res_mode=ops.RES_POST, out=buf(size2)), size1)    # x_left2 += x_left3
+        l1 = up(self.left_conv1_2(l1, res=l2, res_mode=ops.RES_POST, out=buf(size1)), size0)    # x_left += x_left2
+        mid = self.mid_branch(x, out=buf(size0))
+        right = self.right_branch[1](ops.adaptive_avgpool(x, 1), out=buf((1, 1)))
+        out = torch.addcmul(up(right, size0), mid, l1)                                           # mid * left + right
+        return out if padded else _first_channels(out, cout)
 
 
 class LEDNet(nn.Module):
@@ -488,16 +507,19 @@ class LEDNet(nn.Module):
         self.encoder[0].act_dtype = dtype
         return self
 
+    def _lowres_padded(self, x):
+        return self.apn(self.encoder(x), padded=True)
+
     def lowres_logits(self, x):
-        return self.apn(self.encoder(x))
+        return _first_channels(self._lowres_padded(x), self.num_class)
 
     def forward(self, x):
-        return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+        return ops.upsample_bilinear(self._lowres_padded(x), x.shape[2:], True, c=self.num_class)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
-        return ops.upsample_argmax(self.lowres_logits(x), x.shape[2:], True, target=target, confmat=confmat,
-                                   ignore_index=ignore_index)
+        return ops.upsample_argmax(self._lowres_padded(x), x.shape[2:], True, target=target, confmat=confmat,
+                                   ignore_index=ignore_index, num_classes=self.num_class)
 
 
 MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet}
