@@ -24,7 +24,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .modules import (Activation, Conv2d, ConvBNAct, DeConvBNAct, DSConvBNAct, DWConvBNAct, PWConvBNAct,
+from .modules import (_FoldCache, Activation, Conv2d, ConvBNAct, DeConvBNAct, DSConvBNAct, DWConvBNAct, PWConvBNAct,
                       PyramidPoolingModule, _bn_tensors, _check_eval, _FoldCache, conv1x1)
 
 
@@ -362,6 +362,39 @@ class DABNet(nn.Module):
             coff = 0
         return buf
 
+    def _layer8(self, buf2, buf3, c3, cin_img):
+        """layer8 = ConvBNAct(2*64 + 3 -> 128, 3, stride 2).  On the bf16 path K is split across two launches: the
+        n_channel-wide tail (x_d4) runs first as a bare 3x3 stride-2 convolution whose sums enter the 128-channel
+        main convolution as a PRE residual (acc + res -> BN -> act).  The main launch then has K = 128 = 2 x 64:
+        full 128-byte TMA rows and 18 pipeline stages per tile instead of 81 32-byte-row stages for K = 131."""
+        conv, bn, act = self.layer8._parts()
+        cmain = conv.in_channels - cin_img
+        if buf2.dtype != torch.bfloat16 or cmain % 64 or not ops.USE_TENSOR_CORES:
+            return self.layer8(buf2, out=buf3, y_coff=c3)
+        _check_eval(self, bn)
+        tensors = [conv.weight, conv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var, getattr(act, "weight", None)]
+        cache = self.__dict__.setdefault("_rtseg_cache8", _FoldCache())
+
+        def build():
+            main, post = ops.fold_conv(conv, bn, act, in_slice=(0, cmain))
+            side, _ = ops.fold_conv(conv, None, None, in_slice=(cmain, conv.in_channels), tc_small_cin=True)
+            side.shift = None  # the bias (if any) is applied once, by the main launch
+            return main, side, post
+        main, side, post = cache.get(tensors, build)
+        if post is not None:
+            return self.layer8(buf2, out=buf3, y_coff=c3)
+        tail = ops.conv(side, buf2, x_coff=cmain)
+        return ops.conv(main, buf2, res=tail, res_mode=ops.RES_PRE, out=buf3, y_coff=c3)
+
+    def __deepcopy__(self, memo):  # keep the fold cache out of EMA copies (utils/model_ema.py:20)
+        import copy
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            if k != "_rtseg_cache8":
+                new.__dict__[k] = copy.deepcopy(v, memo)
+        return new
+
     def _lowres_padded(self, x):
         dt = self.act_dtype or _param_dtype(self.layer1)
         n, cin, h, w = x.shape
@@ -386,7 +419,7 @@ class DABNet(nn.Module):
         self.layer3(self.layer2(y), out=buf1, y_coff=0)
         self.layer4(buf1, out=buf2, y_coff=c2)
         self._stage(self.layer5_7, buf2, c2)
-        self.layer8(buf2, out=buf3, y_coff=c3)
+        self._layer8(buf2, buf3, c3, cin)
         self._stage([*self.layer9_10, *self.layer11_12, *self.layer13_14], buf3, c3)
         logits = ops.empty_nhwc(n, _pitch8(self.num_class), h8, w8, dt, x.device)   # pitch 24 for 19 classes
         return self.layer15(buf3, out=logits)

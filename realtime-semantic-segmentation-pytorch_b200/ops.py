@@ -179,8 +179,13 @@ def _f32(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
     return None if t is None else t.to(device=device, dtype=torch.float32).contiguous()
 
 
-def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None) -> Tuple[Folded, Optional[torch.nn.Module]]:
-    """Pack nn.Conv2d / nn.ConvTranspose2d (+BN, +activation) for the kernels."""
+def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
+              in_slice: Optional[Tuple[int, int]] = None, tc_small_cin: bool = False
+              ) -> Tuple[Folded, Optional[torch.nn.Module]]:
+    """Pack nn.Conv2d / nn.ConvTranspose2d (+BN, +activation) for the kernels.
+
+    in_slice=(lo, hi) folds only input channels [lo, hi) of a dense conv (a caller that splits K across two
+    launches); tc_small_cin also builds tensor-core weights when that leaves <= 4 input channels."""
     nn = torch.nn
     device = device or conv.weight.device
     code, p0, p1, prelu_w, post = act_spec(act_module)
@@ -206,6 +211,11 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None) -> T
         w_kmaj = w.permute(2, 3, 1, 0)                        # [kh][kw][cout][cin]
     else:
         cin, cout = conv.in_channels, conv.out_channels
+        if in_slice is not None:
+            if conv.groups != 1:
+                raise NotImplementedError("in_slice is for dense convolutions")
+            w = w[:, in_slice[0]:in_slice[1]]
+            cin = w.shape[1]
         if conv.groups == 1:
             kind = "dense"
             w_f32 = w.permute(2, 3, 1, 0).contiguous()       # [kh][kw][cin][cout]
@@ -217,7 +227,7 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None) -> T
         else:
             raise NotImplementedError(f"grouped convolution groups={conv.groups} has no kernel (only 1 or cin)")
     w_tc = None
-    if w_kmaj is not None and (cin % 16 == 0 or (kind == "dense" and cin > 4)):
+    if w_kmaj is not None and (cin % 16 == 0 or (kind == "dense" and (cin > 4 or tc_small_cin))):
         # K (and N) zero-padded to multiples of 16; the conv kernel's input tensor map stops at the last real channel
         cpad, kpad = (cout + 15) // 16 * 16, (cin + 15) // 16 * 16
         w_tc = torch.zeros((kh * kw, cpad, kpad), dtype=torch.bfloat16, device=device)
