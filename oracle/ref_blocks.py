@@ -12,8 +12,8 @@ import torch.nn.functional as F
 BN_EPS = 1e-5  # nn.BatchNorm2d default, never overridden in the reference
 
 # Optional emulation of reduced-precision STORAGE (not arithmetic): when set to torch.bfloat16 every
-# fused layer's output, and the weights of every tensor-core-eligible dense conv (groups == 1,
-# more than 4 input channels), are rounded to bf16 exactly where the CUDA path rounds them; all arithmetic stays
+# fused layer's output, the weights of every dense conv (groups == 1: all of them run on the tensor
+# cores) and the image as the stem reads it are rounded to bf16 exactly where the CUDA path rounds them; all arithmetic stays
 # fp32.  Used by the bf16 parity tests to separate "the kernel is wrong" from "bf16 has 8 bits".
 STORAGE = None
 
@@ -25,7 +25,7 @@ def q(t):
 
 def qw(w, groups=1, transposed=False):
     cin = w.shape[0] if transposed else w.shape[1] * groups
-    if STORAGE is None or groups != 1 or cin <= 4:   # depthwise and image-stem weights stay fp32 in the kernels
+    if STORAGE is None or groups != 1:   # depthwise weights stay fp32 in the kernels
         return w
     return w.to(STORAGE).float()
 
@@ -83,6 +83,8 @@ def conv_bn_act(x, sd, prefix, kernel_size=3, stride=1, dilation=1, act_type="re
 
     `post_add` / `post_act` restate a caller's `y += t; y = act(y)` that follows the block (DABModule,
     SSnbtUnit, AttentionPyramidNetwork) so that storage emulation rounds once, where the fused kernel does."""
+    if groups == 1 and x.shape[1] <= 4:
+        x = q(x)   # the tensor-core stem converts the fp32 image to bf16 while it builds its im2col rows
     y = F.conv2d(x, qw(sd[prefix + "0.weight"], groups), sd.get(prefix + "0.bias"), stride, _pad(kernel_size, dilation),
                  dilation, groups)
     y = batch_norm(y, sd, prefix + "1.")
@@ -120,7 +122,7 @@ def deconv_bn_act(x, sd, prefix, scale_factor=2, act_type="relu", **kw):
 def initial_block(x, sd, prefix, act_type="relu"):
     """InitialBlock (reference models/enet.py:38-48): cat[conv3x3 s2 branch, maxpool(3,2,1) of the input]."""
     a = conv_bn_act(x, sd, prefix + "conv.", 3, 2, 1, act_type)
-    b = F.max_pool2d(x, 3, 2, 1)
+    b = q(F.max_pool2d(x, 3, 2, 1))
     return torch.cat([a, b], dim=1)
 
 

@@ -104,6 +104,14 @@ static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scal
 
 int validate_conv_desc(const rtseg_conv_desc *d, const void *res);
 
+// Geometry of the stride-2 3x3 image stem (stem.cu, stem_tc.cu).
+struct StemParams {
+  int n, h, w, cin, cconv, ho, wo;
+  int64_t sn, sc, sh, sw;  // input strides in elements
+  int y_ct, y_co;
+  int pool;
+};
+
 // ---- device side ---------------------------------------------------------------
 #ifdef __CUDACC__
 

@@ -42,7 +42,8 @@
 
 namespace rtseg {
 
-int dw_tma_timeout_flag();  // dw_tma.cu
+int dw_tma_timeout_flag();   // dw_tma.cu
+int stem_tc_timeout_flag();  // stem_tc.cu
 
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = 32 * kEpiWarps;
@@ -1010,8 +1011,8 @@ extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
 // Reads and clears the device-side watchdog flag (synchronises the stream). Used by tests.
 extern "C" int rtseg_tc_timeout_flag(rtseg_stream_t stream) {
   if (cudaStreamSynchronize(as_stream(stream)) != cudaSuccess) return -1;
-  const int a = read_clear_timeout_flag(), b = dw_tma_timeout_flag();
-  return (a < 0 || b < 0) ? -1 : (a | b);
+  const int a = read_clear_timeout_flag(), b = dw_tma_timeout_flag(), c = stem_tc_timeout_flag();
+  return (a < 0 || b < 0 || c < 0) ? -1 : (a | b | c);
 }
 
 extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,

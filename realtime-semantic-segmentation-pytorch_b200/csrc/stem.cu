@@ -18,12 +18,10 @@
 
 namespace rtseg {
 
-struct StemParams {
-  int n, h, w, cin, cconv, ho, wo;
-  int64_t sn, sc, sh, sw;  // input strides in elements
-  int y_ct, y_co;
-  int pool;
-};
+// (StemParams lives in common.cuh: stem_tc.cu shares it)
+// Tensor-core variant (stem_tc.cu): returns RTSEG_OK when it launched, 1 when the shape is not its business.
+int stem_tc_try(const StemParams &p, int x_dtype, const void *x, const float *w, const Epilogue &ep, void *y,
+                cudaStream_t st);
 
 template <typename TI, typename TO, int CIN, int CC>
 __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__restrict__ x,
@@ -259,6 +257,10 @@ extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x
   }
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   cudaStream_t st = as_stream(stream);
+  if (d->dtype == RTSEG_BF16) {  // bf16 activations: im2col + tcgen05 (bf16 operands, fp32 accumulation)
+    const int rc = stem_tc_try(p, x_dtype, x, w, ep, y, st);
+    if (rc <= 0) return rc;
+  }
   if (x_dtype == RTSEG_F32 && d->dtype == RTSEG_F32) return launch_stem<float, float>(p, x, w, ep, y, st);
   if (x_dtype == RTSEG_F32 && d->dtype == RTSEG_BF16) return launch_stem<float, __nv_bfloat16>(p, x, w, ep, y, st);
   if (x_dtype == RTSEG_BF16 && d->dtype == RTSEG_BF16)
