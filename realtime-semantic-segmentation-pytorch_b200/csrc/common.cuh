@@ -115,22 +115,34 @@ struct StemParams {
 // ---- device side ---------------------------------------------------------------
 #ifdef __CUDACC__
 
+// NaN-propagating max / min: torch's relu / relu6 / hardtanh / max_pool2d hand a NaN through, fmaxf / fminf drop it.
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+  float d;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+  return d;
+}
+__device__ __forceinline__ float fmin_nan(float a, float b) {
+  float d;
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+  return d;
+}
+
 __device__ __forceinline__ float act_apply(float v, int act, float p0, float p1, float slope) {
   switch (act) {
     case RTSEG_ACT_NONE: return v;
-    case RTSEG_ACT_RELU: return fmaxf(v, 0.f);
-    case RTSEG_ACT_RELU6: return fminf(fmaxf(v, 0.f), 6.f);
+    case RTSEG_ACT_RELU: return fmax_nan(v, 0.f);
+    case RTSEG_ACT_RELU6: return fmin_nan(fmax_nan(v, 0.f), 6.f);
     case RTSEG_ACT_LEAKYRELU: return v > 0.f ? v : v * p0;
     case RTSEG_ACT_PRELU: return v > 0.f ? v : v * slope;
     case RTSEG_ACT_ELU: return v > 0.f ? v : p0 * expm1f(v);
-    case RTSEG_ACT_CELU: return fmaxf(v, 0.f) + fminf(0.f, p0 * expm1f(v / p0));
+    case RTSEG_ACT_CELU: return fmax_nan(v, 0.f) + fmin_nan(0.f, p0 * expm1f(v / p0));
     case RTSEG_ACT_SELU: {
       const float alpha = 1.6732632423543772848170429916717f;
       const float lam = 1.0507009873554804934193349852946f;
       return lam * (v > 0.f ? v : alpha * expm1f(v));
     }
-    case RTSEG_ACT_HARDSWISH: return v * fminf(fmaxf(v + 3.f, 0.f), 6.f) * (1.f / 6.f);
-    case RTSEG_ACT_HARDTANH: return fminf(fmaxf(v, p0), p1);
+    case RTSEG_ACT_HARDSWISH: return v * fmin_nan(fmax_nan(v + 3.f, 0.f), 6.f) * (1.f / 6.f);
+    case RTSEG_ACT_HARDTANH: return fmin_nan(fmax_nan(v, p0), p1);
     case RTSEG_ACT_GELU: return 0.5f * v * (1.f + erff(v * 0.70710678118654752440f));
     case RTSEG_ACT_SILU: return v / (1.f + expf(-v));
     case RTSEG_ACT_SIGMOID: return 1.f / (1.f + expf(-v));
@@ -161,11 +173,11 @@ __device__ __forceinline__ float epi_elem(float acc, float rv, float sc, float s
   float v = e.res_mode == RTSEG_RES_PRE ? acc + rv : acc;
   v = fmaf(v, sc, sh);
   if constexpr (MODE == 0) {
-    v = fminf(fmaxf(v, e.lo), e.hi);
-    if (e.res_mode == RTSEG_RES_POST) v = fminf(fmaxf(v + rv, e.lo2), e.hi2);
+    v = fmin_nan(fmax_nan(v, e.lo), e.hi);
+    if (e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
   } else if constexpr (MODE == 1) {
-    v = fmaf(sl, fminf(v, 0.f), fmaxf(v, 0.f));
-    if (e.res_mode == RTSEG_RES_POST) v = fminf(fmaxf(v + rv, e.lo2), e.hi2);
+    v = fmaf(sl, fmin_nan(v, 0.f), fmax_nan(v, 0.f));
+    if (e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
   } else {
     v = act_apply(v, e.act, e.p0, e.p1, sl);
     if (e.res_mode == RTSEG_RES_POST) v = act_apply(v + rv, e.act2, e.p0, e.p1, sl);

@@ -34,6 +34,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <type_traits>
 #include <cstdlib>
 #include <mutex>
 
@@ -145,8 +146,15 @@ struct TcMaps {
 // MODE 0: clamp (none / relu / relu6 / hardtanh).  MODE 1: max(v,0) + slope*min(v,0) (prelu).
 template <int MODE>
 __device__ __forceinline__ float fast_act(float v, float slope, float lo, float hi) {
-  if constexpr (MODE == 1) return fmaf(slope, fminf(v, 0.f), fmaxf(v, 0.f));
-  return fminf(fmaxf(v, lo), hi);
+  if constexpr (MODE == 1) return fmaf(slope, fmin_nan(v, 0.f), fmax_nan(v, 0.f));
+  return fmin_nan(fmax_nan(v, lo), hi);
+}
+
+// The bf16 rounding the labels head compares in (value in the upper 16 bits).
+__device__ __forceinline__ uint32_t bf16_hi_bits(float t) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(t), "f"(0.f));  // {hi = bf16(t), lo = bf16(0) = 0}
+  return d;
 }
 
 __device__ __noinline__ float act_generic(float v, int act, float p0, float p1, float slope) {
@@ -292,25 +300,30 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
             if (elect_one()) {
+            uint32_t st = started;  // bit a: accumulator a already holds a partial sum (this lane's running copy)
             for (int t = 0; t < p.ntaps; ++t) {
               const TcTap &tap = p.taps[t];
-              const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[0] * p.nkb + kb) * blk16);
-              const uint32_t fresh = (started & 1u) | (t > 0 ? 1u : 0u);
-              for (int sub = 0; sub < p.ms; ++sub) {
-                const uint32_t off16 = stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16;
-                uint64_t a_d = a_desc0 + (uint64_t)off16;
-                // rows not aligned to the 8-row swizzle atom: tell the MMA the phase of the first row
-                if (p.a_boff) a_d |= (uint64_t)((((s_a >> 4) + off16) >> 3) & 7u) << 49;
-                const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc) * (uint32_t)p.bn;
-                umma_bf16(d_col, a_d, b_d, idesc, fresh);
+              for (int o = 0; o < tap.nops; ++o) {  // a transposed conv feeds up to four accumulators from one tap
+                const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
+                const uint32_t a_acc = (uint32_t)tap.acc[o];
+                const uint32_t fresh = (st >> a_acc) & 1u;
+                st |= 1u << a_acc;
+                for (int sub = 0; sub < p.ms; ++sub) {
+                  const uint32_t off16 = stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16;
+                  uint64_t a_d = a_desc0 + (uint64_t)off16;
+                  // rows not aligned to the 8-row swizzle atom: tell the MMA the phase of the first row
+                  if (p.a_boff) a_d |= (uint64_t)((((s_a >> 4) + off16) >> 3) & 7u) << 49;
+                  const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
+                  umma_bf16(d_col, a_d, b_d, idesc, fresh);
 #pragma unroll
-                for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                  for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                }
               }
             }
             umma_commit(empty_bar + 8 * stage);
             }
             __syncwarp();
-            started |= 1u;
+            started = 0xfu;  // every accumulator of the unit has received this K block's contribution
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         } else
@@ -411,87 +424,62 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // ---- labels-only transposed conv (the segmentation head): the logits never leave TMEM.
         // The two warps of a lane quarter split the output ROW parity; each thread reduces both column
         // parities of its input pixel and writes two adjacent uint8 labels with one store.  The argmax
-        // runs as four independent compare/select chains (2 output pixels x 2 interleaved channel groups)
-        // merged at the end with "larger value, then smaller index" — the first maximum wins, like
-        // torch.max.  Padded classes evaluate to the clamp's lower bound (shift = -inf in shared memory)
-        // and can never beat a real class.  NaNs poison a running sum and divert to an exact slow path.
+        // runs as four independent integer-max chains (2 output pixels x 2 interleaved channel groups);
+        // padded classes are skipped.
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
 #pragma unroll 1
         for (int sub = 0; sub < p.ms; ++sub) {
           const uint32_t t0 =
               tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)((sub * p.nacc + hsel * 2) * p.bn);
-          float best[2][2];
-          int bidx[2][2];
+          // key = ordered(bf16(logit)) << 16 | (0xffff - class): "largest value, first index on ties" becomes ONE
+          // unsigned max per class.  Non-negative logits (ReLU-family head, lo >= 0): the bf16 bit pattern is already
+          // monotonic.  Otherwise the usual sign fix (negative: flip all bits, positive: set the top bit) after
+          // folding -0 into +0, which torch.max treats as equal.  NaN-propagating clamps keep a NaN logit (0x7fff
+          // after conversion) above +inf (0x7f80), and the index bits make the first NaN win, like torch.max.
+          // No divergent code anywhere near tcgen05.ld (.sync.aligned needs the whole warp).
+          uint32_t key[2][2] = {{0u, 0u}, {0u, 0u}};
+          const bool has_hi = p.hi < 3.0e38f;
+          auto reduce = [&](auto nonneg_tag) {
+            constexpr bool kNonNeg = decltype(nonneg_tag)::value;
 #pragma unroll
-          for (int px = 0; px < 2; ++px) {
-            best[px][0] = best[px][1] = -INFINITY;
-            bidx[px][0] = 0, bidx[px][1] = 8;
-          }
-          float nansum = 0.f;
+            for (int ci = 0; ci < kMaxMyChunks; ++ci) {
+              if (ci < nchunks) {  // warp-uniform
+                const int c0 = ci * 16;
+                uint32_t v[2][16];
+                tmem_ld16(t0 + c0, v[0]);
+                tmem_ld16(t0 + (uint32_t)p.bn + c0, v[1]);
+                tmem_ld_wait();
 #pragma unroll
-          for (int ci = 0; ci < kMaxMyChunks; ++ci) {
-            if (ci < nchunks) {  // warp-uniform
-              const int c0 = ci * 16;
-              uint32_t v[2][16];
-              tmem_ld16(t0 + c0, v[0]);
-              tmem_ld16(t0 + (uint32_t)p.bn + c0, v[1]);
-              tmem_ld_wait();
+                for (int e4 = 0; e4 < 16; e4 += 4) {
+                  if (c0 + e4 < p.cout) {  // whole groups of padded classes: skip (warp-uniform)
+                    const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
+                    const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
+                    const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
 #pragma unroll
-              for (int e4 = 0; e4 < 16; e4 += 4) {
-                if (c0 + e4 < p.cout) {  // whole groups of padded classes: skip their math (warp-uniform)
-                  const float4 sc = lds128(s_scale + (uint32_t)(c0 + e4) * 4);
-                  const float4 sh = lds128(s_shift + (uint32_t)(c0 + e4) * 4);
-                  const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
+                    for (int j = 0; j < 4; ++j) {
+                      if (c0 + e4 + j < p.cout) {  // the last group's padded classes (warp-uniform)
 #pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-#pragma unroll
-                    for (int px = 0; px < 2; ++px) {
-                      float t = fminf(fmaxf(fmaf(__uint_as_float(v[px][e4 + j]), scv[j], shv[j]), p.lo), p.hi);
-                      // compare the values the logits tensor would hold (bf16-rounded)
-                      t = __bfloat162float(__float2bfloat16_rn(t));
-                      nansum += t;
-                      constexpr int kChainSel = 0;
-                      const int h = ((e4 + j) >> 3) & 1;  // compile-time after unrolling
-                      const bool g = t > best[px][h];
-                      best[px][h] = g ? t : best[px][h];
-                      bidx[px][h] = g ? (c0 + e4 + j) : bidx[px][h];
-                      (void)kChainSel;
+                        for (int px = 0; px < 2; ++px) {
+                          float t = fmax_nan(fmaf(__uint_as_float(v[px][e4 + j]), scv[j], shv[j]), p.lo);
+                          if (has_hi) t = fmin_nan(t, p.hi);
+                          uint32_t b = bf16_hi_bits(t);
+                          if constexpr (!kNonNeg) {
+                            b = b == 0x80000000u ? 0u : b;
+                            b = (b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u)) & 0xffff0000u;
+                          }
+                          key[px][j & 1] = max(key[px][j & 1], b | (uint32_t)(0xffff - (c0 + e4 + j)));
+                        }
+                      }
                     }
                   }
                 }
               }
             }
-          }
-          uint32_t lab2 = 0;
-#pragma unroll
-          for (int px = 0; px < 2; ++px) {
-            const bool take1 = best[px][1] > best[px][0] || (best[px][1] == best[px][0] && bidx[px][1] < bidx[px][0]);
-            lab2 |= (uint32_t)(take1 ? bidx[px][1] : bidx[px][0]) << (8 * px);
-          }
-          if (nansum != nansum) {  // a NaN (or inf - inf) somewhere: redo this pixel pair with exact semantics
-            lab2 = 0;
-#pragma unroll 1
-            for (int px = 0; px < 2; ++px) {
-              float bs = 0.f;
-              int bi = 0;
-#pragma unroll 1
-              for (int c0 = 0; c0 < p.bn; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld16(t0 + (uint32_t)(px * p.bn) + c0, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                  if (c0 + j < p.cout) {
-                    float t = fminf(fmaxf(fmaf(__uint_as_float(v[j]), g_scale[c0 + j], g_scale[p.bn + c0 + j]), p.lo), p.hi);
-                    t = __bfloat162float(__float2bfloat16_rn(t));
-                    if (c0 + j == 0 || t > bs || (t != t && bs == bs)) bs = t, bi = c0 + j;
-                  }
-                }
-              }
-              lab2 |= (uint32_t)bi << (8 * px);
-            }
-          }
+          };
+          if (p.lo >= 0.f) reduce(std::true_type{}); else reduce(std::false_type{});
+          const uint32_t k0 = max(key[0][0], key[0][1]), k1 = max(key[1][0], key[1][1]);
+          const uint32_t lab2 = (0xffffu - (k0 & 0xffffu)) | ((0xffffu - (k1 & 0xffffu)) << 8);
           int gy, gx;
           if (pixel(sub, gy, gx)) {
             const int64_t opix = ((int64_t)img * p.oh + (gy * 2 + hsel)) * p.ow + gx * 2;
@@ -568,7 +556,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                   } else {
 #pragma unroll
                     for (int j = 0; j < 4; ++j)
-                      o[j] = fminf(fmaxf(fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi) + rv[j], p.lo2), p.hi2);
+                      o[j] = fmin_nan(fmax_nan(fast_act<MODE>(fmaf(o[j], scv[j], shv[j]), slv[j], p.lo, p.hi) + rv[j], p.lo2), p.hi2);
                   }
                 }
                 pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
@@ -915,7 +903,7 @@ static int max_stack(int n, int gh, int gw, int share = 0) {
 
 // Which A-sharing mode a forward conv can use (0 = none).  RTSEG_TC_SHARE=0 disables, =1 vertical only.
 static int pick_share(const rtseg_conv_desc *d, int gh, int gw, int kb) {
-  static const int knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 7;
+  static const int knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 15;  // bit 3: transposed conv
   if (d->stride != 1) return 0;
   if ((knob & 1) && d->kw == 1 && d->kh >= 2 && (d->kh - 1) * d->dil < (d->kh - 1) * 16 && d->pad_w == 0 && gw >= 8 &&
       gh >= 16)
@@ -1143,9 +1131,17 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
-  const int stack = (labels && !y) ? 1 : max_stack(d->n, d->h, d->w);  // labels-only: small TMEM footprint, 2 CTAs/SM
-  if (!plan_tc(d->cin, cout_pad, 9, 4, staged, stack, false, pl) || (labels && pl.n_tiles != 1))
-    RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
+  // One input tile with a one-pixel halo to the right and below (17 rows of 8*ms + 1 pixels) feeds all four shifted
+  // operands (x, x+1, y+1, both): a quarter of the shared-memory fill traffic of four separate boxes.
+  static const int share_knob = getenv("RTSEG_TC_SHARE") ? atoi(getenv("RTSEG_TC_SHARE")) : 15;
+  bool share = (share_knob & 8) && d->w >= 8 && d->h >= 16;
+  int stack = (labels && !y) ? 1 : max_stack(d->n, d->h, d->w, share ? 3 : 0);  // labels-only: small TMEM footprint, 2 CTAs/SM
+  if (share && !(plan_tc(d->cin, cout_pad, 9, 4, staged, stack, false, pl, 3, 1) && (!labels || pl.n_tiles == 1))) share = false;
+  if (!share) {
+    stack = (labels && !y) ? 1 : max_stack(d->n, d->h, d->w);
+    if (!plan_tc(d->cin, cout_pad, 9, 4, staged, stack, false, pl) || (labels && pl.n_tiles != 1))
+      RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_deconv3x3s2_tc: weights do not fit in shared memory");
+  }
   TcMaps maps;
   TcParams p;
   p.n = d->n, p.gh = d->h, p.gw = d->w;
@@ -1155,6 +1151,20 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   fill_common(p, d, pl, cout_pad);
   const int mode = epilogue_mode(d, slope, p);
   p.a_stages_per_unit = 4 * p.nkb;
+  if (share) {
+    const uint32_t row_b = (uint32_t)pl.kb * 2;
+    p.tw = 8, p.th = 16, p.wstack = 1;
+    p.unit_w = 8 * p.ms, p.unit_h = 16;
+    p.a_share = 1, p.a_dy = 0, p.a_dx = 0, p.a_boff = 0;
+    p.box_w = p.unit_w + 1, p.box_h = 17;
+    p.a_sub16 = (8u * row_b) >> 4;
+    p.a_sbo16 = ((uint32_t)p.box_w * row_b) >> 4;
+    for (int t = 0; t < 4; ++t) p.tap_off16[t] = ((uint32_t)((t >> 1) * p.box_w + (t & 1)) * row_b) >> 4;
+    p.a_tx_bytes = (uint32_t)p.box_w * p.box_h * row_b;
+    p.tiles_w = (int)cdiv(p.gw, p.unit_w), p.tiles_h = (int)cdiv(p.gh, p.unit_h);
+    p.num_m_tiles = (int64_t)p.n * p.tiles_w * p.tiles_h;
+    p.a_stages_per_unit = p.nkb;
+  }
   // four shifted input tiles and the MMAs each one feeds: {ky, kx, accumulator}
   static const int kOps[4][4][3] = {
       {{1, 1, 0}, {1, 2, 1}, {2, 1, 2}, {2, 2, 3}},      // A00

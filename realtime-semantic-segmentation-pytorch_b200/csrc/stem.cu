@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
 #pragma unroll
       for (int ci = 0; ci < CIN; ++ci) {
         const float v = win[ky][kx][ci];
-        if (inb[ky][kx]) mx[ci] = fmaxf(mx[ci], v);
+        if (inb[ky][kx]) mx[ci] = fmax_nan(mx[ci], v);
         const float *wp = &ws[((ky * 3 + kx) * CIN + ci) * CC];
         const float2 vv = make_float2(v, v);
 #pragma unroll
@@ -101,13 +101,13 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
 #pragma unroll
     for (int c = 0; c < CC; ++c)
       if (c < p.cconv)
-        out[c] = fminf(fmaxf(fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f), ep.lo), ep.hi);
+        out[c] = fmin_nan(fmax_nan(fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f), ep.lo), ep.hi);
   } else if (ep.mode == 1) {  // prelu with a slope vector
 #pragma unroll
     for (int c = 0; c < CC; ++c)
       if (c < p.cconv) {
         const float v = fmaf(acc[c], ep.scale ? __ldg(ep.scale + c) : 1.f, ep.shift ? __ldg(ep.shift + c) : 0.f);
-        out[c] = fmaf(__ldg(ep.slope + c), fminf(v, 0.f), fmaxf(v, 0.f));
+        out[c] = fmaf(__ldg(ep.slope + c), fmin_nan(v, 0.f), fmax_nan(v, 0.f));
       }
   } else {
 #pragma unroll
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T
       for (int kx = 0; kx < 3; ++kx) {
         const int wi = wo * 2 - 1 + kx;
         if (wi < 0 || wi >= p.w) continue;
-        m[0] = fmaxf(m[0], ld_f<T>(x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0));
+        m[0] = fmax_nan(m[0], ld_f<T>(x + (((int64_t)n * p.h + hi) * p.w + wi) * p.x_ct + p.x_co + c0));
       }
     }
   } else {
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T
       float v[V];
       Vec16<T>::unpack(raw[t], v);
 #pragma unroll
-      for (int e = 0; e < V; ++e) m[e] = fmaxf(m[e], v[e]);
+      for (int e = 0; e < V; ++e) m[e] = fmax_nan(m[e], v[e]);
     }
   }
   T *yp = y + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.y_ct + p.y_co + c0;

@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
       for (int ci = 0; ci < CIN; ++ci) {
         float m = v[ci];
 #pragma unroll
-        for (int t = 1; t < 9; ++t) m = fmaxf(m, v[t * CIN + ci]);
+        for (int t = 1; t < 9; ++t) m = fmax_nan(m, v[t * CIN + ci]);
         mx[ci] = m;
       }
     } else {
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
         float m = v[4 * CIN + ci];
 #pragma unroll
         for (int t = 0; t < 9; ++t)
-          if ((okmask >> t) & 1) m = fmaxf(m, v[t * CIN + ci]);
+          if ((okmask >> t) & 1) m = fmax_nan(m, v[t * CIN + ci]);
         mx[ci] = m;
       }
     }
@@ -230,8 +230,8 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
         const int c = c8 + e;
         if (c < N) {
           const float t = fmaf(__uint_as_float(acc[c < N ? c : 0]), s_aff[0][c < N ? c : 0], s_aff[1][c < N ? c : 0]);
-          if constexpr (MODE == 1) o[e] = fmaf(s_aff[2][c < N ? c : 0], fminf(t, 0.f), fmaxf(t, 0.f));
-          else o[e] = fminf(fmaxf(t, ep.lo), ep.hi);
+          if constexpr (MODE == 1) o[e] = fmaf(s_aff[2][c < N ? c : 0], fmin_nan(t, 0.f), fmax_nan(t, 0.f));
+          else o[e] = fmin_nan(fmax_nan(t, ep.lo), ep.hi);
         } else {
           o[e] = 0.f;
         }

@@ -279,6 +279,28 @@ def test_deconv(cin, cout, h, w, dtype):
     assert (labels.cpu().long() == own).float().mean().item() == 1.0
 
 
+@pytest.mark.parametrize("act", ["relu", "relu6", "none", "hardtanh"])
+def test_deconv_labels_head_matches_torch_max_on_ties_nan_and_inf(act):
+    """The fused head compares bf16-rounded logits; ties (ReLU zeros, ReLU6 saturation) take the first class and a
+    NaN logit wins like torch.max — checked against the argmax of the kernel's own materialised logits."""
+    from rtseg_b200 import modules, ops
+    m = _randomise(modules.DeConvBNAct(16, 19, act_type=act), 61)
+    with torch.no_grad():
+        m.up_conv[0].weight.mul_(6.0)             # push many logits past 6 so that relu6 / hardtanh saturate
+    x = seeded((1, 16, 12, 140), 62)
+    x[0, :, 3, 5] = float("nan")
+    x[0, 2, 7, 9] = float("inf")
+    xb = x.to("cuda", torch.bfloat16)
+    labels = torch.empty((1, 24, 280), dtype=torch.uint8, device="cuda")
+    with torch.no_grad():
+        logits = m.cuda()(xb)
+        m(xb, labels=labels, want_logits=False)
+    assert ops.tc_timeout_flag() == 0
+    own = logits.float().max(dim=1)[1]
+    assert torch.isnan(logits).any()
+    assert torch.equal(labels.long(), own)
+
+
 # -------------------------------------------------------------------------------- resize ----
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("align", [True, False])
@@ -561,3 +583,28 @@ def test_tensor_core_conv_with_ragged_k(cin, cout, k, stride):
         out = m.cuda()(buf)
     assert out.shape == ref.shape and torch.isfinite(out).all()
     assert rel_err(out, ref) < TOL_BF16
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("act", ["relu", "relu6", "prelu", "hardtanh"])
+def test_activations_propagate_nan_like_torch(act, dtype):
+    """torch's relu / relu6 / hardtanh / prelu / max_pool2d hand a NaN through; fmaxf-style clamps would hide it."""
+    from rtseg_b200 import modules, nets
+    x = seeded((1, 32, 10, 24), 63)
+    x[0, 5, 4, 7] = float("nan")
+    for m, fn in ((modules.ConvBNAct(32, 32, 3, act_type=act), lambda sd, t: B.conv_bn_act(t, sd, "m.", 3, 1, 1, act)),
+                  (modules.DWConvBNAct(32, 32, 3, act_type=act), lambda sd, t: B.dw_conv_bn_act(t, sd, "m.", 3, 1, 1, act))):
+        m = _randomise(m, 64)
+        with torch.no_grad():
+            ref = fn(_sd(m), x)
+        out = _run(m, x, dtype)
+        assert torch.equal(torch.isnan(out), torch.isnan(ref)) and torch.isnan(ref).any()
+    img = seeded((1, 3, 12, 20), 65)
+    img[0, 1, 6, 9] = float("nan")
+    blk = _randomise(nets.InitialBlock(3, 16, act), 66)
+    with torch.no_grad():
+        ref = B.initial_block(img, _sd(blk), "m.", act)
+    blk.act_dtype = dtype
+    with torch.no_grad():
+        out = blk.cuda()(img.cuda()).float().cpu()
+    assert torch.equal(torch.isnan(out), torch.isnan(ref)) and torch.isnan(ref[:, 13:]).any()
