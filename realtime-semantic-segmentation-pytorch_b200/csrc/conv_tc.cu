@@ -300,23 +300,39 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
             if (elect_one()) {
-            uint32_t st = started;  // bit a: accumulator a already holds a partial sum (this lane's running copy)
-            for (int t = 0; t < p.ntaps; ++t) {
-              const TcTap &tap = p.taps[t];
-              for (int o = 0; o < tap.nops; ++o) {  // a transposed conv feeds up to four accumulators from one tap
-                const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
-                const uint32_t a_acc = (uint32_t)tap.acc[o];
-                const uint32_t fresh = (st >> a_acc) & 1u;
-                st |= 1u << a_acc;
+            if (p.nacc == 1) {
+              // forward conv: one accumulator, one weight tap per A tap — the leanest possible issue loop (this single
+              // lane feeds the tensor core; every extra instruction here shows up in the C=128 layers)
+              for (int t = 0; t < p.ntaps; ++t) {
+                const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(p.taps[t].widx[0] * p.nkb + kb) * blk16);
+                const uint32_t fresh = (started & 1u) | (t > 0 ? 1u : 0u);
                 for (int sub = 0; sub < p.ms; ++sub) {
                   const uint32_t off16 = stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16;
                   uint64_t a_d = a_desc0 + (uint64_t)off16;
                   // rows not aligned to the 8-row swizzle atom: tell the MMA the phase of the first row
                   if (p.a_boff) a_d |= (uint64_t)((((s_a >> 4) + off16) >> 3) & 7u) << 49;
-                  const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
+                  const uint32_t d_col = d_tmem + (uint32_t)sub * (uint32_t)p.bn;
                   umma_bf16(d_col, a_d, b_d, idesc, fresh);
 #pragma unroll
                   for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                }
+              }
+            } else {
+              uint32_t st = started;  // bit a: accumulator a already holds a partial sum (this lane's running copy)
+              for (int t = 0; t < p.ntaps; ++t) {
+                const TcTap &tap = p.taps[t];
+                for (int o = 0; o < tap.nops; ++o) {  // a transposed conv feeds up to four accumulators from one tap
+                  const uint64_t b_d = b_desc0 + (uint64_t)((uint32_t)(tap.widx[o] * p.nkb + kb) * blk16);
+                  const uint32_t a_acc = (uint32_t)tap.acc[o];
+                  const uint32_t fresh = (st >> a_acc) & 1u;
+                  st |= 1u << a_acc;
+                  for (int sub = 0; sub < p.ms; ++sub) {
+                    const uint64_t a_d = a_desc0 + (uint64_t)(stage * stage16 + p.tap_off16[t] + (uint32_t)sub * sub16);
+                    const uint32_t d_col = d_tmem + (uint32_t)(sub * p.nacc + (int)a_acc) * (uint32_t)p.bn;
+                    umma_bf16(d_col, a_d, b_d, idesc, fresh);
+#pragma unroll
+                    for (int k = 1; k < KB / 16; ++k) umma_bf16(d_col, a_d + 2 * k, b_d + 2 * k, idesc, 1u);
+                  }
                 }
               }
             }
@@ -767,6 +783,18 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
       }
     }
     if (fixed + 3 * stage_bytes > kSmemBudget) continue;
+    // Residual layers push their residual boxes through the same ring.  When the ring cannot hold one unit's worth
+    // (K blocks + residual boxes; the C=128 layers: 96 KB of weights + two 32 KB staging buffers leave three stages
+    // for 2 + 2 boxes) the producer stalls on its own unit: trade the second output staging buffer for stages.
+    // Measured: C=128 +res 0.51 -> 0.57 of peak; layers whose ring is deep enough keep both buffers (a single
+    // staging buffer costs the non-residual C=128 layers 13 %).  RTSEG_TC_DEEP=0 disables.
+    static const int deep = getenv("RTSEG_TC_DEEP") ? atoi(getenv("RTSEG_TC_DEEP")) : 1;
+    const int unit_boxes = (share ? nkb : nwtaps * nkb) + bn / pick_kb(bn);
+    if (deep && has_res && (share || nwtaps == 1) && out_bufs == 2 && out_buf &&
+        (int)((kSmemBudget - fixed) / stage_bytes) < unit_boxes + 1) {
+      out_bufs = 1;
+      fixed -= out_buf;
+    }
     pl.out_bufs = out_bufs;
     pl.stage_bytes = stage_bytes;
     pl.ms = ms;

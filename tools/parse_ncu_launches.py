@@ -18,7 +18,9 @@ from collections import OrderedDict
 def short(name: str) -> str:
     name = re.sub(r"^void\s+", "", name)
     name = re.sub(r"\(.*$", "", name)
-    return name.replace("rtseg::", "")
+    for junk in ("rtseg::", "<unnamed>::", "unnamed>::", "(anonymous namespace)::"):
+        name = name.replace(junk, "")
+    return name
 
 
 def main():
@@ -50,8 +52,8 @@ def main():
             d[metric] = val * scale
     launches = list(per_launch.values())
     if "--one-step" in sys.argv:
-        # one forward pass = from a stem_kernel launch up to (not including) the next one
-        starts = [i for i, d in enumerate(launches) if d["name"].startswith("stem_kernel")]
+        # one forward pass = from a stem kernel launch up to (not including) the next one
+        starts = [i for i, d in enumerate(launches) if d["name"].startswith(("stem_kernel", "stem_tc_kernel"))]
         k = min(int(sys.argv[sys.argv.index("--one-step") + 1]), len(starts) - 2)
         launches = launches[starts[k]:starts[k + 1]]
         steps = 1
