@@ -276,6 +276,45 @@ int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p
                            const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
                            rtseg_stream_t stream);
 
+/* ---- training-mode pieces ---------------------------------------------
+ * In training the reference's ConvBNAct is Conv2d -> BatchNorm2d(batch statistics) -> activation
+ * as three autograd nodes (models/modules.py:73-85); NonBt1DBlock adds `+= x` before the last
+ * BatchNorm (models/erfnet.py:76-82).  The convolution itself — forward and data gradient — is
+ * rtseg_conv_* above (a data gradient is a convolution with transposed, flipped weights; the data
+ * gradient of a 3x3 stride-2 convolution is rtseg_deconv3x3s2 and vice versa).  The entry points
+ * below are the rest.  `res` (optional) is added to `y` before everything else (u = y + res).
+ * All reductions land in caller-zeroed fp64 buffers of `c` elements.                           */
+/* sum[c] += sum over pixels of u, sumsq[c] += sum of u^2 (sumsq may be NULL: bias gradients). */
+int rtseg_bn_stats(int64_t npix, int32_t c, int32_t dtype, const void *y, int32_t y_ctotal, int32_t y_coff,
+                   const void *res, int32_t r_ctotal, int32_t r_coff, double *sum, double *sumsq,
+                   rtseg_stream_t stream);
+/* z = act(scale[c] * u + shift[c]): BatchNorm with the batch statistics folded into scale/shift. */
+int rtseg_affine_act(int64_t npix, int32_t c, int32_t dtype, const void *y, int32_t y_ctotal, int32_t y_coff,
+                     const void *res, int32_t r_ctotal, int32_t r_coff, const float *scale, const float *shift,
+                     int32_t act, float act_p0, float act_p1, const float *slope, void *z, int32_t z_ctotal,
+                     int32_t z_coff, rtseg_stream_t stream);
+/* g = dz * act'(scale*u + shift), xhat = (u - mean) * invstd: sum_g[c] += sum g, sum_gx[c] += sum g*xhat. */
+int rtseg_bn_act_bwd_reduce(int64_t npix, int32_t c, int32_t dtype, const void *dz, int32_t d_ctotal, int32_t d_coff,
+                            const void *y, int32_t y_ctotal, int32_t y_coff, const void *res, int32_t r_ctotal,
+                            int32_t r_coff, const float *scale, const float *shift, const float *mean,
+                            const float *invstd, int32_t act, float act_p0, float act_p1, const float *slope,
+                            double *sum_g, double *sum_gx, rtseg_stream_t stream);
+/* du = k[c] * (g - mean_g[c] - xhat * mean_gx[c]), k = gamma * invstd: the gradient wrt u (= wrt y and wrt res). */
+int rtseg_bn_act_bwd_apply(int64_t npix, int32_t c, int32_t dtype, const void *dz, int32_t d_ctotal, int32_t d_coff,
+                           const void *y, int32_t y_ctotal, int32_t y_coff, const void *res, int32_t r_ctotal,
+                           int32_t r_coff, const float *scale, const float *shift, const float *mean,
+                           const float *invstd, const float *k, const float *mean_g, const float *mean_gx,
+                           int32_t act, float act_p0, float act_p1, const float *slope, void *du, int32_t u_ctotal,
+                           int32_t u_coff, rtseg_stream_t stream);
+/* Weight gradient of the dense convolution described by d (x: input slice, dy: gradient of the output slice
+ * d->y_ctotal / d->y_coff): dw[kh][kw][cin][cout] (fp32, caller-zeroed) += sum over pixels. */
+int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
+/* Gradient of MaxPool2d(3, 2, 1) (InitialBlock's pool branch, models/enet.py:44): dx = dy routed to the first
+ * maximum of each window. */
+int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,
+                           int32_t x_coff, const void *dy, int32_t g_ctotal, int32_t g_coff, void *dx, int32_t d_ctotal,
+                           int32_t d_coff, rtseg_stream_t stream);
+
 /* F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid, models/dabnet.py:32-34 (padding counted: /9).
  * Input: the caller's NCHW tensor (x_is_nchw = 1) or an NHWC channel slice; output: NHWC channel slice. */
 int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,

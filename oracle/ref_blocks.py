@@ -64,10 +64,16 @@ def activation(x, act_type: str, sd=None, prefix: str = "", **kw):
     raise NotImplementedError(f"Unsupport activation type: {a}")
 
 
+# Training restatement: with TRAINING = True every BatchNorm uses batch statistics (and updates the running
+# statistics in `sd` in place, momentum 0.1) like the reference's modules in .train(); torch autograd on the
+# tensors of `sd` then yields the reference gradients.
+TRAINING = False
+
+
 def batch_norm(x, sd, prefix: str):
-    """nn.BatchNorm2d in eval mode."""
+    """nn.BatchNorm2d: eval mode (running statistics) or, with TRAINING, batch statistics."""
     return F.batch_norm(x, sd[prefix + "running_mean"], sd[prefix + "running_var"], sd[prefix + "weight"],
-                        sd[prefix + "bias"], False, 0.0, BN_EPS)
+                        sd[prefix + "bias"], TRAINING, 0.1 if TRAINING else 0.0, BN_EPS)
 
 
 def _pad(kernel_size, dilation):

@@ -76,6 +76,16 @@ PROTOTYPES = {
     "rtseg_adaptive_avgpool": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "rtseg_avgpool3x3s2": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_channel_shuffle": (c_i32, [c_i64, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_bn_stats": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "rtseg_affine_act": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_f32, c_f32,
+                                 c_vp, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_bn_act_bwd_reduce": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32,
+                                        c_vp, c_vp, c_vp, c_vp, c_i32, c_f32, c_f32, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_bn_act_bwd_apply": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32,
+                                       c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_f32, c_f32, c_vp, c_vp, c_i32, c_i32,
+                                       c_vp]),
+    "rtseg_conv_wgrad": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_maxpool3x3s2_bwd": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_upsample_argmax_host": (c_i32, [c_i32] * 8 + [c_vp, c_vp, c_vp, c_vp]),
 }
 

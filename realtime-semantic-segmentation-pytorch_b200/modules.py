@@ -70,8 +70,13 @@ def _bn_tensors(bn):
 def _check_eval(mod: nn.Module, bn) -> None:
     if bn is not None and bn.training:
         raise NotImplementedError(
-            f"{type(mod).__name__}: training-mode BatchNorm (batch statistics + backward) is not part of the "
-            "inference kernels yet; call .eval() — there is deliberately no cuDNN fallback on this path")
+            f"{type(mod).__name__}: training-mode BatchNorm (batch statistics + backward) has no fused kernel for this "
+            "call (depthwise blocks, slice / residual arguments); call .eval() — there is deliberately no cuDNN "
+            "fallback on this path")
+
+
+def _plain_call(res, res_mode, out, x_coff, y_coff, act2=0, r_coff=0) -> bool:
+    return res is None and res_mode == ops.RES_NONE and out is None and x_coff == 0 and y_coff == 0 and act2 == 0 and r_coff == 0
 
 
 class _FusedConvMixin:
@@ -87,6 +92,9 @@ class _FusedConvMixin:
         return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act))
 
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, act2=0, r_coff=0):
+        if self[1].training and self[0].groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff, act2, r_coff):
+            from . import train   # batch statistics + autograd: Conv -> BN -> act as two tape nodes on rtseg kernels
+            return train.conv_bn_act(self, x)
         _check_eval(self, self[1])
         folded, post = self._folded()
         y = ops.conv(folded, ops.to_nhwc(x), res=res, res_mode=res_mode, out=out, x_coff=x_coff, y_coff=y_coff,
@@ -109,6 +117,15 @@ class Conv2d(nn.Conv2d):
 
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, bn=None, act=None):
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
+        if self.training and (bn is None or bn.training) and self.groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff) \
+                and torch.is_grad_enabled():
+            from . import train
+            y = train.conv(self, x)
+            if bn is not None:
+                return train.bn_act(bn, act, y)
+            if act is not None:
+                raise NotImplementedError("training through a bare convolution with a fused activation is not built")
+            return y
         tensors = [self.weight, self.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
         folded, post = cache.get(tensors, lambda: ops.fold_conv(self, bn, act))
         _check_eval(self, bn)
@@ -243,6 +260,9 @@ class DeConvBNAct(nn.Module):
         return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act))
 
     def forward(self, x, labels=None, want_logits=True):
+        if self.up_conv[1].training and labels is None:
+            from . import train
+            return train.conv_bn_act(self.up_conv, x)
         _check_eval(self, self.up_conv[1])
         folded, post = self._folded()
         y = ops.conv(folded, ops.to_nhwc(x), labels=labels, want_logits=want_logits)

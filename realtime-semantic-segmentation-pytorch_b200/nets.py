@@ -58,6 +58,10 @@ class InitialBlock(nn.Module):
         place the result in a channel slice of a caller-owned buffer (DABNet's concatenations)."""
         conv = self.conv[0]
         cin, cconv = conv.in_channels, conv.out_channels
+        if self.conv[1].training and out is None and x.shape[1] == cin:
+            from . import train   # training: conv branch and pool branch are tape nodes; the cat is a copy
+            xn = ops.to_nhwc(x, self.act_dtype or (x.dtype if x.is_cuda and ops.is_nhwc(x) else _param_dtype(self.conv)))
+            return ops.to_nhwc(torch.cat([train.conv_bn_act(self.conv, xn), train.maxpool3x3s2(xn)], dim=1))
         _check_eval(self, self.conv[1])
         folded, post = self.conv._folded()
         if post is not None:
@@ -97,6 +101,9 @@ class NonBt1DBlock(nn.Module):
         t = self.conv[0](x)
         t = self.conv[1](t)
         t = self.conv[2](t)
+        if self.bn_act[0].training:
+            from . import train   # conv -> (+x) -> BatchNorm(batch statistics) -> act, the add inside the BN node
+            return train.bn_act(self.bn_act[0], self.bn_act[1].activation, train.conv(self.conv[3], t), res=x)
         return self.conv[3](t, res=x, res_mode=ops.RES_PRE, bn=self.bn_act[0], act=self.bn_act[1].activation)
 
 

@@ -200,7 +200,7 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
         raise NotImplementedError("anisotropic stride/dilation is not supported")
     if getattr(conv, "padding_mode", "zeros") != "zeros":
         raise NotImplementedError("only zero padding is supported")
-    if isinstance(conv, nn.ConvTranspose2d):
+    if getattr(conv, "transposed", False):   # nn.ConvTranspose2d (or train._Spec around a bare weight tensor)
         cin, cout = conv.in_channels, conv.out_channels
         if not (kh == 3 and kw == 3 and sh == 2 and ph == 1 and pw == 1 and tuple(conv.output_padding) == (1, 1)
                 and conv.groups == 1 and dh == 1):

@@ -1,0 +1,234 @@
+"""Training-mode forward/backward of the conv + BatchNorm + activation blocks on the rtseg kernels.
+
+In training the reference runs Conv2d -> BatchNorm2d (batch statistics) -> activation as separate autograd
+nodes (models/modules.py:73-85).  Here the same two nodes exist as `torch.autograd.Function`s whose forward and
+backward are librtseg launches — autograd is only the tape:
+
+* `_ConvFn`: forward = the inference convolution kernel without an epilogue; data gradient = the same kernel
+  with transposed / flipped weights (a stride-2 3x3 convolution's data gradient is the 3x3 stride-2 transposed
+  convolution and vice versa); weight gradient = `rtseg_conv_wgrad`; bias gradient = a per-channel sum.
+* `_BNActFn`: batch statistics (`rtseg_bn_stats`, all-reduced over ranks for `nn.SyncBatchNorm`), running-stat
+  update, normalise + activation in one pass (`rtseg_affine_act`), optionally on `y + res` (NonBt1DBlock's
+  `+= x` before its last BatchNorm, models/erfnet.py:76-82); backward = one reduction + one apply pass.
+* `_MaxPoolFn`: InitialBlock's pool branch.
+
+Nothing here falls back to ATen convolutions or cuDNN; unsupported cases (depthwise weight gradients, PReLU
+slope gradients) raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import _lib, ops
+from ._lib import ConvDesc
+
+
+class _Spec:
+    """Quacks like an nn.Conv2d / nn.ConvTranspose2d for ops.fold_conv, around a bare weight tensor."""
+
+    def __init__(self, weight, bias, stride, dilation, padding, transposed):
+        self.weight, self.bias = weight, bias
+        self.kernel_size = tuple(weight.shape[2:])
+        self.stride, self.dilation, self.padding = (stride, stride), (dilation, dilation), tuple(padding)
+        self.transposed = transposed
+        self.groups = 1
+        self.padding_mode = "zeros"
+        self.output_padding = (1, 1)
+        if transposed:
+            self.in_channels, self.out_channels = weight.shape[0], weight.shape[1]
+        else:
+            self.out_channels, self.in_channels = weight.shape[0], weight.shape[1]
+
+
+def _conv_raw(x, weight, bias, stride, dilation, padding, transposed):
+    """y = conv(x) (+ bias) through the inference kernels, no BatchNorm, no activation."""
+    f, _ = ops.fold_conv(_Spec(weight.detach(), None if bias is None else bias.detach(), stride, dilation, padding,
+                               transposed))
+    return ops.conv(f, x)
+
+
+def _zeros64(c, device):
+    return torch.zeros(c, dtype=torch.float64, device=device)
+
+
+def _channel_sums(t, c, res=None, want_sq=True):
+    """Per-channel sum (and sum of squares) of an NHWC tensor (+ res) over all pixels, fp64."""
+    n, ct, h, w = t.shape
+    s = _zeros64(c, t.device)
+    sq = _zeros64(c, t.device) if want_sq else None
+    _lib.check(_lib.load().rtseg_bn_stats(n * h * w, c, ops._dtype_code(t.dtype), t.data_ptr(), ct, 0,
+                                          ops._ptr(res), res.shape[1] if res is not None else 0, 0, s.data_ptr(),
+                                          ops._ptr(sq), ops._stream()), "rtseg_bn_stats")
+    return s, sq
+
+
+class _ConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, dilation, padding, transposed):
+        x = ops.to_nhwc(x)
+        ctx.save_for_backward(x, weight)
+        ctx.meta = (stride, dilation, tuple(padding), transposed, bias is not None)
+        return _conv_raw(x, weight, bias, stride, dilation, padding, transposed)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride, dilation, padding, transposed, has_bias = ctx.meta
+        dy = ops.to_nhwc(dy.to(x.dtype))
+        n, _, h, w = x.shape
+        kh, kw = weight.shape[2:]
+        lib = _lib.load()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            if not transposed and stride == 1:
+                wt = weight.detach().flip(2, 3).transpose(0, 1)                      # (cin, cout, kh, kw): a conv cout -> cin
+                pad = (dilation * (kh - 1) - padding[0], dilation * (kw - 1) - padding[1])
+                dx = _conv_raw(dy, wt, None, 1, dilation, pad, False)
+            elif not transposed:   # 3x3 stride 2 pad 1 on even sizes: the adjoint is the k3 s2 p1 op1 transposed conv
+                if not (stride == 2 and (kh, kw) == (3, 3) and padding == (1, 1) and dilation == 1 and h % 2 == 0 and w % 2 == 0):
+                    raise NotImplementedError("data gradient of this strided convolution has no kernel")
+                dx = _conv_raw(dy, weight, None, 2, 1, (1, 1), True)
+            else:                  # transposed conv: the adjoint is the stride-2 convolution with the same weight tensor
+                dx = _conv_raw(dy, weight, None, 2, 1, (1, 1), False)
+        if ctx.needs_input_grad[1]:
+            # a transposed conv's weight gradient is that of its adjoint convolution (input := dy, output gradient := x)
+            a, g = (dy, x) if transposed else (x, dy)
+            cin, cout = a.shape[1], g.shape[1]
+            d = ConvDesc(n if not transposed else dy.shape[0], a.shape[2], a.shape[3], cin, cout, kh, kw, stride, dilation,
+                         padding[0], padding[1], 1, ops._dtype_code(a.dtype), 0, 0.0, 0.0, 0, 0, cin, 0, cout, 0, 0, 0)
+            acc = torch.zeros((kh, kw, cin, cout), dtype=torch.float32, device=x.device)
+            _lib.check(lib.rtseg_conv_wgrad(C.byref(d), a.data_ptr(), g.data_ptr(), acc.data_ptr(), ops._stream()),
+                       "rtseg_conv_wgrad")
+            dw = acc.permute(3, 2, 0, 1).contiguous().to(weight.dtype)               # both layouts: (g-ch, a-ch, kh, kw)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = _channel_sums(dy, dy.shape[1], want_sq=False)[0].to(weight.dtype)
+        return dx, dw, db, None, None, None, None
+
+
+class _BNActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, res, gamma, beta, bn, act_module):
+        y = ops.to_nhwc(y)
+        n, c, h, w = y.shape
+        if res is not None:
+            res = ops.to_nhwc(res)
+            if res.shape != y.shape or res.dtype != y.dtype:
+                raise ValueError("residual must match the convolution output")
+        code, p0, p1, prelu_w, post = ops.act_spec(act_module)
+        if post is not None or prelu_w is not None:
+            raise NotImplementedError("training through glu / softmax / prelu blocks is not built")
+        dev = y.device
+        s, sq = _channel_sums(y, c, res)
+        count = torch.tensor([float(n * h * w)], dtype=torch.float64, device=dev)
+        sync = isinstance(bn, nn.SyncBatchNorm) and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        if sync:  # SyncBatchNorm (reference utils/parallel.py:29-32): statistics over every rank's pixels
+            packed = torch.cat([s, sq, count])
+            dist.all_reduce(packed)
+            s, sq, count = packed[:c], packed[c:2 * c], packed[2 * c:]
+        mean = s / count
+        var = (sq / count - mean * mean).clamp_(min=0.0)
+        with torch.no_grad():
+            if bn.track_running_stats and bn.running_mean is not None:
+                m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked + 1)
+                unbiased = var * (count / (count - 1).clamp_(min=1.0))
+                bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
+                bn.running_var.mul_(1 - m).add_(unbiased.to(bn.running_var.dtype), alpha=m)
+                bn.num_batches_tracked += 1
+        invstd = torch.rsqrt(var + bn.eps)
+        g64 = gamma.detach().double() if gamma is not None else torch.ones(c, dtype=torch.float64, device=dev)
+        b64 = beta.detach().double() if beta is not None else torch.zeros(c, dtype=torch.float64, device=dev)
+        scale = (g64 * invstd).float()
+        shift = (b64 - mean * g64 * invstd).float()
+        mean32, invstd32 = mean.float(), invstd.float()
+        z = torch.empty_like(y, memory_format=torch.channels_last)
+        _lib.check(_lib.load().rtseg_affine_act(n * h * w, c, ops._dtype_code(y.dtype), y.data_ptr(), c, 0, ops._ptr(res),
+                                                c if res is not None else 0, 0, scale.data_ptr(), shift.data_ptr(), code,
+                                                p0, p1, None, z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
+        ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, (g64 * invstd).float())
+        ctx.meta = (code, p0, p1, sync, float(count.item()) if not sync else None, count if sync else None,
+                    gamma is not None, beta is not None, gamma.dtype if gamma is not None else torch.float32)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        y, res, scale, shift, mean, invstd, k = ctx.saved_tensors
+        code, p0, p1, sync, count_f, count_t, has_g, has_b, pdtype = ctx.meta
+        dz = ops.to_nhwc(dz.to(y.dtype))
+        n, c, h, w = y.shape
+        lib = _lib.load()
+        dt, st = ops._dtype_code(y.dtype), ops._stream()
+        rc = c if res is not None else 0
+        sg, sgx = _zeros64(c, y.device), _zeros64(c, y.device)
+        _lib.check(lib.rtseg_bn_act_bwd_reduce(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
+                                               scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(), code,
+                                               p0, p1, None, sg.data_ptr(), sgx.data_ptr(), st), "rtseg_bn_act_bwd_reduce")
+        dgamma = sgx.to(pdtype) if has_g else None      # this rank's sums: DDP averages parameter gradients itself
+        dbeta = sg.to(pdtype) if has_b else None
+        if sync:
+            packed = torch.cat([sg, sgx])
+            dist.all_reduce(packed)
+            sg, sgx = packed[:c], packed[c:]
+            m = count_t
+        else:
+            m = count_f
+        mg, mgx = (sg / m).float(), (sgx / m).float()
+        du = torch.empty_like(y, memory_format=torch.channels_last)
+        _lib.check(lib.rtseg_bn_act_bwd_apply(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
+                                              scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                              k.data_ptr(), mg.data_ptr(), mgx.data_ptr(), code, p0, p1, None, du.data_ptr(),
+                                              c, 0, st), "rtseg_bn_act_bwd_apply")
+        return du, (du if res is not None else None), dgamma, dbeta, None, None
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = ops.to_nhwc(x)
+        n, c, h, w = x.shape
+        out = ops.empty_nhwc(n, c, (h - 1) // 2 + 1, (w - 1) // 2 + 1, x.dtype, x.device)
+        ops.maxpool3x3s2(x, out, y_coff=0)
+        ctx.save_for_backward(x)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dy = ops.to_nhwc(dy.to(x.dtype))
+        n, c, h, w = x.shape
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        _lib.check(_lib.load().rtseg_maxpool3x3s2_bwd(n, h, w, c, ops._dtype_code(x.dtype), x.data_ptr(), c, 0, dy.data_ptr(),
+                                                      c, 0, dx.data_ptr(), c, 0, ops._stream()), "rtseg_maxpool3x3s2_bwd")
+        return dx
+
+
+# ------------------------------------------------------------------ module-level entry points ----
+def conv(module: nn.Module, x: torch.Tensor) -> torch.Tensor:
+    """Training forward of a bare nn.Conv2d / nn.ConvTranspose2d (dense, zero padding)."""
+    if module.groups != 1:
+        raise NotImplementedError("training through depthwise / grouped convolutions is not built (no weight-gradient kernel)")
+    transposed = bool(getattr(module, "transposed", False))
+    if transposed and not (tuple(module.kernel_size) == (3, 3) and tuple(module.stride) == (2, 2) and
+                           tuple(module.padding) == (1, 1) and tuple(module.output_padding) == (1, 1)):
+        raise NotImplementedError("only ConvTranspose2d(k=3, s=2, p=1, output_padding=1) can be trained through")
+    if module.stride[0] != module.stride[1] or module.dilation[0] != module.dilation[1]:
+        raise NotImplementedError("anisotropic stride/dilation is not supported")
+    return _ConvFn.apply(x, module.weight, module.bias, module.stride[0], module.dilation[0], tuple(module.padding), transposed)
+
+
+def bn_act(bn: nn.Module, act_module: Optional[nn.Module], y: torch.Tensor, res: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Training forward of BatchNorm2d (batch statistics) + activation on y (+ res)."""
+    return _BNActFn.apply(y, res, bn.weight, bn.bias, bn, act_module)
+
+
+def conv_bn_act(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
+    """Training forward of a Sequential(conv, bn, Activation) block (ConvBNAct / PWConvBNAct / DeConvBNAct.up_conv)."""
+    return bn_act(seq[1], seq[2].activation, conv(seq[0], x))
+
+
+def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
+    return _MaxPoolFn.apply(x)

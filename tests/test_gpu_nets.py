@@ -179,8 +179,9 @@ def test_inference_engine_host_io(name, use_graph):
 
 def test_modules_refuse_training_mode_and_cpu():
     from rtseg_b200 import modules
-    m = modules.ConvBNAct(16, 16, 3).cuda()
+    m = modules.DWConvBNAct(16, 16, 3).cuda()   # depthwise blocks have no weight-gradient kernel yet: no silent fallback
     with pytest.raises(NotImplementedError, match="training-mode"):
         m(torch.randn(1, 16, 8, 8, device="cuda"))
+    m = modules.ConvBNAct(16, 16, 3).cuda()
     with pytest.raises(TypeError):
         m.eval()(torch.randn(1, 16, 8, 8, device="cuda").half())
