@@ -17,6 +17,8 @@
 // All tensors NHWC with channel slices, fp32 or bf16; reductions accumulate in fp32 per thread and in fp64
 // across threads (atomics on the caller's zeroed buffer).  These are first, correct kernels on CUDA cores;
 // the weight gradient in particular is a register-tiled split-K GEMM, not yet a tcgen05 one.
+#include <mma.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -226,6 +228,93 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(WgradParams p, const T 
     }
 }
 
+// bf16 variant of the weight gradient on the (legacy, mma.sync) tensor cores: the pixel slab of x (at the tap's
+// shifted positions) and of dy is staged in shared memory exactly as it lies in HBM, [pixel][channel]; read as a
+// column-major A (M = ci, K = pixel) and a row-major B (K = pixel, N = co) it needs no transposition.  fp32
+// accumulation, same split-K + atomics scheme as the CUDA-core kernel above.  (A tcgen05 version wants MN-major
+// UMMA descriptors over the same tiles — next round.)
+__global__ void __launch_bounds__(256) conv_wgrad_wmma_kernel(WgradParams p, const __nv_bfloat16 *__restrict__ x,
+                                                              const __nv_bfloat16 *__restrict__ dy, float *__restrict__ dw) {
+  using namespace nvcuda;
+  constexpr int TK = 64, LD = 64 + 8;
+  __shared__ __align__(32) unsigned char smem_raw[2 * TK * LD * 2];
+  __nv_bfloat16(*As)[LD] = reinterpret_cast<__nv_bfloat16(*)[LD]>(smem_raw);
+  __nv_bfloat16(*Bs)[LD] = reinterpret_cast<__nv_bfloat16(*)[LD]>(smem_raw + TK * LD * 2);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int co_tiles = (p.cout + 63) / 64;
+  const int ci0 = (blockIdx.x / co_tiles) * 64, co0 = (blockIdx.x % co_tiles) * 64;
+  const int tap = blockIdx.y, ky = tap / p.kw, kx = tap % p.kw;
+  const int64_t M = (int64_t)p.n * p.gh * p.gw;
+  const int64_t m_begin = (int64_t)blockIdx.z * p.chunk;
+  const int64_t m_end = m_begin + p.chunk < M ? m_begin + p.chunk : M;
+  const int ci_sub = warp & 3, co_sub = (warp >> 2) * 2;
+  const bool a_vec = p.xs.ct % 8 == 0 && p.xs.co % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  const bool b_vec = p.gs.ct % 8 == 0 && p.gs.co % 8 == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0;
+  wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2];
+  wmma::fill_fragment(acc[0], 0.f);
+  wmma::fill_fragment(acc[1], 0.f);
+
+  for (int64_t m0 = m_begin; m0 < m_end; m0 += TK) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {  // 64 pixels x 8 sixteen-byte vectors per operand, two per thread
+      const int px = (tid >> 3) + 32 * j, cv = (tid & 7) * 8;
+      const int64_t m = m0 + px;
+      uint4 av = make_uint4(0, 0, 0, 0), bv = av;
+      if (m < m_end) {
+        const int jj = (int)(m % p.gw);
+        const int64_t r = m / p.gw;
+        const int ii = (int)(r % p.gh), b = (int)(r / p.gh);
+        const int hi = ii * p.stride - p.pad_h + ky * p.dil, wi = jj * p.stride - p.pad_w + kx * p.dil;
+        if (hi >= 0 && hi < p.h && wi >= 0 && wi < p.w) {
+          const __nv_bfloat16 *xp = x + (((int64_t)b * p.h + hi) * p.w + wi) * p.xs.ct + p.xs.co + ci0 + cv;
+          const __nv_bfloat16 *gp = dy + m * p.gs.ct + p.gs.co + co0 + cv;
+          if (a_vec && ci0 + cv + 8 <= p.cin) {
+            av = __ldg(reinterpret_cast<const uint4 *>(xp));
+          } else {
+            __nv_bfloat16 t[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) t[e] = ci0 + cv + e < p.cin ? xp[e] : __float2bfloat16(0.f);
+            av = *reinterpret_cast<const uint4 *>(t);
+          }
+          if (b_vec && co0 + cv + 8 <= p.cout) {
+            bv = __ldg(reinterpret_cast<const uint4 *>(gp));
+          } else {
+            __nv_bfloat16 t[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) t[e] = co0 + cv + e < p.cout ? gp[e] : __float2bfloat16(0.f);
+            bv = *reinterpret_cast<const uint4 *>(t);
+          }
+        }
+      }
+      *reinterpret_cast<uint4 *>(&As[px][cv]) = av;
+      *reinterpret_cast<uint4 *>(&Bs[px][cv]) = bv;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < TK; kk += 16) {
+      wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::col_major> a;
+      wmma::load_matrix_sync(a, &As[kk][ci_sub * 16], LD);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_major> b;
+        wmma::load_matrix_sync(b, &Bs[kk][(co_sub + j) * 16], LD);
+        wmma::mma_sync(acc[j], a, b, acc[j]);
+      }
+    }
+    __syncthreads();
+  }
+  float(*Cs)[64 + 4] = reinterpret_cast<float(*)[64 + 4]>(smem_raw);  // 64 x 68 floats = 17,408 B <= the operand tiles
+#pragma unroll
+  for (int j = 0; j < 2; ++j) wmma::store_matrix_sync(&Cs[ci_sub * 16][(co_sub + j) * 16], acc[j], 64 + 4, wmma::mem_row_major);
+  __syncthreads();
+  float *dwt = dw + (int64_t)tap * p.cin * p.cout;
+  for (int i = tid; i < 64 * 64; i += 256) {
+    const int ci = ci0 + i / 64, co = co0 + i % 64;
+    const float v = Cs[i / 64][i % 64];
+    if (ci < p.cin && co < p.cout && v != 0.f) atomicAdd(dwt + (int64_t)ci * p.cout + co, v);
+  }
+}
+
 // ---- MaxPool2d(3, 2, 1) backward, gather form: an input pixel collects dy from every window whose FIRST maximum
 // (row-major scan order, like ATen's max_pool2d_with_indices) it is.
 template <typename T>
@@ -373,10 +462,16 @@ extern "C" int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const v
   const int64_t M = (int64_t)p.n * p.gh * p.gw;
   int splits = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(M, 256), (int64_t)num_sms() * 6 / std::max(1, tiles * taps)));
   splits = std::min(splits, 65535);
-  p.chunk = cdiv(cdiv(M, splits), 16) * 16;
+  p.chunk = cdiv(cdiv(M, splits), 64) * 64;
   splits = (int)cdiv(M, p.chunk);
   RTSEG_REQUIRE(taps <= 65535, "too many taps");
   dim3 grid((unsigned)tiles, (unsigned)taps, (unsigned)splits);
+  static const int wmma_knob = getenv("RTSEG_WGRAD_WMMA") ? atoi(getenv("RTSEG_WGRAD_WMMA")) : 1;
+  if (d->dtype == RTSEG_BF16 && wmma_knob) {
+    conv_wgrad_wmma_kernel<<<grid, 256, 0, as_stream(stream)>>>(p, (const __nv_bfloat16 *)x, (const __nv_bfloat16 *)dy, dw);
+    RTSEG_LAUNCH_CHECK("conv_wgrad_wmma_kernel");
+    return RTSEG_OK;
+  }
   RTSEG_BY_DTYPE(d->dtype, (conv_wgrad_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(p, (const T *)x, (const T *)dy, dw)));
   RTSEG_LAUNCH_CHECK("conv_wgrad_kernel");
   return RTSEG_OK;
