@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — images/s at 1024x2048 on N B200s (BASELINE.json metric), one JSON line on rank 0.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet] [--batch B]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet|erfnet_train] [--batch B]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
   python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
 
@@ -26,14 +26,16 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 H, W, NUM_CLASS = 1024, 2048, 19
-DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16}
+DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16, "erfnet_train": 8}
 WORKLOAD_NAME = {
     "erfnet": "ERFNet inference batch {b} at 1024x2048 (BASELINE configs[1])",
     "fastscnn": "Fast-SCNN inference batch {b} at 1024x2048 (BASELINE configs[2])",
     "dabnet": "DABNet inference batch {b} at 1024x2048 (SURVEY §8 a10)",
     "lednet": "LEDNet inference batch {b} at 1024x2048 (SURVEY §8 a11)",
+    "erfnet_train": "ERFNet training step (fwd + OHEM + bwd + SGD), batch {b} per GPU at 1024x1024 (SURVEY §8d config 5)",
 }
-NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet"}
+NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet",
+             "erfnet_train": "ERFNet train step"}
 
 
 def parse_args():
@@ -73,6 +75,45 @@ def cpu_reference_run(workload: str, steps: int, warmup: int):
     return {"value": steps / dt, "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
             "sample": f"{steps} forward passes of 1 image 1x3x{H}x{W} fp32 after {warmup} warm-up "
                       f"(oracle/ref_nets.py, torch CPU)", "ms_per_image": 1e3 * dt / steps}
+
+
+def cpu_reference_train_run(steps: int, warmup: int, size: int = 1024):
+    """The reference's CPU training step restated (oracle, torch autograd on the host cores): ERFNet forward with
+    batch statistics + OHEM loss + backward on ONE size x size crop per step (bounded sample of the batch of 8)."""
+    import torch
+    from oracle import ref_blocks, ref_nets, ref_ohem
+    from tests.helpers import load_specs
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = load_specs()["erfnet"]["spec"]
+    sd0 = ref_nets.make_state(spec, 1, True)
+    x = ref_nets.make_input(0, 1, size, size)
+    g = torch.Generator().manual_seed(1)
+    labels = torch.randint(0, 19, (1, size, size), generator=g)
+
+    def one():
+        sd = {k: v.clone() for k, v in sd0.items()}
+        for k, v in sd.items():
+            if v.dtype.is_floating_point and "running" not in k:
+                v.requires_grad_(True)
+        ref_blocks.TRAINING = True
+        try:
+            logits = ref_nets.erfnet_forward(sd, x)
+        finally:
+            ref_blocks.TRAINING = False
+        ref_ohem.ohem_ce_loss(logits, labels, 0.7, 255)[0].backward()
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    return {"value": steps / dt, "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} training steps (fwd + OHEM + bwd) of 1 crop 1x3x{size}x{size} fp32 after {warmup} warm-up "
+                      f"(oracle/ref_nets.py with batch-statistics BatchNorm, torch autograd, CPU)",
+            "ms_per_image": 1e3 * dt / steps}
 
 
 # --------------------------------------------------------------------------- clocks ----
@@ -264,6 +305,97 @@ def measured_peak():
         return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
 
 
+# ------------------------------------------------------------------- training workload ----
+def wgrad_roofline(model, batch, size, peak_gbs, peak_src):
+    """One eager forward + backward with every rtseg_conv_wgrad launch (the dominant kernel of the training step)
+    bracketed by CUDA events on its stream; achieved = sum of algorithmic bytes / sum of durations."""
+    import ctypes
+    import torch
+    from rtseg_b200 import _lib
+    from rtseg_b200 import loss as rloss
+
+    lib = _lib.load()
+    orig = lib.rtseg_conv_wgrad
+    stream = torch.cuda.current_stream()
+    rec = []
+
+    def timed(dref, a, g, acc, st):
+        d = ctypes.cast(dref, ctypes.POINTER(_lib.ConvDesc)).contents if not hasattr(dref, "_obj") else dref._obj
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        rc = orig(dref, a, g, acc, st)
+        e1.record(stream)
+        e1.synchronize()
+        gh = (d.h + 2 * d.pad_h - d.dil * (d.kh - 1) - 1) // d.stride + 1
+        gw = (d.w + 2 * d.pad_w - d.dil * (d.kw - 1) - 1) // d.stride + 1
+        es = 2 if d.dtype == 1 else 4
+        rec.append((e0.elapsed_time(e1), (d.n * d.h * d.w * d.cin + d.n * gh * gw * d.cout) * es + d.kh * d.kw * d.cin * d.cout * 4))
+        return rc
+
+    m = model.module if hasattr(model, "module") else model
+    x = torch.randn((batch, 3, size, size), device="cuda")
+    y = torch.randint(0, 19, (batch, size, size), device="cuda")
+    lib.rtseg_conv_wgrad = timed
+    try:
+        rloss.OhemCELoss(0.7, 255)(m(x), y).backward()
+        torch.cuda.synchronize()
+    finally:
+        lib.rtseg_conv_wgrad = orig
+    m.zero_grad(set_to_none=True)
+    ms, by = sum(r[0] for r in rec), sum(r[1] for r in rec)
+    achieved = by / (ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "conv_wgrad_wmma_kernel (split-K weight gradient, bf16 mma.sync, fp32 accumulate) — "
+                                      "the largest single kernel of the step",
+            "achieved": round(achieved, 1), "peak": peak_gbs, "unit": "GB/s", "frac": round(achieved / peak_gbs, 4),
+            "traffic": None, "peak_source": peak_src, "launches_per_step": len(rec), "bytes_per_step": int(by),
+            "ms_per_step": round(ms, 4),
+            "note": "algorithmic bytes = x + dy read once + fp32 dW; the kernel re-reads both once per tap and channel tile"}
+
+
+def train_main(args, rank, local_rank, world, batch, workload_name, metric):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import train_bench
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    r = train_bench.run(batch=batch, size=1024, steps=args.steps, warmup=max(3, args.warmup), fp32=False, graph=True)
+    clocks = sampler.stop() if sampler else None
+    line = None
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        roof = wgrad_roofline(r["model"], batch, 1024, peak, peak_src)
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            b = cpu_reference_train_run(2, 1)
+            cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            cpu["value"] = round(cpu["value"], 4)
+        launches = r["launches_per_step"] if r["launches_per_step"] is not None else r["capture_launches"] // 5
+        line = {
+            "metric": metric, "value": round(r["images_per_s"], 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(r["ms_per_step"], 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name, "per_gpu_batch": batch, "global_batch": batch * world,
+                       "weights": "random init, torch.manual_seed(1); fp32 masters, bf16 activations and gradients",
+                       "loss": "OHEM cross entropy thresh 0.7, ignore 255", "optimizer": "SGD lr 0.01*world, momentum 0.9, wd 1e-4",
+                       "batchnorm": "SyncBatchNorm over ranks" if world > 1 else "BatchNorm, batch statistics",
+                       "l2": "every activation and gradient tensor (>= 268 MB at batch 8) exceeds the 126 MB L2",
+                       "parallelism": f"dp{world}: DistributedDataParallel, NCCL gradient all-reduce" if world > 1 else "dp1",
+                       "cuda_graph": r["graph"]},
+            "clocks": clocks,
+            "e2e": {"value": round(r["e2e_images_per_s"], 2), "unit": "images/s", "h2d_bytes_per_step": r["h2d_bytes"],
+                    "d2h_bytes_per_step": r["d2h_bytes"]},
+            "gpu_launches": int(launches * args.steps),
+            "roofline": roof, "cpu_baseline": cpu, "loss": round(r["loss"], 5),
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
 # ---------------------------------------------------------------------------- main ----
 def main():
     args = parse_args()
@@ -274,10 +406,14 @@ def main():
     workload_name = WORKLOAD_NAME[args.workload].format(b=batch)
     metric = f"images/sec @1024x2048 ({NET_LABEL[args.workload]})"
 
+    train = args.workload == "erfnet_train"
+    if train:
+        metric = "images/sec ERFNet training step @1024x1024 (fwd + OHEM + bwd + SGD)"
     if args.impl == "reference":
         if rank != 0:
             return 0
-        base = cpu_reference_run(args.workload, max(1, args.steps), max(0, args.warmup))
+        base = (cpu_reference_train_run(max(1, args.steps), max(0, args.warmup)) if train else
+                cpu_reference_run(args.workload, max(1, args.steps), max(0, args.warmup)))
         line = {
             "impl": "reference", "metric": metric, "value": round(base["value"], 4), "unit": "images/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -306,6 +442,8 @@ def main():
     from rtseg_b200 import _lib
 
     _lib.check(_lib.load().rtseg_device_check(), "rtseg_device_check")
+    if train:
+        return train_main(args, rank, local_rank, world, batch, workload_name, metric)
     torch.manual_seed(1)  # the reference's seed (configs/base_config.py:70); default random init
     model = rtseg_b200.nets.MODEL_HUB[args.workload](num_class=NUM_CLASS).eval().cuda()
     model.set_act_dtype(torch.bfloat16)

@@ -20,6 +20,7 @@
 #include <mma.h>
 
 #include <algorithm>
+#include <initializer_list>
 
 #include "common.cuh"
 
@@ -151,6 +152,157 @@ __global__ void __launch_bounds__(256) bn_act_bwd_apply_kernel(int64_t npix, int
   const float g = ld_f<T>(dz + p * ds.ct + ds.co + ch) * act_grad(v, ap.act, ap.p0, ap.p1, ap.slope ? __ldg(ap.slope + ch) : 0.f);
   const float xh = (u - __ldg(mean + ch)) * __ldg(invstd + ch);
   st_f<T>(du + p * us.ct + us.co + ch, __ldg(k + ch) * (g - __ldg(mg + ch) - xh * __ldg(mgx + ch)));
+}
+
+// ---- 16-byte-vector variants of the four BatchNorm kernels (c % V == 0, every slice 16-byte aligned) -------------
+template <typename T>
+__device__ __forceinline__ void load_u(const T *y, Slice ys, const T *res, Slice rs, int64_t p, int c0, float (&u)[Vec16<T>::N]) {
+  Vec16<T>::load(y + p * ys.ct + ys.co + c0, u);
+  if (res) {
+    float r[Vec16<T>::N];
+    Vec16<T>::load(res + p * rs.ct + rs.co + c0, r);
+#pragma unroll
+    for (int e = 0; e < Vec16<T>::N; ++e) u[e] += r[e];
+  }
+}
+
+template <int V, typename F>
+__device__ __forceinline__ void reduce2_vec(int64_t npix, int c, int ppb, double *out0, double *out1, F f) {
+  extern __shared__ float sm[];  // [2][lanes][cb * V]
+  const int cvn = c / V;
+  const int cb = cvn < (int)blockDim.x ? cvn : (int)blockDim.x;
+  const int lanes = (int)blockDim.x / cb;
+  const int tid = threadIdx.x, lane = tid / cb, cvl = tid % cb;
+  const int64_t p0 = (int64_t)blockIdx.x * ppb;
+  const int64_t p1 = p0 + ppb < npix ? p0 + ppb : npix;
+  const int width = cb * V;
+  for (int cbase = 0; cbase < cvn; cbase += cb) {
+    const int cv = cbase + cvl;
+    float a[V], b[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) a[e] = b[e] = 0.f;
+    if (lane < lanes && cv < cvn)
+      for (int64_t p = p0 + lane; p < p1; p += lanes) f(p, cv * V, a, b);
+    if (lane < lanes) {
+#pragma unroll
+      for (int e = 0; e < V; ++e) sm[lane * width + cvl * V + e] = a[e], sm[(lanes + lane) * width + cvl * V + e] = b[e];
+    }
+    __syncthreads();
+    for (int i = tid; i < width; i += blockDim.x) {
+      const int ch = cbase * V + i;
+      if (ch < c) {
+        double sa = 0.0, sb = 0.0;
+        for (int l = 0; l < lanes; ++l) sa += (double)sm[l * width + i], sb += (double)sm[(lanes + l) * width + i];
+        atomicAdd(out0 + ch, sa);
+        if (out1) atomicAdd(out1 + ch, sb);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_stats_vec_kernel(int64_t npix, int c, int ppb, const T *__restrict__ y, Slice ys,
+                                                           const T *__restrict__ res, Slice rs, double *sum, double *sumsq) {
+  constexpr int V = Vec16<T>::N;
+  reduce2_vec<V>(npix, c, ppb, sum, sumsq, [&](int64_t p, int c0, float (&a)[V], float (&b)[V]) {
+    float u[V];
+    load_u<T>(y, ys, res, rs, p, c0, u);
+#pragma unroll
+    for (int e = 0; e < V; ++e) a[e] += u[e], b[e] = fmaf(u[e], u[e], b[e]);
+  });
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) affine_act_vec_kernel(int64_t npix, int c, const T *__restrict__ y, Slice ys,
+                                                             const T *__restrict__ res, Slice rs, const float *__restrict__ scale,
+                                                             const float *__restrict__ shift, ActP ap, T *__restrict__ z, Slice zs) {
+  constexpr int V = Vec16<T>::N;
+  const int cvn = c / V;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= npix * cvn) return;
+  const int c0 = (int)(idx % cvn) * V;
+  const int64_t p = idx / cvn;
+  float u[V], o[V];
+  load_u<T>(y, ys, res, rs, p, c0, u);
+#pragma unroll
+  for (int e = 0; e < V; ++e) {
+    const float v = fmaf(u[e], scale ? __ldg(scale + c0 + e) : 1.f, shift ? __ldg(shift + c0 + e) : 0.f);
+    o[e] = act_apply(v, ap.act, ap.p0, ap.p1, ap.slope ? __ldg(ap.slope + c0 + e) : 0.f);
+  }
+  Vec16<T>::store(z + p * zs.ct + zs.co + c0, o);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_act_bwd_reduce_vec_kernel(int64_t npix, int c, int ppb, const T *__restrict__ dz, Slice ds,
+                                                                    const T *__restrict__ y, Slice ys, const T *__restrict__ res,
+                                                                    Slice rs, const float *__restrict__ scale,
+                                                                    const float *__restrict__ shift, const float *__restrict__ mean,
+                                                                    const float *__restrict__ invstd, ActP ap, double *sum_g,
+                                                                    double *sum_gx) {
+  constexpr int V = Vec16<T>::N;
+  reduce2_vec<V>(npix, c, ppb, sum_g, sum_gx, [&](int64_t p, int c0, float (&a)[V], float (&b)[V]) {
+    float u[V], d[V];
+    load_u<T>(y, ys, res, rs, p, c0, u);
+    Vec16<T>::load(dz + p * ds.ct + ds.co + c0, d);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const float v = fmaf(u[e], __ldg(scale + c0 + e), __ldg(shift + c0 + e));
+      const float g = d[e] * act_grad(v, ap.act, ap.p0, ap.p1, ap.slope ? __ldg(ap.slope + c0 + e) : 0.f);
+      a[e] += g;
+      b[e] = fmaf(g, (u[e] - __ldg(mean + c0 + e)) * __ldg(invstd + c0 + e), b[e]);
+    }
+  });
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_act_bwd_apply_vec_kernel(int64_t npix, int c, const T *__restrict__ dz, Slice ds,
+                                                                   const T *__restrict__ y, Slice ys, const T *__restrict__ res, Slice rs,
+                                                                   const float *__restrict__ scale, const float *__restrict__ shift,
+                                                                   const float *__restrict__ mean, const float *__restrict__ invstd,
+                                                                   const float *__restrict__ k, const float *__restrict__ mg,
+                                                                   const float *__restrict__ mgx, ActP ap, T *__restrict__ du, Slice us) {
+  constexpr int V = Vec16<T>::N;
+  const int cvn = c / V;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= npix * cvn) return;
+  const int c0 = (int)(idx % cvn) * V;
+  const int64_t p = idx / cvn;
+  float u[V], d[V], o[V];
+  load_u<T>(y, ys, res, rs, p, c0, u);
+  Vec16<T>::load(dz + p * ds.ct + ds.co + c0, d);
+#pragma unroll
+  for (int e = 0; e < V; ++e) {
+    const int ch = c0 + e;
+    const float v = fmaf(u[e], __ldg(scale + ch), __ldg(shift + ch));
+    const float g = d[e] * act_grad(v, ap.act, ap.p0, ap.p1, ap.slope ? __ldg(ap.slope + ch) : 0.f);
+    const float xh = (u[e] - __ldg(mean + ch)) * __ldg(invstd + ch);
+    o[e] = __ldg(k + ch) * (g - __ldg(mg + ch) - xh * __ldg(mgx + ch));
+  }
+  Vec16<T>::store(du + p * us.ct + us.co + c0, o);
+}
+
+// can the slices be read / written as 16-byte channel vectors?
+template <typename... P>
+bool vec_ok(int dtype, int c, std::initializer_list<Slice> slices, P... ptrs) {
+  const int V = dtype == RTSEG_BF16 ? 8 : 4;
+  if (c % V) return false;
+  for (const Slice &s : slices)
+    if (s.ct % V || s.co % V) return false;
+  const uintptr_t bits = (... | reinterpret_cast<uintptr_t>(ptrs));
+  return (bits & 15) == 0;
+}
+
+int reduce_geometry_vec(int64_t npix, int c, int V, int &ppb, unsigned &grid, size_t &smem) {
+  const int cvn = c / V;
+  const int cb = cvn < 256 ? cvn : 256;
+  const int lanes = 256 / cb;
+  ppb = 32 * lanes;  // 32 pixels x V channels per thread
+  const int64_t blocks = cdiv(npix, ppb);
+  if (blocks > INT32_MAX) return -1;
+  grid = (unsigned)blocks;
+  smem = (size_t)2 * lanes * cb * V * sizeof(float);
+  return 0;
 }
 
 // ---- weight gradient: split-K register-tiled GEMM, [64 ci] x [64 co] per block and tap, K = pixels ------------
@@ -387,6 +539,12 @@ extern "C" int rtseg_bn_stats(int64_t npix, int32_t c, int32_t dtype, const void
   size_t smem;
   RTSEG_REQUIRE(reduce_geometry(npix, c, ppb, grid, smem) == 0, "tensor too large");
   const Slice ys{y_ctotal, y_coff}, rs{r_ctotal, r_coff};
+  if (vec_ok(dtype, c, {ys, rs}, y, res) && reduce_geometry_vec(npix, c, dtype == RTSEG_BF16 ? 8 : 4, ppb, grid, smem) == 0) {
+    RTSEG_BY_DTYPE(dtype, (bn_stats_vec_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(npix, c, ppb, (const T *)y, ys,
+                                                                                          (const T *)res, rs, sum, sumsq)));
+    RTSEG_LAUNCH_CHECK("bn_stats_vec_kernel");
+    return RTSEG_OK;
+  }
   RTSEG_BY_DTYPE(dtype, (bn_stats_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(npix, c, ppb, (const T *)y, ys, (const T *)res, rs,
                                                                                     sum, sumsq)));
   RTSEG_LAUNCH_CHECK("bn_stats_kernel");
@@ -402,6 +560,13 @@ extern "C" int rtseg_affine_act(int64_t npix, int32_t c, int32_t dtype, const vo
   RTSEG_REQUIRE(!res || (r_ctotal >= r_coff + c && r_coff >= 0), "bad residual slice");
   const Slice ys{y_ctotal, y_coff}, rs{r_ctotal, r_coff}, zs{z_ctotal, z_coff};
   const ActP ap{act, act_p0, act_p1, slope};
+  if (vec_ok(dtype, c, {ys, rs, zs}, y, res, z)) {
+    const unsigned gv = (unsigned)cdiv(npix * (c / (dtype == RTSEG_BF16 ? 8 : 4)), 256);
+    RTSEG_BY_DTYPE(dtype, (affine_act_vec_kernel<T><<<gv, 256, 0, as_stream(stream)>>>(npix, c, (const T *)y, ys, (const T *)res, rs,
+                                                                                       scale, shift, ap, (T *)z, zs)));
+    RTSEG_LAUNCH_CHECK("affine_act_vec_kernel");
+    return RTSEG_OK;
+  }
   const unsigned grid = (unsigned)cdiv(npix * c, 256);
   RTSEG_BY_DTYPE(dtype, (affine_act_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(npix, c, (const T *)y, ys, (const T *)res, rs, scale,
                                                                                    shift, ap, (T *)z, zs)));
@@ -422,6 +587,13 @@ extern "C" int rtseg_bn_act_bwd_reduce(int64_t npix, int32_t c, int32_t dtype, c
   RTSEG_REQUIRE(reduce_geometry(npix, c, ppb, grid, smem) == 0, "tensor too large");
   const Slice ds{d_ctotal, d_coff}, ys{y_ctotal, y_coff}, rs{r_ctotal, r_coff};
   const ActP ap{act, act_p0, act_p1, slope};
+  if (vec_ok(dtype, c, {ds, ys, rs}, dz, y, res) && reduce_geometry_vec(npix, c, dtype == RTSEG_BF16 ? 8 : 4, ppb, grid, smem) == 0) {
+    RTSEG_BY_DTYPE(dtype, (bn_act_bwd_reduce_vec_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(
+                              npix, c, ppb, (const T *)dz, ds, (const T *)y, ys, (const T *)res, rs, scale, shift, mean, invstd, ap,
+                              sum_g, sum_gx)));
+    RTSEG_LAUNCH_CHECK("bn_act_bwd_reduce_vec_kernel");
+    return RTSEG_OK;
+  }
   RTSEG_BY_DTYPE(dtype, (bn_act_bwd_reduce_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(
                             npix, c, ppb, (const T *)dz, ds, (const T *)y, ys, (const T *)res, rs, scale, shift, mean, invstd, ap,
                             sum_g, sum_gx)));
@@ -439,6 +611,14 @@ extern "C" int rtseg_bn_act_bwd_apply(int64_t npix, int32_t c, int32_t dtype, co
   RTSEG_REQUIRE(npix > 0 && c > 0 && y_ctotal >= y_coff + c && d_ctotal >= d_coff + c && u_ctotal >= u_coff + c, "bad extent");
   const Slice ds{d_ctotal, d_coff}, ys{y_ctotal, y_coff}, rs{r_ctotal, r_coff}, us{u_ctotal, u_coff};
   const ActP ap{act, act_p0, act_p1, slope};
+  if (vec_ok(dtype, c, {ds, ys, rs, us}, dz, y, res, du)) {
+    const unsigned gv = (unsigned)cdiv(npix * (c / (dtype == RTSEG_BF16 ? 8 : 4)), 256);
+    RTSEG_BY_DTYPE(dtype, (bn_act_bwd_apply_vec_kernel<T><<<gv, 256, 0, as_stream(stream)>>>(
+                              npix, c, (const T *)dz, ds, (const T *)y, ys, (const T *)res, rs, scale, shift, mean, invstd, k, mean_g,
+                              mean_gx, ap, (T *)du, us)));
+    RTSEG_LAUNCH_CHECK("bn_act_bwd_apply_vec_kernel");
+    return RTSEG_OK;
+  }
   const unsigned grid = (unsigned)cdiv(npix * c, 256);
   RTSEG_BY_DTYPE(dtype, (bn_act_bwd_apply_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(
                             npix, c, (const T *)dz, ds, (const T *)y, ys, (const T *)res, rs, scale, shift, mean, invstd, k, mean_g,

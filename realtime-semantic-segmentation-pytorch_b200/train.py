@@ -124,7 +124,7 @@ class _BNActFn(torch.autograd.Function):
             raise NotImplementedError("training through glu / softmax / prelu blocks is not built")
         dev = y.device
         s, sq = _channel_sums(y, c, res)
-        count = torch.tensor([float(n * h * w)], dtype=torch.float64, device=dev)
+        count = torch.full((1,), float(n * h * w), dtype=torch.float64, device=dev)   # fill kernel: capturable
         sync = isinstance(bn, nn.SyncBatchNorm) and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
         if sync:  # SyncBatchNorm (reference utils/parallel.py:29-32): statistics over every rank's pixels
             packed = torch.cat([s, sq, count])
@@ -150,7 +150,7 @@ class _BNActFn(torch.autograd.Function):
                                                 c if res is not None else 0, 0, scale.data_ptr(), shift.data_ptr(), code,
                                                 p0, p1, None, z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
         ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, (g64 * invstd).float())
-        ctx.meta = (code, p0, p1, sync, float(count.item()) if not sync else None, count if sync else None,
+        ctx.meta = (code, p0, p1, sync, float(n * h * w) if not sync else None, count if sync else None,
                     gamma is not None, beta is not None, gamma.dtype if gamma is not None else torch.float32)
         return z
 

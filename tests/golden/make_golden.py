@@ -76,6 +76,25 @@ def main():
     with open(os.path.join(HERE, "ohem_cases.json"), "w") as f:
         json.dump(cases, f, indent=1)
 
+    # Training step of the REAL reference (ERFNet in .train(): batch-statistics BatchNorm; its own OhemCELoss; autograd):
+    # loss, every parameter gradient's L2 norm and the updated running statistics' norms pin oracle/ref_blocks.TRAINING.
+    model = ref_import.reference_model("erfnet", 19)
+    spec = [tuple(s) for s in specs["erfnet"]["spec"]]
+    model.load_state_dict(ref_nets.make_state(spec, seed=3, perturb_bn=True), strict=True)
+    model.train()
+    x = ref_nets.make_input(4, 2, 64, 128)
+    g = torch.Generator().manual_seed(5)
+    labels = torch.randint(0, 19, (2, 64, 128), generator=g)
+    labels[torch.rand((2, 64, 128), generator=g) < 0.1] = 255
+    loss = crit(model(x), labels)
+    loss.backward()
+    train = {"loss": float(loss.detach()),
+             "grad_norms": {k: float(p.grad.double().norm()) for k, p in model.named_parameters()},
+             "running_norms": {k: float(v.double().norm()) for k, v in model.state_dict().items() if "running" in k}}
+    print("train step: loss", train["loss"], "params with grads", len(train["grad_norms"]))
+    with open(os.path.join(HERE, "train_step.json"), "w") as f:
+        json.dump(train, f)
+
 
 if __name__ == "__main__":
     main()

@@ -84,3 +84,33 @@ def test_iou_known_answer():
 def test_upsample_argmax_first_max_on_ties():
     x = torch.zeros(1, 3, 2, 2)  # all ties -> index 0 everywhere
     assert (ref_head.upsample_argmax(x, (8, 8)) == 0).all()
+
+
+def test_training_restatement_matches_reference_training_step():
+    """oracle/ref_blocks.TRAINING (batch-statistics BatchNorm) + torch autograd vs the REAL reference's ERFNet.train()
+    step recorded in tests/golden/train_step.json: loss, every gradient's norm, the updated running statistics."""
+    from oracle import ref_blocks as B
+    with open(os.path.join(GOLDEN, "train_step.json")) as f:
+        gold = json.load(f)
+    spec = load_specs()["erfnet"]["spec"]
+    sd = ref_nets.make_state(spec, 3, True)
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.dtype.is_floating_point and "running" not in k}
+    x = ref_nets.make_input(4, 2, 64, 128)
+    g = torch.Generator().manual_seed(5)
+    labels = torch.randint(0, 19, (2, 64, 128), generator=g)
+    labels[torch.rand((2, 64, 128), generator=g) < 0.1] = 255
+    B.TRAINING = True
+    try:
+        logits = ref_nets.erfnet_forward(sd, x)
+    finally:
+        B.TRAINING = False
+    loss = ref_ohem.ohem_ce_loss(logits, labels, 0.7, 255)[0]
+    loss.backward()
+    assert abs(float(loss.detach()) - gold["loss"]) <= 1e-6 * max(1.0, abs(gold["loss"]))
+    assert set(params) == set(gold["grad_norms"])
+    for k, want in gold["grad_norms"].items():
+        got = float(params[k].grad.double().norm())
+        # same ATen kernels, same order: agreement is at rounding level; biases in front of a BatchNorm have ~0 gradients
+        assert abs(got - want) <= 1e-4 * max(want, 1e-3), k
+    for k, want in gold["running_norms"].items():
+        assert abs(float(sd[k].double().norm()) - want) <= 1e-6 * max(want, 1.0), k
