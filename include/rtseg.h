@@ -326,6 +326,12 @@ int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, int32_t dtype
                           int32_t x_ctotal, int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff,
                           rtseg_stream_t stream);
 
+/* Predict epilogue, core/seg_trainer.py:172-191 + utils/utils.py:59-78: out[p] = lut[labels[p]] (uint8 RGB, HWC;
+ * lut = 256 x 3 bytes, the colormap padded to 256 rows) and, when `image` (uint8 HWC, same size) is given,
+ * Pillow's Image.blend(image, pred, alpha) = (uint8)(image + alpha * (pred - image)), 0 <= alpha <= 1. */
+int rtseg_colorize_blend(int64_t npix, const uint8_t *labels, const uint8_t *lut, const uint8_t *image,
+                         float alpha, uint8_t *out, rtseg_stream_t stream);
+
 /* ---- host-buffer convenience (pinned or pageable HOST pointers) ------------
  * One call = H2D copy of the low-resolution logits, the fused head kernel,
  * D2H copy of the uint8 class map, all on `stream`, then a stream

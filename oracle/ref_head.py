@@ -47,3 +47,16 @@ def iou_from_confmat(cm: np.ndarray) -> np.ndarray:
 def miou(cm: np.ndarray) -> float:
     """validate(): iou.mean() over ALL classes, absent ones count as 0 (reference core/seg_trainer.py:136-137)."""
     return float(iou_from_confmat(cm).mean(dtype=np.float32))
+
+
+def colorize_blend(labels: np.ndarray, colormap, image=None, alpha: float = 0.0) -> np.ndarray:
+    """Predict epilogue of reference core/seg_trainer.py:172-191: colormap[labels] as uint8 HWC and, with `image`,
+    Pillow's Image.blend(image, pred, alpha) restated: (uint8)(in1 + alpha * (in2 - in1)) in float32, truncated
+    (libImaging/Blend.c, interpolation branch 0 <= alpha <= 1).  Pinned against Pillow itself in the CPU tests."""
+    lut = np.asarray(colormap, dtype=np.uint8)
+    pred = lut[labels]
+    if image is None:
+        return pred
+    in1, in2 = image.astype(np.int32), pred.astype(np.int32)
+    t = in1.astype(np.float32) + np.float32(alpha) * (in2 - in1).astype(np.float32)
+    return t.astype(np.int32).astype(np.uint8)

@@ -430,9 +430,68 @@ __global__ void __launch_bounds__(256) channel_shuffle2_kernel(int64_t npix, int
   *reinterpret_cast<uint4 *>(y + pix * y_pitch + k * 16) = o;
 }
 
+// ---- predict epilogue: class map -> colour image (+ alpha blend with the input picture) --------------------
+// Reference core/seg_trainer.py:172-191: `colormap[preds.max(dim=1)[1]]` (a LUT gather into an int64 HxWx3 tensor),
+// D2H, `astype(uint8)`, PIL `Image.blend(image, pred, alpha)`.  Here: four pixels per thread, LUT in shared
+// memory, uint8 HWC out; the blend restates Pillow's ImagingBlend for 0 <= alpha <= 1,
+// (UINT8)(in1 + alpha * (in2 - in1)) in single precision WITHOUT fused multiply-add, then truncation.
+__global__ void __launch_bounds__(256) colorize_kernel(int64_t npix, const uint8_t *__restrict__ labels,
+                                                       const uint8_t *__restrict__ lut, const uint8_t *__restrict__ image,
+                                                       float alpha, uint8_t *__restrict__ out) {
+  __shared__ uint8_t s_lut[768];
+  for (int i = threadIdx.x; i < 768; i += blockDim.x) s_lut[i] = lut[i];
+  __syncthreads();
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // group of four pixels
+  const int64_t p0 = q * 4;
+  if (p0 >= npix) return;
+  uint8_t rgb[12];
+  const bool full = p0 + 4 <= npix;
+  uint32_t l4 = 0;
+  if (full && (reinterpret_cast<uintptr_t>(labels) & 3) == 0) {
+    l4 = __ldg(reinterpret_cast<const uint32_t *>(labels + p0));
+  } else {
+    for (int i = 0; i < 4 && p0 + i < npix; ++i) l4 |= (uint32_t)labels[p0 + i] << (8 * i);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int l = (l4 >> (8 * i)) & 255;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) rgb[i * 3 + ch] = s_lut[l * 3 + ch];
+  }
+  if (image) {
+#pragma unroll
+    for (int i = 0; i < 12; ++i) {
+      if (p0 * 3 + i < npix * 3) {
+        const int in1 = image[p0 * 3 + i], in2 = rgb[i];
+        const float t = __fadd_rn((float)in1, __fmul_rn(alpha, (float)(in2 - in1)));
+        rgb[i] = (uint8_t)(int)t;
+      }
+    }
+  }
+  if (full && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+    uint32_t *o = reinterpret_cast<uint32_t *>(out + p0 * 3);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      o[k] = (uint32_t)rgb[4 * k] | ((uint32_t)rgb[4 * k + 1] << 8) | ((uint32_t)rgb[4 * k + 2] << 16) | ((uint32_t)rgb[4 * k + 3] << 24);
+  } else {
+    for (int i = 0; i < 12 && p0 * 3 + i < npix * 3; ++i) out[p0 * 3 + i] = rgb[i];
+  }
+}
+
 }  // namespace rtseg
 
 using namespace rtseg;
+
+extern "C" int rtseg_colorize_blend(int64_t npix, const uint8_t *labels, const uint8_t *lut, const uint8_t *image,
+                                    float alpha, uint8_t *out, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(labels && lut && out, "NULL pointer");
+  RTSEG_REQUIRE(npix > 0, "non-positive extent");
+  RTSEG_REQUIRE(!image || (alpha >= 0.f && alpha <= 1.f), "blend alpha must be in [0, 1] (Pillow's interpolation branch)");
+  const unsigned grid = (unsigned)cdiv(cdiv(npix, 4), 256);
+  colorize_kernel<<<grid, 256, 0, as_stream(stream)>>>(npix, labels, lut, image, alpha, out);
+  RTSEG_LAUNCH_CHECK("colorize_kernel");
+  return RTSEG_OK;
+}
 
 extern "C" int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
                                        int32_t align, int32_t dtype, const void *x, int32_t x_ct, int32_t x_co,

@@ -469,6 +469,33 @@ def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] 
     return out
 
 
+CITYSCAPES_COLORMAP = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (153, 153, 153),
+                       (250, 170, 30), (220, 220, 0), (107, 142, 35), (152, 251, 152), (70, 130, 180), (220, 20, 60),
+                       (255, 0, 0), (0, 0, 142), (0, 0, 70), (0, 60, 100), (0, 80, 100), (0, 0, 230), (119, 11, 32)]
+"""The 'cityscapes' table of reference utils/utils.py:59-66 (data, the only colormap the reference defines)."""
+
+
+def colorize(labels: torch.Tensor, colormap=None, image: Optional[torch.Tensor] = None, alpha: float = 0.0) -> torch.Tensor:
+    """uint8 [N, H, W, 3] colour picture of a uint8 class map, optionally alpha-blended with `image` (uint8 NHWC).
+
+    Replaces `colormap[preds.max(dim=1)[1]]` + `Image.blend(image, pred, blend_alpha)` of reference
+    core/seg_trainer.py:172-191 with one kernel on the device class map (no int64 map, no HxWx3 int64 gather)."""
+    _require_cuda(labels, "colorize")
+    if labels.dtype != torch.uint8 or not labels.is_contiguous():
+        raise TypeError("labels must be a contiguous uint8 class map")
+    colormap = CITYSCAPES_COLORMAP if colormap is None else colormap
+    lut = torch.zeros((256, 3), dtype=torch.uint8)
+    lut[:len(colormap)] = torch.as_tensor(colormap, dtype=torch.uint8)
+    lut = lut.to(labels.device)
+    out = torch.empty((*labels.shape, 3), dtype=torch.uint8, device=labels.device)
+    if image is not None:
+        if image.dtype != torch.uint8 or tuple(image.shape) != tuple(out.shape) or not image.is_contiguous() or not image.is_cuda:
+            raise ValueError("image must be a contiguous uint8 CUDA tensor shaped like the output (N, H, W, 3)")
+    _lib.check(_lib.load().rtseg_colorize_blend(labels.numel(), labels.data_ptr(), lut.data_ptr(), _ptr(image), float(alpha),
+                                                out.data_ptr(), _stream()), "rtseg_colorize_blend")
+    return out
+
+
 def tc_timeout_flag() -> int:
     return int(_lib.load().rtseg_tc_timeout_flag(_stream()))
 

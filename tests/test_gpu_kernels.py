@@ -608,3 +608,21 @@ def test_activations_propagate_nan_like_torch(act, dtype):
     with torch.no_grad():
         out = blk.cuda()(img.cuda()).float().cpu()
     assert torch.equal(torch.isnan(out), torch.isnan(ref)) and torch.isnan(ref[:, 13:]).any()
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 128), (1, 37, 53), (1, 3, 1)])
+def test_colorize_blend_matches_pillow_restatement(shape):
+    """Predict epilogue (reference core/seg_trainer.py:172-191): LUT gather + Pillow blend, bit-exact (uint8)."""
+    from rtseg_b200 import ops
+    rng = np.random.default_rng(12)
+    labels = rng.integers(0, 19, size=shape).astype(np.uint8)
+    image = rng.integers(0, 256, size=(*shape, 3)).astype(np.uint8)
+    lab = torch.from_numpy(labels).cuda()
+    out = ops.colorize(lab)
+    assert out.dtype == torch.uint8 and tuple(out.shape) == (*shape, 3)
+    assert np.array_equal(out.cpu().numpy(), ref_head.colorize_blend(labels, ops.CITYSCAPES_COLORMAP))
+    for alpha in (0.0, 0.3, 0.5, 0.77, 1.0):
+        got = ops.colorize(lab, image=torch.from_numpy(image).cuda(), alpha=alpha).cpu().numpy()
+        assert np.array_equal(got, ref_head.colorize_blend(labels, ops.CITYSCAPES_COLORMAP, image, alpha)), alpha
+    with pytest.raises(RuntimeError):
+        ops.colorize(lab, image=torch.from_numpy(image).cuda(), alpha=1.5)

@@ -114,3 +114,19 @@ def test_training_restatement_matches_reference_training_step():
         assert abs(got - want) <= 1e-4 * max(want, 1e-3), k
     for k, want in gold["running_norms"].items():
         assert abs(float(sd[k].double().norm()) - want) <= 1e-6 * max(want, 1.0), k
+
+
+def test_colorize_blend_restatement_matches_pillow_and_reference_colormap():
+    """ref_head.colorize_blend == colormap LUT + PIL.Image.blend (what reference core/seg_trainer.py:172-191 calls)."""
+    from PIL import Image
+    rng = np.random.default_rng(11)
+    cmap = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (153, 153, 153), (250, 170, 30),
+            (220, 220, 0), (107, 142, 35), (152, 251, 152), (70, 130, 180), (220, 20, 60), (255, 0, 0), (0, 0, 142), (0, 0, 70),
+            (0, 60, 100), (0, 80, 100), (0, 0, 230), (119, 11, 32)]     # utils/utils.py:59-66
+    labels = rng.integers(0, 19, size=(37, 53)).astype(np.uint8)
+    image = rng.integers(0, 256, size=(37, 53, 3)).astype(np.uint8)
+    pred = ref_head.colorize_blend(labels, cmap)
+    assert pred.dtype == np.uint8 and np.array_equal(pred, np.asarray(cmap, dtype=np.uint8)[labels])
+    for alpha in (0.0, 0.3, 0.4, 0.5, 0.77, 1.0):
+        want = np.asarray(Image.blend(Image.fromarray(image), Image.fromarray(pred), alpha))
+        assert np.array_equal(ref_head.colorize_blend(labels, cmap, image, alpha), want), alpha
