@@ -362,9 +362,10 @@ def train_main(args, rank, local_rank, world, batch, workload_name, metric):
     r = train_bench.run(batch=batch, size=1024, steps=args.steps, warmup=max(3, args.warmup), fp32=False, graph=True)
     clocks = sampler.stop() if sampler else None
     line = None
+    peak, peak_src = measured_peak()
+    # every rank runs the instrumented pass: under DDP the SyncBatchNorm all-reduces inside it are collective
+    roof = wgrad_roofline(r["model"], batch, 1024, peak, peak_src)
     if rank == 0:
-        peak, peak_src = measured_peak()
-        roof = wgrad_roofline(r["model"], batch, 1024, peak, peak_src)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             b = cpu_reference_train_run(2, 1)
