@@ -362,10 +362,15 @@ def train_main(args, rank, local_rank, world, batch, workload_name, metric):
     r = train_bench.run(batch=batch, size=1024, steps=args.steps, warmup=max(3, args.warmup), fp32=False, graph=True)
     clocks = sampler.stop() if sampler else None
     line = None
-    peak, peak_src = measured_peak()
-    # every rank runs the instrumented pass: under DDP the SyncBatchNorm all-reduces inside it are collective
-    roof = wgrad_roofline(r["model"], batch, 1024, peak, peak_src)
     if rank == 0:
+        peak, peak_src = measured_peak()
+        # a fresh single-GPU copy of the net (plain BatchNorm, no DDP hooks): the instrumented pass must not issue
+        # collectives that the other ranks do not join
+        del r["model"]
+        torch.cuda.empty_cache()
+        import rtseg_b200
+        probe = rtseg_b200.nets.ERFNet(num_class=19).cuda().train().set_act_dtype(torch.bfloat16)
+        roof = wgrad_roofline(probe, batch, 1024, peak, peak_src)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             b = cpu_reference_train_run(2, 1)
