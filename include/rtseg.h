@@ -309,6 +309,11 @@ int rtseg_bn_act_bwd_apply(int64_t npix, int32_t c, int32_t dtype, const void *d
 /* Weight gradient of the dense convolution described by d (x: input slice, dy: gradient of the output slice
  * d->y_ctotal / d->y_coff): dw[kh][kw][cin][cout] (fp32, caller-zeroed) += sum over pixels. */
 int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
+/* The same gradient on tcgen05 for ERFNet's asymmetric convolutions (bf16, stride 1, 3x1 / 1x3, cin and cout in
+ * {64, 128}): the pixel index is the GEMM's K, x and dy tiles are MN-major UMMA operands exactly as TMA lands
+ * them, the accumulators stay in tensor memory for the whole kernel.  Same arguments and dw layout. */
+int rtseg_conv_wgrad_tc_supported(const rtseg_conv_desc *d);
+int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
 /* Gradient of MaxPool2d(3, 2, 1) (InitialBlock's pool branch, models/enet.py:44): dx = dy routed to the first
  * maximum of each window. */
 int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,

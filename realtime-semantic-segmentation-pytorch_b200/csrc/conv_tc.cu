@@ -1011,6 +1011,155 @@ static bool can_stage_output(const rtseg_conv_desc *d, const void *y) {
   return y != nullptr && d->y_ctotal % 8 == 0 && d->y_coff % 8 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
 }
 
+// ======================================================================= weight gradient on tcgen05 ====
+// dW[tap][ci][co] = sum over pixels of x[pixel + tap][ci] * dy[pixel][co] for the stride-1 dense convs with
+// cin = cout in {64, 128} (60 of ERFNet's 74 convolutions).  The reduction dimension K is the PIXEL index, so both
+// operands are used exactly as TMA lands them for the forward conv — rows of 64 channels (128 bytes), one row per
+// pixel — but read as MN-major UMMA operands (instruction-descriptor bits 15/16): M = input channel, N = output
+// channel, K = pixel, 16 pixels (two 8-row swizzle atoms, SBO = 1024 bytes) per tcgen05.mma.  A 128-row M is two
+// 64-channel boxes LBO bytes apart: the two K blocks of a 128-channel input, or — for 64 channels — the boxes of TWO
+// taps, so that every MMA runs at M = 128.  The accumulators (one per tap or tap pair, fp32 in TMEM) live for the
+// whole kernel: a CTA streams its share of the pixel tiles through a TMA ring, never leaves the MMA loop, and adds
+// its TMEM contents to the caller-zeroed fp32 gradient once at the end (vector red.global).
+struct WgParams {
+  int units, tiles_w, tiles_h, tw, th;
+  int ngroups;               // work items per pixel tile
+  int a_boxes, b_boxes;      // 64-channel boxes per item
+  int n;                     // MMA N = 64 * b_boxes
+  int cin, cout;
+  int stages, stage_bytes;
+  int tmem_cols;
+  // per group: the two A boxes {map coordinates (channel, dx, dy)}, LBO between them (0 = one box, duplicated)
+  int a_c[4][2], a_dx[4][2], a_dy[4][2], a_lbo16[4];
+  int tap_of_half[4][2];     // which tap the lower / upper 64 accumulator rows of group g hold (-1: ignore)
+  int ci_of_half[4][2];      // first input channel of that half
+  int g_c0;                  // first channel of the dy slice
+};
+
+struct WgMaps {
+  CUtensorMap x, g;
+};
+
+constexpr int kWgThreads = 192;  // warp 0 TMA, warp 1 MMA, warps 2-5 final read-out
+
+__device__ __forceinline__ uint64_t wg_desc(uint32_t addr, uint32_t lbo16) {
+  // MN-major, SWIZZLE_128B: leading-byte-offset = distance of the next 64-element block along M/N,
+  // stride-byte-offset = distance of the next 8-row group along K (rows are contiguous: 1024 bytes)
+  return (uint64_t)((addr & 0x3ffffu) >> 4) | ((uint64_t)(lbo16 & 0x3fffu) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const WgParams p,
+                                                                      float *__restrict__ dw) {
+  extern __shared__ __align__(1024) uint8_t wg_smem_raw[];
+  const uint32_t s_base = (smem_u32(wg_smem_raw) + 1023u) & ~1023u;
+  __shared__ __align__(8) uint64_t s_bars[2 * kMaxStages + 1];
+  __shared__ uint32_t s_tmem, s_dead_word;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t full_bar = smem_u32(s_bars), empty_bar = full_bar + 8 * kMaxStages, done_bar = empty_bar + 8 * kMaxStages;
+  volatile uint32_t *dead = &s_dead_word;
+  if (threadIdx.x == 0) {
+    s_dead_word = 0;
+    for (int s = 0; s < p.stages; ++s) mbar_init(full_bar + 8 * s, 1), mbar_init(empty_bar + 8 * s, 1);
+    mbar_init(done_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem;
+  const uint32_t box_bytes = kTileM * 128;  // 128 pixels x 64 channels x 2 bytes
+  const uint32_t b_off = (uint32_t)p.a_boxes * box_bytes;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      prefetch_tmap(&maps.x);
+      prefetch_tmap(&maps.g);
+      uint32_t stage = 0, phase = 0;
+      for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+        const int twi = u % p.tiles_w, r = u / p.tiles_w, thi = r % p.tiles_h, img = r / p.tiles_h;
+        const int w0 = twi * p.tw, h0 = thi * p.th;
+        for (int g = 0; g < p.ngroups; ++g) {
+          mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+          const uint32_t dst = s_base + stage * (uint32_t)p.stage_bytes;
+          const int na = p.a_lbo16[g] ? 2 : 1;
+          mbar_expect_tx(full_bar + 8 * stage, (uint32_t)(na + p.b_boxes) * box_bytes);
+          for (int b = 0; b < na; ++b)
+            tma_load_4d(dst + b * box_bytes, &maps.x, full_bar + 8 * stage, p.a_c[g][b], w0 + p.a_dx[g][b], h0 + p.a_dy[g][b], img);
+          for (int b = 0; b < p.b_boxes; ++b)
+            tma_load_4d(dst + b_off + b * box_bytes, &maps.g, full_bar + 8 * stage, p.g_c0 + b * 64, w0, h0, img);
+          if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // kind::f16, D = f32, A = B = bf16, both MN-major (bits 15, 16), N at bit 17, M = 128 at bit 24
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.n >> 3) << 17) |
+                           ((uint32_t)(kTileM >> 4) << 24);
+    const uint32_t b_lbo16 = box_bytes >> 4;
+    uint32_t stage = 0, phase = 0;
+    bool first = true;
+    for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+      for (int g = 0; g < p.ngroups; ++g) {
+        mbar_wait(full_bar + 8 * stage, phase, dead);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a0 = s_base + stage * (uint32_t)p.stage_bytes;
+          const uint64_t a_d = wg_desc(a0, (uint32_t)p.a_lbo16[g]);
+          const uint64_t b_d = wg_desc(a0 + b_off, b_lbo16);
+          const uint32_t d_col = tmem_base + (uint32_t)(g * p.n);
+#pragma unroll
+          for (int k = 0; k < kTileM / 16; ++k)   // 16 pixels = 2048 bytes per step
+            umma_bf16(d_col, a_d + (uint64_t)(k * 128), b_d + (uint64_t)(k * 128), idesc, (first && k == 0) ? 0u : 1u);
+          umma_commit(empty_bar + 8 * stage);
+        }
+        __syncwarp();
+        if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+      }
+      first = false;
+    }
+    if (elect_one()) umma_commit(done_bar);
+    __syncwarp();
+  } else {
+    // ---- final read-out: lane quarter q of TMEM belongs to warp (q + 2) % 4 ... any warp w reads quarter w % 4
+    const bool any_work = (int)blockIdx.x < p.units;
+    if (any_work) {
+      mbar_wait(done_bar, 0, dead);
+      tc_fence_after();
+      const int q = warp & 3;
+      const int row = q * 32 + lane, half = row >> 6, r64 = row & 63;
+      for (int g = 0; g < p.ngroups; ++g) {
+        const int tap = p.tap_of_half[g][half];
+        const int ci = p.ci_of_half[g][half] + r64;
+        float *dst = dw + ((int64_t)(tap < 0 ? 0 : tap) * p.cin + ci) * p.cout;
+        for (int c0 = 0; c0 < p.n; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * p.n + c0), v);
+          tmem_ld_wait();
+          if (tap >= 0) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c0 + j), "f"(__uint_as_float(v[j])),
+                           "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
 }  // namespace rtseg
 
 using namespace rtseg;
@@ -1229,4 +1378,85 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
   maps.r = maps.a[0];
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   return launch_tc(maps, p, pl, ep, mode, nullptr, y, labels, as_stream(stream));
+}
+
+
+// ---- weight gradient on tcgen05 (see conv_wgrad_tc_kernel) ----------------------------------------------------
+static const char *wgrad_tc_why(const rtseg_conv_desc *d) {
+  if (d->dtype != RTSEG_BF16) return "dtype must be bf16";
+  if (d->groups != 1 || d->stride != 1) return "dense stride-1 convolutions only";
+  if (d->kh * d->kw != 3) return "three taps (3x1 or 1x3) only";
+  if ((d->cin != 64 && d->cin != 128) || (d->cout != 64 && d->cout != 128)) return "cin and cout must be 64 or 128";
+  if (d->x_ctotal % 8 || d->x_coff % 8 || d->y_ctotal % 8 || d->y_coff % 8) return "channel slices must be 16-byte aligned";
+  int gh, gw;
+  rtseg_out_hw(d, &gh, &gw);
+  if (gh != d->h || gw != d->w) return "same-size convolutions only";
+  return nullptr;
+}
+
+extern "C" int rtseg_conv_wgrad_tc_supported(const rtseg_conv_desc *d) { return d && wgrad_tc_why(d) == nullptr ? 1 : 0; }
+
+extern "C" int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(d && x && dy && dw, "NULL pointer");
+  if (const char *why = wgrad_tc_why(d)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_wgrad_tc: %s", why);
+  RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(dy) % 16 == 0 &&
+                    reinterpret_cast<uintptr_t>(dw) % 16 == 0, "tensor pointers must be 16-byte aligned");
+  WgParams p{};
+  pick_tile(d->w, p.tw, p.th);
+  p.tiles_w = (int)cdiv(d->w, p.tw), p.tiles_h = (int)cdiv(d->h, p.th);
+  p.units = d->n * p.tiles_w * p.tiles_h;
+  p.cin = d->cin, p.cout = d->cout;
+  p.a_boxes = 2, p.b_boxes = d->cout / 64, p.n = d->cout;
+  p.g_c0 = d->y_coff;
+  const int lbo_box = (kTileM * 128) >> 4;
+  auto tap_xy = [&](int t, int &dx, int &dy_) {
+    const int ky = t / d->kw, kx = t % d->kw;
+    dx = kx * d->dil - d->pad_w, dy_ = ky * d->dil - d->pad_h;
+  };
+  if (d->cin == 64) {   // two taps per MMA (M = 2 x 64), then the third alone (its upper half is ignored)
+    p.ngroups = 2;
+    for (int g = 0; g < 2; ++g)
+      for (int b = 0; b < 2; ++b) {
+        const int t = g == 0 ? b : 2;
+        p.a_c[g][b] = d->x_coff;
+        tap_xy(t, p.a_dx[g][b], p.a_dy[g][b]);
+        p.ci_of_half[g][b] = 0;
+      }
+    p.a_lbo16[0] = lbo_box, p.a_lbo16[1] = 0;
+    p.tap_of_half[0][0] = 0, p.tap_of_half[0][1] = 1, p.tap_of_half[1][0] = 2, p.tap_of_half[1][1] = -1;
+  } else {              // one tap per MMA, M = the two 64-channel K blocks of the input
+    p.ngroups = 3;
+    for (int g = 0; g < 3; ++g)
+      for (int b = 0; b < 2; ++b) {
+        p.a_c[g][b] = d->x_coff + 64 * b;
+        tap_xy(g, p.a_dx[g][b], p.a_dy[g][b]);
+        p.ci_of_half[g][b] = 64 * b;
+        p.tap_of_half[g][b] = g;
+      }
+    p.a_lbo16[0] = p.a_lbo16[1] = p.a_lbo16[2] = lbo_box;
+  }
+  p.stage_bytes = (p.a_boxes + p.b_boxes) * kTileM * 128;
+  p.stages = std::min<int>(kMaxStages, (int)(200 * 1024) / p.stage_bytes);
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(p.ngroups * p.n)) cols <<= 1;
+  p.tmem_cols = (int)cols;
+  RTSEG_REQUIRE(cols <= 512, "accumulators do not fit in tensor memory");
+  WgMaps maps;
+  const int64_t xc = d->x_ctotal, gc = d->y_ctotal;
+  if (int rc = encode_nhwc_map(&maps.x, x, d->x_coff + d->cin, d->w, d->h, d->n, xc, xc * d->w, xc * d->w * d->h, 64, p.tw, p.th))
+    return rc;
+  if (int rc = encode_nhwc_map(&maps.g, dy, d->y_coff + d->cout, d->w, d->h, d->n, gc, gc * d->w, gc * d->w * d->h, 64, p.tw, p.th))
+    return rc;
+  const int smem = p.stages * p.stage_bytes + 1024;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  RTSEG_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    RTSEG_CUDA(cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024 + 1024));
+    attr_set[dev] = true;
+  }
+  const unsigned grid = (unsigned)std::min(p.units, num_sms());
+  conv_wgrad_tc_kernel<<<grid, kWgThreads, smem, as_stream(stream)>>>(maps, p, dw);
+  RTSEG_LAUNCH_CHECK("conv_wgrad_tc_kernel");
+  return RTSEG_OK;
 }

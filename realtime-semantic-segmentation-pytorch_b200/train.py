@@ -18,6 +18,7 @@ slope gradients) raise.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -26,6 +27,9 @@ import torch.nn as nn
 
 from . import _lib, ops
 from ._lib import ConvDesc
+
+
+WGRAD_TC = os.environ.get("RTSEG_WGRAD_TC", "1") != "0"   # tcgen05 weight gradient where it applies (else mma.sync / CUDA cores)
 
 
 class _Spec:
@@ -102,8 +106,12 @@ class _ConvFn(torch.autograd.Function):
             d = ConvDesc(n if not transposed else dy.shape[0], a.shape[2], a.shape[3], cin, cout, kh, kw, stride, dilation,
                          padding[0], padding[1], 1, ops._dtype_code(a.dtype), 0, 0.0, 0.0, 0, 0, cin, 0, cout, 0, 0, 0)
             acc = torch.zeros((kh, kw, cin, cout), dtype=torch.float32, device=x.device)
-            _lib.check(lib.rtseg_conv_wgrad(C.byref(d), a.data_ptr(), g.data_ptr(), acc.data_ptr(), ops._stream()),
-                       "rtseg_conv_wgrad")
+            if WGRAD_TC and not transposed and lib.rtseg_conv_wgrad_tc_supported(C.byref(d)):
+                _lib.check(lib.rtseg_conv_wgrad_tc(C.byref(d), a.data_ptr(), g.data_ptr(), acc.data_ptr(), ops._stream()),
+                           "rtseg_conv_wgrad_tc")
+            else:
+                _lib.check(lib.rtseg_conv_wgrad(C.byref(d), a.data_ptr(), g.data_ptr(), acc.data_ptr(), ops._stream()),
+                           "rtseg_conv_wgrad")
             dw = acc.permute(3, 2, 0, 1).contiguous().to(weight.dtype)               # both layouts: (g-ch, a-ch, kh, kw)
         if has_bias and ctx.needs_input_grad[2]:
             db = _channel_sums(dy, dy.shape[1], want_sq=False)[0].to(weight.dtype)

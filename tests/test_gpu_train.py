@@ -241,3 +241,33 @@ def test_ddp_syncbn_matches_oracle_on_the_joint_batch(tmp_path):
     for k, v in got["running"].items():
         ref = sd[k].flatten()
         assert float((torch.tensor(v, dtype=torch.float64) - ref).norm() / ref.norm().clamp_min(1e-30)) < 1e-4, k
+
+
+@pytest.mark.parametrize("c,kh,kw,dil,shape", [(64, 3, 1, 1, (2, 32, 40)), (64, 1, 3, 2, (1, 48, 130)), (128, 3, 1, 4, (2, 24, 24)),
+                                               (128, 1, 3, 16, (1, 64, 64)), (64, 1, 3, 1, (3, 17, 9))])
+def test_tcgen05_weight_gradient_matches_torch(c, kh, kw, dil, shape):
+    """rtseg_conv_wgrad_tc (pixel index as the GEMM's K, MN-major UMMA operands, accumulators resident in TMEM) through
+    the C ABI vs torch's conv2d weight gradient on the same bf16 tensors (fp32 accumulation on both sides), and vs
+    the mma.sync kernel it replaces."""
+    import ctypes
+    from rtseg_b200 import _lib, ops
+    from rtseg_b200._lib import ConvDesc
+    lib = _lib.load()
+    n, h, w = shape
+    ph, pw = (dil if kh == 3 else 0), (dil if kw == 3 else 0)
+    x = seeded((n, c, h, w), 90).to(torch.bfloat16)
+    dy = seeded((n, c, h, w), 91).to(torch.bfloat16)
+    ref = torch.nn.grad.conv2d_weight(x.float(), (c, c, kh, kw), dy.float(), stride=1, padding=(ph, pw), dilation=dil)
+    xd = x.cuda().contiguous(memory_format=torch.channels_last)
+    gd = dy.cuda().contiguous(memory_format=torch.channels_last)
+    d = ConvDesc(n, h, w, c, c, kh, kw, 1, dil, ph, pw, 1, 1, 0, 0.0, 0.0, 0, 0, c, 0, c, 0, 0, 0)
+    assert lib.rtseg_conv_wgrad_tc_supported(ctypes.byref(d)) == 1
+    out = {}
+    for name, fn in (("tc", lib.rtseg_conv_wgrad_tc), ("mma", lib.rtseg_conv_wgrad)):
+        acc = torch.zeros((kh, kw, c, c), dtype=torch.float32, device="cuda")
+        _lib.check(fn(ctypes.byref(d), xd.data_ptr(), gd.data_ptr(), acc.data_ptr(), ops._stream()), name)
+        out[name] = acc.permute(3, 2, 0, 1).cpu()
+    assert ops.tc_timeout_flag() == 0
+    assert rel_err(out["tc"], ref) < 1e-5 and rel_err(out["tc"], out["mma"]) < 1e-5
+    d.stride = 2
+    assert lib.rtseg_conv_wgrad_tc_supported(ctypes.byref(d)) == 0     # anything else stays on the other kernels
