@@ -504,6 +504,53 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(int n, int h, int
   st_f<T>(dx + (((int64_t)b * h + iy) * w + ix) * ds.ct + ds.co + ch, g);
 }
 
+// the same with 16-byte channel vectors (c % V == 0, aligned slices): 36 vector loads per V channels instead of per channel
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_vec_kernel(int n, int h, int w, int c, int ho, int wo, const T *__restrict__ x,
+                                                                   Slice xs, const T *__restrict__ dy, Slice gs, T *__restrict__ dx,
+                                                                   Slice ds) {
+  constexpr int V = Vec16<T>::N;
+  const int cvn = c / V;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)n * h * w * cvn) return;
+  const int c0 = (int)(idx % cvn) * V;
+  int64_t r = idx / cvn;
+  const int ix = (int)(r % w);
+  r /= w;
+  const int iy = (int)(r % h), b = (int)(r / h);
+  const T *xb = x + (int64_t)b * h * w * xs.ct + xs.co + c0;
+  float g[V];
+#pragma unroll
+  for (int e = 0; e < V; ++e) g[e] = 0.f;
+  for (int oy = (iy + 1) / 2 - ((iy + 1) % 2 == 0 ? 1 : 0); oy <= (iy + 1) / 2; ++oy) {
+    if (oy < 0 || oy >= ho) continue;
+    for (int ox = (ix + 1) / 2 - ((ix + 1) % 2 == 0 ? 1 : 0); ox <= (ix + 1) / 2; ++ox) {
+      if (ox < 0 || ox >= wo) continue;
+      float best[V];
+      int bpos[V];  // ky * 3 + kx of the first maximum
+#pragma unroll
+      for (int e = 0; e < V; ++e) best[e] = -INFINITY, bpos[e] = -1;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const int yy = oy * 2 - 1 + t / 3, xx = ox * 2 - 1 + t % 3;
+        if (yy < 0 || yy >= h || xx < 0 || xx >= w) continue;
+        float v[V];
+        Vec16<T>::load(xb + ((int64_t)yy * w + xx) * xs.ct, v);
+#pragma unroll
+        for (int e = 0; e < V; ++e)
+          if (v[e] > best[e] || (v[e] != v[e] && best[e] == best[e]) || bpos[e] < 0) best[e] = v[e], bpos[e] = t;
+      }
+      const int mine = (iy - (oy * 2 - 1)) * 3 + (ix - (ox * 2 - 1));
+      float d[V];
+      Vec16<T>::load(dy + (((int64_t)b * ho + oy) * wo + ox) * gs.ct + gs.co + c0, d);
+#pragma unroll
+      for (int e = 0; e < V; ++e)
+        if (bpos[e] == mine) g[e] += d[e];
+    }
+  }
+  Vec16<T>::store(dx + (((int64_t)b * h + iy) * w + ix) * ds.ct + ds.co + c0, g);
+}
+
 int reduce_geometry(int64_t npix, int c, int &ppb, unsigned &grid, size_t &smem) {
   const int cb = c < 256 ? c : 256;
   const int lanes = 256 / cb;
@@ -665,6 +712,13 @@ extern "C" int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c
   RTSEG_REQUIRE(x_ctotal >= x_coff + c && g_ctotal >= g_coff + c && d_ctotal >= d_coff + c, "channel slice out of range");
   const int ho = (h - 1) / 2 + 1, wo = (w - 1) / 2 + 1;
   const Slice xs{x_ctotal, x_coff}, gs{g_ctotal, g_coff}, ds{d_ctotal, d_coff};
+  if (vec_ok(dtype, c, {xs, gs, ds}, x, dy, dx)) {
+    const unsigned gv = (unsigned)cdiv((int64_t)n * h * w * (c / (dtype == RTSEG_BF16 ? 8 : 4)), 256);
+    RTSEG_BY_DTYPE(dtype, (maxpool3x3s2_bwd_vec_kernel<T><<<gv, 256, 0, as_stream(stream)>>>(n, h, w, c, ho, wo, (const T *)x, xs,
+                                                                                            (const T *)dy, gs, (T *)dx, ds)));
+    RTSEG_LAUNCH_CHECK("maxpool3x3s2_bwd_vec_kernel");
+    return RTSEG_OK;
+  }
   const unsigned grid = (unsigned)cdiv((int64_t)n * h * w * c, 256);
   RTSEG_BY_DTYPE(dtype, (maxpool3x3s2_bwd_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(n, h, w, c, ho, wo, (const T *)x, xs,
                                                                                           (const T *)dy, gs, (T *)dx, ds)));

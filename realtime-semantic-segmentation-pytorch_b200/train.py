@@ -53,6 +53,11 @@ def _conv_raw(x, weight, bias, stride, dilation, padding, transposed):
     """y = conv(x) (+ bias) through the inference kernels, no BatchNorm, no activation."""
     f, _ = ops.fold_conv(_Spec(weight.detach(), None if bias is None else bias.detach(), stride, dilation, padding,
                                transposed))
+    if (not transposed and f.cin <= 3 and f.cout <= 32 and (f.kh, f.kw, f.stride, f.dil) == (3, 3, 2, 1)
+            and tuple(padding) == (1, 1) and x.shape[1] == f.cin):
+        # the image stem: the (tensor-core) stem kernel without pooling, BatchNorm or activation — same operand
+        # rounding as in inference instead of the CUDA-core catch-all for 3 input channels
+        return ops.stem(f, x, pool=False, out_dtype=x.dtype)
     return ops.conv(f, x)
 
 
