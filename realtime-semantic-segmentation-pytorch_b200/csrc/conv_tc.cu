@@ -1030,10 +1030,12 @@ struct WgParams {
   int stages, stage_bytes;
   int tmem_cols;
   // per group: the two A boxes {map coordinates (channel, dx, dy)}, LBO between them (0 = one box, duplicated)
-  int a_c[4][2], a_dx[4][2], a_dy[4][2], a_lbo16[4];
-  int tap_of_half[4][2];     // which tap the lower / upper 64 accumulator rows of group g hold (-1: ignore)
-  int ci_of_half[4][2];      // first input channel of that half
+  int a_c[4][3], a_dx[4][3], a_dy[4][3], a_lbo16[4], a_n[4];   // up to three boxes per group
+  int tap_of_blk[4][8];      // which tap block b (bs accumulator rows) of group g holds (-1: ignore)
+  int ci_of_blk[4][8];       // first input channel of that block
   int g_c0;                  // first channel of the dy slice
+  int bs;                    // channels per box / rows per block: 64 (SWIZZLE_128B) or 16 (SWIZZLE_32B)
+  int box_bytes, kstep16, sbo16, layout;
 };
 
 struct WgMaps {
@@ -1042,11 +1044,11 @@ struct WgMaps {
 
 constexpr int kWgThreads = 192;  // warp 0 TMA, warp 1 MMA, warps 2-5 final read-out
 
-__device__ __forceinline__ uint64_t wg_desc(uint32_t addr, uint32_t lbo16) {
-  // MN-major, SWIZZLE_128B: leading-byte-offset = distance of the next 64-element block along M/N,
-  // stride-byte-offset = distance of the next 8-row group along K (rows are contiguous: 1024 bytes)
-  return (uint64_t)((addr & 0x3ffffu) >> 4) | ((uint64_t)(lbo16 & 0x3fffu) << 16) | ((uint64_t)(1024 >> 4) << 32) |
-         (1ull << 46) | (2ull << 61);
+__device__ __forceinline__ uint64_t wg_desc(uint32_t addr, uint32_t lbo16, uint32_t sbo16, uint32_t layout) {
+  // MN-major: leading-byte-offset = distance of the next block (64 channels with SWIZZLE_128B, 16 with SWIZZLE_32B)
+  // along M/N, stride-byte-offset = distance of the next 8-row group along K (rows are contiguous: 8 x row bytes)
+  return (uint64_t)((addr & 0x3ffffu) >> 4) | ((uint64_t)(lbo16 & 0x3fffu) << 16) | ((uint64_t)sbo16 << 32) | (1ull << 46) |
+         ((uint64_t)layout << 61);
 }
 
 __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const WgParams p,
@@ -1073,7 +1075,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem;
-  const uint32_t box_bytes = kTileM * 128;  // 128 pixels x 64 channels x 2 bytes
+  const uint32_t box_bytes = (uint32_t)p.box_bytes;  // 128 pixels x bs channels x 2 bytes
   const uint32_t b_off = (uint32_t)p.a_boxes * box_bytes;
 
   if (warp == 0) {
@@ -1087,12 +1089,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
         for (int g = 0; g < p.ngroups; ++g) {
           mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
           const uint32_t dst = s_base + stage * (uint32_t)p.stage_bytes;
-          const int na = p.a_lbo16[g] ? 2 : 1;
+          const int na = p.a_n[g];
           mbar_expect_tx(full_bar + 8 * stage, (uint32_t)(na + p.b_boxes) * box_bytes);
           for (int b = 0; b < na; ++b)
             tma_load_4d(dst + b * box_bytes, &maps.x, full_bar + 8 * stage, p.a_c[g][b], w0 + p.a_dx[g][b], h0 + p.a_dy[g][b], img);
           for (int b = 0; b < p.b_boxes; ++b)
-            tma_load_4d(dst + b_off + b * box_bytes, &maps.g, full_bar + 8 * stage, p.g_c0 + b * 64, w0, h0, img);
+            tma_load_4d(dst + b_off + b * box_bytes, &maps.g, full_bar + 8 * stage, p.g_c0 + b * p.bs, w0, h0, img);
           if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
         }
       }
@@ -1110,12 +1112,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a0 = s_base + stage * (uint32_t)p.stage_bytes;
-          const uint64_t a_d = wg_desc(a0, (uint32_t)p.a_lbo16[g]);
-          const uint64_t b_d = wg_desc(a0 + b_off, b_lbo16);
+          const uint64_t a_d = wg_desc(a0, (uint32_t)p.a_lbo16[g], (uint32_t)p.sbo16, (uint32_t)p.layout);
+          const uint64_t b_d = wg_desc(a0 + b_off, b_lbo16, (uint32_t)p.sbo16, (uint32_t)p.layout);
           const uint32_t d_col = tmem_base + (uint32_t)(g * p.n);
+          const uint64_t kstep = (uint64_t)p.kstep16;
 #pragma unroll
-          for (int k = 0; k < kTileM / 16; ++k)   // 16 pixels = 2048 bytes per step
-            umma_bf16(d_col, a_d + (uint64_t)(k * 128), b_d + (uint64_t)(k * 128), idesc, (first && k == 0) ? 0u : 1u);
+          for (int k = 0; k < kTileM / 16; ++k)   // 16 pixels per step
+            umma_bf16(d_col, a_d + kstep * k, b_d + kstep * k, idesc, (first && k == 0) ? 0u : 1u);
           umma_commit(empty_bar + 8 * stage);
         }
         __syncwarp();
@@ -1132,10 +1135,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
       mbar_wait(done_bar, 0, dead);
       tc_fence_after();
       const int q = warp & 3;
-      const int row = q * 32 + lane, half = row >> 6, r64 = row & 63;
+      const int row = q * 32 + lane, blk = row / p.bs, rin = row % p.bs;
       for (int g = 0; g < p.ngroups; ++g) {
-        const int tap = p.tap_of_half[g][half];
-        const int ci = p.ci_of_half[g][half] + r64;
+        const int tap = p.tap_of_blk[g][blk];
+        const int ci = p.ci_of_blk[g][blk] + rin;
         float *dst = dw + ((int64_t)(tap < 0 ? 0 : tap) * p.cin + ci) * p.cout;
         for (int c0 = 0; c0 < p.n; c0 += 16) {
           uint32_t v[16];
@@ -1386,7 +1389,8 @@ static const char *wgrad_tc_why(const rtseg_conv_desc *d) {
   if (d->dtype != RTSEG_BF16) return "dtype must be bf16";
   if (d->groups != 1 || d->stride != 1) return "dense stride-1 convolutions only";
   if (d->kh * d->kw != 3) return "three taps (3x1 or 1x3) only";
-  if ((d->cin != 64 && d->cin != 128) || (d->cout != 64 && d->cout != 128)) return "cin and cout must be 64 or 128";
+  if (!(((d->cin == 64 || d->cin == 128) && (d->cout == 64 || d->cout == 128)) || (d->cin == 16 && d->cout == 16)))
+    return "cin and cout must be 64 or 128, or both 16";
   if (d->x_ctotal % 8 || d->x_coff % 8 || d->y_ctotal % 8 || d->y_coff % 8) return "channel slices must be 16-byte aligned";
   int gh, gw;
   rtseg_out_hw(d, &gh, &gw);
@@ -1406,36 +1410,50 @@ extern "C" int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, cons
   p.tiles_w = (int)cdiv(d->w, p.tw), p.tiles_h = (int)cdiv(d->h, p.th);
   p.units = d->n * p.tiles_w * p.tiles_h;
   p.cin = d->cin, p.cout = d->cout;
-  p.a_boxes = 2, p.b_boxes = d->cout / 64, p.n = d->cout;
   p.g_c0 = d->y_coff;
-  const int lbo_box = (kTileM * 128) >> 4;
+  p.bs = d->cin == 16 ? 16 : 64;
+  p.box_bytes = kTileM * p.bs * 2;
+  p.kstep16 = (16 * p.bs * 2) >> 4, p.sbo16 = (8 * p.bs * 2) >> 4, p.layout = p.bs == 64 ? 2 : 6;
+  p.b_boxes = d->cout / p.bs, p.n = d->cout;
+  const int lbo_box = p.box_bytes >> 4;
   auto tap_xy = [&](int t, int &dx, int &dy_) {
     const int ky = t / d->kw, kx = t % d->kw;
     dx = kx * d->dil - d->pad_w, dy_ = ky * d->dil - d->pad_h;
   };
-  if (d->cin == 64) {   // two taps per MMA (M = 2 x 64), then the third alone (its upper half is ignored)
-    p.ngroups = 2;
+  for (int g = 0; g < 4; ++g)
+    for (int b = 0; b < 8; ++b) p.tap_of_blk[g][b] = -1, p.ci_of_blk[g][b] = 0;
+  if (d->cin == 16) {   // the three taps are three 16-row blocks of one M = 128 MMA (rows 48.. hold junk and are ignored)
+    p.ngroups = 1, p.a_boxes = 3, p.a_n[0] = 3, p.a_lbo16[0] = lbo_box;
+    for (int b = 0; b < 3; ++b) {
+      p.a_c[0][b] = d->x_coff;
+      tap_xy(b, p.a_dx[0][b], p.a_dy[0][b]);
+      p.tap_of_blk[0][b] = b;
+    }
+  } else if (d->cin == 64) {   // two taps per MMA (M = 2 x 64), then the third alone (its upper half is ignored)
+    p.ngroups = 2, p.a_boxes = 2;
     for (int g = 0; g < 2; ++g)
       for (int b = 0; b < 2; ++b) {
         const int t = g == 0 ? b : 2;
         p.a_c[g][b] = d->x_coff;
         tap_xy(t, p.a_dx[g][b], p.a_dy[g][b]);
-        p.ci_of_half[g][b] = 0;
       }
-    p.a_lbo16[0] = lbo_box, p.a_lbo16[1] = 0;
-    p.tap_of_half[0][0] = 0, p.tap_of_half[0][1] = 1, p.tap_of_half[1][0] = 2, p.tap_of_half[1][1] = -1;
+    p.a_lbo16[0] = lbo_box, p.a_lbo16[1] = 0, p.a_n[0] = 2, p.a_n[1] = 1;
+    p.tap_of_blk[0][0] = 0, p.tap_of_blk[0][1] = 1, p.tap_of_blk[1][0] = 2;
   } else {              // one tap per MMA, M = the two 64-channel K blocks of the input
-    p.ngroups = 3;
-    for (int g = 0; g < 3; ++g)
+    p.ngroups = 3, p.a_boxes = 2;
+    for (int g = 0; g < 3; ++g) {
       for (int b = 0; b < 2; ++b) {
         p.a_c[g][b] = d->x_coff + 64 * b;
         tap_xy(g, p.a_dx[g][b], p.a_dy[g][b]);
-        p.ci_of_half[g][b] = 64 * b;
-        p.tap_of_half[g][b] = g;
+        p.ci_of_blk[g][b] = 64 * b;
+        p.tap_of_blk[g][b] = g;
       }
-    p.a_lbo16[0] = p.a_lbo16[1] = p.a_lbo16[2] = lbo_box;
+      p.a_lbo16[g] = lbo_box, p.a_n[g] = 2;
+    }
   }
-  p.stage_bytes = (p.a_boxes + p.b_boxes) * kTileM * 128;
+  // a stage always spans the eight (128 / bs) blocks an M = 128 MMA walks from the first A box
+  p.stage_bytes = std::max((p.a_boxes + p.b_boxes) * p.box_bytes, (kTileM / p.bs) * p.box_bytes);
+  p.stage_bytes = (p.stage_bytes + 1023) / 1024 * 1024;
   p.stages = std::min<int>(kMaxStages, (int)(200 * 1024) / p.stage_bytes);
   uint32_t cols = 32;
   while (cols < (uint32_t)(p.ngroups * p.n)) cols <<= 1;
@@ -1443,9 +1461,9 @@ extern "C" int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, cons
   RTSEG_REQUIRE(cols <= 512, "accumulators do not fit in tensor memory");
   WgMaps maps;
   const int64_t xc = d->x_ctotal, gc = d->y_ctotal;
-  if (int rc = encode_nhwc_map(&maps.x, x, d->x_coff + d->cin, d->w, d->h, d->n, xc, xc * d->w, xc * d->w * d->h, 64, p.tw, p.th))
+  if (int rc = encode_nhwc_map(&maps.x, x, d->x_coff + d->cin, d->w, d->h, d->n, xc, xc * d->w, xc * d->w * d->h, p.bs, p.tw, p.th))
     return rc;
-  if (int rc = encode_nhwc_map(&maps.g, dy, d->y_coff + d->cout, d->w, d->h, d->n, gc, gc * d->w, gc * d->w * d->h, 64, p.tw, p.th))
+  if (int rc = encode_nhwc_map(&maps.g, dy, d->y_coff + d->cout, d->w, d->h, d->n, gc, gc * d->w, gc * d->w * d->h, p.bs, p.tw, p.th))
     return rc;
   const int smem = p.stages * p.stage_bytes + 1024;
   static bool attr_set[64] = {false};

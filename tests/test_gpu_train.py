@@ -244,7 +244,8 @@ def test_ddp_syncbn_matches_oracle_on_the_joint_batch(tmp_path):
 
 
 @pytest.mark.parametrize("c,kh,kw,dil,shape", [(64, 3, 1, 1, (2, 32, 40)), (64, 1, 3, 2, (1, 48, 130)), (128, 3, 1, 4, (2, 24, 24)),
-                                               (128, 1, 3, 16, (1, 64, 64)), (64, 1, 3, 1, (3, 17, 9))])
+                                               (128, 1, 3, 16, (1, 64, 64)), (64, 1, 3, 1, (3, 17, 9)), (16, 3, 1, 1, (2, 40, 48)),
+                                               (16, 1, 3, 1, (1, 33, 70))])
 def test_tcgen05_weight_gradient_matches_torch(c, kh, kw, dil, shape):
     """rtseg_conv_wgrad_tc (pixel index as the GEMM's K, MN-major UMMA operands, accumulators resident in TMEM) through
     the C ABI vs torch's conv2d weight gradient on the same bf16 tensors (fp32 accumulation on both sides), and vs
