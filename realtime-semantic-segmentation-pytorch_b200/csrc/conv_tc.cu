@@ -1023,23 +1023,27 @@ static bool can_stage_output(const rtseg_conv_desc *d, const void *y) {
 // its TMEM contents to the caller-zeroed fp32 gradient once at the end (vector red.global).
 struct WgParams {
   int units, tiles_w, tiles_h, tw, th;
-  int ngroups;               // work items per pixel tile
-  int a_boxes, b_boxes;      // 64-channel boxes per item
-  int n;                     // MMA N = 64 * b_boxes
+  int ngroups;               // work items (MMA groups) per pixel tile, <= 8
+  int b_boxes;               // dy boxes per item
+  int n;                     // MMA N = cout
   int cin, cout;
   int stages, stage_bytes;
   int tmem_cols;
-  // per group: the two A boxes {map coordinates (channel, dx, dy)}, LBO between them (0 = one box, duplicated)
-  int a_c[4][3], a_dx[4][3], a_dy[4][3], a_lbo16[4], a_n[4];   // up to three boxes per group
-  int tap_of_blk[4][8];      // which tap block b (bs accumulator rows) of group g holds (-1: ignore)
-  int ci_of_blk[4][8];       // first input channel of that block
+  // group g = up to 128 / bs_a boxes of x, one per (tap, input-channel block); box b = {tensor map, coordinates}
+  int a_n[8];
+  short a_map[8][8], a_c[8][8], a_dx[8][8], a_dy[8][8];
+  short tap_of_blk[8][8];    // which tap block b (bs_a accumulator rows) of group g holds (-1: ignore)
+  short ci_of_blk[8][8];     // first input channel of that block
+  int a_lbo16[8];            // 0 = a single box, read twice
   int g_c0;                  // first channel of the dy slice
-  int bs;                    // channels per box / rows per block: 64 (SWIZZLE_128B) or 16 (SWIZZLE_32B)
-  int box_bytes, kstep16, sbo16, layout;
+  int bs_a, bs_b;            // channels per box: 64 (SWIZZLE_128B) or 16 (SWIZZLE_32B), per operand
+  int box_a, box_b, a_region;
+  int kstep_a, sbo_a, layout_a, kstep_b, sbo_b, layout_b;
 };
 
 struct WgMaps {
-  CUtensorMap x, g;
+  CUtensorMap x[4];          // input (parity views for stride 2)
+  CUtensorMap g;
 };
 
 constexpr int kWgThreads = 192;  // warp 0 TMA, warp 1 MMA, warps 2-5 final read-out
@@ -1075,12 +1079,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem;
-  const uint32_t box_bytes = (uint32_t)p.box_bytes;  // 128 pixels x bs channels x 2 bytes
-  const uint32_t b_off = (uint32_t)p.a_boxes * box_bytes;
+  const uint32_t box_a = (uint32_t)p.box_a, box_b = (uint32_t)p.box_b;  // 128 pixels x bs channels x 2 bytes
+  const uint32_t b_off = (uint32_t)p.a_region;
 
   if (warp == 0) {
     if (lane == 0) {
-      prefetch_tmap(&maps.x);
+      prefetch_tmap(&maps.x[0]);
       prefetch_tmap(&maps.g);
       uint32_t stage = 0, phase = 0;
       for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
@@ -1090,11 +1094,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
           mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
           const uint32_t dst = s_base + stage * (uint32_t)p.stage_bytes;
           const int na = p.a_n[g];
-          mbar_expect_tx(full_bar + 8 * stage, (uint32_t)(na + p.b_boxes) * box_bytes);
+          mbar_expect_tx(full_bar + 8 * stage, (uint32_t)na * box_a + (uint32_t)p.b_boxes * box_b);
           for (int b = 0; b < na; ++b)
-            tma_load_4d(dst + b * box_bytes, &maps.x, full_bar + 8 * stage, p.a_c[g][b], w0 + p.a_dx[g][b], h0 + p.a_dy[g][b], img);
+            tma_load_4d(dst + b * box_a, &maps.x[p.a_map[g][b]], full_bar + 8 * stage, p.a_c[g][b], w0 + p.a_dx[g][b],
+                        h0 + p.a_dy[g][b], img);
           for (int b = 0; b < p.b_boxes; ++b)
-            tma_load_4d(dst + b_off + b * box_bytes, &maps.g, full_bar + 8 * stage, p.g_c0 + b * p.bs, w0, h0, img);
+            tma_load_4d(dst + b_off + b * box_b, &maps.g, full_bar + 8 * stage, p.g_c0 + b * p.bs_b, w0, h0, img);
           if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
         }
       }
@@ -1103,7 +1108,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
     // kind::f16, D = f32, A = B = bf16, both MN-major (bits 15, 16), N at bit 17, M = 128 at bit 24
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.n >> 3) << 17) |
                            ((uint32_t)(kTileM >> 4) << 24);
-    const uint32_t b_lbo16 = box_bytes >> 4;
+    const uint32_t b_lbo16 = box_b >> 4;
     uint32_t stage = 0, phase = 0;
     bool first = true;
     for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
@@ -1112,13 +1117,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a0 = s_base + stage * (uint32_t)p.stage_bytes;
-          const uint64_t a_d = wg_desc(a0, (uint32_t)p.a_lbo16[g], (uint32_t)p.sbo16, (uint32_t)p.layout);
-          const uint64_t b_d = wg_desc(a0 + b_off, b_lbo16, (uint32_t)p.sbo16, (uint32_t)p.layout);
+          const uint64_t a_d = wg_desc(a0, (uint32_t)p.a_lbo16[g], (uint32_t)p.sbo_a, (uint32_t)p.layout_a);
+          const uint64_t b_d = wg_desc(a0 + b_off, b_lbo16, (uint32_t)p.sbo_b, (uint32_t)p.layout_b);
           const uint32_t d_col = tmem_base + (uint32_t)(g * p.n);
-          const uint64_t kstep = (uint64_t)p.kstep16;
+          const uint64_t ka = (uint64_t)p.kstep_a, kb = (uint64_t)p.kstep_b;
 #pragma unroll
           for (int k = 0; k < kTileM / 16; ++k)   // 16 pixels per step
-            umma_bf16(d_col, a_d + kstep * k, b_d + kstep * k, idesc, (first && k == 0) ? 0u : 1u);
+            umma_bf16(d_col, a_d + ka * k, b_d + kb * k, idesc, (first && k == 0) ? 0u : 1u);
           umma_commit(empty_bar + 8 * stage);
         }
         __syncwarp();
@@ -1135,7 +1140,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
       mbar_wait(done_bar, 0, dead);
       tc_fence_after();
       const int q = warp & 3;
-      const int row = q * 32 + lane, blk = row / p.bs, rin = row % p.bs;
+      const int row = q * 32 + lane, blk = row / p.bs_a, rin = row % p.bs_a;
       for (int g = 0; g < p.ngroups; ++g) {
         const int tap = p.tap_of_blk[g][blk];
         const int ci = p.ci_of_blk[g][blk] + rin;
@@ -1387,14 +1392,19 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
 // ---- weight gradient on tcgen05 (see conv_wgrad_tc_kernel) ----------------------------------------------------
 static const char *wgrad_tc_why(const rtseg_conv_desc *d) {
   if (d->dtype != RTSEG_BF16) return "dtype must be bf16";
-  if (d->groups != 1 || d->stride != 1) return "dense stride-1 convolutions only";
-  if (d->kh * d->kw != 3) return "three taps (3x1 or 1x3) only";
-  if (!(((d->cin == 64 || d->cin == 128) && (d->cout == 64 || d->cout == 128)) || (d->cin == 16 && d->cout == 16)))
-    return "cin and cout must be 64 or 128, or both 16";
+  if (d->groups != 1) return "dense convolutions only";
+  if (d->kh * d->kw > 9) return "at most nine taps";
+  if (d->cin % 16 || d->cout % 16 || d->cout > 256) return "cin and cout must be multiples of 16, cout <= 256";
   if (d->x_ctotal % 8 || d->x_coff % 8 || d->y_ctotal % 8 || d->y_coff % 8) return "channel slices must be 16-byte aligned";
   int gh, gw;
   rtseg_out_hw(d, &gh, &gw);
-  if (gh != d->h || gw != d->w) return "same-size convolutions only";
+  if (d->stride == 1) {
+    if (gh != d->h || gw != d->w) return "stride 1 needs a same-size convolution";
+  } else if (d->stride == 2) {
+    if ((d->h & 1) || (d->w & 1) || gh * 2 != d->h || gw * 2 != d->w) return "stride 2 needs even sizes and an exact halving";
+  } else {
+    return "stride must be 1 or 2";
+  }
   return nullptr;
 }
 
@@ -1405,67 +1415,61 @@ extern "C" int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, cons
   if (const char *why = wgrad_tc_why(d)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_wgrad_tc: %s", why);
   RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(dy) % 16 == 0 &&
                     reinterpret_cast<uintptr_t>(dw) % 16 == 0, "tensor pointers must be 16-byte aligned");
+  int gh, gw;
+  rtseg_out_hw(d, &gh, &gw);
   WgParams p{};
-  pick_tile(d->w, p.tw, p.th);
-  p.tiles_w = (int)cdiv(d->w, p.tw), p.tiles_h = (int)cdiv(d->h, p.th);
+  pick_tile(gw, p.tw, p.th);
+  p.tiles_w = (int)cdiv(gw, p.tw), p.tiles_h = (int)cdiv(gh, p.th);
   p.units = d->n * p.tiles_w * p.tiles_h;
-  p.cin = d->cin, p.cout = d->cout;
+  p.cin = d->cin, p.cout = d->cout, p.n = d->cout;
   p.g_c0 = d->y_coff;
-  p.bs = d->cin == 16 ? 16 : 64;
-  p.box_bytes = kTileM * p.bs * 2;
-  p.kstep16 = (16 * p.bs * 2) >> 4, p.sbo16 = (8 * p.bs * 2) >> 4, p.layout = p.bs == 64 ? 2 : 6;
-  p.b_boxes = d->cout / p.bs, p.n = d->cout;
-  const int lbo_box = p.box_bytes >> 4;
-  auto tap_xy = [&](int t, int &dx, int &dy_) {
-    const int ky = t / d->kw, kx = t % d->kw;
-    dx = kx * d->dil - d->pad_w, dy_ = ky * d->dil - d->pad_h;
-  };
-  for (int g = 0; g < 4; ++g)
-    for (int b = 0; b < 8; ++b) p.tap_of_blk[g][b] = -1, p.ci_of_blk[g][b] = 0;
-  if (d->cin == 16) {   // the three taps are three 16-row blocks of one M = 128 MMA (rows 48.. hold junk and are ignored)
-    p.ngroups = 1, p.a_boxes = 3, p.a_n[0] = 3, p.a_lbo16[0] = lbo_box;
-    for (int b = 0; b < 3; ++b) {
-      p.a_c[0][b] = d->x_coff;
-      tap_xy(b, p.a_dx[0][b], p.a_dy[0][b]);
-      p.tap_of_blk[0][b] = b;
-    }
-  } else if (d->cin == 64) {   // two taps per MMA (M = 2 x 64), then the third alone (its upper half is ignored)
-    p.ngroups = 2, p.a_boxes = 2;
-    for (int g = 0; g < 2; ++g)
-      for (int b = 0; b < 2; ++b) {
-        const int t = g == 0 ? b : 2;
-        p.a_c[g][b] = d->x_coff;
-        tap_xy(t, p.a_dx[g][b], p.a_dy[g][b]);
-      }
-    p.a_lbo16[0] = lbo_box, p.a_lbo16[1] = 0, p.a_n[0] = 2, p.a_n[1] = 1;
-    p.tap_of_blk[0][0] = 0, p.tap_of_blk[0][1] = 1, p.tap_of_blk[1][0] = 2;
-  } else {              // one tap per MMA, M = the two 64-channel K blocks of the input
-    p.ngroups = 3, p.a_boxes = 2;
-    for (int g = 0; g < 3; ++g) {
-      for (int b = 0; b < 2; ++b) {
-        p.a_c[g][b] = d->x_coff + 64 * b;
-        tap_xy(g, p.a_dx[g][b], p.a_dy[g][b]);
-        p.ci_of_blk[g][b] = 64 * b;
-        p.tap_of_blk[g][b] = g;
-      }
-      p.a_lbo16[g] = lbo_box, p.a_n[g] = 2;
-    }
-  }
-  // a stage always spans the eight (128 / bs) blocks an M = 128 MMA walks from the first A box
-  p.stage_bytes = std::max((p.a_boxes + p.b_boxes) * p.box_bytes, (kTileM / p.bs) * p.box_bytes);
-  p.stage_bytes = (p.stage_bytes + 1023) / 1024 * 1024;
+  p.bs_a = d->cin % 64 == 0 ? 64 : 16, p.bs_b = d->cout % 64 == 0 ? 64 : 16;
+  p.box_a = kTileM * p.bs_a * 2, p.box_b = kTileM * p.bs_b * 2;
+  p.kstep_a = (16 * p.bs_a * 2) >> 4, p.sbo_a = (8 * p.bs_a * 2) >> 4, p.layout_a = p.bs_a == 64 ? 2 : 6;
+  p.kstep_b = (16 * p.bs_b * 2) >> 4, p.sbo_b = (8 * p.bs_b * 2) >> 4, p.layout_b = p.bs_b == 64 ? 2 : 6;
+  p.b_boxes = d->cout / p.bs_b;
+  const int per = kTileM / p.bs_a;          // x boxes (accumulator row blocks) per MMA group
+  p.a_region = per * p.box_a;               // an M = 128 MMA always walks `per` blocks from the first box
+  p.stage_bytes = (p.a_region + p.b_boxes * p.box_b + 1023) / 1024 * 1024;
   p.stages = std::min<int>(kMaxStages, (int)(200 * 1024) / p.stage_bytes);
-  uint32_t cols = 32;
-  while (cols < (uint32_t)(p.ngroups * p.n)) cols <<= 1;
-  p.tmem_cols = (int)cols;
-  RTSEG_REQUIRE(cols <= 512, "accumulators do not fit in tensor memory");
+  RTSEG_REQUIRE(p.stages >= 2, "operand tiles do not fit in shared memory");
+
+  // tensor maps: stride 1 = the plain NHWC view; stride 2 = one view per input parity (row, column)
   WgMaps maps;
   const int64_t xc = d->x_ctotal, gc = d->y_ctotal;
-  if (int rc = encode_nhwc_map(&maps.x, x, d->x_coff + d->cin, d->w, d->h, d->n, xc, xc * d->w, xc * d->w * d->h, p.bs, p.tw, p.th))
+  if (d->stride == 1) {
+    if (int rc = encode_nhwc_map(&maps.x[0], x, d->x_coff + d->cin, d->w, d->h, d->n, xc, xc * d->w, xc * d->w * d->h, p.bs_a, p.tw, p.th))
+      return rc;
+    for (int i = 1; i < 4; ++i) maps.x[i] = maps.x[0];
+  } else {
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw) {
+        const __nv_bfloat16 *base = static_cast<const __nv_bfloat16 *>(x) + ((int64_t)ph * d->w + pw) * xc;
+        if (int rc = encode_nhwc_map(&maps.x[ph * 2 + pw], base, d->x_coff + d->cin, d->w / 2, d->h / 2, d->n, 2 * xc, 2 * xc * d->w,
+                                     xc * d->w * d->h, p.bs_a, p.tw, p.th))
+          return rc;
+      }
+  }
+  if (int rc = encode_nhwc_map(&maps.g, dy, d->y_coff + d->cout, gw, gh, d->n, gc, gc * gw, gc * gw * gh, p.bs_b, p.tw, p.th))
     return rc;
-  if (int rc = encode_nhwc_map(&maps.g, dy, d->y_coff + d->cout, d->w, d->h, d->n, gc, gc * d->w, gc * d->w * d->h, p.bs, p.tw, p.th))
-    return rc;
-  const int smem = p.stages * p.stage_bytes + 1024;
+
+  // every (tap, input-channel block) is one x box = one block of accumulator rows; `per` of them form an MMA group
+  struct Box { int tap, ci, map, dx, dy; };
+  Box boxes[9 * 16];
+  int nboxes = 0;
+  const int kblocks = d->cin / p.bs_a;
+  RTSEG_REQUIRE(d->kh * d->kw * kblocks <= 9 * 16, "too many operand boxes");
+  for (int t = 0; t < d->kh * d->kw; ++t) {
+    const int oy = (t / d->kw) * d->dil - d->pad_h, ox = (t % d->kw) * d->dil - d->pad_w;   // input = stride * out + o
+    int map = 0, dx = ox, dy_ = oy;
+    if (d->stride == 2) {
+      const int ph = ((oy % 2) + 2) % 2, pw = ((ox % 2) + 2) % 2;
+      map = ph * 2 + pw, dy_ = (oy - ph) / 2, dx = (ox - pw) / 2;
+    }
+    for (int kb = 0; kb < kblocks; ++kb) boxes[nboxes++] = Box{t, kb * p.bs_a, map, dx, dy_};
+  }
+  const int groups_total = (nboxes + per - 1) / per;
+  const int groups_per_launch = std::min(8, 512 / p.n);
   static bool attr_set[64] = {false};
   int dev = 0;
   RTSEG_CUDA(cudaGetDevice(&dev));
@@ -1473,8 +1477,29 @@ extern "C" int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, cons
     RTSEG_CUDA(cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024 + 1024));
     attr_set[dev] = true;
   }
+  const int smem = p.stages * p.stage_bytes + 1024;
   const unsigned grid = (unsigned)std::min(p.units, num_sms());
-  conv_wgrad_tc_kernel<<<grid, kWgThreads, smem, as_stream(stream)>>>(maps, p, dw);
-  RTSEG_LAUNCH_CHECK("conv_wgrad_tc_kernel");
+  for (int g0 = 0; g0 < groups_total; g0 += groups_per_launch) {   // more groups than tensor memory holds: several launches
+    p.ngroups = std::min(groups_per_launch, groups_total - g0);
+    for (int g = 0; g < 8; ++g) {
+      p.a_n[g] = 0, p.a_lbo16[g] = 0;
+      for (int b = 0; b < 8; ++b) p.tap_of_blk[g][b] = -1, p.ci_of_blk[g][b] = 0, p.a_map[g][b] = 0, p.a_c[g][b] = 0, p.a_dx[g][b] = 0, p.a_dy[g][b] = 0;
+    }
+    for (int g = 0; g < p.ngroups; ++g) {
+      const int first = (g0 + g) * per, cnt = std::min(per, nboxes - first);
+      p.a_n[g] = cnt;
+      p.a_lbo16[g] = cnt > 1 ? p.box_a >> 4 : 0;
+      for (int b = 0; b < cnt; ++b) {
+        const Box &bx = boxes[first + b];
+        p.a_map[g][b] = (short)bx.map, p.a_c[g][b] = (short)(d->x_coff + bx.ci), p.a_dx[g][b] = (short)bx.dx, p.a_dy[g][b] = (short)bx.dy;
+        p.tap_of_blk[g][b] = (short)bx.tap, p.ci_of_blk[g][b] = (short)bx.ci;
+      }
+    }
+    uint32_t cols = 32;
+    while (cols < (uint32_t)(p.ngroups * p.n)) cols <<= 1;
+    p.tmem_cols = (int)cols;
+    conv_wgrad_tc_kernel<<<grid, kWgThreads, smem, as_stream(stream)>>>(maps, p, dw);
+    RTSEG_LAUNCH_CHECK("conv_wgrad_tc_kernel");
+  }
   return RTSEG_OK;
 }

@@ -111,7 +111,7 @@ class _ConvFn(torch.autograd.Function):
             d = ConvDesc(n if not transposed else dy.shape[0], a.shape[2], a.shape[3], cin, cout, kh, kw, stride, dilation,
                          padding[0], padding[1], 1, ops._dtype_code(a.dtype), 0, 0.0, 0.0, 0, 0, cin, 0, cout, 0, 0, 0)
             acc = torch.zeros((kh, kw, cin, cout), dtype=torch.float32, device=x.device)
-            if WGRAD_TC and not transposed and lib.rtseg_conv_wgrad_tc_supported(C.byref(d)):
+            if WGRAD_TC and lib.rtseg_conv_wgrad_tc_supported(C.byref(d)):
                 _lib.check(lib.rtseg_conv_wgrad_tc(C.byref(d), a.data_ptr(), g.data_ptr(), acc.data_ptr(), ops._stream()),
                            "rtseg_conv_wgrad_tc")
             else:

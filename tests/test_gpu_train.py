@@ -270,5 +270,31 @@ def test_tcgen05_weight_gradient_matches_torch(c, kh, kw, dil, shape):
         out[name] = acc.permute(3, 2, 0, 1).cpu()
     assert ops.tc_timeout_flag() == 0
     assert rel_err(out["tc"], ref) < 1e-5 and rel_err(out["tc"], out["mma"]) < 1e-5
-    d.stride = 2
+    d.cin = 19
     assert lib.rtseg_conv_wgrad_tc_supported(ctypes.byref(d)) == 0     # anything else stays on the other kernels
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,shape", [(16, 48, 3, 2, (2, 32, 48)), (64, 64, 3, 2, (1, 40, 24)), (64, 128, 3, 2, (2, 16, 32)),
+                                                     (16, 64, 3, 2, (1, 64, 64)), (64, 32, 3, 1, (1, 24, 40)), (48, 16, 1, 1, (2, 9, 20))])
+def test_tcgen05_weight_gradient_strided_and_mixed_channels(cin, cout, k, stride, shape):
+    """The same kernel on the down-samplers (3x3 stride 2: parity views of the input), on the adjoint convolutions of
+    the transposed convs (64 -> 128, 16 -> 64), and on mixed block sizes (16-channel SWIZZLE_32B x, 64-channel dy ...);
+    nine taps x 128 output channels need two launches (tensor memory holds 512 columns)."""
+    import ctypes
+    from rtseg_b200 import _lib, ops
+    from rtseg_b200._lib import ConvDesc
+    lib = _lib.load()
+    n, h, w = shape
+    pad = (k - 1) // 2
+    x = seeded((n, cin, h, w), 92).to(torch.bfloat16)
+    ho, wo = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    dy = seeded((n, cout, ho, wo), 93).to(torch.bfloat16)
+    ref = torch.nn.grad.conv2d_weight(x.float(), (cout, cin, k, k), dy.float(), stride=stride, padding=pad)
+    xd = x.cuda().contiguous(memory_format=torch.channels_last)
+    gd = dy.cuda().contiguous(memory_format=torch.channels_last)
+    d = ConvDesc(n, h, w, cin, cout, k, k, stride, 1, pad, pad, 1, 1, 0, 0.0, 0.0, 0, 0, cin, 0, cout, 0, 0, 0)
+    assert lib.rtseg_conv_wgrad_tc_supported(ctypes.byref(d)) == 1
+    acc = torch.zeros((k, k, cin, cout), dtype=torch.float32, device="cuda")
+    _lib.check(lib.rtseg_conv_wgrad_tc(ctypes.byref(d), xd.data_ptr(), gd.data_ptr(), acc.data_ptr(), ops._stream()), "wgrad_tc")
+    assert ops.tc_timeout_flag() == 0
+    assert rel_err(acc.permute(3, 2, 0, 1).cpu(), ref) < 1e-5
