@@ -181,8 +181,10 @@ __device__ __forceinline__ void reduce2_vec(int64_t npix, int c, int ppb, double
     float a[V], b[V];
 #pragma unroll
     for (int e = 0; e < V; ++e) a[e] = b[e] = 0.f;
-    if (lane < lanes && cv < cvn)
-      for (int64_t p = p0 + lane; p < p1; p += lanes) f(p, cv * V, a, b);
+    if (lane < lanes && cv < cvn) {
+#pragma unroll 4
+      for (int64_t p = p0 + lane; p < p1; p += lanes) f(p, cv * V, a, b);   // unrolled: four pixels' loads in flight
+    }
     if (lane < lanes) {
 #pragma unroll
       for (int e = 0; e < V; ++e) sm[lane * width + cvl * V + e] = a[e], sm[(lanes + lane) * width + cvl * V + e] = b[e];
@@ -297,7 +299,7 @@ int reduce_geometry_vec(int64_t npix, int c, int V, int &ppb, unsigned &grid, si
   const int cvn = c / V;
   const int cb = cvn < 256 ? cvn : 256;
   const int lanes = 256 / cb;
-  ppb = 32 * lanes;  // 32 pixels x V channels per thread
+  ppb = 16 * lanes;  // 16 pixels x V channels per thread
   const int64_t blocks = cdiv(npix, ppb);
   if (blocks > INT32_MAX) return -1;
   grid = (unsigned)blocks;
