@@ -306,6 +306,18 @@ int rtseg_bn_act_bwd_apply(int64_t npix, int32_t c, int32_t dtype, const void *d
                            const float *invstd, const float *k, const float *mean_g, const float *mean_gx,
                            int32_t act, float act_p0, float act_p1, const float *slope, void *du, int32_t u_ctotal,
                            int32_t u_coff, rtseg_stream_t stream);
+/* The per-channel arithmetic between those passes, one launch each (nn.BatchNorm2d, torch/nn/modules/batchnorm.py
+ * semantics as called by models/modules.py:81): stats = [sum | sumsq] from rtseg_bn_stats; the element count comes
+ * from count_dev (a device double, e.g. all-reduced under SyncBatchNorm) or, when NULL, count_host.
+ * out (5*c floats) = [mean | invstd | scale | shift | gamma*invstd]; running statistics (optional) are updated in
+ * place with `momentum` and the unbiased variance. */
+int rtseg_bn_finalize(int32_t c, const double *stats, const double *count_dev, double count_host, const float *gamma,
+                      const float *beta, double eps, double momentum, float *running_mean, float *running_var,
+                      float *out, rtseg_stream_t stream);
+/* local_sums = this rank's [sum g | sum g*xhat] from rtseg_bn_act_bwd_reduce, global_sums = the same summed over
+ * ranks (the same pointer without SyncBatchNorm); out (4*c floats) = [mean g | mean g*xhat | dgamma | dbeta]. */
+int rtseg_bn_bwd_finalize(int32_t c, const double *local_sums, const double *global_sums, const double *count_dev,
+                          double count_host, float *out, rtseg_stream_t stream);
 /* Weight gradient of the dense convolution described by d (x: input slice, dy: gradient of the output slice
  * d->y_ctotal / d->y_coff): dw[kh][kw][cin][cout] (fp32, caller-zeroed) += sum over pixels. */
 int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);

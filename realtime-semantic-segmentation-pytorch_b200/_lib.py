@@ -84,6 +84,8 @@ PROTOTYPES = {
     "rtseg_bn_act_bwd_apply": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32,
                                        c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_f32, c_f32, c_vp, c_vp, c_i32, c_i32,
                                        c_vp]),
+    "rtseg_bn_finalize": (c_i32, [c_i32, c_vp, c_vp, C.c_double, c_vp, c_vp, C.c_double, C.c_double, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_bn_bwd_finalize": (c_i32, [c_i32, c_vp, c_vp, c_vp, C.c_double, c_vp, c_vp]),
     "rtseg_conv_wgrad": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_conv_wgrad_tc_supported": (c_i32, [_DP]),
     "rtseg_conv_wgrad_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),

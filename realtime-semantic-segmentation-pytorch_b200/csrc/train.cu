@@ -553,6 +553,45 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_vec_kernel(int n, int h,
   Vec16<T>::store(dx + (((int64_t)b * h + iy) * w + ix) * ds.ct + ds.co + c0, g);
 }
 
+// ---- the per-channel arithmetic between the reduction and the element-wise pass, one launch instead of ~20 tiny ones
+// stats = [sum | sumsq] (fp64); out = [mean | invstd | scale | shift | k] (fp32), k = gamma * invstd; running statistics
+// updated in place like nn.BatchNorm2d (momentum, unbiased variance).
+__global__ void bn_finalize_kernel(int c, const double *__restrict__ stats, const double *__restrict__ count_dev, double count_host,
+                                   const float *__restrict__ gamma, const float *__restrict__ beta, double eps, double momentum,
+                                   float *__restrict__ running_mean, float *__restrict__ running_var, float *__restrict__ out) {
+  const double count = count_dev ? *count_dev : count_host;
+  for (int ch = blockIdx.x * blockDim.x + threadIdx.x; ch < c; ch += gridDim.x * blockDim.x) {
+    const double mean = stats[ch] / count;
+    double var = stats[c + ch] / count - mean * mean;
+    var = var < 0.0 ? 0.0 : var;
+    const double invstd = rsqrt(var + eps);
+    const double g = gamma ? (double)gamma[ch] : 1.0, b = beta ? (double)beta[ch] : 0.0;
+    out[ch] = (float)mean;
+    out[c + ch] = (float)invstd;
+    out[2 * c + ch] = (float)(g * invstd);
+    out[3 * c + ch] = (float)(b - mean * g * invstd);
+    out[4 * c + ch] = (float)(g * invstd);
+    if (running_mean) {
+      const double unbiased = var * (count / (count > 1.0 ? count - 1.0 : 1.0));
+      running_mean[ch] = (float)((1.0 - momentum) * (double)running_mean[ch] + momentum * mean);
+      running_var[ch] = (float)((1.0 - momentum) * (double)running_var[ch] + momentum * unbiased);
+    }
+  }
+}
+
+// local = this rank's [sum g | sum g*xhat], global = the same summed over ranks (== local without SyncBatchNorm);
+// out = [mean g | mean g*xhat | dgamma | dbeta] (fp32): parameter gradients from the local sums (DDP averages them)
+__global__ void bn_bwd_finalize_kernel(int c, const double *__restrict__ local, const double *__restrict__ global_,
+                                       const double *__restrict__ count_dev, double count_host, float *__restrict__ out) {
+  const double count = count_dev ? *count_dev : count_host;
+  for (int ch = blockIdx.x * blockDim.x + threadIdx.x; ch < c; ch += gridDim.x * blockDim.x) {
+    out[ch] = (float)(global_[ch] / count);
+    out[c + ch] = (float)(global_[c + ch] / count);
+    out[2 * c + ch] = (float)local[c + ch];
+    out[3 * c + ch] = (float)local[ch];
+  }
+}
+
 int reduce_geometry(int64_t npix, int c, int &ppb, unsigned &grid, size_t &smem) {
   const int cb = c < 256 ? c : 256;
   const int lanes = 256 / cb;
@@ -725,5 +764,26 @@ extern "C" int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c
   RTSEG_BY_DTYPE(dtype, (maxpool3x3s2_bwd_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(n, h, w, c, ho, wo, (const T *)x, xs,
                                                                                           (const T *)dy, gs, (T *)dx, ds)));
   RTSEG_LAUNCH_CHECK("maxpool3x3s2_bwd_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_bn_finalize(int32_t c, const double *stats, const double *count_dev, double count_host, const float *gamma,
+                                 const float *beta, double eps, double momentum, float *running_mean, float *running_var,
+                                 float *out, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(stats && out && c > 0, "NULL pointer or non-positive channel count");
+  RTSEG_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "running_mean and running_var go together");
+  RTSEG_REQUIRE(count_dev || count_host > 0, "element count must be positive");
+  bn_finalize_kernel<<<(unsigned)cdiv(c, 256), 256, 0, as_stream(stream)>>>(c, stats, count_dev, count_host, gamma, beta, eps, momentum,
+                                                                         running_mean, running_var, out);
+  RTSEG_LAUNCH_CHECK("bn_finalize_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_bn_bwd_finalize(int32_t c, const double *local_sums, const double *global_sums, const double *count_dev,
+                                     double count_host, float *out, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(local_sums && global_sums && out && c > 0, "NULL pointer or non-positive channel count");
+  RTSEG_REQUIRE(count_dev || count_host > 0, "element count must be positive");
+  bn_bwd_finalize_kernel<<<(unsigned)cdiv(c, 256), 256, 0, as_stream(stream)>>>(c, local_sums, global_sums, count_dev, count_host, out);
+  RTSEG_LAUNCH_CHECK("bn_bwd_finalize_kernel");
   return RTSEG_OK;
 }

@@ -136,34 +136,57 @@ class _BNActFn(torch.autograd.Function):
         if post is not None or prelu_w is not None:
             raise NotImplementedError("training through glu / softmax / prelu blocks is not built")
         dev = y.device
-        s, sq = _channel_sums(y, c, res)
-        count = torch.full((1,), float(n * h * w), dtype=torch.float64, device=dev)   # fill kernel: capturable
+        lib = _lib.load()
+        npix = n * h * w
         sync = isinstance(bn, nn.SyncBatchNorm) and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        if sync:  # SyncBatchNorm (reference utils/parallel.py:29-32): statistics over every rank's pixels
-            packed = torch.cat([s, sq, count])
-            dist.all_reduce(packed)
-            s, sq, count = packed[:c], packed[c:2 * c], packed[2 * c:]
-        mean = s / count
-        var = (sq / count - mean * mean).clamp_(min=0.0)
-        with torch.no_grad():
-            if bn.track_running_stats and bn.running_mean is not None:
-                m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked + 1)
-                unbiased = var * (count / (count - 1).clamp_(min=1.0))
-                bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
-                bn.running_var.mul_(1 - m).add_(unbiased.to(bn.running_var.dtype), alpha=m)
-                bn.num_batches_tracked += 1
-        invstd = torch.rsqrt(var + bn.eps)
-        g64 = gamma.detach().double() if gamma is not None else torch.ones(c, dtype=torch.float64, device=dev)
-        b64 = beta.detach().double() if beta is not None else torch.zeros(c, dtype=torch.float64, device=dev)
-        scale = (g64 * invstd).float()
-        shift = (b64 - mean * g64 * invstd).float()
-        mean32, invstd32 = mean.float(), invstd.float()
+        # [sum | sumsq | count] in one fp64 buffer: one all-reduce under SyncBatchNorm (reference utils/parallel.py:29-32)
+        st64 = torch.zeros(2 * c + 1, dtype=torch.float64, device=dev)
+        _lib.check(lib.rtseg_bn_stats(npix, c, ops._dtype_code(y.dtype), y.data_ptr(), c, 0, ops._ptr(res),
+                                      c if res is not None else 0, 0, st64.data_ptr(), st64.data_ptr() + 8 * c, ops._stream()),
+                   "rtseg_bn_stats")
+        count = None
+        if sync:
+            st64[2 * c:].fill_(float(npix))
+            dist.all_reduce(st64)
+            count = st64[2 * c:]
+        running = bn.track_running_stats and bn.running_mean is not None
+        fast = (bn.momentum is not None and all(t is None or (t.dtype == torch.float32 and t.is_cuda and t.is_contiguous())
+                                                for t in (gamma, beta, bn.running_mean if running else None,
+                                                          bn.running_var if running else None)))
+        if fast:    # mean / invstd / scale / shift / running statistics in one launch
+            out32 = torch.empty(5 * c, dtype=torch.float32, device=dev)
+            _lib.check(lib.rtseg_bn_finalize(c, st64.data_ptr(), ops._ptr(count), float(npix), ops._ptr(gamma), ops._ptr(beta),
+                                             float(bn.eps), float(bn.momentum), ops._ptr(bn.running_mean) if running else None,
+                                             ops._ptr(bn.running_var) if running else None, out32.data_ptr(), ops._stream()),
+                       "rtseg_bn_finalize")
+            mean32, invstd32, scale, shift, kk = (out32[i * c:(i + 1) * c] for i in range(5))
+            if running:
+                with torch.no_grad():
+                    bn.num_batches_tracked += 1
+        else:
+            s_, sq = st64[:c], st64[c:2 * c]
+            cnt = count if sync else torch.full((1,), float(npix), dtype=torch.float64, device=dev)
+            mean = s_ / cnt
+            var = (sq / cnt - mean * mean).clamp_(min=0.0)
+            with torch.no_grad():
+                if running:
+                    m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked + 1)
+                    unbiased = var * (cnt / (cnt - 1).clamp_(min=1.0))
+                    bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
+                    bn.running_var.mul_(1 - m).add_(unbiased.to(bn.running_var.dtype), alpha=m)
+                    bn.num_batches_tracked += 1
+            invstd = torch.rsqrt(var + bn.eps)
+            g64 = gamma.detach().double() if gamma is not None else torch.ones(c, dtype=torch.float64, device=dev)
+            b64 = beta.detach().double() if beta is not None else torch.zeros(c, dtype=torch.float64, device=dev)
+            scale = (g64 * invstd).float()
+            shift = (b64 - mean * g64 * invstd).float()
+            mean32, invstd32, kk = mean.float(), invstd.float(), (g64 * invstd).float()
         z = torch.empty_like(y, memory_format=torch.channels_last)
         _lib.check(_lib.load().rtseg_affine_act(n * h * w, c, ops._dtype_code(y.dtype), y.data_ptr(), c, 0, ops._ptr(res),
                                                 c if res is not None else 0, 0, scale.data_ptr(), shift.data_ptr(), code,
                                                 p0, p1, None, z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
-        ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, (g64 * invstd).float())
-        ctx.meta = (code, p0, p1, sync, float(n * h * w) if not sync else None, count if sync else None,
+        ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, kk)
+        ctx.meta = (code, p0, p1, sync, float(npix) if not sync else None, count if sync else None,
                     gamma is not None, beta is not None, gamma.dtype if gamma is not None else torch.float32)
         return z
 
@@ -176,20 +199,21 @@ class _BNActFn(torch.autograd.Function):
         lib = _lib.load()
         dt, st = ops._dtype_code(y.dtype), ops._stream()
         rc = c if res is not None else 0
-        sg, sgx = _zeros64(c, y.device), _zeros64(c, y.device)
+        local = torch.zeros(2 * c, dtype=torch.float64, device=y.device)     # [sum g | sum g * xhat]
         _lib.check(lib.rtseg_bn_act_bwd_reduce(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
                                                scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(), code,
-                                               p0, p1, None, sg.data_ptr(), sgx.data_ptr(), st), "rtseg_bn_act_bwd_reduce")
-        dgamma = sgx.to(pdtype) if has_g else None      # this rank's sums: DDP averages parameter gradients itself
-        dbeta = sg.to(pdtype) if has_b else None
-        if sync:
-            packed = torch.cat([sg, sgx])
-            dist.all_reduce(packed)
-            sg, sgx = packed[:c], packed[c:]
-            m = count_t
-        else:
-            m = count_f
-        mg, mgx = (sg / m).float(), (sgx / m).float()
+                                               p0, p1, None, local.data_ptr(), local.data_ptr() + 8 * c, st), "rtseg_bn_act_bwd_reduce")
+        glob = local
+        if sync:     # the normalisation's own gradient needs the sums over every rank's pixels
+            glob = local.clone()
+            dist.all_reduce(glob)
+        out32 = torch.empty(4 * c, dtype=torch.float32, device=y.device)
+        _lib.check(lib.rtseg_bn_bwd_finalize(c, local.data_ptr(), glob.data_ptr(), ops._ptr(count_t), count_f or 0.0,
+                                             out32.data_ptr(), st), "rtseg_bn_bwd_finalize")
+        mg, mgx = out32[:c], out32[c:2 * c]
+        # parameter gradients from this rank's sums: DDP averages them itself
+        dgamma = out32[2 * c:3 * c].to(pdtype) if has_g else None
+        dbeta = out32[3 * c:].to(pdtype) if has_b else None
         du = torch.empty_like(y, memory_format=torch.channels_last)
         _lib.check(lib.rtseg_bn_act_bwd_apply(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
                                               scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
