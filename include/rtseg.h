@@ -219,7 +219,10 @@ int rtseg_confmat_update(int64_t npix, int32_t c, int32_t ignore_index, const vo
 
 /* ---- K12': OHEM cross entropy ---------------------------------------------
  * Replaces OhemCELoss.forward, core/loss.py:13-20.  logits are NCHW
- * (layout = 0, what the reference trainer passes) or NHWC (layout = 1),
+ * (layout = 0, what the reference trainer passes) or NHWC (layout = 1; with
+ * layout = 1 | pitch << 8 the pixels are `pitch` >= c elements apart: the
+ * classes are the first c channels of a wider, aligned buffer, and the
+ * gradient of rtseg_ohem_bwd has the same geometry with zeroed padding),
  * f32 or bf16; labels int64 [n][h][w].
  *   thresh      = -log(config.ohem_thrs) as fp32 (core/loss.py:9)
  *   loss_px     fp32 [n*h*w] scratch: per-pixel CE (0 where ignored)

@@ -57,7 +57,7 @@ __device__ __forceinline__ float logit_at(const T *base, int64_t cstride, int c)
 
 // pass 1 ------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) ohem_ce_kernel(int64_t npix, int c, int64_t hw, int layout,
+__global__ void __launch_bounds__(256) ohem_ce_kernel(int64_t npix, int c, int64_t hw, int layout, int pitch,
                                                       const T *__restrict__ logits, const int64_t *__restrict__ labels,
                                                       int ignore_index, float thresh, float *__restrict__ loss_px,
                                                       OhemWs *__restrict__ ws) {
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(256) ohem_ce_kernel(int64_t npix, int c, int64
         const int64_t b = pix / hw, s = pix % hw;
         base = logits + b * c * hw + s;
         cs = hw;
-      } else {  // NHWC
-        base = logits + pix * c;
+      } else {  // NHWC, pixels `pitch` elements apart (pitch >= c: a class map inside a wider, aligned buffer)
+        base = logits + pix * pitch;
         cs = 1;
       }
       float m = -FLT_MAX;
@@ -219,7 +219,7 @@ __global__ void ohem_finalize_kernel(OhemWs *ws, float *out) {
 
 // backward ------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) ohem_bwd_kernel(int64_t npix, int c, int64_t hw, int layout,
+__global__ void __launch_bounds__(256) ohem_bwd_kernel(int64_t npix, int c, int64_t hw, int layout, int pitch,
                                                        const T *__restrict__ logits, const int64_t *__restrict__ labels,
                                                        int ignore_index, const float *__restrict__ loss_px,
                                                        const OhemWs *__restrict__ ws, const float *__restrict__ grad_out,
@@ -235,9 +235,10 @@ __global__ void __launch_bounds__(256) ohem_bwd_kernel(int64_t npix, int c, int6
     gbase = grad + b * c * hw + s;
     cs = hw;
   } else {
-    base = logits + pix * c;
-    gbase = grad + pix * c;
+    base = logits + pix * pitch;
+    gbase = grad + pix * pitch;
     cs = 1;
+    for (int k = c; k < pitch; ++k) st_f<T>(gbase + k, 0.f);  // the padding channels carry no gradient
   }
   const int64_t lab = __ldg(labels + pix);
   float wgt = 0.f;
@@ -280,7 +281,10 @@ extern "C" int rtseg_ohem_fwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_
                               float *loss_px, void *workspace, float *out, rtseg_stream_t stream) {
   RTSEG_REQUIRE(logits && labels && loss_px && workspace && out, "NULL pointer");
   RTSEG_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0, "non-positive extent");
-  RTSEG_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (NCHW) or 1 (NHWC)");
+  const int pitch = (layout >> 8) ? (layout >> 8) : c;   // NHWC pixel pitch in elements, encoded as layout = 1 | pitch << 8
+  layout &= 0xff;
+  RTSEG_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (NCHW) or 1 (NHWC, optionally | pitch << 8)");
+  RTSEG_REQUIRE(pitch >= c && (layout == 1 || pitch == c), "pixel pitch must be >= c and needs the NHWC layout");
   RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(workspace) % 8 == 0, "workspace must be 8-byte aligned");
   cudaStream_t st = as_stream(stream);
   OhemWs *ws = static_cast<OhemWs *>(workspace);
@@ -288,10 +292,10 @@ extern "C" int rtseg_ohem_fwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_
   RTSEG_CUDA(cudaMemsetAsync(ws, 0, sizeof(OhemWs), st));
   const unsigned grid = (unsigned)std::min<int64_t>(cdiv(npix, 256), (int64_t)num_sms() * 16);
   if (dtype == RTSEG_BF16)
-    ohem_ce_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, hw, layout, (const __nv_bfloat16 *)logits, labels,
+    ohem_ce_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, hw, layout, pitch, (const __nv_bfloat16 *)logits, labels,
                                                         ignore_index, thresh, loss_px, ws);
   else if (dtype == RTSEG_F32)
-    ohem_ce_kernel<float><<<grid, 256, 0, st>>>(npix, c, hw, layout, (const float *)logits, labels, ignore_index,
+    ohem_ce_kernel<float><<<grid, 256, 0, st>>>(npix, c, hw, layout, pitch, (const float *)logits, labels, ignore_index,
                                                 thresh, loss_px, ws);
   else
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
@@ -320,16 +324,19 @@ extern "C" int rtseg_ohem_bwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_
                               rtseg_stream_t stream) {
   RTSEG_REQUIRE(logits && labels && loss_px && workspace && grad_out && grad_logits, "NULL pointer");
   RTSEG_REQUIRE(n > 0 && c > 0 && h > 0 && w > 0, "non-positive extent");
-  RTSEG_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (NCHW) or 1 (NHWC)");
+  const int pitch = (layout >> 8) ? (layout >> 8) : c;   // NHWC pixel pitch in elements, encoded as layout = 1 | pitch << 8
+  layout &= 0xff;
+  RTSEG_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (NCHW) or 1 (NHWC, optionally | pitch << 8)");
+  RTSEG_REQUIRE(pitch >= c && (layout == 1 || pitch == c), "pixel pitch must be >= c and needs the NHWC layout");
   cudaStream_t st = as_stream(stream);
   const OhemWs *ws = static_cast<const OhemWs *>(workspace);
   const int64_t hw = (int64_t)h * w, npix = (int64_t)n * hw;
   const unsigned grid = (unsigned)cdiv(npix, 256);
   if (dtype == RTSEG_BF16)
-    ohem_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, hw, layout, (const __nv_bfloat16 *)logits, labels,
+    ohem_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, hw, layout, pitch, (const __nv_bfloat16 *)logits, labels,
                                                          ignore_index, loss_px, ws, grad_out, (__nv_bfloat16 *)grad_logits);
   else if (dtype == RTSEG_F32)
-    ohem_bwd_kernel<float><<<grid, 256, 0, st>>>(npix, c, hw, layout, (const float *)logits, labels, ignore_index,
+    ohem_bwd_kernel<float><<<grid, 256, 0, st>>>(npix, c, hw, layout, pitch, (const float *)logits, labels, ignore_index,
                                                  loss_px, ws, grad_out, (float *)grad_logits);
   else
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");

@@ -13,10 +13,15 @@ class _OhemFunction(torch.autograd.Function):
         ops._require_cuda(logits, "OhemCELoss")
         if logits.dtype not in (torch.float32, torch.bfloat16):
             logits = logits.float()  # fp16 autocast outputs: CE is an fp32 op under autocast anyway
+        n_, c_, h_, w_ = logits.shape
+        pitch = logits.stride(3) if logits.dim() == 4 else 0
         if logits.is_contiguous():
             layout = 0
         elif ops.is_nhwc(logits):
             layout = 1
+        elif (logits.stride(1) == 1 and pitch > c_ and logits.stride(2) == w_ * pitch and logits.stride(0) == h_ * w_ * pitch
+              and pitch < (1 << 20)):
+            layout = 1 | (pitch << 8)   # the first c channels of a wider (16-byte aligned) NHWC buffer, read in place
         else:
             logits, layout = logits.contiguous(), 0
         if labels.dtype != torch.int64:
@@ -43,7 +48,11 @@ class _OhemFunction(torch.autograd.Function):
         logits, labels, loss_px, ws = ctx.saved_tensors
         layout, ignore_index = ctx.meta
         n, c, h, w = logits.shape
-        grad = torch.empty_like(logits)  # preserves the NCHW / channels_last layout
+        if layout >> 8:   # same padded NHWC geometry as the logits; the kernel zeroes the padding channels
+            pitch = layout >> 8
+            grad = torch.empty((n, h, w, pitch), dtype=logits.dtype, device=logits.device).permute(0, 3, 1, 2)[:, :c]
+        else:
+            grad = torch.empty_like(logits)  # preserves the NCHW / channels_last layout
         g = grad_out.detach().to(device=logits.device, dtype=torch.float32).reshape(1).contiguous()
         _lib.check(_lib.load().rtseg_ohem_bwd(n, c, h, w, layout, ops._dtype_code(logits.dtype), logits.data_ptr(),
                                               labels.data_ptr(), ignore_index, loss_px.data_ptr(), ws.data_ptr(),

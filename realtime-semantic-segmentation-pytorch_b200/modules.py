@@ -262,7 +262,7 @@ class DeConvBNAct(nn.Module):
     def forward(self, x, labels=None, want_logits=True):
         if self.up_conv[1].training and labels is None:
             from . import train
-            return train.conv_bn_act(self.up_conv, x)
+            return train.conv_bn_act_aligned(self.up_conv, x)   # == conv_bn_act unless cout needs channel padding
         _check_eval(self, self.up_conv[1])
         folded, post = self._folded()
         y = ops.conv(folded, ops.to_nhwc(x), labels=labels, want_logits=want_logits)

@@ -138,7 +138,8 @@ class _BNActFn(torch.autograd.Function):
         dev = y.device
         lib = _lib.load()
         npix = n * h * w
-        sync = isinstance(bn, nn.SyncBatchNorm) and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        sync = (getattr(bn, "rtseg_sync", isinstance(bn, nn.SyncBatchNorm)) and dist.is_available() and dist.is_initialized()
+                and dist.get_world_size() > 1)
         # [sum | sumsq | count] in one fp64 buffer: one all-reduce under SyncBatchNorm (reference utils/parallel.py:29-32)
         st64 = torch.zeros(2 * c + 1, dtype=torch.float64, device=dev)
         _lib.check(lib.rtseg_bn_stats(npix, c, ops._dtype_code(y.dtype), y.data_ptr(), c, 0, ops._ptr(res),
@@ -269,3 +270,69 @@ def conv_bn_act(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
 
 def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
     return _MaxPoolFn.apply(x)
+
+
+class _FirstChannelsFn(torch.autograd.Function):
+    """z[:, :c] of a channel-padded NHWC tensor as a VIEW; the gradient comes back as the padded buffer itself when the
+    consumer (OhemCELoss) produced it in the same padded geometry — no zero-fill + copy of a full-resolution tensor."""
+
+    @staticmethod
+    def forward(ctx, z, c):
+        ctx.shape = tuple(z.shape)
+        return z[:, :c]
+
+    @staticmethod
+    def backward(ctx, g):
+        n, cp, h, w = ctx.shape
+        if (g.dim() == 4 and g.stride(1) == 1 and g.stride(3) == cp and g.stride(2) == w * cp and g.stride(0) == h * w * cp
+                and g.storage_offset() == 0 and g.untyped_storage().nbytes() >= n * h * w * cp * g.element_size()):
+            return torch.as_strided(g, (n, cp, h, w), (h * w * cp, 1, w * cp, cp)), None   # padding already zero
+        full = torch.zeros((n, cp, h, w), dtype=g.dtype, device=g.device).contiguous(memory_format=torch.channels_last)
+        full[:, :g.shape[1]] = g
+        return full, None
+
+
+class _PaddedBN:
+    """BatchNorm2d stand-in with `pad` extra channels (weight 1, bias 0): what _BNActFn needs, running statistics copied back."""
+
+    def __init__(self, bn, pad):
+        self.bn, self.pad = bn, pad
+        self.eps, self.momentum, self.track_running_stats = bn.eps, bn.momentum, bn.track_running_stats
+        self.rtseg_sync = isinstance(bn, nn.SyncBatchNorm)
+        dev = bn.weight.device
+        self.running_mean = self.running_var = None
+        if bn.running_mean is not None:
+            self.running_mean = torch.cat([bn.running_mean.detach().float(), torch.zeros(pad, device=dev)])
+            self.running_var = torch.cat([bn.running_var.detach().float(), torch.ones(pad, device=dev)])
+        self.num_batches_tracked = bn.num_batches_tracked
+        self.weight = torch.cat([bn.weight, torch.ones(pad, device=dev, dtype=bn.weight.dtype)])
+        self.bias = torch.cat([bn.bias, torch.zeros(pad, device=dev, dtype=bn.bias.dtype)])
+
+    def commit(self):
+        if self.running_mean is not None:
+            c = self.bn.running_mean.numel()
+            with torch.no_grad():
+                self.bn.running_mean.copy_(self.running_mean[:c])
+                self.bn.running_var.copy_(self.running_var[:c])
+
+
+def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
+    """conv_bn_act for an output channel count that is not a multiple of 16 (the 19-class logits layer) on bf16
+    activations: the layer is run as if it had ceil16(cout) outputs — zero weights, BatchNorm weight 1 / bias 0 for the
+    extra channels — so that forward, data gradient, weight gradient and the BatchNorm passes all take the aligned
+    (tensor-core / vector) kernels; the result is the first cout channels of that buffer, as a view."""
+    import torch.nn.functional as F
+    conv, bn, act = seq[0], seq[1], seq[2].activation
+    cout = conv.out_channels
+    cp = (cout + 15) // 16 * 16
+    transposed = bool(getattr(conv, "transposed", False))
+    if cp == cout or x.dtype != torch.bfloat16 or conv.groups != 1 or bn.weight is None or bn.bias is None:
+        return conv_bn_act(seq, x)
+    pad = cp - cout
+    w_p = F.pad(conv.weight, (0, 0, 0, 0, 0, pad) if transposed else (0, 0, 0, 0, 0, 0, 0, pad))
+    b_p = F.pad(conv.bias, (0, pad)) if conv.bias is not None else None
+    y = _ConvFn.apply(x, w_p, b_p, conv.stride[0], conv.dilation[0], tuple(conv.padding), transposed)
+    pbn = _PaddedBN(bn, pad)
+    z = _BNActFn.apply(y, None, pbn.weight, pbn.bias, pbn, act)
+    pbn.commit()
+    return _FirstChannelsFn.apply(z, cout)

@@ -298,3 +298,26 @@ def test_tcgen05_weight_gradient_strided_and_mixed_channels(cin, cout, k, stride
     _lib.check(lib.rtseg_conv_wgrad_tc(ctypes.byref(d), xd.data_ptr(), gd.data_ptr(), acc.data_ptr(), ops._stream()), "wgrad_tc")
     assert ops.tc_timeout_flag() == 0
     assert rel_err(acc.permute(3, 2, 0, 1).cpu(), ref) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_ohem_reads_class_maps_inside_a_padded_buffer(dtype):
+    """Training keeps the 19-class logits as the first channels of a 32-channel (16-byte aligned) NHWC buffer;
+    OhemCELoss must read them in place and return a gradient in the same geometry: identical loss and gradient."""
+    from rtseg_b200 import loss as rloss
+    g = torch.Generator().manual_seed(21)
+    logits = torch.randn((2, 19, 24, 40), generator=g).to(dtype)
+    labels = torch.randint(0, 19, (2, 24, 40), generator=g)
+    labels[torch.rand((2, 24, 40), generator=g) < 0.1] = 255
+    dense = logits.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    buf = torch.full((2, 24, 40, 32), float("nan"), dtype=dtype, device="cuda")     # poison: the padding must never be read
+    buf[..., :19] = logits.cuda().permute(0, 2, 3, 1)
+    padded = buf.permute(0, 3, 1, 2)[:, :19].requires_grad_(True)
+    assert not padded.is_contiguous() and not padded.is_contiguous(memory_format=torch.channels_last)
+    crit = rloss.OhemCELoss(0.7, 255)
+    l0 = crit(dense, labels.cuda())
+    l0.backward()
+    l1 = crit(padded, labels.cuda())
+    l1.backward()
+    assert l0.item() == l1.item()
+    assert torch.equal(dense.grad, padded.grad)
