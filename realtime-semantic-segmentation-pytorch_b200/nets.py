@@ -61,7 +61,8 @@ class InitialBlock(nn.Module):
         if self.conv[1].training and out is None and x.shape[1] == cin:
             from . import train   # training: conv branch and pool branch are tape nodes; the cat is a copy
             xn = ops.to_nhwc(x, self.act_dtype or (x.dtype if x.is_cuda and ops.is_nhwc(x) else _param_dtype(self.conv)))
-            return ops.to_nhwc(torch.cat([train.conv_bn_act(self.conv, xn), train.maxpool3x3s2(xn)], dim=1))
+            conv_out = train.conv_bn_act_aligned(self.conv, xn, pad_input=True) if cin <= 4 else train.conv_bn_act(self.conv, xn)
+            return ops.to_nhwc(torch.cat([conv_out, train.maxpool3x3s2(xn)], dim=1))
         _check_eval(self, self.conv[1])
         folded, post = self.conv._folded()
         if post is not None:

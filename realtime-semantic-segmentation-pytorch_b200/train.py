@@ -316,7 +316,7 @@ class _PaddedBN:
                 self.bn.running_var.copy_(self.running_var[:c])
 
 
-def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
+def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor, pad_input: bool = False) -> torch.Tensor:
     """conv_bn_act for an output channel count that is not a multiple of 16 (the 19-class logits layer) on bf16
     activations: the layer is run as if it had ceil16(cout) outputs — zero weights, BatchNorm weight 1 / bias 0 for the
     extra channels — so that forward, data gradient, weight gradient and the BatchNorm passes all take the aligned
@@ -329,7 +329,16 @@ def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
     if cp == cout or x.dtype != torch.bfloat16 or conv.groups != 1 or bn.weight is None or bn.bias is None:
         return conv_bn_act(seq, x)
     pad = cp - cout
-    w_p = F.pad(conv.weight, (0, 0, 0, 0, 0, pad) if transposed else (0, 0, 0, 0, 0, 0, 0, pad))
+    cin_pad = 0
+    if pad_input and not transposed and conv.in_channels % 16:
+        # the image stem: 3 input channels become 16 (zero channels, zero weights) so that the forward and the weight
+        # gradient run on the tensor cores instead of the 3-channel catch-all kernels
+        cin_pad = (conv.in_channels + 15) // 16 * 16 - conv.in_channels
+        xp = torch.zeros((x.shape[0], conv.in_channels + cin_pad, x.shape[2], x.shape[3]), dtype=x.dtype,
+                         device=x.device).contiguous(memory_format=torch.channels_last)
+        xp[:, :conv.in_channels] = x
+        x = xp
+    w_p = F.pad(conv.weight, (0, 0, 0, 0, 0, pad) if transposed else (0, 0, 0, 0, 0, cin_pad, 0, pad))
     b_p = F.pad(conv.bias, (0, pad)) if conv.bias is not None else None
     y = _ConvFn.apply(x, w_p, b_p, conv.stride[0], conv.dilation[0], tuple(conv.padding), transposed)
     pbn = _PaddedBN(bn, pad)

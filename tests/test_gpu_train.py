@@ -107,7 +107,7 @@ def test_non_bt_1d_training_step(channels, dil, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("cin,cout", [(16, 64), (64, 128)])
+@pytest.mark.parametrize("cin,cout", [(16, 64), (64, 128), (3, 16)])
 def test_initial_block_training_step(cin, cout, dtype):
     from rtseg_b200 import nets
     m = _randomise(nets.InitialBlock(cin, cout, "relu"), 76)
