@@ -207,9 +207,14 @@ def test_ddp_syncbn_matches_oracle_on_the_joint_batch(tmp_path):
     import sys
     out = tmp_path / "ddp.json"
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    import socket
+    with socket.socket() as sock:       # a free rendezvous port (a fixed one may still be in TIME_WAIT from an earlier run)
+        sock.bind(("127.0.0.1", 0))
+        port = sock.getsockname()[1]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", "29533", os.path.join(root, "tests", "_ddp_worker.py"), str(out)]
-    subprocess.run(cmd, check=True, timeout=300, cwd=root)
+           "--master-port", str(port), os.path.join(root, "tests", "_ddp_worker.py"), str(out)]
+    run = subprocess.run(cmd, timeout=300, cwd=root, capture_output=True, text=True)
+    assert run.returncode == 0, "torchrun worker failed:\n" + (run.stdout + run.stderr)[-3000:]
     got = json.load(open(out))
     spec = load_specs()["erfnet"]["spec"]
     sd0 = ref_nets.make_state(spec, 3, True)
