@@ -307,38 +307,43 @@ def measured_peak():
 
 # ------------------------------------------------------------------- training workload ----
 def wgrad_roofline(model, batch, size, peak_gbs, peak_src):
-    """One eager forward + backward with every rtseg_conv_wgrad launch (the dominant kernel of the training step)
-    bracketed by CUDA events on its stream; achieved = sum of algorithmic bytes / sum of durations."""
-    import ctypes
+    """One eager forward + backward with the launches of the step's two big kernel families — the BatchNorm backward
+    passes (reduce + apply) and the weight gradients — bracketed by CUDA events on their stream; the family with the
+    larger share of the time is reported: achieved = sum of its algorithmic bytes / sum of its durations."""
     import torch
     from rtseg_b200 import _lib
     from rtseg_b200 import loss as rloss
 
     lib = _lib.load()
-    origs = {"rtseg_conv_wgrad": lib.rtseg_conv_wgrad, "rtseg_conv_wgrad_tc": lib.rtseg_conv_wgrad_tc}
     stream = torch.cuda.current_stream()
     rec = []
 
-    def make_timed(name):
-        orig = origs[name]
-
-        def timed(dref, a, g, acc, st):
-            return _timed(orig, name, dref, a, g, acc, st)
-        return timed
-
-    def _timed(orig, name, dref, a, g, acc, st):
-        d = ctypes.cast(dref, ctypes.POINTER(_lib.ConvDesc)).contents if not hasattr(dref, "_obj") else dref._obj
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        rc = orig(dref, a, g, acc, st)
-        e1.record(stream)
-        e1.synchronize()
+    def conv_bytes(a):
+        d = a[0]._obj
         gh = (d.h + 2 * d.pad_h - d.dil * (d.kh - 1) - 1) // d.stride + 1
         gw = (d.w + 2 * d.pad_w - d.dil * (d.kw - 1) - 1) // d.stride + 1
         es = 2 if d.dtype == 1 else 4
-        rec.append((e0.elapsed_time(e1), (d.n * d.h * d.w * d.cin + d.n * gh * gw * d.cout) * es + d.kh * d.kw * d.cin * d.cout * 4,
-                    name))
-        return rc
+        return (d.n * d.h * d.w * d.cin + d.n * gh * gw * d.cout) * es + d.kh * d.kw * d.cin * d.cout * 4
+
+    def bn_bytes(extra):   # args: npix, c, dtype, dz, .., .., y, .., .., res, ...: dz + y (+ res) read, `extra` tensors written
+        return lambda a: a[0] * a[1] * (2 if a[2] == 1 else 4) * (2 + (1 if a[9] else 0) + extra)
+
+    fams = {"rtseg_conv_wgrad": ("wgrad", conv_bytes), "rtseg_conv_wgrad_tc": ("wgrad", conv_bytes),
+            "rtseg_bn_act_bwd_reduce": ("bn_bwd", bn_bytes(0)), "rtseg_bn_act_bwd_apply": ("bn_bwd", bn_bytes(1))}
+    origs = {name: getattr(lib, name) for name in fams}
+
+    def make_timed(name):
+        orig, (fam, nbytes) = origs[name], fams[name]
+
+        def timed(*a):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            rc = orig(*a)
+            e1.record(stream)
+            e1.synchronize()
+            rec.append((fam, name, e0.elapsed_time(e1), nbytes(a)))
+            return rc
+        return timed
 
     m = model.module if hasattr(model, "module") else model
     x = torch.randn((batch, 3, size, size), device="cuda")
@@ -352,18 +357,25 @@ def wgrad_roofline(model, batch, size, peak_gbs, peak_src):
         for name, fn in origs.items():
             setattr(lib, name, fn)
     m.zero_grad(set_to_none=True)
-    ms, by = sum(r[0] for r in rec), sum(r[1] for r in rec)
+    tot = {}
+    for fam, name, ms, by in rec:
+        t = tot.setdefault(fam, [0.0, 0.0, 0])
+        t[0] += ms
+        t[1] += by
+        t[2] += 1
+    top = max(tot, key=lambda k: tot[k][0])
+    ms, by, cnt = tot[top]
     achieved = by / (ms * 1e-3) / 1e9
-    tc = [r for r in rec if r[2] == "rtseg_conv_wgrad_tc"]
-    tc_ms, tc_by = sum(r[0] for r in tc), sum(r[1] for r in tc)
-    return {"bound": "hbm", "kernel": "weight-gradient kernels — the largest kernel family of the step: conv_wgrad_tc_kernel "
-                                      f"(tcgen05, MN-major operands, TMEM-resident accumulators; {len(tc)} launches, {tc_ms:.2f} ms, "
-                                      f"{tc_by / max(tc_ms, 1e-9) / 1e6:.0f} GB/s) + conv_wgrad_wmma_kernel (mma.sync; 16-channel, "
-                                      "strided and transposed layers)",
+    label = {"bn_bwd": "bn_act_bwd_reduce_vec_kernel + bn_act_bwd_apply_vec_kernel (BatchNorm + activation backward: one "
+                       "reduction and one apply pass over dz, y [, res])",
+             "wgrad": "conv_wgrad_tc_kernel (tcgen05 weight gradient, MN-major operands, TMEM-resident accumulators)"}[top]
+    others = "; ".join(f"{k}: {v[2]} launches, {v[0]:.2f} ms, {v[1] / max(v[0], 1e-9) / 1e6:.0f} GB/s" for k, v in sorted(tot.items()))
+    return {"bound": "hbm", "kernel": label + " — the largest kernel family of the step",
             "achieved": round(achieved, 1), "peak": peak_gbs, "unit": "GB/s", "frac": round(achieved / peak_gbs, 4),
-            "traffic": None, "peak_source": peak_src, "launches_per_step": len(rec), "bytes_per_step": int(by),
-            "ms_per_step": round(ms, 4),
-            "note": "algorithmic bytes = x + dy read once + fp32 dW"}
+            "traffic": None, "peak_source": peak_src, "launches_per_step": cnt, "bytes_per_step": int(by),
+            "ms_per_step": round(ms, 4), "families": others,
+            "note": "algorithmic bytes: BatchNorm backward = dz + y (+ res) read per pass, du written by the apply pass; "
+                    "weight gradient = x + dy read once + fp32 dW"}
 
 
 def train_main(args, rank, local_rank, world, batch, workload_name, metric):
