@@ -270,6 +270,69 @@ __global__ void __launch_bounds__(256) ohem_bwd_kernel(int64_t npix, int c, int6
   }
 }
 
+// bf16 NHWC class maps whose pixels are 16-byte aligned (pitch % 8 == 0, e.g. 19 classes in a pitch-32 buffer): the
+// whole pixel is read and written as 16-byte vectors, same arithmetic (and order) as ohem_bwd_kernel.
+template <int CP>  // CP = pitch, a multiple of 8, <= 32
+__global__ void __launch_bounds__(256) ohem_bwd_nhwc_vec_kernel(int64_t npix, int c, const __nv_bfloat16 *__restrict__ logits,
+                                                                const int64_t *__restrict__ labels, int ignore_index,
+                                                                const float *__restrict__ loss_px, const OhemWs *__restrict__ ws,
+                                                                const float *__restrict__ grad_out, __nv_bfloat16 *__restrict__ grad) {
+  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= npix) return;
+  const int64_t lab = __ldg(labels + pix);
+  float wgt = 0.f;
+  if (lab != (int64_t)ignore_index) {
+    const float loss = loss_px[pix];
+    if (ws->branch == 0) {
+      wgt = loss > ws->thresh ? 1.f / (float)ws->n_hard : 0.f;
+    } else {
+      const unsigned int key = loss_key(loss);
+      if (key > ws->kth_key)
+        wgt = 1.f / (float)ws->k;
+      else if (key == ws->kth_key)
+        wgt = (float)((double)ws->need_eq / (double)ws->count_eq / (double)ws->k);
+    }
+  }
+  wgt *= __ldg(grad_out);
+  uint4 *gp = reinterpret_cast<uint4 *>(grad + pix * CP);
+  if (wgt == 0.f) {
+#pragma unroll
+    for (int q = 0; q < CP / 8; ++q) gp[q] = make_uint4(0, 0, 0, 0);
+    return;
+  }
+  float x[CP];
+  const uint4 *lp = reinterpret_cast<const uint4 *>(logits + pix * CP);
+#pragma unroll
+  for (int q = 0; q < CP / 8; ++q) {
+    const uint4 t = __ldg(lp + q);
+    const uint32_t w4[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[q * 8 + 2 * i] = __uint_as_float(w4[i] << 16), x[q * 8 + 2 * i + 1] = __uint_as_float(w4[i] & 0xffff0000u);
+  }
+  float m = -FLT_MAX;
+#pragma unroll
+  for (int k = 0; k < CP; ++k)
+    if (k < c) m = fmaxf(m, x[k]);
+  float sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < CP; ++k)
+    if (k < c) sum += expf(x[k] - m);
+  const float inv = 1.f / sum;
+  float g[CP];
+#pragma unroll
+  for (int k = 0; k < CP; ++k) g[k] = k < c ? (expf(x[k] - m) * inv - (k == (int)lab ? 1.f : 0.f)) * wgt : 0.f;
+#pragma unroll
+  for (int q = 0; q < CP / 8; ++q) {
+    uint32_t o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(g[q * 8 + 2 * i], g[q * 8 + 2 * i + 1]);
+      o[i] = *reinterpret_cast<const uint32_t *>(&h);
+    }
+    gp[q] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 }  // namespace rtseg
 
 using namespace rtseg;
@@ -332,6 +395,17 @@ extern "C" int rtseg_ohem_bwd(int32_t n, int32_t c, int32_t h, int32_t w, int32_
   const OhemWs *ws = static_cast<const OhemWs *>(workspace);
   const int64_t hw = (int64_t)h * w, npix = (int64_t)n * hw;
   const unsigned grid = (unsigned)cdiv(npix, 256);
+  if (dtype == RTSEG_BF16 && layout == 1 && (pitch == 24 || pitch == 32) && reinterpret_cast<uintptr_t>(logits) % 16 == 0 &&
+      reinterpret_cast<uintptr_t>(grad_logits) % 16 == 0) {
+    if (pitch == 32)
+      ohem_bwd_nhwc_vec_kernel<32><<<grid, 256, 0, st>>>(npix, c, (const __nv_bfloat16 *)logits, labels, ignore_index, loss_px, ws,
+                                                         grad_out, (__nv_bfloat16 *)grad_logits);
+    else
+      ohem_bwd_nhwc_vec_kernel<24><<<grid, 256, 0, st>>>(npix, c, (const __nv_bfloat16 *)logits, labels, ignore_index, loss_px, ws,
+                                                         grad_out, (__nv_bfloat16 *)grad_logits);
+    RTSEG_LAUNCH_CHECK("ohem_bwd_nhwc_vec_kernel");
+    return RTSEG_OK;
+  }
   if (dtype == RTSEG_BF16)
     ohem_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(npix, c, hw, layout, pitch, (const __nv_bfloat16 *)logits, labels,
                                                          ignore_index, loss_px, ws, grad_out, (__nv_bfloat16 *)grad_logits);
