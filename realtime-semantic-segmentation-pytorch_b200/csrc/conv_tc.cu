@@ -248,11 +248,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           tma_load_2d(s_b + (uint32_t)(t * p.nkb + kb) * p.b_block_bytes, &maps.b, b_bar, kb * KB,
                       t * p.cout_pad + co_base);
       uint32_t stage = 0, phase = 0;
-      for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
-        const int twi = (int)(tile % p.tiles_w);
-        const int64_t r = tile / p.tiles_w;
-        const int thi = (int)(r % p.tiles_h);
-        const int img = (int)(r / p.tiles_h);
+      // tile -> (image, tile row, tile column), advanced by the decomposed grid stride: no division per tile
+      const int64_t r0 = (int64_t)blockIdx.x / p.tiles_w, rs = (int64_t)gridDim.x / p.tiles_w;
+      int twi = (int)((int64_t)blockIdx.x % p.tiles_w), thi = (int)(r0 % p.tiles_h), img = (int)(r0 / p.tiles_h);
+      const int step_w = (int)((int64_t)gridDim.x % p.tiles_w), step_h = (int)(rs % p.tiles_h), step_n = (int)(rs / p.tiles_h);
+      auto next_tile = [&]() {
+        twi += step_w;
+        if (twi >= p.tiles_w) twi -= p.tiles_w, ++thi;
+        thi += step_h;
+        if (thi >= p.tiles_h) thi -= p.tiles_h, ++img;
+        img += step_n;
+      };
+      for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x, next_tile()) {
         const int w0 = twi * unit_w, h0 = thi * unit_h;
         if (p.a_share) {
           for (int kb = 0; kb < p.nkb; ++kb) {
