@@ -34,6 +34,24 @@ struct DwTmaParams {
 };
 
 // S = stride, CB = channels per block (CB*2 bytes per pixel row in the tile), TH x TW = output tile
+// Persistent-CTA tile walk: (image, tile row, tile column) of tile blockIdx.x + k * gridDim.x, advanced by the
+// decomposed grid stride so that the tile loop has no division.
+struct TileWalk {
+  int twi, thi, img, sw, sh, sn, tiles_w, tiles_h;
+  __device__ TileWalk(int tiles_w_, int tiles_h_) : tiles_w(tiles_w_), tiles_h(tiles_h_) {
+    const int r0 = (int)blockIdx.x / tiles_w, rs = (int)gridDim.x / tiles_w;
+    twi = (int)blockIdx.x % tiles_w, thi = r0 % tiles_h, img = r0 / tiles_h;
+    sw = (int)gridDim.x % tiles_w, sh = rs % tiles_h, sn = rs / tiles_h;
+  }
+  __device__ __forceinline__ void next() {
+    twi += sw;
+    if (twi >= tiles_w) twi -= tiles_w, ++thi;
+    thi += sh;
+    if (thi >= tiles_h) thi -= tiles_h, ++img;
+    img += sn;
+  }
+};
+
 template <int S, int CB, int TH, int TW, int MODE>
 __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_constant__ CUtensorMap xmap,
                                                               const DwTmaParams p,
@@ -73,11 +91,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
     if (lane == 0) {
       prefetch_tmap(&xmap);
       uint32_t stage = 0, phase = 0;
-      for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int twi = (int)(tile % p.tiles_w);
-        const int64_t r = tile / p.tiles_w;
-        const int thi = (int)(r % p.tiles_h);
-        const int img = (int)(r / p.tiles_h);
+      TileWalk tw(p.tiles_w, p.tiles_h);
+      for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, tw.next()) {
+        const int twi = tw.twi, thi = tw.thi, img = tw.img;
         mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
         mbar_expect_tx(full_bar + 8 * stage, kStageBytes);
         tma_load_4d(s_base + stage * kStagePitch, &xmap, full_bar + 8 * stage, p.x_coff + cblk * CB, twi * TW * S - 1,
@@ -110,11 +126,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
 
   const uint32_t lane_off = (uint32_t)(tr * S * TWI + tc0 * S) * kRowBytes + (uint32_t)cv * 16;
   uint32_t stage = 0, phase = 0;
-  for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-    const int twi = (int)(tile % p.tiles_w);
-    const int64_t r = tile / p.tiles_w;
-    const int thi = (int)(r % p.tiles_h);
-    const int img = (int)(r / p.tiles_h);
+  TileWalk tw(p.tiles_w, p.tiles_h);
+  for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, tw.next()) {
+    const int twi = tw.twi, thi = tw.thi, img = tw.img;
 
     float2 acc[PX][4];
 #pragma unroll
