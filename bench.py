@@ -429,6 +429,9 @@ def train_main(args, rank, local_rank, world, batch, workload_name, metric):
 
 
 # ---------------------------------------------------------------------------- main ----
+_PHASE = ["set-up, warm-up and device-timed steps"]
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -515,6 +518,7 @@ def main():
     value = world * batch * args.steps / (dev_ms * 1e-3)
 
     # ---- end to end through the public API (pinned host in, host class map out) --------------------
+    _PHASE[0] = "end to end (pinned host in, host class map out)"
     for i in range(2):
         eng(host_in[i])
     barrier()
@@ -536,8 +540,10 @@ def main():
     line = None
     if rank == 0:
         peak, peak_src = measured_peak()
+        _PHASE[0] = "roofline pass (dominant kernel family timed with CUDA events)"
         roof = dominant_kernel_roofline(model, args.workload, batch, peak, peak_src)
         cpu = None
+        _PHASE[0] = "cpu baseline"
         if world == 1 and not args.no_cpu_baseline:
             b = cpu_reference_run(args.workload, 3, 1)
             cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -568,4 +574,9 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    try:
+        sys.exit(main())
+    except Exception:
+        # say which phase of the run raised (a CUDA error surfaces at the next synchronising call)
+        print(f"bench.py failed in phase: {_PHASE[0]}", file=sys.stderr, flush=True)
+        raise
