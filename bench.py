@@ -296,6 +296,36 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             "frac_of_8TBps_nominal": round(achieved / 8000.0, 4)}
 
 
+PARITY_MIN_AGREE = 0.99   # bf16 class map vs the fp32 oracle on the benchmark's own weights (default init)
+
+
+def parity_check(model, eng, workload: str):
+    """Checks the output of the timed configuration itself: the class maps the engine produced for the first and
+    the last image of slot 0's resident batch (bf16 path, CUDA graph) against the CPU oracle's fp32 argmax on the
+    same images and the same weights.  The run fails below PARITY_MIN_AGREE."""
+    import torch
+    from oracle import ref_nets
+
+    labels = eng.run_device(0)
+    torch.cuda.synchronize()
+    idx = sorted({0, eng.batch - 1})
+    x = eng.slots[0].x[idx].float().cpu()
+    got = labels[idx].cpu().long()
+    sd = {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+    torch.set_num_threads(os.cpu_count() or 1)
+    with torch.no_grad():
+        ref = ref_nets.FORWARD[workload](sd, x)
+    want = ref.max(1)[1]
+    per_image = (got == want).float().mean(dim=(1, 2)).tolist()
+    agree = float((got == want).float().mean().item())
+    out = {"argmax_agree": round(agree, 6), "per_image": [round(v, 6) for v in per_image], "n_images": len(idx),
+           "images": idx, "classes_present": int(want.unique().numel()), "min_required": PARITY_MIN_AGREE,
+           "oracle": "oracle/ref_nets.py fp32 on the host, same weights and inputs; labels from the timed bf16 graph"}
+    if min(per_image) < PARITY_MIN_AGREE:
+        raise SystemExit(f"bench.py: parity check failed: {json.dumps(out)}")
+    return out
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -537,6 +567,17 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * batch * args.steps / float(t.item())
 
+    # ---- self-check: watchdog flag on every rank, class maps of the first and last image against the oracle ----
+    _PHASE[0] = "parity check (class maps of image 0 and image B-1 against the CPU oracle)"
+    from rtseg_b200 import ops as _ops
+    flag = torch.tensor([_ops.tc_timeout_flag()], device="cuda", dtype=torch.int32)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+    if int(flag.item()) != 0:
+        raise SystemExit("bench.py: a tensor-core kernel hit its barrier watchdog during the timed region "
+                         "(rtseg_tc_timeout_flag set): the numbers of this run are void")
+    parity = parity_check(model, eng, args.workload) if rank == 0 else None
+
     line = None
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -564,6 +605,7 @@ def main():
             "gpu_launches": int(eng.launches_per_step * args.steps + eager_launches),
             "roofline": roof,
             "cpu_baseline": cpu,
+            "parity_check": parity,
         }
     if world > 1:
         dist.barrier()

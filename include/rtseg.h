@@ -146,6 +146,17 @@ int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, c
  * a device flag instead of hanging the GPU.  This call synchronises `stream`,
  * returns the flag (1 = a kernel gave up since the last call) and clears it. */
 int rtseg_tc_timeout_flag(rtseg_stream_t stream);
+/* Diagnostics (no reference counterpart; the reference has no kernels to plan):
+ * the execution plan rtseg_conv_tc would choose for `d`, so that a test can
+ * assert which regime it exercised.  info = {K block, N tile, N tiles,
+ * sub-tiles per unit, ring stages, staging buffers, halo-sharing mode, unit
+ * tiles, grid.x (persistent CTAs), shared-memory bytes, TMEM columns, residual
+ * boxes per unit}.  units / grid.x = unit tiles every CTA walks. */
+int rtseg_conv_tc_plan_info(const rtseg_conv_desc *d, int32_t info[12]);
+/* Diagnostics (no reference counterpart): launches of the TMA-staged depthwise
+ * kernel (dw_tma_kernel) by this process.  rtseg_conv_dw picks that kernel for
+ * bf16 3x3 dilation-1 layers with at least 65,536 output pixels. */
+uint64_t rtseg_dw_tma_launch_count(void);
 
 /* ---- K4'+K8: network stem ------------------------------------------------
  * Replaces InitialBlock, models/enet.py:38-48 (conv 3x3 s2 + BN + act on

@@ -56,6 +56,8 @@ PROTOTYPES = {
     "rtseg_conv_tc_supported": (c_i32, [_DP]),
     "rtseg_conv_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_tc_timeout_flag": (c_i32, [c_vp]),
+    "rtseg_conv_tc_plan_info": (c_i32, [_DP, C.POINTER(c_i32)]),
+    "rtseg_dw_tma_launch_count": (c_u64, []),
     "rtseg_stem": (c_i32, [_DP, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_maxpool3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp]),
     "rtseg_deconv3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -383,10 +383,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
           }
         }
-        for (int sb = 0; sb < p.res_boxes; ++sb)  // residual stages belong to the epilogue
-          if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
         if (elect_one()) umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
         __syncwarp();
+        // The residual stages belong to the epilogue, but this warp must still SEE each of their fills complete
+        // before it moves on: a parity wait can only tell "this lap" from "the previous lap".  If the ring is
+        // shorter than one unit's boxes (stages < A boxes + residual boxes), the slot of a later A tile held a
+        // residual box one lap earlier; skipping that fill unobserved let the wait for the A tile succeed on the
+        // lap before it (stale operand, then a second release of the slot and barrier phases out of step).
+        for (int sb = 0; sb < p.res_boxes; ++sb) {
+          mbar_wait(full_bar + 8 * stage, phase, dead);
+          if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
+        }
         if (++acc == 2) acc = 0, acc_phase ^= 1;
       }
     }
@@ -537,6 +544,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // registers while the MMAs of this tile are still running, TMEM loads one chunk ahead.
         // Residual sub-boxes of this unit: ring stages right behind the unit's A stages.
         uint32_t res_first = 0;  // ring slot of residual sub-box 0 (sub-box sb sits sb slots further, modulo)
+        // Order matters: the accumulator barrier first.  Once it has fired every A fill of this unit has completed,
+        // so the slot of each residual box is at most one lap behind and the parity wait below cannot succeed on
+        // an older lap (it could when the ring is shorter than one unit's boxes and the slot still held an A tile
+        // of the same unit).
+        mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
+        tc_fence_after();
         if constexpr (RES) {
           ring_advance(p.a_stages_per_unit);
           res_first = ring;
@@ -550,8 +563,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           }
           ring_advance(p.res_boxes);
         }
-        mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
-        tc_fence_after();
         for (int a = 0; a < p.nacc; ++a) {
           const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
           epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
@@ -1218,6 +1229,95 @@ extern "C" int rtseg_tc_timeout_flag(rtseg_stream_t stream) {
   return (a < 0 || b < 0 || c < 0) ? -1 : (a | b | c);
 }
 
+// Invariants of a plan the kernel relies on but cannot check cheaply on the device: the shared-memory carve-up fits
+// the launch's allocation, every TMA box fits its ring stage and the tensor-map limits, every shifted UMMA descriptor
+// stays inside the bytes its TMA box delivered, tensor memory holds both accumulator stages, and one unit's residual
+// boxes fit in the ring (more residual boxes than stages would wait on their own slots).
+static int check_plan(const TcParams &p, const TcPlan &pl) {
+  const uint32_t row_b = (uint32_t)pl.kb * 2;
+  const uint32_t carve = p.b_bytes + (uint32_t)p.stages * p.stage_bytes + (uint32_t)p.out_bufs * p.out_buf_bytes +
+                         3u * (uint32_t)p.bn * 4 + (2 * kMaxStages + 5) * 8 + 8;
+  RTSEG_REQUIRE(carve <= pl.smem_bytes && pl.smem_bytes + 1024 <= kSmemBudget + 2048, "conv_tc plan: shared-memory carve-up exceeds the allocation");
+  RTSEG_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "conv_tc plan: ring depth out of range");
+  RTSEG_REQUIRE(p.box_w >= 1 && p.box_w <= 256 && p.box_h >= 1 && p.box_h <= 256, "conv_tc plan: A box exceeds the TMA box limit");
+  RTSEG_REQUIRE(p.unit_w <= 256 && p.unit_h <= 256, "conv_tc plan: output box exceeds the TMA box limit");
+  RTSEG_REQUIRE(p.a_tx_bytes == (uint32_t)p.box_w * p.box_h * row_b && p.a_tx_bytes <= p.stage_bytes,
+                "conv_tc plan: A box does not fit its ring stage");
+  RTSEG_REQUIRE(p.stage_bytes % 1024 == 0 && p.b_block_bytes % 1024 == 0, "conv_tc plan: stage / weight block not swizzle-atom aligned");
+  RTSEG_REQUIRE((uint32_t)p.unit_w * p.unit_h == (uint32_t)p.ms * kTileM,
+                "conv_tc plan: unit tile is not ms x 128 pixels");
+  if (p.a_share) {
+    uint32_t last = 0;
+    const int ntap = p.ntaps;
+    for (int t = 0; t < ntap; ++t) last = std::max(last, p.tap_off16[t]);
+    const uint32_t end = (last + (uint32_t)(p.ms - 1) * p.a_sub16 + 15u * p.a_sbo16) * 16u + 8u * row_b;
+    RTSEG_REQUIRE(end <= p.a_tx_bytes, "conv_tc plan: a shifted tap descriptor reads past the halo box");
+  } else {
+    RTSEG_REQUIRE(((uint32_t)(p.ms - 1) * p.a_sub16 + 15u * p.a_sbo16) * 16u + 8u * row_b <= p.a_tx_bytes,
+                  "conv_tc plan: a sub-tile descriptor reads past the A box");
+  }
+  RTSEG_REQUIRE((uint32_t)(2 * p.ms * p.nacc * p.bn) <= p.tmem_cols && p.tmem_cols <= 512, "conv_tc plan: accumulators exceed tensor memory");
+  if (p.res_boxes) {
+    RTSEG_REQUIRE(p.res_boxes <= 4 && p.res_boxes <= p.stages, "conv_tc plan: residual boxes of one unit do not fit in the ring");
+    RTSEG_REQUIRE((uint32_t)p.ms * kTileM * (uint32_t)p.ob * 2 <= p.stage_bytes, "conv_tc plan: residual box does not fit its ring stage");
+  }
+  if (p.y_mode == 2)
+    RTSEG_REQUIRE((uint32_t)p.ms * kTileM * (uint32_t)p.bn * 2 == p.out_buf_bytes, "conv_tc plan: staging buffer size mismatch");
+  RTSEG_REQUIRE(p.ms * (p.bn / 16) <= 2 * kMaxMyChunks, "conv_tc plan: more 16-column chunks than the epilogue warps own");
+  return RTSEG_OK;
+}
+
+// Plans a forward conv: tile shape, A-sharing mode, stack depth, ring depth, epilogue mode.  `d` is the K-padded
+// descriptor.  Shared by rtseg_conv_tc and rtseg_conv_tc_plan_info so that tests can see the plan a launch would use.
+static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slope, TcPlan &pl, TcParams &p, int &share,
+                        int &mode) {
+  const int cout_pad = (d->cout + 15) / 16 * 16;
+  const int ntaps = d->kh * d->kw;
+  p.n = d->n;
+  rtseg_out_hw(d, &p.gh, &p.gw);
+  share = pick_share(d, p.gh, p.gw, pick_kb(d->cin));
+  const int halo = (share == 1 || share == 3) ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw, share), d->res_mode != RTSEG_RES_NONE, pl,
+               share, halo)) {
+    share = 0;
+    if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
+      RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
+                 d->cin, cout_pad);
+  }
+  p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
+  for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
+  p.ntaps = ntaps;
+  p.y_mode = staged ? 2 : 1;
+  fill_common(p, d, pl, cout_pad, share);
+  mode = epilogue_mode(d, slope, p);
+  p.a_stages_per_unit = share ? p.nkb : ntaps * p.nkb;
+  const bool has_res = d->res_mode != RTSEG_RES_NONE;
+  const bool ring_res = has_res && staged && mode <= 1 && pl.bn / pl.ob <= 4;
+  if (has_res && !ring_res) mode = 2;  // general path reads the residual with plain loads
+  if (ring_res) p.res_boxes = pl.bn / pl.ob;
+  return RTSEG_OK;
+}
+
+// Test / diagnostics hook: the execution plan rtseg_conv_tc would use for `d` with a 16-byte-aligned output.
+// info = {kb, bn, n_tiles, ms, stages, out_bufs, share, units, grid_x, smem_bytes, tmem_cols, res_boxes}.
+extern "C" int rtseg_conv_tc_plan_info(const rtseg_conv_desc *d, int32_t info[12]) {
+  RTSEG_REQUIRE(d && info, "NULL argument");
+  const char *why;
+  if (check_tc_common(d, false, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: %s", why);
+  rtseg_conv_desc padded = *d;
+  padded.cin = (d->cin + 15) / 16 * 16;
+  TcPlan pl;
+  TcParams p;
+  int share = 0, mode = 0;
+  const bool staged = d->y_ctotal % 8 == 0 && d->y_coff % 8 == 0;
+  if (int rc = plan_forward(&padded, staged, nullptr, pl, p, share, mode)) return rc;
+  const int gx = (int)std::min<int64_t>(p.num_m_tiles, std::max(1, num_sms() / pl.n_tiles));
+  const int32_t v[12] = {pl.kb, pl.bn, pl.n_tiles, pl.ms, pl.stages, pl.out_bufs, share, (int32_t)p.num_m_tiles, gx,
+                         (int32_t)pl.smem_bytes, (int32_t)pl.tmem_cols, p.res_boxes};
+  for (int i = 0; i < 12; ++i) info[i] = v[i];
+  return RTSEG_OK;
+}
+
 extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,
                              const float *shift, const float *slope, const void *res, void *y,
                              rtseg_stream_t stream) {
@@ -1239,28 +1339,10 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   const bool staged = can_stage_output(d, y);
   TcPlan pl;
   TcParams p;
-  p.n = d->n;
-  rtseg_out_hw(d, &p.gh, &p.gw);
-  int share = pick_share(d, p.gh, p.gw, pick_kb(d->cin));
-  const int halo = (share == 1 || share == 3) ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
-  if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw, share), d->res_mode != RTSEG_RES_NONE, pl,
-               share, halo)) {
-    share = 0;
-    if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
-      RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
-                 d->cin, cout_pad);
-  }
-  p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
-  for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
-  p.ntaps = ntaps;
-  p.y_mode = staged ? 2 : 1;
-  fill_common(p, d, pl, cout_pad, share);
-  int mode = epilogue_mode(d, slope, p);
-  p.a_stages_per_unit = share ? p.nkb : ntaps * p.nkb;
-  const bool has_res = d->res_mode != RTSEG_RES_NONE;
-  const bool ring_res = has_res && staged && mode <= 1 && pl.bn / pl.ob <= 4;
-  if (has_res && !ring_res) mode = 2;  // general path reads the residual with plain loads
-  if (ring_res) p.res_boxes = pl.bn / pl.ob;
+  int share = 0, mode = 0;
+  if (int rc = plan_forward(d, staged, slope, pl, p, share, mode)) return rc;
+  const bool ring_res = p.res_boxes > 0;
+  if (int rc = check_plan(p, pl)) return rc;
 
   TcMaps maps;
   const int64_t ct = d->x_ctotal;
@@ -1414,6 +1496,7 @@ extern "C" int rtseg_deconv3x3s2_tc(const rtseg_conv_desc *d, const void *x, con
     }
   }
   maps.r = maps.a[0];
+  if (int rc = check_plan(p, pl)) return rc;
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   return launch_tc(maps, p, pl, ep, mode, nullptr, y, labels, as_stream(stream));
 }

@@ -13,6 +13,7 @@
 //     16-byte vectors (full 128-byte lines per pixel).
 // Input is read from HBM exactly once (+ halo), output written once.
 #include <algorithm>
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
@@ -203,6 +204,8 @@ static EncodeTiledFnDw get_encode_fn_dw() {
 
 int dw_tma_timeout_flag() { return read_clear_timeout_flag(); }
 
+static std::atomic<uint64_t> g_dw_tma_launches{0};
+
 template <int S, int CB, int TH, int TW>
 static int launch_dw_tma(const rtseg_conv_desc *d, const void *x, const float *w, const Epilogue &ep, void *y,
                          cudaStream_t st) {
@@ -217,6 +220,9 @@ static int launch_dw_tma(const rtseg_conv_desc *d, const void *x, const float *w
   p.stages = (int)std::min<uint32_t>(kDwMaxStages, (200u * 1024u) / kStagePitch);
   if (p.stages < 2) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "dw_tma: tile does not fit in shared memory");
   const uint32_t smem = (uint32_t)p.stages * kStagePitch + 8 * 2 * kDwMaxStages + 16 + 128;
+  static_assert(THI <= 256 && TWI <= 256 && CB * 2 % 16 == 0, "halo tile exceeds the TMA box limits");
+  RTSEG_REQUIRE(smem <= 210 * 1024, "dw_tma: shared-memory plan exceeds the kernel's limit");
+  RTSEG_REQUIRE(d->x_coff + d->cin <= d->x_ctotal && d->y_coff + d->cin <= d->y_ctotal, "dw_tma: channel slice outside its buffer");
 
   EncodeTiledFnDw enc = get_encode_fn_dw();
   if (!enc) RTSEG_FAIL(RTSEG_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
@@ -255,6 +261,7 @@ static int launch_dw_tma(const rtseg_conv_desc *d, const void *x, const float *w
     RTSEG_DW_TMA(2);
 #undef RTSEG_DW_TMA
   RTSEG_LAUNCH_CHECK("dw_tma_kernel");
+  g_dw_tma_launches.fetch_add(1, std::memory_order_relaxed);
   return RTSEG_OK;
 }
 
@@ -283,3 +290,7 @@ int dw_tma_try(const rtseg_conv_desc *d, const void *x, const float *w, const Ep
 }
 
 }  // namespace rtseg
+
+// Diagnostics: how many times the TMA-staged depthwise kernel has been launched by this process (tests assert that a
+// layer above the size gate really took this kernel and not the register kernels of conv_dw.cu).
+extern "C" uint64_t rtseg_dw_tma_launch_count(void) { return rtseg::g_dw_tma_launches.load(std::memory_order_relaxed); }
