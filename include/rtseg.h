@@ -170,6 +170,15 @@ int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int
                const void *x, const float *w, const float *scale, const float *shift,
                const float *slope, void *y, rtseg_stream_t stream);
 
+/* The same stem fed by the decoded image itself: x is uint8 [n][h][w][cin] (HWC, cin <= 4).  Replaces the dataset's
+ * AT.Normalize(mean, std) + ToTensorV2 (datasets/cityscapes.py:122-123) and images.to(device, float32)
+ * (core/seg_trainer.py:42) in front of InitialBlock / the stride-2 stems: every sample is normalised while the stem
+ * builds its window, v = (float(x) - mean*255) * (1 / (std*255)) — the two fp32 operations albumentations performs —
+ * so a step ships 3 bytes per pixel to the device instead of 12.  mean_host / std_host: cin floats on the HOST. */
+int rtseg_stem_u8(const rtseg_conv_desc *d, int32_t pool, const uint8_t *x, const float *mean_host,
+                  const float *std_host, const float *w, const float *scale, const float *shift,
+                  const float *slope, void *y, rtseg_stream_t stream);
+
 /* MaxPool2d(3,2,1) branch of InitialBlock (models/enet.py:43) for NHWC inputs
  * with many channels; writes a channel slice of y. Uses d->n,h,w,cin,
  * x_ctotal/x_coff, y_ctotal/y_coff, dtype. */
@@ -351,6 +360,10 @@ int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t d
 int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
                        const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
                        int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream);
+/* The first level of that pyramid from the uint8 HWC image (normalised like rtseg_stem_u8, datasets/cityscapes.py:122-123). */
+int rtseg_avgpool3x3s2_u8(int32_t n, int32_t h, int32_t w, int32_t c, const uint8_t *x, const float *mean_host,
+                          const float *std_host, int32_t y_dtype, void *y, int32_t y_ctotal, int32_t y_coff,
+                          rtseg_stream_t stream);
 /* channel_shuffle, models/modules.py:18-32 (used by SSnbtUnit, models/lednet.py:87): NHWC slices,
  * out[.., i*groups + g] = in[.., g*(c/groups) + i]; x and y must not alias.                      */
 int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, int32_t dtype, const void *x,

@@ -59,6 +59,7 @@ PROTOTYPES = {
     "rtseg_conv_tc_plan_info": (c_i32, [_DP, C.POINTER(c_i32)]),
     "rtseg_dw_tma_launch_count": (c_u64, []),
     "rtseg_stem": (c_i32, [_DP, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_stem_u8": (c_i32, [_DP, c_i32, c_vp, C.POINTER(c_f32), C.POINTER(c_f32), c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_maxpool3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp]),
     "rtseg_deconv3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_deconv3x3s2_tc_supported": (c_i32, [_DP]),
@@ -77,6 +78,7 @@ PROTOTYPES = {
     "rtseg_nhwc_to_nchw": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "rtseg_adaptive_avgpool": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "rtseg_avgpool3x3s2": (c_i32, [c_i32] * 6 + [c_vp, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_avgpool3x3s2_u8": (c_i32, [c_i32] * 4 + [c_vp, C.POINTER(c_f32), C.POINTER(c_f32), c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_channel_shuffle": (c_i32, [c_i64, c_i32, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_bn_stats": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "rtseg_affine_act": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_f32, c_f32,
@@ -116,8 +118,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     with _lock:
         if _lib is not None:
             return _lib
-        path = _build.LIB_PATH
-        if build_if_missing and _build.sources_newer_than_lib():
+        path = os.environ.get("RTSEG_LIB_PATH") or _build.LIB_PATH   # RTSEG_LIB_PATH: A/B runs of two builds
+        if path == _build.LIB_PATH and build_if_missing and _build.sources_newer_than_lib():
             try:
                 _build.build_library()
             except Exception as e:  # stale-but-present library is still usable

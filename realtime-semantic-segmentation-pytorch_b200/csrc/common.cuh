@@ -105,11 +105,35 @@ static inline Epilogue make_epilogue(const rtseg_conv_desc *d, const float *scal
 int validate_conv_desc(const rtseg_conv_desc *d, const void *res);
 
 // Geometry of the stride-2 3x3 image stem (stem.cu, stem_tc.cu).
+// Dataset normalisation of a uint8 image, exactly as albumentations.Normalize computes it in fp32 (reference
+// datasets/cityscapes.py:122-123): v = (float(x) - mean*255) * (1 / (std*255)).  Ignored for float / bf16 inputs.
+struct ImgNorm {
+  float m255[4];
+  float rden[4];
+};
+
+// Internal dtype code of uint8 image inputs (the public rtseg_dtype covers activations only).
+constexpr int RTSEG_U8 = 2;
+
+// mean / std -> the two fp32 constants per channel, rounded where albumentations rounds them: float32 arrays
+// multiplied by max_pixel_value = 255 in float32, then np.reciprocal in float32.
+static inline int make_img_norm(int c, const float *mean_host, const float *std_host, ImgNorm &nz) {
+  for (int i = 0; i < 4; ++i) nz.m255[i] = 0.f, nz.rden[i] = 1.f;
+  for (int i = 0; i < c; ++i) {
+    const float s255 = std_host[i] * 255.0f;
+    if (!(s255 > 0.f)) return -1;
+    nz.m255[i] = mean_host[i] * 255.0f;
+    nz.rden[i] = 1.0f / s255;
+  }
+  return 0;
+}
+
 struct StemParams {
   int n, h, w, cin, cconv, ho, wo;
   int64_t sn, sc, sh, sw;  // input strides in elements
   int y_ct, y_co;
   int pool;
+  ImgNorm nz;              // uint8 inputs only
 };
 
 // ---- device side ---------------------------------------------------------------
@@ -206,6 +230,16 @@ __device__ __forceinline__ float ld_f<float>(const float *p) {
 template <>
 __device__ __forceinline__ float ld_f<__nv_bfloat16>(const __nv_bfloat16 *p) {
   return __bfloat162float(*p);
+}
+// Image element -> float: a uint8 sample is normalised on the way in (two fp32 operations, never contracted into an
+// FMA, so the fp32 path reproduces albumentations' arithmetic bit for bit); float / bf16 samples are taken as they are.
+template <typename T>
+__device__ __forceinline__ float ld_img(const T *p, const ImgNorm &nz, int ch) {
+  if constexpr (sizeof(T) == 1) {
+    return __fmul_rn(__fsub_rn((float)__ldg(reinterpret_cast<const unsigned char *>(p)), nz.m255[ch]), nz.rden[ch]);
+  } else {
+    return ld_f<T>(p);
+  }
 }
 template <typename T>
 __device__ __forceinline__ void st_f(T *p, float v);

@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) avgpool3x3s2_kernel(int n, int h, int w, int c, int ho, int wo, int64_t sn,
                                                            int64_t sc, int64_t sh, int64_t sw, const TI *__restrict__ x,
-                                                           TO *__restrict__ y, int y_ct, int y_co) {
+                                                           TO *__restrict__ y, int y_ct, int y_co, ImgNorm nz) {
   const int64_t total = (int64_t)n * ho * wo * c;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= total) return;
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(256) avgpool3x3s2_kernel(int n, int h, int w, 
 #pragma unroll
     for (int kx = 0; kx < 3; ++kx) {
       const int ix = ox * 2 - 1 + kx;
-      if (iy >= 0 && iy < h && ix >= 0 && ix < w) s += ld_f<TI>(x + b * sn + ch * sc + iy * sh + ix * sw);
+      if (iy >= 0 && iy < h && ix >= 0 && ix < w) s += ld_img<TI>(x + b * sn + ch * sc + iy * sh + ix * sw, nz, ch & 3);
     }
   }
   st_f<TO>(y + (((int64_t)b * ho + oy) * wo + ox) * y_ct + y_co + ch, s * (1.f / 9.f));
@@ -694,9 +694,9 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
   return RTSEG_OK;
 }
 
-extern "C" int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
-                                  const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
-                                  int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream) {
+static int avgpool3x3s2_impl(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
+                             const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
+                             int32_t y_ctotal, int32_t y_coff, const ImgNorm &nz, rtseg_stream_t stream) {
   RTSEG_REQUIRE(x && y, "NULL pointer");
   RTSEG_REQUIRE(n > 0 && h > 0 && w > 0 && c > 0 && y_ctotal >= y_coff + c && y_coff >= 0, "bad extent");
   const int ho = (h - 1) / 2 + 1, wo = (w - 1) / 2 + 1;
@@ -706,15 +706,17 @@ extern "C" int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, in
   } else {
     RTSEG_REQUIRE(x_ctotal >= x_coff + c && x_coff >= 0, "input channel slice out of range");
     sn = (int64_t)h * w * x_ctotal, sc = 1, sh = (int64_t)w * x_ctotal, sw = x_ctotal;
-    x = static_cast<const char *>(x) + (size_t)x_coff * (x_dtype == RTSEG_BF16 ? 2 : 4);
+    x = static_cast<const char *>(x) + (size_t)x_coff * (x_dtype == RTSEG_BF16 ? 2 : (x_dtype == RTSEG_U8 ? 1 : 4));
   }
   const int64_t total = (int64_t)n * ho * wo * c;
   const unsigned grid = (unsigned)cdiv(total, 256);
   cudaStream_t st = as_stream(stream);
 #define RTSEG_AVG(TI_, TO_)                                                                                     \
   avgpool3x3s2_kernel<TI_, TO_><<<grid, 256, 0, st>>>(n, h, w, c, ho, wo, sn, sc, sh, sw, (const TI_ *)x, (TO_ *)y, \
-                                                      y_ctotal, y_coff)
-  if (x_dtype == RTSEG_F32 && y_dtype == RTSEG_F32) RTSEG_AVG(float, float);
+                                                      y_ctotal, y_coff, nz)
+  if (x_dtype == RTSEG_U8 && y_dtype == RTSEG_F32) RTSEG_AVG(uint8_t, float);
+  else if (x_dtype == RTSEG_U8 && y_dtype == RTSEG_BF16) RTSEG_AVG(uint8_t, __nv_bfloat16);
+  else if (x_dtype == RTSEG_F32 && y_dtype == RTSEG_F32) RTSEG_AVG(float, float);
   else if (x_dtype == RTSEG_F32 && y_dtype == RTSEG_BF16) RTSEG_AVG(float, __nv_bfloat16);
   else if (x_dtype == RTSEG_BF16 && y_dtype == RTSEG_BF16) RTSEG_AVG(__nv_bfloat16, __nv_bfloat16);
   else if (x_dtype == RTSEG_BF16 && y_dtype == RTSEG_F32) RTSEG_AVG(__nv_bfloat16, float);
@@ -722,6 +724,23 @@ extern "C" int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, in
 #undef RTSEG_AVG
   RTSEG_LAUNCH_CHECK("avgpool3x3s2_kernel");
   return RTSEG_OK;
+}
+
+extern "C" int rtseg_avgpool3x3s2(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,
+                                  const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
+                                  int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x_dtype == RTSEG_F32 || x_dtype == RTSEG_BF16, "unknown dtype");
+  const ImgNorm nz{};
+  return avgpool3x3s2_impl(n, h, w, c, x_is_nchw, x_dtype, x, x_ctotal, x_coff, y_dtype, y, y_ctotal, y_coff, nz, stream);
+}
+
+extern "C" int rtseg_avgpool3x3s2_u8(int32_t n, int32_t h, int32_t w, int32_t c, const uint8_t *x, const float *mean_host,
+                                     const float *std_host, int32_t y_dtype, void *y, int32_t y_ctotal, int32_t y_coff,
+                                     rtseg_stream_t stream) {
+  RTSEG_REQUIRE(mean_host && std_host && c >= 1 && c <= 4, "uint8 images have 1 to 4 channels");
+  ImgNorm nz{};
+  RTSEG_REQUIRE(make_img_norm(c, mean_host, std_host, nz) == 0, "std must be positive");
+  return avgpool3x3s2_impl(n, h, w, c, 0, RTSEG_U8, x, c, 0, y_dtype, y, y_ctotal, y_coff, nz, stream);
 }
 
 extern "C" int rtseg_channel_shuffle(int64_t npix, int32_t c, int32_t groups, int32_t dtype, const void *x,

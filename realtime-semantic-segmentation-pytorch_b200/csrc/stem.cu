@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) stem_kernel(StemParams p, const TI *__res
       inb[ky][kx] = hi >= 0 && hi < p.h && wi >= 0 && wi < p.w;
 #pragma unroll
       for (int ci = 0; ci < CIN; ++ci)
-        win[ky][kx][ci] = inb[ky][kx] ? ld_f<TI>(xn + ci * p.sc + hi * p.sh + wi * p.sw) : 0.f;
+        win[ky][kx][ci] = inb[ky][kx] ? ld_img<TI>(xn + ci * p.sc + hi * p.sh + wi * p.sw, p.nz, ci) : 0.f;
     }
   }
 #pragma unroll
@@ -233,9 +233,9 @@ static int launch_stem(const StemParams &p, const void *x, const float *w, const
 
 }  // namespace rtseg
 
-extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int32_t pool, const void *x,
-                          const float *w, const float *scale, const float *shift, const float *slope, void *y,
-                          rtseg_stream_t stream) {
+static int stem_impl(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int32_t pool, const void *x,
+                     const rtseg::ImgNorm &nz, const float *w, const float *scale, const float *shift, const float *slope,
+                     void *y, rtseg_stream_t stream) {
   using namespace rtseg;
   RTSEG_REQUIRE(d && x && w && y, "NULL argument");
   RTSEG_REQUIRE(d->kh == 3 && d->kw == 3 && d->stride == 2 && d->dil == 1 && d->pad_h == 1 && d->pad_w == 1 &&
@@ -247,13 +247,14 @@ extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x
   p.n = d->n, p.h = d->h, p.w = d->w, p.cin = d->cin, p.cconv = d->cout;
   p.ho = (d->h - 1) / 2 + 1, p.wo = (d->w - 1) / 2 + 1;
   p.pool = pool ? 1 : 0;
+  p.nz = nz;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff;
   RTSEG_REQUIRE(p.y_ct >= p.y_co + p.cconv + (p.pool ? p.cin : 0), "output channel slice too small");
   if (x_is_nchw) {
     p.sn = (int64_t)d->cin * d->h * d->w, p.sc = (int64_t)d->h * d->w, p.sh = d->w, p.sw = 1;
   } else {
     p.sn = (int64_t)d->h * d->w * d->x_ctotal, p.sc = 1, p.sh = (int64_t)d->w * d->x_ctotal, p.sw = d->x_ctotal;
-    x = static_cast<const char *>(x) + (size_t)d->x_coff * (x_dtype == RTSEG_BF16 ? 2 : 4);
+    x = static_cast<const char *>(x) + (size_t)d->x_coff * (x_dtype == RTSEG_BF16 ? 2 : (x_dtype == rtseg::RTSEG_U8 ? 1 : 4));
   }
   const Epilogue ep = make_epilogue(d, scale, shift, slope);
   cudaStream_t st = as_stream(stream);
@@ -266,7 +267,27 @@ extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x
   if (x_dtype == RTSEG_BF16 && d->dtype == RTSEG_BF16)
     return launch_stem<__nv_bfloat16, __nv_bfloat16>(p, x, w, ep, y, st);
   if (x_dtype == RTSEG_BF16 && d->dtype == RTSEG_F32) return launch_stem<__nv_bfloat16, float>(p, x, w, ep, y, st);
+  if (x_dtype == RTSEG_U8 && d->dtype == RTSEG_F32) return launch_stem<uint8_t, float>(p, x, w, ep, y, st);
+  if (x_dtype == RTSEG_U8 && d->dtype == RTSEG_BF16) return launch_stem<uint8_t, __nv_bfloat16>(p, x, w, ep, y, st);
   RTSEG_FAIL(RTSEG_ERR_INVALID, "bad dtype combination");
+}
+
+extern "C" int rtseg_stem(const rtseg_conv_desc *d, int32_t x_is_nchw, int32_t x_dtype, int32_t pool, const void *x,
+                          const float *w, const float *scale, const float *shift, const float *slope, void *y,
+                          rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x_dtype == RTSEG_F32 || x_dtype == RTSEG_BF16, "rtseg_stem takes fp32 or bf16 images (uint8: rtseg_stem_u8)");
+  const rtseg::ImgNorm nz{};
+  return stem_impl(d, x_is_nchw, x_dtype, pool, x, nz, w, scale, shift, slope, y, stream);
+}
+
+extern "C" int rtseg_stem_u8(const rtseg_conv_desc *d, int32_t pool, const uint8_t *x, const float *mean_host,
+                             const float *std_host, const float *w, const float *scale, const float *shift,
+                             const float *slope, void *y, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(d && mean_host && std_host, "NULL argument");
+  RTSEG_REQUIRE(d->cin >= 1 && d->cin <= 4, "uint8 images have 1 to 4 channels");
+  rtseg::ImgNorm nz{};
+  RTSEG_REQUIRE(rtseg::make_img_norm(d->cin, mean_host, std_host, nz) == 0, "std must be positive");
+  return stem_impl(d, 0, rtseg::RTSEG_U8, pool, x, nz, w, scale, shift, slope, y, stream);
 }
 
 extern "C" int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void *y, rtseg_stream_t stream) {

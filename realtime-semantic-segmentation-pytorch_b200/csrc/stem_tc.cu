@@ -36,9 +36,6 @@ __device__ __forceinline__ uint32_t sw64_off(int r, int c) {
   return (uint32_t)r * kRowBytes + ((uint32_t)(c ^ ((r >> 1) & 3)) << 4);
 }
 
-template <typename TI>
-__device__ __forceinline__ float ld_in(const TI *p) { return ld_f<TI>(p); }
-
 template <typename TI, int CIN, int N, int MODE, bool NCHW>
 __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const TI *__restrict__ x,
                                                            const float *__restrict__ wgt, Epilogue ep,
@@ -134,7 +131,7 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
         for (int ky = 0; ky < 3; ++ky) {
           const TI *rp = base + off[ci][ky];
 #pragma unroll
-          for (int kx = 0; kx < 3; ++kx) v[(ky * 3 + kx) * CIN + ci] = ld_in<TI>(rp + kx * kxs);
+          for (int kx = 0; kx < 3; ++kx) v[(ky * 3 + kx) * CIN + ci] = ld_img<TI>(rp + kx * kxs, p.nz, ci);
         }
     } else {
       okmask = 0;
@@ -146,7 +143,7 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
           okmask |= ok ? 1 << (ky * 3 + kx) : 0;
 #pragma unroll
           for (int ci = 0; ci < CIN; ++ci)
-            v[(ky * 3 + kx) * CIN + ci] = ok ? ld_in<TI>(base + off[ci][ky] + kx * kxs) : 0.f;
+            v[(ky * 3 + kx) * CIN + ci] = ok ? ld_img<TI>(base + off[ci][ky] + kx * kxs, p.nz, ci) : 0.f;
         }
       if (!valid) pixel = -1;
     }
@@ -295,6 +292,7 @@ int stem_tc_try(const StemParams &p, int x_dtype, const void *x, const float *w,
   __nv_bfloat16 *yo = static_cast<__nv_bfloat16 *>(y);
   if (x_dtype == RTSEG_F32) return launch_in<float>(p, static_cast<const float *>(x), w, ep, yo, st);
   if (x_dtype == RTSEG_BF16) return launch_in<__nv_bfloat16>(p, static_cast<const __nv_bfloat16 *>(x), w, ep, yo, st);
+  if (x_dtype == RTSEG_U8) return launch_in<uint8_t>(p, static_cast<const uint8_t *>(x), w, ep, yo, st);
   return 1;
 }
 

@@ -2,6 +2,8 @@
 
     eng = InferenceEngine(model, batch=16, height=1024, width=2048)   # model: nets.ERFNet / FastSCNN, .eval()
     labels = eng(host_images)        # pinned fp32 NCHW in  ->  pinned uint8 [N, H, W] class map out
+    eng = InferenceEngine(model, ..., in_dtype=torch.uint8)           # decoded uint8 [N, H, W, 3] images in: a quarter
+                                                                      # of the bytes; normalised inside the stem kernel
 
 The model's forward is a fixed sequence of librtseg launches with static shapes, so it is
 captured once into a CUDA graph (no per-launch host overhead, no tracing compiler) and replayed.
@@ -20,7 +22,11 @@ from . import _lib
 class _Slot:
     def __init__(self, eng: "InferenceEngine"):
         dev = eng.device
-        self.x = torch.empty((eng.batch, eng.in_channels, eng.height, eng.width), dtype=eng.in_dtype, device=dev)
+        if eng.in_dtype == torch.uint8:   # decoded images: HWC bytes, NCHW-logical view (what the stems read)
+            self.x = torch.empty((eng.batch, eng.height, eng.width, eng.in_channels), dtype=torch.uint8,
+                                 device=dev).permute(0, 3, 1, 2)
+        else:
+            self.x = torch.empty((eng.batch, eng.in_channels, eng.height, eng.width), dtype=eng.in_dtype, device=dev)
         self.labels = torch.empty((eng.batch, eng.height, eng.width), dtype=torch.uint8, device=dev)
         self.host_out = torch.empty((eng.batch, eng.height, eng.width), dtype=torch.uint8, pin_memory=True)
         self.stream = torch.cuda.Stream(device=dev)
@@ -90,6 +96,9 @@ class InferenceEngine:
     # -- host path --------------------------------------------------------------------------
     def submit(self, host_images: torch.Tensor) -> int:
         """Enqueue H2D copy + forward + D2H copy for one batch; returns the slot index."""
+        if self.in_dtype == torch.uint8 and host_images.dim() == 4 and host_images.dtype == torch.uint8:
+            from . import ops
+            host_images = ops.as_image_u8(host_images)   # [N, H, W, C] bytes -> NCHW-logical view, no copy
         if tuple(host_images.shape) != tuple(self.slots[0].x.shape) or host_images.dtype != self.in_dtype:
             raise ValueError(f"expected {tuple(self.slots[0].x.shape)} {self.in_dtype} input")
         i = self._next

@@ -60,7 +60,8 @@ class InitialBlock(nn.Module):
         cin, cconv = conv.in_channels, conv.out_channels
         if self.conv[1].training and out is None and x.shape[1] == cin:
             from . import train   # training: conv branch and pool branch are tape nodes; the cat is a copy
-            xn = ops.to_nhwc(x, self.act_dtype or (x.dtype if x.is_cuda and ops.is_nhwc(x) else _param_dtype(self.conv)))
+            xn = ops.to_nhwc(x, self.act_dtype or (x.dtype if x.is_cuda and ops.is_nhwc(x) and x.dtype != torch.uint8
+                                                    else _param_dtype(self.conv)))
             conv_out = train.conv_bn_act_aligned(self.conv, xn, pad_input=True) if cin <= 4 else train.conv_bn_act(self.conv, xn)
             return ops.to_nhwc(torch.cat([conv_out, train.maxpool3x3s2(xn)], dim=1))
         _check_eval(self, self.conv[1])
@@ -205,7 +206,7 @@ class LearningToDownsample(nn.Sequential):
                 raise NotImplementedError("non-pointwise activation in the stem")
             x = ops.stem(folded, x, pool=False, out_dtype=self.act_dtype or _param_dtype(stem))
         else:
-            x = stem(x)
+            x = stem(ops.to_nhwc(x, self.act_dtype or _param_dtype(stem)) if x.dtype == torch.uint8 else x)
         return self[2](self[1](x))
 
 

@@ -53,6 +53,8 @@ def empty_nhwc(n: int, c: int, h: int, w: int, dtype, device) -> torch.Tensor:
 def to_nhwc(x: torch.Tensor, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
     """Dense-NHWC copy of an NCHW tensor (our transpose kernel), or x itself if already NHWC."""
     _require_cuda(x, "to_nhwc")
+    if x.dtype == torch.uint8:   # a decoded image outside the stem kernels (training, unusual stems)
+        return normalize_u8(x, dtype or torch.float32)
     dtype = dtype or x.dtype
     if is_nhwc(x) and x.dtype == dtype:
         return x
@@ -318,11 +320,68 @@ def conv(f: Folded, x: torch.Tensor, *, res: Optional[torch.Tensor] = None, res_
     return out
 
 
+# Normalisation applied to uint8 images inside the stem kernels: the constants of reference
+# datasets/cityscapes.py:122-123 (AT.Normalize).  set_image_norm() changes them for other datasets.
+IMAGE_MEAN = (0.485, 0.456, 0.406)
+IMAGE_STD = (0.229, 0.224, 0.225)
+
+
+def set_image_norm(mean, std) -> None:
+    global IMAGE_MEAN, IMAGE_STD
+    mean, std = tuple(float(v) for v in mean), tuple(float(v) for v in std)
+    if len(mean) != len(std) or not 1 <= len(mean) <= 4 or min(std) <= 0:
+        raise ValueError("mean / std: 1 to 4 channels, std > 0")
+    IMAGE_MEAN, IMAGE_STD = mean, std
+
+
+def _norm_args(cin: int):
+    if cin > len(IMAGE_MEAN):
+        raise ValueError(f"a {cin}-channel uint8 image needs {cin} mean / std values (ops.set_image_norm)")
+    arr = C.c_float * cin
+    return arr(*IMAGE_MEAN[:cin]), arr(*IMAGE_STD[:cin])
+
+
+def as_image_u8(x: torch.Tensor) -> torch.Tensor:
+    """A decoded uint8 image batch as the NCHW-logical, HWC-stored tensor the stems read.
+
+    Accepts [N, H, W, C] (what a decoder produces) or an [N, C, H, W] tensor that is already channels_last."""
+    if x.dtype != torch.uint8 or x.dim() != 4:
+        raise TypeError("expected a 4-d uint8 image batch")
+    if x.shape[1] <= 4 and is_nhwc(x):
+        return x
+    if x.shape[3] <= 4 and x.is_contiguous():
+        return x.permute(0, 3, 1, 2)
+    raise ValueError("uint8 images must be stored HWC: [N, H, W, C] contiguous or [N, C, H, W] channels_last, C <= 4")
+
+
+def normalize_u8(x: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """The normalised float image the reference's data pipeline would hand to the model (NHWC storage): only for
+    callers that need the tensor itself; the stems normalise while they read and never materialise it."""
+    _require_cuda(x, "normalize_u8")
+    x = as_image_u8(x)
+    n, c, h, w = x.shape
+    mean = torch.tensor(IMAGE_MEAN[:c], dtype=torch.float32, device=x.device) * 255.0
+    rden = torch.reciprocal(torch.tensor(IMAGE_STD[:c], dtype=torch.float32, device=x.device) * 255.0)
+    return ((x.float() - mean.view(1, c, 1, 1)) * rden.view(1, c, 1, 1)).to(dtype).contiguous(memory_format=torch.channels_last)
+
+
 def stem(f: Folded, x: torch.Tensor, pool: bool, out_dtype: torch.dtype, out: Optional[torch.Tensor] = None,
          y_coff: int = 0) -> torch.Tensor:
-    """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor."""
+    """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor, or from the uint8 HWC image
+    (normalisation of reference datasets/cityscapes.py:122-123 applied while the window is read)."""
     _require_cuda(x, "stem")
     n, cin, h, w = x.shape
+    if x.dtype == torch.uint8:
+        x = as_image_u8(x)
+        ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+        if out is None:
+            out = empty_nhwc(n, f.cout + (cin if pool else 0), ho, wo, out_dtype, x.device)
+        d = _desc(f, n, h, w, _dtype_code(out_dtype), cin, 0, out.shape[1], y_coff)
+        mean, std = _norm_args(cin)
+        _lib.check(_lib.load().rtseg_stem_u8(C.byref(d), 1 if pool else 0, x.data_ptr(), mean, std, f.w_f32.data_ptr(),
+                                             _ptr(f.scale), _ptr(f.shift), _ptr(f.slope), out.data_ptr(), _stream()),
+                   "rtseg_stem_u8")
+        return out
     if x.is_contiguous():
         nchw = 1
     elif is_nhwc(x):
@@ -506,6 +565,14 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
     _require_cuda(x, "avgpool3x3s2")
     n, x_ct, h, w = x.shape
     c = c if c is not None else x_ct
+    if x.dtype == torch.uint8:   # the decoded image: normalised while it is read
+        x = as_image_u8(x)
+        if x_coff or c != x_ct or out is None:
+            raise ValueError("uint8 images are pooled whole, into a caller-provided buffer")
+        mean, std = _norm_args(c)
+        _lib.check(_lib.load().rtseg_avgpool3x3s2_u8(n, h, w, c, x.data_ptr(), mean, std, _dtype_code(out.dtype),
+                                                     out.data_ptr(), out.shape[1], y_coff, _stream()), "rtseg_avgpool3x3s2_u8")
+        return out
     if x.is_contiguous() and x_coff == 0 and c == x_ct:
         nchw = 1
     elif is_nhwc(x):

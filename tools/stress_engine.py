@@ -35,7 +35,11 @@ def main():
     for s in eng.slots:
         s.x.copy_(torch.randn(s.x.shape, generator=g, device="cuda"))
     torch.cuda.synchronize()
-    first = [eng.run_device(i).clone() for i in range(2)]
+    first = []
+    for i in range(2):
+        out = eng.run_device(i)           # enqueued on the slot's own stream
+        torch.cuda.synchronize()
+        first.append(out.clone())
     torch.cuda.synchronize()
     bad = flags = 0
     t0 = time.time()
