@@ -56,6 +56,7 @@ class InitialBlock(nn.Module):
     def forward(self, x, out=None, y_coff=0):
         """`x` may be a wider NHWC buffer whose first in_channels channels are the input; `out` / `y_coff`
         place the result in a channel slice of a caller-owned buffer (DABNet's concatenations)."""
+        x = ops.image_view(x)
         conv = self.conv[0]
         cin, cconv = conv.in_channels, conv.out_channels
         if self.conv[1].training and out is None and x.shape[1] == cin:
@@ -140,7 +141,7 @@ class ERFNet(nn.Module):
         return self
 
     def _trunk(self, x):
-        x = self.layer1(x)
+        x = self.layer1(ops.image_view(x))
         x = self.layer2(x)
         x = self.layer3_7(x)
         x = self.layer8(x)
@@ -156,6 +157,7 @@ class ERFNet(nn.Module):
 
     def predict(self, x, labels: Optional[torch.Tensor] = None) -> torch.Tensor:
         """uint8 class map [N, H, W] == forward(x).max(dim=1)[1]; the logits are never materialised."""
+        x = ops.image_view(x)
         n, _, h, w = x.shape
         if labels is None:
             labels = torch.empty((n, h, w), dtype=torch.uint8, device=x.device)
@@ -197,6 +199,7 @@ class LearningToDownsample(nn.Sequential):
         )
 
     def forward(self, x):
+        x = ops.image_view(x)
         stem = self[0]
         conv = stem[0]
         if conv.in_channels <= 4 and conv.out_channels <= 32:
@@ -276,7 +279,7 @@ class FastSCNN(nn.Module):
         return self
 
     def _features(self, x):
-        hi = self.learning_to_downsample(x)
+        hi = self.learning_to_downsample(ops.image_view(x))
         lo = self.global_feature_extractor(hi)
         return self.classifier[1](self.classifier[0](self.feature_fusion(hi, lo)))
 
@@ -285,11 +288,13 @@ class FastSCNN(nn.Module):
 
     def forward(self, x):
         """Full-resolution logits like the reference (bilinear x8, align_corners=True)."""
+        x = ops.image_view(x)
         return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
         """uint8 class map via the fused upsample+argmax head (+ confusion-matrix update)."""
+        x = ops.image_view(x)
         f = self._features(x)
         n, _, h, w = f.shape
         # the 19-class head writes into a 32-channel (16-byte aligned) buffer so that its output leaves the
@@ -405,6 +410,7 @@ class DABNet(nn.Module):
         return new
 
     def _lowres_padded(self, x):
+        x = ops.image_view(x)
         dt = self.act_dtype or _param_dtype(self.layer1)
         n, cin, h, w = x.shape
         half = lambda v: (v - 1) // 2 + 1
@@ -437,10 +443,12 @@ class DABNet(nn.Module):
         return _first_channels(self._lowres_padded(x), self.num_class)
 
     def forward(self, x):
+        x = ops.image_view(x)
         return ops.upsample_bilinear(self._lowres_padded(x), x.shape[2:], True, c=self.num_class)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
+        x = ops.image_view(x)
         return ops.upsample_argmax(self._lowres_padded(x), x.shape[2:], True, target=target, confmat=confmat,
                                    ignore_index=ignore_index, num_classes=self.num_class)
 
@@ -550,16 +558,18 @@ class LEDNet(nn.Module):
         return self
 
     def _lowres_padded(self, x):
-        return self.apn(self.encoder(x), padded=True)
+        return self.apn(self.encoder(ops.image_view(x)), padded=True)
 
     def lowres_logits(self, x):
         return _first_channels(self._lowres_padded(x), self.num_class)
 
     def forward(self, x):
+        x = ops.image_view(x)
         return ops.upsample_bilinear(self._lowres_padded(x), x.shape[2:], True, c=self.num_class)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
                 ignore_index: int = 255) -> torch.Tensor:
+        x = ops.image_view(x)
         return ops.upsample_argmax(self._lowres_padded(x), x.shape[2:], True, target=target, confmat=confmat,
                                    ignore_index=ignore_index, num_classes=self.num_class)
 

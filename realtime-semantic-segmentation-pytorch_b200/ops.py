@@ -354,6 +354,11 @@ def as_image_u8(x: torch.Tensor) -> torch.Tensor:
     raise ValueError("uint8 images must be stored HWC: [N, H, W, C] contiguous or [N, C, H, W] channels_last, C <= 4")
 
 
+def image_view(x: torch.Tensor) -> torch.Tensor:
+    """Entry point of every net / stem: a uint8 batch becomes its NCHW-logical HWC-stored view, anything else passes."""
+    return as_image_u8(x) if x.dtype == torch.uint8 else x
+
+
 def normalize_u8(x: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.Tensor:
     """The normalised float image the reference's data pipeline would hand to the model (NHWC storage): only for
     callers that need the tensor itself; the stems normalise while they read and never materialise it."""
@@ -370,9 +375,10 @@ def stem(f: Folded, x: torch.Tensor, pool: bool, out_dtype: torch.dtype, out: Op
     """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor, or from the uint8 HWC image
     (normalisation of reference datasets/cityscapes.py:122-123 applied while the window is read)."""
     _require_cuda(x, "stem")
-    n, cin, h, w = x.shape
     if x.dtype == torch.uint8:
         x = as_image_u8(x)
+    n, cin, h, w = x.shape
+    if x.dtype == torch.uint8:
         ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
         if out is None:
             out = empty_nhwc(n, f.cout + (cin if pool else 0), ho, wo, out_dtype, x.device)
@@ -563,10 +569,11 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
                  y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
     """F.avg_pool2d(x, 3, 2, 1) (reference models/dabnet.py:32-34) from an NCHW or NHWC tensor into an NHWC slice."""
     _require_cuda(x, "avgpool3x3s2")
+    if x.dtype == torch.uint8:
+        x = as_image_u8(x)
     n, x_ct, h, w = x.shape
     c = c if c is not None else x_ct
     if x.dtype == torch.uint8:   # the decoded image: normalised while it is read
-        x = as_image_u8(x)
         if x_coff or c != x_ct or out is None:
             raise ValueError("uint8 images are pooled whole, into a caller-provided buffer")
         mean, std = _norm_args(c)
