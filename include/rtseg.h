@@ -379,7 +379,10 @@ int rtseg_colorize_blend(int64_t npix, const uint8_t *labels, const uint8_t *lut
 /* ---- host-buffer convenience (pinned or pageable HOST pointers) ------------
  * One call = H2D copy of the low-resolution logits, the fused head kernel,
  * D2H copy of the uint8 class map, all on `stream`, then a stream
- * synchronise.  `dev_scratch` must hold logits bytes + n*ho*wo bytes.       */
+ * synchronise.  `dev_scratch` must hold logits bytes + n*ho*wo bytes
+ * (rtseg_upsample_argmax_host_scratch_bytes returns exactly that).          */
+size_t rtseg_upsample_argmax_host_scratch_bytes(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
+                                                int32_t dtype);
 int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo,
                                int32_t align_corners, int32_t dtype, const void *x_host,
                                uint8_t *labels_host, void *dev_scratch, rtseg_stream_t stream);

@@ -264,6 +264,18 @@ class DeferredLogits(torch.Tensor):
             return func(*[unwrap(a) for a in args], **{k: unwrap(v) for k, v in kwargs.items()})
 
 
+    @classmethod
+    def __torch_dispatch__(cls, func, types, args=(), kwargs=None):
+        # Reached only by calls that bypass __torch_function__ (C++-side callers): same rule, materialise and run.
+        def unwrap(a):
+            if isinstance(a, DeferredLogits):
+                return a.materialise()
+            if isinstance(a, (list, tuple)):
+                return type(a)(unwrap(v) for v in a)
+            return a
+        return func(*[unwrap(a) for a in args], **{k: unwrap(v) for k, v in (kwargs or {}).items()})
+
+
 class _LazyMax:
     """Result of `deferred.max(dim=1)`: `[1]` / `.indices` is the fused class map (int64, like torch.max);
     `[0]` / `.values` materialises the logits."""
@@ -285,7 +297,11 @@ class _LazyMax:
         return self._val
 
     def __getitem__(self, i):
-        return (self.values, self.indices)[i]
+        if i in (0, -2):
+            return self.values
+        if i in (1, -1):
+            return self.indices
+        raise IndexError("max(dim) returns (values, indices)")
 
     def __iter__(self):
         return iter((self.values, self.indices))

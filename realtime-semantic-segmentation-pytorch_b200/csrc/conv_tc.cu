@@ -923,7 +923,9 @@ static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &p
 
 static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, int mode,
                      const void *res, void *y, uint8_t *labels, cudaStream_t st) {
-  if (labels != nullptr && p.y_mode == 0 && p.nacc == 4 && mode == 0 && pl.n_tiles == 1 && (p.ow & 1) == 0)
+  // mode 3 writes two adjacent labels with one 16-bit store: the class map must be 2-byte aligned (rows are: ow even)
+  if (labels != nullptr && p.y_mode == 0 && p.nacc == 4 && mode == 0 && pl.n_tiles == 1 && (p.ow & 1) == 0 &&
+      reinterpret_cast<uintptr_t>(labels) % 2 == 0)
     mode = 3;
   else if (labels != nullptr || p.y_mode != 2)
     mode = 2;

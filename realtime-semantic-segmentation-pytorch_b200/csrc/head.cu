@@ -108,7 +108,9 @@ __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool val
 // horizontally interpolated row A and the difference D = B - A (channels >= c padded with -inf / 0),
 // so that one output pixel costs, per class, one FFMA (A + ly1*D) and a branch-free compare/select —
 // the x8 upsampled logits exist only in registers.  NaNs (which must win, torch.max semantics) are
-// detected when a source row is loaded and handled by a slow exact path.
+// and infinities (inf - inf in D, inf + -inf in A + ly1*D would turn into NaNs torch does not produce) are detected
+// when a source row is loaded; such threads evaluate torch's own expression ly0*(lx0*p00 + lx1*p01) + ly1*(...)
+// straight from memory.  Padded channels hold -inf and the compare is strict, so the label never leaves [0, c).
 template <typename T, int CMAX>
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int n, int hi, int wi, int c, int ct, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
@@ -140,10 +142,10 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     const T *p1 = xb + ((int64_t)i * wi + x1) * ct;
 #pragma unroll
     for (int k = 0; k < CMAX; ++k) {
-      float v = -FLT_MAX;
+      float v = -INFINITY;
       if (k < c) {
         v = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
-        has_nan |= (v != v);
+        has_nan |= !(fabsf(v) <= FLT_MAX);   // NaN or +-inf
       }
       row[k] = v;
     }
@@ -181,11 +183,15 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
           best = g ? v : best;
           label = g ? k : label;
         }
-      } else {  // exact torch.max semantics with NaNs present: the first NaN wins
-        float best = rowA[0] + ly1 * rowD[0];
-#pragma unroll
-        for (int k = 1; k < CMAX; ++k)  // static indices: the row caches must stay in registers
-          if (k < c) argmax_step(fmaf(ly1, rowD[k], rowA[k]), k, best, label);
+      } else {  // non-finite logits in this column: torch's expression and torch.max semantics (the first NaN wins)
+        const T *r0 = xb + (int64_t)y0 * wi * ct, *r1 = xb + (int64_t)y1 * wi * ct;
+        float best = 0.f;
+        for (int k = 0; k < c; ++k) {
+          const float a = lx0 * ld_f<T>(r0 + (int64_t)x0 * ct + k) + lx1 * ld_f<T>(r0 + (int64_t)x1 * ct + k);
+          const float bb = lx0 * ld_f<T>(r1 + (int64_t)x0 * ct + k) + lx1 * ld_f<T>(r1 + (int64_t)x1 * ct + k);
+          const float v = ly0 * a + ly1 * bb;
+          if (k == 0) best = v; else argmax_step(v, k, best, label);
+        }
       }
       const int64_t opix = ((int64_t)b * ho + oy) * wo + ox;
       if (lab8) lab8[opix] = (uint8_t)label;
@@ -682,9 +688,10 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
   const size_t es = dtype == RTSEG_BF16 ? 2 : 4;
   size_t in_bytes = (size_t)n * hi * wi * c * es;
   const size_t out_bytes = (size_t)n * ho * wo;
-  const size_t in_padded = (in_bytes + 255) / 256 * 256;
   cudaStream_t st = as_stream(stream);
-  uint8_t *dlab = static_cast<uint8_t *>(dev_scratch) + in_padded;
+  // the uint8 class map sits directly behind the logits (a byte buffer needs no alignment): the documented scratch
+  // size, logits bytes + n*ho*wo, is exactly what is touched (rtseg_upsample_argmax_host_scratch_bytes)
+  uint8_t *dlab = static_cast<uint8_t *>(dev_scratch) + in_bytes;
   RTSEG_CUDA(cudaMemcpyAsync(dev_scratch, x_host, in_bytes, cudaMemcpyHostToDevice, st));
   if (int rc = rtseg_upsample_argmax(n, hi, wi, c, c, ho, wo, align, dtype, dev_scratch, dlab, nullptr, nullptr, 255,
                                      nullptr, stream))
@@ -692,6 +699,12 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
   RTSEG_CUDA(cudaMemcpyAsync(labels_host, dlab, out_bytes, cudaMemcpyDeviceToHost, st));
   RTSEG_CUDA(cudaStreamSynchronize(st));
   return RTSEG_OK;
+}
+
+extern "C" size_t rtseg_upsample_argmax_host_scratch_bytes(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho,
+                                                          int32_t wo, int32_t dtype) {
+  if (n <= 0 || hi <= 0 || wi <= 0 || c <= 0 || ho <= 0 || wo <= 0) return 0;
+  return (size_t)n * hi * wi * c * (dtype == RTSEG_BF16 ? 2 : 4) + (size_t)n * ho * wo;
 }
 
 static int avgpool3x3s2_impl(int32_t n, int32_t h, int32_t w, int32_t c, int32_t x_is_nchw, int32_t x_dtype,

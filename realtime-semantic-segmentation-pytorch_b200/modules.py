@@ -89,7 +89,7 @@ class _FusedConvMixin:
         conv, bn, act = self._parts()
         tensors = [conv.weight, conv.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
-        return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act))
+        return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act, host=True))
 
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, act2=0, r_coff=0):
         if self[1].training and self[0].groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff, act2, r_coff):
@@ -127,7 +127,7 @@ class Conv2d(nn.Conv2d):
                 raise NotImplementedError("training through a bare convolution with a fused activation is not built")
             return y
         tensors = [self.weight, self.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
-        folded, post = cache.get(tensors, lambda: ops.fold_conv(self, bn, act))
+        folded, post = cache.get(tensors, lambda: ops.fold_conv(self, bn, act, host=True))
         _check_eval(self, bn)
         y = ops.conv(folded, ops.to_nhwc(x), res=res, res_mode=res_mode, out=out, x_coff=x_coff, y_coff=y_coff)
         return post(y) if post is not None else y
@@ -257,7 +257,7 @@ class DeConvBNAct(nn.Module):
         conv, bn, act = self.up_conv[0], self.up_conv[1], self.up_conv[2].activation
         tensors = [conv.weight, conv.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
-        return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act))
+        return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act, host=True))
 
     def forward(self, x, labels=None, want_logits=True):
         if self.up_conv[1].training and labels is None:
@@ -288,6 +288,10 @@ class PyramidPoolingModule(nn.Module):
         self.conv = PWConvBNAct(2 * in_channels, out_channels, act_type=act_type, bias=bias)
 
     def forward(self, x):
+        if self.conv[1].training or (torch.is_grad_enabled() and x.requires_grad):
+            raise NotImplementedError("PyramidPoolingModule: the pooling / resize kernels have no backward, so a training-"
+                                      "mode forward would leave the stage convolutions without gradients; call .eval() "
+                                      "under torch.no_grad() (no silent partial autograd graph)")
         x = ops.to_nhwc(x)
         n, c, h, w = x.shape
         stages = [self.stage1, self.stage2, self.stage3, self.stage4]

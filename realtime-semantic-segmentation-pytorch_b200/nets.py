@@ -390,8 +390,8 @@ class DABNet(nn.Module):
         cache = self.__dict__.setdefault("_rtseg_cache8", _FoldCache())
 
         def build():
-            main, post = ops.fold_conv(conv, bn, act, in_slice=(0, cmain))
-            side, _ = ops.fold_conv(conv, None, None, in_slice=(cmain, conv.in_channels), tc_small_cin=True)
+            main, post = ops.fold_conv(conv, bn, act, in_slice=(0, cmain), host=True)
+            side, _ = ops.fold_conv(conv, None, None, in_slice=(cmain, conv.in_channels), tc_small_cin=True, host=True)
             side.shift = None  # the bias (if any) is applied once, by the main launch
             return main, side, post
         main, side, post = cache.get(tensors, build)

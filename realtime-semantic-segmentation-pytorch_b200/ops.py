@@ -34,6 +34,14 @@ def _require_cuda(x: torch.Tensor, what: str) -> None:
     _lib.sync_device(x.device.index)
 
 
+def _no_tape(x: torch.Tensor, what: str) -> None:
+    """Raw pointer launches are invisible to autograd: refuse inputs that are on the tape instead of silently
+    cutting the graph (the training path wraps its kernels in autograd Functions, train.py)."""
+    if torch.is_grad_enabled() and x.requires_grad:
+        raise NotImplementedError(f"{what} has no backward kernel: it cannot run on a tensor that requires grad "
+                                  "(call under torch.no_grad() / model.eval(), or use the modules train.py covers)")
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -159,21 +167,24 @@ def act_spec(module) -> Tuple[int, float, float, Optional[torch.Tensor], Optiona
     raise NotImplementedError(f"no fused epilogue for activation {type(m).__name__}")
 
 
-def fold_affine(cout: int, bias: Optional[torch.Tensor], bn: Optional[torch.nn.BatchNorm2d]):
+def fold_affine(cout: int, bias: Optional[torch.Tensor], bn: Optional[torch.nn.BatchNorm2d], host: bool = False):
     """Eval-mode BatchNorm (+ conv bias) as per-channel fp32 (scale, shift), folded in fp64."""
+    # host=True (inference fold caches): a few hundred bytes per layer, folded on the CPU so that no device kernels are
+    # spent on parameter preparation.  host=False (training, inside a captured step): stays on the device, no sync.
+    f64 = (lambda t: t.detach().to("cpu", torch.float64)) if host else (lambda t: t.detach().double())
     if bn is None:
         if bias is None:
             return None, None
-        return None, bias.detach().double()
+        return None, f64(bias)
     if bn.running_mean is None or bn.running_var is None:
         raise NotImplementedError("BatchNorm2d(track_running_stats=False) cannot be folded")
-    g = bn.weight.detach().double() if bn.weight is not None else torch.ones(cout, dtype=torch.float64, device=bn.running_mean.device)
-    b = bn.bias.detach().double() if bn.bias is not None else torch.zeros_like(g)
-    mean, var = bn.running_mean.detach().double(), bn.running_var.detach().double()
+    mean, var = f64(bn.running_mean), f64(bn.running_var)
+    g = f64(bn.weight) if bn.weight is not None else torch.ones_like(mean)
+    b = f64(bn.bias) if bn.bias is not None else torch.zeros_like(g)
     scale = g / torch.sqrt(var + bn.eps)
     shift = b - mean * scale
     if bias is not None:
-        shift = shift + bias.detach().double() * scale
+        shift = shift + f64(bias) * scale
     return scale, shift
 
 
@@ -182,7 +193,7 @@ def _f32(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
 
 
 def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
-              in_slice: Optional[Tuple[int, int]] = None, tc_small_cin: bool = False
+              in_slice: Optional[Tuple[int, int]] = None, tc_small_cin: bool = False, host: bool = False
               ) -> Tuple[Folded, Optional[torch.nn.Module]]:
     """Pack nn.Conv2d / nn.ConvTranspose2d (+BN, +activation) for the kernels.
 
@@ -191,7 +202,8 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
     nn = torch.nn
     device = device or conv.weight.device
     code, p0, p1, prelu_w, post = act_spec(act_module)
-    w = conv.weight.detach().to(device=device, dtype=torch.float32)
+    # host=True: packed on the CPU and uploaded once per layout (inference caches); else packed on the device
+    w = conv.weight.detach().to(device="cpu" if host else device, dtype=torch.float32)
     kh, kw = conv.kernel_size
     sh, sw = conv.stride
     dh, dw_ = conv.dilation
@@ -232,16 +244,17 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
     if w_kmaj is not None and (cin % 16 == 0 or (kind == "dense" and (cin > 4 or tc_small_cin))):
         # K (and N) zero-padded to multiples of 16; the conv kernel's input tensor map stops at the last real channel
         cpad, kpad = (cout + 15) // 16 * 16, (cin + 15) // 16 * 16
-        w_tc = torch.zeros((kh * kw, cpad, kpad), dtype=torch.bfloat16, device=device)
+        w_tc = torch.zeros((kh * kw, cpad, kpad), dtype=torch.bfloat16, device=w.device)
         w_tc[:, :cout, :cin] = w_kmaj.reshape(kh * kw, cout, cin).to(torch.bfloat16)
-    scale, shift = fold_affine(cout, conv.bias, bn)
+        w_tc = w_tc.to(device)
+    scale, shift = fold_affine(cout, conv.bias, bn, host)
     slope = None
     if prelu_w is not None:
-        slope = prelu_w.detach().float().reshape(-1)
+        slope = prelu_w.detach().to(w.device, torch.float32).reshape(-1)
         slope = slope.expand(cout) if slope.numel() == 1 else slope
         if slope.numel() != cout:
             raise ValueError("PReLU num_parameters must be 1 or the number of output channels")
-    f = Folded(kind, cin, cout, kh, kw, sh, dh, ph, pw, w_f32, w_tc, _f32(scale, device), _f32(shift, device),
+    f = Folded(kind, cin, cout, kh, kw, sh, dh, ph, pw, w_f32.to(device), w_tc, _f32(scale, device), _f32(shift, device),
                _f32(slope, device), code, p0, p1)
     return f, post
 
@@ -419,6 +432,7 @@ def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor, y_coff: int, x_coff: int = 
 def upsample_bilinear(x: torch.Tensor, size: Tuple[int, int], align_corners: bool, out: Optional[torch.Tensor] = None,
                       y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
     _require_cuda(x, "upsample_bilinear")
+    _no_tape(x, "upsample_bilinear")
     if not is_nhwc(x):
         x = to_nhwc(x)
     n, x_ct, hi, wi = x.shape
@@ -442,6 +456,7 @@ def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: 
     utils/metrics.py.  `logits` is the low-resolution [N, C, h, w] tensor.
     """
     _require_cuda(logits, "upsample_argmax")
+    _no_tape(logits, "upsample_argmax")
     x = to_nhwc(logits)
     n, x_ct, hi, wi = x.shape
     c = num_classes if num_classes is not None else x_ct  # a padded logits buffer carries extra channels
@@ -515,6 +530,7 @@ def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] 
     grid of equal cells that the target cells tile exactly, then to p x p — the mean of equal-sized cell means
     is the cell mean, and every block of the first stage reads a short run of pixels."""
     _require_cuda(x, "adaptive_avgpool")
+    _no_tape(x, "adaptive_avgpool")
     n, x_ct, h, w = x.shape
     c = c if c is not None else x_ct
     out_dtype = out_dtype or x.dtype
@@ -569,6 +585,7 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
                  y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
     """F.avg_pool2d(x, 3, 2, 1) (reference models/dabnet.py:32-34) from an NCHW or NHWC tensor into an NHWC slice."""
     _require_cuda(x, "avgpool3x3s2")
+    _no_tape(x, "avgpool3x3s2")
     if x.dtype == torch.uint8:
         x = as_image_u8(x)
     n, x_ct, h, w = x.shape
@@ -600,6 +617,7 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
 def channel_shuffle(x: torch.Tensor, groups: int = 2) -> torch.Tensor:
     """channel_shuffle (reference models/modules.py:18-32) as one NHWC permutation kernel."""
     _require_cuda(x, "channel_shuffle")
+    _no_tape(x, "channel_shuffle")
     x = to_nhwc(x)
     n, c, h, w = x.shape
     out = torch.empty_like(x, memory_format=torch.channels_last)

@@ -490,6 +490,84 @@ def test_c_abi_host_buffer_entry_point():
     assert ctypes.sizeof(ctypes.c_void_p) == 8
 
 
+def test_c_abi_host_buffer_scratch_is_exactly_the_documented_size():
+    """A caller that sizes the scratch as include/rtseg.h says (logits bytes + n*ho*wo) must not be written past:
+    logits size not a multiple of 256 bytes, guard bytes behind the scratch stay untouched."""
+    from rtseg_b200 import _lib
+    lib = _lib.load()
+    _lib.sync_device(0)
+    n, hi, wi, c, ho, wo = 1, 7, 9, 19, 28, 36            # 7*9*19*4 = 4788 bytes, 4788 % 256 = 180
+    need = lib.rtseg_upsample_argmax_host_scratch_bytes(n, hi, wi, c, ho, wo, 0)
+    assert need == n * hi * wi * c * 4 + n * ho * wo and (n * hi * wi * c * 4) % 256 != 0
+    x = seeded((n, hi, wi, c), 46).contiguous()
+    labels = torch.empty((n, ho, wo), dtype=torch.uint8)
+    buf = torch.full((need + 512,), 0xA5, dtype=torch.uint8, device="cuda")
+    rc = lib.rtseg_upsample_argmax_host(n, hi, wi, c, ho, wo, 1, 0, x.data_ptr(), labels.data_ptr(), buf.data_ptr(),
+                                        torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, _lib.last_error()
+    assert (buf[need:] == 0xA5).all(), "the call wrote behind the documented scratch size"
+    ref = ref_head.upsample_argmax(x.permute(0, 3, 1, 2), (ho, wo), True)
+    assert (labels.long() == ref).float().mean().item() >= 0.999
+
+
+@pytest.mark.parametrize("align", [True, False])
+def test_fused_head_with_infinite_logits_matches_torch(align):
+    """+inf / -inf logits: torch interpolates them to +-inf (or NaN where inf meets -inf or a zero weight) and max picks
+    accordingly; a pixel whose logits are all -inf keeps class 0 and never lands outside [0, c) in the histogram."""
+    from rtseg_b200 import ops
+    c, hi, wi, ho, wo = 19, 12, 16, 96, 128
+    x = seeded((2, c, hi, wi), 47)
+    x[0, 3, 2, 3] = float("inf")
+    x[0, 5, 2, 4] = float("-inf")
+    x[0, 7, 6:8, 6:8] = float("inf")
+    x[1, :, 4, 5] = float("-inf")           # every class -inf at one source pixel
+    x[1, :, 4, 6] = float("-inf")
+    x[1, :, 5, 5:7] = float("-inf")
+    x[1, 2, 9, 9] = float("nan")
+    up = F.interpolate(x, (ho, wo), mode="bilinear", align_corners=align)
+    ref = up.max(dim=1)[1]
+    target = torch.randint(0, c, (2, ho, wo), generator=torch.Generator().manual_seed(3))
+    cm = torch.zeros((c, c), dtype=torch.int64, device="cuda")
+    got = ops.upsample_argmax(x.cuda(), (ho, wo), align, target=target.cuda(), confmat=cm).cpu().long()
+    assert int(got.max()) < c
+    finite = torch.isfinite(up).all(dim=1)
+    top2 = up.topk(2, dim=1)[0]
+    clear = ~finite | ((top2[:, 0] - top2[:, 1]) > 1e-4)
+    assert (got[clear] == ref[clear]).all(), "non-finite pixels must follow torch.max exactly"
+    assert cm.sum().item() == target.numel()
+    assert np.array_equal(cm.cpu().numpy(), ref_head.confusion_matrix(got.numpy(), target.numpy(), c, 255))
+
+
+def test_labels_head_accepts_an_odd_label_address():
+    """The 16-bit paired label store needs a 2-byte aligned class map; an odd address takes the general path."""
+    from rtseg_b200 import modules, ops
+    m = _randomise(modules.DeConvBNAct(16, 19, act_type="relu"), 63).cuda()
+    x = seeded((1, 16, 20, 72), 64).to("cuda", torch.bfloat16)
+    raw = torch.zeros(40 * 144 + 2, dtype=torch.uint8, device="cuda")
+    even, odd = raw[:40 * 144].view(1, 40, 144), raw[1:40 * 144 + 1].view(1, 40, 144)
+    with torch.no_grad():
+        m(x, labels=even, want_logits=False)
+        want = even.clone()
+        raw.zero_()
+        m(x, labels=odd, want_logits=False)
+    assert ops.tc_timeout_flag() == 0
+    assert odd.data_ptr() % 2 == 1 and torch.equal(odd, want)
+
+
+def test_raw_ops_refuse_tensors_on_the_autograd_tape():
+    from rtseg_b200 import modules, ops
+    x = torch.randn(1, 8, 8, 8, device="cuda", requires_grad=True)
+    for fn in (lambda: ops.upsample_bilinear(x, (16, 16), True), lambda: ops.adaptive_avgpool(x, 2),
+               lambda: ops.channel_shuffle(x, 2), lambda: ops.avgpool3x3s2(x)):
+        with pytest.raises(NotImplementedError, match="no backward"):
+            fn()
+    ppm = modules.PyramidPoolingModule(8, 8, "relu").cuda()       # training mode
+    with pytest.raises(NotImplementedError, match="PyramidPoolingModule"):
+        ppm(x.detach())
+    with torch.no_grad():
+        assert ppm.eval()(x).shape == (1, 8, 8, 8)
+
+
 # --------------------------------------------------- DABNet / LEDNet building blocks ----
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("shape", [(2, 3, 32, 64), (1, 3, 17, 33), (1, 8, 9, 7)])

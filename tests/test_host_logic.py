@@ -163,3 +163,73 @@ def test_shard_range_partitions_batch():
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             sizes = [b - a for a, b in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+# ------------------------------------------------------------------ convert() / fused_head() host logic (no GPU) ----
+def test_convert_reclasses_reference_layout_in_place():
+    import rtseg_b200
+    from rtseg_b200 import modules, nets
+    from tests import ref_layout
+    for name, counts in (("erfnet", {"NonBt1DBlock": 17, "InitialBlock": 3, "Conv2d": 17, "ERFNet": 1}),
+                         ("fastscnn", {"InvertedResidual": 8, "FeatureFusionModule": 1, "LearningToDownsample": 1, "FastSCNN": 1})):
+        m = ref_layout.LAYOUTS[name](num_class=19)
+        before = {k: v.data_ptr() for k, v in m.state_dict().items()}
+        assert rtseg_b200.convert(m) is m
+        assert isinstance(m, nets.MODEL_HUB[name]) and m.num_class == 19 and hasattr(m, "predict")
+        assert {k: v.data_ptr() for k, v in m.state_dict().items()} == before      # same tensors, same keys, same order
+        assert m._rtseg_converted == counts
+        assert rtseg_b200.convert(m)._rtseg_converted == {}                         # idempotent
+    assert isinstance(m.feature_fusion.higher_res_conv, modules.Conv2d)
+
+
+def test_convert_leaves_lookalike_classes_alone():
+    """A class that only shares a NAME with a known block (other model files of the reference define their own
+    InitialBlock / InvertedResidual variants) must keep its forward."""
+    import torch.nn as nn
+    import rtseg_b200
+
+    class NonBt1DBlock(nn.Module):   # same name, different structure
+        def __init__(self):
+            super().__init__()
+            self.conv = nn.Sequential(nn.Conv2d(4, 4, 3, padding=1), nn.ReLU())
+
+        def forward(self, x):
+            return self.conv(x)
+
+    m = nn.Sequential(NonBt1DBlock())
+    rtseg_b200.convert(m)
+    assert type(m[0]) is NonBt1DBlock and type(m[0].conv[0]) is nn.Conv2d and m._rtseg_converted == {}
+
+
+def test_deferred_logits_routes_max_to_the_fused_head(monkeypatch):
+    """fused_head() logic with the two kernels stubbed by their torch definitions (CPU): max / argmax over dim 1 never
+    materialise the logits, every other use does, and the values equal plain interpolate + max."""
+    import torch.nn.functional as F
+    import sys
+    import rtseg_b200
+    cv = sys.modules[rtseg_b200.convert.__module__]      # the module (the package re-exports the function under the same name)
+    calls = {"argmax": 0, "bilinear": 0}
+
+    def fake_argmax(low, size, align, out_dtype=torch.int64, **kw):
+        calls["argmax"] += 1
+        return F.interpolate(low, size, mode="bilinear", align_corners=align).max(1)[1].to(out_dtype)
+
+    def fake_bilinear(low, size, align, **kw):
+        calls["bilinear"] += 1
+        return F.interpolate(low, size, mode="bilinear", align_corners=align)
+    monkeypatch.setattr(cv.ops, "upsample_argmax", fake_argmax)
+    monkeypatch.setattr(cv.ops, "upsample_bilinear", fake_bilinear)
+    low = torch.randn(2, 5, 4, 6)
+    want = F.interpolate(low, (16, 24), mode="bilinear", align_corners=True)
+    d = cv.DeferredLogits(low, (16, 24), True)
+    assert tuple(d.shape) == (2, 5, 16, 24) and d.size()[2:] == (16, 24) and d.dim() == 4 and d.dtype == torch.float32
+    assert torch.equal(d.max(dim=1)[1], want.max(1)[1]) and torch.equal(torch.max(d, 1)[1], want.max(1)[1])
+    assert torch.equal(d.argmax(dim=1), want.argmax(1)) and torch.equal(d.max(1, keepdim=True)[1], want.max(1, keepdim=True)[1])
+    assert calls == {"argmax": 4, "bilinear": 0}
+    values, indices = d.max(dim=1)
+    assert torch.equal(values, want.max(1)[0]) and calls["bilinear"] == 1           # values need the logits
+    assert torch.equal(d + 1, want + 1) and torch.equal(torch.softmax(d, 1), torch.softmax(want, 1))
+    assert calls["bilinear"] == 1                                                    # materialised once, then cached
+    # the mode only defers CUDA tensors: on the CPU F.interpolate stays itself
+    with cv.fused_head():
+        assert not isinstance(F.interpolate(low, (16, 24), mode="bilinear", align_corners=True), cv.DeferredLogits)

@@ -58,6 +58,10 @@ def test_static_scratch_entry_point_matches_allocating_one_twice_in_a_row():
         # same kernels, same inputs: loss within the tolerance the other OHEM tests use, same branch and count
         assert abs(got[0].item() - want[0].item()) <= 1e-5 * max(1.0, abs(want[0].item()))
         assert got[2].item() == want[2].item() and got[3].item() == want[3].item()
+        # and against the CPU oracle itself (reference core/loss.py:6-20 restated), not only against the sibling entry point
+        from oracle import ref_ohem
+        ref_loss = ref_ohem.ohem_ce_loss(logits.cpu(), labels.cpu(), 0.7)[0].item()
+        assert abs(got[0].item() - ref_loss) <= 1e-5 * max(1.0, abs(ref_loss))
     assert {0.0, 1.0} == {float(_reference_entry_point(lib, lg, lb, thresh)[3]) for lg, lb in cases}
 
 
