@@ -297,7 +297,7 @@ class PyramidPoolingModule(nn.Module):
         stages = [self.stage1, self.stage2, self.stage3, self.stage4]
         hid = stages[0][1].out_channels
         cat = ops.empty_nhwc(n, c + 4 * hid, h, w, x.dtype, x.device)
-        cat[:, :c].copy_(x)  # data movement only
+        ops.copy_into_slice(x, cat)  # the pass-through operand of the concat
         for i, st in enumerate(stages):
             p = st[0].output_size
             p = p if isinstance(p, int) else p[0]

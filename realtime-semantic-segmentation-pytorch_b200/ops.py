@@ -614,6 +614,19 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
     return out
 
 
+def copy_into_slice(x: torch.Tensor, out: torch.Tensor, y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    """out[:, y_coff : y_coff + c] = x[:, x_coff : x_coff + c] for NHWC buffers: the permutation kernel with one group
+    (the identity permutation) — how a concat's pass-through operand reaches its slice without an ATen copy."""
+    _require_cuda(x, "copy_into_slice")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct - x_coff
+    if not (is_nhwc(x) and is_nhwc(out)) or x.dtype != out.dtype or tuple(out.shape[2:]) != (h, w) or out.shape[0] != n:
+        raise ValueError("copy_into_slice needs NHWC tensors of one dtype and one spatial size")
+    _lib.check(_lib.load().rtseg_channel_shuffle(n * h * w, c, 1, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                                 out.data_ptr(), out.shape[1], y_coff, _stream()), "rtseg_channel_shuffle")
+    return out
+
+
 def channel_shuffle(x: torch.Tensor, groups: int = 2) -> torch.Tensor:
     """channel_shuffle (reference models/modules.py:18-32) as one NHWC permutation kernel."""
     _require_cuda(x, "channel_shuffle")
