@@ -141,6 +141,20 @@ int rtseg_conv_tc_supported(const rtseg_conv_desc *d);
 int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, const float *scale,
                   const float *shift, const float *slope, const void *res, void *y,
                   rtseg_stream_t stream);
+/* ---- two convolutions of a NonBt1D block in one launch (tcgen05, bf16) -----
+ * Replaces ConvBNAct(c, c, (3,1)) -> ConvBNAct(c, c, (1,3)) — models/erfnet.py:65-66 — and the block tail
+ * ConvBNAct(c, c, (3,1)) -> Conv2d(c, c, (1,3)) -> `x += residual` -> BatchNorm2d -> Activation —
+ * models/erfnet.py:67-70, 77-81 — for undilated blocks with c in {16, 64}: the intermediate tensor stays in
+ * shared memory (written by the first epilogue in the layout the second MMA reads), so the pair moves
+ * (read x, write y) instead of (read x, write t, read t, write y) through HBM.
+ *   d       describes the FIRST conv (kh = 3, kw = 1, pad (1, 0), stride 1, dil 1, cin == cout) and carries the
+ *           second stage's activation (act, act_p0, act_p1), res_mode (NONE or PRE) and the x / y / r slices
+ *   w1, w2  bf16 [3][c][c] (tap, cout, cin); scale / shift: folded BatchNorm of each stage (NULL = identity)
+ *   act1    activation after the first conv: none / relu / relu6                                           */
+int rtseg_conv_pair_tc_supported(const rtseg_conv_desc *d, int32_t act1);
+int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const void *w1_bf16, const float *scale1,
+                       const float *shift1, int32_t act1, const void *w2_bf16, const float *scale2,
+                       const float *shift2, const void *res, void *y, rtseg_stream_t stream);
 /* Every mbarrier wait in the tensor-core kernels carries a ~2 s watchdog: a
  * lost TMA or a wrong descriptor ends the kernel with garbage output and sets
  * a device flag instead of hanging the GPU.  This call synchronises `stream`,

@@ -115,6 +115,12 @@ class _FusedConvMixin:
 class Conv2d(nn.Conv2d):
     """Bare convolution (what conv1x1 / conv3x3 return) routed to the same kernels."""
 
+    def folded(self, bn=None, act=None):
+        """(Folded, post module) of this convolution with an optional BatchNorm / activation behind it."""
+        cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
+        tensors = [self.weight, self.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
+        return cache.get(tensors, lambda: ops.fold_conv(self, bn, act, host=True))
+
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, bn=None, act=None):
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
         if self.training and (bn is None or bn.training) and self.groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff) \

@@ -99,8 +99,25 @@ class NonBt1DBlock(nn.Module):
         )
         self.bn_act = nn.Sequential(nn.BatchNorm2d(channels), Activation(act_type, inplace=True))
 
+    def _pairs(self, x):
+        """The block as two fused pair launches when the kernel covers it (bf16, undilated, 16 / 64 channels)."""
+        if self.bn_act[0].training or any(self.conv[i][1].training for i in range(3)) or x.dtype != torch.bfloat16:
+            return None
+        fa, pa = self.conv[0]._folded()
+        fb, pb = self.conv[1]._folded()
+        fc, pc = self.conv[2]._folded()
+        fd, pd = self.conv[3].folded(self.bn_act[0], self.bn_act[1].activation)
+        if pa is not None or pb is not None or pc is not None or pd is not None:
+            return None
+        if not (ops.conv_pair_supported(fa, fb, x) and ops.conv_pair_supported(fc, fd, x, res=x)):
+            return None
+        return ops.conv_pair(fc, fd, ops.conv_pair(fa, fb, x), res=x)
+
     def forward(self, x):
         x = ops.to_nhwc(x)
+        y = self._pairs(x)
+        if y is not None:
+            return y
         t = self.conv[0](x)
         t = self.conv[1](t)
         t = self.conv[2](t)

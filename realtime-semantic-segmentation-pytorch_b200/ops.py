@@ -383,6 +383,47 @@ def normalize_u8(x: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.T
     return ((x.float() - mean.view(1, c, 1, 1)) * rden.view(1, c, 1, 1)).to(dtype).contiguous(memory_format=torch.channels_last)
 
 
+USE_PAIR_FUSION = True   # module-level switch (tests / A-B runs): fused 3x1 -> 1x3 pairs of NonBt1D blocks
+
+
+def conv_pair_supported(fa: Folded, fb: Folded, x: torch.Tensor, res: Optional[torch.Tensor] = None) -> bool:
+    """Can `conv(fb, conv(fa, x)) (+ res before fb's BatchNorm)` run as one rtseg_conv_pair_tc launch?"""
+    if not (USE_PAIR_FUSION and USE_TENSOR_CORES and x.is_cuda and x.dtype == torch.bfloat16 and is_nhwc(x)):
+        return False
+    if fa.kind != "dense" or fb.kind != "dense" or fa.w_tc is None or fb.w_tc is None or fa.slope is not None or fb.slope is not None:
+        return False
+    if (fa.kh, fa.kw, fa.pad_h, fa.pad_w, fa.stride, fa.dil) != (3, 1, 1, 0, 1, 1) or \
+            (fb.kh, fb.kw, fb.pad_h, fb.pad_w, fb.stride, fb.dil) != (1, 3, 0, 1, 1, 1):
+        return False
+    if not (fa.cin == fa.cout == fb.cin == fb.cout == x.shape[1]):
+        return False
+    n, ct, h, w = x.shape
+    d = _desc(fa, n, h, w, BF16, ct, 0, fb.cout, 0, RES_PRE if res is not None else RES_NONE, fb.cout if res is not None else 0, 0,
+              act=fb.act)
+    d.act_p0, d.act_p1 = fb.p0, fb.p1
+    return bool(_lib.load().rtseg_conv_pair_tc_supported(C.byref(d), fa.act))
+
+
+def conv_pair(fa: Folded, fb: Folded, x: torch.Tensor, res: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """act_b(bn_b(conv1x3_b(act_a(bn_a(conv3x1_a(x)))) [+ res])) in one launch (reference models/erfnet.py:65-71, 77-81)."""
+    _require_cuda(x, "conv_pair")
+    n, ct, h, w = x.shape
+    if out is None:
+        out = empty_nhwc(n, fb.cout, h, w, x.dtype, x.device)
+    r_ct = 0
+    if res is not None:
+        if not is_nhwc(res) or res.dtype != x.dtype or tuple(res.shape) != (n, res.shape[1], h, w):
+            raise ValueError("bad residual tensor")
+        r_ct = res.shape[1]
+    d = _desc(fa, n, h, w, BF16, ct, 0, out.shape[1], 0, RES_PRE if res is not None else RES_NONE, r_ct, 0, act=fb.act)
+    d.act_p0, d.act_p1 = fb.p0, fb.p1
+    _lib.check(_lib.load().rtseg_conv_pair_tc(C.byref(d), x.data_ptr(), fa.w_tc.data_ptr(), _ptr(fa.scale), _ptr(fa.shift),
+                                              fa.act, fb.w_tc.data_ptr(), _ptr(fb.scale), _ptr(fb.shift), _ptr(res),
+                                              out.data_ptr(), _stream()), "rtseg_conv_pair_tc")
+    return out
+
+
 def stem(f: Folded, x: torch.Tensor, pool: bool, out_dtype: torch.dtype, out: Optional[torch.Tensor] = None,
          y_coff: int = 0) -> torch.Tensor:
     """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor, or from the uint8 HWC image
