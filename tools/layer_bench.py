@@ -69,6 +69,15 @@ def erfnet_layers(batch, only, reps):
                     continue
                 with torch.no_grad():
                     report(name, time_ms(fn, reps), passes * elems * 2 + 3 * c * c * 2, 2.0 * 3 * c * c * batch * h * w)
+            if d == 1 and c in (16, 64):   # fused pairs: algorithmic bytes = read x (+ res), write y — no intermediate
+                fa, fb = blk.conv[0]._folded()[0], blk.conv[1]._folded()[0]
+                fc, fd = blk.conv[2]._folded()[0], blk.conv[3].folded(blk.bn_act[0], blk.bn_act[1].activation)[0]
+                for name, fn, passes in [(f"{tag} pair 3x1->1x3 (one launch)", lambda: ops.conv_pair(fa, fb, x), 2),
+                                         (f"{tag} pair 3x1->1x3 +res+bn+act (one launch)", lambda: ops.conv_pair(fc, fd, x, res=r), 3)]:
+                    if only and only not in name:
+                        continue
+                    with torch.no_grad():
+                        report(name, time_ms(fn, reps), passes * elems * 2 + 6 * c * c * 2, 2.0 * 6 * c * c * batch * h * w)
         del x, r
     # downsamplers and deconvs
     for name, mod, shape in [
