@@ -19,8 +19,8 @@
 // column of a tile row are halo: stage 2 produces garbage there, which is never stored.  T outside the image is
 // forced to zero by the stage-1 epilogue (the second convolution pads T, not X).
 //
-// Roles (320 threads, one persistent CTA per SM): warp 0 streams X tiles through an mbarrier ring with TMA; warp 1
-// issues both stages' MMAs (stage 1 of tile i+1 ahead of stage 2 of tile i); warps 2-9 run the two epilogues
+// Roles (576 threads, one persistent CTA per SM): warp 0 streams X tiles through an mbarrier ring with TMA; warp 1
+// issues both stages' MMAs (stage 1 of tile i+1 ahead of stage 2 of tile i); warps 2-17 run the two epilogues
 // interleaved — A(i): stage-1 accumulator -> BN/ReLU -> T in shared memory; B(i-1): stage-2 accumulator (+ residual,
 // which a TMA load has placed in the staging buffer) -> BN/act -> staging -> TMA store.  Accumulators are double
 // buffered in TMEM for both stages.
@@ -37,7 +37,7 @@ namespace rtseg {
 
 namespace {
 
-constexpr int kPairEpiWarps = 8;
+constexpr int kPairEpiWarps = 16;   // four warps per TMEM lane quarter: the epilogues are issue-bound, not bandwidth-bound
 constexpr int kPairEpiThreads = 32 * kPairEpiWarps;
 constexpr int kPairThreads = 64 + kPairEpiThreads;
 constexpr int kPairMaxNx = 6;
@@ -73,6 +73,39 @@ __device__ __forceinline__ uint64_t pair_desc(uint32_t addr) {
   return (uint64_t)((addr & 0x3ffffu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
 }
 
+// {lo half = bf16(max(a, 0)), hi half = bf16(max(b, 0))}: conversion and ReLU in one instruction (NaN stays NaN).
+__device__ __forceinline__ uint32_t pack_relu_bf16(float a, float b) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
+
+// 16 accumulator columns (+ residual) -> folded BatchNorm -> clamp -> 8 packed bf16 pairs.  RELU: the clamp is
+// [0, inf) and rides in the conversion; otherwise NaN-propagating max / min with (lo, hi).
+template <bool RELU, bool RES>
+__device__ __forceinline__ void affine_pack16(const uint32_t (&v)[16], const float (&rv)[16], uint32_t s_sc, uint32_t s_sh,
+                                              float lo, float hi, uint32_t (&pk)[8]) {
+#pragma unroll
+  for (int e4 = 0; e4 < 16; e4 += 4) {
+    const float4 sc = lds128(s_sc + (uint32_t)e4 * 4), sh = lds128(s_sh + (uint32_t)e4 * 4);
+    float o[4] = {__uint_as_float(v[e4]), __uint_as_float(v[e4 + 1]), __uint_as_float(v[e4 + 2]), __uint_as_float(v[e4 + 3])};
+    if constexpr (RES) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) o[u] += rv[e4 + u];   // += x before the BatchNorm (reference models/erfnet.py:79-80)
+    }
+    o[0] = fmaf(o[0], sc.x, sh.x), o[1] = fmaf(o[1], sc.y, sh.y), o[2] = fmaf(o[2], sc.z, sh.z), o[3] = fmaf(o[3], sc.w, sh.w);
+    if constexpr (RELU) {
+      pk[(e4 >> 1) + 0] = pack_relu_bf16(o[0], o[1]);
+      pk[(e4 >> 1) + 1] = pack_relu_bf16(o[2], o[3]);
+    } else {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) o[u] = fmin_nan(fmax_nan(o[u], lo), hi);
+      pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
+      pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
+    }
+  }
+}
+
 template <int KB, bool RES>
 __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __grid_constant__ PairMaps maps,
                                                                        const PairParams p, const float *__restrict__ scale1,
@@ -87,16 +120,16 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
   const uint32_t s_w = s_base;                                 // 6 weight blocks: W1[0..2], W2[0..2]
   const uint32_t s_x = s_w + 6 * p.w_block_bytes;
   const uint32_t s_t1 = s_x + (uint32_t)p.nx * p.x_stage_bytes;
-  const uint32_t s_out = s_t1 + p.t1_bytes;
+  const uint32_t s_out = s_t1 + 2 * p.t1_bytes;                // T is double buffered: A(i+1) never waits for stage 2 of tile i
   const uint32_t s_aff = s_out + (uint32_t)p.out_bufs * p.out_buf_bytes;  // scale1, shift1, scale2, shift2
   const uint32_t s_bars = s_aff + 4u * KB * 4;
   const uint32_t full_x = s_bars, empty_x = full_x + 8 * kPairMaxNx;
   const uint32_t w_bar = empty_x + 8 * kPairMaxNx;
   const uint32_t s1_full = w_bar + 8, s1_empty = s1_full + 16, s2_full = s1_empty + 16, s2_empty = s2_full + 16;
-  const uint32_t t1_full = s2_empty + 16, res_full = t1_full + 8;
+  const uint32_t t1_full = s2_empty + 16, res_full = t1_full + 16;  // t1_full[2]: one per T buffer; res_full[3]: one per staging buffer
   uint8_t *gen = smem_raw + (s_base - smem_u32(smem_raw));
   float *g_aff = reinterpret_cast<float *>(gen + (s_aff - s_base));
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(gen + (res_full + 16 - s_base));
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(gen + (res_full + 24 - s_base));
   volatile uint32_t *dead = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -106,9 +139,10 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     for (int s = 0; s < 2; ++s) {
       mbar_init(s1_full + 8 * s, 1), mbar_init(s1_empty + 8 * s, kPairEpiWarps);
       mbar_init(s2_full + 8 * s, 1), mbar_init(s2_empty + 8 * s, kPairEpiWarps);
-      mbar_init(res_full + 8 * s, 1);
     }
-    mbar_init(t1_full, kPairEpiWarps);
+    for (int s = 0; s < 3; ++s) mbar_init(res_full + 8 * s, 1);
+    // one barrier per T buffer: a warp that runs one tile ahead arrives on the other barrier, never on this one early
+    for (int s = 0; s < 2; ++s) mbar_init(t1_full + 8 * s, kPairEpiWarps);
     *dead = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -189,11 +223,11 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     };
     auto issue_s2 = [&](int i) {
       const uint32_t b = (uint32_t)i & 1u, use = (uint32_t)i >> 1;
-      mbar_wait(t1_full, (uint32_t)i & 1u, dead);               // every epilogue warp has written (and fenced) its part of T
+      mbar_wait(t1_full + 8 * b, use & 1u, dead);               // every epilogue warp has written (and fenced) its part of T[b]
       mbar_wait(s2_empty + 8 * b, (use & 1u) ^ 1u, dead);
       tc_fence_after();
       if (elect_one()) {
-        const uint64_t a0 = pair_desc<KB>(s_t1) - (uint64_t)(kRowB >> 4);   // tap 0 starts one pixel row before g
+        const uint64_t a0 = pair_desc<KB>(s_t1 + b * p.t1_bytes) - (uint64_t)(kRowB >> 4);   // tap 0 starts one pixel row before g
         for (int m = 0; m < p.mc; ++m) {
           const uint32_t d = tmem_base + (2u + b) * acc_cols + (uint32_t)(m * KB);
 #pragma unroll
@@ -217,53 +251,64 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     // ========================================================= epilogue ====
     const int e = warp - 2;
     const int q = warp & 3;          // TMEM lane quarter of this warp
-    const int hsel = e >> 2;         // which of the two warps of the quarter
+    const int sub = e >> 2;          // which of the four warps of the quarter: items sub, sub + 4, ...
     const int row = q * 32 + lane;   // pixel inside a chunk
     const bool elected = threadIdx.x == 64;
     const int items = p.mc * kGroups;                 // (chunk, 16-column group) pairs per stage
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
     const uint32_t s_sc1 = s_aff, s_sh1 = s_aff + KB * 4, s_sc2 = s_aff + 2 * KB * 4, s_sh2 = s_aff + 3 * KB * 4;
+    const bool relu1 = p.lo1 == 0.f && p.hi1 > 3.0e38f, relu2 = p.lo2 == 0.f && p.hi2 > 3.0e38f;   // warp-uniform
 
-    if (RES && elected) {  // residual tiles of the first two units: straight into the staging buffers
+    if (RES && elected) {  // residual tiles of the first units: straight into the staging buffers
       prefetch_tmap(&maps.r);
-      for (int j = 0; j < 2 && j < n_my; ++j) {
+      for (int j = 0; j < p.out_bufs && j < n_my; ++j) {
         int w0, h0, img;
         tile_coords(j, w0, h0, img);
         mbar_expect_tx(res_full + 8 * j, p.o_tx_bytes);
         tma_load_4d(s_out + (uint32_t)j * p.out_buf_bytes, &maps.r, res_full + 8 * j, p.r_coff, w0, h0, img);
       }
     }
+    // tile -> (image, tile row, tile column), advanced by the decomposed grid stride: no division per tile
+    int twi, thi, img, step_w, step_h, step_n;
+    {
+      const int r0 = (int)blockIdx.x / p.tiles_w, rs = (int)gridDim.x / p.tiles_w;
+      twi = (int)blockIdx.x % p.tiles_w, thi = r0 % p.tiles_h, img = r0 / p.tiles_h;
+      step_w = (int)gridDim.x % p.tiles_w, step_h = rs % p.tiles_h, step_n = rs / p.tiles_h;
+    }
+    int pw0 = 0, ph0 = 0, pimg = 0;   // coordinates of the previous tile (stage B works one tile behind stage A)
+    uint32_t ob = 0, ob_use = 0;      // staging buffer of the tile stage B handles, and how often it has been used
+    float no_res[16];                 // (placeholder operand of the residual-free instantiations)
+#pragma unroll
+    for (int u = 0; u < 16; ++u) no_res[u] = 0.f;
 
     for (int i = 0; i <= n_my; ++i) {
+      const int w0 = twi * p.tw, h0 = thi * p.th, img0 = img;
       if (i < n_my) {
         // ---- A(i): stage-1 accumulator -> BN + clamp -> T (bf16, swizzled K-major) ----
         const uint32_t b = (uint32_t)i & 1u, use = (uint32_t)i >> 1;
-        int w0, h0, img;
-        tile_coords(i, w0, h0, img);
         mbar_wait(s1_full + 8 * b, use & 1u, dead);
-        if (i >= 1) mbar_wait(s2_full + 8 * (b ^ 1u), ((uint32_t)(i - 1) >> 1) & 1u, dead);   // stage 2 of tile i-1 has read T
+        // T[b] is free: stage 2 of tile i-2 read it, and B(i-2) — earlier in this warp's program order — waited for
+        // that stage's accumulator barrier
         tc_fence_after();
-        for (int k = hsel; k < items; k += 2) {
+        const uint32_t t_buf = s_t1 + b * p.t1_bytes;
+        const bool border = w0 == 0 || w0 + p.tw >= p.w;    // only these tiles hold T columns outside the image
+        for (int k = sub; k < items; k += 4) {
           const int m = k / kGroups, c0 = (k - m * kGroups) * 16;
-          uint32_t v[16];
+          uint32_t v[16], pk[8];
           tmem_ld16(lane_base + b * acc_cols + (uint32_t)(m * KB + c0), v);
           tmem_ld_wait();
+          if (relu1) affine_pack16<true, false>(v, no_res, s_sc1 + (uint32_t)c0 * 4, s_sh1 + (uint32_t)c0 * 4, p.lo1, p.hi1, pk);
+          else affine_pack16<false, false>(v, no_res, s_sc1 + (uint32_t)c0 * 4, s_sh1 + (uint32_t)c0 * 4, p.lo1, p.hi1, pk);
           const int g = m * 128 + row;
-          const int cimg = w0 - 1 + (g & (p.p - 1));
-          const float keep = (cimg >= 0 && cimg < p.w) ? 1.f : 0.f;   // T outside the image is the second conv's zero padding
-          uint32_t pk[8];
+          if (border) {   // T outside the image is the second conv's zero padding
+            const int cimg = w0 - 1 + (g & (p.p - 1));
+            if (cimg < 0 || cimg >= p.w) {
 #pragma unroll
-          for (int e4 = 0; e4 < 16; e4 += 4) {
-            const float4 sc = lds128(s_sc1 + (uint32_t)(c0 + e4) * 4), sh = lds128(s_sh1 + (uint32_t)(c0 + e4) * 4);
-            const float o0 = keep * fmin_nan(fmax_nan(fmaf(__uint_as_float(v[e4 + 0]), sc.x, sh.x), p.lo1), p.hi1);
-            const float o1 = keep * fmin_nan(fmax_nan(fmaf(__uint_as_float(v[e4 + 1]), sc.y, sh.y), p.lo1), p.hi1);
-            const float o2 = keep * fmin_nan(fmax_nan(fmaf(__uint_as_float(v[e4 + 2]), sc.z, sh.z), p.lo1), p.hi1);
-            const float o3 = keep * fmin_nan(fmax_nan(fmaf(__uint_as_float(v[e4 + 3]), sc.w, sh.w), p.lo1), p.hi1);
-            pk[(e4 >> 1) + 0] = pack_bf16(o0, o1);
-            pk[(e4 >> 1) + 1] = pack_bf16(o2, o3);
+              for (int u = 0; u < 8; ++u) pk[u] = 0u;
+            }
           }
           const uint32_t off0 = (uint32_t)g * kRowB + (uint32_t)c0 * 2;
-          const uint32_t a = s_t1 + (off0 ^ (((off0 >> 7) & kSwMask) << 4));
+          const uint32_t a = t_buf + (off0 ^ (((off0 >> 7) & kSwMask) << 4));
           sts128(a, pk[0], pk[1], pk[2], pk[3]);
           sts128(a ^ 16u, pk[4], pk[5], pk[6], pk[7]);
         }
@@ -272,21 +317,19 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(s1_empty + 8 * b);
-          mbar_arrive(t1_full);
+          mbar_arrive(t1_full + 8 * b);
         }
       }
       if (i >= 1) {
         // ---- B(j): stage-2 accumulator (+ residual) -> BN + clamp -> staging (compact TH x TW) -> TMA store ----
         const int j = i - 1;
         const uint32_t b = (uint32_t)j & 1u, use = (uint32_t)j >> 1;
-        int w0, h0, img;
-        tile_coords(j, w0, h0, img);
-        const uint32_t buf = s_out + (p.out_bufs == 2 ? b : 0u) * p.out_buf_bytes;
+        const uint32_t buf = s_out + ob * p.out_buf_bytes;
         mbar_wait(s2_full + 8 * b, use & 1u, dead);
-        if constexpr (RES) mbar_wait(res_full + 8 * b, use & 1u, dead);
+        if constexpr (RES) mbar_wait(res_full + 8 * ob, ob_use & 1u, dead);
         tc_fence_after();
-        if constexpr (!RES) pair_bar_sync(2);   // the elected thread has seen the previous store read the staging buffer
-        for (int k = hsel; k < items; k += 2) {
+        if constexpr (!RES) pair_bar_sync(2);   // the elected thread has seen the store before last read this buffer out
+        for (int k = sub; k < items; k += 4) {
           const int m = k / kGroups, c0 = (k - m * kGroups) * 16;
           uint32_t v[16];
           tmem_ld16(lane_base + (2u + b) * acc_cols + (uint32_t)(m * KB + c0), v);
@@ -305,21 +348,8 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
               for (int u = 0; u < 8; ++u) rv[2 * u] = bf16_lo(w8[u]), rv[2 * u + 1] = bf16_hi(w8[u]);
             }
             uint32_t pk[8];
-#pragma unroll
-            for (int e4 = 0; e4 < 16; e4 += 4) {
-              const float4 sc = lds128(s_sc2 + (uint32_t)(c0 + e4) * 4), sh = lds128(s_sh2 + (uint32_t)(c0 + e4) * 4);
-              float o[4] = {__uint_as_float(v[e4]), __uint_as_float(v[e4 + 1]), __uint_as_float(v[e4 + 2]), __uint_as_float(v[e4 + 3])};
-              if constexpr (RES) {
-#pragma unroll
-                for (int u = 0; u < 4; ++u) o[u] += rv[e4 + u];   // += x before the BatchNorm (reference models/erfnet.py:79-80)
-              }
-              o[0] = fmin_nan(fmax_nan(fmaf(o[0], sc.x, sh.x), p.lo2), p.hi2);
-              o[1] = fmin_nan(fmax_nan(fmaf(o[1], sc.y, sh.y), p.lo2), p.hi2);
-              o[2] = fmin_nan(fmax_nan(fmaf(o[2], sc.z, sh.z), p.lo2), p.hi2);
-              o[3] = fmin_nan(fmax_nan(fmaf(o[3], sc.w, sh.w), p.lo2), p.hi2);
-              pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
-              pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
-            }
+            if (relu2) affine_pack16<true, RES>(v, RES ? rv : no_res, s_sc2 + (uint32_t)c0 * 4, s_sh2 + (uint32_t)c0 * 4, p.lo2, p.hi2, pk);
+            else affine_pack16<false, RES>(v, RES ? rv : no_res, s_sc2 + (uint32_t)c0 * 4, s_sh2 + (uint32_t)c0 * 4, p.lo2, p.hi2, pk);
             sts128(a, pk[0], pk[1], pk[2], pk[3]);
             sts128(a ^ 16u, pk[4], pk[5], pk[6], pk[7]);
           }
@@ -330,17 +360,26 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         if (lane == 0) mbar_arrive(s2_empty + 8 * b);
         pair_bar_sync(1);        // every warp has written its part of the staging tile
         if (elected) {
-          tma_store_4d(&maps.y, buf, p.y_coff, w0, h0, img);
+          tma_store_4d(&maps.y, buf, p.y_coff, pw0, ph0, pimg);
           bulk_commit();
-          bulk_wait_read<0>();   // the staging buffer may be written again
-          if (RES && j + 2 < n_my) {   // ... first by the residual tile of the unit that uses this buffer next
+          bulk_wait_read<1>();   // the store BEFORE this one has read its buffer out: that buffer may be written again
+          if (RES && j >= 1 && j + 2 < n_my) {   // ... first by the residual tile of the unit that uses it next
             int w2, h2, img2;
             tile_coords(j + 2, w2, h2, img2);
-            mbar_expect_tx(res_full + 8 * b, p.o_tx_bytes);
-            tma_load_4d(buf, &maps.r, res_full + 8 * b, p.r_coff, w2, h2, img2);
+            const uint32_t nb = ob == 0 ? (uint32_t)p.out_bufs - 1u : ob - 1u;   // buffer of tile j-1 == buffer of tile j+2
+            mbar_expect_tx(res_full + 8 * nb, p.o_tx_bytes);
+            tma_load_4d(s_out + nb * p.out_buf_bytes, &maps.r, res_full + 8 * nb, p.r_coff, w2, h2, img2);
           }
         }
+        if (++ob == (uint32_t)p.out_bufs) ob = 0, ++ob_use;
       }
+      pw0 = w0, ph0 = h0, pimg = img0;
+      // next tile of this CTA
+      twi += step_w;
+      if (twi >= p.tiles_w) twi -= p.tiles_w, ++thi;
+      thi += step_h;
+      if (thi >= p.tiles_h) thi -= p.tiles_h, ++img;
+      img += step_n;
     }
     if (elected) bulk_wait_all();
   }
@@ -448,7 +487,7 @@ extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const
   PairParams p{};
   p.n = d->n, p.h = d->h, p.w = d->w, p.c = c;
   // 64 channels: 128-byte pixel rows, small tiles and a deep X ring; 16 channels: 32-byte rows, large tiles
-  if (c == 64) p.th = 4, p.p = 32; else p.th = 16, p.p = 64;
+  if (c == 64) p.th = 4, p.p = 32; else p.th = 8, p.p = 64;
   static const int th_knob = getenv("RTSEG_PAIR_TH") ? atoi(getenv("RTSEG_PAIR_TH")) : 0;
   if (th_knob > 0 && (th_knob * p.p) % 128 == 0) p.th = th_knob;
   p.tw = p.p - 2;
@@ -460,7 +499,7 @@ extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const
   p.num_tiles = (int)tiles;
   p.x_coff = d->x_coff, p.y_coff = d->y_coff, p.r_coff = d->r_coff;
   p.has_res = has_res ? 1 : 0;
-  p.out_bufs = has_res ? 2 : 1;
+  p.out_bufs = has_res ? 3 : 2;   // stores never block the epilogue; a residual tile lands two units ahead
   const uint32_t row_b = (uint32_t)c * 2;
   auto up1k = [](uint32_t v) { return (v + 1023u) / 1024u * 1024u; };
   p.x_tx_bytes = (uint32_t)(p.th + 2) * p.p * row_b;
@@ -469,8 +508,8 @@ extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const
   p.o_tx_bytes = (uint32_t)p.th * p.tw * row_b;
   p.out_buf_bytes = up1k(p.o_tx_bytes + row_b);   // (the pixel row behind T that tap 2 of the last pixel reads lies in here)
   p.w_block_bytes = up1k((uint32_t)c * row_b);
-  const uint32_t misc = 4u * c * 4 + (2 * kPairMaxNx + 12) * 8 + 64;
-  const uint32_t fixed = 6 * p.w_block_bytes + p.t1_bytes + (uint32_t)p.out_bufs * p.out_buf_bytes + misc;
+  const uint32_t misc = 4u * c * 4 + (2 * kPairMaxNx + 14) * 8 + 64;
+  const uint32_t fixed = 6 * p.w_block_bytes + 2 * p.t1_bytes + (uint32_t)p.out_bufs * p.out_buf_bytes + misc;
   RTSEG_REQUIRE(fixed + 2 * p.x_stage_bytes <= kPairSmemBudget, "pair plan: tiles do not fit in shared memory");
   p.nx = (int)std::min<uint32_t>(kPairMaxNx, (kPairSmemBudget - fixed) / p.x_stage_bytes);
   const uint32_t smem = fixed + (uint32_t)p.nx * p.x_stage_bytes + 1024;
