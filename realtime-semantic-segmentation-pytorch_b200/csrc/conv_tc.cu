@@ -55,7 +55,7 @@ constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 4;
 constexpr int kOutBufs = 2;
 constexpr int kMaxMyChunks = 8;  // 16-column chunks one epilogue warp may own (bn <= 256 split over two warps)
-constexpr uint32_t kSmemBudget = 220 * 1024;
+constexpr uint32_t kSmemBudget = 224 * 1024;
 
 struct TcTap {
   int16_t map;  // which A tensor map (parity view)
@@ -104,6 +104,7 @@ struct TcParams {
   uint32_t b_bytes;        // all resident weight blocks
   uint32_t out_buf_bytes;  // one staging buffer = ms * 128 * bn * 2
   int out_bufs;            // 2 (store of unit u overlaps the epilogue of u+1) or 1 when shared memory is tight
+  int split_out;           // 1: a staging buffer holds ONE ob-channel sub-box; the epilogue runs bn / ob passes per unit
   uint32_t tmem_cols;
   float lo, hi;            // fast epilogue: clamp(v, lo, hi) covers none / relu / relu6 / hardtanh
   float lo2, hi2;          // ... and clamp(v + res, lo2, hi2) the activation after a POST residual
@@ -431,8 +432,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       ck_tcol[ci] = (uint32_t)(sub * p.nacc * p.bn + c0);
       // 32-byte-aligned offset of the chunk in the staged box; its second 16-byte half is `^ 16`
       const uint32_t off0 = stage_row(sub) * ob_bytes + (uint32_t)(c0 % p.ob) * 2;
-      ck_st0[ci] = (uint32_t)(c0 / p.ob) * box_bytes + (off0 ^ (((off0 >> 7) & sw_mask) << 4));
+      // (split staging: the buffer holds this chunk's sub-box only)
+      ck_st0[ci] = (p.split_out ? 0u : (uint32_t)(c0 / p.ob) * box_bytes) + (off0 ^ (((off0 >> 7) & sw_mask) << 4));
     }
+    const uint32_t st_sb_bytes = p.split_out ? 0u : box_bytes;   // distance of consecutive sub-boxes inside a staging buffer
     uint32_t acc = 0, acc_phase = 0, unit = 0;
     uint32_t ring = 0, ring_phase = 0;  // position in the A ring (the residual stages live there)
     auto ring_advance = [&](int nsteps) {
@@ -564,14 +567,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           ring_advance(p.res_boxes);
         }
         for (int a = 0; a < p.nacc; ++a) {
-          const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
-          epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
           const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * acc_cols + (uint32_t)(a * p.bn);
           uint32_t v[2][16];
-          if (my_chunks > 0) tmem_ld16(tbase + ck_tcol[0], v[0]);
+          if (my_chunks > 0) tmem_ld16(tbase + ck_tcol[0], v[0]);   // (the prefetch chain runs on across passes)
+          // Split staging (wide layers, ms == 1): one pass per ob-channel sub-box through half-size staging buffers —
+          // the shared memory this frees goes to the A ring, and bytes in flight are what bound these layers.
+          const int npass = p.split_out ? p.bn / p.ob : 1;
+          for (int pass = 0; pass < npass; ++pass) {
+          const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
+          epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
 #pragma unroll
           for (int ci = 0; ci < kMy; ++ci) {
-            if (ci < my_chunks) {  // warp-uniform
+            if (ci < my_chunks && (!p.split_out || (int)(ck_meta[ci] >> 24) == pass)) {  // warp-uniform
               tmem_ld_wait();
               if (ci + 1 < kMy && ci + 1 < my_chunks) tmem_ld16(tbase + ck_tcol[ci + 1], v[(ci + 1) & 1]);
               const int c0 = (int)(ck_meta[ci] & 0xffffu);
@@ -580,7 +587,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 const uint32_t sb = ck_meta[ci] >> 24;
                 uint32_t rslot = res_first + sb;
                 if (rslot >= (uint32_t)p.stages) rslot -= (uint32_t)p.stages;
-                const uint32_t ra = s_a + rslot * kStageBytes + (ck_st0[ci] - sb * box_bytes);
+                const uint32_t ra = s_a + rslot * kStageBytes + (ck_st0[ci] - sb * st_sb_bytes);
                 const float4 f0 = lds128(ra), f1 = lds128(ra ^ 16u);
                 rres0 = make_uint4(__float_as_uint(f0.x), __float_as_uint(f0.y), __float_as_uint(f0.z), __float_as_uint(f0.w));
                 rres1 = make_uint4(__float_as_uint(f1.x), __float_as_uint(f1.y), __float_as_uint(f1.z), __float_as_uint(f1.w));
@@ -627,7 +634,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           fence_async_smem();
           epi_bar_sync(1);  // every warp has written its part of the staging tile
           if constexpr (RES) {
-            if (elected) {  // ... and has read its residual chunks: hand the ring stages back to the producer
+            if (elected && pass == npass - 1) {  // ... and has read its residual chunks: hand the ring stages back to the producer
               uint32_t rs = res_first;
               for (int sb = 0; sb < p.res_boxes; ++sb) {
                 mbar_arrive(empty_bar + 8 * rs);
@@ -636,14 +643,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
             }
           }
           if (elected) {
-            const int nbox = p.bn / p.ob;
-            for (int sb = 0; sb < nbox; ++sb)
-              tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * unit_w,
-                           thi * unit_h, img);
+            if (p.split_out) {
+              tma_store_4d(&maps.c[a], buf, p.y_co + co_base + pass * p.ob, twi * unit_w, thi * unit_h, img);
+            } else {
+              const int nbox = p.bn / p.ob;
+              for (int sb = 0; sb < nbox; ++sb)
+                tma_store_4d(&maps.c[a], buf + (uint32_t)sb * box_bytes, p.y_co + co_base + sb * p.ob, twi * unit_w,
+                             thi * unit_h, img);
+            }
             bulk_commit();
             if (p.out_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();  // the OTHER buffer is free again for the next unit
           }
           ++unit;
+          }
         }
       } else {
         // ---- general path: any activation, fused argmax, unaligned channel counts.  Compact code
@@ -764,7 +776,7 @@ static CUtensorMapSwizzle swizzle_for(int kb) {
 static int pick_kb(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : 16); }
 
 struct TcPlan {
-  int kb, bn, n_tiles, stages, ob, ms, out_bufs;
+  int kb, bn, n_tiles, stages, ob, ms, out_bufs, split_out;
   uint32_t b_block_bytes, b_bytes, out_buf_bytes, smem_bytes, tmem_cols, stage_bytes;
 };
 
@@ -784,7 +796,7 @@ static uint32_t tc_stage_bytes(int share, int halo, int ms, int kb) {
 }
 
 static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out, int max_ms, bool has_res,
-                    TcPlan &pl, int share = 0, int halo = 0) {
+                    TcPlan &pl, int share = 0, int halo = 0, bool allow_split = false) {
   const int chunk_cap = 2 * kMaxMyChunks;  // 16-column chunks per unit (two warps share)
   pl.kb = pick_kb(cin);
   const int nkb = cin / pl.kb;
@@ -835,6 +847,16 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
         (int)((kSmemBudget - fixed) / stage_bytes) < unit_boxes + 1) {
       out_bufs = 1;
       fixed -= out_buf;
+    }
+    // Split staging: stage one ob-channel sub-box at a time through two half-size buffers when that buys ring stages.
+    pl.split_out = 0;
+    static const int split_knob = getenv("RTSEG_TC_SPLIT") ? atoi(getenv("RTSEG_TC_SPLIT")) : 1;
+    if (split_knob && allow_split && out_buf && ms == 1 && nacc == 1 && bn / pick_kb(bn) >= 2) {
+      const uint32_t half = (uint32_t)kTileM * pick_kb(bn) * 2;
+      const uint32_t fixed_split = b_bytes + 2 * half + misc;
+      if ((kSmemBudget - fixed_split) / stage_bytes > (kSmemBudget - fixed) / stage_bytes) {
+        pl.split_out = 1, out_bufs = 2, out_buf = half, fixed = fixed_split;
+      }
     }
     pl.out_bufs = out_bufs;
     pl.stage_bytes = stage_bytes;
@@ -992,6 +1014,7 @@ static void fill_common(TcParams &p, const rtseg_conv_desc *d, const TcPlan &pl,
   p.bn = pl.bn, p.nkb = d->cin / pl.kb, p.stages = pl.stages, p.ob = pl.ob;
   p.b_block_bytes = pl.b_block_bytes, p.b_bytes = pl.b_bytes, p.out_buf_bytes = pl.out_buf_bytes;
   p.out_bufs = pl.out_bufs;
+  p.split_out = pl.split_out;
   p.tmem_cols = pl.tmem_cols;
   p.x_coff = d->x_coff;
   p.y_ct = d->y_ctotal, p.y_co = d->y_coff, p.r_ct = d->r_ctotal, p.r_co = d->r_coff;
@@ -1264,7 +1287,9 @@ static int check_plan(const TcParams &p, const TcPlan &pl) {
     RTSEG_REQUIRE((uint32_t)p.ms * kTileM * (uint32_t)p.ob * 2 <= p.stage_bytes, "conv_tc plan: residual box does not fit its ring stage");
   }
   if (p.y_mode == 2)
-    RTSEG_REQUIRE((uint32_t)p.ms * kTileM * (uint32_t)p.bn * 2 == p.out_buf_bytes, "conv_tc plan: staging buffer size mismatch");
+    RTSEG_REQUIRE((uint32_t)p.ms * kTileM * (uint32_t)(p.split_out ? p.ob : p.bn) * 2 == p.out_buf_bytes &&
+                      (!p.split_out || (p.ms == 1 && p.out_bufs == 2 && p.nacc == 1)),
+                  "conv_tc plan: staging buffer size mismatch");
   RTSEG_REQUIRE(p.ms * (p.bn / 16) <= 2 * kMaxMyChunks, "conv_tc plan: more 16-column chunks than the epilogue warps own");
   return RTSEG_OK;
 }
@@ -1272,17 +1297,23 @@ static int check_plan(const TcParams &p, const TcPlan &pl) {
 // Plans a forward conv: tile shape, A-sharing mode, stack depth, ring depth, epilogue mode.  `d` is the K-padded
 // descriptor.  Shared by rtseg_conv_tc and rtseg_conv_tc_plan_info so that tests can see the plan a launch would use.
 static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slope, TcPlan &pl, TcParams &p, int &share,
-                        int &mode) {
+                        int &mode, bool may_split = true) {
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const int ntaps = d->kh * d->kw;
   p.n = d->n;
   rtseg_out_hw(d, &p.gh, &p.gw);
   share = pick_share(d, p.gh, p.gw, pick_kb(d->cin));
   const int halo = (share == 1 || share == 3) ? (d->kh - 1) * d->dil : (share == 2 ? (d->kw - 1) * d->dil : 0);
+  // split staging lives in the fast epilogue (clamp / slope activations); the general path stages whole units
+  // (a residual that cannot ride the ring — more than four sub-boxes — also takes the general path)
+  const int nbox_max = cout_pad / 16;
+  const bool fast_epi = may_split && epilogue_mode(d, slope, p) <= 1 &&
+                        (d->res_mode == RTSEG_RES_NONE || nbox_max <= 4 || cout_pad % 64 == 0);
   if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw, share), d->res_mode != RTSEG_RES_NONE, pl,
-               share, halo)) {
+               share, halo, fast_epi)) {
     share = 0;
-    if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl))
+    if (!plan_tc(d->cin, cout_pad, ntaps, 1, staged, max_stack(p.n, p.gh, p.gw), d->res_mode != RTSEG_RES_NONE, pl, 0, 0,
+                 fast_epi))
       RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
                  d->cin, cout_pad);
   }
@@ -1297,6 +1328,8 @@ static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slop
   const bool ring_res = has_res && staged && mode <= 1 && pl.bn / pl.ob <= 4;
   if (has_res && !ring_res) mode = 2;  // general path reads the residual with plain loads
   if (ring_res) p.res_boxes = pl.bn / pl.ob;
+  if (pl.split_out && mode == 2)   // the general epilogue stages whole units: plan again without split staging
+    return plan_forward(d, staged, slope, pl, p, share, mode, false);
   return RTSEG_OK;
 }
 
