@@ -150,11 +150,14 @@ int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void *w_bf16, c
  *   d       describes the FIRST conv (kh = 3, kw = 1, pad (1, 0), stride 1, dil 1, cin == cout) and carries the
  *           second stage's activation (act, act_p0, act_p1), res_mode (NONE or PRE) and the x / y / r slices
  *   w1, w2  bf16 [3][c][c] (tap, cout, cin); scale / shift: folded BatchNorm of each stage (NULL = identity)
- *   act1    activation after the first conv: none / relu / relu6                                           */
+ *   act1    activation after the first conv: none / relu / relu6
+ *   w_scaled  bit 0 / bit 1: w1 / w2 already carry their BatchNorm scale (w' = bf16(scale[co] * w)); the kernel then
+ *           adds the shift through one extra MMA per tile and that stage's epilogue does no arithmetic (scale1 /
+ *           scale2 are then only used for a PRE residual: v = acc + scale2 * res)                            */
 int rtseg_conv_pair_tc_supported(const rtseg_conv_desc *d, int32_t act1);
 int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const void *w1_bf16, const float *scale1,
                        const float *shift1, int32_t act1, const void *w2_bf16, const float *scale2,
-                       const float *shift2, const void *res, void *y, rtseg_stream_t stream);
+                       const float *shift2, int32_t w_scaled, const void *res, void *y, rtseg_stream_t stream);
 /* Every mbarrier wait in the tensor-core kernels carries a ~2 s watchdog: a
  * lost TMA or a wrong descriptor ends the kernel with garbage output and sets
  * a device flag instead of hanging the GPU.  This call synchronises `stream`,

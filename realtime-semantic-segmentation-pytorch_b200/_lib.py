@@ -56,7 +56,7 @@ PROTOTYPES = {
     "rtseg_conv_tc_supported": (c_i32, [_DP]),
     "rtseg_conv_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_conv_pair_tc_supported": (c_i32, [_DP, c_i32]),
-    "rtseg_conv_pair_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_conv_pair_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "rtseg_tc_timeout_flag": (c_i32, [c_vp]),
     "rtseg_conv_tc_plan_info": (c_i32, [_DP, C.POINTER(c_i32)]),
     "rtseg_dw_tma_launch_count": (c_u64, []),

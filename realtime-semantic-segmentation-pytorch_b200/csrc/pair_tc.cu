@@ -19,6 +19,14 @@
 // column of a tile row are halo: stage 2 produces garbage there, which is never stored.  T outside the image is
 // forced to zero by the stage-1 epilogue (the second convolution pads T, not X).
 //
+// BatchNorm without epilogue arithmetic.  When the caller hands over weights that already carry the BatchNorm scale
+// (w' = bf16(scale[co] * w), flag bits of `w_scaled`), the shift enters the accumulator through the tensor core as
+// well: the first MMA of every chunk multiplies a constant [128 x 16] tile whose first two columns are 1 by a
+// [c x 16] tile whose first two columns hold the bf16 pair (hi, lo) with hi + lo = shift[co] (16 mantissa bits), and
+// the convolution's MMAs accumulate on top.  The epilogue of such a stage is tcgen05.ld -> cvt.rn.relu.bf16x2 ->
+// st.shared: no shared-memory reads of scale / shift, no FMAs — these epilogues are issue- and shared-memory-pipe
+// bound, not bandwidth bound.  A PRE residual still needs its scale: v = acc + scale[co] * res.
+//
 // Roles (576 threads, one persistent CTA per SM): warp 0 streams X tiles through an mbarrier ring with TMA; warp 1
 // issues both stages' MMAs (stage 1 of tile i+1 ahead of stage 2 of tile i); warps 2-17 run the two epilogues
 // interleaved — A(i): stage-1 accumulator -> BN/ReLU -> T in shared memory; B(i-1): stage-2 accumulator (+ residual,
@@ -53,6 +61,7 @@ struct PairParams {
   int x_coff, y_coff, r_coff;
   int nx;                   // X ring depth
   int has_res, out_bufs;
+  int fold1, fold2;         // stage 1 / 2: weights carry the BatchNorm scale and the shift enters through the bias MMA
   uint32_t x_stage_bytes, t1_bytes, out_buf_bytes, w_block_bytes, x_tx_bytes, o_tx_bytes;
   uint32_t tmem_cols;
   float lo1, hi1, lo2, hi2;
@@ -82,18 +91,28 @@ __device__ __forceinline__ uint32_t pack_relu_bf16(float a, float b) {
 
 // 16 accumulator columns (+ residual) -> folded BatchNorm -> clamp -> 8 packed bf16 pairs.  RELU: the clamp is
 // [0, inf) and rides in the conversion; otherwise NaN-propagating max / min with (lo, hi).
-template <bool RELU, bool RES>
+// FOLD: the accumulator already holds scale * conv + shift (pre-scaled weights, bias MMA); a residual then enters as
+// acc + scale * res.
+template <bool RELU, bool RES, bool FOLD>
 __device__ __forceinline__ void affine_pack16(const uint32_t (&v)[16], const float (&rv)[16], uint32_t s_sc, uint32_t s_sh,
                                               float lo, float hi, uint32_t (&pk)[8]) {
 #pragma unroll
   for (int e4 = 0; e4 < 16; e4 += 4) {
-    const float4 sc = lds128(s_sc + (uint32_t)e4 * 4), sh = lds128(s_sh + (uint32_t)e4 * 4);
     float o[4] = {__uint_as_float(v[e4]), __uint_as_float(v[e4 + 1]), __uint_as_float(v[e4 + 2]), __uint_as_float(v[e4 + 3])};
-    if constexpr (RES) {
+    if constexpr (FOLD) {
+      if constexpr (RES) {
+        const float4 sc = lds128(s_sc + (uint32_t)e4 * 4);
+        o[0] = fmaf(rv[e4], sc.x, o[0]), o[1] = fmaf(rv[e4 + 1], sc.y, o[1]);
+        o[2] = fmaf(rv[e4 + 2], sc.z, o[2]), o[3] = fmaf(rv[e4 + 3], sc.w, o[3]);
+      }
+    } else {
+      const float4 sc = lds128(s_sc + (uint32_t)e4 * 4), sh = lds128(s_sh + (uint32_t)e4 * 4);
+      if constexpr (RES) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) o[u] += rv[e4 + u];   // += x before the BatchNorm (reference models/erfnet.py:79-80)
+        for (int u = 0; u < 4; ++u) o[u] += rv[e4 + u];   // += x before the BatchNorm (reference models/erfnet.py:79-80)
+      }
+      o[0] = fmaf(o[0], sc.x, sh.x), o[1] = fmaf(o[1], sc.y, sh.y), o[2] = fmaf(o[2], sc.z, sh.z), o[3] = fmaf(o[3], sc.w, sh.w);
     }
-    o[0] = fmaf(o[0], sc.x, sh.x), o[1] = fmaf(o[1], sc.y, sh.y), o[2] = fmaf(o[2], sc.z, sh.z), o[3] = fmaf(o[3], sc.w, sh.w);
     if constexpr (RELU) {
       pk[(e4 >> 1) + 0] = pack_relu_bf16(o[0], o[1]);
       pk[(e4 >> 1) + 1] = pack_relu_bf16(o[2], o[3]);
@@ -104,6 +123,13 @@ __device__ __forceinline__ void affine_pack16(const uint32_t (&v)[16], const flo
       pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
     }
   }
+}
+
+__device__ __forceinline__ float g_aff_src(const float *v, int i) { return v ? v[i] : 0.f; }
+
+// 32-byte-row K-major operand (K = 16), SWIZZLE_32B: the bias MMA's two tiles.
+__device__ __forceinline__ uint64_t bias_desc(uint32_t addr) {
+  return (uint64_t)((addr & 0x3ffffu) >> 4) | (1ull << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);
 }
 
 template <int KB, bool RES>
@@ -122,7 +148,9 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
   const uint32_t s_t1 = s_x + (uint32_t)p.nx * p.x_stage_bytes;
   const uint32_t s_out = s_t1 + 2 * p.t1_bytes;                // T is double buffered: A(i+1) never waits for stage 2 of tile i
   const uint32_t s_aff = s_out + (uint32_t)p.out_bufs * p.out_buf_bytes;  // scale1, shift1, scale2, shift2
-  const uint32_t s_bars = s_aff + 4u * KB * 4;
+  const uint32_t s_ones = (s_aff + 4u * KB * 4 + 255u) & ~255u;            // [128 x 16] bf16, SWIZZLE_32B: columns 0, 1 = 1
+  const uint32_t s_bias = s_ones + 128u * 32u;                              // 2 x [KB x 16] bf16: columns 0, 1 = (hi, lo) of shift
+  const uint32_t s_bars = s_bias + 2u * KB * 32u;
   const uint32_t full_x = s_bars, empty_x = full_x + 8 * kPairMaxNx;
   const uint32_t w_bar = empty_x + 8 * kPairMaxNx;
   const uint32_t s1_full = w_bar + 8, s1_empty = s1_full + 16, s2_full = s1_empty + 16, s2_empty = s2_full + 16;
@@ -152,6 +180,27 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     g_aff[2 * KB + i] = scale2 ? scale2[i] : 1.f;
     g_aff[3 * KB + i] = shift2 ? shift2[i] : 0.f;
   }
+  // constant operand tiles of the bias MMA (K-major, 32-byte rows, SWIZZLE_32B: 16-byte chunk j of row r sits at
+  // r*32 + ((j ^ ((r >> 2) & 1)) << 4))
+  for (int r = threadIdx.x; r < 128 + 2 * KB; r += blockDim.x) {
+    uint32_t w0 = 0x3f803f80u;   // (1.0, 1.0)
+    uint32_t base = s_ones;
+    int rr = r;
+    if (r >= 128) {
+      rr = r - 128;
+      const int st = rr / KB, co = rr - st * KB;
+      const float sh = g_aff_src(st == 0 ? shift1 : shift2, co);
+      const __nv_bfloat16 hi = __float2bfloat16_rn(sh);
+      const __nv_bfloat16 lo = __float2bfloat16_rn(sh - __bfloat162float(hi));
+      w0 = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16);
+      base = s_bias;
+    }
+    const uint32_t a = base + (uint32_t)rr * 32u;
+    const uint32_t c0 = ((uint32_t)(rr >> 2) & 1u) << 4;
+    sts128(a + c0, w0, 0u, 0u, 0u);
+    sts128(a + (c0 ^ 16u), 0u, 0u, 0u, 0u);
+  }
+  fence_async_smem();
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(p.tmem_cols)
                  : "memory");
@@ -196,6 +245,7 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     const uint32_t wblk16 = p.w_block_bytes >> 4;
     const uint32_t chunk16 = (128u * kRowB) >> 4;          // one 128-pixel chunk of a tile
     const uint32_t vtap16 = ((uint32_t)p.p * kRowB) >> 4;  // one tile row down
+    const uint64_t ones_d = bias_desc(s_ones), bias_d = bias_desc(s_bias);
     mbar_wait(w_bar, 0, dead);
     uint32_t xs = 0, xph = 0;
     auto issue_s1 = [&](int j) {
@@ -207,12 +257,13 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         const uint64_t a0 = pair_desc<KB>(s_x + xs * p.x_stage_bytes);
         for (int m = 0; m < p.mc; ++m) {
           const uint32_t d = tmem_base + b * acc_cols + (uint32_t)(m * KB);
+          if (p.fold1) umma_bf16(d, ones_d, bias_d, idesc, 0u);   // accumulator := shift1 (exact to 16 mantissa bits)
 #pragma unroll
           for (int t = 0; t < 3; ++t) {
             const uint64_t a_d = a0 + (uint64_t)((uint32_t)m * chunk16 + (uint32_t)t * vtap16);
             const uint64_t b_d = w_desc0 + (uint64_t)((uint32_t)t * wblk16);
 #pragma unroll
-            for (int k = 0; k < KB / 16; ++k) umma_bf16(d, a_d + 2 * k, b_d + 2 * k, idesc, (t | k) ? 1u : 0u);
+            for (int k = 0; k < KB / 16; ++k) umma_bf16(d, a_d + 2 * k, b_d + 2 * k, idesc, (t | k | p.fold1) ? 1u : 0u);
           }
         }
         umma_commit(empty_x + 8 * xs);      // the X tile is free once these MMAs have read it
@@ -230,12 +281,13 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         const uint64_t a0 = pair_desc<KB>(s_t1 + b * p.t1_bytes) - (uint64_t)(kRowB >> 4);   // tap 0 starts one pixel row before g
         for (int m = 0; m < p.mc; ++m) {
           const uint32_t d = tmem_base + (2u + b) * acc_cols + (uint32_t)(m * KB);
+          if (p.fold2) umma_bf16(d, ones_d, bias_d + (uint64_t)((KB * 32) >> 4), idesc, 0u);   // accumulator := shift2
 #pragma unroll
           for (int t = 0; t < 3; ++t) {
             const uint64_t a_d = a0 + (uint64_t)((uint32_t)m * chunk16 + (uint32_t)t * (kRowB >> 4));
             const uint64_t b_d = w_desc0 + (uint64_t)((uint32_t)(3 + t) * wblk16);
 #pragma unroll
-            for (int k = 0; k < KB / 16; ++k) umma_bf16(d, a_d + 2 * k, b_d + 2 * k, idesc, (t | k) ? 1u : 0u);
+            for (int k = 0; k < KB / 16; ++k) umma_bf16(d, a_d + 2 * k, b_d + 2 * k, idesc, (t | k | p.fold2) ? 1u : 0u);
           }
         }
         umma_commit(s2_full + 8 * b);       // stage-2 accumulators complete; T may be overwritten
@@ -297,8 +349,14 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
           uint32_t v[16], pk[8];
           tmem_ld16(lane_base + b * acc_cols + (uint32_t)(m * KB + c0), v);
           tmem_ld_wait();
-          if (relu1) affine_pack16<true, false>(v, no_res, s_sc1 + (uint32_t)c0 * 4, s_sh1 + (uint32_t)c0 * 4, p.lo1, p.hi1, pk);
-          else affine_pack16<false, false>(v, no_res, s_sc1 + (uint32_t)c0 * 4, s_sh1 + (uint32_t)c0 * 4, p.lo1, p.hi1, pk);
+          const uint32_t sc_a = s_sc1 + (uint32_t)c0 * 4, sh_a = s_sh1 + (uint32_t)c0 * 4;
+          if (p.fold1) {
+            if (relu1) affine_pack16<true, false, true>(v, no_res, sc_a, sh_a, p.lo1, p.hi1, pk);
+            else affine_pack16<false, false, true>(v, no_res, sc_a, sh_a, p.lo1, p.hi1, pk);
+          } else {
+            if (relu1) affine_pack16<true, false, false>(v, no_res, sc_a, sh_a, p.lo1, p.hi1, pk);
+            else affine_pack16<false, false, false>(v, no_res, sc_a, sh_a, p.lo1, p.hi1, pk);
+          }
           const int g = m * 128 + row;
           if (border) {   // T outside the image is the second conv's zero padding
             const int cimg = w0 - 1 + (g & (p.p - 1));
@@ -348,8 +406,14 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
               for (int u = 0; u < 8; ++u) rv[2 * u] = bf16_lo(w8[u]), rv[2 * u + 1] = bf16_hi(w8[u]);
             }
             uint32_t pk[8];
-            if (relu2) affine_pack16<true, RES>(v, RES ? rv : no_res, s_sc2 + (uint32_t)c0 * 4, s_sh2 + (uint32_t)c0 * 4, p.lo2, p.hi2, pk);
-            else affine_pack16<false, RES>(v, RES ? rv : no_res, s_sc2 + (uint32_t)c0 * 4, s_sh2 + (uint32_t)c0 * 4, p.lo2, p.hi2, pk);
+            const uint32_t sc_a = s_sc2 + (uint32_t)c0 * 4, sh_a = s_sh2 + (uint32_t)c0 * 4;
+            if (p.fold2) {
+              if (relu2) affine_pack16<true, RES, true>(v, RES ? rv : no_res, sc_a, sh_a, p.lo2, p.hi2, pk);
+              else affine_pack16<false, RES, true>(v, RES ? rv : no_res, sc_a, sh_a, p.lo2, p.hi2, pk);
+            } else {
+              if (relu2) affine_pack16<true, RES, false>(v, RES ? rv : no_res, sc_a, sh_a, p.lo2, p.hi2, pk);
+              else affine_pack16<false, RES, false>(v, RES ? rv : no_res, sc_a, sh_a, p.lo2, p.hi2, pk);
+            }
             sts128(a, pk[0], pk[1], pk[2], pk[3]);
             sts128(a ^ 16u, pk[4], pk[5], pk[6], pk[7]);
           }
@@ -473,7 +537,7 @@ extern "C" int rtseg_conv_pair_tc_supported(const rtseg_conv_desc *d, int32_t ac
 
 extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const void *w1_bf16, const float *scale1,
                                   const float *shift1, int32_t act1, const void *w2_bf16, const float *scale2,
-                                  const float *shift2, const void *res, void *y, rtseg_stream_t stream) {
+                                  const float *shift2, int32_t w_scaled, const void *res, void *y, rtseg_stream_t stream) {
   RTSEG_REQUIRE(d && x && w1_bf16 && w2_bf16 && y, "NULL argument");
   RTSEG_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0, "non-positive extent");
   if (const char *why = pair_why(d, act1)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_pair_tc: %s", why);
@@ -499,6 +563,8 @@ extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const
   p.num_tiles = (int)tiles;
   p.x_coff = d->x_coff, p.y_coff = d->y_coff, p.r_coff = d->r_coff;
   p.has_res = has_res ? 1 : 0;
+  p.fold1 = (w_scaled & 1) ? 1 : 0, p.fold2 = (w_scaled & 2) ? 1 : 0;
+  RTSEG_REQUIRE(!(p.fold2 && has_res) || scale2, "pre-scaled second-stage weights with a residual still need scale2 (v = acc + scale2 * res)");
   p.out_bufs = has_res ? 3 : 2;   // stores never block the epilogue; a residual tile lands two units ahead
   const uint32_t row_b = (uint32_t)c * 2;
   auto up1k = [](uint32_t v) { return (v + 1023u) / 1024u * 1024u; };
@@ -508,7 +574,7 @@ extern "C" int rtseg_conv_pair_tc(const rtseg_conv_desc *d, const void *x, const
   p.o_tx_bytes = (uint32_t)p.th * p.tw * row_b;
   p.out_buf_bytes = up1k(p.o_tx_bytes + row_b);   // (the pixel row behind T that tap 2 of the last pixel reads lies in here)
   p.w_block_bytes = up1k((uint32_t)c * row_b);
-  const uint32_t misc = 4u * c * 4 + (2 * kPairMaxNx + 14) * 8 + 64;
+  const uint32_t misc = 4u * c * 4 + 256 + 128 * 32 + 2u * c * 32 + (2 * kPairMaxNx + 14) * 8 + 64;
   const uint32_t fixed = 6 * p.w_block_bytes + 2 * p.t1_bytes + (uint32_t)p.out_bufs * p.out_buf_bytes + misc;
   RTSEG_REQUIRE(fixed + 2 * p.x_stage_bytes <= kPairSmemBudget, "pair plan: tiles do not fit in shared memory");
   p.nx = (int)std::min<uint32_t>(kPairMaxNx, (kPairSmemBudget - fixed) / p.x_stage_bytes);

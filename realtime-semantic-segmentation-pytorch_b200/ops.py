@@ -117,6 +117,7 @@ class Folded:
     act: int = 0
     p0: float = 0.0
     p1: float = 0.0
+    w_tc_scaled: Optional[torch.Tensor] = None   # bf16(scale[co] * w): the pair kernel's BatchNorm-in-the-MMA form
 
     @property
     def groups(self) -> int:
@@ -248,6 +249,13 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
         w_tc[:, :cout, :cin] = w_kmaj.reshape(kh * kw, cout, cin).to(torch.bfloat16)
         w_tc = w_tc.to(device)
     scale, shift = fold_affine(cout, conv.bias, bn, host)
+    w_tc_scaled = None
+    if w_tc is not None and scale is not None and kind == "dense" and host and cin == cout and cin in (16, 64) \
+            and (kh, kw) in ((3, 1), (1, 3)):
+        # pair kernel (pair_tc.cu): the BatchNorm scale rides in the weights, rounded to bf16 once after scaling
+        ws = torch.zeros((kh * kw, cpad, kpad), dtype=torch.bfloat16)
+        ws[:, :cout, :cin] = (w_kmaj.reshape(kh * kw, cout, cin).double() * scale.view(1, cout, 1)).to(torch.bfloat16)
+        w_tc_scaled = ws.to(device)
     slope = None
     if prelu_w is not None:
         slope = prelu_w.detach().to(w.device, torch.float32).reshape(-1)
@@ -255,7 +263,7 @@ def fold_conv(conv: torch.nn.Module, bn=None, act_module=None, device=None,
         if slope.numel() != cout:
             raise ValueError("PReLU num_parameters must be 1 or the number of output channels")
     f = Folded(kind, cin, cout, kh, kw, sh, dh, ph, pw, w_f32.to(device), w_tc, _f32(scale, device), _f32(shift, device),
-               _f32(slope, device), code, p0, p1)
+               _f32(slope, device), code, p0, p1, w_tc_scaled)
     return f, post
 
 
@@ -384,6 +392,7 @@ def normalize_u8(x: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.T
 
 
 USE_PAIR_FUSION = True   # module-level switch (tests / A-B runs): fused 3x1 -> 1x3 pairs of NonBt1D blocks
+PAIR_FOLD_BN = True      # ... with the BatchNorm scale in the weights and the shift added by a bias MMA
 
 
 def conv_pair_supported(fa: Folded, fb: Folded, x: torch.Tensor, res: Optional[torch.Tensor] = None) -> bool:
@@ -418,8 +427,13 @@ def conv_pair(fa: Folded, fb: Folded, x: torch.Tensor, res: Optional[torch.Tenso
         r_ct = res.shape[1]
     d = _desc(fa, n, h, w, BF16, ct, 0, out.shape[1], 0, RES_PRE if res is not None else RES_NONE, r_ct, 0, act=fb.act)
     d.act_p0, d.act_p1 = fb.p0, fb.p1
-    _lib.check(_lib.load().rtseg_conv_pair_tc(C.byref(d), x.data_ptr(), fa.w_tc.data_ptr(), _ptr(fa.scale), _ptr(fa.shift),
-                                              fa.act, fb.w_tc.data_ptr(), _ptr(fb.scale), _ptr(fb.shift), _ptr(res),
+    wa, wb, flags = fa.w_tc, fb.w_tc, 0
+    if PAIR_FOLD_BN and fa.w_tc_scaled is not None:
+        wa, flags = fa.w_tc_scaled, flags | 1
+    if PAIR_FOLD_BN and fb.w_tc_scaled is not None:
+        wb, flags = fb.w_tc_scaled, flags | 2
+    _lib.check(_lib.load().rtseg_conv_pair_tc(C.byref(d), x.data_ptr(), wa.data_ptr(), _ptr(fa.scale), _ptr(fa.shift),
+                                              fa.act, wb.data_ptr(), _ptr(fb.scale), _ptr(fb.shift), flags, _ptr(res),
                                               out.data_ptr(), _stream()), "rtseg_conv_pair_tc")
     return out
 

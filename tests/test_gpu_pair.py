@@ -42,10 +42,14 @@ def _oracle_pair(x, blk_sd, res):
     return F.relu(B.batch_norm(y + xq, blk_sd, "m.bn_act.0."))
 
 
+@pytest.mark.parametrize("fold", [True, False], ids=["bn-in-mma", "bn-in-epilogue"])
 @pytest.mark.parametrize("res", [False, True])
 @pytest.mark.parametrize("c,n,h,w", CASES)
-def test_pair_kernel_vs_oracle(c, n, h, w, res):
+def test_pair_kernel_vs_oracle(c, n, h, w, res, fold, monkeypatch):
+    """fold=True: weights carry the BatchNorm scale and the shift is added by the bias MMA (the default);
+    fold=False: scale and shift applied by the epilogue like conv_tc.cu does."""
     from rtseg_b200 import _lib, nets, ops
+    monkeypatch.setattr(ops, "PAIR_FOLD_BN", fold)
     blk = _randomise(nets.NonBt1DBlock(c, 1), 70 + c).cuda()
     sd = _sd(blk)
     x = seeded((n, c, h, w), 71)
