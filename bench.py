@@ -199,7 +199,12 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
         return e0.elapsed_time(e1) / reps
 
     if workload == "erfnet":
+        # Every NonBt1D block is timed the way the net runs it: undilated 16- / 64-channel blocks as two fused pair
+        # launches (conv_pair_tc_kernel: algorithmic bytes = read x [+ residual], write y — the intermediate never
+        # reaches HBM), the dilated 128-channel blocks as four conv_tc_kernel launches.  The family with the larger
+        # share of the step is reported; the other one is listed next to it.
         res_hw = {64: (256, 512), 128: (128, 256), 16: (512, 1024)}
+        fam = {"pair": [0.0, 0.0, 0], "conv_tc": [0.0, 0.0, 0]}
         for blk in [m for m in model.modules() if isinstance(m, nets.NonBt1DBlock)]:
             c = blk.conv[0][0].in_channels
             h, w = res_hw[c]
@@ -207,19 +212,37 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             if key not in per_cfg:
                 x = torch.randn((batch, c, h, w), device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
                 r = torch.randn_like(x)
-                ms = [time_call(lambda i=i: blk.conv[i](x)) for i in range(3)]
-                ms.append(time_call(lambda: blk.conv[3](x, res=r, res_mode=ops.RES_PRE, bn=blk.bn_act[0],
-                                                        act=blk.bn_act[1].activation)))
                 elems = batch * c * h * w
                 wbytes = 3 * c * c * 2 + 8 * c
-                by = [2 * elems * 2 + wbytes] * 3 + [3 * elems * 2 + wbytes]
-                per_cfg[key] = (ms, by)
+                with torch.no_grad():
+                    fused = blk._pairs(x) is not None
+                if fused:
+                    fa, fb = blk.conv[0]._folded()[0], blk.conv[1]._folded()[0]
+                    fc, fd = blk.conv[2]._folded()[0], blk.conv[3].folded(blk.bn_act[0], blk.bn_act[1].activation)[0]
+                    ms = [time_call(lambda: ops.conv_pair(fa, fb, x)), time_call(lambda: ops.conv_pair(fc, fd, x, res=r))]
+                    by = [2 * elems * 2 + 2 * wbytes, 3 * elems * 2 + 2 * wbytes]
+                    per_cfg[key] = ("pair", ms, by)
+                else:
+                    ms = [time_call(lambda i=i: blk.conv[i](x)) for i in range(3)]
+                    ms.append(time_call(lambda: blk.conv[3](x, res=r, res_mode=ops.RES_PRE, bn=blk.bn_act[0],
+                                                            act=blk.bn_act[1].activation)))
+                    by = [2 * elems * 2 + wbytes] * 3 + [3 * elems * 2 + wbytes]
+                    per_cfg[key] = ("conv_tc", ms, by)
                 del x, r
-            ms, by = per_cfg[key]
-            total_ms += sum(ms)
-            total_bytes += sum(by)
-            launches += 4
-        kernel = "conv_tc_kernel (tcgen05 implicit GEMM, 3x1/1x3 dilated, fused BN/act/residual)"
+            name, ms, by = per_cfg[key]
+            fam[name][0] += sum(ms)
+            fam[name][1] += sum(by)
+            fam[name][2] += len(ms)
+        top = max(fam, key=lambda k: fam[k][0])
+        total_ms, total_bytes, launches = fam[top]
+        label = {"pair": "conv_pair_tc_kernel (tcgen05: 3x1 -> 1x3 pair of a NonBt1D block in one launch, intermediate tile in "
+                         "shared memory, BatchNorm in the MMA, fused residual)",
+                 "conv_tc": "conv_tc_kernel (tcgen05 implicit GEMM, 3x1/1x3 dilated, fused BN/act/residual)"}
+        kernel = label[top]
+        families = {label[k].split(" ")[0]: {"launches_per_step": v[2], "ms_per_step": round(v[0], 4), "bytes_per_step": int(v[1]),
+                                             "achieved_gbs": round(v[1] / (v[0] * 1e-3) / 1e9, 1) if v[0] else None,
+                                             "frac": round(v[1] / (v[0] * 1e-3) / 1e9 / peak_gbs, 4) if v[0] else None}
+                    for k, v in fam.items()}
     elif workload in ("dabnet", "lednet"):
         # every fused conv layer is captured with the tensors / keyword arguments the net really passes, timed
         # alone, and binned by kernel family; the family with the largest share of the time is reported
@@ -280,21 +303,25 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             total_bytes += (x.numel() + y.numel()) * 2 + m[0].weight.numel() * 4 + 8 * y.shape[1]
             launches += 1
             del x, y
-        kernel = "dw_win_kernel / dw_vec_kernel (NHWC depthwise 3x3 + BN + act)"
+        kernel = "dw_tma_kernel / dw_win_kernel (NHWC depthwise 3x3 + BN + act; TMA-staged halo tiles for the large maps)"
     achieved = total_bytes / (total_ms * 1e-3) / 1e9
     # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the same kernel family over one step, from the
     # committed ncu launch list of this command (profiles/launches_r01.md); null for workloads not captured.
-    traffic = None
-    if workload == "erfnet" and batch == 16:
-        try:
-            with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
-                traffic = int(json.load(f)["conv_tc_dram_bytes_per_step"])
-        except Exception:
-            traffic = None
+    traffic, traffic_note = None, None
+    try:   # ncu dram__bytes_read.sum + dram__bytes_write.sum of the same family over one step (tools/parse_ncu_launches.py)
+        with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
+            tr = json.load(f).get(workload, {})
+        if tr.get("batch") == batch:
+            fam_key = kernel.split(" ")[0].split("_kernel")[0]
+            for k, v in tr.get("families", {}).items():
+                if k.startswith(fam_key):
+                    traffic, traffic_note = int(v["dram_bytes_per_step"]), v.get("note")
+    except Exception:
+        traffic = None
+    out_families = locals().get("families")
     return {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 1), "peak": peak_gbs, "unit": "GB/s",
-            "frac": round(achieved / peak_gbs, 4), "traffic": traffic,
-            "traffic_note": "DRAM bytes per step of all 73 conv_tc launches (ncu, profiles/launches_r01.md); "
-                            "bytes_per_step is the algorithmic figure of the 68 timed launches",
+            "frac": round(achieved / peak_gbs, 4), "traffic": traffic, "traffic_note": traffic_note,
+            "families": out_families,
             "peak_source": peak_src,
             "launches_per_step": launches, "bytes_per_step": int(total_bytes), "ms_per_step": round(total_ms, 4),
             "frac_of_8TBps_nominal": round(achieved / 8000.0, 4)}

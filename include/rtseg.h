@@ -366,6 +366,31 @@ int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, fl
  * them, the accumulators stay in tensor memory for the whole kernel.  Same arguments and dw layout. */
 int rtseg_conv_wgrad_tc_supported(const rtseg_conv_desc *d);
 int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
+/* ---- f3: optimizer step + weight mirror in one launch ----------------------
+ * Replaces torch.optim.SGD.step() as the reference configures it (utils/optimizer.py:8-12: lr, momentum, weight
+ * decay; dampening 0, no Nesterov) followed by ModelEmaV2.update (utils/model_ema.py:28-40:
+ * e = decay * e + (1 - decay) * m for EVERY state-dict entry, or e = m when EMA is off), called once per iteration
+ * at core/seg_trainer.py:104-108.  The caller describes all tensors once in a device-resident chunk table (one
+ * entry per <= rtseg_opt_chunk_elems() consecutive elements; build it with the pointers of the parameters, their
+ * gradients, momentum buffers and mirror tensors) and then launches one kernel per iteration.
+ *   p   parameter or buffer (fp32; int64 with RTSEG_OPT_INT64: num_batches_tracked)
+ *   g   gradient or NULL (buffers: mirrored only)        m   momentum buffer (zero before the first step) or NULL
+ *   e   mirror (same dtype as p) or NULL
+ *   hyper_dev  4 floats on the device: lr, momentum, weight_decay, decay — rewritten by the host between steps
+ *              (a captured CUDA graph sees the scheduler's new learning rate)                                   */
+#define RTSEG_OPT_INT64 1
+typedef struct rtseg_opt_chunk {
+  float *p;
+  const float *g;
+  float *m;
+  void *e;
+  int32_t n;
+  int32_t flags;
+} rtseg_opt_chunk;
+int32_t rtseg_opt_chunk_elems(void);
+int rtseg_sgd_ema_step(const rtseg_opt_chunk *chunks_dev, int32_t nchunks, const float *hyper_dev, int32_t use_ema,
+                       rtseg_stream_t stream);
+
 /* Gradient of MaxPool2d(3, 2, 1) (InitialBlock's pool branch, models/enet.py:44): dx = dy routed to the first
  * maximum of each window. */
 int rtseg_maxpool3x3s2_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,

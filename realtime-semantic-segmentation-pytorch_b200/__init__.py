@@ -13,9 +13,10 @@ hyphenated name, so a two-line shim package at the repo root points here).
     parallel.py  set_device / parallel_model / de_parallel (reference utils/parallel.py)
     engine.py    CUDA-graph inference engine with pinned-host I/O (what bench.py times)
     inject.py    installs modules.py under the reference's `models.modules` name
+    optim.py     FusedSGD / FusedModelEma: optimizer step + EMA mirror in one launch (utils/optimizer.py, utils/model_ema.py)
     convert.py   convert(model): re-classes a built model's blocks to the fused ones; fused_head(): deferred final interpolate
 """
-from . import _lib, ops  # noqa: F401
+from . import _lib, ops, optim  # noqa: F401
 from .convert import DeferredLogits, convert, fused_head, predict_labels  # noqa: F401
 from .engine import InferenceEngine  # noqa: F401
 from .loss import OhemCELoss, get_loss_fn  # noqa: F401

@@ -95,6 +95,8 @@ PROTOTYPES = {
     "rtseg_conv_wgrad": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_conv_wgrad_tc_supported": (c_i32, [_DP]),
     "rtseg_conv_wgrad_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_opt_chunk_elems": (c_i32, []),
+    "rtseg_sgd_ema_step": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp]),
     "rtseg_maxpool3x3s2_bwd": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_colorize_blend": (c_i32, [c_i64, c_vp, c_vp, c_vp, c_f32, c_vp, c_vp]),
     "rtseg_upsample_argmax_host_scratch_bytes": (c_sz, [c_i32] * 7),

@@ -71,6 +71,15 @@ struct PairMaps {
   CUtensorMap x, w1, w2, y, r;
 };
 
+#ifdef RTSEG_PAIR_TRACE
+// Development aid (tools/pair_trace.py builds with -DRTSEG_PAIR_TRACE): CTA 0 records clock64() at the hand-over
+// points of its first tiles.  Not compiled into the product library.
+__device__ long long g_pair_trace[64][16];
+#define PAIR_TRACE(tile_, ev_) do { if (blockIdx.x == 0 && (tile_) < 64) g_pair_trace[(tile_)][(ev_)] = clock64(); } while (0)
+#else
+#define PAIR_TRACE(tile_, ev_) do { } while (0)
+#endif
+
 __device__ __forceinline__ void pair_bar_sync(int id) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kPairEpiThreads) : "memory");
 }
@@ -235,6 +244,7 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         mbar_wait(empty_x + 8 * stage, phase ^ 1, dead);
         mbar_expect_tx(full_x + 8 * stage, p.x_tx_bytes);
         tma_load_4d(s_x + stage * p.x_stage_bytes, &maps.x, full_x + 8 * stage, p.x_coff, w0 - 1, h0 - 1, img);
+        PAIR_TRACE(j, 0);
         if (++stage == (uint32_t)p.nx) stage = 0, phase ^= 1;
       }
     }
@@ -251,8 +261,10 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
     auto issue_s1 = [&](int j) {
       const uint32_t b = (uint32_t)j & 1u, use = (uint32_t)j >> 1;
       mbar_wait(full_x + 8 * xs, xph, dead);
+      if (lane == 0) PAIR_TRACE(j, 1);
       mbar_wait(s1_empty + 8 * b, (use & 1u) ^ 1u, dead);
       tc_fence_after();
+      if (lane == 0) PAIR_TRACE(j, 2);
       if (elect_one()) {
         const uint64_t a0 = pair_desc<KB>(s_x + xs * p.x_stage_bytes);
         for (int m = 0; m < p.mc; ++m) {
@@ -277,6 +289,7 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
       mbar_wait(t1_full + 8 * b, use & 1u, dead);               // every epilogue warp has written (and fenced) its part of T[b]
       mbar_wait(s2_empty + 8 * b, (use & 1u) ^ 1u, dead);
       tc_fence_after();
+      if (lane == 0) PAIR_TRACE(i, 3);
       if (elect_one()) {
         const uint64_t a0 = pair_desc<KB>(s_t1 + b * p.t1_bytes) - (uint64_t)(kRowB >> 4);   // tap 0 starts one pixel row before g
         for (int m = 0; m < p.mc; ++m) {
@@ -339,6 +352,7 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         // ---- A(i): stage-1 accumulator -> BN + clamp -> T (bf16, swizzled K-major) ----
         const uint32_t b = (uint32_t)i & 1u, use = (uint32_t)i >> 1;
         mbar_wait(s1_full + 8 * b, use & 1u, dead);
+        if (elected) PAIR_TRACE(i, 4);
         // T[b] is free: stage 2 of tile i-2 read it, and B(i-2) — earlier in this warp's program order — waited for
         // that stage's accumulator barrier
         tc_fence_after();
@@ -377,6 +391,7 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
           mbar_arrive(s1_empty + 8 * b);
           mbar_arrive(t1_full + 8 * b);
         }
+        if (elected) PAIR_TRACE(i, 5);
       }
       if (i >= 1) {
         // ---- B(j): stage-2 accumulator (+ residual) -> BN + clamp -> staging (compact TH x TW) -> TMA store ----
@@ -384,9 +399,11 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         const uint32_t b = (uint32_t)j & 1u, use = (uint32_t)j >> 1;
         const uint32_t buf = s_out + ob * p.out_buf_bytes;
         mbar_wait(s2_full + 8 * b, use & 1u, dead);
+        if (elected) PAIR_TRACE(j, 6);
         if constexpr (RES) mbar_wait(res_full + 8 * ob, ob_use & 1u, dead);
         tc_fence_after();
         if constexpr (!RES) pair_bar_sync(2);   // the elected thread has seen the store before last read this buffer out
+        if (elected) PAIR_TRACE(j, 7);
         for (int k = sub; k < items; k += 4) {
           const int m = k / kGroups, c0 = (k - m * kGroups) * 16;
           uint32_t v[16];
@@ -422,11 +439,14 @@ __global__ void __launch_bounds__(kPairThreads, 1) conv_pair_tc_kernel(const __g
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(s2_empty + 8 * b);
+        if (elected) PAIR_TRACE(j, 8);
         pair_bar_sync(1);        // every warp has written its part of the staging tile
         if (elected) {
+          PAIR_TRACE(j, 9);
           tma_store_4d(&maps.y, buf, p.y_coff, pw0, ph0, pimg);
           bulk_commit();
           bulk_wait_read<1>();   // the store BEFORE this one has read its buffer out: that buffer may be written again
+          PAIR_TRACE(j, 10);
           if (RES && j >= 1 && j + 2 < n_my) {   // ... first by the residual tile of the unit that uses it next
             int w2, h2, img2;
             tile_coords(j + 2, w2, h2, img2);
@@ -529,6 +549,12 @@ const char *pair_why(const rtseg_conv_desc *d, int act1) {
 }  // namespace rtseg
 
 using namespace rtseg;
+
+#ifdef RTSEG_PAIR_TRACE
+extern "C" int rtseg_pair_trace_read(long long *out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_pair_trace, sizeof(long long) * 64 * 16) == cudaSuccess ? 0 : -3;
+}
+#endif
 
 extern "C" int rtseg_conv_pair_tc_supported(const rtseg_conv_desc *d, int32_t act1) {
   static const int knob = getenv("RTSEG_PAIR_TC") ? atoi(getenv("RTSEG_PAIR_TC")) : 1;

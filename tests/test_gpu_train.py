@@ -326,3 +326,86 @@ def test_ohem_reads_class_maps_inside_a_padded_buffer(dtype):
     l1.backward()
     assert l0.item() == l1.item()
     assert torch.equal(dense.grad, padded.grad)
+
+
+# ------------------------------------------------------------------ f3: fused optimizer step + EMA mirror ----
+def test_fused_sgd_matches_torch_sgd_and_the_oracle():
+    """rtseg_sgd_ema_step against torch.optim.SGD on an ERFNet's parameters (three steps, momentum + weight decay) and
+    against the oracle's update rule; one launch per step."""
+    import rtseg_b200
+    from rtseg_b200 import _lib, nets
+    torch.manual_seed(3)
+    a = nets.ERFNet(num_class=19).cuda()
+    b = nets.ERFNet(num_class=19).cuda()
+    b.load_state_dict(a.state_dict())
+    fused = rtseg_b200.optim.FusedSGD(a.parameters(), lr=0.08, momentum=0.9, weight_decay=1e-4)
+    stock = torch.optim.SGD(b.parameters(), lr=0.08, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator(device="cuda").manual_seed(4)
+    for step in range(3):
+        grads = [torch.randn(p.shape, device="cuda", generator=g) * 0.1 for p in a.parameters()]
+        for pa, pb, gr in zip(a.parameters(), b.parameters(), grads):
+            pa.grad, pb.grad = gr.clone(), gr.clone()
+        before = _lib.launch_count()
+        fused.step()
+        assert _lib.launch_count() - before == 1
+        stock.step()
+        if step == 1:
+            for grp in fused.param_groups + stock.param_groups:   # a scheduler changing the learning rate between steps
+                grp["lr"] = 0.02
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(pa, pb, rtol=2e-6, atol=1e-7)
+    for pa, st in zip(a.parameters(), (fused.state[p]["momentum_buffer"] for p in a.parameters())):
+        assert st.shape == pa.shape
+
+
+def test_fused_sgd_single_step_matches_oracle_rule():
+    import rtseg_b200
+    from oracle import ref_optim
+    g = torch.Generator().manual_seed(5)
+    shapes = [(13, 3, 3, 3), (13,), (4097,), (128, 128, 3, 1)]
+    ps = [torch.randn(s, generator=g) for s in shapes]
+    gs = [torch.randn(s, generator=g) for s in shapes]
+    params = [torch.nn.Parameter(p.clone().cuda()) for p in ps]
+    for p, gr in zip(params, gs):
+        p.grad = gr.clone().cuda()
+    opt = rtseg_b200.optim.FusedSGD(params, lr=0.05, momentum=0.9, weight_decay=1e-3)
+    opt.step()
+    opt.step()                       # same gradients again: exercises the momentum buffer
+    bufs = [None] * len(ps)
+    ref_optim.sgd_step(ps, gs, bufs, 0.05, 0.9, 1e-3)
+    ref_optim.sgd_step(ps, gs, bufs, 0.05, 0.9, 1e-3)
+    for p, want in zip(params, ps):
+        assert torch.allclose(p.detach().cpu(), want, rtol=2e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("use_ema", [True, False])
+def test_fused_ema_mirror_matches_reference_rule(use_ema):
+    """FusedModelEma.update / FusedSGD.step(ema=...) against utils/model_ema.py:28-40 restated (every state-dict entry,
+    incl. BatchNorm statistics and the int64 counters)."""
+    import rtseg_b200
+    from oracle import ref_optim
+    from rtseg_b200 import nets
+    torch.manual_seed(6)
+    model = nets.ERFNet(num_class=19).cuda()
+    ema = rtseg_b200.optim.FusedModelEma(model, use_ema=use_ema, total_itrs=10)
+    with torch.no_grad():
+        for k, v in model.state_dict().items():      # move the model away from its copy
+            if v.dtype.is_floating_point:
+                v.add_(torch.randn_like(v) * 0.1)
+            else:
+                v.add_(7)
+    want = [v.detach().cpu().clone() for v in ema.ema.state_dict().values()]
+    ref_optim.ema_update(want, [v.detach().cpu() for v in model.state_dict().values()], 3, 10, use_ema)
+    ema.update(model, 3)
+    for (k, got), w in zip(ema.ema.state_dict().items(), want):
+        assert got.dtype == w.dtype
+        assert torch.allclose(got.cpu().double(), w.double(), rtol=1e-6, atol=1e-7), k
+    # and fused into the optimizer's launch: parameters are mirrored AFTER their update
+    opt = rtseg_b200.optim.FusedSGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0)
+    for p in model.parameters():
+        p.grad = torch.ones_like(p)
+    before = [v.detach().cpu().clone() for v in ema.ema.state_dict().values()]
+    opt.step(ema=ema, model=model, cur_itrs=5)
+    ref_optim.ema_update(before, [v.detach().cpu() for v in model.state_dict().values()], 5, 10, use_ema)
+    for (k, got), w in zip(ema.ema.state_dict().items(), before):
+        assert torch.allclose(got.cpu().double(), w.double(), rtol=1e-6, atol=1e-7), k

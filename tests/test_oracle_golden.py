@@ -144,3 +144,22 @@ def test_uint8_normalisation_restatement_matches_the_textbook_formula():
     want = (torch.from_numpy(img).permute(0, 3, 1, 2).double() / 255.0 - mean) / std
     assert got.shape == (1, 3, 16, 16) and got.dtype == torch.float64
     assert (got - want).abs().max().item() < 2e-6
+
+
+def test_sgd_restatement_matches_torch_optim_sgd():
+    """oracle/ref_optim.sgd_step against torch.optim.SGD (the reference's optimizer, utils/optimizer.py:8-12): three steps."""
+    from oracle import ref_optim
+    g = torch.Generator().manual_seed(0)
+    ps = [torch.randn(s, generator=g) for s in ((7, 3), (5,), (2, 2, 3, 1))]
+    mine = [p.clone() for p in ps]
+    theirs = [torch.nn.Parameter(p.clone()) for p in ps]
+    opt = torch.optim.SGD(theirs, lr=0.08, momentum=0.9, weight_decay=1e-4)
+    bufs = [None] * len(ps)
+    for _ in range(3):
+        grads = [torch.randn(p.shape, generator=g) for p in ps]
+        for t, gr in zip(theirs, grads):
+            t.grad = gr.clone()
+        opt.step()
+        ref_optim.sgd_step(mine, grads, bufs, 0.08, 0.9, 1e-4)
+    for a, b in zip(mine, theirs):
+        assert torch.allclose(a, b.detach(), rtol=1e-6, atol=1e-7)
