@@ -244,6 +244,11 @@ int rtseg_argmax_nhwc(int64_t npix, int32_t c, int32_t c_total, int32_t dtype, c
 int rtseg_argmax_nchw(int32_t n, int32_t c, int64_t hw, int32_t dtype, const void *x,
                       uint8_t *labels_u8, int64_t *labels_i64, rtseg_stream_t stream);
 
+/* Label maps for the auxiliary heads: F.interpolate(masks.unsqueeze(1).float(), aux_size, mode='nearest') then
+ * .long(), core/seg_trainer.py:58-62 — int64 [n][hi][wi] -> [n][ho][wo], src = min(floor(dst * in/out), in - 1). */
+int rtseg_resize_nearest_i64(int32_t n, int32_t hi, int32_t wi, int32_t ho, int32_t wo, const int64_t *x, int64_t *y,
+                             rtseg_stream_t stream);
+
 /* ---- K13': confusion matrix ----------------------------------------------
  * Replaces torchmetrics JaccardIndex.update as called at utils/metrics.py:4-7
  * / core/seg_trainer.py:131: drop target == ignore_index, confmat[t][p] += 1.

@@ -19,7 +19,7 @@ hyphenated name, so a two-line shim package at the repo root points here).
 from . import _lib, ops, optim  # noqa: F401
 from .convert import DeferredLogits, convert, fused_head, predict_labels  # noqa: F401
 from .engine import InferenceEngine  # noqa: F401
-from .loss import OhemCELoss, get_loss_fn  # noqa: F401
+from .loss import OhemCELoss, get_loss_fn, loss_with_aux_heads  # noqa: F401
 from .metrics import SegMetrics, get_seg_metrics, iou_from_confmat  # noqa: F401
 from .nets import ERFNet, FastSCNN, get_model  # noqa: F401
 from .ops import upsample_argmax  # noqa: F401

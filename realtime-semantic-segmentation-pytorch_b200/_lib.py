@@ -70,6 +70,7 @@ PROTOTYPES = {
     "rtseg_upsample_argmax": (c_i32, [c_i32] * 9 + [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "rtseg_argmax_nhwc": (c_i32, [c_i64, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_argmax_nchw": (c_i32, [c_i32, c_i32, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_resize_nearest_i64": (c_i32, [c_i32] * 5 + [c_vp, c_vp, c_vp]),
     "rtseg_confmat_update": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_ohem_workspace_bytes": (c_sz, []),
     "rtseg_ohem_fwd": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_f32, c_vp, c_vp, c_vp, c_vp]),

@@ -217,6 +217,21 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
   }
 }
 
+// ------------------------------------------------ nearest resize of label maps ----
+// F.interpolate(masks.unsqueeze(1).float(), size, mode='nearest') of the auxiliary-head path (reference
+// core/seg_trainer.py:60-61): src = min(floor(dst * (in / out)), in - 1) with the ratio in fp32, like ATen's
+// nearest_neighbor_compute_source_index.  Labels stay int64 (the float detour of the reference is exact for them).
+__global__ void __launch_bounds__(256) resize_nearest_i64_kernel(int n, int hi, int wi, int ho, int wo, float sy, float sx,
+                                                                 const int64_t *__restrict__ x, int64_t *__restrict__ y) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)n * ho * wo) return;
+  const int ox = (int)(tid % wo);
+  const int64_t r = tid / wo;
+  const int oy = (int)(r % ho), b = (int)(r / ho);
+  const int iy = min((int)floorf((float)oy * sy), hi - 1), ix = min((int)floorf((float)ox * sx), wi - 1);
+  y[tid] = __ldg(x + ((int64_t)b * hi + iy) * wi + ix);
+}
+
 // ------------------------------------------------------------------ argmax ----
 template <typename T>
 __global__ void __launch_bounds__(256) argmax_nhwc_kernel(int64_t npix, int c, int c_total, const T *__restrict__ x,
@@ -698,6 +713,17 @@ extern "C" int rtseg_upsample_argmax_host(int32_t n, int32_t hi, int32_t wi, int
     return rc;
   RTSEG_CUDA(cudaMemcpyAsync(labels_host, dlab, out_bytes, cudaMemcpyDeviceToHost, st));
   RTSEG_CUDA(cudaStreamSynchronize(st));
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_resize_nearest_i64(int32_t n, int32_t hi, int32_t wi, int32_t ho, int32_t wo, const int64_t *x, int64_t *y,
+                                        rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && ho > 0 && wo > 0, "non-positive extent");
+  const int64_t total = (int64_t)n * ho * wo;
+  resize_nearest_i64_kernel<<<(unsigned)cdiv(total, 256), 256, 0, as_stream(stream)>>>(
+      n, hi, wi, ho, wo, (float)hi / (float)ho, (float)wi / (float)wo, x, y);
+  RTSEG_LAUNCH_CHECK("resize_nearest_i64_kernel");
   return RTSEG_OK;
 }
 

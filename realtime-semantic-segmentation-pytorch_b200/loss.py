@@ -76,6 +76,20 @@ class OhemCELoss(nn.Module):
         return _OhemFunction.apply(logits, labels, self.thresh, self.ignore_index)
 
 
+def loss_with_aux_heads(loss_fn, preds, preds_aux, masks, aux_coef=None):
+    """Main loss + coefficient-weighted loss of every auxiliary head against the label map resized ('nearest') to that
+    head's resolution — the `config.use_aux` branch of reference core/seg_trainer.py:53-65, with the resize on the
+    rtseg kernel (int64 in, int64 out) instead of a float round trip through F.interpolate."""
+    loss = loss_fn(preds, masks)
+    if aux_coef is None:
+        aux_coef = [1.0] * len(preds_aux)
+    elif len(preds_aux) != len(aux_coef):
+        raise ValueError("Auxiliary loss coefficient length does not match.")
+    for coef, aux in zip(aux_coef, preds_aux):
+        loss = loss + float(coef) * loss_fn(aux, ops.resize_labels_nearest(masks, aux.shape[2:]))
+    return loss
+
+
 def get_loss_fn(config, device):
     """Factory with the reference's contract (core/loss.py:55-71)."""
     if config.loss_type == "ohem":

@@ -539,6 +539,20 @@ def upsample_argmax(logits: torch.Tensor, size: Tuple[int, int], align_corners: 
     return l8 if l8 is not None else l64
 
 
+def resize_labels_nearest(masks: torch.Tensor, size: Tuple[int, int]) -> torch.Tensor:
+    """int64 label maps [N, H, W] -> [N, h, w] with 'nearest' sampling: what reference core/seg_trainer.py:58-62 gets
+    from F.interpolate(masks.unsqueeze(1).float(), size, mode='nearest').squeeze(1).long()."""
+    _require_cuda(masks, "resize_labels_nearest")
+    if masks.dim() != 3:
+        raise ValueError("masks must be [N, H, W]")
+    m = masks.long().contiguous()
+    n, hi, wi = m.shape
+    out = torch.empty((n, int(size[0]), int(size[1])), dtype=torch.int64, device=m.device)
+    _lib.check(_lib.load().rtseg_resize_nearest_i64(n, hi, wi, int(size[0]), int(size[1]), m.data_ptr(), out.data_ptr(),
+                                                    _stream()), "rtseg_resize_nearest_i64")
+    return out
+
+
 def argmax_channels(x: torch.Tensor, out_dtype: torch.dtype = torch.int64) -> torch.Tensor:
     """preds.max(dim=1)[1] (reference core/seg_trainer.py:172) for NCHW or NHWC storage."""
     _require_cuda(x, "argmax_channels")

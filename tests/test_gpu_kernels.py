@@ -704,3 +704,35 @@ def test_colorize_blend_matches_pillow_restatement(shape):
         assert np.array_equal(got, ref_head.colorize_blend(labels, ops.CITYSCAPES_COLORMAP, image, alpha)), alpha
     with pytest.raises(RuntimeError):
         ops.colorize(lab, image=torch.from_numpy(image).cuda(), alpha=1.5)
+
+
+# ------------------------------------------------------------------ auxiliary-head path ----
+@pytest.mark.parametrize("hi,wi,ho,wo", [(64, 128, 8, 16), (37, 53, 19, 27), (16, 16, 64, 48), (1024, 1024, 128, 128), (9, 7, 9, 7)])
+def test_nearest_resize_of_label_maps_matches_interpolate(hi, wi, ho, wo):
+    """reference core/seg_trainer.py:58-62: masks.unsqueeze(1).float() -> F.interpolate(nearest) -> .long()"""
+    from rtseg_b200 import ops
+    g = torch.Generator().manual_seed(80)
+    masks = torch.randint(0, 19, (2, hi, wi), generator=g)
+    masks[torch.rand((2, hi, wi), generator=g) < 0.1] = 255
+    want = F.interpolate(masks.unsqueeze(1).float(), (ho, wo), mode="nearest").squeeze(1).long()
+    got = ops.resize_labels_nearest(masks.cuda(), (ho, wo))
+    assert got.dtype == torch.int64 and torch.equal(got.cpu(), want)
+
+
+def test_loss_with_aux_heads_matches_reference_composition():
+    """loss + sum_i coef_i * loss(aux_i, nearest(masks -> aux_i size)) with the OHEM loss (both restated by the oracle)."""
+    import rtseg_b200
+    g = torch.Generator().manual_seed(81)
+    masks = torch.randint(0, 19, (2, 64, 96), generator=g)
+    masks[torch.rand((2, 64, 96), generator=g) < 0.1] = 255
+    preds = torch.randn((2, 19, 64, 96), generator=g)
+    aux = [torch.randn((2, 19, 8, 12), generator=g), torch.randn((2, 19, 16, 24), generator=g)]
+    coef = [0.4, 0.7]
+    want = ref_ohem.ohem_ce_loss(preds, masks, 0.7)[0]
+    for c, a in zip(coef, aux):
+        m = F.interpolate(masks.unsqueeze(1).float(), a.shape[2:], mode="nearest").squeeze(1).long()
+        want = want + c * ref_ohem.ohem_ce_loss(a, m, 0.7)[0]
+    fn = rtseg_b200.OhemCELoss(0.7)
+    got = rtseg_b200.loss_with_aux_heads(fn, preds.cuda().requires_grad_(True), [a.cuda() for a in aux], masks.cuda(), coef)
+    assert abs(got.item() - want.item()) < 1e-5 * max(1.0, abs(want.item()))
+    got.backward()

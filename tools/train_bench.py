@@ -33,7 +33,10 @@ def build(batch, size, fp32, rank, local, world):
         model = torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
     crit = rloss.OhemCELoss(0.7, 255)
-    opt = torch.optim.SGD(model.parameters(), lr=0.01 * world, momentum=0.9, weight_decay=1e-4)
+    if os.environ.get("RTSEG_TORCH_SGD") == "1":     # A/B: the stock optimizer (~5 ATen kernels per parameter tensor)
+        opt = torch.optim.SGD(model.parameters(), lr=0.01 * world, momentum=0.9, weight_decay=1e-4)
+    else:                                             # one rtseg launch per step
+        opt = rtseg_b200.optim.FusedSGD(model.parameters(), lr=0.01 * world, momentum=0.9, weight_decay=1e-4)
     g = torch.Generator(device="cuda").manual_seed(rank)
     x = torch.randn((batch, 3, size, size), device="cuda", generator=g)
     y = torch.randint(0, 19, (batch, size, size), device="cuda", generator=g)
