@@ -201,6 +201,19 @@ int rtseg_stem_u8(const rtseg_conv_desc *d, int32_t pool, const uint8_t *x, cons
  * x_ctotal/x_coff, y_ctotal/y_coff, dtype. */
 int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void *y, rtseg_stream_t stream);
 
+/* ---- f1: ENet's pooling pair ------------------------------------------------
+ * nn.MaxPool2d(2, 2, return_indices=True) of the downsampling Bottleneck (models/enet.py:130-131, 168-170) and
+ * nn.MaxUnpool2d(2, 2) of the upsampling one (:138-139, 176-178).  NHWC channel slices.  `idx` is this library's
+ * own index format — one byte per pooled element [n][h/2][w/2][c], the position 0..3 of the maximum inside its 2x2
+ * window (row-major); torch's flat index is (2*hp + idx/2) * w + 2*wp + idx%2.  Selection = ATen's: first maximum
+ * in row-major order, a NaN always taken.  The unpool writes every output element (zeros included; output size
+ * 2*hp (+1) x 2*wp (+1) for odd originals), so its output needs no clearing. */
+int rtseg_maxpool2x2_idx(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,
+                         int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff, uint8_t *idx, rtseg_stream_t stream);
+int rtseg_maxunpool2x2(int32_t n, int32_t hp, int32_t wp, int32_t c, int32_t ho, int32_t wo, int32_t dtype, const void *x,
+                       int32_t x_ctotal, int32_t x_coff, const uint8_t *idx, void *y, int32_t y_ctotal, int32_t y_coff,
+                       rtseg_stream_t stream);
+
 /* ---- K5': transposed conv 3x3 s2 p1 op1 + BN + act -----------------------
  * Replaces DeConvBNAct, models/modules.py:89-108 (scale_factor 2).
  * d->h,w are the INPUT size; output is 2h x 2w.  d->kh=kw=3, stride=2.

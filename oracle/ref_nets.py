@@ -171,7 +171,63 @@ def lednet_forward(sd, x, act_type="relu"):
     return F.interpolate(lednet_lowres_logits(sd, x, act_type), x.shape[2:], mode="bilinear", align_corners=True)
 
 
-FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward, "dabnet": dabnet_forward, "lednet": lednet_forward}
+# ------------------------------------------------------------------------------- ENet ----
+def enet_bottleneck(x, sd, prefix, conv_type, dilation=1, indices=None, act_type="prelu"):
+    """Bottleneck (reference models/enet.py:119-181), eval mode (Dropout = identity).  Inner ConvBNActs are ReLU
+    (their default act_type); the block's own activation is `act_type` applied after the add."""
+    p = prefix + "right_init_conv."
+    if conv_type == "downsampling":
+        r = B.conv_bn_act(x, sd, p + "0.", 3, 2, 1, "relu")
+        r = B.conv_bn_act(r, sd, p + "1.", 3, 1, 1, "relu")
+    elif conv_type == "upsampling":
+        r = B.conv_bn_act(x, sd, p + "0.", 1, 1, 1, "relu")
+        r = B.q(F.conv_transpose2d(r, B.qw(sd[p + "1.up_conv.weight"], 1, True), None, 2, 1, 1))
+    elif conv_type == "asymmetric":
+        r = B.conv_bn_act(x, sd, p + "0.", 1, 1, 1, "relu")
+        r = B.conv_bn_act(r, sd, p + "1.", (5, 1), 1, 1, "relu")
+        r = B.conv_bn_act(r, sd, p + "2.", (1, 5), 1, 1, "relu")
+    else:  # regular / dilate
+        r = B.conv_bn_act(x, sd, p + "0.", 1, 1, 1, "relu")
+        r = B.conv_bn_act(r, sd, p + "1.", 3, 1, dilation, "relu")
+    r = F.conv2d(r, B.qw(sd[prefix + "right_last_conv.0.weight"]))
+    if conv_type == "downsampling":
+        left, idx = F.max_pool2d(x, 2, 2, return_indices=True)
+        left = B.conv_bn_act(B.q(left), sd, prefix + "left_conv.", 1, 1, 1, "relu")
+        return B.q(B.activation(left + r, act_type, sd, prefix + "act.")), idx
+    if conv_type == "upsampling":
+        left = B.conv_bn_act(x, sd, prefix + "left_conv.", 1, 1, 1, "relu")
+        left = F.max_unpool2d(left, indices, 2, 2)
+        return B.q(B.activation(left + r, act_type, sd, prefix + "act."))
+    return B.q(B.activation(x + r, act_type, sd, prefix + "act."))
+
+
+_ENET_STAGE23 = [("regular", 1), ("dilate", 2), ("asymmetric", 1), ("dilate", 4), ("regular", 1), ("dilate", 8),
+                 ("asymmetric", 1), ("dilate", 16)]   # reference models/enet.py:76-85
+
+
+def enet_forward(sd, x, act_type="prelu"):
+    """ENet.forward (reference models/enet.py:25-35), upsample_type='deconvolution' (the default)."""
+    x = B.initial_block(x, sd, "initial.", act_type)
+    x, idx1 = enet_bottleneck(x, sd, "bottleneck1.conv_pool.", "downsampling", act_type=act_type)
+    for i in range(4):
+        x = enet_bottleneck(x, sd, f"bottleneck1.conv_regular.{i}.", "regular", act_type=act_type)
+    x, idx2 = enet_bottleneck(x, sd, "bottleneck2.conv_pool.", "downsampling", act_type=act_type)
+    for stage in ("bottleneck2", "bottleneck3"):
+        for i, (kind, d) in enumerate(_ENET_STAGE23):
+            x = enet_bottleneck(x, sd, f"{stage}.conv_regular.{i}.", kind, d, act_type=act_type)
+    x = enet_bottleneck(x, sd, "bottleneck4.conv_unpool.", "upsampling", indices=idx2, act_type=act_type)
+    x = enet_bottleneck(x, sd, "bottleneck4.conv_regular.", "regular", act_type=act_type)
+    x = enet_bottleneck(x, sd, "bottleneck4.conv_extra.", "regular", act_type=act_type)
+    x = enet_bottleneck(x, sd, "bottleneck5.conv_unpool.", "upsampling", indices=idx1, act_type=act_type)
+    x = enet_bottleneck(x, sd, "bottleneck5.conv_regular.", "regular", act_type=act_type)
+    # fullconv = Upsample(16, num_class, scale_factor=2, act_type) WITHOUT upsample_type (models/enet.py:24), i.e. the
+    # ConvBNAct 1x1 + nn.Upsample(scale_factor=2, mode='bilinear') branch (:197-201), align_corners=False
+    x = B.conv_bn_act(x, sd, "fullconv.up_conv.0.", 1, 1, 1, act_type)
+    return B.q(F.interpolate(x, scale_factor=2, mode="bilinear"))
+
+
+FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward, "dabnet": dabnet_forward, "lednet": lednet_forward,
+           "enet": enet_forward}
 
 
 # --------------------------------------------------------------------- seeded weights ----

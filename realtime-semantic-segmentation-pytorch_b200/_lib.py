@@ -63,6 +63,8 @@ PROTOTYPES = {
     "rtseg_stem": (c_i32, [_DP, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_stem_u8": (c_i32, [_DP, c_i32, c_vp, C.POINTER(c_f32), C.POINTER(c_f32), c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_maxpool3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp]),
+    "rtseg_maxpool2x2_idx": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "rtseg_maxunpool2x2": (c_i32, [c_i32] * 7 + [c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_deconv3x3s2": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_deconv3x3s2_tc_supported": (c_i32, [_DP]),
     "rtseg_deconv3x3s2_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

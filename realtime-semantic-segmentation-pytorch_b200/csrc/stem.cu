@@ -207,6 +207,82 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(PoolParams p, const T
   }
 }
 
+// ---- ENet's pooling pair -------------------------------------------------------------------------
+// nn.MaxPool2d(2, 2, return_indices=True) and nn.MaxUnpool2d(2, 2) of the down- / up-sampling Bottlenecks (reference
+// models/enet.py:130-131, 138-139, 168-178).  NHWC, channel slices in and out.  The index of a window's maximum is
+// kept as its position inside the 2x2 window (0..3, row-major, one byte per element) — every window owns its four
+// output pixels, so the unpool is a pure gather: no scatter, no memset of the (three quarters zero) output.
+// Selection follows ATen: scan the window row-major, take a value if it is greater than the running maximum or NaN.
+struct Pool2Params {
+  int n, h, w, c, ho, wo;   // input h x w, pooled ho x wo = floor(h / 2) x floor(w / 2)
+  int x_ct, x_co, y_ct, y_co;
+};
+
+template <typename T, int V>
+__global__ void __launch_bounds__(256) maxpool2x2_idx_kernel(Pool2Params p, const T *__restrict__ x, T *__restrict__ y,
+                                                             uint8_t *__restrict__ idx) {
+  const int cv_n = p.c / V;
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * cv_n;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cv_n) * V;
+  int64_t r = tid / cv_n;
+  const int wo = (int)(r % p.wo);
+  r /= p.wo;
+  const int ho = (int)(r % p.ho), n = (int)(r / p.ho);
+  float best[V];
+  int pos[V];
+  const T *base = x + (((int64_t)n * p.h + ho * 2) * p.w + wo * 2) * p.x_ct + p.x_co + c0;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const T *q = base + ((int64_t)(t >> 1) * p.w + (t & 1)) * p.x_ct;
+    float v[V];
+    if constexpr (V == 1) v[0] = ld_f<T>(q);
+    else Vec16<T>::unpack(Vec16<T>::ldg(q), v);
+#pragma unroll
+    for (int e = 0; e < V; ++e)
+      if (t == 0 || v[e] > best[e] || v[e] != v[e]) best[e] = v[e], pos[e] = t;
+  }
+  const int64_t opix = ((int64_t)n * p.ho + ho) * p.wo + wo;
+  T *yp = y + opix * p.y_ct + p.y_co + c0;
+  if constexpr (V == 1) st_f<T>(yp, best[0]);
+  else Vec16<T>::store(yp, best);
+#pragma unroll
+  for (int e = 0; e < V; ++e) idx[opix * p.c + c0 + e] = (uint8_t)pos[e];
+}
+
+// y[n][oy][ox][c] = x[n][oy/2][ox/2][c] if idx says so, else 0; output rows / columns beyond 2*hp (odd sizes) are zero
+template <typename T, int V>
+__global__ void __launch_bounds__(256) maxunpool2x2_kernel(Pool2Params p, const T *__restrict__ x,
+                                                           const uint8_t *__restrict__ idx, T *__restrict__ y) {
+  const int cv_n = p.c / V;
+  const int64_t total = (int64_t)p.n * p.h * p.w * cv_n;   // here h x w is the OUTPUT (unpooled) size, ho x wo the pooled input
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cv_n) * V;
+  int64_t r = tid / cv_n;
+  const int ox = (int)(r % p.w);
+  r /= p.w;
+  const int oy = (int)(r % p.h), n = (int)(r / p.h);
+  float out[V];
+#pragma unroll
+  for (int e = 0; e < V; ++e) out[e] = 0.f;
+  const int hp = oy >> 1, wp = ox >> 1;
+  if (hp < p.ho && wp < p.wo) {
+    const int64_t ipix = ((int64_t)n * p.ho + hp) * p.wo + wp;
+    const int me = (oy & 1) * 2 + (ox & 1);
+    float v[V];
+    if constexpr (V == 1) v[0] = ld_f<T>(x + ipix * p.x_ct + p.x_co + c0);
+    else Vec16<T>::unpack(Vec16<T>::ldg(x + ipix * p.x_ct + p.x_co + c0), v);
+#pragma unroll
+    for (int e = 0; e < V; ++e)
+      if ((int)idx[ipix * p.c + c0 + e] == me) out[e] = v[e];
+  }
+  T *yp = y + (((int64_t)n * p.h + oy) * p.w + ox) * p.y_ct + p.y_co + c0;
+  if constexpr (V == 1) st_f<T>(yp, out[0]);
+  else Vec16<T>::store(yp, out);
+}
+
 template <typename TI, typename TO>
 static int launch_stem(const StemParams &p, const void *x, const float *w, const Epilogue &ep, void *y,
                        cudaStream_t st) {
@@ -331,5 +407,64 @@ extern "C" int rtseg_maxpool3x3s2(const rtseg_conv_desc *d, const void *x, void 
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
   }
   RTSEG_LAUNCH_CHECK("maxpool3x3s2_kernel");
+  return RTSEG_OK;
+}
+
+
+static bool pool2_vec_ok(const rtseg::Pool2Params &p, int V, const void *x, const void *y) {
+  return p.c % V == 0 && p.x_ct % V == 0 && p.x_co % V == 0 && p.y_ct % V == 0 && p.y_co % V == 0 &&
+         reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
+}
+
+extern "C" int rtseg_maxpool2x2_idx(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,
+                                    int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff, uint8_t *idx,
+                                    rtseg_stream_t stream) {
+  using namespace rtseg;
+  RTSEG_REQUIRE(x && y && idx, "NULL argument");
+  RTSEG_REQUIRE(n > 0 && h >= 2 && w >= 2 && c > 0, "extent too small for a 2x2 window");
+  RTSEG_REQUIRE(x_coff >= 0 && y_coff >= 0 && x_ctotal >= x_coff + c && y_ctotal >= y_coff + c, "channel slice out of range");
+  Pool2Params p{n, h, w, c, h / 2, w / 2, x_ctotal, x_coff, y_ctotal, y_coff};
+  cudaStream_t st = as_stream(stream);
+  const int V = dtype == RTSEG_BF16 ? 8 : 4;
+  const bool vec = pool2_vec_ok(p, V, x, y);
+  const int64_t total = (int64_t)n * p.ho * p.wo * (vec ? c / V : c);
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  if (dtype == RTSEG_BF16) {
+    if (vec) maxpool2x2_idx_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y, idx);
+    else maxpool2x2_idx_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, (__nv_bfloat16 *)y, idx);
+  } else if (dtype == RTSEG_F32) {
+    if (vec) maxpool2x2_idx_kernel<float, 4><<<grid, 256, 0, st>>>(p, (const float *)x, (float *)y, idx);
+    else maxpool2x2_idx_kernel<float, 1><<<grid, 256, 0, st>>>(p, (const float *)x, (float *)y, idx);
+  } else {
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  }
+  RTSEG_LAUNCH_CHECK("maxpool2x2_idx_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_maxunpool2x2(int32_t n, int32_t hp, int32_t wp, int32_t c, int32_t ho, int32_t wo, int32_t dtype,
+                                  const void *x, int32_t x_ctotal, int32_t x_coff, const uint8_t *idx, void *y,
+                                  int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream) {
+  using namespace rtseg;
+  RTSEG_REQUIRE(x && y && idx, "NULL argument");
+  RTSEG_REQUIRE(n > 0 && hp > 0 && wp > 0 && c > 0 && ho >= 2 * hp && wo >= 2 * wp && ho <= 2 * hp + 1 && wo <= 2 * wp + 1,
+                "output size must be 2*h (+1) x 2*w (+1)");
+  RTSEG_REQUIRE(x_coff >= 0 && y_coff >= 0 && x_ctotal >= x_coff + c && y_ctotal >= y_coff + c, "channel slice out of range");
+  Pool2Params p{n, ho, wo, c, hp, wp, x_ctotal, x_coff, y_ctotal, y_coff};
+  cudaStream_t st = as_stream(stream);
+  const int V = dtype == RTSEG_BF16 ? 8 : 4;
+  const bool vec = pool2_vec_ok(p, V, x, y);
+  const int64_t total = (int64_t)n * ho * wo * (vec ? c / V : c);
+  const unsigned grid = (unsigned)cdiv(total, 256);
+  if (dtype == RTSEG_BF16) {
+    if (vec) maxunpool2x2_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, idx, (__nv_bfloat16 *)y);
+    else maxunpool2x2_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(p, (const __nv_bfloat16 *)x, idx, (__nv_bfloat16 *)y);
+  } else if (dtype == RTSEG_F32) {
+    if (vec) maxunpool2x2_kernel<float, 4><<<grid, 256, 0, st>>>(p, (const float *)x, idx, (float *)y);
+    else maxunpool2x2_kernel<float, 1><<<grid, 256, 0, st>>>(p, (const float *)x, idx, (float *)y);
+  } else {
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  }
+  RTSEG_LAUNCH_CHECK("maxunpool2x2_kernel");
   return RTSEG_OK;
 }

@@ -591,7 +591,194 @@ class LEDNet(nn.Module):
                                    ignore_index=ignore_index, num_classes=self.num_class)
 
 
-MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet}
+# -------------------------------------------------------------------------------- ENet ----
+class Upsample(nn.Module):
+    """reference models/enet.py:184-204: a bare ConvTranspose2d(k, s = 2, bias=False) ('deconvolution') or
+    ConvBNAct 1x1 + bilinear nn.Upsample (any other type)."""
+
+    def __init__(self, in_channels, out_channels, scale_factor=2, kernel_size=None, upsample_type=None, act_type="relu"):
+        super().__init__()
+        if upsample_type == "deconvolution":
+            if kernel_size is None:
+                kernel_size = 2 * scale_factor - 1
+            self.up_conv = nn.ConvTranspose2d(in_channels, out_channels, kernel_size=kernel_size, stride=scale_factor,
+                                              padding=(kernel_size - 1) // 2, output_padding=1, bias=False)
+        else:
+            self.up_conv = nn.Sequential(ConvBNAct(in_channels, out_channels, 1, act_type=act_type),
+                                         nn.Upsample(scale_factor=scale_factor, mode="bilinear"))
+
+    def _folded(self):
+        cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
+        return cache.get([self.up_conv.weight], lambda: ops.fold_conv(self.up_conv, None, None, host=True))
+
+    def forward(self, x, labels=None, want_logits=True):
+        x = ops.to_nhwc(x)
+        if isinstance(self.up_conv, nn.ConvTranspose2d):
+            return ops.conv(self._folded()[0], x, labels=labels, want_logits=want_logits)
+        y = self.up_conv[0](x)
+        sf = self.up_conv[1].scale_factor
+        return ops.upsample_bilinear(y, (int(y.shape[2] * sf), int(y.shape[3] * sf)), False)
+
+    __deepcopy__ = Conv2d.__deepcopy__
+
+
+class Bottleneck(nn.Module):
+    """ENet bottleneck — reference models/enet.py:119-181.  The shortcut add (or the pooled / unpooled left branch)
+    and the PReLU are the epilogue of the last 1x1 convolution; MaxPool2d(2, 2, return_indices) / MaxUnpool2d are the
+    rtseg pooling pair (one byte per index)."""
+
+    def __init__(self, in_channels, out_channels, conv_type, act_type="prelu", upsample_type="regular", dilation=1,
+                 drop_p=0.1, shrink_ratio=0.25):
+        super().__init__()
+        self.conv_type = conv_type
+        hid = int(in_channels * shrink_ratio)
+        if conv_type == "regular":
+            self.right_init_conv = nn.Sequential(ConvBNAct(in_channels, hid, 1), ConvBNAct(hid, hid))
+        elif conv_type == "downsampling":
+            self.left_pool = nn.MaxPool2d(2, 2, return_indices=True)
+            self.left_conv = ConvBNAct(in_channels, out_channels, 1)
+            self.right_init_conv = nn.Sequential(ConvBNAct(in_channels, hid, 3, 2), ConvBNAct(hid, hid))
+        elif conv_type == "upsampling":
+            self.left_conv = ConvBNAct(in_channels, out_channels, 1)
+            self.left_pool = nn.MaxUnpool2d(2, 2)
+            self.right_init_conv = nn.Sequential(ConvBNAct(in_channels, hid, 1),
+                                                 Upsample(hid, hid, scale_factor=2, kernel_size=3, upsample_type=upsample_type))
+        elif conv_type == "dilate":
+            self.right_init_conv = nn.Sequential(ConvBNAct(in_channels, hid, 1), ConvBNAct(hid, hid, dilation=dilation))
+        elif conv_type == "asymmetric":
+            self.right_init_conv = nn.Sequential(ConvBNAct(in_channels, hid, 1), ConvBNAct(hid, hid, (5, 1)),
+                                                 ConvBNAct(hid, hid, (1, 5)))
+        else:
+            raise ValueError(f"[!] Unsupport convolution type: {conv_type}")
+        self.right_last_conv = nn.Sequential(conv1x1(hid, out_channels), nn.Dropout(drop_p))
+        self.act = Activation(act_type)
+
+    def forward(self, x, indices=None):
+        if self.training:
+            raise NotImplementedError("ENet Bottleneck: training (Dropout, PReLU gradients) has no rtseg path; call .eval()")
+        x = ops.to_nhwc(x)
+        right = self.right_init_conv(x)
+        last, act = self.right_last_conv[0], self.act.activation
+        if self.conv_type == "downsampling":
+            pooled, idx = ops.maxpool2x2_with_indices(x)
+            left = self.left_conv(pooled)
+            return last(right, res=left, res_mode=ops.RES_PRE, act=act), idx      # act(x_left + x_right)
+        if self.conv_type == "upsampling":
+            if indices is None:
+                raise ValueError("Upsampling-type conv needs pooling indices.")
+            left = ops.maxunpool2x2(self.left_conv(x), indices)
+            return last(right, res=left, res_mode=ops.RES_PRE, act=act)
+        return last(right, res=x, res_mode=ops.RES_PRE, act=act)                   # act(x + x_right)
+
+
+class BottleNeck1(nn.Module):
+    """reference models/enet.py:51-66"""
+
+    def __init__(self, in_channels, out_channels, act_type="prelu", drop_p=0.01):
+        super().__init__()
+        self.conv_pool = Bottleneck(in_channels, out_channels, "downsampling", act_type, drop_p=drop_p)
+        self.conv_regular = nn.Sequential(*[Bottleneck(out_channels, out_channels, "regular", act_type, drop_p=drop_p)
+                                            for _ in range(4)])
+
+    def forward(self, x):
+        x, indices = self.conv_pool(x)
+        return self.conv_regular(x), indices
+
+
+class BottleNeck23(nn.Module):
+    """reference models/enet.py:69-95"""
+
+    def __init__(self, in_channels, out_channels, act_type="prelu", downsample=True):
+        super().__init__()
+        self.downsample = downsample
+        if downsample:
+            self.conv_pool = Bottleneck(in_channels, out_channels, "downsampling", act_type=act_type)
+        c = out_channels
+        self.conv_regular = nn.Sequential(
+            Bottleneck(c, c, "regular", act_type), Bottleneck(c, c, "dilate", act_type, dilation=2),
+            Bottleneck(c, c, "asymmetric", act_type), Bottleneck(c, c, "dilate", act_type, dilation=4),
+            Bottleneck(c, c, "regular", act_type), Bottleneck(c, c, "dilate", act_type, dilation=8),
+            Bottleneck(c, c, "asymmetric", act_type), Bottleneck(c, c, "dilate", act_type, dilation=16))
+
+    def forward(self, x):
+        indices = None
+        if self.downsample:
+            x, indices = self.conv_pool(x)
+        x = self.conv_regular(x)
+        return (x, indices) if self.downsample else x
+
+
+class BottleNeck45(nn.Module):
+    """reference models/enet.py:98-116"""
+
+    def __init__(self, in_channels, out_channels, act_type="prelu", upsample_type=None, extra_conv=False):
+        super().__init__()
+        self.extra_conv = extra_conv
+        self.conv_unpool = Bottleneck(in_channels, out_channels, "upsampling", act_type, upsample_type)
+        self.conv_regular = Bottleneck(out_channels, out_channels, "regular", act_type)
+        if extra_conv:
+            self.conv_extra = Bottleneck(out_channels, out_channels, "regular", act_type)
+
+    def forward(self, x, indices):
+        x = self.conv_regular(self.conv_unpool(x, indices))
+        return self.conv_extra(x) if self.extra_conv else x
+
+
+class ENet(nn.Module):
+    """ENet — reference models/enet.py:14-35 (same attribute names / state-dict keys; BASELINE configs[0])."""
+
+    def __init__(self, num_class=1, n_channel=3, act_type="prelu", upsample_type="deconvolution"):
+        super().__init__()
+        self.initial = InitialBlock(n_channel, 16, act_type)
+        self.bottleneck1 = BottleNeck1(16, 64, act_type)
+        self.bottleneck2 = BottleNeck23(64, 128, act_type, True)
+        self.bottleneck3 = BottleNeck23(128, 128, act_type, False)
+        self.bottleneck4 = BottleNeck45(128, 64, act_type, upsample_type, True)
+        self.bottleneck5 = BottleNeck45(64, 16, act_type, upsample_type, False)
+        # (the reference does not hand upsample_type to this one, models/enet.py:24: the head is always
+        # ConvBNAct 1x1 + bilinear x2, align_corners=False)
+        self.fullconv = Upsample(16, num_class, scale_factor=2, act_type=act_type)
+        self.num_class = num_class
+
+    def set_act_dtype(self, dtype: Optional[torch.dtype]):
+        self.initial.act_dtype = dtype
+        return self
+
+    def _trunk(self, x):
+        x = self.initial(ops.image_view(x))
+        x, indices1 = self.bottleneck1(x)
+        x, indices2 = self.bottleneck2(x)
+        x = self.bottleneck3(x)
+        x = self.bottleneck4(x, indices2)
+        return self.bottleneck5(x, indices1)
+
+    def forward(self, x):
+        return self.fullconv(self._trunk(x))
+
+    HEAD_ALIGN_CORNERS = False   # nn.Upsample(scale_factor=2, mode='bilinear') of the head (the other nets: True)
+
+    def lowres_logits(self, x):
+        """The head's 1x1 ConvBNAct output (half resolution), before its bilinear x2."""
+        if isinstance(self.fullconv.up_conv, nn.ConvTranspose2d):
+            raise NotImplementedError("a transposed-conv head has no low-resolution logits")
+        return self.fullconv.up_conv[0](self._trunk(x))
+
+    def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
+                ignore_index: int = 255) -> torch.Tensor:
+        """uint8 class map: the head's bilinear x2 and the argmax run as the fused upsample+argmax kernel."""
+        x = ops.image_view(x)
+        f = self._trunk(x)
+        if isinstance(self.fullconv.up_conv, nn.ConvTranspose2d):
+            n, _, h, w = x.shape
+            labels = torch.empty((n, h, w), dtype=torch.uint8, device=x.device)
+            self.fullconv(f, labels=labels, want_logits=False)
+            return labels
+        low = self.fullconv.up_conv[0](f)
+        return ops.upsample_argmax(low, (2 * low.shape[2], 2 * low.shape[3]), False, target=target, confmat=confmat,
+                                   ignore_index=ignore_index)
+
+
+MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet, "enet": ENet}
 
 
 def get_model(config) -> nn.Module:
@@ -606,6 +793,6 @@ def get_model(config) -> nn.Module:
     return MODEL_HUB[name](num_class=config.num_class)
 
 
-__all__ = ["ERFNet", "FastSCNN", "DABNet", "LEDNet", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "DABModule",
+__all__ = ["ERFNet", "FastSCNN", "DABNet", "LEDNet", "ENet", "Bottleneck", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "DABModule",
            "SSnbtUnit", "get_model", "MODEL_HUB"]
 _ = (_bn_tensors, _FoldCache)

@@ -483,6 +483,40 @@ def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor, y_coff: int, x_coff: int = 
     return out
 
 
+def maxpool2x2_with_indices(x: torch.Tensor, out: Optional[torch.Tensor] = None, y_coff: int = 0, x_coff: int = 0,
+                            c: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """nn.MaxPool2d(2, 2, return_indices=True) (reference models/enet.py:130-131) on an NHWC tensor.
+    Returns (pooled NHWC tensor, uint8 [N, H/2, W/2, C] window positions — see include/rtseg.h)."""
+    _require_cuda(x, "maxpool2x2_with_indices")
+    _no_tape(x, "maxpool2x2_with_indices")
+    x = to_nhwc(x)
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct - x_coff
+    ho, wo = h // 2, w // 2
+    if out is None:
+        out = empty_nhwc(n, c, ho, wo, x.dtype, x.device)
+    idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device)
+    _lib.check(_lib.load().rtseg_maxpool2x2_idx(n, h, w, c, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff, out.data_ptr(),
+                                                out.shape[1], y_coff, idx.data_ptr(), _stream()), "rtseg_maxpool2x2_idx")
+    return out, idx
+
+
+def maxunpool2x2(x: torch.Tensor, idx: torch.Tensor, size: Optional[Tuple[int, int]] = None) -> torch.Tensor:
+    """nn.MaxUnpool2d(2, 2)(x, indices) (reference models/enet.py:138-139, 176-178) with the indices of
+    maxpool2x2_with_indices; `size` = (H, W) of the tensor that was pooled (default 2h x 2w)."""
+    _require_cuda(x, "maxunpool2x2")
+    _no_tape(x, "maxunpool2x2")
+    x = to_nhwc(x)
+    n, c, hp, wp = x.shape
+    if idx.dtype != torch.uint8 or tuple(idx.shape) != (n, hp, wp, c) or not idx.is_contiguous():
+        raise ValueError("indices must be the uint8 [N, h, w, C] tensor maxpool2x2_with_indices returned")
+    ho, wo = (2 * hp, 2 * wp) if size is None else (int(size[0]), int(size[1]))
+    out = empty_nhwc(n, c, ho, wo, x.dtype, x.device)
+    _lib.check(_lib.load().rtseg_maxunpool2x2(n, hp, wp, c, ho, wo, _dtype_code(x.dtype), x.data_ptr(), c, 0, idx.data_ptr(),
+                                              out.data_ptr(), c, 0, _stream()), "rtseg_maxunpool2x2")
+    return out
+
+
 # -------------------------------------------------------------------- head ops ----
 def upsample_bilinear(x: torch.Tensor, size: Tuple[int, int], align_corners: bool, out: Optional[torch.Tensor] = None,
                       y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:

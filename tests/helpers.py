@@ -23,7 +23,9 @@ def load_specs():
 
 
 def load_net_outputs():
-    return dict(np.load(os.path.join(GOLDEN, "net_outputs.npz")))
+    out = dict(np.load(os.path.join(GOLDEN, "net_outputs.npz")))
+    out.update(dict(np.load(os.path.join(GOLDEN, "enet_outputs.npz"))))   # tests/golden/make_golden_enet.py
+    return out
 
 
 def rel_err(out: torch.Tensor, ref: torch.Tensor) -> float:
@@ -38,4 +40,4 @@ def seeded(shape, seed, scale=1.0):
     return torch.randn(shape, generator=g) * scale
 
 # the four networks of SURVEY §8 (a7, a9, a10, a11) that have an rtseg_b200 implementation
-NETS = ["erfnet", "fastscnn", "dabnet", "lednet"]
+NETS = ["erfnet", "fastscnn", "dabnet", "lednet", "enet"]
