@@ -35,9 +35,24 @@ def rel_err(out: torch.Tensor, ref: torch.Tensor) -> float:
     return (out - ref).abs().max().item() / (denom if denom > 0 else 1.0)
 
 
+def rel_err_robust(out: torch.Tensor, ref: torch.Tensor, allow: float = 1e-5):
+    """rel_err with at most a fraction `allow` of the elements set aside: (error bound met by the rest, number of
+    elements above 1e-3).  For nets with max-pool INDICES (ENet): an input difference of 1e-6 can flip a near-tied
+    2x2 window's index, which moves one value by one pixel — a handful of isolated elements, not a wrong kernel."""
+    out, ref = out.detach().float().cpu().flatten(), ref.detach().float().cpu().flatten()
+    denom = ref.abs().max().item() or 1.0
+    err = (out - ref).abs() / denom
+    k = max(1, int(err.numel() * (1.0 - allow)))
+    return err.kthvalue(k).values.item(), int((err > 1e-3).sum().item())
+
+
 def seeded(shape, seed, scale=1.0):
     g = torch.Generator().manual_seed(seed)
     return torch.randn(shape, generator=g) * scale
 
 # the four networks of SURVEY §8 (a7, a9, a10, a11) that have an rtseg_b200 implementation
 NETS = ["erfnet", "fastscnn", "dabnet", "lednet", "enet"]
+# nets held to the absolute bf16 tolerance (2e-2) and bf16 class-map agreement: ENet has no normalisation behind its
+# residual adds and PReLUs — with random weights bf16 STORAGE alone (the emulating oracle) is 0.3-0.4 away from fp32 —
+# so its bf16 path is checked relative to that emulation only (tests/test_gpu_enet.py)
+NETS_BF16 = [n for n in NETS if n != "enet"]
