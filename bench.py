@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — images/s at 1024x2048 on N B200s (BASELINE.json metric), one JSON line on rank 0.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet|erfnet_train] [--batch B]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet|enet|erfnet_train] [--batch B]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
   python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
 
@@ -26,15 +26,22 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 H, W, NUM_CLASS = 1024, 2048, 19
-DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16, "erfnet_train": 8}
+# ENet is BASELINE configs[0]: the reference's own speed protocol (tools/test_speed.py: ratio 0.5 -> 512 x 1024)
+WORKLOAD_HW = {"enet": (512, 1024)}
+DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16, "enet": 16, "erfnet_train": 8}
+
+
+def hw_of(workload):
+    return WORKLOAD_HW.get(workload, (H, W))
 WORKLOAD_NAME = {
     "erfnet": "ERFNet inference batch {b} at 1024x2048 (BASELINE configs[1])",
     "fastscnn": "Fast-SCNN inference batch {b} at 1024x2048 (BASELINE configs[2])",
     "dabnet": "DABNet inference batch {b} at 1024x2048 (SURVEY §8 a10)",
     "lednet": "LEDNet inference batch {b} at 1024x2048 (SURVEY §8 a11)",
+    "enet": "ENet inference batch {b} at 512x1024 (BASELINE configs[0]: tools/test_speed.py size; CPU arm = that protocol)",
     "erfnet_train": "ERFNet training step (fwd + OHEM + bwd + SGD), batch {b} per GPU at 1024x1024 (SURVEY §8d config 5)",
 }
-NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet",
+NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet", "enet": "ENet",
              "erfnet_train": "ERFNet train step"}
 
 
@@ -67,6 +74,9 @@ def cpu_reference_run(workload: str, steps: int, warmup: int):
     torch.set_num_threads(cores)
     spec = load_specs()[workload]["spec"]
     sd = ref_nets.make_state(spec, 1, True)
+    H, W = hw_of(workload)
+    if workload == "enet":      # config 1: 10 warm-ups, >= 20 timed iterations (reference tools/test_speed.py:29-60 minus the cuda syncs)
+        steps, warmup = max(steps, 20), max(warmup, 10)
     x = ref_nets.make_input(0, 1, H, W)
     fwd = ref_nets.FORWARD[workload]
     with torch.no_grad():
@@ -243,7 +253,7 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
                                              "achieved_gbs": round(v[1] / (v[0] * 1e-3) / 1e9, 1) if v[0] else None,
                                              "frac": round(v[1] / (v[0] * 1e-3) / 1e9 / peak_gbs, 4) if v[0] else None}
                     for k, v in fam.items()}
-    elif workload in ("dabnet", "lednet"):
+    elif workload in ("dabnet", "lednet", "enet"):
         # every fused conv layer is captured with the tensors / keyword arguments the net really passes, timed
         # alone, and binned by kernel family; the family with the largest share of the time is reported
         from rtseg_b200.modules import Conv2d, _FusedConvMixin
@@ -252,7 +262,7 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
             if isinstance(m, (Conv2d, _FusedConvMixin)):
                 hooks.append(m.register_forward_pre_hook(
                     lambda mod, a, kw: calls.append((mod, a, dict(kw))), with_kwargs=True))
-        x_in = torch.randn((batch, 3, H, W), device=dev)
+        x_in = torch.randn((batch, 3, *hw_of(workload)), device=dev)
         with torch.no_grad():
             model.lowres_logits(x_in)
         for hk in hooks:
@@ -328,6 +338,9 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
 
 
 PARITY_MIN_AGREE = 0.985  # bf16 class map vs the fp32 oracle on the benchmark's own weights (default init)
+# ENet (no normalisation behind its residual adds): bf16 storage alone moves ~4 % of a random-init class map; the
+# parity tests hold its bf16 path to the storage-emulating oracle instead (tests/test_gpu_enet.py)
+PARITY_MIN_BY_WORKLOAD = {"enet": 0.93}
 
 
 def parity_check(model, eng, workload: str):
@@ -355,9 +368,10 @@ def parity_check(model, eng, workload: str):
     per_image = (got == want).float().mean(dim=(1, 2)).tolist()
     agree = float((got == want).float().mean().item())
     out = {"argmax_agree": round(agree, 6), "per_image": [round(v, 6) for v in per_image], "n_images": len(idx),
-           "images": idx, "classes_present": int(want.unique().numel()), "min_required": PARITY_MIN_AGREE,
+           "images": idx, "classes_present": int(want.unique().numel()),
+           "min_required": PARITY_MIN_BY_WORKLOAD.get(workload, PARITY_MIN_AGREE),
            "oracle": "oracle/ref_nets.py fp32 on the host, same weights and inputs; labels from the timed bf16 graph"}
-    if min(per_image) < PARITY_MIN_AGREE:
+    if min(per_image) < out["min_required"]:
         raise SystemExit(f"bench.py: parity check failed: {json.dumps(out)}")
     return out
 
@@ -505,7 +519,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     batch = args.batch or DEFAULT_BATCH[args.workload]
     workload_name = WORKLOAD_NAME[args.workload].format(b=batch)
-    metric = f"images/sec @1024x2048 ({NET_LABEL[args.workload]})"
+    metric = "images/sec @%dx%d (%s)" % (*hw_of(args.workload), NET_LABEL[args.workload])
 
     train = args.workload == "erfnet_train"
     if train:
@@ -596,7 +610,7 @@ def library_baseline(workload: str, batch: int, steps: int = 5):
             b = batch
             while True:
                 try:
-                    x = torch.randn((b, 3, H, W), device="cuda").to(dt)
+                    x = torch.randn((b, 3, *hw_of(workload)), device="cuda").to(dt)
                     if cl:
                         x = x.contiguous(memory_format=torch.channels_last)
                     fwd = ref_nets.FORWARD[workload]
@@ -637,12 +651,13 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     from rtseg_b200 import _lib
 
     workload_name = WORKLOAD_NAME[workload].format(b=batch)
-    metric = f"images/sec @1024x2048 ({NET_LABEL[workload]})"
+    metric = "images/sec @%dx%d (%s)" % (*hw_of(workload), NET_LABEL[workload])
     _PHASE[0] = f"{workload}: set-up, warm-up and device-timed steps"
     torch.manual_seed(1)  # the reference's seed (configs/base_config.py:70); default random init
     model = rtseg_b200.nets.MODEL_HUB[workload](num_class=NUM_CLASS).eval().cuda()
     model.set_act_dtype(torch.bfloat16)
     u8 = args.input == "u8"
+    H, W = hw_of(workload)
     eng = rtseg_b200.InferenceEngine(model, batch=batch, height=H, width=W, use_graph=True, slots=2,
                                      in_dtype=torch.uint8 if u8 else torch.float32)
 
