@@ -724,6 +724,8 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if args.workload == "erfnet_train":
+            os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")   # DDP step captured in a CUDA graph (tools/train_bench.py)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     import rtseg_b200

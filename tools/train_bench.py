@@ -31,7 +31,11 @@ def build(batch, size, fp32, rank, local, world):
         model.set_act_dtype(torch.bfloat16)
     if world > 1:
         model = torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
-        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
+        side = torch.cuda.Stream()      # DDP built on a side stream: a requirement for capturing its step in a CUDA graph
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
+        torch.cuda.current_stream().wait_stream(side)
     crit = rloss.OhemCELoss(0.7, 255)
     if os.environ.get("RTSEG_TORCH_SGD") == "1":     # A/B: the stock optimizer (~5 ATen kernels per parameter tensor)
         opt = torch.optim.SGD(model.parameters(), lr=0.01 * world, momentum=0.9, weight_decay=1e-4)
@@ -52,15 +56,19 @@ def make_step(model, crit, opt, x, y, graph, world):
         opt.step()
         return loss
 
-    if not (graph and world == 1):
+    ddp_graph = os.environ.get("RTSEG_DDP_GRAPH", "1") == "1"
+    if not graph or (world > 1 and not ddp_graph):
         return eager
+    # One CUDA graph for the whole step.  Under DDP the graph also holds the NCCL collectives (the bucketed gradient
+    # all-reduce and the 148 small SyncBatchNorm all-reduces): ~3,000 kernel launches and the collectives' launch
+    # latency leave the host's critical path.  DDP rebuilds its buckets after the first iterations, hence 11 warm-ups.
     for _ in range(2):
         eager()
     torch.cuda.synchronize()
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):   # warm-up on a side stream with the gradients kept allocated
-        for _ in range(2):
+        for _ in range(2 if world == 1 else 11):
             opt.zero_grad(set_to_none=False)
             crit(model(x), y).backward()
             opt.step()
@@ -85,6 +93,7 @@ def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True):
     own_pg = False
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")   # the watchdog thread must not touch a capturing stream
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         own_pg = True
     from rtseg_b200 import _lib
@@ -95,10 +104,11 @@ def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True):
         loss = step()
     torch.cuda.synchronize()
     launches_before = _lib.launch_count()
-    if not (graph and world == 1):   # count one eager step's librtseg launches
+    graphed = getattr(step, "__name__", "") == "replay"
+    if not graphed:   # count one eager step's librtseg launches
         step()
         torch.cuda.synchronize()
-    per_step = (_lib.launch_count() - launches_before) if not (graph and world == 1) else None
+    per_step = (_lib.launch_count() - launches_before) if not graphed else None
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -125,7 +135,7 @@ def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True):
         dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
     out = {"ms_per_step": ms.item(), "images_per_s": world * batch / ms.item() * 1e3,
            "e2e_images_per_s": world * batch / e2e.item(), "h2d_bytes": hx.numel() * 4 + hy.numel() * 8, "d2h_bytes": 4,
-           "loss": lv, "world": world, "batch": batch, "size": size, "graph": bool(graph and world == 1),
+           "loss": lv, "world": world, "batch": batch, "size": size, "graph": bool(graphed),
            "launches_per_step": per_step, "capture_launches": _lib.launch_count() - l0,
            "peak_mem_gib": torch.cuda.max_memory_allocated() / 2 ** 30, "model": model}
     if own_pg:
