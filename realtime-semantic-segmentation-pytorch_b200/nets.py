@@ -318,9 +318,35 @@ class FastSCNN(nn.Module):
         # tensor-core kernel through the TMA-store path; the fused head reads the first num_class channels
         cpad = (self.num_class + 15) // 16 * 16
         buf = ops.empty_nhwc(n, cpad, h, w, f.dtype, f.device)
-        self.classifier[2](f, out=buf)
+        head = self.classifier[2]
+        if f.dtype == torch.bfloat16 and not head[1].training and ops.USE_TENSOR_CORES and head[0].in_channels % 16 == 0:
+            # the buffer is private: write all cpad channels (zero weights -> the pad channels hold act(0)), so that
+            # every pixel leaves the kernel as one full 64-byte row instead of a 38-byte partial one
+            ops.conv(self._padded_head(cpad), f, out=buf)
+        else:
+            head(f, out=buf)
         return ops.upsample_argmax(buf, x.shape[2:], True, target=target, confmat=confmat, ignore_index=ignore_index,
                                    num_classes=self.num_class)
+
+    def _padded_head(self, cpad):
+        """classifier[2] folded with its output channels padded to cpad (scale 1, shift 0, zero weights)."""
+        import dataclasses
+        head = self.classifier[2]
+        folded, post = head._folded()
+        if post is not None:
+            raise NotImplementedError("non-pointwise activation in the classifier head")
+        cached = self.__dict__.get("_rtseg_head_pad")
+        if cached is None or cached[0] is not folded:
+            def pad(t, fill):
+                out = torch.full((cpad,), fill, dtype=torch.float32, device=folded.w_tc.device)
+                if t is not None:
+                    out[:folded.cout] = t
+                return out
+            fp = dataclasses.replace(folded, cout=cpad, scale=pad(folded.scale, 1.0), shift=pad(folded.shift, 0.0),
+                                     slope=None if folded.slope is None else pad(folded.slope, 0.0), w_tc_scaled=None)
+            cached = (folded, fp)
+            self.__dict__["_rtseg_head_pad"] = cached
+        return cached[1]
 
 
 # ------------------------------------------------------------------------------ DABNet ----
