@@ -850,7 +850,11 @@ static bool plan_tc(int cin, int cout_pad, int nwtaps, int nacc, bool staged_out
     }
     // Split staging: stage one ob-channel sub-box at a time through two half-size buffers when that buys ring stages.
     pl.split_out = 0;
-    static const int split_knob = getenv("RTSEG_TC_SPLIT") ? atoi(getenv("RTSEG_TC_SPLIT")) : 1;
+    // Measured (round 2, B200): five ring stages instead of three did NOT speed the 128-channel layers up (0.0735 vs
+    // 0.0698 ms per layer, Fast-SCNN's wide pointwise layers 4 % slower) — those layers are bound by the shared-memory
+    // data pipe (tensor-core operand fetch 37 % + LSU 22 % of its cycles under ncu), not by bytes in flight, and the
+    // second bar.sync pair per unit costs more than the stages give.  Off by default; RTSEG_TC_SPLIT=1 enables it.
+    static const int split_knob = getenv("RTSEG_TC_SPLIT") ? atoi(getenv("RTSEG_TC_SPLIT")) : 0;
     if (split_knob && allow_split && out_buf && ms == 1 && nacc == 1 && bn / pick_kb(bn) >= 2) {
       const uint32_t half = (uint32_t)kTileM * pick_kb(bn) * 2;
       const uint32_t fixed_split = b_bytes + 2 * half + misc;
