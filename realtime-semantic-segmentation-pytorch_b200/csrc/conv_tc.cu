@@ -111,6 +111,15 @@ struct TcParams {
   TcTap taps[kMaxTcTaps];
 };
 
+#ifdef RTSEG_TC_TRACE
+// Development aid (tools/tc_trace.py builds with -DRTSEG_TC_TRACE): CTA 0 records clock64() at the hand-over points of
+// its first tiles.  Not compiled into the product library.
+__device__ long long g_tc_trace[64][16];
+#define TC_TRACE(tile_, ev_) do { if (blockIdx.x == 0 && blockIdx.y == 0 && (tile_) < 64) g_tc_trace[(tile_)][(ev_)] = clock64(); } while (0)
+#else
+#define TC_TRACE(tile_, ev_) do { } while (0)
+#endif
+
 __device__ __forceinline__ void epi_bar_sync(int id) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kEpiThreads) : "memory");
 }
@@ -265,6 +274,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         if (p.a_share) {
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+            TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), kb == 0 ? 0 : 1);
             mbar_expect_tx(full_bar + 8 * stage, p.a_tx_bytes);
             tma_load_4d(s_a + stage * kStageBytes, &maps.a[0], full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.a_dx,
                         h0 + p.a_dy, img);
@@ -307,6 +317,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
         mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, dead);
         tc_fence_after();
+        if (lane == 0) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), 2);
         const uint32_t d_tmem = tmem_base + acc * acc_cols;
         uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
         if (p.a_share) {
@@ -314,6 +325,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int kb = 0; kb < p.nkb; ++kb) {
             mbar_wait(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
+            if (lane == 0) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), kb == 0 ? 3 : 4);
             if (elect_one()) {
             if (p.nacc == 1) {
               // forward conv: one accumulator, one weight tap per A tap — the leanest possible issue loop (this single
@@ -386,6 +398,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         }
         if (elect_one()) umma_commit(tfull_bar + 8 * acc);  // accumulators complete -> epilogue
         __syncwarp();
+        if (lane == 0) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), 5);
         // The residual stages belong to the epilogue, but this warp must still SEE each of their fills complete
         // before it moves on: a parity wait can only tell "this lap" from "the previous lap".  If the ring is
         // shorter than one unit's boxes (stages < A boxes + residual boxes), the slot of a later A tile held a
@@ -553,6 +566,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // of the same unit).
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
+        if (elected) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), 6);
         if constexpr (RES) {
           ring_advance(p.a_stages_per_unit);
           res_first = ring;
@@ -737,6 +751,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);
+      if (elected) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), 7);
       if (++acc == 2) acc = 0, acc_phase ^= 1;
     }
     if (elected && p.y_mode == 2) bulk_wait_all();
@@ -1241,6 +1256,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_tc_kernel(const __gr
 }  // namespace rtseg
 
 using namespace rtseg;
+
+#ifdef RTSEG_TC_TRACE
+extern "C" int rtseg_tc_trace_read(long long *out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_tc_trace, sizeof(long long) * 64 * 16) == cudaSuccess ? 0 : -3;
+}
+#endif
 
 extern "C" int rtseg_conv_tc_supported(const rtseg_conv_desc *d) {
   if (!d) return 0;
