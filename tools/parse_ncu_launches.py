@@ -51,6 +51,43 @@ def main():
             scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
             d[metric] = val * scale
     launches = list(per_launch.values())
+    if "--families" in sys.argv:
+        # round-2 form: one step per workload (a step = the launches from one image-stem launch up to the next),
+        # DRAM traffic and time share per kernel family -> JSON on stdout (profiles/traffic_rNN.json)
+        starts = [i for i, d in enumerate(launches) if d["name"].startswith(("stem_kernel", "stem_tc_kernel"))]
+        out = {"source": path, "note": "ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum "
+                                        "--clock-control none on `python bench.py --steps 2 --warmup 3`: launches are serialised and "
+                                        "cold, read the SHARES; one step = stem launch .. next stem launch"}
+        steps_by = {}
+        for a, b in zip(starts[:-1], starts[1:]):
+            step = launches[a:b]
+            wl = "erfnet" if any(x["name"].startswith("conv_pair_tc_kernel") for x in step) else (
+                "fastscnn" if any(x["name"].startswith("dw_tma_kernel") for x in step) else None)
+            if wl is None or len(step) < 20:
+                continue
+            steps_by.setdefault(wl, []).append(step)
+        seen = {}
+        for wl, steps_ in steps_by.items():   # a forward pass has the most common launch count (the roofline pass of
+            from collections import Counter   # bench.py re-launches single layers behind the last stem: not a step)
+            n_mode = Counter(len(x) for x in steps_).most_common(1)[0][0]
+            seen[wl] = [x for x in steps_ if len(x) == n_mode][-1]
+        for wl, step in seen.items():
+            total = sum(x.get("us", 0.0) for x in step) or 1.0
+            fams = {}
+            for x in step:
+                f = fams.setdefault(x["name"].split("<")[0], {"launches": 0, "us": 0.0, "rd": 0.0, "wr": 0.0})
+                f["launches"] += 1
+                f["us"] += x.get("us", 0.0)
+                f["rd"] += x.get("dram__bytes_read.sum", 0.0)
+                f["wr"] += x.get("dram__bytes_write.sum", 0.0)
+            out[wl] = {"batch": 16 if wl == "erfnet" else 32, "launches_per_step": len(step), "us_per_step_under_ncu": round(total, 1),
+                       "families": {k: {"launches_per_step": v["launches"], "share_of_step": round(v["us"] / total, 4),
+                                        "dram_bytes_per_step": int(v["rd"] + v["wr"]), "dram_read_bytes": int(v["rd"]),
+                                        "dram_write_bytes": int(v["wr"]),
+                                        "note": "dram__bytes_read.sum + dram__bytes_write.sum over this family's launches of one step"}
+                                    for k, v in sorted(fams.items(), key=lambda kv: -kv[1]["us"])}}
+        print(json.dumps(out, indent=1))
+        return
     if "--one-step" in sys.argv:
         # one forward pass = from a stem kernel launch up to (not including) the next one
         starts = [i for i, d in enumerate(launches) if d["name"].startswith(("stem_kernel", "stem_tc_kernel"))]
