@@ -91,13 +91,6 @@ __device__ __forceinline__ uint64_t pair_desc(uint32_t addr) {
   return (uint64_t)((addr & 0x3ffffu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
 }
 
-// {lo half = bf16(max(a, 0)), hi half = bf16(max(b, 0))}: conversion and ReLU in one instruction (NaN stays NaN).
-__device__ __forceinline__ uint32_t pack_relu_bf16(float a, float b) {
-  uint32_t d;
-  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
-  return d;
-}
-
 // 16 accumulator columns (+ residual) -> folded BatchNorm -> clamp -> 8 packed bf16 pairs.  RELU: the clamp is
 // [0, inf) and rides in the conversion; otherwise NaN-propagating max / min with (lo, hi).
 // FOLD: the accumulator already holds scale * conv + shift (pre-scaled weights, bias MMA); a residual then enters as

@@ -130,6 +130,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<const uint32_t *>(&h);
 }
+// {lo half = bf16(max(a, 0)), hi half = bf16(max(b, 0))}: conversion and ReLU in one instruction (NaN stays NaN).
+__device__ __forceinline__ uint32_t pack_relu_bf16(float a, float b) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
+  return d;
+}
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
