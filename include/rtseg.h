@@ -384,6 +384,26 @@ int rtseg_conv_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, fl
  * them, the accumulators stay in tensor memory for the whole kernel.  Same arguments and dw layout. */
 int rtseg_conv_wgrad_tc_supported(const rtseg_conv_desc *d);
 int rtseg_conv_wgrad_tc(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
+/* Row T, depthwise blocks (reference models/modules.py:46-59 `DWConvBNAct` under autograd; channel multiplier 1):
+ * d describes the FORWARD convolution (n, h, w = its input; x_ctotal / x_coff = the slice of x and dx, y_ctotal /
+ * y_coff = the slice of dy).  w and dw are fp32 [kh][kw][c]; dw is caller-zeroed and accumulated into. */
+int rtseg_conv_dw_bwd_data(const rtseg_conv_desc *d, const void *dy, const float *w, void *dx, rtseg_stream_t stream);
+int rtseg_conv_dw_wgrad(const rtseg_conv_desc *d, const void *x, const void *dy, float *dw, rtseg_stream_t stream);
+/* Slope gradient of nn.PReLU (reference models/modules.py:119; enet.py:165 `self.act(x + x_right)`):
+ * dslope[c] (fp64, caller-zeroed) += sum over pixels of dz * v * [v <= 0], v = scale[c] * (y + res) + shift[c];
+ * scale / shift / res may be NULL (v = y). */
+int rtseg_prelu_slope_grad(int64_t npix, int32_t c, int32_t dtype, const void *dz, int32_t d_ctotal, int32_t d_coff,
+                           const void *y, int32_t y_ctotal, int32_t y_coff, const void *res, int32_t r_ctotal,
+                           int32_t r_coff, const float *scale, const float *shift, double *dslope, rtseg_stream_t stream);
+/* Adjoints of the resize / pooling steps inside Fast-SCNN's pyramid pooling, feature fusion and output head
+ * (reference models/modules.py:145-156, fastscnn.py:30, 88) for the training step: dx of rtseg_upsample_bilinear
+ * (a gather per input pixel with the forward's own index arithmetic: deterministic) and of rtseg_adaptive_avgpool
+ * (dy: dense NHWC [n][p][p][c] in `dtype`). */
+int rtseg_upsample_bilinear_bwd(int32_t n, int32_t hi, int32_t wi, int32_t c, int32_t ho, int32_t wo, int32_t align_corners,
+                                int32_t dtype, const void *dy, int32_t g_ctotal, int32_t g_coff, void *dx, int32_t x_ctotal,
+                                int32_t x_coff, rtseg_stream_t stream);
+int rtseg_adaptive_avgpool_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype, const void *dy, void *dx,
+                               int32_t x_ctotal, int32_t x_coff, rtseg_stream_t stream);
 /* ---- f3: optimizer step + weight mirror in one launch ----------------------
  * Replaces torch.optim.SGD.step() as the reference configures it (utils/optimizer.py:8-12: lr, momentum, weight
  * decay; dampening 0, no Nesterov) followed by ModelEmaV2.update (utils/model_ema.py:28-40:

@@ -98,6 +98,12 @@ PROTOTYPES = {
     "rtseg_conv_wgrad": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_conv_wgrad_tc_supported": (c_i32, [_DP]),
     "rtseg_conv_wgrad_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_conv_dw_bwd_data": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_conv_dw_wgrad": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_prelu_slope_grad": (c_i32, [c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_vp,
+                                       c_vp, c_vp]),
+    "rtseg_upsample_bilinear_bwd": (c_i32, [c_i32] * 8 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_adaptive_avgpool_bwd": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_opt_chunk_elems": (c_i32, []),
     "rtseg_sgd_ema_step": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp]),
     "rtseg_maxpool3x3s2_bwd": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),

@@ -315,6 +315,28 @@ struct Vec16<__nv_bfloat16> {
   }
 };
 
+// ---- bilinear resize geometry (F.interpolate(mode='bilinear')), shared by the forward and adjoint kernels ----
+__host__ __device__ __forceinline__ float resize_scale(int in, int out, int align) {
+  if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f;
+  return (float)in / (float)out;
+}
+
+__device__ __forceinline__ void src_index(int dst, float scale, int in, int align, int &i0, int &i1, float &l0,
+                                          float &l1) {
+  float s;
+  if (align) {
+    s = scale * (float)dst;
+  } else {
+    s = scale * ((float)dst + 0.5f) - 0.5f;
+    if (s < 0.f) s = 0.f;
+  }
+  i0 = (int)s;
+  if (i0 > in - 1) i0 = in - 1;
+  i1 = i0 + (i0 < in - 1 ? 1 : 0);
+  l1 = s - (float)i0;
+  l0 = 1.f - l1;
+}
+
 #endif  // __CUDACC__
 
 }  // namespace rtseg

@@ -22,27 +22,6 @@
 
 namespace rtseg {
 
-__host__ __device__ __forceinline__ float resize_scale(int in, int out, int align) {
-  if (align) return out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f;
-  return (float)in / (float)out;
-}
-
-__device__ __forceinline__ void src_index(int dst, float scale, int in, int align, int &i0, int &i1, float &l0,
-                                          float &l1) {
-  float s;
-  if (align) {
-    s = scale * (float)dst;
-  } else {
-    s = scale * ((float)dst + 0.5f) - 0.5f;
-    if (s < 0.f) s = 0.f;
-  }
-  i0 = (int)s;
-  if (i0 > in - 1) i0 = in - 1;
-  i1 = i0 + (i0 < in - 1 ? 1 : 0);
-  l1 = s - (float)i0;
-  l0 = 1.f - l1;
-}
-
 // torch.max(dim) semantics: first maximal index, NaN beats everything.
 __device__ __forceinline__ void argmax_step(float v, int c, float &best, int &idx) {
   if (v > best || (v != v && best == best)) {

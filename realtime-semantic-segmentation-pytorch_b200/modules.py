@@ -92,9 +92,12 @@ class _FusedConvMixin:
         return cache.get(tensors, lambda: ops.fold_conv(conv, bn, act, host=True))
 
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, act2=0, r_coff=0):
-        if self[1].training and self[0].groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff, act2, r_coff):
+        if self[1].training and out is None and x_coff == 0 and y_coff == 0 and r_coff == 0 and act2 == 0 \
+                and res_mode in (ops.RES_NONE, ops.RES_POST):
             from . import train   # batch statistics + autograd: Conv -> BN -> act as two tape nodes on rtseg kernels
-            return train.conv_bn_act(self, x)
+            z = train.conv_bn_act(self, x)
+            # a POST residual is the block's `x + conv(x)` (reference fastscnn.py:119, dabnet.py:95-97): a plain add node
+            return z if res_mode == ops.RES_NONE else z + ops.to_nhwc(res)
         _check_eval(self, self[1])
         folded, post = self._folded()
         y = ops.conv(folded, ops.to_nhwc(x), res=res, res_mode=res_mode, out=out, x_coff=x_coff, y_coff=y_coff,
@@ -123,14 +126,15 @@ class Conv2d(nn.Conv2d):
 
     def forward(self, x, res=None, res_mode=ops.RES_NONE, out=None, x_coff=0, y_coff=0, bn=None, act=None):
         cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
-        if self.training and (bn is None or bn.training) and self.groups == 1 and _plain_call(res, res_mode, out, x_coff, y_coff) \
-                and torch.is_grad_enabled():
+        if self.training and (bn is None or bn.training) and out is None and x_coff == 0 and y_coff == 0 \
+                and res_mode in (ops.RES_NONE, ops.RES_PRE) and torch.is_grad_enabled():
             from . import train
             y = train.conv(self, x)
+            pre = res if res_mode == ops.RES_PRE else None     # act(bn(conv(x) + res)), reference fastscnn.py:90-92
             if bn is not None:
-                return train.bn_act(bn, act, y)
-            if act is not None:
-                raise NotImplementedError("training through a bare convolution with a fused activation is not built")
+                return train.bn_act(bn, act, y, res=pre)
+            if act is not None or pre is not None:
+                return train.act(act, y, pre)                 # act(conv(x) + res), reference enet.py:165-181
             return y
         tensors = [self.weight, self.bias, *_bn_tensors(bn), getattr(act, "weight", None)]
         folded, post = cache.get(tensors, lambda: ops.fold_conv(self, bn, act, host=True))
@@ -294,13 +298,20 @@ class PyramidPoolingModule(nn.Module):
         self.conv = PWConvBNAct(2 * in_channels, out_channels, act_type=act_type, bias=bias)
 
     def forward(self, x):
-        if self.conv[1].training or (torch.is_grad_enabled() and x.requires_grad):
-            raise NotImplementedError("PyramidPoolingModule: the pooling / resize kernels have no backward, so a training-"
-                                      "mode forward would leave the stage convolutions without gradients; call .eval() "
-                                      "under torch.no_grad() (no silent partial autograd graph)")
         x = ops.to_nhwc(x)
         n, c, h, w = x.shape
         stages = [self.stage1, self.stage2, self.stage3, self.stage4]
+        if self.conv[1].training or (torch.is_grad_enabled() and x.requires_grad):
+            from . import train   # tape nodes with adjoint kernels; the concat is a copy node, as in the reference
+            if not (self.conv[1].training and torch.is_grad_enabled()):
+                raise NotImplementedError("PyramidPoolingModule: gradients need .train() (batch-statistics BatchNorm) — no "
+                                          "silent partial autograd graph")
+            feats = [x]
+            for st in stages:
+                p = st[0].output_size
+                p = int(p if isinstance(p, int) else p[0])
+                feats.append(train.upsample_bilinear(st[1](train.adaptive_avgpool(x, p)), (h, w), True))
+            return self.conv(ops.to_nhwc(torch.cat(feats, dim=1)))
         hid = stages[0][1].out_channels
         cat = ops.empty_nhwc(n, c + 4 * hid, h, w, x.dtype, x.device)
         ops.copy_into_slice(x, cat)  # the pass-through operand of the concat

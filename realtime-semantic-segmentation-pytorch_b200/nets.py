@@ -219,8 +219,11 @@ class LearningToDownsample(nn.Sequential):
         x = ops.image_view(x)
         stem = self[0]
         conv = stem[0]
-        if conv.in_channels <= 4 and conv.out_channels <= 32:
-            _check_eval(self, stem[1])
+        if stem[1].training:
+            from . import train   # the stem as tape nodes (3 input channels padded to 16 for the tensor-core kernels)
+            xn = ops.to_nhwc(x, self.act_dtype or _param_dtype(stem))
+            x = train.conv_bn_act_aligned(stem, xn, pad_input=True) if conv.in_channels <= 4 else stem(xn)
+        elif conv.in_channels <= 4 and conv.out_channels <= 32:
             folded, post = stem._folded()
             if post is not None:
                 raise NotImplementedError("non-pointwise activation in the stem")
@@ -263,7 +266,11 @@ class FeatureFusionModule(nn.Module):
     def forward(self, higher_res_feat, lower_res_feat):
         size = higher_res_feat.shape[2:]
         hi = self.higher_res_conv(higher_res_feat)
-        lo = ops.upsample_bilinear(lower_res_feat, size, True)
+        if self.non_linear[0].training:
+            from . import train
+            lo = train.upsample_bilinear(lower_res_feat, size, True)
+        else:
+            lo = ops.upsample_bilinear(lower_res_feat, size, True)
         lo = self.lower_res_conv[0](lo)
         return self.lower_res_conv[1](lo, res=hi, res_mode=ops.RES_PRE, bn=self.non_linear[0],
                                       act=self.non_linear[1].activation)
@@ -306,6 +313,9 @@ class FastSCNN(nn.Module):
     def forward(self, x):
         """Full-resolution logits like the reference (bilinear x8, align_corners=True)."""
         x = ops.image_view(x)
+        if self.classifier[2][1].training:
+            from . import train
+            return train.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
         return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
@@ -680,11 +690,15 @@ class Bottleneck(nn.Module):
         self.act = Activation(act_type)
 
     def forward(self, x, indices=None):
-        if self.training:
-            raise NotImplementedError("ENet Bottleneck: training (Dropout, PReLU gradients) has no rtseg path; call .eval()")
         x = ops.to_nhwc(x)
-        right = self.right_init_conv(x)
         last, act = self.right_last_conv[0], self.act.activation
+        if self.training:
+            if self.conv_type in ("downsampling", "upsampling"):
+                raise NotImplementedError("ENet Bottleneck: the pooling pair has no adjoint kernels; only the regular / dilate / "
+                                          "asymmetric bottlenecks train on this path")
+            from . import train   # Dropout is torch's own elementwise mask node (reference enet.py:160)
+            return train.act(act, self.right_last_conv[1](last(self.right_init_conv(x))), x)
+        right = self.right_init_conv(x)
         if self.conv_type == "downsampling":
             pooled, idx = ops.maxpool2x2_with_indices(x)
             left = self.left_conv(pooled)

@@ -11,9 +11,15 @@ backward are librtseg launches — autograd is only the tape:
   update, normalise + activation in one pass (`rtseg_affine_act`), optionally on `y + res` (NonBt1DBlock's
   `+= x` before its last BatchNorm, models/erfnet.py:76-82); backward = one reduction + one apply pass.
 * `_MaxPoolFn`: InitialBlock's pool branch.
+* `_DWConvFn`: depthwise convolutions (DWConvBNAct, reference models/modules.py:46-59): forward = the inference
+  depthwise kernel, data gradient = `rtseg_conv_dw_bwd_data`, weight gradient = `rtseg_conv_dw_wgrad`.
+* PReLU (reference models/modules.py:119): the slope rides through `_BNActFn` / `_ActFn`; its gradient is
+  `rtseg_prelu_slope_grad`.
+* `_BilinearFn`, `_AdaptiveAvgPoolFn`: the resize / pooling steps of Fast-SCNN's pyramid pooling, feature fusion
+  and output head (reference models/modules.py:134-158, fastscnn.py:30, 88) with their adjoint kernels.
 
-Nothing here falls back to ATen convolutions or cuDNN; unsupported cases (depthwise weight gradients, PReLU
-slope gradients) raise.
+Nothing here falls back to ATen convolutions or cuDNN; unsupported cases (grouped convolutions other than
+depthwise with multiplier 1, glu / softmax blocks) raise.
 """
 from __future__ import annotations
 
@@ -35,18 +41,18 @@ WGRAD_TC = os.environ.get("RTSEG_WGRAD_TC", "1") != "0"   # tcgen05 weight gradi
 class _Spec:
     """Quacks like an nn.Conv2d / nn.ConvTranspose2d for ops.fold_conv, around a bare weight tensor."""
 
-    def __init__(self, weight, bias, stride, dilation, padding, transposed):
+    def __init__(self, weight, bias, stride, dilation, padding, transposed, groups=1):
         self.weight, self.bias = weight, bias
         self.kernel_size = tuple(weight.shape[2:])
         self.stride, self.dilation, self.padding = (stride, stride), (dilation, dilation), tuple(padding)
         self.transposed = transposed
-        self.groups = 1
+        self.groups = groups
         self.padding_mode = "zeros"
         self.output_padding = (1, 1)
         if transposed:
             self.in_channels, self.out_channels = weight.shape[0], weight.shape[1]
         else:
-            self.out_channels, self.in_channels = weight.shape[0], weight.shape[1]
+            self.out_channels, self.in_channels = weight.shape[0], weight.shape[1] * groups
 
 
 def _conv_raw(x, weight, bias, stride, dilation, padding, transposed):
@@ -123,18 +129,78 @@ class _ConvFn(torch.autograd.Function):
         return dx, dw, db, None, None, None, None
 
 
+class _DWConvFn(torch.autograd.Function):
+    """Depthwise convolution (groups = cin = cout): reference models/modules.py:46-59 under autograd."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, dilation, padding):
+        x = ops.to_nhwc(x)
+        c = weight.shape[0]
+        ctx.save_for_backward(x, weight)
+        ctx.meta = (stride, dilation, tuple(padding), bias is not None)
+        f, _ = ops.fold_conv(_Spec(weight.detach(), None if bias is None else bias.detach(), stride, dilation, padding, False,
+                                   groups=c))
+        return ops.conv(f, x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride, dilation, padding, has_bias = ctx.meta
+        dy = ops.to_nhwc(dy.to(x.dtype))
+        n, c, h, w = x.shape
+        kh, kw = weight.shape[2:]
+        lib = _lib.load()
+        d = ConvDesc(n, h, w, c, c, kh, kw, stride, dilation, padding[0], padding[1], c, ops._dtype_code(x.dtype), 0, 0.0, 0.0,
+                     0, 0, c, 0, c, 0, 0, 0)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            w32 = weight.detach()[:, 0].permute(1, 2, 0).float().contiguous()          # [kh][kw][c]
+            dx = torch.empty_like(x, memory_format=torch.channels_last)
+            _lib.check(lib.rtseg_conv_dw_bwd_data(C.byref(d), dy.data_ptr(), w32.data_ptr(), dx.data_ptr(), ops._stream()),
+                       "rtseg_conv_dw_bwd_data")
+        if ctx.needs_input_grad[1]:
+            acc = torch.zeros((kh, kw, c), dtype=torch.float32, device=x.device)
+            _lib.check(lib.rtseg_conv_dw_wgrad(C.byref(d), x.data_ptr(), dy.data_ptr(), acc.data_ptr(), ops._stream()),
+                       "rtseg_conv_dw_wgrad")
+            dw = acc.permute(2, 0, 1).unsqueeze(1).contiguous().to(weight.dtype)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = _channel_sums(dy, c, want_sq=False)[0].to(weight.dtype)
+        return dx, dw, db, None, None, None
+
+
+def _slope32(prelu_w, c):
+    """The PReLU weight (1 or c parameters) as c contiguous fp32 slopes."""
+    s = prelu_w.detach().float().reshape(-1)
+    if s.numel() not in (1, c):
+        raise ValueError("PReLU num_parameters must be 1 or the number of channels")
+    return s.expand(c).contiguous()
+
+
+def _slope_grad(prelu_w, dz, y, res, scale, shift):
+    """d loss / d PReLU weight: per-channel sums of dz * v * [v <= 0] (summed over channels for a single slope)."""
+    n, c, h, w = y.shape
+    acc = _zeros64(c, y.device)
+    _lib.check(_lib.load().rtseg_prelu_slope_grad(n * h * w, c, ops._dtype_code(y.dtype), dz.data_ptr(), c, 0, y.data_ptr(), c, 0,
+                                                  ops._ptr(res), c if res is not None else 0, 0, ops._ptr(scale), ops._ptr(shift),
+                                                  acc.data_ptr(), ops._stream()), "rtseg_prelu_slope_grad")
+    if prelu_w.numel() == 1:
+        acc = acc.sum()
+    return acc.reshape(prelu_w.shape).to(prelu_w.dtype)
+
+
 class _BNActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, y, res, gamma, beta, bn, act_module):
+    def forward(ctx, y, res, gamma, beta, prelu_w, bn, act_module):
         y = ops.to_nhwc(y)
         n, c, h, w = y.shape
         if res is not None:
             res = ops.to_nhwc(res)
             if res.shape != y.shape or res.dtype != y.dtype:
                 raise ValueError("residual must match the convolution output")
-        code, p0, p1, prelu_w, post = ops.act_spec(act_module)
-        if post is not None or prelu_w is not None:
-            raise NotImplementedError("training through glu / softmax / prelu blocks is not built")
+        code, p0, p1, _, post = ops.act_spec(act_module)
+        if post is not None:
+            raise NotImplementedError("training through glu / softmax blocks is not built")
+        slope = _slope32(prelu_w, c) if prelu_w is not None else None
         dev = y.device
         lib = _lib.load()
         npix = n * h * w
@@ -185,15 +251,15 @@ class _BNActFn(torch.autograd.Function):
         z = torch.empty_like(y, memory_format=torch.channels_last)
         _lib.check(_lib.load().rtseg_affine_act(n * h * w, c, ops._dtype_code(y.dtype), y.data_ptr(), c, 0, ops._ptr(res),
                                                 c if res is not None else 0, 0, scale.data_ptr(), shift.data_ptr(), code,
-                                                p0, p1, None, z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
-        ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, kk)
+                                                p0, p1, ops._ptr(slope), z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
+        ctx.save_for_backward(y, res, scale, shift, mean32, invstd32, kk, slope, prelu_w)
         ctx.meta = (code, p0, p1, sync, float(npix) if not sync else None, count if sync else None,
                     gamma is not None, beta is not None, gamma.dtype if gamma is not None else torch.float32)
         return z
 
     @staticmethod
     def backward(ctx, dz):
-        y, res, scale, shift, mean, invstd, k = ctx.saved_tensors
+        y, res, scale, shift, mean, invstd, k, slope, prelu_w = ctx.saved_tensors
         code, p0, p1, sync, count_f, count_t, has_g, has_b, pdtype = ctx.meta
         dz = ops.to_nhwc(dz.to(y.dtype))
         n, c, h, w = y.shape
@@ -203,7 +269,8 @@ class _BNActFn(torch.autograd.Function):
         local = torch.zeros(2 * c, dtype=torch.float64, device=y.device)     # [sum g | sum g * xhat]
         _lib.check(lib.rtseg_bn_act_bwd_reduce(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
                                                scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(), code,
-                                               p0, p1, None, local.data_ptr(), local.data_ptr() + 8 * c, st), "rtseg_bn_act_bwd_reduce")
+                                               p0, p1, ops._ptr(slope), local.data_ptr(), local.data_ptr() + 8 * c, st),
+                   "rtseg_bn_act_bwd_reduce")
         glob = local
         if sync:     # the normalisation's own gradient needs the sums over every rank's pixels
             glob = local.clone()
@@ -218,9 +285,12 @@ class _BNActFn(torch.autograd.Function):
         du = torch.empty_like(y, memory_format=torch.channels_last)
         _lib.check(lib.rtseg_bn_act_bwd_apply(n * h * w, c, dt, dz.data_ptr(), c, 0, y.data_ptr(), c, 0, ops._ptr(res), rc, 0,
                                               scale.data_ptr(), shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
-                                              k.data_ptr(), mg.data_ptr(), mgx.data_ptr(), code, p0, p1, None, du.data_ptr(),
-                                              c, 0, st), "rtseg_bn_act_bwd_apply")
-        return du, (du if res is not None else None), dgamma, dbeta, None, None
+                                              k.data_ptr(), mg.data_ptr(), mgx.data_ptr(), code, p0, p1, ops._ptr(slope),
+                                              du.data_ptr(), c, 0, st), "rtseg_bn_act_bwd_apply")
+        dslope = None
+        if prelu_w is not None and ctx.needs_input_grad[4]:
+            dslope = _slope_grad(prelu_w, dz, y, res, scale, shift)
+        return du, (du if res is not None else None), dgamma, dbeta, dslope, None, None
 
 
 class _MaxPoolFn(torch.autograd.Function):
@@ -244,12 +314,99 @@ class _MaxPoolFn(torch.autograd.Function):
         return dx
 
 
+class _ActFn(torch.autograd.Function):
+    """act(x + res) without a BatchNorm in front (reference enet.py:165-181 `self.act(x_left + x_right)`)."""
+
+    @staticmethod
+    def forward(ctx, x, res, prelu_w, act_module):
+        x = ops.to_nhwc(x)
+        n, c, h, w = x.shape
+        if res is not None:
+            res = ops.to_nhwc(res)
+            if res.shape != x.shape or res.dtype != x.dtype:
+                raise ValueError("residual must match the activation input")
+        code, p0, p1, _, post = ops.act_spec(act_module)
+        if post is not None:
+            raise NotImplementedError("training through glu / softmax is not built")
+        slope = _slope32(prelu_w, c) if prelu_w is not None else None
+        z = torch.empty_like(x, memory_format=torch.channels_last)
+        _lib.check(_lib.load().rtseg_affine_act(n * h * w, c, ops._dtype_code(x.dtype), x.data_ptr(), c, 0, ops._ptr(res),
+                                                c if res is not None else 0, 0, None, None, code, p0, p1, ops._ptr(slope),
+                                                z.data_ptr(), c, 0, ops._stream()), "rtseg_affine_act")
+        ctx.save_for_backward(x, res, slope, prelu_w)
+        ctx.meta = (code, p0, p1)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, res, slope, prelu_w = ctx.saved_tensors
+        code, p0, p1 = ctx.meta
+        dz = ops.to_nhwc(dz.to(x.dtype))
+        n, c, h, w = x.shape
+        # du = dz * act'(u): the BatchNorm backward pass with scale 1, shift 0 and no statistics terms
+        one = torch.ones(c, dtype=torch.float32, device=x.device)
+        zero = torch.zeros(c, dtype=torch.float32, device=x.device)
+        du = torch.empty_like(x, memory_format=torch.channels_last)
+        rc = c if res is not None else 0
+        _lib.check(_lib.load().rtseg_bn_act_bwd_apply(n * h * w, c, ops._dtype_code(x.dtype), dz.data_ptr(), c, 0, x.data_ptr(), c,
+                                                      0, ops._ptr(res), rc, 0, one.data_ptr(), zero.data_ptr(), zero.data_ptr(),
+                                                      zero.data_ptr(), one.data_ptr(), zero.data_ptr(), zero.data_ptr(), code,
+                                                      p0, p1, ops._ptr(slope), du.data_ptr(), c, 0, ops._stream()),
+                   "rtseg_bn_act_bwd_apply")
+        dslope = None
+        if prelu_w is not None and ctx.needs_input_grad[2]:
+            dslope = _slope_grad(prelu_w, dz, x, res, None, None)
+        return du, (du if res is not None else None), dslope, None
+
+
+class _BilinearFn(torch.autograd.Function):
+    """F.interpolate(x, size, mode='bilinear', align_corners=...) (reference fastscnn.py:30, 88; modules.py:153-156)."""
+
+    @staticmethod
+    def forward(ctx, x, size, align_corners):
+        x = ops.to_nhwc(x)
+        ctx.meta = (tuple(x.shape), int(size[0]), int(size[1]), bool(align_corners))
+        return ops.upsample_bilinear(x, size, align_corners)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (n, c, hi, wi), ho, wo, align = ctx.meta
+        dy = ops.to_nhwc(dy)
+        dx = ops.empty_nhwc(n, c, hi, wi, dy.dtype, dy.device)
+        _lib.check(_lib.load().rtseg_upsample_bilinear_bwd(n, hi, wi, c, ho, wo, int(align), ops._dtype_code(dy.dtype),
+                                                           dy.data_ptr(), c, 0, dx.data_ptr(), c, 0, ops._stream()),
+                   "rtseg_upsample_bilinear_bwd")
+        return dx, None, None
+
+
+class _AdaptiveAvgPoolFn(torch.autograd.Function):
+    """nn.AdaptiveAvgPool2d(p) (reference models/modules.py:145-149)."""
+
+    @staticmethod
+    def forward(ctx, x, p):
+        x = ops.to_nhwc(x)
+        ctx.meta = (tuple(x.shape), int(p))
+        return ops.adaptive_avgpool(x, int(p))
+
+    @staticmethod
+    def backward(ctx, dy):
+        (n, c, h, w), p = ctx.meta
+        dy = ops.to_nhwc(dy)
+        dx = ops.empty_nhwc(n, c, h, w, dy.dtype, dy.device)
+        _lib.check(_lib.load().rtseg_adaptive_avgpool_bwd(n, h, w, c, p, ops._dtype_code(dy.dtype), dy.data_ptr(), dx.data_ptr(),
+                                                          c, 0, ops._stream()), "rtseg_adaptive_avgpool_bwd")
+        return dx, None
+
+
 # ------------------------------------------------------------------ module-level entry points ----
 def conv(module: nn.Module, x: torch.Tensor) -> torch.Tensor:
     """Training forward of a bare nn.Conv2d / nn.ConvTranspose2d (dense, zero padding)."""
-    if module.groups != 1:
-        raise NotImplementedError("training through depthwise / grouped convolutions is not built (no weight-gradient kernel)")
     transposed = bool(getattr(module, "transposed", False))
+    if module.groups != 1:
+        if transposed or module.groups != module.in_channels or module.out_channels != module.in_channels \
+                or module.stride[0] != module.stride[1] or module.dilation[0] != module.dilation[1]:
+            raise NotImplementedError("training through grouped convolutions other than depthwise (multiplier 1) is not built")
+        return _DWConvFn.apply(x, module.weight, module.bias, module.stride[0], module.dilation[0], tuple(module.padding))
     if transposed and not (tuple(module.kernel_size) == (3, 3) and tuple(module.stride) == (2, 2) and
                            tuple(module.padding) == (1, 1) and tuple(module.output_padding) == (1, 1)):
         raise NotImplementedError("only ConvTranspose2d(k=3, s=2, p=1, output_padding=1) can be trained through")
@@ -260,7 +417,16 @@ def conv(module: nn.Module, x: torch.Tensor) -> torch.Tensor:
 
 def bn_act(bn: nn.Module, act_module: Optional[nn.Module], y: torch.Tensor, res: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Training forward of BatchNorm2d (batch statistics) + activation on y (+ res)."""
-    return _BNActFn.apply(y, res, bn.weight, bn.bias, bn, act_module)
+    return _BNActFn.apply(y, res, bn.weight, bn.bias, _prelu_weight(act_module), bn, act_module)
+
+
+def _prelu_weight(act_module):
+    return act_module.weight if isinstance(act_module, nn.PReLU) else None
+
+
+def act(act_module: Optional[nn.Module], x: torch.Tensor, res: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Training forward of a stand-alone activation on x (+ res)."""
+    return _ActFn.apply(x, res, _prelu_weight(act_module), act_module)
 
 
 def conv_bn_act(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
@@ -270,6 +436,19 @@ def conv_bn_act(seq: nn.Module, x: torch.Tensor) -> torch.Tensor:
 
 def maxpool3x3s2(x: torch.Tensor) -> torch.Tensor:
     return _MaxPoolFn.apply(x)
+
+
+def upsample_bilinear(x: torch.Tensor, size, align_corners: bool) -> torch.Tensor:
+    return _BilinearFn.apply(x, tuple(size), align_corners)
+
+
+def adaptive_avgpool(x: torch.Tensor, p: int) -> torch.Tensor:
+    return _AdaptiveAvgPoolFn.apply(x, p)
+
+
+def taping(*tensors) -> bool:
+    """True when a call with these inputs has to leave autograd nodes behind."""
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
 
 
 class _FirstChannelsFn(torch.autograd.Function):
@@ -342,6 +521,6 @@ def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor, pad_input: bool = False
     b_p = F.pad(conv.bias, (0, pad)) if conv.bias is not None else None
     y = _ConvFn.apply(x, w_p, b_p, conv.stride[0], conv.dilation[0], tuple(conv.padding), transposed)
     pbn = _PaddedBN(bn, pad)
-    z = _BNActFn.apply(y, None, pbn.weight, pbn.bias, pbn, act)
+    z = _BNActFn.apply(y, None, pbn.weight, pbn.bias, _prelu_weight(act), pbn, act)
     pbn.commit()
     return _FirstChannelsFn.apply(z, cout)

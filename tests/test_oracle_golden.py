@@ -163,3 +163,33 @@ def test_sgd_restatement_matches_torch_optim_sgd():
         ref_optim.sgd_step(mine, grads, bufs, 0.08, 0.9, 1e-4)
     for a, b in zip(mine, theirs):
         assert torch.allclose(a, b.detach(), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("name,seed,in_seed,label_seed,hw", [("fastscnn", 13, 14, 15, (128, 256)), ("dabnet", 23, 24, 25, (64, 128))])
+def test_training_restatement_matches_reference_step_of_the_depthwise_nets(name, seed, in_seed, label_seed, hw):
+    """Row T: the oracle's Fast-SCNN / DABNet in TRAINING mode + torch autograd vs the REAL reference's .train() step
+    (tests/golden/train_step_dw.json, written by make_golden_train.py): depthwise convolutions, PReLU slopes,
+    pyramid pooling and the bilinear resizes all carry gradients here."""
+    from oracle import ref_blocks as B
+    with open(os.path.join(GOLDEN, "train_step_dw.json")) as f:
+        gold = json.load(f)[name]
+    sd = ref_nets.make_state(load_specs()[name]["spec"], seed, True)
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.dtype.is_floating_point and "running" not in k}
+    x = ref_nets.make_input(in_seed, 2, *hw)
+    g = torch.Generator().manual_seed(label_seed)
+    labels = torch.randint(0, 19, (2, *hw), generator=g)
+    labels[torch.rand((2, *hw), generator=g) < 0.1] = 255
+    B.TRAINING = True
+    try:
+        logits = ref_nets.FORWARD[name](sd, x)
+    finally:
+        B.TRAINING = False
+    loss = ref_ohem.ohem_ce_loss(logits, labels, 0.7, 255)[0]
+    loss.backward()
+    assert abs(float(loss.detach()) - gold["loss"]) <= 1e-6 * max(1.0, abs(gold["loss"]))
+    assert set(params) == set(gold["grad_norms"])
+    for k, want in gold["grad_norms"].items():
+        got = float(params[k].grad.double().norm())
+        assert abs(got - want) <= 1e-4 * max(want, 1e-3), k
+    for k, want in gold["running_norms"].items():
+        assert abs(float(sd[k].double().norm()) - want) <= 1e-6 * max(want, 1.0), k
