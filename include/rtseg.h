@@ -334,6 +334,20 @@ int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p
                            const void *x, int32_t x_ctotal, int32_t x_coff, int32_t y_dtype, void *y,
                            rtseg_stream_t stream);
 
+/* ---- f1: fused glue of the two-branch nets (config 4) ------------------------------------------
+ * y = act( a (+|*) g(resize(b)) ): `b` ([n][hb][wb], channel slice allowed) is resized to a's (h, w) with
+ * F.interpolate(mode='bilinear', align_corners=True) on the fly (hb = wb = 1: a broadcast), g = sigmoid when
+ * b_sigmoid, op 0 = add / 1 = multiply, act a pointwise rtseg_act (no PReLU).  One pass instead of the reference's
+ * interpolate / sigmoid / mul / add / relu kernels: models/bisenetv2.py:166-170, :190-201; models/ddrnet.py:165,
+ * :238-243, :277-291.  y may alias a. */
+int rtseg_combine_up(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *a, int32_t a_ctotal,
+                     int32_t a_coff, const void *b, int32_t hb, int32_t wb, int32_t b_ctotal, int32_t b_coff, int32_t op,
+                     int32_t b_sigmoid, int32_t act, float act_p0, float act_p1, void *y, int32_t y_ctotal, int32_t y_coff,
+                     rtseg_stream_t stream);
+/* nn.AvgPool2d(k, s, p), count_include_pad=True, floor mode (models/ddrnet.py:266-275, models/bisenetv2.py:182). */
+int rtseg_avgpool2d(int32_t n, int32_t h, int32_t w, int32_t c, int32_t k, int32_t s, int32_t p, int32_t dtype, const void *x,
+                    int32_t x_ctotal, int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream);
+
 /* ---- training-mode pieces ---------------------------------------------
  * In training the reference's ConvBNAct is Conv2d -> BatchNorm2d(batch statistics) -> activation
  * as three autograd nodes (models/modules.py:73-85); NonBt1DBlock adds `+= x` before the last

@@ -104,6 +104,9 @@ PROTOTYPES = {
                                        c_vp, c_vp]),
     "rtseg_upsample_bilinear_bwd": (c_i32, [c_i32] * 8 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_adaptive_avgpool_bwd": (c_i32, [c_i32] * 6 + [c_vp, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_combine_up": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_f32,
+                                 c_f32, c_vp, c_i32, c_i32, c_vp]),
+    "rtseg_avgpool2d": (c_i32, [c_i32] * 8 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
     "rtseg_opt_chunk_elems": (c_i32, []),
     "rtseg_sgd_ema_step": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp]),
     "rtseg_maxpool3x3s2_bwd": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),

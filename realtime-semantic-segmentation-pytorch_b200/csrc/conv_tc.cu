@@ -1358,6 +1358,23 @@ static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slop
   return RTSEG_OK;
 }
 
+// A vertically dilated k x 1 convolution (same padding, stride 1) with dilation d = f * d' is the SAME convolution
+// with dilation d' on the same memory read as h / f rows of f * w pixels: row r of that view is the real rows
+// r*f .. r*f + f-1 side by side, so the real row y +- d is the view row r +- d' at the same column, and the zero rows
+// above / below the image stay where they are.  The vertical halo of a 16-row tile then costs 2 d' view rows instead
+// of 2 d real rows (ERFNet's 3x1 d = 4 / 8 / 16 layers, reference models/erfnet.py:69).  Input, output and residual
+// share the geometry, so all three are reinterpreted.  f = the largest divisor of d that leaves >= 16 view rows.
+static void fold_vertical_dilation(rtseg_conv_desc &d) {
+  static const int knob = getenv("RTSEG_TC_FOLD_DIL") ? atoi(getenv("RTSEG_TC_FOLD_DIL")) : 1;
+  if (!knob || d.kw != 1 || d.kh < 2 || d.dil < 2 || d.stride != 1) return;
+  if (d.pad_w != 0 || d.pad_h != d.dil * (d.kh - 1) / 2) return;
+  int f = 1;
+  for (int c = 2; c <= d.dil; ++c)
+    if (d.dil % c == 0 && d.h % c == 0 && d.h / c >= 16 && (int64_t)d.w * c <= (1 << 24)) f = c;
+  if (f == 1) return;
+  d.h /= f, d.w *= f, d.dil /= f, d.pad_h = d.dil * (d.kh - 1) / 2;
+}
+
 // Test / diagnostics hook: the execution plan rtseg_conv_tc would use for `d` with a 16-byte-aligned output.
 // info = {kb, bn, n_tiles, ms, stages, out_bufs, share, units, grid_x, smem_bytes, tmem_cols, res_boxes}.
 extern "C" int rtseg_conv_tc_plan_info(const rtseg_conv_desc *d, int32_t info[12]) {
@@ -1366,6 +1383,7 @@ extern "C" int rtseg_conv_tc_plan_info(const rtseg_conv_desc *d, int32_t info[12
   if (check_tc_common(d, false, &why)) RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: %s", why);
   rtseg_conv_desc padded = *d;
   padded.cin = (d->cin + 15) / 16 * 16;
+  fold_vertical_dilation(padded);
   TcPlan pl;
   TcParams p;
   int share = 0, mode = 0;
@@ -1393,6 +1411,7 @@ extern "C" int rtseg_conv_tc(const rtseg_conv_desc *d, const void *x, const void
   const int cin_real = d->cin;
   rtseg_conv_desc padded = *d;
   padded.cin = (d->cin + 15) / 16 * 16;
+  fold_vertical_dilation(padded);
   d = &padded;
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const int ntaps = d->kh * d->kw;

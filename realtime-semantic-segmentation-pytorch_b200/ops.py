@@ -717,6 +717,48 @@ def avgpool3x3s2(x: torch.Tensor, out_dtype: Optional[torch.dtype] = None, out: 
     return out
 
 
+def combine_up(a: torch.Tensor, b: torch.Tensor, op: str = "add", b_sigmoid: bool = False, act_module=None,
+               out: Optional[torch.Tensor] = None, y_coff: int = 0, a_coff: int = 0, b_coff: int = 0,
+               c: Optional[int] = None) -> torch.Tensor:
+    """act(a (+|*) g(resize(b))) in one pass: `b` is bilinearly resized (align_corners=True) to a's size on the fly
+    ([n, c, 1, 1]: a broadcast), g = sigmoid when b_sigmoid.  The glue between the convolutions of BiSeNetv2's
+    aggregation layer and DDRNet's bilateral fusion / DAPPM (reference models/bisenetv2.py:166-201,
+    models/ddrnet.py:165, 238-243, 277-291)."""
+    _require_cuda(a, "combine_up")
+    _no_tape(a, "combine_up")
+    _no_tape(b, "combine_up")
+    if not is_nhwc(a) or not is_nhwc(b) or a.dtype != b.dtype or a.shape[0] != b.shape[0]:
+        raise ValueError("combine_up expects two NHWC tensors of one dtype and batch size")
+    n, a_ct, h, w = a.shape
+    c = c if c is not None else a_ct - a_coff
+    code, p0, p1, prelu_w, post = act_spec(act_module)
+    if prelu_w is not None or post is not None:
+        raise NotImplementedError("combine_up: pointwise activations without parameters only")
+    if out is None:
+        out = empty_nhwc(n, c, h, w, a.dtype, a.device)
+    elif not is_nhwc(out) or out.dtype != a.dtype or tuple(out.shape[2:]) != (h, w) or out.shape[0] != n:
+        raise ValueError("bad output buffer")
+    _lib.check(_lib.load().rtseg_combine_up(n, h, w, c, _dtype_code(a.dtype), a.data_ptr(), a_ct, a_coff, b.data_ptr(),
+                                            b.shape[2], b.shape[3], b.shape[1], b_coff, {"add": 0, "mul": 1}[op],
+                                            int(bool(b_sigmoid)), code, p0, p1, out.data_ptr(), out.shape[1], y_coff,
+                                            _stream()), "rtseg_combine_up")
+    return out
+
+
+def avgpool2d(x: torch.Tensor, k: int, s: int, p: int, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
+    """nn.AvgPool2d(k, s, p) (count_include_pad=True) on an NHWC tensor — reference models/ddrnet.py:266-275."""
+    _require_cuda(x, "avgpool2d")
+    _no_tape(x, "avgpool2d")
+    if not is_nhwc(x):
+        raise ValueError("avgpool2d expects an NHWC tensor")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct - x_coff
+    out = empty_nhwc(n, c, (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1, x.dtype, x.device)
+    _lib.check(_lib.load().rtseg_avgpool2d(n, h, w, c, k, s, p, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                           out.data_ptr(), c, 0, _stream()), "rtseg_avgpool2d")
+    return out
+
+
 def copy_into_slice(x: torch.Tensor, out: torch.Tensor, y_coff: int = 0, x_coff: int = 0, c: Optional[int] = None) -> torch.Tensor:
     """out[:, y_coff : y_coff + c] = x[:, x_coff : x_coff + c] for NHWC buffers: the permutation kernel with one group
     (the identity permutation) — how a concat's pass-through operand reaches its slice without an ATen copy."""

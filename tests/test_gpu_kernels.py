@@ -561,9 +561,12 @@ def test_raw_ops_refuse_tensors_on_the_autograd_tape():
                lambda: ops.channel_shuffle(x, 2), lambda: ops.avgpool3x3s2(x)):
         with pytest.raises(NotImplementedError, match="no backward"):
             fn()
-    ppm = modules.PyramidPoolingModule(8, 8, "relu").cuda()       # training mode
+    ppm = modules.PyramidPoolingModule(8, 8, "relu").cuda()       # training mode: tape nodes with adjoint kernels (row T)
+    out = ppm(x)
+    out.sum().backward()
+    assert x.grad is not None and all(p.grad is not None for p in ppm.parameters())
     with pytest.raises(NotImplementedError, match="PyramidPoolingModule"):
-        ppm(x.detach())
+        ppm.eval()(x)                                              # eval-mode BatchNorm with a taped input: refused
     with torch.no_grad():
         assert ppm.eval()(x).shape == (1, 8, 8, 8)
 

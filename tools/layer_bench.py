@@ -54,7 +54,7 @@ def report(name, ms, nbytes, flops=0.0):
 
 
 def erfnet_layers(batch, only, reps):
-    cfgs = [("c64", 64, 256, 512, [1]), ("c128", 128, 128, 256, [1, 2, 16]), ("c16", 16, 512, 1024, [1])]
+    cfgs = [("c64", 64, 256, 512, [1]), ("c128", 128, 128, 256, [1, 2, 4, 8, 16]), ("c16", 16, 512, 1024, [1])]
     for tag, c, h, w, dils in cfgs:
         x, r = nhwc_rand((batch, c, h, w)), nhwc_rand((batch, c, h, w))
         elems = batch * c * h * w
