@@ -226,8 +226,10 @@ def enet_forward(sd, x, act_type="prelu"):
     return B.q(F.interpolate(x, scale_factor=2, mode="bilinear"))
 
 
+from .ref_nets_dual import bisenetv2_forward, ddrnet_forward  # noqa: E402  (the two-branch nets of config 4)
+
 FORWARD = {"erfnet": erfnet_forward, "fastscnn": fastscnn_forward, "dabnet": dabnet_forward, "lednet": lednet_forward,
-           "enet": enet_forward}
+           "enet": enet_forward, "bisenetv2": bisenetv2_forward, "ddrnet": ddrnet_forward}
 
 
 # --------------------------------------------------------------------- seeded weights ----

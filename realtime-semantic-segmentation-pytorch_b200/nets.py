@@ -818,7 +818,11 @@ class ENet(nn.Module):
                                    ignore_index=ignore_index)
 
 
-MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet, "enet": ENet}
+from .nets_dual import BiSeNetv2, DDRNet  # noqa: E402  (config 4; they use this module's leaf blocks only via modules.py)
+
+MODEL_HUB = {"erfnet": ERFNet, "fastscnn": FastSCNN, "dabnet": DABNet, "lednet": LEDNet, "enet": ENet,
+             "bisenetv2": BiSeNetv2, "ddrnet": DDRNet}
+AUX_MODELS = ("bisenetv2", "ddrnet")   # reference models/__init__.py:13-14
 
 
 def get_model(config) -> nn.Module:
@@ -826,13 +830,15 @@ def get_model(config) -> nn.Module:
     name = config.model
     if name not in MODEL_HUB:
         raise NotImplementedError(f"Unsupport model type: {name}")
-    if getattr(config, "use_aux", False):
-        raise ValueError(f"Model {name} does not support auxiliary heads.\n")
     if getattr(config, "use_detail_head", False):
         raise ValueError(f"Model {name} does not support detail heads.\n")
+    if name in AUX_MODELS:
+        return MODEL_HUB[name](num_class=config.num_class, use_aux=bool(getattr(config, "use_aux", False)))
+    if getattr(config, "use_aux", False):
+        raise ValueError(f"Model {name} does not support auxiliary heads.\n")
     return MODEL_HUB[name](num_class=config.num_class)
 
 
-__all__ = ["ERFNet", "FastSCNN", "DABNet", "LEDNet", "ENet", "Bottleneck", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "DABModule",
+__all__ = ["ERFNet", "FastSCNN", "DABNet", "LEDNet", "ENet", "BiSeNetv2", "DDRNet", "Bottleneck", "InitialBlock", "NonBt1DBlock", "InvertedResidual", "DABModule",
            "SSnbtUnit", "get_model", "MODEL_HUB"]
 _ = (_bn_tensors, _FoldCache)

@@ -23,7 +23,8 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .modules import Activation, ConvBNAct, DWConvBNAct, PWConvBNAct, SegHead, _check_eval, conv1x1, conv3x3
+from .modules import (Activation, ConvBNAct, DWConvBNAct, PWConvBNAct, SegHead, _bn_tensors, _check_eval, _FoldCache, conv1x1,
+                      conv3x3)
 
 
 def _param_dtype(m: nn.Module) -> torch.dtype:
@@ -142,9 +143,11 @@ class ContextEmbeddingBlock(nn.Module):
         x = ops.to_nhwc(x)
         bn = self.pool[1]
         _check_eval(self, bn)
+        cache = self.__dict__.setdefault("_rtseg_cache", _FoldCache())
+        scale, shift = cache.get(_bn_tensors(bn), lambda: tuple(t.float().view(1, -1, 1, 1) for t in
+                                                                ops.fold_affine(x.shape[1], None, bn)))
         pooled = ops.adaptive_avgpool(x, 1, out_dtype=torch.float32)          # [n, c, 1, 1] fp32
-        scale, shift = ops.fold_affine(x.shape[1], None, bn)                    # eval BatchNorm on a 1x1 map: tiny
-        pooled = (pooled.double() * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)).to(x.dtype)
+        pooled = torch.addcmul(shift, pooled, scale).to(x.dtype)                # eval BatchNorm on a 1x1 map: n * c values
         res = self.conv_mid(pooled.contiguous(memory_format=torch.channels_last))
         return self.conv_last(ops.combine_up(x, res, "add"))                     # res + x: a broadcast add
 

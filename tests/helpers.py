@@ -25,6 +25,7 @@ def load_specs():
 def load_net_outputs():
     out = dict(np.load(os.path.join(GOLDEN, "net_outputs.npz")))
     out.update(dict(np.load(os.path.join(GOLDEN, "enet_outputs.npz"))))   # tests/golden/make_golden_enet.py
+    out.update(dict(np.load(os.path.join(GOLDEN, "cfg4_outputs.npz"))))   # tests/golden/make_golden_cfg4.py (64 x 128 input)
     return out
 
 

@@ -193,3 +193,18 @@ def test_training_restatement_matches_reference_step_of_the_depthwise_nets(name,
         assert abs(got - want) <= 1e-4 * max(want, 1e-3), k
     for k, want in gold["running_norms"].items():
         assert abs(float(sd[k].double().norm()) - want) <= 1e-6 * max(want, 1.0), k
+
+
+@pytest.mark.parametrize("name", ["bisenetv2", "ddrnet"])
+@pytest.mark.parametrize("tag,perturb", [("perturbed", True), ("identity_bn", False)])
+def test_config4_restatement_matches_reference_vectors(name, tag, perturb):
+    """oracle/ref_nets_dual.py vs the REAL reference's BiSeNetv2 / DDRNet logits (tests/golden/cfg4_outputs.npz)."""
+    specs, golden = load_specs(), load_net_outputs()
+    sd = ref_nets.make_state(specs[name]["spec"], seed=1, perturb_bn=perturb)
+    x = ref_nets.make_input(0, 1, 64, 128)
+    with torch.no_grad():
+        y = ref_nets.FORWARD[name](sd, x)
+    ref = torch.from_numpy(golden[f"{name}.{tag}"])
+    assert y.shape == ref.shape
+    assert rel_err(y, ref) < 1e-5
+    assert (y.argmax(1) == ref.argmax(1)).float().mean().item() >= 0.9999
