@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — images/s at 1024x2048 on N B200s (BASELINE.json metric), one JSON line on rank 0.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet|enet|erfnet_train] [--batch B]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload erfnet|fastscnn|dabnet|lednet|enet|bisenetv2|ddrnet|head_miou|erfnet_train] [--batch B]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
   python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
 
@@ -28,7 +28,10 @@ sys.path.insert(0, ROOT)
 H, W, NUM_CLASS = 1024, 2048, 19
 # ENet is BASELINE configs[0]: the reference's own speed protocol (tools/test_speed.py: ratio 0.5 -> 512 x 1024)
 WORKLOAD_HW = {"enet": (512, 1024)}
-DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16, "enet": 16, "erfnet_train": 8, "head_miou": 16}
+DEFAULT_BATCH = {"erfnet": 16, "fastscnn": 32, "dabnet": 16, "lednet": 16, "enet": 16, "erfnet_train": 8, "head_miou": 16,
+                 "bisenetv2": 16, "ddrnet": 16}
+# BASELINE configs[3] (mIoU evaluation): model -> fused head + confusion matrix -> int64 all-reduce -> IoU
+EVAL_WORKLOADS = ("bisenetv2", "ddrnet")
 
 
 def hw_of(workload):
@@ -39,11 +42,16 @@ WORKLOAD_NAME = {
     "dabnet": "DABNet inference batch {b} at 1024x2048 (SURVEY §8 a10)",
     "lednet": "LEDNet inference batch {b} at 1024x2048 (SURVEY §8 a11)",
     "enet": "ENet inference batch {b} at 512x1024 (BASELINE configs[0]: tools/test_speed.py size; CPU arm = that protocol)",
+    "bisenetv2": "BiSeNetv2 mIoU evaluation, batch {b} per GPU at 1024x2048 (BASELINE configs[3]): model -> fused x8 bilinear + argmax "
+                 "+ confusion matrix against int64 masks -> one int64 all-reduce -> IoU",
+    "ddrnet": "DDRNet-23-slim mIoU evaluation, batch {b} per GPU at 1024x2048 (BASELINE configs[3]): model -> fused x8 bilinear + "
+              "argmax + confusion matrix against int64 masks -> one int64 all-reduce -> IoU",
     "head_miou": "segmentation head + mIoU of BASELINE configs[3] (BiSeNetv2 / DDRNet-23-slim output geometry: 19 x 128 x 256 "
                  "logits per 1024x2048 image), batch {b} per GPU: fused x8 bilinear + argmax + confusion matrix, int64 all-reduce, IoU",
     "erfnet_train": "ERFNet training step (fwd + OHEM + bwd + SGD), batch {b} per GPU at 1024x1024 (SURVEY §8d config 5)",
 }
 NET_LABEL = {"erfnet": "ERFNet", "fastscnn": "Fast-SCNN", "dabnet": "DABNet", "lednet": "LEDNet", "enet": "ENet", "head_miou": "head + mIoU",
+             "bisenetv2": "BiSeNetv2 + mIoU", "ddrnet": "DDRNet-23-slim + mIoU",
              "erfnet_train": "ERFNet train step"}
 
 
@@ -282,7 +290,7 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
                                              "achieved_gbs": round(v[1] / (v[0] * 1e-3) / 1e9, 1) if v[0] else None,
                                              "frac": round(v[1] / (v[0] * 1e-3) / 1e9 / peak_gbs, 4) if v[0] else None}
                     for k, v in fam.items()}
-    elif workload in ("dabnet", "lednet", "enet"):
+    elif workload in ("dabnet", "lednet", "enet", "bisenetv2", "ddrnet"):
         # every fused conv layer is captured with the tensors / keyword arguments the net really passes, timed
         # alone, and binned by kernel family; the family with the largest share of the time is reported
         from rtseg_b200.modules import Conv2d, _FusedConvMixin
@@ -369,7 +377,7 @@ def dominant_kernel_roofline(model, workload: str, batch: int, peak_gbs: float, 
 PARITY_MIN_AGREE = 0.985  # bf16 class map vs the fp32 oracle on the benchmark's own weights (default init)
 # ENet (no normalisation behind its residual adds): bf16 storage alone moves ~4 % of a random-init class map; the
 # parity tests hold its bf16 path to the storage-emulating oracle instead (tests/test_gpu_enet.py)
-PARITY_MIN_BY_WORKLOAD = {"enet": 0.93}
+PARITY_MIN_BY_WORKLOAD = {"enet": 0.93, "bisenetv2": 0.93}   # (BiSeNetv2: a sigmoid gate on un-normalised features)
 
 
 def parity_check(model, eng, workload: str):
@@ -835,8 +843,11 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     model.set_act_dtype(torch.bfloat16)
     u8 = args.input == "u8"
     H, W = hw_of(workload)
+    evaluate = workload in EVAL_WORKLOADS
+    met = rtseg_b200.SegMetrics(NUM_CLASS, 255).to("cuda") if evaluate else None
     eng = rtseg_b200.InferenceEngine(model, batch=batch, height=H, width=W, use_graph=True, slots=2,
-                                     in_dtype=torch.uint8 if u8 else torch.float32)
+                                     in_dtype=torch.uint8 if u8 else torch.float32,
+                                     confmat=met.confmat if evaluate else None)
 
     # synthetic inputs: per-rank seeds, resident on the device for `value`, pinned on the host for `e2e`
     g = torch.Generator(device="cuda").manual_seed(rank)
@@ -849,6 +860,12 @@ def run_inference(workload, batch, args, rank, local_rank, world):
         host_in = [torch.randint(0, 256, (batch, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
     else:
         host_in = [torch.randn(eng.slots[0].x.shape).pin_memory() for _ in range(2)]
+    host_masks = [None, None]
+    if evaluate:    # int64 masks as the reference's dataset yields them, 10 % ignored pixels
+        for s in eng.slots:
+            s.target.copy_(torch.randint(0, NUM_CLASS, s.target.shape, generator=g, device="cuda"))
+            s.target[torch.rand(s.target.shape, generator=g, device="cuda") < 0.1] = 255
+        host_masks = [eng.slots[i].target.cpu().pin_memory() for i in range(2)]
 
     def barrier():
         if world > 1:
@@ -859,6 +876,10 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     stream = eng.slots[0].stream
     for _ in range(max(3, args.warmup)):
         eng.run_device(0)
+    if evaluate:
+        with torch.cuda.stream(stream):
+            met.compute()      # warms the all-reduce up
+            met.reset()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -866,6 +887,9 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     e0.record(stream)
     for _ in range(args.steps):
         eng.run_device(0)
+    if evaluate:               # once per evaluation, inside the timed region: all-reduce of the int64 matrix + IoU
+        with torch.cuda.stream(stream):
+            iou = met.compute()
     e1.record(stream)
     barrier()
     dev_ms = e0.elapsed_time(e1)
@@ -879,17 +903,39 @@ def run_inference(workload, batch, args, rank, local_rank, world):
 
     # ---- end to end through the public API (pinned host in, host class map out) --------------------
     _PHASE[0] = f"{workload}: end to end (pinned host in, host class map out)"
+    eval_check = None
+    if evaluate:
+        # the matrix the timed steps accumulated: K passes over slot 0's batch = K x the matrix of one pass, and that
+        # one is bit-exact against the restated torchmetrics matrix of the engine's own class map (oracle/ref_head.py)
+        import numpy as np
+        from oracle import ref_head
+        total = met.confmat.clone()
+        met.reset()
+        lab = eng.run_device(0)
+        torch.cuda.synchronize()
+        one = met.confmat.cpu().numpy()
+        want = ref_head.confusion_matrix(lab.cpu().numpy(), eng.slots[0].target.cpu().numpy(), NUM_CLASS, 255)
+        eval_check = {"confmat_exact_from_kernel_labels": bool(np.array_equal(one, want)),
+                      "timed_matrix_is_steps_x_one_pass": bool(torch.equal(total.cpu(), torch.from_numpy(one) * args.steps)),
+                      "pixels_counted_per_pass": int(one.sum()), "miou": round(float(iou.mean().item()), 6)}
+        if not (eval_check["confmat_exact_from_kernel_labels"] and eval_check["timed_matrix_is_steps_x_one_pass"]):
+            raise SystemExit(f"bench.py: confusion-matrix check failed: {json.dumps(eval_check)}")
+        met.reset()
     for i in range(2):
-        eng(host_in[i])
+        eng(host_in[i], host_masks[i])
+    if evaluate:
+        met.reset()
     barrier()
     t0 = time.perf_counter()
     pending = []
     for i in range(args.steps):
-        pending.append(eng.submit(host_in[i % 2]))
+        pending.append(eng.submit(host_in[i % 2], host_masks[i % 2]))
         if len(pending) == 2:
             eng.collect(pending.pop(0))
     while pending:
         eng.collect(pending.pop(0))
+    if evaluate:
+        eval_check["miou_e2e"] = round(float(met.compute().mean().item()), 6)      # all-reduce + IoU + read-back
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
@@ -939,6 +985,12 @@ def run_inference(workload, batch, args, rank, local_rank, world):
             "cpu_baseline": cpu,
             "parity_check": parity,
         }
+        if evaluate:
+            line["parity_check"].update(eval_check)
+            line["config"]["masks"] = "int64 [N, H, W], randint(0, 19) with 10 % set to 255 (ignored), copied in with the images"
+            line["config"]["collective"] = ("one all-reduce of the 19 x 19 int64 confusion matrix per evaluation (NCCL), inside the "
+                                            "timed region" if world > 1 else "none (one rank)")
+            line["config"]["output"] = "uint8 class map + int64 confusion matrix -> IoU"
     del eng, model
     torch.cuda.empty_cache()
     return line

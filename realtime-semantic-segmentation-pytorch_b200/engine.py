@@ -9,6 +9,10 @@ The model's forward is a fixed sequence of librtseg launches with static shapes,
 captured once into a CUDA graph (no per-launch host overhead, no tracing compiler) and replayed.
 Host I/O uses pinned staging buffers and two copy/compute slots so that the H2D copy of
 batch i+1 overlaps the kernels of batch i (`submit` / `collect`).
+
+    eng = InferenceEngine(model, ..., confmat=metrics.confmat)        # evaluation (reference core/seg_trainer.py:118-136):
+    eng(host_images, host_masks)                                      # the fused head also adds each batch to the int64
+    iou = metrics.compute()                                           # confusion matrix; compute() all-reduces it once
 """
 from __future__ import annotations
 
@@ -28,6 +32,8 @@ class _Slot:
         else:
             self.x = torch.empty((eng.batch, eng.in_channels, eng.height, eng.width), dtype=eng.in_dtype, device=dev)
         self.labels = torch.empty((eng.batch, eng.height, eng.width), dtype=torch.uint8, device=dev)
+        self.target = (torch.full((eng.batch, eng.height, eng.width), eng.ignore_index, dtype=torch.int64, device=dev)
+                       if eng.confmat is not None else None)
         self.host_out = torch.empty((eng.batch, eng.height, eng.width), dtype=torch.uint8, pin_memory=True)
         self.stream = torch.cuda.Stream(device=dev)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
@@ -38,7 +44,7 @@ class _Slot:
 class InferenceEngine:
     def __init__(self, model: torch.nn.Module, batch: int, height: int, width: int, in_channels: int = 3,
                  in_dtype: torch.dtype = torch.float32, device: Optional[torch.device] = None, use_graph: bool = True,
-                 slots: int = 2):
+                 slots: int = 2, confmat: Optional[torch.Tensor] = None, ignore_index: int = 255):
         if not hasattr(model, "predict"):
             raise TypeError("InferenceEngine needs a model with predict(x, labels=...) (rtseg_b200.nets)")
         if model.training:
@@ -50,6 +56,8 @@ class InferenceEngine:
         self.batch, self.height, self.width, self.in_channels = batch, height, width, in_channels
         self.in_dtype = in_dtype
         self.use_graph = use_graph
+        # evaluation: an int64 [C, C] device matrix the fused head adds every batch to (masks come in with the images)
+        self.confmat, self.ignore_index = confmat, ignore_index
         _lib.load()
         with torch.cuda.device(self.device):
             self.slots: List[_Slot] = [_Slot(self) for _ in range(slots)]
@@ -59,7 +67,8 @@ class InferenceEngine:
 
     # -- one slot = static input + static output + captured graph ------------------
     def _run_model(self, s: _Slot):
-        out = self.model.predict(s.x)
+        out = (self.model.predict(s.x) if self.confmat is None else
+               self.model.predict(s.x, target=s.target, confmat=self.confmat, ignore_index=self.ignore_index))
         if out.data_ptr() != s.labels.data_ptr():
             s.labels = out  # keep the tensor the graph writes
 
@@ -67,7 +76,7 @@ class InferenceEngine:
         with torch.no_grad(), torch.cuda.stream(s.stream):
             s.x.zero_()
             before = _lib.launch_count()
-            self._run_model(s)  # warm-up: builds fold caches, sets func attributes
+            self._run_model(s)  # warm-up: builds fold caches, sets func attributes (targets are all `ignore`: nothing counted)
             s.launches = _lib.launch_count() - before
             s.stream.synchronize()
             if self.use_graph:
@@ -94,8 +103,10 @@ class InferenceEngine:
         return s.labels
 
     # -- host path --------------------------------------------------------------------------
-    def submit(self, host_images: torch.Tensor) -> int:
+    def submit(self, host_images: torch.Tensor, host_masks: Optional[torch.Tensor] = None) -> int:
         """Enqueue H2D copy + forward + D2H copy for one batch; returns the slot index."""
+        if (host_masks is not None) != (self.confmat is not None):
+            raise ValueError("masks are passed exactly when the engine was built with a confusion matrix")
         if self.in_dtype == torch.uint8 and host_images.dim() == 4 and host_images.dtype == torch.uint8:
             from . import ops
             host_images = ops.as_image_u8(host_images)   # [N, H, W, C] bytes -> NCHW-logical view, no copy
@@ -106,6 +117,8 @@ class InferenceEngine:
         s = self.slots[i]
         with torch.no_grad(), torch.cuda.stream(s.stream):
             s.x.copy_(host_images, non_blocking=True)
+            if host_masks is not None:
+                s.target.copy_(host_masks, non_blocking=True)
             if s.graph is not None:
                 s.graph.replay()
             else:
@@ -120,11 +133,12 @@ class InferenceEngine:
         s.done.synchronize()
         return s.host_out
 
-    def __call__(self, host_images: torch.Tensor) -> torch.Tensor:
-        return self.collect(self.submit(host_images))
+    def __call__(self, host_images: torch.Tensor, host_masks: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self.collect(self.submit(host_images, host_masks))
 
     def h2d_bytes(self) -> int:
-        return self.slots[0].x.numel() * self.slots[0].x.element_size()
+        s = self.slots[0]
+        return s.x.numel() * s.x.element_size() + (s.target.numel() * 8 if s.target is not None else 0)
 
     def d2h_bytes(self) -> int:
         return self.slots[0].host_out.numel()

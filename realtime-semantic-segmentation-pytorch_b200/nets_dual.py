@@ -42,6 +42,32 @@ def _image_stem(block: ConvBNAct, x: torch.Tensor, act_dtype: Optional[torch.dty
         if post is not None:
             raise NotImplementedError("non-pointwise activation in the stem")
         return ops.stem(folded, x, pool=False, out_dtype=dtype)
+    if conv.in_channels <= 4 and conv.out_channels <= 64 and conv.out_channels % 16 == 0 \
+            and tuple(conv.kernel_size) == (3, 3) and tuple(conv.stride) == (2, 2):
+        # BiSeNetv2's 3 -> 64 detail stem (models/bisenetv2.py:47): two 32-output stem launches, each writing its
+        # channel slice — the image (uint8 or fp32) is read by the stem kernel itself, never normalised into a copy
+        import dataclasses
+        _check_eval(block, block[1])
+        folded, post = block._folded()
+        if post is not None:
+            raise NotImplementedError("non-pointwise activation in the stem")
+        halves = block.__dict__.get("_rtseg_stem_halves")
+        if halves is None or halves[0] is not folded:
+            def cut(t, lo, hi):
+                return None if t is None else t[lo:hi].contiguous()
+            parts = []
+            for lo in range(0, folded.cout, 32):
+                hi = min(lo + 32, folded.cout)
+                parts.append((lo, dataclasses.replace(folded, cout=hi - lo, w_f32=folded.w_f32[..., lo:hi].contiguous(), w_tc=None,
+                                                      scale=cut(folded.scale, lo, hi), shift=cut(folded.shift, lo, hi),
+                                                      slope=cut(folded.slope, lo, hi), w_tc_scaled=None)))
+            halves = (folded, parts)
+            block.__dict__["_rtseg_stem_halves"] = halves
+        n, _, h, w = x.shape
+        out = ops.empty_nhwc(n, folded.cout, (h - 1) // 2 + 1, (w - 1) // 2 + 1, dtype, x.device)
+        for lo, part in halves[1]:
+            ops.stem(part, x, pool=False, out_dtype=dtype, out=out, y_coff=lo)
+        return out
     if x.dtype == torch.uint8:
         return block(ops.normalize_u8(x, dtype))
     return block(ops.to_nhwc(x, dtype))
