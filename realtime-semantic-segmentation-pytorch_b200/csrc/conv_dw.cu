@@ -273,6 +273,65 @@ __global__ void __launch_bounds__(256) dw_vec_kernel(DwParams p, const T *__rest
   }
 }
 
+// ---- channel multiplier m >= 2 (BiSeNetv2's x6 depthwise expansion, reference models/bisenetv2.py:139-149) ------
+// One thread = one output pixel x one 16-byte vector of OUTPUT channels.  Output channel co reads input channel
+// co / m, and the host only takes this kernel when every vector's V outputs come from at most two neighbouring
+// input channels (m = 6, V = 8: always), so a tap costs two scalar input loads (L1 hits: neighbouring threads share
+// them), two float4 weight loads and V FMAs.  The layer is bound by its output: 1/m of the bytes are reads.
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) dw_mult_kernel(DwParams p, const T *__restrict__ x, const float *__restrict__ wgt,
+                                                      Epilogue ep, const T *__restrict__ res, T *__restrict__ y) {
+  constexpr int V = Vec16<T>::N;
+  const int cvecs = p.cout / V;
+  const int64_t total = (int64_t)p.n * p.ho * p.wo * cvecs;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cvecs) * V;
+  int64_t r = tid / cvecs;
+  const int wo = (int)(r % p.wo);
+  r /= p.wo;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int ci0 = c0 / p.mult;
+  const int phase = c0 - ci0 * p.mult;          // outputs with phase + e >= mult read input channel ci0 + 1
+  const bool two = phase + V - 1 >= p.mult;
+  float acc[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) acc[v] = 0.f;
+  const T *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + ci0;
+  for (int ky = 0; ky < p.kh; ++ky) {
+    const int hi = ho * p.stride - p.pad_h + ky * p.dil;
+    if (hi < 0 || hi >= p.h) continue;
+    for (int kx = 0; kx < p.kw; ++kx) {
+      const int wi = wo * p.stride - p.pad_w + kx * p.dil;
+      if (wi < 0 || wi >= p.w) continue;
+      const T *xp = xn + ((int64_t)hi * p.w + wi) * p.x_ct;
+      const float x0 = ld_f<T>(xp), x1 = two ? ld_f<T>(xp + 1) : 0.f;
+      const float *wp = wgt + (int64_t)(ky * p.kw + kx) * p.cout + c0;
+#pragma unroll
+      for (int v = 0; v < V; v += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(wp + v));
+        acc[v] = fmaf(phase + v >= p.mult ? x1 : x0, t.x, acc[v]);
+        acc[v + 1] = fmaf(phase + v + 1 >= p.mult ? x1 : x0, t.y, acc[v + 1]);
+        acc[v + 2] = fmaf(phase + v + 2 >= p.mult ? x1 : x0, t.z, acc[v + 2]);
+        acc[v + 3] = fmaf(phase + v + 3 >= p.mult ? x1 : x0, t.w, acc[v + 3]);
+      }
+    }
+  }
+  const int64_t pix = ((int64_t)n * p.ho + ho) * p.wo + wo;
+  float sc[V], sh[V], sl[V], rv[V], ov[V];
+  load_affine<V>(ep, c0, sc, sh, sl);
+  if (ep.res_mode != RTSEG_RES_NONE) {
+    Vec16<T>::load(res + pix * p.r_ct + p.r_co + c0, rv);
+  } else {
+#pragma unroll
+    for (int v = 0; v < V; ++v) rv[v] = 0.f;
+  }
+#pragma unroll
+  for (int v = 0; v < V; ++v) ov[v] = epi_elem<MODE>(acc[v], rv[v], sc[v], sh[v], sl[v], ep);
+  Vec16<T>::store(y + pix * p.y_ct + p.y_co + c0, ov);
+}
+
 // ---- scalar fallback: channel multiplier, odd channel counts, unaligned slices ---
 template <typename T>
 __global__ void __launch_bounds__(256) dw_scalar_kernel(DwParams p, const T *__restrict__ x,
@@ -326,6 +385,19 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
                       d->y_ctotal % V == 0 && d->y_coff % V == 0 &&
                       (d->res_mode == RTSEG_RES_NONE || (d->r_ctotal % V == 0 && d->r_coff % V == 0));
   const int threads = 256;
+  // channel multiplier: vector kernel when every output vector reads at most two neighbouring input channels
+  bool mult_ok = aligned && p.mult >= 2 && d->cout % V == 0 && d->y_ctotal % V == 0 && d->y_coff % V == 0 &&
+                 (d->res_mode == RTSEG_RES_NONE || (d->r_ctotal % V == 0 && d->r_coff % V == 0));
+  for (int c0 = 0; mult_ok && c0 < d->cout; c0 += V) mult_ok = (c0 % p.mult) + V - 1 < 2 * p.mult;
+  if (mult_ok) {
+    const int64_t total = (int64_t)p.n * p.ho * p.wo * (d->cout / V);
+    const unsigned grid = (unsigned)cdiv(total, threads);
+    if (ep.mode == 0) dw_mult_kernel<T, 0><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
+    else if (ep.mode == 1) dw_mult_kernel<T, 1><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
+    else dw_mult_kernel<T, 2><<<grid, threads, 0, st>>>(p, x, w, ep, res, y);
+    RTSEG_LAUNCH_CHECK("dw_mult_kernel");
+    return RTSEG_OK;
+  }
   if (!vec_ok) {
     const int64_t total = (int64_t)p.n * p.ho * p.wo * p.cout;
     dw_scalar_kernel<T><<<(unsigned)cdiv(total, threads), threads, 0, st>>>(p, x, w, ep, res, y);

@@ -66,6 +66,10 @@ def to_nhwc(x: torch.Tensor, dtype: Optional[torch.dtype] = None) -> torch.Tenso
     dtype = dtype or x.dtype
     if is_nhwc(x) and x.dtype == dtype:
         return x
+    if torch.is_grad_enabled() and x.requires_grad:
+        # on the autograd tape (training, a leaf in NCHW): torch's own differentiable layout / dtype change —
+        # the raw transpose kernel below would silently cut the graph
+        return x.to(dtype).contiguous(memory_format=torch.channels_last)
     n, c, h, w = x.shape
     if is_nhwc(x):  # dtype change only: treat as [n*h*w, c] -> same layout
         src = x.permute(0, 2, 3, 1).reshape(1, 1, n * h * w, c)  # view, "NCHW" with c'=1

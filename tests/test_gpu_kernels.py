@@ -78,7 +78,12 @@ DW_CASES = [
     (32, 32, (1, 3), 1, 1, 11, 75, "relu"),
     (32, 32, (3, 1), 2, 1, 20, 30, "relu6"),  # ADSCNet: (3,1) with stride 2 halves both dims
     (19, 19, 3, 1, 1, 10, 12, "none"),        # odd channels -> scalar kernel
-    (16, 96, 3, 2, 1, 12, 20, "relu"),        # channel multiplier 6 (BiSeNetv2)
+    (16, 96, 3, 2, 1, 12, 20, "relu"),        # channel multiplier 6 (BiSeNetv2): vector kernel, two input channels per vector
+    (32, 192, 3, 1, 1, 13, 21, "none"),
+    (128, 768, 3, 1, 1, 8, 9, "prelu"),
+    (64, 256, 3, 1, 1, 10, 12, "relu"),       # multiplier 4
+    (12, 24, 3, 2, 1, 10, 12, "relu"),        # multiplier 2: a vector would span four input channels -> scalar kernel
+    (8, 40, (1, 3), 1, 2, 9, 17, "relu6"),    # multiplier 5, dilated 1x3
     (24, 24, 5, 1, 1, 14, 18, "hardswish"),
 ]
 

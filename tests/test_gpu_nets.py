@@ -282,9 +282,12 @@ def test_two_engine_slots_replayed_concurrently_stay_deterministic(name):
 
 def test_modules_refuse_training_mode_and_cpu():
     from rtseg_b200 import modules
-    m = modules.DWConvBNAct(16, 16, 3).cuda()   # depthwise blocks have no weight-gradient kernel yet: no silent fallback
-    with pytest.raises(NotImplementedError, match="training-mode"):
+    m = modules.DWConvBNAct(16, 32, 3).cuda()   # depthwise channel multipliers have no gradient kernels: no silent fallback
+    with pytest.raises(NotImplementedError, match="depthwise"):
         m(torch.randn(1, 16, 8, 8, device="cuda"))
+    m = modules.DWConvBNAct(16, 16, 3).cuda()   # ... and a slice / residual call has no training form
+    with pytest.raises(NotImplementedError, match="training-mode"):
+        m(torch.randn(1, 32, 8, 8, device="cuda").contiguous(memory_format=torch.channels_last), x_coff=16)
     m = modules.ConvBNAct(16, 16, 3).cuda()
     with pytest.raises(TypeError):
         m.eval()(torch.randn(1, 16, 8, 8, device="cuda").half())

@@ -136,6 +136,42 @@ def fastscnn_layers(batch, only, reps):
         del x, y
 
 
+def net_layers(name, batch, only, reps):
+    """Every fused conv layer of a net from nets.MODEL_HUB, with the tensors / keyword arguments the net really passes."""
+    from rtseg_b200.modules import Conv2d, _FusedConvMixin
+    model = nets.MODEL_HUB[name](19).eval().cuda().set_act_dtype(torch.bfloat16)
+    calls, hooks = [], []
+    for mname, m in model.named_modules():
+        if isinstance(m, (Conv2d, _FusedConvMixin)):
+            hooks.append(m.register_forward_pre_hook(
+                lambda mod, a, kw, mname=mname: calls.append((mname, mod, a, dict(kw))), with_kwargs=True))
+    with torch.no_grad():
+        model.lowres_logits(torch.randn((batch, 3, 1024, 2048), device="cuda"))
+    for h in hooks:
+        h.remove()
+    total = 0.0
+    with torch.no_grad():
+        for mname, mod, a, kw in calls:
+            if only and only not in mname:
+                continue
+            conv = mod if isinstance(mod, Conv2d) else mod[0]
+            x = a[0]
+            if x.dtype != torch.bfloat16:
+                continue
+            y = mod(*a, **kw)
+            ms = time_ms(lambda: mod(*a, **kw), reps)
+            total += ms
+            n, _, hh, ww = x.shape
+            by = (n * hh * ww * conv.in_channels + y.shape[0] * y.shape[2] * y.shape[3] * conv.out_channels *
+                  (2 if kw.get("res") is not None else 1)) * 2
+            kind = "dw" if conv.groups > 1 else "pw" if tuple(conv.kernel_size) == (1, 1) else "cv"
+            k = "x".join(map(str, conv.kernel_size))
+            report(f"{kind} {mname[-30:]} {conv.in_channels}->{conv.out_channels} k{k} s{conv.stride[0]} @{hh}x{ww}", ms, by,
+                   2.0 * y.shape[0] * y.shape[2] * y.shape[3] * conv.out_channels * conv.in_channels // conv.groups *
+                   conv.kernel_size[0] * conv.kernel_size[1])
+    print(f"sum of the conv layers: {total:.3f} ms", flush=True)
+
+
 def head_layers(batch, only, reps):
     x = nhwc_rand((batch, 19, 128, 256))
     target = torch.randint(0, 19, (batch, 1024, 2048), device="cuda")
@@ -172,4 +208,7 @@ if __name__ == "__main__":
     a = ap.parse_args()
     torch.cuda.set_device(0)
     for s in a.set.split(","):
+        if s.startswith("net:"):
+            net_layers(s[4:], a.batch, a.only, a.reps)
+            continue
         {"erfnet": erfnet_layers, "fastscnn": fastscnn_layers, "head": head_layers}[s](a.batch, a.only, a.reps)
