@@ -15,7 +15,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "librtseg.so")
-SOURCES = ["runtime.cu", "conv_dw.cu", "dw_tma.cu", "conv_dense.cu", "conv_tc.cu", "pair_tc.cu", "stem.cu", "stem_tc.cu", "head.cu", "ohem.cu", "train.cu", "train_dw.cu", "fuse_ops.cu", "optim.cu"]
+SOURCES = ["runtime.cu", "conv_dw.cu", "dw_tma.cu", "conv_dense.cu", "conv_tc.cu", "pair_tc.cu", "dwpw_tc.cu", "stem.cu", "stem_tc.cu", "head.cu", "ohem.cu", "train.cu", "train_dw.cu", "fuse_ops.cu", "optim.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",

@@ -53,6 +53,34 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, volatil
   mbar_wait_slow(bar, parity, dead);
 }
 
+// A wait for warps that are NOT on the critical path of a CUDA-core-bound kernel (dwpw_tc.cu: the MMA issuer, the
+// epilogue warps and the TMA producer wait most of the time while the depthwise workers need every issue slot): the
+// try_wait carries a suspend-time hint and the watchdog clock is read once per 64 polls, so a waiting warp issues a
+// handful of instructions per microsecond instead of a tight loop.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, volatile uint32_t *dead) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  for (uint32_t it = 1;; ++it) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(2000u)
+        : "memory");
+    if (ok) return;
+    if ((it & 63u) == 0) {
+      if (*dead) return;
+      if (clock64() - t0 > 4000000000LL) {
+        *dead = 1;
+        atomicExch(&g_tc_timeout_flag, 1u);
+        return;
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2,
                                             int c3) {
   asm volatile(

@@ -246,6 +246,31 @@ class DSConvBNAct(nn.Sequential):
         )
 
 
+    def forward(self, x, out=None, y_coff=0):
+        y = dw_then_pw(self[0], self[1]._folded() if not self[1][1].training else None, x, out=out, y_coff=y_coff)
+        if y is not None:
+            return y
+        return self[1](self[0](x), out=out, y_coff=y_coff) if out is not None else self[1](self[0](x))
+
+
+def dw_then_pw(dw: "DWConvBNAct", pw_folded, x, res=None, res_mode=ops.RES_NONE, out=None, y_coff=0, r_coff=0, act2=0):
+    """DWConvBNAct -> (pointwise conv + BN + act [+ residual]) as ONE launch when the fused kernel applies (eval mode,
+    bf16, 3x3 stride 1, channels a multiple of 64, 64 / 128 outputs); None otherwise — the caller then runs the two layers.
+    `pw_folded` = (Folded, post module) of the pointwise layer, or None."""
+    if pw_folded is None or dw[1].training or not isinstance(x, torch.Tensor) or not x.is_cuda or x.dtype != torch.bfloat16:
+        return None
+    if torch.is_grad_enabled() and x.requires_grad:
+        return None
+    fpw, post = pw_folded
+    fdw, post_dw = dw._folded()
+    if post is not None or post_dw is not None:
+        return None
+    x = ops.to_nhwc(x)
+    if not ops.dwpw_supported(fdw, fpw, x, res_mode, res, out, 0, y_coff, r_coff, act2):
+        return None
+    return ops.dwpw(fdw, fpw, x, res=res, res_mode=res_mode, out=out, y_coff=y_coff, r_coff=r_coff, act2=act2)
+
+
 class DeConvBNAct(nn.Module):
     """ConvTranspose2d -> BN -> act (reference models/modules.py:89-108); kernel for scale_factor 2."""
 

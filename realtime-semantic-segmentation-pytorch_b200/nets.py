@@ -25,7 +25,7 @@ import torch.nn as nn
 
 from . import ops
 from .modules import (_FoldCache, Activation, Conv2d, ConvBNAct, DeConvBNAct, DSConvBNAct, DWConvBNAct, PWConvBNAct,
-                      PyramidPoolingModule, _bn_tensors, _check_eval, _FoldCache, conv1x1)
+                      PyramidPoolingModule, _bn_tensors, _check_eval, _FoldCache, conv1x1, dw_then_pw)
 
 
 def _param_dtype(m: nn.Module) -> torch.dtype:
@@ -197,7 +197,14 @@ class InvertedResidual(nn.Module):
 
     def forward(self, x):
         x = ops.to_nhwc(x)
-        t = self.conv[1](self.conv[0](x))
+        t = self.conv[0](x)
+        # depthwise 3x3 + linear projection (+ x) in one launch: the 6x-expanded depthwise output never reaches HBM
+        proj = None if self.conv[2][1].training else self.conv[2]._folded()
+        y = (dw_then_pw(self.conv[1], proj, t, res=x, res_mode=ops.RES_POST) if self.use_res_connect else
+             dw_then_pw(self.conv[1], proj, t))
+        if y is not None:
+            return y
+        t = self.conv[1](t)
         if self.use_res_connect:  # x + conv(x): the add rides in the projection's epilogue
             return self.conv[2](t, res=x, res_mode=ops.RES_POST)
         return self.conv[2](t)
@@ -271,9 +278,13 @@ class FeatureFusionModule(nn.Module):
             lo = train.upsample_bilinear(lower_res_feat, size, True)
         else:
             lo = ops.upsample_bilinear(lower_res_feat, size, True)
+        bn, act = self.non_linear[0], self.non_linear[1].activation
+        if not bn.training:   # depthwise 3x3 -> 1x1 conv -> + hi -> BN -> act in one launch
+            y = dw_then_pw(self.lower_res_conv[0], self.lower_res_conv[1].folded(bn, act), lo, res=hi, res_mode=ops.RES_PRE)
+            if y is not None:
+                return y
         lo = self.lower_res_conv[0](lo)
-        return self.lower_res_conv[1](lo, res=hi, res_mode=ops.RES_PRE, bn=self.non_linear[0],
-                                      act=self.non_linear[1].activation)
+        return self.lower_res_conv[1](lo, res=hi, res_mode=ops.RES_PRE, bn=bn, act=act)
 
 
 class Classifier(nn.Sequential):

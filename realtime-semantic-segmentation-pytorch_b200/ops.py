@@ -442,6 +442,53 @@ def conv_pair(fa: Folded, fb: Folded, x: torch.Tensor, res: Optional[torch.Tenso
     return out
 
 
+USE_DWPW_FUSION = True   # module-level switch (tests / A-B runs): depthwise 3x3 + pointwise 1x1 in one launch
+
+
+def _dwpw_descs(fdw: Folded, fpw: Folded, x: torch.Tensor, x_coff: int, y_ct: int, y_coff: int, res_mode: int, r_ct: int,
+                r_coff: int, act2: int):
+    n, x_ct, h, w = x.shape
+    ddw = _desc(fdw, n, h, w, BF16, x_ct, x_coff, fdw.cout, 0)
+    dpw = _desc(fpw, n, h, w, BF16, fdw.cout, 0, y_ct, y_coff, res_mode, r_ct, r_coff, act2)
+    return ddw, dpw
+
+
+def dwpw_supported(fdw: Folded, fpw: Folded, x: torch.Tensor, res_mode: int = RES_NONE, res: Optional[torch.Tensor] = None,
+                   out: Optional[torch.Tensor] = None, x_coff: int = 0, y_coff: int = 0, r_coff: int = 0, act2: int = 0) -> bool:
+    """Can `conv(fpw, conv(fdw, x))` (depthwise 3x3 -> pointwise 1x1, + residual) run as one rtseg_dwpw_tc launch?"""
+    if not (USE_DWPW_FUSION and USE_TENSOR_CORES and x.is_cuda and x.dtype == torch.bfloat16 and is_nhwc(x)):
+        return False
+    if fdw.kind != "dw" or fpw.kind != "dense" or fpw.w_tc is None or fdw.slope is not None or fpw.slope is not None:
+        return False
+    if fpw.w_tc.shape[1] != fpw.cout or fpw.w_tc.shape[2] != fpw.cin:     # padded weights: not this kernel's layout
+        return False
+    y_ct = out.shape[1] if out is not None else fpw.cout
+    r_ct = res.shape[1] if res is not None else 0
+    ddw, dpw = _dwpw_descs(fdw, fpw, x, x_coff, y_ct, y_coff, res_mode, r_ct, r_coff, act2)
+    return bool(_lib.load().rtseg_dwpw_tc_supported(C.byref(ddw), C.byref(dpw)))
+
+
+def dwpw(fdw: Folded, fpw: Folded, x: torch.Tensor, res: Optional[torch.Tensor] = None, res_mode: int = RES_NONE,
+         out: Optional[torch.Tensor] = None, x_coff: int = 0, y_coff: int = 0, r_coff: int = 0, act2: int = 0) -> torch.Tensor:
+    """DWConvBNAct(3x3) -> PWConvBNAct / conv1x1 (+ BN, + residual) in one launch (reference models/modules.py:36-42,
+    models/fastscnn.py:80-92, 113-121): the depthwise output stays in shared memory as the pointwise MMA's A tile."""
+    _require_cuda(x, "dwpw")
+    _no_tape(x, "dwpw")
+    n, _, h, w = x.shape
+    if out is None:
+        out = empty_nhwc(n, fpw.cout, h, w, x.dtype, x.device)
+    elif not is_nhwc(out) or out.dtype != x.dtype or tuple(out.shape[2:]) != (h, w) or out.shape[0] != n:
+        raise ValueError("bad output buffer")
+    if res_mode != RES_NONE and (res is None or not is_nhwc(res) or res.dtype != x.dtype or tuple(res.shape[2:]) != (h, w)):
+        raise ValueError("bad residual tensor")
+    ddw, dpw = _dwpw_descs(fdw, fpw, x, x_coff, out.shape[1], y_coff, res_mode, res.shape[1] if res is not None else 0,
+                           r_coff, act2)
+    _lib.check(_lib.load().rtseg_dwpw_tc(C.byref(ddw), x.data_ptr(), fdw.w_f32.data_ptr(), _ptr(fdw.scale), _ptr(fdw.shift),
+                                         C.byref(dpw), fpw.w_tc.data_ptr(), _ptr(fpw.scale), _ptr(fpw.shift), _ptr(res),
+                                         out.data_ptr(), _stream()), "rtseg_dwpw_tc")
+    return out
+
+
 def stem(f: Folded, x: torch.Tensor, pool: bool, out_dtype: torch.dtype, out: Optional[torch.Tensor] = None,
          y_coff: int = 0) -> torch.Tensor:
     """InitialBlock / stride-2 stem straight from the caller's NCHW (or NHWC) tensor, or from the uint8 HWC image
