@@ -134,6 +134,7 @@ struct StemParams {
   int y_ct, y_co;
   int pool;
   ImgNorm nz;              // uint8 inputs only
+  int u8_words = 0;        // uint8 HWC, 3 channels, 4-byte aligned rows: windows are read as aligned 32-bit words
 };
 
 // ---- device side ---------------------------------------------------------------

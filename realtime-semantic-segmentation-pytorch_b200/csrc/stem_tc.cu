@@ -123,7 +123,25 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
     const int iy0 = oy * 2 - 1, ix0 = ox * 2 - 1;
     const TI *base = x + ((int64_t)b * p.sn + (int64_t)iy0 * p.sh + (int64_t)ix0 * kxs);
     const bool interior = valid && iy0 >= 0 && iy0 + 2 < p.h && ix0 >= 0 && ix0 + 2 < p.w;
-    if (interior) {
+    if (interior && sizeof(TI) == 1 && !NCHW && CIN == 3 && p.u8_words) {
+      // decoded uint8 HWC image: a window row is 9 contiguous bytes.  Three aligned 32-bit loads cover them wherever
+      // they start (the launcher checked 4-byte aligned rows and a 4-byte multiple of total bytes, so no word
+      // reaches past the buffer); two funnel shifts line the bytes up.  9 loads per pixel instead of 27.
+      okmask = 0x1ff;
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(base + off[0][ky]);
+        const uint32_t r8 = (uint32_t)(a & 3u) * 8u;
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+        const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2);
+        const uint32_t s[3] = {__funnelshift_r(w0, w1, r8), __funnelshift_r(w1, w2, r8), w2 >> r8};
+#pragma unroll
+        for (int j = 0; j < 9; ++j) {
+          const uint32_t byte = (s[j >> 2] >> (8 * (j & 3))) & 0xffu;
+          v[ky * 9 + j] = __fmul_rn(__fsub_rn((float)byte, p.nz.m255[j % 3]), p.nz.rden[j % 3]);   // v[(ky*3 + kx)*3 + ci], j = kx*3 + ci
+        }
+      }
+    } else if (interior) {
       okmask = 0x1ff;
 #pragma unroll
       for (int ci = 0; ci < CIN; ++ci)
@@ -292,7 +310,13 @@ int stem_tc_try(const StemParams &p, int x_dtype, const void *x, const float *w,
   __nv_bfloat16 *yo = static_cast<__nv_bfloat16 *>(y);
   if (x_dtype == RTSEG_F32) return launch_in<float>(p, static_cast<const float *>(x), w, ep, yo, st);
   if (x_dtype == RTSEG_BF16) return launch_in<__nv_bfloat16>(p, static_cast<const __nv_bfloat16 *>(x), w, ep, yo, st);
-  if (x_dtype == RTSEG_U8) return launch_in<uint8_t>(p, static_cast<const uint8_t *>(x), w, ep, yo, st);
+  if (x_dtype == RTSEG_U8) {
+    StemParams q = p;
+    static const int words_knob = getenv("RTSEG_STEM_U8_WORDS") ? atoi(getenv("RTSEG_STEM_U8_WORDS")) : 1;
+    q.u8_words = words_knob && p.cin == 3 && p.sc == 1 && p.sw == 3 && p.sh % 4 == 0 && p.sn % 4 == 0 &&
+                 reinterpret_cast<uintptr_t>(x) % 4 == 0;
+    return launch_in<uint8_t>(q, static_cast<const uint8_t *>(x), w, ep, yo, st);
+  }
   return 1;
 }
 
