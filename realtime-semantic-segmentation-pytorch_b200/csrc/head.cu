@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256) bilinear_kernel(int n, int hi, int wi, in
 
 // ------------------------------------------------- fused upsample + argmax ----
 constexpr int kHeadThreads = 128;  // output columns per block
-constexpr int kHeadRows = 16;      // output rows per thread
+constexpr int kHeadRows = 32;      // output rows per thread (x8 heads: ~4 source-row pairs, each loaded once)
 constexpr int kMaxBins = 32 * 32;
 
 __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool valid) {
@@ -94,7 +94,7 @@ template <typename T, int CMAX>
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int n, int hi, int wi, int c, int ct, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
     uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
-    unsigned long long *__restrict__ confmat) {
+    unsigned long long *__restrict__ confmat, int vec) {
   __shared__ int hist[kMaxBins];
   const bool do_cm = target != nullptr;
   if (do_cm) {
@@ -113,21 +113,44 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
 
   float rowA[CMAX], rowD[CMAX];  // A and (B - A)
   int ia = -1, ib = -1;
+  int run_bin = 0, run_cnt = 0;  // confusion-matrix bin of the current run of rows and its length
   bool has_nan = false;
 
-  // horizontally interpolated source row i, channels >= c padded so that they never win
+  // horizontally interpolated source row i, channels >= c padded so that they never win.  bf16 logits in a 16-byte
+  // aligned buffer (`vec`) are read as 16-byte vectors: ceil(CMAX / 8) loads per corner pixel instead of CMAX.
   auto load_row = [&](int i, float(&row)[CMAX]) {
     const T *p0 = xb + ((int64_t)i * wi + x0) * ct;
     const T *p1 = xb + ((int64_t)i * wi + x1) * ct;
+    float bad = 0.f;   // max |v| with NaNs kept: one compare per row instead of one per class
+    if (sizeof(T) == 2 && vec) {
+      constexpr int NV = (CMAX + 7) / 8;
+      uint32_t q0[NV * 4], q1[NV * 4];
 #pragma unroll
-    for (int k = 0; k < CMAX; ++k) {
-      float v = -INFINITY;
-      if (k < c) {
-        v = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
-        has_nan |= !(fabsf(v) <= FLT_MAX);   // NaN or +-inf
+      for (int j = 0; j < NV; ++j) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4 *>(p0) + j), bq = __ldg(reinterpret_cast<const uint4 *>(p1) + j);
+        q0[4 * j] = a.x, q0[4 * j + 1] = a.y, q0[4 * j + 2] = a.z, q0[4 * j + 3] = a.w;
+        q1[4 * j] = bq.x, q1[4 * j + 1] = bq.y, q1[4 * j + 2] = bq.z, q1[4 * j + 3] = bq.w;
       }
-      row[k] = v;
+#pragma unroll
+      for (int k = 0; k < CMAX; ++k) {
+        const float a = __uint_as_float((k & 1) ? (q0[k >> 1] & 0xffff0000u) : (q0[k >> 1] << 16));
+        const float bq = __uint_as_float((k & 1) ? (q1[k >> 1] & 0xffff0000u) : (q1[k >> 1] << 16));
+        const float v = lx0 * a + lx1 * bq;
+        bad = fmax_nan(bad, (k < c) ? fabsf(v) : 0.f);
+        row[k] = (k < c) ? v : -INFINITY;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < CMAX; ++k) {
+        float v = -INFINITY;
+        if (k < c) {
+          v = lx0 * ld_f<T>(p0 + k) + lx1 * ld_f<T>(p1 + k);
+          bad = fmax_nan(bad, fabsf(v));
+        }
+        row[k] = v;
+      }
     }
+    has_nan |= !(bad <= FLT_MAX);   // NaN or +-inf somewhere in this row
   };
 
   for (int ry = 0; ry < kHeadRows; ++ry) {
@@ -176,18 +199,23 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
       if (lab8) lab8[opix] = (uint8_t)label;
       if (lab64) lab64[opix] = (int64_t)label;
     }
-    if (do_cm) {
-      bool valid = false;
-      int bin = 0;
-      if (col_ok) {
-        const int64_t t = __ldg(target + ((int64_t)b * ho + oy) * wo + ox);
-        valid = t != (int64_t)ignore_index && t >= 0 && t < c;
-        bin = valid ? (int)t * c + label : 0;
+    if (do_cm && col_ok) {
+      // a thread walks one image column: consecutive rows mostly fall into the same (target, prediction) bin, so
+      // the count runs in a register and reaches the shared histogram once per run, not once per pixel
+      const int64_t t = __ldg(target + ((int64_t)b * ho + oy) * wo + ox);
+      if (t != (int64_t)ignore_index && t >= 0 && t < c) {
+        const int bin = (int)t * c + label;
+        if (bin == run_bin) {
+          ++run_cnt;
+        } else {
+          if (run_cnt) atomicAdd(&hist[run_bin], run_cnt);
+          run_bin = bin, run_cnt = 1;
+        }
       }
-      hist_add_aggregated(hist, bin, valid);
     }
   }
   if (do_cm) {
+    if (run_cnt) atomicAdd(&hist[run_bin], run_cnt);
     __syncthreads();
     for (int i = threadIdx.x; i < c * c; i += blockDim.x) {
       const int v = hist[i];
@@ -537,14 +565,16 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ct, int ho, 
   const T *xs = static_cast<const T *>(x);
 #define RTSEG_HEAD(CM)                                                                                              \
   if (c <= CM) {                                                                                                    \
+    const int vec = sizeof(T) == 2 && ct % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && (CM + 7) / 8 * 8 <= ct; \
     upsample_argmax_kernel<T, CM><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64, \
-                                                                 target, ignore, cm);                              \
+                                                                 target, ignore, cm, vec);                         \
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");                                                                   \
     return RTSEG_OK;                                                                                                \
   }
   if (c == 19) {  // Cityscapes: exact instantiation, no padded classes
+    const int vec = sizeof(T) == 2 && ct % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && 24 <= ct;
     upsample_argmax_kernel<T, 19><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
-                                                                 target, ignore, cm);
+                                                                 target, ignore, cm, vec);
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");
     return RTSEG_OK;
   }
