@@ -430,6 +430,11 @@ int rtseg_upsample_bilinear_bwd(int32_t n, int32_t hi, int32_t wi, int32_t c, in
                                 int32_t x_coff, rtseg_stream_t stream);
 int rtseg_adaptive_avgpool_bwd(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p, int32_t dtype, const void *dy, void *dx,
                                int32_t x_ctotal, int32_t x_coff, rtseg_stream_t stream);
+/* Adjoint of rtseg_maxunpool2x2 (ENet's upsampling bottleneck, models/enet.py:176-178): dx [n][hp][wp][c] dense NHWC =
+ * dy [n][ho][wo][c] at the position each one-byte index points to.  (The adjoint of rtseg_maxpool2x2_idx is
+ * rtseg_maxunpool2x2 itself, applied to the gradient.) */
+int rtseg_maxunpool2x2_bwd(int32_t n, int32_t hp, int32_t wp, int32_t c, int32_t ho, int32_t wo, int32_t dtype, const void *dy,
+                           const uint8_t *idx, void *dx, rtseg_stream_t stream);
 /* ---- f3: optimizer step + weight mirror in one launch ----------------------
  * Replaces torch.optim.SGD.step() as the reference configures it (utils/optimizer.py:8-12: lr, momentum, weight
  * decay; dampening 0, no Nesterov) followed by ModelEmaV2.update (utils/model_ema.py:28-40:

@@ -281,6 +281,24 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_bwd_kernel(int n, int h,
   st_f<T>(dx + (((int64_t)b * h + iy) * w + ix) * x_ct + x_co + ch, acc);
 }
 
+// ---- adjoint of MaxUnpool2d(2, 2): every pooled position reads the gradient at the place its index points to ----
+template <typename T>
+__global__ void __launch_bounds__(256) gather2x2_kernel(int n, int hp, int wp, int c, int ho, int wo, const T *__restrict__ dy,
+                                                        const uint8_t *__restrict__ idx, T *__restrict__ dx) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)n * hp * wp * c) return;
+  const int ch = (int)(i % c);
+  int64_t r = i / c;
+  const int px = (int)(r % wp);
+  r /= wp;
+  const int py = (int)(r % hp);
+  const int img = (int)(r / hp);
+  const int pos = (int)idx[i];
+  const int oy = 2 * py + (pos >> 1), ox = 2 * px + (pos & 1);
+  const float v = (oy < ho && ox < wo) ? ld_f<T>(dy + (((int64_t)img * ho + oy) * wo + ox) * c + ch) : 0.f;
+  st_f<T>(dx + i, v);
+}
+
 int fill_geom(const rtseg_conv_desc *d, DwGeom &g) {
   if (d->groups != d->cin || d->cout != d->cin) return -1;   // channel multiplier 1 only
   if (d->stride < 1 || d->dil < 1 || d->kh < 1 || d->kw < 1) return -1;
@@ -447,5 +465,23 @@ extern "C" int rtseg_adaptive_avgpool_bwd(int32_t n, int32_t h, int32_t w, int32
   else
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
   RTSEG_LAUNCH_CHECK("adaptive_avgpool_bwd_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_maxunpool2x2_bwd(int32_t n, int32_t hp, int32_t wp, int32_t c, int32_t ho, int32_t wo, int32_t dtype,
+                                      const void *dy, const uint8_t *idx, void *dx, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(dy && idx && dx, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && hp > 0 && wp > 0 && c > 0 && ho >= 2 * hp && wo >= 2 * wp, "bad extent");
+  const int64_t threads = (int64_t)n * hp * wp * c;
+  RTSEG_REQUIRE(cdiv(threads, 256) <= INT32_MAX, "tensor too large");
+  const unsigned grid = (unsigned)cdiv(threads, 256);
+  if (dtype == RTSEG_BF16)
+    gather2x2_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(n, hp, wp, c, ho, wo, (const __nv_bfloat16 *)dy, idx,
+                                                                        (__nv_bfloat16 *)dx);
+  else if (dtype == RTSEG_F32)
+    gather2x2_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(n, hp, wp, c, ho, wo, (const float *)dy, idx, (float *)dx);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("gather2x2_kernel");
   return RTSEG_OK;
 }

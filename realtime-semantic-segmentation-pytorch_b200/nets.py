@@ -506,8 +506,31 @@ class DABNet(nn.Module):
     def lowres_logits(self, x):
         return _first_channels(self._lowres_padded(x), self.num_class)
 
+    def _train_forward(self, x):
+        """The reference's own graph (models/dabnet.py:36-61) as tape nodes: the three concatenations are torch copy
+        nodes here, exactly as in the reference; the average-pool pyramid of the image needs no gradient."""
+        from . import train
+        dt = self.act_dtype or _param_dtype(self.layer1)
+        cat = lambda ts: ops.to_nhwc(torch.cat(ts, dim=1))
+        with torch.no_grad():
+            x_d2 = ops.avgpool3x3s2(x, out_dtype=dt)
+            x_d4 = ops.avgpool3x3s2(x_d2)
+            x_d8 = ops.avgpool3x3s2(x_d4)
+        stem = self.layer1
+        xn = ops.to_nhwc(x, dt)
+        y = train.conv_bn_act_aligned(stem, xn, pad_input=True) if stem[0].in_channels <= 4 else stem(xn)
+        y = self.layer3(self.layer2(y))
+        b2 = self.layer4(cat([y, x_d2]))
+        y = self.layer5_7(b2)
+        b3 = self.layer8(cat([y, b2, x_d4]))
+        y = self.layer13_14(self.layer11_12(self.layer9_10(b3)))
+        y = self.layer15(cat([y, b3, x_d8]))
+        return train.upsample_bilinear(y, x.shape[2:], True)
+
     def forward(self, x):
         x = ops.image_view(x)
+        if self.layer1[1].training:
+            return self._train_forward(x)
         return ops.upsample_bilinear(self._lowres_padded(x), x.shape[2:], True, c=self.num_class)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,
@@ -660,7 +683,15 @@ class Upsample(nn.Module):
 
     def forward(self, x, labels=None, want_logits=True):
         x = ops.to_nhwc(x)
-        if isinstance(self.up_conv, nn.ConvTranspose2d):
+        deconv = isinstance(self.up_conv, nn.ConvTranspose2d)
+        if self.training and labels is None:
+            from . import train   # tape nodes: the transposed conv's gradients are its adjoint stride-2 convolution
+            if deconv:
+                return train.conv(self.up_conv, x)
+            y = self.up_conv[0](x)
+            sf = self.up_conv[1].scale_factor
+            return train.upsample_bilinear(y, (int(y.shape[2] * sf), int(y.shape[3] * sf)), False)
+        if deconv:
             return ops.conv(self._folded()[0], x, labels=labels, want_logits=want_logits)
         y = self.up_conv[0](x)
         sf = self.up_conv[1].scale_factor
@@ -704,11 +735,16 @@ class Bottleneck(nn.Module):
         x = ops.to_nhwc(x)
         last, act = self.right_last_conv[0], self.act.activation
         if self.training:
-            if self.conv_type in ("downsampling", "upsampling"):
-                raise NotImplementedError("ENet Bottleneck: the pooling pair has no adjoint kernels; only the regular / dilate / "
-                                          "asymmetric bottlenecks train on this path")
             from . import train   # Dropout is torch's own elementwise mask node (reference enet.py:160)
-            return train.act(act, self.right_last_conv[1](last(self.right_init_conv(x))), x)
+            right = self.right_last_conv[1](last(self.right_init_conv(x)))
+            if self.conv_type == "downsampling":
+                pooled, idx = train.maxpool2x2_with_indices(x)       # adjoint = the unpooling kernel
+                return train.act(act, self.left_conv(pooled), right), idx
+            if self.conv_type == "upsampling":
+                if indices is None:
+                    raise ValueError("Upsampling-type conv needs pooling indices.")
+                return train.act(act, train.maxunpool2x2(self.left_conv(x), indices), right)
+            return train.act(act, right, x)
         right = self.right_init_conv(x)
         if self.conv_type == "downsampling":
             pooled, idx = ops.maxpool2x2_with_indices(x)

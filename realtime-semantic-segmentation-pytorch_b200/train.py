@@ -398,6 +398,46 @@ class _AdaptiveAvgPoolFn(torch.autograd.Function):
         return dx, None
 
 
+class _MaxPool2x2IdxFn(torch.autograd.Function):
+    """nn.MaxPool2d(2, 2, return_indices=True) (reference models/enet.py:130-131): the adjoint is the unpooling kernel."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = ops.to_nhwc(x)
+        pooled, idx = ops.maxpool2x2_with_indices(x)
+        ctx.save_for_backward(idx)
+        ctx.size = (x.shape[2], x.shape[3])
+        ctx.mark_non_differentiable(idx)
+        return pooled, idx
+
+    @staticmethod
+    def backward(ctx, dy, _didx):
+        (idx,) = ctx.saved_tensors
+        return ops.maxunpool2x2(ops.to_nhwc(dy), idx, ctx.size)
+
+
+class _MaxUnpoolFn(torch.autograd.Function):
+    """nn.MaxUnpool2d(2, 2)(x, indices) (reference models/enet.py:176-178)."""
+
+    @staticmethod
+    def forward(ctx, x, idx, size):
+        x = ops.to_nhwc(x)
+        ctx.save_for_backward(idx)
+        ctx.shape = tuple(x.shape)
+        return ops.maxunpool2x2(x, idx, size)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        n, c, hp, wp = ctx.shape
+        dy = ops.to_nhwc(dy)
+        dx = ops.empty_nhwc(n, c, hp, wp, dy.dtype, dy.device)
+        _lib.check(_lib.load().rtseg_maxunpool2x2_bwd(n, hp, wp, c, dy.shape[2], dy.shape[3], ops._dtype_code(dy.dtype),
+                                                      dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), ops._stream()),
+                   "rtseg_maxunpool2x2_bwd")
+        return dx, None, None
+
+
 # ------------------------------------------------------------------ module-level entry points ----
 def conv(module: nn.Module, x: torch.Tensor) -> torch.Tensor:
     """Training forward of a bare nn.Conv2d / nn.ConvTranspose2d (dense, zero padding)."""
@@ -444,6 +484,14 @@ def upsample_bilinear(x: torch.Tensor, size, align_corners: bool) -> torch.Tenso
 
 def adaptive_avgpool(x: torch.Tensor, p: int) -> torch.Tensor:
     return _AdaptiveAvgPoolFn.apply(x, p)
+
+
+def maxpool2x2_with_indices(x: torch.Tensor):
+    return _MaxPool2x2IdxFn.apply(x)
+
+
+def maxunpool2x2(x: torch.Tensor, idx: torch.Tensor, size=None) -> torch.Tensor:
+    return _MaxUnpoolFn.apply(x, idx, size)
 
 
 def taping(*tensors) -> bool:

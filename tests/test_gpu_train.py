@@ -366,6 +366,154 @@ def test_fastscnn_training_step_matches_oracle_loss_and_gradients():
             assert l2(v.float().cpu(), sd64[k]) < 1e-4, k
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c,h,w", [(16, 16, 24), (64, 9, 14), (20, 7, 5)])
+def test_pooling_pair_adjoints_match_torch_autograd(c, h, w, dtype):
+    """MaxPool2d(2, 2, return_indices) / MaxUnpool2d (reference models/enet.py:130-139, 176-178) under autograd."""
+    import torch.nn.functional as F
+    from rtseg_b200 import train
+    x = seeded((2, c, h, w), 230).to(dtype)
+    hp, wp = h // 2, w // 2
+    g1, g2 = seeded((2, c, hp, wp), 231).to(dtype), seeded((2, c, h, w), 232).to(dtype)
+    xr = x.float().clone().requires_grad_(True)
+    pr, ir = F.max_pool2d(xr, 2, 2, return_indices=True)
+    pr.backward(g1.float())
+    v = seeded((2, c, hp, wp), 233).to(dtype)
+    vr = v.float().clone().requires_grad_(True)
+    F.max_unpool2d(vr, ir, 2, 2, output_size=(h, w)).backward(g2.float())
+    xg = x.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    pooled, idx = train.maxpool2x2_with_indices(xg)
+    pooled.backward(g1.cuda())
+    vg = v.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    train.maxunpool2x2(vg, idx, (h, w)).backward(g2.cuda())
+    assert torch.equal(xg.grad.float().cpu(), xr.grad) and torch.equal(vg.grad.float().cpu(), vr.grad)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("conv_type,upsample_type", [("downsampling", None), ("upsampling", "deconvolution"), ("upsampling", "regular")])
+def test_enet_pooling_bottlenecks_training_step(conv_type, upsample_type, dtype):
+    import torch.nn.functional as F
+    from rtseg_b200 import nets
+    cin, cout = (16, 64) if conv_type == "downsampling" else (64, 16)
+    m = _randomise(nets.Bottleneck(cin, cout, conv_type, upsample_type=upsample_type or "regular", drop_p=0.0), 234)
+    with torch.no_grad():
+        m.act.activation.weight.fill_(0.2)
+    if conv_type == "downsampling":
+        x = seeded((2, cin, 16, 24), 235)
+        _check(_First(m), lambda sd, t: ref_nets.enet_bottleneck(t, _strip(sd), "m.", conv_type)[0], x, dtype, 236)
+    else:
+        x = seeded((2, cin, 8, 12), 235)
+        src = seeded((2, cout, 16, 24), 237)
+        idx = F.max_pool2d(src, 2, 2, return_indices=True)[1]
+        pos = ((idx // 24) % 2 * 2 + (idx % 24) % 2).to(torch.uint8).permute(0, 2, 3, 1).contiguous().cuda()   # one-byte window positions
+        if upsample_type == "deconvolution":
+            fn = lambda sd, t: ref_nets.enet_bottleneck(t, _strip(sd), "m.", conv_type, indices=idx)
+        else:   # the reference's non-deconvolution Upsample: ConvBNAct 1x1 + bilinear x2 (models/enet.py:195-198)
+            def fn(sd, t):
+                sd = _strip(sd)
+                r = B.conv_bn_act(t, sd, "m.right_init_conv.0.", 1, 1, 1, "relu")
+                r = B.conv_bn_act(r, sd, "m.right_init_conv.1.up_conv.0.", 1, 1, 1, "relu")
+                r = F.interpolate(r, scale_factor=2, mode="bilinear")
+                r = F.conv2d(r, sd["m.right_last_conv.0.weight"])
+                left = F.max_unpool2d(B.conv_bn_act(t, sd, "m.left_conv.", 1, 1, 1, "relu"), idx, 2, 2)
+                return B.activation(left + r, "prelu", sd, "m.act.")
+        _check(_WithIdx(m, pos), fn, x, dtype, 238)
+
+
+class _First(torch.nn.Module):
+    """Bottleneck('downsampling') returns (x, indices): the step is taken through x."""
+
+    def __init__(self, m):
+        super().__init__()
+        self.m = m
+
+    def forward(self, x):
+        return self.m(x)[0]
+
+
+class _WithIdx(torch.nn.Module):
+    def __init__(self, m, idx):
+        super().__init__()
+        self.m, self.idx = m, idx
+
+    def forward(self, x):
+        return self.m(x, self.idx)
+
+
+def _strip(sd):
+    """state-dict keys of the wrapper modules above: 'm.m.' -> 'm.'"""
+    return {("m." + k[4:] if k.startswith("m.m.") else k): v for k, v in sd.items()}
+
+
+def _net_step_check(name, forward, seed, in_seed, label_seed, hw, prepare=None, grad_floor=1.5e-2):
+    from rtseg_b200 import loss as rloss
+    from rtseg_b200 import nets
+    spec = load_specs()[name]["spec"]
+    sd0 = ref_nets.make_state(spec, seed, True)
+    x = ref_nets.make_input(in_seed, 2, *hw)
+    g = torch.Generator().manual_seed(label_seed)
+    labels = torch.randint(0, 19, (2, *hw), generator=g)
+    labels[torch.rand((2, *hw), generator=g) < 0.1] = 255
+    lg64, loss64, g64, sd64 = _oracle_net_step(forward, sd0, x, labels, torch.float64)
+    lg32, loss32, g32, _ = _oracle_net_step(forward, sd0, x, labels, torch.float32)
+    m = nets.MODEL_HUB[name](num_class=19)
+    m.load_state_dict(sd0, strict=True)
+    if prepare:
+        prepare(m)
+    m = m.cuda().train()
+    out = m(x.cuda())
+    loss = rloss.OhemCELoss(0.7, 255)(out, labels.cuda())
+    loss.backward()
+
+    def l2(a, b):
+        return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+    named = dict(m.named_parameters())
+    keys = [k for k in named if not (k.endswith(".bias") and sd0[k[:-4] + "weight"].dim() == 4)]
+    assert all(named[k].grad is not None for k in keys), [k for k in keys if named[k].grad is None]
+    ours = torch.cat([named[k].grad.double().cpu().flatten() for k in keys])
+    o32 = torch.cat([g32[k].double().flatten() for k in keys])
+    o64 = torch.cat([g64[k].flatten() for k in keys])
+    e_logits, f_logits = l2(out.float().cpu(), lg64), l2(lg32, lg64)
+    e_grad, f_grad = l2(ours, o64), l2(o32, o64)
+    print(f"{name} training step: loss {loss.item():.6f} (fp64 oracle {loss64.item():.6f}); vs fp64 oracle, L2: logits "
+          f"{e_logits:.2e} (fp32 oracle itself {f_logits:.2e}), gradients {e_grad:.2e} (fp32 oracle itself {f_grad:.2e})")
+    assert abs(loss.item() - loss64.item()) <= 1e-5 * max(1.0, abs(loss64.item()))
+    assert e_logits <= max(1e-5, 4 * f_logits)
+    # OhemCELoss is discontinuous in the logits: a pixel whose loss sits within rounding of the threshold enters or
+    # leaves the hard set and moves EVERY gradient by ~1 / n_hard (seen as the same ~1e-2 relative error on all conv
+    # weights while the loss itself, the conv / BatchNorm / bilinear gradients taken alone and dL/dlogits on the
+    # oracle's own logits agree to 3e-7).  Hence a floor instead of the 1e-4 a smooth loss would allow.
+    assert e_grad <= max(grad_floor, 4 * f_grad)
+    for k, v in m.state_dict().items():
+        if "running" in k:
+            assert l2(v.float().cpu(), sd64[k]) < 1e-4, k
+    return loss.item()
+
+
+def test_dabnet_training_step_matches_oracle_and_reference_golden():
+    """DABNet in .train() (reference models/dabnet.py:36-61: depthwise asymmetric branches, PReLU everywhere, three
+    concatenations with the image pyramid): loss, gradients, running statistics against the oracle; the loss also
+    against the REAL reference's recorded step (tests/golden/train_step_dw.json)."""
+    import json
+    import os
+    from tests.helpers import GOLDEN
+    loss = _net_step_check("dabnet", ref_nets.dabnet_forward, 23, 24, 25, (64, 128))
+    with open(os.path.join(GOLDEN, "train_step_dw.json")) as f:
+        gold = json.load(f)["dabnet"]
+    assert abs(loss - gold["loss"]) <= 1e-5 * max(1.0, abs(gold["loss"]))
+
+
+def test_enet_training_step_matches_oracle():
+    """ENet in .train() with Dropout p = 0 (torch's own mask node otherwise): pooling pair with indices, transposed-conv
+    upsampling bottlenecks, PReLU slopes, the bilinear head (reference models/enet.py:14-35)."""
+    def no_dropout(m):
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+    _net_step_check("enet", ref_nets.enet_forward, 33, 34, 35, (64, 128), prepare=no_dropout)
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (run with gpurun --gpus 2)")
 def test_ddp_syncbn_matches_oracle_on_the_joint_batch(tmp_path):
     """Two ranks, DistributedDataParallel + SyncBatchNorm (reference utils/parallel.py:29-38), two images each: batch
