@@ -182,6 +182,15 @@ __device__ __noinline__ float act_generic(float v, int act, float p0, float p1, 
 // MODE 1: slope epilogue (leakyrelu / prelu), staged output.
 // MODE 2: everything else (any activation, fused argmax, unaligned output, labels only).
 // MODE 3: transposed conv with labels only (clamp activation): argmax straight out of TMEM.
+// The labels head (MODE 3) is bound by its epilogue warps' issue slots: there the producer and the MMA issuer — which
+// wait most of the time — use the suspend-hinted wait (they were 30 % of the issued instructions).  Everywhere else
+// these two warps sit on the critical path and keep the tight poll (hinted waits cost 5-8 % on the 128-channel layers).
+template <int MODE>
+__device__ __forceinline__ void tc_wait(uint32_t bar, uint32_t parity, volatile uint32_t *dead) {
+  if constexpr (MODE == 3) mbar_wait_relaxed(bar, parity, dead);
+  else mbar_wait(bar, parity, dead);
+}
+
 template <int KB, int MODE, bool RES>
 __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps, const TcParams p,
                                                                 Epilogue ep, const __nv_bfloat16 *__restrict__ res,
@@ -273,7 +282,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         const int w0 = twi * unit_w, h0 = thi * unit_h;
         if (p.a_share) {
           for (int kb = 0; kb < p.nkb; ++kb) {
-            mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+            tc_wait<MODE>(empty_bar + 8 * stage, phase ^ 1, dead);
             TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), kb == 0 ? 0 : 1);
             mbar_expect_tx(full_bar + 8 * stage, p.a_tx_bytes);
             tma_load_4d(s_a + stage * kStageBytes, &maps.a[0], full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.a_dx,
@@ -284,7 +293,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           for (int t = 0; t < p.ntaps; ++t) {
             const CUtensorMap *am = &maps.a[p.taps[t].map];
             for (int kb = 0; kb < p.nkb; ++kb) {
-              mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+              tc_wait<MODE>(empty_bar + 8 * stage, phase ^ 1, dead);
               mbar_expect_tx(full_bar + 8 * stage, p.a_tx_bytes);
               tma_load_4d(s_a + stage * kStageBytes, am, full_bar + 8 * stage, p.x_coff + kb * KB, w0 + p.taps[t].dx,
                           h0 + p.taps[t].dy, img);
@@ -295,7 +304,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // The residual tile rides the same ring (consumed by the epilogue warps, not by the MMA): it is
         // in shared memory, swizzled like the output staging tile, long before its accumulator is ready.
         for (int sb = 0; sb < p.res_boxes; ++sb) {
-          mbar_wait(empty_bar + 8 * stage, phase ^ 1, dead);
+          tc_wait<MODE>(empty_bar + 8 * stage, phase ^ 1, dead);
           mbar_expect_tx(full_bar + 8 * stage, (uint32_t)p.ms * kTileM * (uint32_t)p.ob * 2);
           tma_load_4d(s_a + stage * kStageBytes, &maps.r, full_bar + 8 * stage, p.r_co + co_base + sb * p.ob, w0, h0, img);
           if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
@@ -315,7 +324,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       mbar_wait(b_bar, 0, dead);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int64_t tile = blockIdx.x; tile < p.num_m_tiles; tile += gridDim.x) {
-        mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, dead);
+        tc_wait<MODE>(tempty_bar + 8 * acc, acc_phase ^ 1, dead);
         tc_fence_after();
         if (lane == 0) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), 2);
         const uint32_t d_tmem = tmem_base + acc * acc_cols;
@@ -323,7 +332,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         if (p.a_share) {
           // one stage per kb holds the rows of every tap; tap t starts tap_off16[t] into it
           for (int kb = 0; kb < p.nkb; ++kb) {
-            mbar_wait(full_bar + 8 * stage, phase, dead);
+            tc_wait<MODE>(full_bar + 8 * stage, phase, dead);
             tc_fence_after();
             if (lane == 0) TC_TRACE((int)((tile - blockIdx.x) / gridDim.x), kb == 0 ? 3 : 4);
             if (elect_one()) {
