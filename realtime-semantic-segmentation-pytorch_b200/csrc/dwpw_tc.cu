@@ -105,11 +105,14 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // depthwise taps with the BatchNorm scale folded in (fp32), shifts, pointwise scale / shift
-  for (int i = threadIdx.x; i < 9 * p.c; i += blockDim.x) {
-    const int ch = i % p.c;
-    g_dw[i] = w_dw[i] * (scale_dw ? scale_dw[ch] : 1.f);
+  // layout: [tap 0..8, shift][64-channel block][half 0 / 1][8-channel vector j][4 floats]: the eight vectors j of one
+  // (tap, block, half) are 128 contiguous bytes, so a quarter warp (j = 0..7) reads them without bank conflicts
+  for (int i = threadIdx.x; i < 10 * p.c; i += blockDim.x) {
+    const int tp = i / p.c, ch = i - tp * p.c;
+    const int kb = ch >> 6, j = (ch >> 3) & 7, e = ch & 7;
+    const float v = tp < 9 ? w_dw[i] * (scale_dw ? scale_dw[ch] : 1.f) : (shift_dw ? shift_dw[ch] : 0.f);
+    g_dw[(tp * p.nkb + kb) * 64 + (e >> 2) * 32 + j * 4 + (e & 3)] = v;
   }
-  for (int i = threadIdx.x; i < p.c; i += blockDim.x) g_dw[9 * p.c + i] = shift_dw ? shift_dw[i] : 0.f;
   for (int i = threadIdx.x; i < p.nout; i += blockDim.x) {
     g_aff[i] = scale_pw ? scale_pw[i] : 1.f;
     g_aff[p.nout + i] = shift_pw ? shift_pw[i] : 0.f;
@@ -263,16 +266,16 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
     for (int j = 0; j < n_my; ++j) {
       for (int kb = 0; kb < p.nkb; ++kb) {
         // this thread's taps (BatchNorm scale folded in) and shift for channels [kb*64 + j8*8, +8)
-        const int cbase = kb * 64 + j8 * 8;
         float2 wt[9][4], shf[4];
+        const uint32_t wbase = s_dw + (uint32_t)(kb * 64 + j8 * 4) * 4;
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
-          const float4 lo4 = lds128(s_dw + (uint32_t)(tp * p.c + cbase) * 4), hi4 = lds128(s_dw + (uint32_t)(tp * p.c + cbase + 4) * 4);
+          const float4 lo4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64) * 4), hi4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64 + 32) * 4);
           wt[tp][0] = make_float2(lo4.x, lo4.y), wt[tp][1] = make_float2(lo4.z, lo4.w);
           wt[tp][2] = make_float2(hi4.x, hi4.y), wt[tp][3] = make_float2(hi4.z, hi4.w);
         }
         {
-          const float4 lo4 = lds128(s_dw + (uint32_t)(9 * p.c + cbase) * 4), hi4 = lds128(s_dw + (uint32_t)(9 * p.c + cbase + 4) * 4);
+          const float4 lo4 = lds128(wbase + (uint32_t)(9 * p.nkb * 64) * 4), hi4 = lds128(wbase + (uint32_t)(9 * p.nkb * 64 + 32) * 4);
           shf[0] = make_float2(lo4.x, lo4.y), shf[1] = make_float2(lo4.z, lo4.w);
           shf[2] = make_float2(hi4.x, hi4.y), shf[3] = make_float2(hi4.z, hi4.w);
         }
