@@ -122,3 +122,35 @@ def test_fused_path_declines_what_it_does_not_cover():
             before = _lib.launch_count()
             m(x)
         assert _lib.launch_count() - before == 2
+
+
+def test_fused_kernel_in_the_timed_regime_many_tiles_per_cta_two_streams():
+    """The shape bench.py times (Fast-SCNN's classifier at batch 32: 8,192 tiles, 55 per CTA, every ring slot and both
+    accumulators reused many times): equal to the two-launch path, bit-identical from launch to launch, and unchanged
+    when two streams run it concurrently (the engine's two slots do)."""
+    from rtseg_b200 import modules, ops
+    m = _randomise(modules.DSConvBNAct(128, 128, 3, 1), 311).eval().cuda()
+    xs = [_nhwc16(seeded((32, 128, 128, 256), 312 + i)) for i in range(2)]
+    with torch.no_grad():
+        ops.USE_DWPW_FUSION = False
+        try:
+            two = [m(x) for x in xs]
+        finally:
+            ops.USE_DWPW_FUSION = True
+        one = [m(x) for x in xs]
+        for a, b in zip(one, two):
+            assert rel_err(a, b) < TOL_BF16 / 2
+        for _ in range(10):
+            assert torch.equal(m(xs[0]), one[0])
+        streams = [torch.cuda.Stream() for _ in range(2)]
+        torch.cuda.synchronize()
+        outs = [[], []]
+        for _ in range(8):
+            for i, st in enumerate(streams):
+                with torch.cuda.stream(st):
+                    outs[i].append(m(xs[i]))
+        torch.cuda.synchronize()
+        for i in range(2):
+            for o in outs[i]:
+                assert torch.equal(o, one[i])
+    assert ops.tc_timeout_flag() == 0
