@@ -167,6 +167,12 @@ __device__ __forceinline__ uint32_t bf16x2_bits(float a, float b) {
   return d;
 }
 
+__device__ __forceinline__ uint32_t bf16x2_relu_bits(float a, float b) {   // {hi = bf16(max(a, 0)), lo = bf16(max(b, 0))}
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
+  return d;
+}
+
 // The bf16 rounding the labels head compares in (value in the upper 16 bits).
 __device__ __forceinline__ uint32_t bf16_hi_bits(float t) {
   uint32_t d;
@@ -510,8 +516,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           // No divergent code anywhere near tcgen05.ld (.sync.aligned needs the whole warp).
           uint32_t key[2][2] = {{0u, 0u}, {0u, 0u}};
           const bool has_hi = p.hi < 3.0e38f;
-          auto reduce = [&](auto nonneg_tag) {
+          auto reduce = [&](auto nonneg_tag, auto relu_tag) {
             constexpr bool kNonNeg = decltype(nonneg_tag)::value;
+            constexpr bool kRelu = decltype(relu_tag)::value;   // plain ReLU: the clamp rides in the key's conversion
 #pragma unroll
             for (int ci = 0; ci < kMaxMyChunks; ++ci) {
               if (ci < nchunks) {  // warp-uniform
@@ -533,9 +540,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                       if (c0 + e4 + j >= p.cout) continue;
 #pragma unroll
                       for (int px = 0; px < 2; ++px) {
-                        float t = fmax_nan(fmaf(__uint_as_float(v[px][e4 + j]), scv[j], shv[j]), p.lo);
-                        if (has_hi) t = fmin_nan(t, p.hi);
+                        float t = fmaf(__uint_as_float(v[px][e4 + j]), scv[j], shv[j]);
                         uint32_t k;
+                        if constexpr (kRelu) {
+                          // cvt.rn.relu.bf16x2: {bf16(max(logit, 0)), bf16(256 - class)} in ONE instruction (a NaN
+                          // stays a NaN and wins, as with the NaN-propagating clamp below)
+                          k = bf16x2_relu_bits(t, (float)(256 - (c0 + e4 + j)));
+                          key[px][j & 1] = max(key[px][j & 1], k);
+                          continue;
+                        }
+                        t = fmax_nan(t, p.lo);
+                        if (has_hi) t = fmin_nan(t, p.hi);
                         if constexpr (kNonNeg) {
                           // one conversion builds the whole key: {bf16(logit), bf16(256 - class)}; 256 - class is
                           // an exact, positive bf16 for all 256 classes the tensor-core path takes
@@ -554,7 +569,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
               }
             }
           };
-          if (p.lo >= 0.f) reduce(std::true_type{}); else reduce(std::false_type{});
+          if (p.lo == 0.f && !has_hi) reduce(std::true_type{}, std::true_type{});
+          else if (p.lo >= 0.f) reduce(std::true_type{}, std::false_type{});
+          else reduce(std::false_type{}, std::false_type{});
           const uint32_t k0 = max(key[0][0], key[0][1]), k1 = max(key[1][0], key[1][1]);
           // class = 256 - value of the low bf16
           const uint32_t lab2 = (uint32_t)(256 - (int)__uint_as_float(k0 << 16)) | ((uint32_t)(256 - (int)__uint_as_float(k1 << 16)) << 8);
