@@ -28,6 +28,7 @@ from torch.overrides import TorchFunctionMode
 
 from . import modules as M
 from . import nets as N
+from . import nets_dual as D
 from . import ops
 
 
@@ -137,6 +138,106 @@ def _net_lednet(m) -> Optional[int]:
     return None
 
 
+# ---- round 2: ENet (models/enet.py), BiSeNetv2 (models/bisenetv2.py), DDRNet (models/ddrnet.py) ----
+def _chk_seghead(m) -> bool:
+    return _seq(m, 2) and _is_cba(m[0]) and isinstance(m[1], nn.Conv2d)
+
+
+def _chk_enet_upsample(m) -> bool:
+    u = getattr(m, "up_conv", None)
+    if isinstance(u, nn.ConvTranspose2d):
+        return u.kernel_size == (3, 3) and u.stride == (2, 2) and u.padding == (1, 1) and u.output_padding == (1, 1) and u.bias is None
+    return _seq(u, 2) and _is_cba(u[0]) and isinstance(u[1], nn.Upsample)
+
+
+def _chk_enet_bottleneck(m) -> bool:
+    if getattr(m, "conv_type", None) not in ("regular", "downsampling", "upsampling", "dilate", "asymmetric"):
+        return False
+    last = getattr(m, "right_last_conv", None)
+    return (isinstance(getattr(m, "right_init_conv", None), nn.Sequential) and _is_cba(m.right_init_conv[0]) and _seq(last, 2)
+            and isinstance(last[0], nn.Conv2d) and isinstance(last[1], nn.Dropout) and hasattr(getattr(m, "act", None), "activation"))
+
+
+def _chk_ge(m) -> bool:
+    lb = getattr(m, "left_branch", None)
+    return (isinstance(lb, nn.Sequential) and len(lb) in (3, 4) and all(_is_cba(x) for x in lb) and hasattr(m, "stride")
+            and hasattr(getattr(m, "act", None), "activation") and (m.stride != 2 or _seq(getattr(m, "right_branch", None), 2)))
+
+
+def _chk_stemblock(m) -> bool:
+    return (_is_cba(getattr(m, "conv_init", None)) and _seq(getattr(m, "left_branch", None), 2) and _is_cba(m.left_branch[0])
+            and isinstance(getattr(m, "right_branch", None), nn.MaxPool2d) and _is_cba(getattr(m, "conv_last", None)))
+
+
+def _chk_ceb(m) -> bool:
+    return (_seq(getattr(m, "pool", None), 2) and isinstance(m.pool[0], nn.AdaptiveAvgPool2d)
+            and isinstance(m.pool[1], nn.modules.batchnorm._BatchNorm) and _is_cba(getattr(m, "conv_mid", None))
+            and isinstance(getattr(m, "conv_last", None), nn.Conv2d))
+
+
+def _chk_bga(m) -> bool:
+    return (_seq(getattr(m, "detail_high", None), 2) and _is_cba(m.detail_high[0]) and isinstance(m.detail_high[1], nn.Conv2d)
+            and _seq(getattr(m, "detail_low", None), 2) and isinstance(m.detail_low[1], nn.AvgPool2d)
+            and _seq(getattr(m, "semantic_high", None), 3) and isinstance(m.semantic_high[2], nn.Sigmoid)
+            and _seq(getattr(m, "semantic_low", None), 3) and isinstance(m.semantic_low[1], nn.Conv2d)
+            and _is_cba(getattr(m, "conv_last", None)))
+
+
+def _chk_detail(m) -> bool:
+    return _seq(m, 8) and all(_is_cba(x) for x in m)
+
+
+def _chk_semantic(m) -> bool:
+    return _has(m, "stage1to2", "stage3", "stage4", "stage5_1to4", "stage5_5") and hasattr(m, "use_aux")
+
+
+def _chk_rb(m) -> bool:
+    return (_is_cba(getattr(m, "conv1", None)) and _is_cba(getattr(m, "conv2", None)) and not hasattr(m, "conv3")
+            and hasattr(m, "downsample") and isinstance(getattr(m, "act", None), nn.Module))
+
+
+def _chk_rbb(m) -> bool:
+    return all(_is_cba(getattr(m, k, None)) for k in ("conv1", "conv2", "conv3")) and hasattr(m, "downsample") \
+        and hasattr(getattr(m, "act", None), "activation")
+
+
+def _chk_bfusion(m) -> bool:
+    return _is_cba(getattr(m, "conv_low", None)) and _is_cba(getattr(m, "conv_high", None)) and hasattr(getattr(m, "act", None), "activation")
+
+
+def _chk_dappm(m) -> bool:
+    return (all(_is_cba(getattr(m, f"conv{i}", None)) for i in range(6)) and _is_cba(getattr(m, "conv_last", None))
+            and all(_seq(getattr(m, f"pool{i}", None), 2) and isinstance(getattr(m, f"pool{i}")[1], nn.Conv2d) for i in range(2, 6)))
+
+
+def _chk_stage4(m) -> bool:
+    return _has(m, "low_conv1", "high_conv1", "bilateral_fusion1") and hasattr(m, "extra_conv")
+
+
+def _chk_stage5(m) -> bool:
+    return _has(m, "low_conv1", "high_conv1", "bilateral_fusion", "low_conv2", "high_conv2", "dappm")
+
+
+def _net_enet(m) -> Optional[int]:
+    if _has(m, "initial", "bottleneck1", "bottleneck2", "bottleneck3", "bottleneck4", "bottleneck5", "fullconv") \
+            and _chk_enet_upsample(m.fullconv):
+        u = m.fullconv.up_conv
+        return u.out_channels if isinstance(u, nn.ConvTranspose2d) else u[0][0].out_channels
+    return None
+
+
+def _net_bisenetv2(m) -> Optional[int]:
+    if _has(m, "detail_branch", "semantic_branch", "bga_layer", "seg_head") and _chk_seghead(m.seg_head):
+        return m.seg_head[1].out_channels
+    return None
+
+
+def _net_ddrnet(m) -> Optional[int]:
+    if _has(m, "conv1", "conv2", "conv3", "conv4", "conv5", "seg_head") and _chk_seghead(m.seg_head) and _is_cba(m.conv1):
+        return m.seg_head[1].out_channels
+    return None
+
+
 # class name -> (fused class, structure check)
 _BLOCKS: Dict[str, Tuple[type, Callable]] = {
     "ConvBNAct": (M.ConvBNAct, _is_cba),
@@ -154,14 +255,31 @@ _BLOCKS: Dict[str, Tuple[type, Callable]] = {
     "DABModule": (N.DABModule, _chk_dab),
     "SSnbtUnit": (N.SSnbtUnit, _chk_ssnbt),
     "AttentionPyramidNetwork": (N.AttentionPyramidNetwork, _chk_apn),
+    "SegHead": (M.SegHead, _chk_seghead),
+    "Upsample": (N.Upsample, _chk_enet_upsample),
+    "Bottleneck": (N.Bottleneck, _chk_enet_bottleneck),
+    "GatherExpansionLayer": (D.GatherExpansionLayer, _chk_ge),
+    "StemBlock": (D.StemBlock, _chk_stemblock),
+    "ContextEmbeddingBlock": (D.ContextEmbeddingBlock, _chk_ceb),
+    "BilateralGuidedAggregationLayer": (D.BilateralGuidedAggregationLayer, _chk_bga),
+    "DetailBranch": (D.DetailBranch, _chk_detail),
+    "SemanticBranch": (D.SemanticBranch, _chk_semantic),
+    "RB": (D.RB, _chk_rb),
+    "RBB": (D.RBB, _chk_rbb),
+    "BilateralFusion": (D.BilateralFusion, _chk_bfusion),
+    "DAPPM": (D.DAPPM, _chk_dappm),
+    "Stage4": (D.Stage4, _chk_stage4),
+    "Stage5": (D.Stage5, _chk_stage5),
 }
 _NETS: Dict[str, Tuple[type, Callable]] = {
     "ERFNet": (N.ERFNet, _net_erfnet), "FastSCNN": (N.FastSCNN, _net_fastscnn),
     "DABNet": (N.DABNet, _net_dabnet), "LEDNet": (N.LEDNet, _net_lednet),
+    "ENet": (N.ENet, _net_enet), "BiSeNetv2": (D.BiSeNetv2, _net_bisenetv2), "DDRNet": (D.DDRNet, _net_ddrnet),
 }
 
 
-_BARE_CONV_OWNERS = (N.NonBt1DBlock, N.FeatureFusionModule, M.PyramidPoolingModule, N.SSnbtUnit, N.DABNet)
+_BARE_CONV_OWNERS = (N.NonBt1DBlock, N.FeatureFusionModule, M.PyramidPoolingModule, N.SSnbtUnit, N.DABNet, M.SegHead, N.Bottleneck,
+                     D.ContextEmbeddingBlock, D.BilateralGuidedAggregationLayer, D.DAPPM)
 
 
 def convert(model: nn.Module, verbose: bool = False) -> nn.Module:

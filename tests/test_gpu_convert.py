@@ -102,3 +102,29 @@ def test_fused_head_mode_defers_the_final_interpolate():
         assert not isinstance(full, rtseg_b200.DeferredLogits) and rel_err(full, ref) < TOL_FP32
         assert rel_err(vals, ref.max(1)[0]) < TOL_FP32
         assert torch.equal(rtseg_b200.predict_labels(m, x.cuda()), labels)
+
+
+@pytest.mark.parametrize("name,hw", [("enet", (64, 96)), ("bisenetv2", (64, 128)), ("ddrnet", (64, 128))])
+def test_convert_of_the_round2_nets_runs_the_fused_forward(name, hw):
+    """A net in the reference's attribute layout (same-named stand-in classes, bare nn.Conv2d) after convert(): the same
+    class map and logits as the fused net built directly, bit for bit, and no cuDNN / ATen convolution, pooling, cat or
+    interpolation kernel in the profile."""
+    import rtseg_b200
+    from rtseg_b200 import nets
+    from tests.test_host_logic import _defused
+    sd = ref_nets.make_state(load_specs()[name]["spec"], 3, True)
+    kw = {} if name == "enet" else {"use_aux": False}
+    fused = nets.MODEL_HUB[name](num_class=19, **kw)
+    fused.load_state_dict(sd, strict=True)
+    m = rtseg_b200.convert(_defused(fused)).eval().cuda()
+    fused = fused.eval().cuda()
+    x = ref_nets.make_input(4, 2, *hw).cuda()
+    with torch.no_grad():
+        want = fused(x)
+        m(x)
+        got, names = _kernels(lambda: m(x))
+    assert torch.equal(got, want)
+    bad = [n for n in names if any(f in n.lower() for f in FORBIDDEN) and "rtseg" not in n.lower()]
+    assert not bad, bad[:5]
+    with torch.no_grad():
+        assert torch.equal(m.predict(x), fused.predict(x))

@@ -182,6 +182,60 @@ def test_convert_reclasses_reference_layout_in_place():
     assert isinstance(m.feature_fusion.higher_res_conv, modules.Conv2d)
 
 
+def _defused(model):
+    """A copy of a fused net whose block / net classes are same-named stand-ins from outside rtseg_b200 (no forward of
+    ours), and whose bare convolutions are plain nn.Conv2d: the attribute layout the reference's model files produce."""
+    import copy
+    import sys
+    import torch.nn as nn
+    import rtseg_b200
+    from rtseg_b200 import modules
+    conv = sys.modules[rtseg_b200.convert.__module__]
+    leaves = (modules.ConvBNAct, modules.DWConvBNAct, modules.PWConvBNAct, modules.DSConvBNAct, modules.DeConvBNAct, modules.Activation)
+    m = copy.deepcopy(model)
+    for mod in m.modules():
+        cls = type(mod)
+        if cls is modules.Conv2d:
+            mod.__class__ = nn.Conv2d
+        elif cls.__module__.startswith("rtseg_b200") and not isinstance(mod, leaves) and (cls.__name__ in conv._BLOCKS or cls.__name__ in conv._NETS):
+            mod.__class__ = type(cls.__name__, (nn.Sequential if isinstance(mod, nn.Sequential) else nn.Module,), {})
+    return m
+
+
+def test_convert_reclasses_the_round2_nets_from_their_attribute_layout():
+    """ENet / BiSeNetv2 / DDRNet (reference models/enet.py, bisenetv2.py, ddrnet.py): every block and the net itself come
+    back as the fused classes, same tensors, same keys."""
+    import rtseg_b200
+    from rtseg_b200 import nets
+    for name in ("enet", "bisenetv2", "ddrnet"):
+        fused = nets.MODEL_HUB[name](num_class=19)
+        m = _defused(fused)
+        assert not type(m).__module__.startswith("rtseg_b200")   # (pure containers — Stage2, BottleNeck1 ... — keep their class)
+        before = {k: v.data_ptr() for k, v in m.state_dict().items()}
+        rtseg_b200.convert(m)
+        assert [type(x) for x in m.modules()] == [type(x) for x in fused.modules()]
+        assert {k: v.data_ptr() for k, v in m.state_dict().items()} == before and m.num_class == 19
+        assert rtseg_b200.convert(m)._rtseg_converted == {}
+
+
+def test_convert_on_the_real_reference_models():
+    """Build container only: the reference's OWN BiSeNetv2 / DDRNet / ENet objects (its classes, its leaf modules) are
+    re-classed in place; what stays a reference class is a pure container whose forward only calls its children."""
+    import pytest
+    import rtseg_b200
+    from oracle import ref_import
+    from rtseg_b200 import nets
+    if not ref_import.available():
+        pytest.skip("needs /root/reference")
+    for name in ("ddrnet", "bisenetv2", "enet"):
+        m = ref_import.reference_model(name, 19)
+        keys = list(m.state_dict().keys())
+        rtseg_b200.convert(m)
+        assert type(m) is nets.MODEL_HUB[name] and list(m.state_dict().keys()) == keys
+        left = {type(x).__name__ for x in m.modules() if not type(x).__module__.startswith(("torch", "rtseg_b200"))}
+        assert left <= {"Stage2", "Stage3", "BottleNeck1", "BottleNeck23", "BottleNeck45"}, left
+
+
 def test_convert_leaves_lookalike_classes_alone():
     """A class that only shares a NAME with a known block (other model files of the reference define their own
     InitialBlock / InvertedResidual variants) must keep its forward."""
