@@ -332,6 +332,88 @@ __global__ void __launch_bounds__(256) dw_mult_kernel(DwParams p, const T *__res
   Vec16<T>::store(y + pix * p.y_ct + p.y_co + c0, ov);
 }
 
+// ---- channel multiplier, bf16, 3x3: one thread = ONE input channel and its M output channels, PX pixels of a row ----
+// With the taps of its M filters (9 M floats, BatchNorm scale folded in) in registers for the whole walk, an output
+// pixel costs 3 new input loads (a 3 x 3 window sliding along the row), 9 M FMAs and M / 2 four-byte stores — no
+// per-tap weight loads and no input selects (dw_mult_kernel spends two thirds of its instructions on those).  Lanes
+// are neighbouring input channels, so a warp stores 32 M contiguous bf16 per pixel.
+template <int M, int S, int PX, int MODE>
+__global__ void __launch_bounds__(128) dw_chan_kernel(DwParams p, const __nv_bfloat16 *__restrict__ x,
+                                                      const float *__restrict__ wgt, Epilogue ep, __nv_bfloat16 *__restrict__ y) {
+  const int wq_n = (p.wo + PX - 1) / PX;
+  const int64_t total = (int64_t)p.n * p.ho * wq_n * p.c;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int ci = (int)(tid % p.c);
+  int64_t r = tid / p.c;
+  const int wq = (int)(r % wq_n);
+  r /= wq_n;
+  const int ho = (int)(r % p.ho);
+  const int n = (int)(r / p.ho);
+  const int co0 = ci * M;
+  float w[9][M], sh[M], sl[M];
+#pragma unroll
+  for (int j = 0; j < M; ++j) {
+    const float sc = ep.scale ? __ldg(ep.scale + co0 + j) : 1.f;
+    sh[j] = ep.shift ? __ldg(ep.shift + co0 + j) : 0.f;
+    sl[j] = (ep.slope && ep.act == RTSEG_ACT_PRELU) ? __ldg(ep.slope + co0 + j) : 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) w[t][j] = __ldg(wgt + (int64_t)t * p.cout + co0 + j) * sc;
+  }
+  const __nv_bfloat16 *xn = x + (int64_t)n * p.h * p.w * p.x_ct + p.x_co + ci;
+  const int hi0 = ho * S - p.pad_h;
+  const __nv_bfloat16 *row[3];
+  bool rok[3];
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    rok[ky] = hi0 + ky >= 0 && hi0 + ky < p.h;
+    row[ky] = xn + (int64_t)(rok[ky] ? hi0 + ky : 0) * p.w * p.x_ct;
+  }
+  auto ld = [&](int ky, int wi) -> float {
+    return (rok[ky] && wi >= 0 && wi < p.w) ? __bfloat162float(row[ky][(int64_t)wi * p.x_ct]) : 0.f;
+  };
+  const int wo0 = wq * PX;
+  float win[3][3];   // win[ky][kx] for the current output pixel
+  int wi = wo0 * S - p.pad_w;
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    win[ky][0] = ld(ky, wi), win[ky][1] = ld(ky, wi + 1);
+  }
+  __nv_bfloat16 *yp = y + (((int64_t)n * p.ho + ho) * p.wo + wo0) * p.y_ct + p.y_co + co0;
+#pragma unroll
+  for (int i = 0; i < PX; ++i) {
+    if (wo0 + i >= p.wo) break;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) win[ky][2] = ld(ky, wi + 2);
+    float acc[M];
+#pragma unroll
+    for (int j = 0; j < M; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx)
+#pragma unroll
+        for (int j = 0; j < M; ++j) acc[j] = fmaf(win[ky][kx], w[ky * 3 + kx][j], acc[j]);
+    uint32_t *out = reinterpret_cast<uint32_t *>(yp + (int64_t)i * p.y_ct);
+#pragma unroll
+    for (int j = 0; j < M; j += 2) {
+      const float a = epi_elem<MODE>(acc[j], 0.f, 1.f, sh[j], sl[j], ep), b = epi_elem<MODE>(acc[j + 1], 0.f, 1.f, sh[j + 1], sl[j + 1], ep);
+      const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+      out[j >> 1] = *reinterpret_cast<const uint32_t *>(&h);
+    }
+    // slide the window: stride 1 keeps two columns, stride 2 one
+    if (S == 1) {
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) win[ky][0] = win[ky][1], win[ky][1] = win[ky][2];
+      wi += 1;
+    } else {
+      wi += 2;
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) win[ky][0] = win[ky][2], win[ky][1] = ld(ky, wi + 1);
+    }
+  }
+}
+
 // ---- scalar fallback: channel multiplier, odd channel counts, unaligned slices ---
 template <typename T>
 __global__ void __launch_bounds__(256) dw_scalar_kernel(DwParams p, const T *__restrict__ x,
@@ -389,6 +471,26 @@ static int launch_dw(const rtseg_conv_desc *d, const void *x_, const float *w, c
   bool mult_ok = aligned && p.mult >= 2 && d->cout % V == 0 && d->y_ctotal % V == 0 && d->y_coff % V == 0 &&
                  (d->res_mode == RTSEG_RES_NONE || (d->r_ctotal % V == 0 && d->r_coff % V == 0));
   for (int c0 = 0; mult_ok && c0 < d->cout; c0 += V) mult_ok = (c0 % p.mult) + V - 1 < 2 * p.mult;
+  // bf16 3x3 with multiplier 6 (BiSeNetv2's gather-expansion layers), no residual: one thread per input channel
+  static const int chan_knob = getenv("RTSEG_DW_CHAN") ? atoi(getenv("RTSEG_DW_CHAN")) : 1;
+  if (chan_knob && sizeof(T) == 2 && p.mult == 6 && d->kh == 3 && d->kw == 3 && d->dil == 1 && (d->stride == 1 || d->stride == 2) &&
+      d->res_mode == RTSEG_RES_NONE && d->y_ctotal % 2 == 0 && d->y_coff % 2 == 0 && reinterpret_cast<uintptr_t>(y) % 4 == 0) {
+    constexpr int PX = 8;
+    const int64_t total = (int64_t)p.n * p.ho * cdiv(p.wo, PX) * p.c;
+    const unsigned grid = (unsigned)cdiv(total, 128);
+    auto xb = reinterpret_cast<const __nv_bfloat16 *>(x);
+    auto yb = reinterpret_cast<__nv_bfloat16 *>(y);
+#define RTSEG_DW_CHAN(S_)                                                                   \
+    do {                                                                                      \
+      if (ep.mode == 0) dw_chan_kernel<6, S_, PX, 0><<<grid, 128, 0, st>>>(p, xb, w, ep, yb);      \
+      else if (ep.mode == 1) dw_chan_kernel<6, S_, PX, 1><<<grid, 128, 0, st>>>(p, xb, w, ep, yb); \
+      else dw_chan_kernel<6, S_, PX, 2><<<grid, 128, 0, st>>>(p, xb, w, ep, yb);                   \
+    } while (0)
+    if (d->stride == 1) RTSEG_DW_CHAN(1); else RTSEG_DW_CHAN(2);
+#undef RTSEG_DW_CHAN
+    RTSEG_LAUNCH_CHECK("dw_chan_kernel");
+    return RTSEG_OK;
+  }
   if (mult_ok) {
     const int64_t total = (int64_t)p.n * p.ho * p.wo * (d->cout / V);
     const unsigned grid = (unsigned)cdiv(total, threads);
