@@ -845,7 +845,8 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     H, W = hw_of(workload)
     evaluate = workload in EVAL_WORKLOADS
     met = rtseg_b200.SegMetrics(NUM_CLASS, 255).to("cuda") if evaluate else None
-    eng = rtseg_b200.InferenceEngine(model, batch=batch, height=H, width=W, use_graph=True, slots=2,
+    n_slots = int(os.environ.get("RTSEG_BENCH_SLOTS", "3"))   # copy / compute slots of the end-to-end pipeline
+    eng = rtseg_b200.InferenceEngine(model, batch=batch, height=H, width=W, use_graph=True, slots=n_slots,
                                      in_dtype=torch.uint8 if u8 else torch.float32,
                                      confmat=met.confmat if evaluate else None)
 
@@ -921,8 +922,8 @@ def run_inference(workload, batch, args, rank, local_rank, world):
         if not (eval_check["confmat_exact_from_kernel_labels"] and eval_check["timed_matrix_is_steps_x_one_pass"]):
             raise SystemExit(f"bench.py: confusion-matrix check failed: {json.dumps(eval_check)}")
         met.reset()
-    for i in range(2):
-        eng(host_in[i], host_masks[i])
+    for i in range(n_slots):
+        eng(host_in[i % 2], host_masks[i % 2])
     if evaluate:
         met.reset()
     barrier()
@@ -930,7 +931,7 @@ def run_inference(workload, batch, args, rank, local_rank, world):
     pending = []
     for i in range(args.steps):
         pending.append(eng.submit(host_in[i % 2], host_masks[i % 2]))
-        if len(pending) == 2:
+        if len(pending) == n_slots:
             eng.collect(pending.pop(0))
     while pending:
         eng.collect(pending.pop(0))
@@ -979,7 +980,7 @@ def run_inference(workload, batch, args, rank, local_rank, world):
                        "cuda_graph": True},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 2), "unit": "images/s", "h2d_bytes_per_step": eng.h2d_bytes(),
-                    "d2h_bytes_per_step": eng.d2h_bytes(), "pipelined_slots": 2},
+                    "d2h_bytes_per_step": eng.d2h_bytes(), "pipelined_slots": n_slots},
             "gpu_launches": int(eng.launches_per_step * args.steps + eager_launches),
             "roofline": roof,
             "cpu_baseline": cpu,
