@@ -117,7 +117,7 @@ class InferenceEngine:
         s = self.slots[i]
         with torch.no_grad(), torch.cuda.stream(s.stream):
             s.x.copy_(host_images, non_blocking=True)
-            if host_masks is not None:
+            if host_masks is not None:   # int64 as the reference's dataset yields them, or uint8 as stored (widened on the device)
                 s.target.copy_(host_masks, non_blocking=True)
             if s.graph is not None:
                 s.graph.replay()
