@@ -338,9 +338,11 @@ int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t p
  * `DSConvBNAct` (models/modules.py:36-42), the depthwise + projection tail of `InvertedResidual`
  * (models/fastscnn.py:113-121) and FeatureFusionModule's low-resolution branch (:80-92): the depthwise output
  * (for InvertedResidual the 6x-expanded tensor) never reaches HBM — CUDA cores write it as the bf16 A tile of the
- * pointwise convolution's tcgen05.mma.  dw: the depthwise op (3x3, stride 1, padding 1, multiplier 1, channels a
- * multiple of 64, x slice, act none / relu / relu6); pw: the 1x1 op (cout 64 or 128, y slice, residual slice and mode,
- * act / act2).  w_dw: fp32 [3][3][c]; w_pw_bf16: [cout][c] K-major.  bf16 NHWC only. */
+ * pointwise convolution's tcgen05.mma.  dw: the depthwise op (3x3, padding 1, multiplier 1, x slice, act none / relu /
+ * relu6); pw: the 1x1 op on the depthwise op's output grid (y slice, residual slice and mode, act / act2).  Two shapes:
+ * stride 1 with channels a multiple of 64 (<= 512) and 64 / 128 outputs (residual PRE / POST allowed); stride 2 on an
+ * even-sized input with channels and outputs multiples of 16 (<= 64), no residual (Fast-SCNN's learning-to-downsample
+ * pairs, models/fastscnn.py:38-40).  w_dw: fp32 [3][3][c]; w_pw_bf16: [cout][c] K-major.  bf16 NHWC only. */
 int rtseg_dwpw_tc_supported(const rtseg_conv_desc *dw, const rtseg_conv_desc *pw);
 int rtseg_dwpw_tc(const rtseg_conv_desc *dw, const void *x, const float *w_dw, const float *scale_dw, const float *shift_dw,
                   const rtseg_conv_desc *pw, const void *w_pw_bf16, const float *scale_pw, const float *shift_pw,

@@ -448,8 +448,9 @@ USE_DWPW_FUSION = True   # module-level switch (tests / A-B runs): depthwise 3x3
 def _dwpw_descs(fdw: Folded, fpw: Folded, x: torch.Tensor, x_coff: int, y_ct: int, y_coff: int, res_mode: int, r_ct: int,
                 r_coff: int, act2: int):
     n, x_ct, h, w = x.shape
+    ho, wo = out_hw(fdw, h, w)
     ddw = _desc(fdw, n, h, w, BF16, x_ct, x_coff, fdw.cout, 0)
-    dpw = _desc(fpw, n, h, w, BF16, fdw.cout, 0, y_ct, y_coff, res_mode, r_ct, r_coff, act2)
+    dpw = _desc(fpw, n, ho, wo, BF16, fdw.cout, 0, y_ct, y_coff, res_mode, r_ct, r_coff, act2)
     return ddw, dpw
 
 
@@ -474,7 +475,8 @@ def dwpw(fdw: Folded, fpw: Folded, x: torch.Tensor, res: Optional[torch.Tensor] 
     models/fastscnn.py:80-92, 113-121): the depthwise output stays in shared memory as the pointwise MMA's A tile."""
     _require_cuda(x, "dwpw")
     _no_tape(x, "dwpw")
-    n, _, h, w = x.shape
+    n = x.shape[0]
+    h, w = out_hw(fdw, x.shape[2], x.shape[3])      # the pointwise op's grid (stride-2 depthwise: half the input)
     if out is None:
         out = empty_nhwc(n, fpw.cout, h, w, x.dtype, x.device)
     elif not is_nhwc(out) or out.dtype != x.dtype or tuple(out.shape[2:]) != (h, w) or out.shape[0] != n:

@@ -112,9 +112,24 @@ def test_feature_fusion_lower_branch_fused(shape):
     assert rel_err(one, _emulated(ref_fn)) < TOL_BF16
 
 
+@pytest.mark.parametrize("shape", [(2, 16, 32), (2, 34, 50), (1, 8, 16), (3, 64, 96)])
+@pytest.mark.parametrize("cin,cout,act", [(32, 48, "relu"), (48, 64, "relu"), (16, 16, "relu6"), (64, 32, "none")])
+def test_ds_conv_stride2_fused_matches_oracle_and_two_launch_path(cin, cout, act, shape):
+    """The stride-2 narrow-layer variant: Fast-SCNN's learning-to-downsample pairs (reference models/fastscnn.py:38-40)."""
+    from rtseg_b200 import modules
+    n, h, w = shape
+    m = _randomise(modules.DSConvBNAct(cin, cout, 3, 2, act_type=act), 320)
+    x = seeded((n, cin, h, w), 321)
+    xq = x.to(torch.bfloat16).float()
+    ref = _emulated(lambda: B.ds_conv_bn_act(xq, _sd(m), "m.", 3, 2, 1, act))
+    one, two, launches = _both(m, _nhwc16(x))
+    assert launches == 1
+    assert one.shape == ref.shape and rel_err(one, ref) < TOL_BF16 and rel_err(one, two) < TOL_BF16 / 2
+
+
 def test_fused_path_declines_what_it_does_not_cover():
     from rtseg_b200 import _lib, modules
-    for args in ((32, 48, 3, 2), (48, 64, 3, 2), (128, 128, 3, 1, 2), (128, 19, 3, 1)):   # stride 2, dilation 2, 19 outputs
+    for args in ((32, 48, 3, 2, 2), (384, 64, 3, 2), (128, 128, 3, 1, 2), (128, 19, 3, 1)):   # dilation 2, wide stride 2, 19 outputs
         m = _randomise(modules.DSConvBNAct(*args), 309).eval().cuda()
         x = _nhwc16(seeded((1, args[0], 16, 24), 310))
         with torch.no_grad():
