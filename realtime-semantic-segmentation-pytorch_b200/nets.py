@@ -326,7 +326,10 @@ class FastSCNN(nn.Module):
         x = ops.image_view(x)
         if self.classifier[2][1].training:
             from . import train
-            return train.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
+            # the 19-class layer runs with 32 outputs (zero weights for the pad), the x8 resize and its adjoint work on
+            # whole 16-byte channel vectors of that buffer, and the loss reads the first 19 channels in place
+            z = train.conv_bn_act_aligned(self.classifier[2], self._features(x), keep_padding=True)
+            return train.first_channels(train.upsample_bilinear(z, x.shape[2:], True), self.num_class)
         return ops.upsample_bilinear(self.lowres_logits(x), x.shape[2:], True)
 
     def predict(self, x, target: Optional[torch.Tensor] = None, confmat: Optional[torch.Tensor] = None,

@@ -543,7 +543,7 @@ class _PaddedBN:
                 self.bn.running_var.copy_(self.running_var[:c])
 
 
-def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor, pad_input: bool = False) -> torch.Tensor:
+def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor, pad_input: bool = False, keep_padding: bool = False) -> torch.Tensor:
     """conv_bn_act for an output channel count that is not a multiple of 16 (the 19-class logits layer) on bf16
     activations: the layer is run as if it had ceil16(cout) outputs — zero weights, BatchNorm weight 1 / bias 0 for the
     extra channels — so that forward, data gradient, weight gradient and the BatchNorm passes all take the aligned
@@ -571,4 +571,11 @@ def conv_bn_act_aligned(seq: nn.Module, x: torch.Tensor, pad_input: bool = False
     pbn = _PaddedBN(bn, pad)
     z = _BNActFn.apply(y, None, pbn.weight, pbn.bias, _prelu_weight(act), pbn, act)
     pbn.commit()
-    return _FirstChannelsFn.apply(z, cout)
+    # keep_padding: the caller goes on in the padded geometry (e.g. a vectorised resize of the 32-channel logits buffer)
+    # and takes the first cout channels itself with first_channels()
+    return z if keep_padding else _FirstChannelsFn.apply(z, cout)
+
+
+def first_channels(z: torch.Tensor, c: int) -> torch.Tensor:
+    """z[:, :c] of a channel-padded NHWC tensor as a view whose gradient comes back in the padded geometry."""
+    return z if z.shape[1] == c else _FirstChannelsFn.apply(z, c)

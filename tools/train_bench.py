@@ -21,12 +21,12 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 
-def build(batch, size, fp32, rank, local, world):
+def build(batch, size, fp32, rank, local, world, model_name="erfnet"):
     import rtseg_b200  # noqa: F401
     from rtseg_b200 import loss as rloss
     from rtseg_b200 import nets
     torch.manual_seed(1)
-    model = nets.ERFNet(num_class=19).cuda().train()
+    model = nets.MODEL_HUB[model_name](num_class=19).cuda().train()   # erfnet | fastscnn | dabnet | enet train on this path
     if not fp32:
         model.set_act_dtype(torch.bfloat16)
     if world > 1:
@@ -86,7 +86,7 @@ def make_step(model, crit, opt, x, y, graph, world):
     return replay
 
 
-def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True):
+def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True, model_name="erfnet"):
     """Times the step; returns a dict (rank 0) with device-timed and end-to-end images/s.  Call under torchrun for N > 1."""
     rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(local)
@@ -97,7 +97,7 @@ def run(batch=8, size=1024, steps=5, warmup=2, fp32=False, graph=True):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         own_pg = True
     from rtseg_b200 import _lib
-    model, crit, opt, x, y = build(batch, size, fp32, rank, local, world)
+    model, crit, opt, x, y = build(batch, size, fp32, rank, local, world, model_name)
     l0 = _lib.launch_count()
     step = make_step(model, crit, opt, x, y, graph, world)
     for _ in range(max(1, warmup)):
@@ -150,18 +150,19 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--fp32", action="store_true")
+    ap.add_argument("--model", default="erfnet", choices=["erfnet", "fastscnn", "dabnet", "enet"])
     ap.add_argument("--graph", action="store_true", help="capture the whole step in one CUDA graph (1 GPU)")
     ap.add_argument("--profile", action="store_true")
     args = ap.parse_args()
-    r = run(args.batch, args.size, args.steps, args.warmup, args.fp32, args.graph)
+    r = run(args.batch, args.size, args.steps, args.warmup, args.fp32, args.graph, args.model)
     if int(os.environ.get("RANK", 0)) == 0:
-        print(f"ERFNet train step: {r['ms_per_step']:.1f} ms, {r['images_per_s']:.1f} images/s device-timed, "
+        print(f"{args.model} train step: {r['ms_per_step']:.1f} ms, {r['images_per_s']:.1f} images/s device-timed, "
               f"{r['e2e_images_per_s']:.1f} images/s end to end ({r['world']} GPU(s), batch {r['batch']}/GPU, "
               f"{r['size']}x{r['size']}, {'fp32' if args.fp32 else 'bf16'}, graph={r['graph']}), loss {r['loss']:.4f}, "
               f"peak mem {r['peak_mem_gib']:.1f} GiB")
     if args.profile and int(os.environ.get("RANK", 0)) == 0 and not r["graph"]:
         from torch.profiler import ProfilerActivity, profile
-        model, crit, opt, x, y = build(args.batch, args.size, args.fp32, 0, 0, 1)
+        model, crit, opt, x, y = build(args.batch, args.size, args.fp32, 0, 0, 1, args.model)
         step = make_step(model, crit, opt, x, y, False, 1)
         step()
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
