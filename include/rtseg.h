@@ -362,6 +362,11 @@ int rtseg_combine_up(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, 
 int rtseg_avgpool2d(int32_t n, int32_t h, int32_t w, int32_t c, int32_t k, int32_t s, int32_t p, int32_t dtype, const void *x,
                     int32_t x_ctotal, int32_t x_coff, void *y, int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream);
 
+/* The four poolings of PyramidPoolingModule (models/modules.py:145-149: AdaptiveAvgPool2d(1), (2), (4), (6)) in one pass
+ * over the map (h, w multiples of 4); y1 / y2 / y4 / y6: dense NHWC [n][p][p][c] in `dtype`. */
+int rtseg_pyramid_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,
+                          int32_t x_coff, void *y1, void *y2, void *y4, void *y6, rtseg_stream_t stream);
+
 /* ---- training-mode pieces ---------------------------------------------
  * In training the reference's ConvBNAct is Conv2d -> BatchNorm2d(batch statistics) -> activation
  * as three autograd nodes (models/modules.py:73-85); NonBt1DBlock adds `+= x` before the last

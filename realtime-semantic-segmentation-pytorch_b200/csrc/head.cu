@@ -392,6 +392,86 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_kernel(int h, int w, int
 }
 
 
+// ---- pyramid pooling in one pass: AdaptiveAvgPool2d(1), (2), (4) and (6) of the same map ------------------------
+// PyramidPoolingModule (reference models/modules.py:145-149) pools one feature map four times; each of those launches
+// re-reads the map and the 1 x 1 one is a single long serial sum per block.  Here a block owns (image, 32 channels),
+// reads its slice once — lanes = channels, a warp walks whole rows with eight loads in flight — and adds every pixel to
+// its 4 x 4 cell (h, w multiples of 4: the 1-, 2- and 4-bin levels are exact unions of those cells) and to the up to
+// four overlapping 6 x 6 bins.  Every warp sums into its own shared-memory copy (no atomics: the result does not depend
+// on the order warps run in); the copies meet in a fixed order at the end.
+template <typename T>
+__global__ void __launch_bounds__(256) pyramid_pool_kernel(int h, int w, int c, const T *__restrict__ x, int x_ct, int x_co,
+                                                           T *__restrict__ y1, T *__restrict__ y2, T *__restrict__ y4,
+                                                           T *__restrict__ y6) {
+  extern __shared__ float pp_smem[];   // [8 warps][16 + 36 bins][32 channels]
+  const int b = blockIdx.x, c0 = blockIdx.y * 32;
+  const int lane = threadIdx.x % 32, ty = threadIdx.x / 32;
+  for (int i = threadIdx.x; i < 8 * 52 * 32; i += 256) pp_smem[i] = 0.f;
+  __syncthreads();
+  float *mine = pp_smem + ty * 52 * 32 + lane;      // bin k of this (warp, lane): mine[k * 32]
+  const int ch = c0 + lane;
+  if (ch < c) {
+    const T *xb = x + (int64_t)b * h * w * x_ct + x_co + ch;
+    const int ch4 = h / 4, cw4 = w / 4;
+    for (int yy = ty; yy < h; yy += 8) {
+      const int cy = yy / ch4;
+      int r6[2], nr = 0;                          // 6-bin rows that contain yy (adaptive bins overlap by one row)
+      for (int i = 0; i < 6; ++i)
+        if ((i * h) / 6 <= yy && yy < ((i + 1) * h + 5) / 6 && nr < 2) r6[nr++] = i;
+      const T *xr = xb + (int64_t)yy * w * x_ct;
+      int cx = 0, cx_end = cw4;                   // current 4 x 4 cell column and its end
+      int j6 = 0;                                 // first 6-bin column that can still contain xx
+      float acc = 0.f;
+      for (int x0 = 0; x0 < w; x0 += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = (x0 + u < w) ? ld_f<T>(xr + (int64_t)(x0 + u) * x_ct) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int xx = x0 + u;
+          if (xx >= w) break;
+          if (xx == cx_end) {
+            mine[(cy * 4 + cx) * 32] += acc;
+            acc = 0.f, ++cx, cx_end += cw4;
+          }
+          acc += v[u];
+          while (j6 < 5 && xx >= ((j6 + 1) * w + 5) / 6) ++j6;       // bins left of xx are done
+          for (int j = j6; j < 6 && (j * w) / 6 <= xx; ++j)             // at most two columns contain xx
+            for (int k = 0; k < nr; ++k) mine[(16 + r6[k] * 6 + j) * 32] += v[u];
+        }
+      }
+      mine[(cy * 4 + cx) * 32] += acc;
+    }
+  }
+  __syncthreads();
+  auto total = [&](int bin) {   // the eight warps' copies, in a fixed order
+    float t = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) t += pp_smem[(wv * 52 + bin) * 32 + lane];
+    return t;
+  };
+  if (ch < c) {
+    const float n16 = 1.f / (float)((h / 4) * (w / 4));
+    for (int i = ty; i < 16; i += 8) st_f<T>(y4 + ((int64_t)b * 16 + i) * c + ch, total(i) * n16);
+    for (int i = ty; i < 4; i += 8) {
+      const int qy = i / 2, qx = i % 2;
+      const float t = total((2 * qy) * 4 + 2 * qx) + total((2 * qy) * 4 + 2 * qx + 1) + total((2 * qy + 1) * 4 + 2 * qx) +
+                      total((2 * qy + 1) * 4 + 2 * qx + 1);
+      st_f<T>(y2 + ((int64_t)b * 4 + i) * c + ch, t * n16 * 0.25f);
+    }
+    if (ty == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 16; ++i) t += total(i);
+      st_f<T>(y1 + (int64_t)b * c + ch, t * n16 * (1.f / 16.f));
+    }
+    for (int i = ty; i < 36; i += 8) {
+      const int pi = i / 6, pj = i % 6;
+      const int cnt = (((pi + 1) * h + 5) / 6 - (pi * h) / 6) * (((pj + 1) * w + 5) / 6 - (pj * w) / 6);
+      st_f<T>(y6 + ((int64_t)b * 36 + i) * c + ch, total(16 + i) / (float)cnt);
+    }
+  }
+}
+
 // ------------------------------------------------- avg-pool 3x3 s2 p1, channel shuffle ----
 // F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid (reference models/dabnet.py:32-34): padding counts
 // (count_include_pad=True, the default), i.e. always divide by 9.  Input strides are explicit so that the
@@ -701,6 +781,35 @@ extern "C" int rtseg_adaptive_avgpool(int32_t n, int32_t h, int32_t w, int32_t c
   else RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
 #undef RTSEG_AAP
   RTSEG_LAUNCH_CHECK("adaptive_avgpool_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_pyramid_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ct,
+                                     int32_t x_co, void *y1, void *y2, void *y4, void *y6, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(x && y1 && y2 && y4 && y6, "NULL pointer");
+  RTSEG_REQUIRE(n > 0 && h >= 4 && w >= 4 && c > 0 && x_ct >= x_co + c && x_co >= 0, "bad extent");
+  RTSEG_REQUIRE(h % 4 == 0 && w % 4 == 0, "rtseg_pyramid_avgpool: h and w must be multiples of 4");
+  RTSEG_REQUIRE(cdiv(c, 32) <= 65535, "extent too large");
+  dim3 grid((unsigned)n, (unsigned)cdiv(c, 32));
+  cudaStream_t st = as_stream(stream);
+  constexpr size_t kSmem = 8 * 52 * 32 * sizeof(float);   // 53,248 B: above the 48 KB default
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  RTSEG_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    RTSEG_CUDA(cudaFuncSetAttribute(pyramid_pool_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    RTSEG_CUDA(cudaFuncSetAttribute(pyramid_pool_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    attr_set[dev] = true;
+  }
+  if (dtype == RTSEG_BF16)
+    pyramid_pool_kernel<__nv_bfloat16><<<grid, 256, kSmem, st>>>(h, w, c, (const __nv_bfloat16 *)x, x_ct, x_co, (__nv_bfloat16 *)y1,
+                                                                 (__nv_bfloat16 *)y2, (__nv_bfloat16 *)y4, (__nv_bfloat16 *)y6);
+  else if (dtype == RTSEG_F32)
+    pyramid_pool_kernel<float><<<grid, 256, kSmem, st>>>(h, w, c, (const float *)x, x_ct, x_co, (float *)y1, (float *)y2,
+                                                         (float *)y4, (float *)y6);
+  else
+    RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
+  RTSEG_LAUNCH_CHECK("pyramid_pool_kernel");
   return RTSEG_OK;
 }
 

@@ -322,7 +322,27 @@ class PyramidPoolingModule(nn.Module):
             setattr(self, f"stage{i}", nn.Sequential(nn.AdaptiveAvgPool2d(p), conv1x1(in_channels, hid_channels)))
         self.conv = PWConvBNAct(2 * in_channels, out_channels, act_type=act_type, bias=bias)
 
-    def forward(self, x):
+    def concat_buffer(self, like: torch.Tensor, n: int, h: int, w: int) -> torch.Tensor:
+        """The buffer the module's concat lives in: a producer may write the pass-through operand (channels [0, c)) straight
+        into it and hand it to forward(cat=...) — the copy of x into the concat then never happens."""
+        c = self.stage1[1].in_channels
+        return ops.empty_nhwc(n, c + 4 * self.stage1[1].out_channels, h, w, like.dtype, like.device)
+
+    def forward(self, x, cat=None):
+        """cat: a concat_buffer() whose first channels already hold x (then `x` is ignored)."""
+        if cat is not None:
+            c = self.stage1[1].in_channels
+            n, _, h, w = cat.shape
+            stages = [self.stage1, self.stage2, self.stage3, self.stage4]
+            hid = stages[0][1].out_channels
+            sizes = [int(st[0].output_size if isinstance(st[0].output_size, int) else st[0].output_size[0]) for st in stages]
+            if sizes == [1, 2, 4, 6] and h % 4 == 0 and w % 4 == 0:
+                pooled = ops.pyramid_avgpool(cat, 0, c)
+            else:
+                pooled = [ops.adaptive_avgpool(cat, p, 0, c) for p in sizes]
+            for i, st in enumerate(stages):
+                ops.upsample_bilinear(st[1](pooled[i]), (h, w), True, out=cat, y_coff=c + i * hid)
+            return self.conv(cat)
         x = ops.to_nhwc(x)
         n, c, h, w = x.shape
         stages = [self.stage1, self.stage2, self.stage3, self.stage4]
@@ -340,13 +360,7 @@ class PyramidPoolingModule(nn.Module):
         hid = stages[0][1].out_channels
         cat = ops.empty_nhwc(n, c + 4 * hid, h, w, x.dtype, x.device)
         ops.copy_into_slice(x, cat)  # the pass-through operand of the concat
-        for i, st in enumerate(stages):
-            p = st[0].output_size
-            p = p if isinstance(p, int) else p[0]
-            pooled = ops.adaptive_avgpool(x, int(p))
-            z = st[1](pooled)
-            ops.upsample_bilinear(z, (h, w), True, out=cat, y_coff=c + i * hid)
-        return self.conv(cat)
+        return self.forward(None, cat=cat)
 
 
 class SegHead(nn.Sequential):

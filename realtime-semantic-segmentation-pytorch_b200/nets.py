@@ -195,19 +195,21 @@ class InvertedResidual(nn.Module):
             ConvBNAct(hid, out_channels, 1, act_type="none"),
         )
 
-    def forward(self, x):
+    def forward(self, x, out=None, y_coff=0):
+        """out / y_coff (inference): write the result into a channel slice of a caller-owned buffer."""
         x = ops.to_nhwc(x)
         t = self.conv[0](x)
+        kw = {} if out is None else {"out": out, "y_coff": y_coff}
         # depthwise 3x3 + linear projection (+ x) in one launch: the 6x-expanded depthwise output never reaches HBM
         proj = None if self.conv[2][1].training else self.conv[2]._folded()
-        y = (dw_then_pw(self.conv[1], proj, t, res=x, res_mode=ops.RES_POST) if self.use_res_connect else
-             dw_then_pw(self.conv[1], proj, t))
+        y = (dw_then_pw(self.conv[1], proj, t, res=x, res_mode=ops.RES_POST, **kw) if self.use_res_connect else
+             dw_then_pw(self.conv[1], proj, t, **kw))
         if y is not None:
             return y
         t = self.conv[1](t)
         if self.use_res_connect:  # x + conv(x): the add rides in the projection's epilogue
-            return self.conv[2](t, res=x, res_mode=ops.RES_POST)
-        return self.conv[2](t)
+            return self.conv[2](t, res=x, res_mode=ops.RES_POST, **kw)
+        return self.conv[2](t, **kw)
 
 
 class LearningToDownsample(nn.Sequential):
@@ -254,7 +256,20 @@ class GlobalFeatureExtractor(nn.Module):
         self.ppm = PyramidPoolingModule(in_channels, out_channels, act_type=act_type, bias=True)
 
     def forward(self, x):
-        return self.ppm(self.bottlenecks(x))
+        if self.ppm.conv[1].training or (torch.is_grad_enabled() and isinstance(x, torch.Tensor) and x.requires_grad):
+            return self.ppm(self.bottlenecks(x))
+        # inference: the last bottleneck writes its output straight into the pyramid module's concat buffer
+        blocks = list(self.bottlenecks)
+        for blk in blocks[:-1]:
+            x = blk(x)
+        x = ops.to_nhwc(x)
+        n, _, h, w = x.shape
+        last = blocks[-1]
+        stride = last.conv[1][0].stride[0]
+        ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
+        cat = self.ppm.concat_buffer(x, n, ho, wo)
+        last(x, out=cat, y_coff=0)
+        return self.ppm(None, cat=cat)
 
 
 class FeatureFusionModule(nn.Module):

@@ -706,6 +706,19 @@ def adaptive_avgpool(x: torch.Tensor, p: int, x_coff: int = 0, c: Optional[int] 
     return out
 
 
+def pyramid_avgpool(x: torch.Tensor, x_coff: int = 0, c: Optional[int] = None):
+    """AdaptiveAvgPool2d(1), (2), (4), (6) of one NHWC map (channel slice allowed) in ONE pass — the four poolings of
+    PyramidPoolingModule (reference models/modules.py:145-149).  h and w must be multiples of 4."""
+    _require_cuda(x, "pyramid_avgpool")
+    _no_tape(x, "pyramid_avgpool")
+    n, x_ct, h, w = x.shape
+    c = c if c is not None else x_ct - x_coff
+    outs = [empty_nhwc(n, c, p, p, x.dtype, x.device) for p in (1, 2, 4, 6)]
+    _lib.check(_lib.load().rtseg_pyramid_avgpool(n, h, w, c, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
+                                                 *[o.data_ptr() for o in outs], _stream()), "rtseg_pyramid_avgpool")
+    return outs
+
+
 CITYSCAPES_COLORMAP = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (153, 153, 153),
                        (250, 170, 30), (220, 220, 0), (107, 142, 35), (152, 251, 152), (70, 130, 180), (220, 20, 60),
                        (255, 0, 0), (0, 0, 142), (0, 0, 70), (0, 60, 100), (0, 80, 100), (0, 0, 230), (119, 11, 32)]

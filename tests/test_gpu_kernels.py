@@ -576,6 +576,22 @@ def test_raw_ops_refuse_tensors_on_the_autograd_tape():
         assert ppm.eval()(x).shape == (1, 8, 8, 8)
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("c,h,w,ct,coff", [(128, 32, 64, 128, 0), (128, 32, 64, 256, 0), (48, 8, 12, 64, 16), (19, 4, 4, 19, 0), (64, 16, 20, 64, 0)])
+def test_pyramid_avgpool_matches_four_adaptive_pools(c, h, w, ct, coff, dtype):
+    """AdaptiveAvgPool2d(1 / 2 / 4 / 6) in one pass (PyramidPoolingModule, reference models/modules.py:145-149); the
+    result is the same from launch to launch (no atomics)."""
+    from rtseg_b200 import ops
+    x = seeded((2, ct, h, w), 60).to(dtype)
+    xg = x.cuda().contiguous(memory_format=torch.channels_last)
+    outs = ops.pyramid_avgpool(xg, coff, c)
+    again = ops.pyramid_avgpool(xg, coff, c)
+    tol = 2e-6 if dtype == torch.float32 else TOL_BF16 / 4
+    for p, o, o2 in zip((1, 2, 4, 6), outs, again):
+        ref = F.adaptive_avg_pool2d(x[:, coff:coff + c].float(), p)
+        assert tuple(o.shape) == (2, c, p, p) and rel_err(o, ref) < tol and torch.equal(o, o2)
+
+
 # --------------------------------------------------- DABNet / LEDNet building blocks ----
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("shape", [(2, 3, 32, 64), (1, 3, 17, 33), (1, 8, 9, 7)])
