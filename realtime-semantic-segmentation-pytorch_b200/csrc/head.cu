@@ -68,6 +68,70 @@ __global__ void __launch_bounds__(256) bilinear_kernel(int n, int hi, int wi, in
   }
 }
 
+// Upsampling variant: a thread owns one output column x V channels and walks R consecutive output rows.  The column's
+// two source columns and weights are fixed; a source row is lerped horizontally once and reused by every output row
+// that samples it (x4: ~1.5 source rows per 4 outputs instead of 8 row loads) — same expression tree as above, so the
+// two kernels agree bit for bit.
+template <typename T, int V, int R>
+__global__ void __launch_bounds__(256) bilinear_rows_kernel(int n, int hi, int wi, int c, int ho, int wo, int align, float sy,
+                                                            float sx, const T *__restrict__ x, int x_ct, int x_co,
+                                                            T *__restrict__ y, int y_ct, int y_co) {
+  const int cv_n = c / V;
+  const int hq = (ho + R - 1) / R;
+  const int64_t total = (int64_t)n * hq * wo * cv_n;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= total) return;
+  const int c0 = (int)(tid % cv_n) * V;
+  int64_t r = tid / cv_n;
+  const int ox = (int)(r % wo);
+  r /= wo;
+  const int oyq = (int)(r % hq);
+  const int b = (int)(r / hq);
+  int x0, x1;
+  float lx0, lx1;
+  src_index(ox, sx, wi, align, x0, x1, lx0, lx1);
+  const T *xb = x + (int64_t)b * hi * wi * x_ct + x_co + c0;
+  int ya = -1, yb = -1;          // source rows held in ha / hb
+  float ha[V], hb[V];
+  auto hrow = [&](int yy, float (&h)[V]) {
+    float a[V], bq[V];
+    Vec16<T>::load(xb + ((int64_t)yy * wi + x0) * x_ct, a);
+    Vec16<T>::load(xb + ((int64_t)yy * wi + x1) * x_ct, bq);
+#pragma unroll
+    for (int e = 0; e < V; ++e) h[e] = lx0 * a[e] + lx1 * bq[e];
+  };
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    const int oy = oyq * R + i;
+    if (oy >= ho) break;
+    int y0, y1;
+    float ly0, ly1;
+    src_index(oy, sy, hi, align, y0, y1, ly0, ly1);
+    if (y0 != ya) {
+      if (y0 == yb) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) ha[e] = hb[e];
+      } else {
+        hrow(y0, ha);
+      }
+      ya = y0;
+    }
+    if (y1 != yb) {
+      if (y1 == ya) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) hb[e] = ha[e];
+      } else {
+        hrow(y1, hb);
+      }
+      yb = y1;
+    }
+    float o[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) o[e] = ly0 * ha[e] + ly1 * hb[e];
+    Vec16<T>::store(y + (((int64_t)b * ho + oy) * wo + ox) * y_ct + y_co + c0, o);
+  }
+}
+
 // ------------------------------------------------- fused upsample + argmax ----
 constexpr int kHeadThreads = 128;  // output columns per block
 constexpr int kHeadRows = 32;      // output rows per thread (x8 heads: ~4 source-row pairs, each loaded once)
@@ -614,10 +678,16 @@ extern "C" int rtseg_upsample_bilinear(int32_t n, int32_t hi, int32_t wi, int32_
                    reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
   const int64_t total = (int64_t)n * ho * wo * (vec ? c / V : c);
   const unsigned grid = (unsigned)cdiv(total, 256);
+  static const int rows_knob = getenv("RTSEG_BILINEAR_ROWS") ? atoi(getenv("RTSEG_BILINEAR_ROWS")) : 1;
+  const bool rows4 = rows_knob && vec && ho >= 2 * hi;   // upsampling: output rows share their source rows
+  const unsigned grid_rows = (unsigned)cdiv((int64_t)n * cdiv(ho, 4) * wo * (c / V), 256);
   if (dtype == RTSEG_BF16) {
     auto xs = (const __nv_bfloat16 *)x;
     auto ys = (__nv_bfloat16 *)y;
-    if (vec)
+    if (vec && rows4)
+      bilinear_rows_kernel<__nv_bfloat16, 8, 4><<<grid_rows, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys,
+                                                                           y_ct, y_co);
+    else if (vec)
       bilinear_kernel<__nv_bfloat16, 8><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
     else
       bilinear_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(n, hi, wi, c, ho, wo, align, sy, sx, xs, x_ct, x_co, ys, y_ct, y_co);
