@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
   const int total = p.n * p.ho * p.wo;  // < 2^31 (checked by the launcher)
   const int ctot = p.cconv + (p.pool ? CIN : 0);
   uint32_t phase = 0;
+  const bool relu_only = ep.lo == 0.f && ep.hi == INFINITY;
 
   // Index arithmetic is what this kernel would otherwise spend its issue slots on (the first version executed
   // ~690 instructions per pixel, 28 of them loads), hence: 32-bit pixel decomposition, element offsets of the
@@ -107,17 +108,29 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
 
   // Loads the 3x3xCIN window of this thread's pixel of `tile` (loads only: they stay in flight across whatever
   // the caller does next).  okmask: bit t set when tap t lies inside the image (0x1ff for interior pixels).
+  // Aligned rows: the tile's (image, row, tile-in-row) is carried from tile to tile (a tile advances by gridDim.x, i.e.
+  // by a fixed number of rows and tiles-in-row) instead of being divided out of the tile index every time.
+  int nx_b = 0, nx_oy = 0, nx_tx = 0, step_row = 0, step_tx = 0;
+  if (rows_aligned) {
+    const int row0 = (int)blockIdx.x / tiles_per_row;
+    nx_tx = (int)blockIdx.x - row0 * tiles_per_row;
+    nx_b = row0 / p.ho, nx_oy = row0 - nx_b * p.ho;
+    step_row = (int)gridDim.x / tiles_per_row, step_tx = (int)gridDim.x - step_row * tiles_per_row;
+  }
   auto load_window = [&](int tile, float (&v)[K], int &pixel, int &okmask) {
-    int row, ox;
+    int row, ox, b, oy;
     if (rows_aligned) {
-      row = tile / tiles_per_row;
-      ox = (tile - row * tiles_per_row) * kRows + tid;
+      b = nx_b, oy = nx_oy, ox = nx_tx * kRows + tid;
+      row = b * p.ho + oy;
+      nx_tx += step_tx, nx_oy += step_row;
+      if (nx_tx >= tiles_per_row) nx_tx -= tiles_per_row, ++nx_oy;
+      while (nx_oy >= p.ho) nx_oy -= p.ho, ++nx_b;
     } else {
       const unsigned q = (unsigned)tile * kRows + tid;
       row = (int)(q / (unsigned)p.wo);
       ox = (int)(q - (unsigned)row * (unsigned)p.wo);
+      b = row / p.ho, oy = row - b * p.ho;
     }
-    const int b = row / p.ho, oy = row - b * p.ho;
     pixel = row * p.wo + ox;
     const bool valid = tile < num_tiles && pixel < total;
     const int iy0 = oy * 2 - 1, ix0 = ox * 2 - 1;
@@ -239,6 +252,18 @@ __global__ void __launch_bounds__(kRows, 5) stem_tc_kernel(StemParams p, const T
     // 16-byte chunks; the pooled channels are the last CIN channels of the last chunk (ctot % 8 == 0)
 #pragma unroll
     for (int c8 = 0; c8 < N + 8; c8 += 8) {
+      if (MODE == 0 && relu_only && c8 < N && !(p.pool && c8 + 8 == ctot)) {
+        // plain ReLU: the clamp rides on the bf16 conversion (cvt.rn.relu), two channels per instruction
+        uint32_t pk[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = (c8 + 2 * e) < N ? c8 + 2 * e : 0;
+          pk[e] = pack_relu_bf16(fmaf(__uint_as_float(acc[c]), s_aff[0][c], s_aff[1][c]),
+                                 fmaf(__uint_as_float(acc[c + 1]), s_aff[0][c + 1], s_aff[1][c + 1]));
+        }
+        if (cur_pixel >= 0 && c8 < ctot) *reinterpret_cast<uint4 *>(yp + c8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        continue;
+      }
       float o[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
