@@ -160,11 +160,18 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
     unsigned long long *__restrict__ confmat, int vec) {
   __shared__ int hist[kMaxBins];
+  __shared__ int4 s_rows[kHeadRows];   // per output row of this block: {y0, y1, bits(ly0), bits(ly1)} (the same for every column)
   const bool do_cm = target != nullptr;
   if (do_cm) {
     for (int i = threadIdx.x; i < c * c; i += blockDim.x) hist[i] = 0;
-    __syncthreads();
   }
+  if (threadIdx.x < kHeadRows) {
+    int y0, y1;
+    float ly0, ly1;
+    src_index(min((int)(blockIdx.y * kHeadRows + threadIdx.x), ho - 1), sy, hi, align, y0, y1, ly0, ly1);
+    s_rows[threadIdx.x] = make_int4(y0, y1, __float_as_int(ly0), __float_as_int(ly1));
+  }
+  __syncthreads();
   const int ox = blockIdx.x * kHeadThreads + threadIdx.x;
   const int oy_begin = blockIdx.y * kHeadRows;
   const int b = blockIdx.z;
@@ -217,16 +224,18 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     has_nan |= !(bad <= FLT_MAX);   // NaN or +-inf somewhere in this row
   };
 
-  for (int ry = 0; ry < kHeadRows; ++ry) {
+  int64_t opix = ((int64_t)b * ho + oy_begin) * wo + ox;
+  for (int ry = 0; ry < kHeadRows; ++ry, opix += wo) {
     const int oy = oy_begin + ry;
     if (oy >= ho) break;  // uniform across the block
-    int y0, y1;
-    float ly0, ly1;
-    src_index(oy, sy, hi, align, y0, y1, ly0, ly1);
+    const int4 sr = s_rows[ry];
+    const int y0 = sr.x, y1 = sr.y;
+    const float ly0 = __int_as_float(sr.z), ly1 = __int_as_float(sr.w);
     int label = 0;
     if (col_ok) {
       if (!(y0 == ia && y1 == ib)) {
-        // new source-row pair: A <- row y0, D <- row y1 - A
+        // new source-row pair: A <- row y0, D <- row y1 - A.  (Keeping B in registers to skip the reload of A when the
+        // window moves down one row costs 19 registers: measured faster alone, slower with the confusion matrix.)
         float rowB[CMAX];
         if (y0 != ia) load_row(y0, rowA);  // (A + D would reproduce the old B only up to a rounding: reload)
         ia = y0;
@@ -259,14 +268,13 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
           if (k == 0) best = v; else argmax_step(v, k, best, label);
         }
       }
-      const int64_t opix = ((int64_t)b * ho + oy) * wo + ox;
       if (lab8) lab8[opix] = (uint8_t)label;
       if (lab64) lab64[opix] = (int64_t)label;
     }
     if (do_cm && col_ok) {
       // a thread walks one image column: consecutive rows mostly fall into the same (target, prediction) bin, so
       // the count runs in a register and reaches the shared histogram once per run, not once per pixel
-      const int64_t t = __ldg(target + ((int64_t)b * ho + oy) * wo + ox);
+      const int64_t t = __ldg(target + opix);
       if (t != (int64_t)ignore_index && t >= 0 && t < c) {
         const int bin = (int)t * c + label;
         if (bin == run_bin) {
