@@ -265,34 +265,42 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
     const bool relu1 = p.lo1 == 0.f && p.hi1 > 3.0e38f;   // warp-uniform
     for (int j = 0; j < n_my; ++j) {
       for (int kb = 0; kb < p.nkb; ++kb) {
-        // this thread's taps (BatchNorm scale folded in) and shift for channels [kb*64 + j8*8, +8)
-        float2 wt[9][4], shf[4];
+        // This thread's taps (BatchNorm scale folded in) and shift for channels [kb*64 + j8*8, +8) are read from shared
+        // memory one filter row at a time, next to that row's six input vectors: 12 loads issued back to back, then the
+        // row's 48 packed FMAs.  (All nine taps in registers — 72 of them — left no room to have loads in flight, and
+        // every input vector was consumed the moment it was requested.)
         const uint32_t wbase = s_dw + (uint32_t)(kb * 64 + j8 * 4) * 4;
-#pragma unroll
-        for (int tp = 0; tp < 9; ++tp) {
-          const float4 lo4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64) * 4), hi4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64 + 32) * 4);
-          wt[tp][0] = make_float2(lo4.x, lo4.y), wt[tp][1] = make_float2(lo4.z, lo4.w);
-          wt[tp][2] = make_float2(hi4.x, hi4.y), wt[tp][3] = make_float2(hi4.z, hi4.w);
-        }
+        float2 acc[4][4];
         {
           const float4 lo4 = lds128(wbase + (uint32_t)(9 * p.nkb * 64) * 4), hi4 = lds128(wbase + (uint32_t)(9 * p.nkb * 64 + 32) * 4);
-          shf[0] = make_float2(lo4.x, lo4.y), shf[1] = make_float2(lo4.z, lo4.w);
-          shf[2] = make_float2(hi4.x, hi4.y), shf[3] = make_float2(hi4.z, hi4.w);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            acc[i][0] = make_float2(lo4.x, lo4.y), acc[i][1] = make_float2(lo4.z, lo4.w);
+            acc[i][2] = make_float2(hi4.x, hi4.y), acc[i][3] = make_float2(hi4.z, hi4.w);
+          }
         }
-        float2 acc[4][4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int e = 0; e < 4; ++e) acc[i][e] = shf[e];
         mbar_wait(x_full + 8 * xs, xph, dead);
         const uint32_t xb = s_x + xs * kDpXStage;
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
+          float4 raw[6];
 #pragma unroll
           for (int cx = 0; cx < 6; ++cx) {
             const uint32_t pix = (uint32_t)((ty + dy) * kDpBW + tx0 + cx);            // pixel row of the box
-            const float4 raw = lds128(xb + pix * 128u + (((uint32_t)j8 ^ (pix & 7u)) << 4));
-            const uint32_t rw[4] = {__float_as_uint(raw.x), __float_as_uint(raw.y), __float_as_uint(raw.z), __float_as_uint(raw.w)};
+            raw[cx] = lds128(xb + pix * 128u + (((uint32_t)j8 ^ (pix & 7u)) << 4));
+          }
+          float2 wt[3][4];
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) {
+            const int tp = dy * 3 + dx;
+            const float4 lo4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64) * 4), hi4 = lds128(wbase + (uint32_t)(tp * p.nkb * 64 + 32) * 4);
+            wt[dx][0] = make_float2(lo4.x, lo4.y), wt[dx][1] = make_float2(lo4.z, lo4.w);
+            wt[dx][2] = make_float2(hi4.x, hi4.y), wt[dx][3] = make_float2(hi4.z, hi4.w);
+          }
+#pragma unroll
+          for (int cx = 0; cx < 6; ++cx) {
+            const uint32_t rw[4] = {__float_as_uint(raw[cx].x), __float_as_uint(raw[cx].y), __float_as_uint(raw[cx].z),
+                                    __float_as_uint(raw[cx].w)};
             float2 xv[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) xv[e] = make_float2(bf16_lo(rw[e]), bf16_hi(rw[e]));
@@ -301,7 +309,7 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
               const int dx = cx - i;                                                    // tap column for output pixel i
               if (dx >= 0 && dx < 3) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) acc[i][e] = __ffma2_rn(xv[e], wt[dy * 3 + dx][e], acc[i][e]);   // packed fp32 FMA
+                for (int e = 0; e < 4; ++e) acc[i][e] = __ffma2_rn(xv[e], wt[dx][e], acc[i][e]);   // packed fp32 FMA
               }
             }
           }
