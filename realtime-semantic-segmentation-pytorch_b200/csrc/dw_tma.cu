@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
   }
   float sc[8], sh[8], sl[8];
   load_affine<8>(ep, c0, sc, sh, sl);
+  const bool relu_only = ep.lo == 0.f && ep.hi > 3.0e38f && ep.res_mode == RTSEG_RES_NONE;   // uniform
 
   const uint32_t lane_off = (uint32_t)(tr * S * TWI + tc0 * S) * kRowBytes + (uint32_t)cv * 16;
   uint32_t stage = 0, phase = 0;
@@ -141,9 +142,18 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
     const uint32_t tile_base = s_base + stage * kStagePitch + lane_off;
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
+      // the row's NW input vectors are requested back to back (one exposed shared-memory latency per filter row; a load
+      // consumed the moment it was issued cost one per vector)
+      constexpr int kBatch = (NW + 1) / 2;   // half a row at a time: the whole row would not fit in the register budget
+      float4 raw[kBatch];
 #pragma unroll
       for (int j = 0; j < NW; ++j) {
-        const float4 rawf = lds128(tile_base + (uint32_t)(ky * TWI + j) * kRowBytes);
+        if (j % kBatch == 0) {
+#pragma unroll
+          for (int q = 0; q < kBatch; ++q)
+            if (j + q < NW) raw[q] = lds128(tile_base + (uint32_t)(ky * TWI + j + q) * kRowBytes);
+        }
+        const float4 rawf = raw[j % kBatch];
         const uint32_t w4[4] = {__float_as_uint(rawf.x), __float_as_uint(rawf.y), __float_as_uint(rawf.z),
                                 __float_as_uint(rawf.w)};
         float2 xv[4];
@@ -172,13 +182,22 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
 #pragma unroll
       for (int i = 0; i < PX; ++i) {
         if (ox0 + i < p.wo) {
-          float ov[8];
+          if (MODE == 0 && relu_only) {
+            // plain ReLU (every depthwise layer of Fast-SCNN): the clamp rides in the bf16 conversion
+            uint32_t pk[4];
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            ov[2 * v] = epi_elem<MODE>(acc[i][v].x, 0.f, sc[2 * v], sh[2 * v], sl[2 * v], ep);
-            ov[2 * v + 1] = epi_elem<MODE>(acc[i][v].y, 0.f, sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
+            for (int v = 0; v < 4; ++v)
+              pk[v] = pack_relu_bf16(fmaf(acc[i][v].x, sc[2 * v], sh[2 * v]), fmaf(acc[i][v].y, sc[2 * v + 1], sh[2 * v + 1]));
+            *reinterpret_cast<uint4 *>(yrow + (int64_t)i * p.y_ct) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          } else {
+            float ov[8];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              ov[2 * v] = epi_elem<MODE>(acc[i][v].x, 0.f, sc[2 * v], sh[2 * v], sl[2 * v], ep);
+              ov[2 * v + 1] = epi_elem<MODE>(acc[i][v].y, 0.f, sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
+            }
+            Vec16<__nv_bfloat16>::store(yrow + (int64_t)i * p.y_ct, ov);
           }
-          Vec16<__nv_bfloat16>::store(yrow + (int64_t)i * p.y_ct, ov);
         }
       }
     }
