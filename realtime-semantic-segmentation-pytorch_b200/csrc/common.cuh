@@ -193,19 +193,20 @@ __device__ __forceinline__ float epilogue_apply(float acc, float res, int c, con
 }
 
 // One output element with the per-channel affine already in registers.  MODE as in Epilogue::mode.
-template <int MODE>
+// RES = false: the caller has no residual input (the add / select per element would be wasted issue slots).
+template <int MODE, bool RES = true>
 __device__ __forceinline__ float epi_elem(float acc, float rv, float sc, float sh, float sl, const Epilogue &e) {
-  float v = e.res_mode == RTSEG_RES_PRE ? acc + rv : acc;
+  float v = (RES && e.res_mode == RTSEG_RES_PRE) ? acc + rv : acc;
   v = fmaf(v, sc, sh);
   if constexpr (MODE == 0) {
     v = fmin_nan(fmax_nan(v, e.lo), e.hi);
-    if (e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
+    if (RES && e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
   } else if constexpr (MODE == 1) {
     v = fmaf(sl, fmin_nan(v, 0.f), fmax_nan(v, 0.f));
-    if (e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
+    if (RES && e.res_mode == RTSEG_RES_POST) v = fmin_nan(fmax_nan(v + rv, e.lo2), e.hi2);
   } else {
     v = act_apply(v, e.act, e.p0, e.p1, sl);
-    if (e.res_mode == RTSEG_RES_POST) v = act_apply(v + rv, e.act2, e.p0, e.p1, sl);
+    if (RES && e.res_mode == RTSEG_RES_POST) v = act_apply(v + rv, e.act2, e.p0, e.p1, sl);
   }
   return v;
 }

@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(128) dw_chan_kernel(DwParams p, const __nv_bfl
     uint32_t *out = reinterpret_cast<uint32_t *>(yp + (int64_t)i * p.y_ct);
 #pragma unroll
     for (int j = 0; j < M; j += 2) {
-      const float a = epi_elem<MODE>(acc[j], 0.f, 1.f, sh[j], sl[j], ep), b = epi_elem<MODE>(acc[j + 1], 0.f, 1.f, sh[j + 1], sl[j + 1], ep);
+      const float a = epi_elem<MODE, false>(acc[j], 0.f, 1.f, sh[j], sl[j], ep), b = epi_elem<MODE, false>(acc[j + 1], 0.f, 1.f, sh[j + 1], sl[j + 1], ep);
       const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
       out[j >> 1] = *reinterpret_cast<const uint32_t *>(&h);
     }

@@ -193,8 +193,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_tma_kernel(const __grid_cons
             float ov[8];
 #pragma unroll
             for (int v = 0; v < 4; ++v) {
-              ov[2 * v] = epi_elem<MODE>(acc[i][v].x, 0.f, sc[2 * v], sh[2 * v], sl[2 * v], ep);
-              ov[2 * v + 1] = epi_elem<MODE>(acc[i][v].y, 0.f, sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
+              ov[2 * v] = epi_elem<MODE, false>(acc[i][v].x, 0.f, sc[2 * v], sh[2 * v], sl[2 * v], ep);
+              ov[2 * v + 1] = epi_elem<MODE, false>(acc[i][v].y, 0.f, sc[2 * v + 1], sh[2 * v + 1], sl[2 * v + 1], ep);
             }
             Vec16<__nv_bfloat16>::store(yrow + (int64_t)i * p.y_ct, ov);
           }
