@@ -197,7 +197,7 @@ __device__ __forceinline__ void tc_wait(uint32_t bar, uint32_t parity, volatile 
   else mbar_wait(bar, parity, dead);
 }
 
-template <int KB, int MODE, bool RES>
+template <int KB, int MODE, bool RES, bool DIRECT = false>
 __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps, const TcParams p,
                                                                 Epilogue ep, const __nv_bfloat16 *__restrict__ res,
                                                                 __nv_bfloat16 *__restrict__ y,
@@ -615,7 +615,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
           const int npass = p.split_out ? p.bn / p.ob : 1;
           for (int pass = 0; pass < npass; ++pass) {
           const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
-          epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
+          constexpr bool direct = DIRECT;   // no staging buffers in this plan: rows go straight to global memory
+                                            // (a template flag: as a run-time branch it slowed the staged layers down)
+          if constexpr (!direct) epi_bar_sync(2);  // the staging buffer's previous TMA store has been read out
 #pragma unroll
           for (int ci = 0; ci < kMy; ++ci) {
             if (ci < my_chunks && (!p.split_out || (int)(ck_meta[ci] >> 24) == pass)) {  // warp-uniform
@@ -666,11 +668,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 pk[(e4 >> 1) + 0] = pack_bf16(o[0], o[1]);
                 pk[(e4 >> 1) + 1] = pack_bf16(o[2], o[3]);
               }
-              // staged, swizzled exactly like the TMA store's tensor map expects (offsets hoisted)
-              sts128(buf + ck_st0[ci], pk[0], pk[1], pk[2], pk[3]);
-              sts128(buf + (ck_st0[ci] ^ 16u), pk[4], pk[5], pk[6], pk[7]);
+              if constexpr (direct) {
+                int gy, gx;
+                if (pixel((int)((ck_meta[ci] >> 16) & 0xffu), gy, gx)) {
+                  const int64_t opix = ((int64_t)img * p.oh + (gy * p.ostride + p.oy0[a])) * p.ow + (gx * p.ostride + p.ox0[a]);
+                  uint4 *yp = reinterpret_cast<uint4 *>(y + opix * p.y_ct + p.y_co + co_base + c0);
+                  yp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                  yp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+              } else {
+                // staged, swizzled exactly like the TMA store's tensor map expects (offsets hoisted)
+                sts128(buf + ck_st0[ci], pk[0], pk[1], pk[2], pk[3]);
+                sts128(buf + (ck_st0[ci] ^ 16u), pk[4], pk[5], pk[6], pk[7]);
+              }
             }
           }
+          if constexpr (direct) { ++unit; continue; }
           fence_async_smem();
           epi_bar_sync(1);  // every warp has written its part of the staging tile
           if constexpr (RES) {
@@ -702,6 +715,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         // (rolled chunk loop, out-of-line activation) — correctness first, used off the hot path.
         mbar_wait(tfull_bar + 8 * acc, acc_phase, dead);
         tc_fence_after();
+        // direct stores go out as 16-byte vectors when every 16-channel chunk is whole and 16-byte aligned
+        const bool vec_out = p.y_mode == 1 && p.cout % 16 == 0 && p.y_ct % 8 == 0 && p.y_co % 8 == 0 &&
+                             (reinterpret_cast<uintptr_t>(y) & 15) == 0;
         for (int a = 0; a < p.nacc; ++a) {
           const uint32_t buf = s_out + (p.out_bufs == 2 ? (unit & 1u) : 0u) * p.out_buf_bytes;
           if (p.y_mode == 2) epi_bar_sync(2);
@@ -746,8 +762,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                   best = vr, best_idx = cg + j;
                 }
               }
-              if (p.y_mode == 1 && valid && cg + j < p.cout)
+              if (p.y_mode == 1 && !vec_out && valid && cg + j < p.cout)
                 y[opix * p.y_ct + p.y_co + cg + j] = __float2bfloat16_rn(t);
+            }
+            if (p.y_mode == 1 && vec_out && valid && cg < p.cout) {   // the chunk's 32 bytes as two 16-byte stores
+              uint4 *yp = reinterpret_cast<uint4 *>(y + opix * p.y_ct + p.y_co + cg);
+              yp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              yp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
             }
             if (p.y_mode == 2) {
               const uint32_t box = buf + (uint32_t)(c0 / p.ob) * box_bytes;
@@ -965,14 +986,14 @@ static int encode_weight_map(CUtensorMap *m, const void *w, int cin, int rows, i
   return RTSEG_OK;
 }
 
-template <int KB, int MODE, bool RES>
+template <int KB, int MODE, bool RES, bool DIRECT = false>
 static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, const void *res,
                           void *y, uint8_t *labels, cudaStream_t st) {
   static bool attr_set[64] = {false};
   int dev = 0;
   RTSEG_CUDA(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB, MODE, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    RTSEG_CUDA(cudaFuncSetAttribute(conv_tc_kernel<KB, MODE, RES, DIRECT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kSmemBudget + 2048));
     attr_set[dev] = true;
   }
@@ -982,7 +1003,7 @@ static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &p
   const int sms = num_sms() * ctas_per_sm;
   const int gx = (int)std::min<int64_t>(p.num_m_tiles, std::max(1, sms / pl.n_tiles));
   dim3 grid((unsigned)gx, (unsigned)pl.n_tiles);
-  conv_tc_kernel<KB, MODE, RES><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
+  conv_tc_kernel<KB, MODE, RES, DIRECT><<<grid, kTcThreads, pl.smem_bytes + 1024, st>>>(
       maps, p, ep, static_cast<const __nv_bfloat16 *>(res), static_cast<__nv_bfloat16 *>(y), labels);
   RTSEG_LAUNCH_CHECK("conv_tc_kernel");
   return RTSEG_OK;
@@ -991,13 +1012,19 @@ static int launch_tc_inst(const TcMaps &maps, const TcParams &p, const TcPlan &p
 static int launch_tc(const TcMaps &maps, const TcParams &p, const TcPlan &pl, const Epilogue &ep, int mode,
                      const void *res, void *y, uint8_t *labels, cudaStream_t st) {
   // mode 3 writes two adjacent labels with one 16-bit store: the class map must be 2-byte aligned (rows are: ow even)
+  // direct (unstaged) stores stay on the fast epilogue when every 16-channel chunk is whole and 16-byte aligned
+  const bool direct_fast = p.y_mode == 1 && mode <= 1 && p.res_boxes == 0 && !pl.split_out && p.cout % 16 == 0 &&
+                           p.y_ct % 8 == 0 && p.y_co % 8 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
   if (labels != nullptr && p.y_mode == 0 && p.nacc == 4 && mode == 0 && pl.n_tiles == 1 && (p.ow & 1) == 0 &&
       reinterpret_cast<uintptr_t>(labels) % 2 == 0)
     mode = 3;
-  else if (labels != nullptr || p.y_mode != 2)
+  else if (labels != nullptr || (p.y_mode != 2 && !direct_fast))
     mode = 2;
   const bool has_res = p.res_boxes > 0;
 #define RTSEG_TC(KB_)                                                                                          \
+  if (direct_fast && mode <= 1)                                                                                \
+    return mode == 0 ? launch_tc_inst<KB_, 0, false, true>(maps, p, pl, ep, res, y, labels, st)                \
+                     : launch_tc_inst<KB_, 1, false, true>(maps, p, pl, ep, res, y, labels, st);               \
   return mode == 3   ? launch_tc_inst<KB_, 3, false>(maps, p, pl, ep, res, y, labels, st)                      \
          : mode == 2 ? launch_tc_inst<KB_, 2, false>(maps, p, pl, ep, res, y, labels, st)                      \
          : mode == 0 ? (has_res ? launch_tc_inst<KB_, 0, true>(maps, p, pl, ep, res, y, labels, st)            \
@@ -1348,7 +1375,7 @@ static int check_plan(const TcParams &p, const TcPlan &pl) {
 // Plans a forward conv: tile shape, A-sharing mode, stack depth, ring depth, epilogue mode.  `d` is the K-padded
 // descriptor.  Shared by rtseg_conv_tc and rtseg_conv_tc_plan_info so that tests can see the plan a launch would use.
 static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slope, TcPlan &pl, TcParams &p, int &share,
-                        int &mode, bool may_split = true) {
+                        int &mode, bool may_split = true, bool may_unstage = true) {
   const int cout_pad = (d->cout + 15) / 16 * 16;
   const int ntaps = d->kh * d->kw;
   p.n = d->n;
@@ -1367,6 +1394,17 @@ static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slop
                  fast_epi))
       RTSEG_FAIL(RTSEG_ERR_UNSUPPORTED, "rtseg_conv_tc: weights (%d taps x %d x %d) do not fit in shared memory", ntaps,
                  d->cin, cout_pad);
+  }
+  // Dense k x k layers whose resident weights leave no room for the output staging buffers fall back to narrow N
+  // tiles (128 -> 128 3x3: N = 32, every input box fetched four times, MMAs a quarter wide).  Without staging (the
+  // epilogue stores its rows straight to global memory, 2 * N contiguous bytes per thread) the same layer runs at
+  // N = 64 — measured 0.40 -> see DESIGN.md.  Only taken when it widens the N tile and no residual rides the ring.
+  static const int unstage_knob = getenv("RTSEG_TC_UNSTAGE") ? atoi(getenv("RTSEG_TC_UNSTAGE")) : 1;
+  if (unstage_knob && may_unstage && staged && pl.n_tiles > 1 && ntaps > 3 && d->res_mode == RTSEG_RES_NONE) {
+    TcPlan alt;
+    bool ok = plan_tc(d->cin, cout_pad, ntaps, 1, false, max_stack(p.n, p.gh, p.gw, share), false, alt, share, halo, false);
+    if (!ok) ok = plan_tc(d->cin, cout_pad, ntaps, 1, false, max_stack(p.n, p.gh, p.gw), false, alt, 0, 0, false);
+    if (ok && alt.bn > pl.bn) return plan_forward(d, false, slope, pl, p, share, mode, may_split, false);
   }
   p.oh = p.gh, p.ow = p.gw, p.ostride = 1, p.nacc = 1;
   for (int a = 0; a < kMaxAcc; ++a) p.oy0[a] = p.ox0[a] = 0;
