@@ -485,6 +485,9 @@ __global__ void __launch_bounds__(256) pyramid_pool_kernel(int h, int w, int c, 
   if (ch < c) {
     const T *xb = x + (int64_t)b * h * w * x_ct + x_co + ch;
     const int ch4 = h / 4, cw4 = w / 4;
+    int lo6[6], hi6[6];                           // adaptive 6-bin columns [lo, hi)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) lo6[j] = (j * w) / 6, hi6[j] = ((j + 1) * w + 5) / 6;
     for (int yy = ty; yy < h; yy += 8) {
       const int cy = yy / ch4;
       int r6[2], nr = 0;                          // 6-bin rows that contain yy (adaptive bins overlap by one row)
@@ -492,8 +495,10 @@ __global__ void __launch_bounds__(256) pyramid_pool_kernel(int h, int w, int c, 
         if ((i * h) / 6 <= yy && yy < ((i + 1) * h + 5) / 6 && nr < 2) r6[nr++] = i;
       const T *xr = xb + (int64_t)yy * w * x_ct;
       int cx = 0, cx_end = cw4;                   // current 4 x 4 cell column and its end
-      int j6 = 0;                                 // first 6-bin column that can still contain xx
       float acc = 0.f;
+      // the row's six (overlapping) column bins are summed in registers, pixel order kept, and reach the shared
+      // copies once per row: a shared-memory read-modify-write per pixel and bin was the whole kernel (0.10 ms)
+      float a6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       for (int x0 = 0; x0 < w; x0 += 8) {
         float v[8];
 #pragma unroll
@@ -507,12 +512,15 @@ __global__ void __launch_bounds__(256) pyramid_pool_kernel(int h, int w, int c, 
             acc = 0.f, ++cx, cx_end += cw4;
           }
           acc += v[u];
-          while (j6 < 5 && xx >= ((j6 + 1) * w + 5) / 6) ++j6;       // bins left of xx are done
-          for (int j = j6; j < 6 && (j * w) / 6 <= xx; ++j)             // at most two columns contain xx
-            for (int k = 0; k < nr; ++k) mine[(16 + r6[k] * 6 + j) * 32] += v[u];
+#pragma unroll
+          for (int j = 0; j < 6; ++j)
+            if (xx >= lo6[j] && xx < hi6[j]) a6[j] += v[u];
         }
       }
       mine[(cy * 4 + cx) * 32] += acc;
+#pragma unroll
+      for (int j = 0; j < 6; ++j)
+        for (int k = 0; k < nr; ++k) mine[(16 + r6[k] * 6 + j) * 32] += a6[j];
     }
   }
   __syncthreads();
