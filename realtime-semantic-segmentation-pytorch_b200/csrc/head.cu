@@ -154,7 +154,7 @@ __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool val
 // and infinities (inf - inf in D, inf + -inf in A + ly1*D would turn into NaNs torch does not produce) are detected
 // when a source row is loaded; such threads evaluate torch's own expression ly0*(lx0*p00 + lx1*p01) + ly1*(...)
 // straight from memory.  Padded channels hold -inf and the compare is strict, so the label never leaves [0, c).
-template <typename T, int CMAX>
+template <typename T, int CMAX, bool EXACT = false>   // EXACT: c == CMAX, no padded classes to mask
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int n, int hi, int wi, int c, int ct, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
     uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
@@ -189,9 +189,10 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
 
   // horizontally interpolated source row i, channels >= c padded so that they never win.  bf16 logits in a 16-byte
   // aligned buffer (`vec`) are read as 16-byte vectors: ceil(CMAX / 8) loads per corner pixel instead of CMAX.
+  const int row_pitch = wi * ct, off0 = x0 * ct, off1 = x1 * ct;   // elements; one image fits 31 bits (checked by the launcher)
   auto load_row = [&](int i, float(&row)[CMAX]) {
-    const T *p0 = xb + ((int64_t)i * wi + x0) * ct;
-    const T *p1 = xb + ((int64_t)i * wi + x1) * ct;
+    const T *p0 = xb + (i * row_pitch + off0);
+    const T *p1 = xb + (i * row_pitch + off1);
     float bad = 0.f;   // max |v| with NaNs kept: one compare per row instead of one per class
     if (sizeof(T) == 2 && vec) {
       constexpr int NV = (CMAX + 7) / 8;
@@ -207,8 +208,8 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
         const float a = __uint_as_float((k & 1) ? (q0[k >> 1] & 0xffff0000u) : (q0[k >> 1] << 16));
         const float bq = __uint_as_float((k & 1) ? (q1[k >> 1] & 0xffff0000u) : (q1[k >> 1] << 16));
         const float v = lx0 * a + lx1 * bq;
-        bad = fmax_nan(bad, (k < c) ? fabsf(v) : 0.f);
-        row[k] = (k < c) ? v : -INFINITY;
+        bad = fmax_nan(bad, (EXACT || k < c) ? fabsf(v) : 0.f);
+        row[k] = (EXACT || k < c) ? v : -INFINITY;
       }
     } else {
 #pragma unroll
@@ -245,7 +246,7 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
         } else {
           load_row(y1, rowB);
 #pragma unroll
-          for (int k = 0; k < CMAX; ++k) rowD[k] = (k < c) ? rowB[k] - rowA[k] : 0.f;
+          for (int k = 0; k < CMAX; ++k) rowD[k] = (EXACT || k < c) ? rowB[k] - rowA[k] : 0.f;
         }
         ib = y1;
       }
@@ -739,7 +740,7 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ct, int ho, 
   }
   if (c == 19) {  // Cityscapes: exact instantiation, no padded classes
     const int vec = sizeof(T) == 2 && ct % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && 24 <= ct;
-    upsample_argmax_kernel<T, 19><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
+    upsample_argmax_kernel<T, 19, true><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
                                                                  target, ignore, cm, vec);
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");
     return RTSEG_OK;
@@ -760,6 +761,7 @@ extern "C" int rtseg_upsample_argmax(int32_t n, int32_t hi, int32_t wi, int32_t 
   RTSEG_REQUIRE(n > 0 && hi > 0 && wi > 0 && c > 0 && ho > 0 && wo > 0, "non-positive extent");
   RTSEG_REQUIRE(x_ctotal >= c, "x_ctotal (%d) smaller than the class count (%d)", x_ctotal, c);
   RTSEG_REQUIRE(n <= 65535 && cdiv(ho, kHeadRows) <= 65535, "batch or height too large for one launch");
+  RTSEG_REQUIRE((int64_t)hi * wi * x_ctotal < INT32_MAX, "one image of logits must hold fewer than 2^31 elements");
   RTSEG_REQUIRE((target == nullptr) == (confmat == nullptr), "target and confmat must be given together");
   RTSEG_REQUIRE(labels_u8 || labels_i64 || confmat, "nothing to compute");
   cudaStream_t st = as_stream(stream);
