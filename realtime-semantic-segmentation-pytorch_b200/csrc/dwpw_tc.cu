@@ -355,7 +355,13 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
 // (2 TH + 1) x (2 TW + 1) input pixels per tile and block, a depthwise thread owns ONE output pixel x 8 channels (nine
 // 16-byte window reads), one K = 16 MMA per block; staging rows are N x 2 bytes, unswizzled.
 constexpr int kD2BH = 2 * kDpTH + 1, kD2BW = 2 * kDpTW + 1;
-constexpr uint32_t kD2XStage = ((uint32_t)kD2BH * kD2BW * 32u + 1023u) / 1024u * 1024u;
+// The input box arrives as TWO boxes, its even and its odd columns (TMA traversal stride 2 along w): a tap then reads
+// NEIGHBOURING 32-byte pixel slots for neighbouring output pixels — a quarter warp covers 128 contiguous bytes.  With
+// all 33 columns in one box the taps read every other slot and every shared load ran into a 2-way bank conflict
+// (ncu: 27 M of 80 M wavefronts, LSU data pipe 88 % busy).
+constexpr int kD2HW = kDpTW + 1;                                             // pixels per row of a half box
+constexpr uint32_t kD2Half = ((uint32_t)kD2BH * kD2HW * 32u + 127u) / 128u * 128u;
+constexpr uint32_t kD2XStage = (2 * kD2Half + 1023u) / 1024u * 1024u;   // the A tiles behind the ring stay 1 KB aligned
 constexpr int kD2MaxStages = 8;
 
 __device__ __forceinline__ uint64_t d2_desc(uint32_t addr) {   // K-major, 32-byte rows, SWIZZLE_32B, 8-row groups 256 B apart
@@ -431,8 +437,9 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_s2_tc_kernel(const __grid_
         tile_coords(j, w0, h0, img);
         for (int kb = 0; kb < p.nkb; ++kb) {
           mbar_wait_relaxed(x_empty + 8 * stage, phase ^ 1, dead);
-          mbar_expect_tx(x_full + 8 * stage, (uint32_t)kD2BH * kD2BW * 32u);
+          mbar_expect_tx(x_full + 8 * stage, 2u * (uint32_t)kD2BH * kD2HW * 32u);
           tma_load_4d(s_x + stage * kD2XStage, &maps.x, x_full + 8 * stage, p.x_coff + kb * 16, 2 * w0 - 1, 2 * h0 - 1, img);
+          tma_load_4d(s_x + stage * kD2XStage + kD2Half, &maps.x, x_full + 8 * stage, p.x_coff + kb * 16, 2 * w0, 2 * h0 - 1, img);
           if (++stage == (uint32_t)p.stages) stage = 0, phase ^= 1;
         }
       }
@@ -530,8 +537,9 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_s2_tc_kernel(const __grid_
         for (int dy = 0; dy < 3; ++dy) {
 #pragma unroll
           for (int dx = 0; dx < 3; ++dx) {
-            const uint32_t pix = (uint32_t)((2 * ty + dy) * kD2BW + 2 * tx + dx);
-            const float4 raw = lds128(xb + pix * 32u + (((uint32_t)j2 ^ ((pix >> 2) & 1u)) << 4));
+            // dx = 0 / 2: even columns tx / tx + 1; dx = 1: odd column tx
+            const uint32_t pix = (uint32_t)((2 * ty + dy) * kD2HW + tx + (dx >> 1));
+            const float4 raw = lds128(xb + (dx == 1 ? kD2Half : 0u) + pix * 32u + (uint32_t)j2 * 16u);
             const uint32_t rw[4] = {__float_as_uint(raw.x), __float_as_uint(raw.y), __float_as_uint(raw.z), __float_as_uint(raw.w)};
             const float4 wl = lds128(wbase + (uint32_t)((dy * 3 + dx) * p.c) * 4), wh = lds128(wbase + (uint32_t)((dy * 3 + dx) * p.c + 4) * 4);
             acc[0] = __ffma2_rn(make_float2(bf16_lo(rw[0]), bf16_hi(rw[0])), make_float2(wl.x, wl.y), acc[0]);
@@ -586,14 +594,15 @@ EncodeTiledFnDp dp_encode_fn() {
 }
 
 // 4-D bf16 map over channels [0, cdim) of an NHWC buffer with `ct` channels per pixel; box = 64 x bw x bh x 1, SWIZZLE_128B
+// es_w: traversal stride along w (2 = every other column of the bw-wide box: (bw + 1) / 2 pixels per row arrive)
 int dp_nhwc_map(CUtensorMap *m, const void *base, int cdim, int ct, int w, int h, int n, int bw, int bh, int bc = 64,
-                CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_128B) {
+                CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_128B, int es_w = 1) {
   EncodeTiledFnDp enc = dp_encode_fn();
   if (!enc) RTSEG_FAIL(RTSEG_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[4] = {(cuuint64_t)cdim, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
   const cuuint64_t strides[3] = {(cuuint64_t)ct * 2, (cuuint64_t)ct * w * 2, (cuuint64_t)ct * w * h * 2};
   const cuuint32_t box[4] = {(cuuint32_t)bc, (cuuint32_t)bw, (cuuint32_t)bh, 1};
-  const cuuint32_t es[4] = {1, 1, 1, 1};
+  const cuuint32_t es[4] = {1, (cuuint32_t)es_w, 1, 1};
   const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, strides, box, es,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -692,7 +701,7 @@ static int launch_dwpw_s2(const rtseg_conv_desc *dw, const void *x, const float 
   epilogue_mode(dw->act, 0, RTSEG_RES_NONE, nullptr, dw->act_p0, dw->act_p1, p.lo1, p.hi1, lo2, hi2);
   epilogue_mode(pw->act, 0, RTSEG_RES_NONE, nullptr, pw->act_p0, pw->act_p1, p.lo, p.hi, p.lo2, p.hi2);
   DpMaps maps;
-  if (int rc = dp_nhwc_map(&maps.x, x, dw->x_coff + p.c, dw->x_ctotal, dw->w, dw->h, p.n, kD2BW, kD2BH, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return rc;
+  if (int rc = dp_nhwc_map(&maps.x, x, dw->x_coff + p.c, dw->x_ctotal, dw->w, dw->h, p.n, kD2BW, kD2BH, 16, CU_TENSOR_MAP_SWIZZLE_NONE, 2)) return rc;
   if (int rc = dp_nhwc_map(&maps.y, y, pw->y_coff + p.nout, pw->y_ctotal, p.w, p.h, p.n, kDpTW, kDpTH, p.nout, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
   if (int rc = dp_weight_map(&maps.w, w_pw_bf16, p.c, p.nout, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return rc;
   const unsigned grid = (unsigned)std::min<int64_t>(tiles, num_sms());
