@@ -199,6 +199,19 @@ __global__ void __launch_bounds__(kDpThreads, 1) dwpw_tc_kernel(const __grid_con
 #pragma unroll
         for (int u = 0; u < 16; ++u)
           rres[u] = (inside && u * 8 < p.nout) ? __ldg(reinterpret_cast<const uint4 *>(rp + u * 8)) : make_uint4(0u, 0u, 0u, 0u);
+        // ... and the NEXT tile's row is pulled into L2 now: when the epilogue is the slowest stage the accumulator
+        // is ready at once and the loads above would wait a full DRAM latency per tile (ncu: the residual unpack held
+        // 8 % of the stall samples)
+        if (j + 1 < n_my) {
+          int w1, h1, img1;
+          tile_coords(j + 1, w1, h1, img1);
+          const int ny = h1 + ty, nx = w1 + tx;
+          if (ny < p.h && nx < p.w) {
+            const __nv_bfloat16 *np = res + (((int64_t)img1 * p.h + ny) * p.w + nx) * p.r_ct + p.r_coff;
+            for (int b = 0; b < p.nout * 2; b += 128)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(np) + b));
+          }
+        }
       }
       mbar_wait_relaxed(t_full + 8 * acc, use & 1u, dead);
       tc_fence_after();
