@@ -366,6 +366,17 @@ int rtseg_avgpool2d(int32_t n, int32_t h, int32_t w, int32_t c, int32_t k, int32
  * over the map (h, w multiples of 4); y1 / y2 / y4 / y6: dense NHWC [n][p][p][c] in `dtype`. */
 int rtseg_pyramid_avgpool(int32_t n, int32_t h, int32_t w, int32_t c, int32_t dtype, const void *x, int32_t x_ctotal,
                           int32_t x_coff, void *y1, void *y2, void *y4, void *y6, rtseg_stream_t stream);
+/* The four branches of PyramidPoolingModule behind the pooling, reference
+ * models/modules.py:145-156: conv1x1 (no BatchNorm, optional bias) of the 1x1 /
+ * 2x2 / 4x4 / 6x6 pooled maps y1..y6 (bf16 NHWC, c channels, as written by
+ * rtseg_pyramid_avgpool) and F.interpolate(..., (h, w), bilinear,
+ * align_corners=True) of each result, written to channels [y_coff + b*hid,
+ * +hid) of the NHWC concat buffer `cat` (torch.cat, modules.py:156).
+ * weights: fp32 [4][hid][c] (rounded to bf16 in the kernel, like the tensor-core
+ * convolutions it replaces), bias: fp32 [4][hid] or NULL. */
+int rtseg_ppm_branches(int32_t n, int32_t h, int32_t w, int32_t c, int32_t hid, int32_t dtype, const void *y1,
+                       const void *y2, const void *y4, const void *y6, const float *weights, const float *bias,
+                       void *cat, int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream);
 
 /* ---- training-mode pieces ---------------------------------------------
  * In training the reference's ConvBNAct is Conv2d -> BatchNorm2d(batch statistics) -> activation

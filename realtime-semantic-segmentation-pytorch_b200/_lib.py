@@ -111,6 +111,7 @@ PROTOTYPES = {
     "rtseg_dwpw_tc": (c_i32, [_DP, c_vp, c_vp, c_vp, c_vp, _DP, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "rtseg_maxunpool2x2_bwd": (c_i32, [c_i32] * 7 + [c_vp, c_vp, c_vp, c_vp]),
     "rtseg_pyramid_avgpool": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "rtseg_ppm_branches": (c_i32, [c_i32] * 6 + [c_vp] * 7 + [c_i32, c_i32, c_vp]),
     "rtseg_opt_chunk_elems": (c_i32, []),
     "rtseg_sgd_ema_step": (c_i32, [c_vp, c_i32, c_vp, c_i32, c_vp]),
     "rtseg_maxpool3x3s2_bwd": (c_i32, [c_i32] * 5 + [c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),

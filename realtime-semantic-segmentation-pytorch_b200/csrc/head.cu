@@ -154,14 +154,15 @@ __device__ __forceinline__ void hist_add_aggregated(int *hist, int bin, bool val
 // and infinities (inf - inf in D, inf + -inf in A + ly1*D would turn into NaNs torch does not produce) are detected
 // when a source row is loaded; such threads evaluate torch's own expression ly0*(lx0*p00 + lx1*p01) + ly1*(...)
 // straight from memory.  Padded channels hold -inf and the compare is strict, so the label never leaves [0, c).
-template <typename T, int CMAX, bool EXACT = false>   // EXACT: c == CMAX, no padded classes to mask
+template <typename T, int CMAX, bool EXACT = false, bool PLAIN = false>   // EXACT: c == CMAX, no padded classes to mask;
+                                                                          // PLAIN: uint8 class map only (no int64 map, no confusion matrix)
 __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
     int n, int hi, int wi, int c, int ct, int ho, int wo, int align, float sy, float sx, const T *__restrict__ x,
     uint8_t *__restrict__ lab8, int64_t *__restrict__ lab64, const int64_t *__restrict__ target, int ignore_index,
     unsigned long long *__restrict__ confmat, int vec) {
   __shared__ int hist[kMaxBins];
   __shared__ int4 s_rows[kHeadRows];   // per output row of this block: {y0, y1, bits(ly0), bits(ly1)} (the same for every column)
-  const bool do_cm = target != nullptr;
+  const bool do_cm = !PLAIN && target != nullptr;
   if (do_cm) {
     for (int i = threadIdx.x; i < c * c; i += blockDim.x) hist[i] = 0;
   }
@@ -269,8 +270,8 @@ __global__ void __launch_bounds__(kHeadThreads) upsample_argmax_kernel(
           if (k == 0) best = v; else argmax_step(v, k, best, label);
         }
       }
-      if (lab8) lab8[opix] = (uint8_t)label;
-      if (lab64) lab64[opix] = (int64_t)label;
+      if (PLAIN || lab8) lab8[opix] = (uint8_t)label;
+      if (!PLAIN && lab64) lab64[opix] = (int64_t)label;
     }
     if (do_cm && col_ok) {
       // a thread walks one image column: consecutive rows mostly fall into the same (target, prediction) bin, so
@@ -553,6 +554,91 @@ __global__ void __launch_bounds__(256) pyramid_pool_kernel(int h, int w, int c, 
   }
 }
 
+// ------------------------------------------------- pyramid branches: 1x1 conv + bilinear resize + concat ----
+// The four branches of PyramidPoolingModule behind the pooling (reference models/modules.py:145-156): conv1x1 of the
+// 1x1 / 2x2 / 4x4 / 6x6 pooled maps (57 pixels in all) and the align_corners=True resize of each result to h x w, written
+// into its channel slice of the concat buffer.  As eight launches (four tensor-core convolutions on 1-36 pixels, four
+// resizes) this was latency only; here a block recomputes the 57 x hid conv outputs of its image into shared memory
+// (bf16 inputs and bf16-rounded weights, fp32 accumulate, result rounded to bf16 like the stored tensor it replaces)
+// and resizes its share of the output pixels, 16-byte channel vectors.
+constexpr int kPpmPix = 1 + 4 + 16 + 36;
+__global__ void __launch_bounds__(256) ppm_branches_kernel(int h, int w, int c, int hid, const __nv_bfloat16 *__restrict__ y1,
+                                                           const __nv_bfloat16 *__restrict__ y2,
+                                                           const __nv_bfloat16 *__restrict__ y4,
+                                                           const __nv_bfloat16 *__restrict__ y6,
+                                                           const float *__restrict__ wgt, const float *__restrict__ bias,
+                                                           __nv_bfloat16 *__restrict__ cat, int y_ct, int y_co) {
+  // shared memory: z [57][hid] fp32 | pooled inputs [57][c] bf16 | bf16-rounded weights [4 * hid][c + 8] (rows padded by
+  // 16 bytes: a quarter warp's eight rows then cover 128 contiguous bank bytes).  Every output re-reading its weight row
+  // from L2 made the first version slower than the eight launches it replaced.
+  extern __shared__ __align__(16) unsigned char ppm_smem[];
+  float *ppm_z = reinterpret_cast<float *>(ppm_smem);
+  __nv_bfloat16 *sx = reinterpret_cast<__nv_bfloat16 *>(ppm_smem + (size_t)kPpmPix * hid * 4);
+  __nv_bfloat16 *sw = sx + (size_t)kPpmPix * c;
+  const int wp = c + 8;
+  const int b = blockIdx.x;
+  const int psz[4] = {1, 2, 4, 6}, pbase[4] = {0, 1, 5, 21};
+  const __nv_bfloat16 *src[4] = {y1 + (int64_t)b * c, y2 + (int64_t)b * 4 * c, y4 + (int64_t)b * 16 * c, y6 + (int64_t)b * 36 * c};
+  for (int br = 0; br < 4; ++br) {
+    const int nv = psz[br] * psz[br] * c / 8;
+    const uint4 *g = reinterpret_cast<const uint4 *>(src[br]);
+    uint4 *d = reinterpret_cast<uint4 *>(sx + (size_t)pbase[br] * c);
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) d[i] = __ldg(g + i);
+  }
+  for (int i = threadIdx.x; i < 4 * hid * c / 4; i += blockDim.x) {
+    const float4 f = __ldg(reinterpret_cast<const float4 *>(wgt) + i);
+    const int row = (i * 4) / c, col = (i * 4) - row * c;
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(f.x, f.y), hi = __floats2bfloat162_rn(f.z, f.w);
+    *reinterpret_cast<uint2 *>(sw + (size_t)row * wp + col) =
+        make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < kPpmPix * hid; o += blockDim.x) {
+    const int pix = o / hid, k = o - pix * hid;
+    const int br = pix >= 21 ? 3 : (pix >= 5 ? 2 : (pix >= 1 ? 1 : 0));
+    const uint4 *xp = reinterpret_cast<const uint4 *>(sx + (size_t)pix * c);
+    const uint4 *wr = reinterpret_cast<const uint4 *>(sw + (size_t)(br * hid + k) * wp);
+    float acc = 0.f;
+    for (int i = 0; i < c / 8; ++i) {
+      const uint4 q = xp[i], wq = wr[i];
+      const uint32_t qs[4] = {q.x, q.y, q.z, q.w}, ws[4] = {wq.x, wq.y, wq.z, wq.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        acc = fmaf(__uint_as_float(qs[e] << 16), __uint_as_float(ws[e] << 16), acc);
+        acc = fmaf(__uint_as_float(qs[e] & 0xffff0000u), __uint_as_float(ws[e] & 0xffff0000u), acc);
+      }
+    }
+    if (bias) acc += bias[br * hid + k];
+    ppm_z[o] = __bfloat162float(__float2bfloat16_rn(acc));
+  }
+  __syncthreads();
+  const int vec_per_pix = 4 * hid / 8;                       // 16-byte vectors of one output pixel (all four branches)
+  const int per_blk = (h * w + gridDim.y - 1) / gridDim.y;
+  const int p0 = blockIdx.y * per_blk, p1 = min(h * w, p0 + per_blk);
+  for (int t = p0 * vec_per_pix + threadIdx.x; t < p1 * vec_per_pix; t += blockDim.x) {
+    const int pix = t / vec_per_pix, v = t - pix * vec_per_pix;
+    const int oy = pix / w, ox = pix - oy * w;
+    const int br = (v * 8) / hid, k0 = v * 8 - br * hid;
+    const int ps = psz[br];
+    int ya, yb, xa, xb;
+    float ly0, ly1, lx0, lx1;
+    src_index(oy, resize_scale(ps, h, 1), ps, 1, ya, yb, ly0, ly1);
+    src_index(ox, resize_scale(ps, w, 1), ps, 1, xa, xb, lx0, lx1);
+    const float *z = ppm_z + (int64_t)pbase[br] * hid + k0;
+    const float *z00 = z + (ya * ps + xa) * hid, *z01 = z + (ya * ps + xb) * hid;
+    const float *z10 = z + (yb * ps + xa) * hid, *z11 = z + (yb * ps + xb) * hid;
+    uint32_t pk[4];
+#pragma unroll
+    for (int e = 0; e < 8; e += 2) {
+      const float o0 = ly0 * (lx0 * z00[e] + lx1 * z01[e]) + ly1 * (lx0 * z10[e] + lx1 * z11[e]);
+      const float o1 = ly0 * (lx0 * z00[e + 1] + lx1 * z01[e + 1]) + ly1 * (lx0 * z10[e + 1] + lx1 * z11[e + 1]);
+      const __nv_bfloat162 hh = __floats2bfloat162_rn(o0, o1);
+      pk[e >> 1] = *reinterpret_cast<const uint32_t *>(&hh);
+    }
+    *reinterpret_cast<uint4 *>(cat + ((int64_t)b * h * w + pix) * y_ct + y_co + v * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+  }
+}
+
 // ------------------------------------------------- avg-pool 3x3 s2 p1, channel shuffle ----
 // F.avg_pool2d(x, 3, 2, 1) of DABNet's input pyramid (reference models/dabnet.py:32-34): padding counts
 // (count_include_pad=True, the default), i.e. always divide by 9.  Input strides are explicit so that the
@@ -740,8 +826,12 @@ static int launch_upsample_argmax(int n, int hi, int wi, int c, int ct, int ho, 
   }
   if (c == 19) {  // Cityscapes: exact instantiation, no padded classes
     const int vec = sizeof(T) == 2 && ct % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 && 24 <= ct;
-    upsample_argmax_kernel<T, 19, true><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
-                                                                 target, ignore, cm, vec);
+    if (l8 && !l64 && !target)
+      upsample_argmax_kernel<T, 19, true, true><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8,
+                                                                               l64, target, ignore, cm, vec);
+    else
+      upsample_argmax_kernel<T, 19, true><<<grid, kHeadThreads, 0, st>>>(n, hi, wi, c, ct, ho, wo, align, sy, sx, xs, l8, l64,
+                                                                         target, ignore, cm, vec);
     RTSEG_LAUNCH_CHECK("upsample_argmax_kernel");
     return RTSEG_OK;
   }
@@ -898,6 +988,37 @@ extern "C" int rtseg_pyramid_avgpool(int32_t n, int32_t h, int32_t w, int32_t c,
   else
     RTSEG_FAIL(RTSEG_ERR_INVALID, "unknown dtype");
   RTSEG_LAUNCH_CHECK("pyramid_pool_kernel");
+  return RTSEG_OK;
+}
+
+extern "C" int rtseg_ppm_branches(int32_t n, int32_t h, int32_t w, int32_t c, int32_t hid, int32_t dtype, const void *y1,
+                                  const void *y2, const void *y4, const void *y6, const float *weights, const float *bias,
+                                  void *cat, int32_t y_ctotal, int32_t y_coff, rtseg_stream_t stream) {
+  RTSEG_REQUIRE(y1 && y2 && y4 && y6 && weights && cat, "NULL pointer");
+  RTSEG_REQUIRE(dtype == RTSEG_BF16, "rtseg_ppm_branches: bf16 activations only");
+  RTSEG_REQUIRE(n > 0 && h > 1 && w > 1 && c > 0 && hid > 0 && n <= 65535, "bad extent");
+  RTSEG_REQUIRE(c % 8 == 0 && hid % 8 == 0, "rtseg_ppm_branches: c and hid must be multiples of 8");
+  RTSEG_REQUIRE(y_coff >= 0 && y_coff % 8 == 0 && y_ctotal % 8 == 0 && y_coff + 4 * hid <= y_ctotal, "channel slice outside its buffer or unaligned");
+  RTSEG_REQUIRE(reinterpret_cast<uintptr_t>(cat) % 16 == 0 && reinterpret_cast<uintptr_t>(weights) % 16 == 0 &&
+                    reinterpret_cast<uintptr_t>(y1) % 16 == 0 && reinterpret_cast<uintptr_t>(y2) % 16 == 0 &&
+                    reinterpret_cast<uintptr_t>(y4) % 16 == 0 && reinterpret_cast<uintptr_t>(y6) % 16 == 0,
+                "pointers must be 16-byte aligned");
+  const size_t smem = (size_t)kPpmPix * hid * sizeof(float) + (size_t)kPpmPix * c * 2 + (size_t)4 * hid * (c + 8) * 2;
+  RTSEG_REQUIRE(smem <= 200 * 1024, "rtseg_ppm_branches: c x hid too large for the shared-memory plan");
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  RTSEG_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    RTSEG_CUDA(cudaFuncSetAttribute(ppm_branches_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set[dev] = true;
+  }
+  // blocks per image: each recomputes the 57 x hid conv outputs, so few of them — but enough to fill the GPU
+  const int split = std::max(1, std::min((int)cdiv((int64_t)h * w, 256), (int)cdiv(2 * num_sms(), n)));
+  dim3 grid((unsigned)n, (unsigned)std::min(split, 16));
+  ppm_branches_kernel<<<grid, 256, smem, as_stream(stream)>>>(h, w, c, hid, (const __nv_bfloat16 *)y1, (const __nv_bfloat16 *)y2,
+                                                              (const __nv_bfloat16 *)y4, (const __nv_bfloat16 *)y6, weights, bias,
+                                                              (__nv_bfloat16 *)cat, y_ctotal, y_coff);
+  RTSEG_LAUNCH_CHECK("ppm_branches_kernel");
   return RTSEG_OK;
 }
 

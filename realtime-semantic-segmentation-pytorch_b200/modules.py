@@ -328,6 +328,21 @@ class PyramidPoolingModule(nn.Module):
         c = self.stage1[1].in_channels
         return ops.empty_nhwc(n, c + 4 * self.stage1[1].out_channels, h, w, like.dtype, like.device)
 
+    def _stacked_branch_weights(self, convs):
+        """fp32 [4, hid, c] (+ [4, hid] bias) of the four branch convolutions, rebuilt when a weight changes."""
+        key = tuple((cv.weight.data_ptr(), cv.weight._version, None if cv.bias is None else cv.bias._version) for cv in convs)
+        cached = getattr(self, "_branch_cache", None)
+        if cached is None or cached[0] != key:
+            with torch.no_grad():
+                wts = torch.stack([cv.weight.detach().float().reshape(cv.out_channels, cv.in_channels) for cv in convs]).contiguous()
+                bias = None
+                if any(cv.bias is not None for cv in convs):
+                    bias = torch.stack([cv.bias.detach().float() if cv.bias is not None else
+                                        torch.zeros(cv.out_channels, device=wts.device) for cv in convs]).contiguous()
+            cached = (key, wts, bias)
+            self._branch_cache = cached
+        return cached[1], cached[2]
+
     def forward(self, x, cat=None):
         """cat: a concat_buffer() whose first channels already hold x (then `x` is ignored)."""
         if cat is not None:
@@ -338,6 +353,13 @@ class PyramidPoolingModule(nn.Module):
             sizes = [int(st[0].output_size if isinstance(st[0].output_size, int) else st[0].output_size[0]) for st in stages]
             if sizes == [1, 2, 4, 6] and h % 4 == 0 and w % 4 == 0:
                 pooled = ops.pyramid_avgpool(cat, 0, c)
+                convs = [st[1] for st in stages]
+                if (ops.USE_PPM_FUSION and cat.dtype == torch.bfloat16 and c % 8 == 0 and hid % 8 == 0 and hid <= 192 and
+                        all(type(cv) is Conv2d and cv.kernel_size == (1, 1) and cv.stride == (1, 1) and cv.groups == 1
+                            and cv.out_channels == hid for cv in convs)):
+                    wts, bias = self._stacked_branch_weights(convs)
+                    ops.ppm_branches(pooled, wts, bias, cat, c)      # four conv1x1 + resize branches, one launch
+                    return self.conv(cat)
             else:
                 pooled = [ops.adaptive_avgpool(cat, p, 0, c) for p in sizes]
             for i, st in enumerate(stages):

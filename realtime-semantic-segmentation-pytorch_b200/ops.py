@@ -8,6 +8,7 @@ channel slice of a wider NHWC buffer is passed as (buffer, c_offset, channels).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Optional, Tuple
 
@@ -717,6 +718,31 @@ def pyramid_avgpool(x: torch.Tensor, x_coff: int = 0, c: Optional[int] = None):
     _lib.check(_lib.load().rtseg_pyramid_avgpool(n, h, w, c, _dtype_code(x.dtype), x.data_ptr(), x_ct, x_coff,
                                                  *[o.data_ptr() for o in outs], _stream()), "rtseg_pyramid_avgpool")
     return outs
+
+
+USE_PPM_FUSION = os.environ.get("RTSEG_PPM_FUSION", "1") != "0"   # module-level switch (tests / A-B runs): the pyramid's four conv1x1 + resize branches in one launch
+
+
+def ppm_branches(pooled, weights: torch.Tensor, bias: Optional[torch.Tensor], cat: torch.Tensor, y_coff: int) -> torch.Tensor:
+    """conv1x1 + bilinear resize (align_corners=True) of the four pooled maps of PyramidPoolingModule into channels
+    [y_coff, y_coff + 4 * hid) of the NHWC concat buffer `cat` (reference models/modules.py:145-156) — one launch.
+
+    pooled: the four tensors of pyramid_avgpool(); weights: fp32 [4, hid, c]; bias: fp32 [4, hid] or None."""
+    _require_cuda(cat, "ppm_branches")
+    _no_tape(cat, "ppm_branches")
+    n, y_ct, h, w = cat.shape
+    c = pooled[0].shape[1]
+    hid = weights.shape[1]
+    if cat.dtype != torch.bfloat16 or any(t.dtype != torch.bfloat16 for t in pooled):
+        raise TypeError("ppm_branches: bf16 activations only")
+    if weights.dtype != torch.float32 or not weights.is_contiguous() or tuple(weights.shape) != (4, hid, c):
+        raise ValueError("ppm_branches: weights must be contiguous fp32 [4, hid, c]")
+    if [tuple(t.shape) for t in pooled] != [(n, c, p, p) for p in (1, 2, 4, 6)]:
+        raise ValueError("ppm_branches: pooled maps must be [n, c, p, p] for p = 1, 2, 4, 6")
+    _lib.check(_lib.load().rtseg_ppm_branches(n, h, w, c, hid, _dtype_code(cat.dtype), *[t.data_ptr() for t in pooled],
+                                              weights.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                              cat.data_ptr(), y_ct, y_coff, _stream()), "rtseg_ppm_branches")
+    return cat
 
 
 CITYSCAPES_COLORMAP = [(128, 64, 128), (244, 35, 232), (70, 70, 70), (102, 102, 156), (190, 153, 153), (153, 153, 153),

@@ -592,6 +592,36 @@ def test_pyramid_avgpool_matches_four_adaptive_pools(c, h, w, ct, coff, dtype):
         assert tuple(o.shape) == (2, c, p, p) and rel_err(o, ref) < tol and torch.equal(o, o2)
 
 
+@pytest.mark.parametrize("n,c,hid,h,w,ct", [(2, 128, 32, 32, 64, 256), (1, 64, 16, 8, 12, 128), (3, 32, 8, 4, 4, 64)])
+def test_ppm_branches_match_conv_and_resize(n, c, hid, h, w, ct):
+    """conv1x1 + F.interpolate(bilinear, align_corners=True) of the four pooled maps into the concat buffer in ONE launch
+    (PyramidPoolingModule, reference models/modules.py:145-156): against torch on the bf16-rounded operands, and against
+    the unfused rtseg path (tensor-core conv1x1 + resize kernel per branch) through the module."""
+    from rtseg_b200 import modules, ops
+    x = seeded((n, c, h, w), 71).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    pooled = ops.pyramid_avgpool(x, 0, c)
+    wts = (seeded((4, hid, c), 72) * 0.2).cuda().contiguous()
+    bias = seeded((4, hid), 73).cuda().contiguous()
+    cat = torch.full((n, ct, h, w), 7.0, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ops.ppm_branches(pooled, wts, bias, cat, ct - 4 * hid)
+    assert torch.all(cat[:, :ct - 4 * hid] == 7.0)                       # channels outside the slice untouched
+    for b, p in enumerate((1, 2, 4, 6)):
+        z = F.conv2d(pooled[b].float(), wts[b].to(torch.bfloat16).float()[:, :, None, None], bias[b])
+        ref = F.interpolate(z.to(torch.bfloat16).float(), (h, w), mode="bilinear", align_corners=True)
+        got = cat[:, ct - 4 * hid + b * hid: ct - 4 * hid + (b + 1) * hid].float()
+        assert rel_err(got, ref) < TOL_BF16, (b, rel_err(got, ref))
+    if c == 128:   # the module, fused against unfused
+        m = _randomise(modules.PyramidPoolingModule(c, c, "relu"), 74).eval().cuda()
+        with torch.no_grad():
+            fused = m(x)
+            ops.USE_PPM_FUSION = False
+            try:
+                plain = m(x)
+            finally:
+                ops.USE_PPM_FUSION = True
+        assert rel_err(fused, plain) < TOL_BF16
+
+
 # --------------------------------------------------- DABNet / LEDNet building blocks ----
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("shape", [(2, 3, 32, 64), (1, 3, 17, 33), (1, 8, 9, 7)])
