@@ -329,19 +329,19 @@ class PyramidPoolingModule(nn.Module):
         return ops.empty_nhwc(n, c + 4 * self.stage1[1].out_channels, h, w, like.dtype, like.device)
 
     def _stacked_branch_weights(self, convs):
-        """fp32 [4, hid, c] (+ [4, hid] bias) of the four branch convolutions, rebuilt when a weight changes."""
-        key = tuple((cv.weight.data_ptr(), cv.weight._version, None if cv.bias is None else cv.bias._version) for cv in convs)
-        cached = getattr(self, "_branch_cache", None)
-        if cached is None or cached[0] != key:
+        """fp32 [4, hid, c] (+ [4, hid] bias) of the four branch convolutions; rebuilt when a weight changes (_FoldCache)."""
+        cache = self.__dict__.setdefault("_branch_cache", _FoldCache())
+
+        def build():
             with torch.no_grad():
                 wts = torch.stack([cv.weight.detach().float().reshape(cv.out_channels, cv.in_channels) for cv in convs]).contiguous()
                 bias = None
                 if any(cv.bias is not None for cv in convs):
                     bias = torch.stack([cv.bias.detach().float() if cv.bias is not None else
                                         torch.zeros(cv.out_channels, device=wts.device) for cv in convs]).contiguous()
-            cached = (key, wts, bias)
-            self._branch_cache = cached
-        return cached[1], cached[2]
+            return wts, bias
+
+        return cache.get([cv.weight for cv in convs] + [cv.bias for cv in convs], build)
 
     def forward(self, x, cat=None):
         """cat: a concat_buffer() whose first channels already hold x (then `x` is ignored)."""
