@@ -287,3 +287,28 @@ def test_deferred_logits_routes_max_to_the_fused_head(monkeypatch):
     # the mode only defers CUDA tensors: on the CPU F.interpolate stays itself
     with cv.fused_head():
         assert not isinstance(F.interpolate(low, (16, 24), mode="bilinear", align_corners=True), cv.DeferredLogits)
+
+
+def test_pyramid_branch_weights_are_stacked_once_and_follow_the_parameters():
+    """PyramidPoolingModule (reference models/modules.py:134-158): the one-launch branch kernel reads the four conv1x1
+    weights as ONE fp32 [4, hid, c] tensor; the stack is cached on parameter versions (like the folded convolutions) and
+    never enters state_dict."""
+    import copy
+    import torch
+    from rtseg_b200 import modules
+    m = modules.PyramidPoolingModule(16, 16, "relu")
+    convs = [m.stage1[1], m.stage2[1], m.stage3[1], m.stage4[1]]
+    w, b = m._stacked_branch_weights(convs)
+    assert tuple(w.shape) == (4, 4, 16) and w.dtype == torch.float32 and w.is_contiguous() and b is None
+    for i, cv in enumerate(convs):
+        assert torch.equal(w[i], cv.weight.detach().reshape(4, 16))
+    assert m._stacked_branch_weights(convs)[0] is w                      # cached
+    with torch.no_grad():
+        convs[2].weight.mul_(2.0)                                         # in-place update bumps the version
+    w2, _ = m._stacked_branch_weights(convs)
+    assert w2 is not w and torch.equal(w2[2], convs[2].weight.detach().reshape(4, 16))
+    assert all("_branch" not in k for k in m.state_dict())
+    sd = {k: (torch.randn_like(v) if v.is_floating_point() else v.clone()) for k, v in m.state_dict().items()}
+    m.load_state_dict(sd)
+    assert torch.equal(m._stacked_branch_weights(convs)[0][0], sd["stage1.1.weight"].reshape(4, 16))
+    copy.deepcopy(m)                                                       # the cache does not break module copies
