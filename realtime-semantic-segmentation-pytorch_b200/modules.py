@@ -354,7 +354,9 @@ class PyramidPoolingModule(nn.Module):
             if sizes == [1, 2, 4, 6] and h % 4 == 0 and w % 4 == 0:
                 pooled = ops.pyramid_avgpool(cat, 0, c)
                 convs = [st[1] for st in stages]
-                if (ops.USE_PPM_FUSION and cat.dtype == torch.bfloat16 and c % 8 == 0 and hid % 8 == 0 and hid <= 192 and
+                # the one-launch kernel keeps the 57 pooled pixels, the four weight matrices and its results in shared memory
+                fits = 57 * hid * 4 + 57 * c * 2 + 4 * hid * (c + 8) * 2 <= 200 * 1024
+                if (ops.USE_PPM_FUSION and cat.dtype == torch.bfloat16 and c % 8 == 0 and hid % 8 == 0 and fits and
                         all(type(cv) is Conv2d and cv.kernel_size == (1, 1) and cv.stride == (1, 1) and cv.groups == 1
                             and cv.out_channels == hid for cv in convs)):
                     wts, bias = self._stacked_branch_weights(convs)
