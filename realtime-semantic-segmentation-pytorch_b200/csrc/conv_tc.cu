@@ -1401,7 +1401,8 @@ static int plan_forward(const rtseg_conv_desc *d, bool staged, const float *slop
   // N = 64: 0.40 -> 0.22 ms at 16 x 128 x 256 (BiSeNetv2 7.78 -> 6.94 ms, DDRNet 4.85 -> 4.60 ms per step).  Only taken
   // when it widens the N tile and no residual rides the ring.
   static const int unstage_knob = getenv("RTSEG_TC_UNSTAGE") ? atoi(getenv("RTSEG_TC_UNSTAGE")) : 1;
-  if (unstage_knob && may_unstage && staged && pl.n_tiles > 1 && ntaps > 3 && d->res_mode == RTSEG_RES_NONE) {
+  if (unstage_knob && may_unstage && staged && pl.n_tiles > 1 && ntaps > 3 && d->res_mode == RTSEG_RES_NONE &&
+      d->cout % 16 == 0) {   // (whole 16-channel chunks: the fast epilogue's direct stores are 16-byte vectors)
     TcPlan alt;
     bool ok = plan_tc(d->cin, cout_pad, ntaps, 1, false, max_stack(p.n, p.gh, p.gw, share), false, alt, share, halo, false);
     if (!ok) ok = plan_tc(d->cin, cout_pad, ntaps, 1, false, max_stack(p.n, p.gh, p.gw), false, alt, 0, 0, false);
